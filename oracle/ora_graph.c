@@ -1,0 +1,511 @@
+/*
+ * ora_graph.c -- CPU restatement of graph.go's layer search and insertion.  TEST INFRASTRUCTURE ONLY
+ * (see hnsw_oracle.h).  Citations are file:line into the reference tree.
+ *
+ * Storage differs from the reference on purpose (rows instead of pointers/maps); behaviour does not:
+ *   - a node is a row id (int32, insertion order); key[row] is the reference's K (int64 here);
+ *   - a node inserted with level L is a member of layers 0..L (graph.go:510-515);
+ *   - layer-0 neighbour lists live in adj0[row*(M+1)..], upper layers in adjU[(upper_off[row]+l-1)*(M+1)..];
+ *   - every neighbour list is kept sorted by key, which is both the order the reference sorts into before
+ *     expanding (graph.go:137-138) and the documented stand-in for Go's random map iteration order.
+ */
+#define _GNU_SOURCE
+#include <math.h>
+#include <pthread.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "hnsw_oracle.h"
+
+struct ora_graph {
+  int dim, M, metric, flavor, stride; /* stride = M+1 slots per list */
+  int64_t n, cap;
+  float *vec;
+  int64_t *key;
+  int32_t *level;
+  int32_t *adj0;
+  int32_t *deg0;
+  int32_t *upper_off;
+  int32_t *adjU;
+  int32_t *degU;
+  int64_t nU, capU;
+  int n_layers;
+  int32_t entry[ORA_MAX_LAYERS];
+  int64_t layer_size[ORA_MAX_LAYERS];
+  /* visited stamps for the single-threaded paths */
+  uint32_t *stamp;
+  uint32_t epoch;
+  ora_counters ctr;
+};
+
+typedef struct {
+  uint32_t *stamp;
+  uint32_t epoch;
+  int64_t cap;
+} visited_t;
+
+ora_graph *ora_graph_new(int dim, int M, int metric, int flavor) {
+  ora_graph *g = (ora_graph *)calloc(1, sizeof *g);
+  g->dim = dim;
+  g->M = M;
+  g->metric = metric;
+  g->flavor = flavor;
+  g->stride = M + 1;
+  for (int i = 0; i < ORA_MAX_LAYERS; i++) g->entry[i] = -1;
+  return g;
+}
+void ora_graph_free(ora_graph *g) {
+  if (!g) return;
+  free(g->vec);
+  free(g->key);
+  free(g->level);
+  free(g->adj0);
+  free(g->deg0);
+  free(g->upper_off);
+  free(g->adjU);
+  free(g->degU);
+  free(g->stamp);
+  free(g);
+}
+int64_t ora_graph_len(const ora_graph *g) { return g->n_layers ? g->layer_size[0] : 0; } /* graph.go:829-838 */
+int ora_graph_layers(const ora_graph *g) { return g->n_layers; }
+int ora_graph_M(const ora_graph *g) { return g->M; }
+int ora_graph_metric(const ora_graph *g) { return g->metric; }
+int ora_graph_dim(const ora_graph *g) { return g->dim; }
+int64_t ora_graph_layer_size(const ora_graph *g, int l) { return (l >= 0 && l < g->n_layers) ? g->layer_size[l] : 0; }
+int32_t ora_graph_entry(const ora_graph *g, int l) { return (l >= 0 && l < g->n_layers) ? g->entry[l] : -1; }
+void ora_graph_set_entry(ora_graph *g, int l, int32_t row) {
+  if (l >= 0 && l < ORA_MAX_LAYERS) g->entry[l] = row;
+}
+int ora_graph_level(const ora_graph *g, int32_t row) { return g->level[row]; }
+int64_t ora_graph_key(const ora_graph *g, int32_t row) { return g->key[row]; }
+const float *ora_graph_vector(const ora_graph *g, int32_t row) { return g->vec + (size_t)row * g->dim; }
+void ora_graph_counters(const ora_graph *g, ora_counters *out) { *out = g->ctr; }
+void ora_graph_reset_counters(ora_graph *g) { memset(&g->ctr, 0, sizeof g->ctr); }
+
+static inline int32_t *list_ptr(const ora_graph *g, int layer, int32_t row, int32_t **deg) {
+  if (layer == 0) {
+    *deg = &g->deg0[row];
+    return g->adj0 + (size_t)row * g->stride;
+  }
+  if (g->level[row] < layer) {
+    *deg = NULL;
+    return NULL;
+  }
+  int64_t slot = (int64_t)g->upper_off[row] + (layer - 1);
+  *deg = &g->degU[slot];
+  return g->adjU + (size_t)slot * g->stride;
+}
+
+int ora_graph_neighbors(const ora_graph *g, int layer, int32_t row, int32_t *out) {
+  int32_t *deg;
+  int32_t *l = list_ptr(g, layer, row, &deg);
+  if (!l) return -1;
+  memcpy(out, l, sizeof(int32_t) * (size_t)*deg);
+  return *deg;
+}
+
+static void grow_rows(ora_graph *g) {
+  int64_t cap = g->cap ? g->cap * 2 : 1024;
+  g->vec = (float *)realloc(g->vec, sizeof(float) * (size_t)cap * g->dim);
+  g->key = (int64_t *)realloc(g->key, sizeof(int64_t) * (size_t)cap);
+  g->level = (int32_t *)realloc(g->level, sizeof(int32_t) * (size_t)cap);
+  g->adj0 = (int32_t *)realloc(g->adj0, sizeof(int32_t) * (size_t)cap * g->stride);
+  g->deg0 = (int32_t *)realloc(g->deg0, sizeof(int32_t) * (size_t)cap);
+  g->upper_off = (int32_t *)realloc(g->upper_off, sizeof(int32_t) * (size_t)cap);
+  g->stamp = (uint32_t *)realloc(g->stamp, sizeof(uint32_t) * (size_t)cap);
+  memset(g->stamp + g->cap, 0, sizeof(uint32_t) * (size_t)(cap - g->cap));
+  g->cap = cap;
+}
+
+/* append storage for a node that will be a member of layers 0..level; no links, no layer bookkeeping */
+static int32_t new_row(ora_graph *g, int64_t key, const float *vec, int level) {
+  if (g->n == g->cap) grow_rows(g);
+  int32_t row = (int32_t)g->n++;
+  memcpy(g->vec + (size_t)row * g->dim, vec, sizeof(float) * (size_t)g->dim);
+  g->key[row] = key;
+  g->level[row] = level;
+  g->deg0[row] = 0;
+  g->upper_off[row] = -1;
+  if (level > 0) {
+    while (g->nU + level > g->capU) {
+      int64_t cap = g->capU ? g->capU * 2 : 1024;
+      g->adjU = (int32_t *)realloc(g->adjU, sizeof(int32_t) * (size_t)cap * g->stride);
+      g->degU = (int32_t *)realloc(g->degU, sizeof(int32_t) * (size_t)cap);
+      g->capU = cap;
+    }
+    g->upper_off[row] = (int32_t)g->nU;
+    for (int l = 0; l < level; l++) g->degU[g->nU + l] = 0;
+    g->nU += level;
+  }
+  return row;
+}
+
+/* ---- sorted-by-key list primitives (Go: map insert / delete on layerNode.neighbors) --------- */
+static int list_find(const ora_graph *g, const int32_t *l, int deg, int32_t row) {
+  for (int i = 0; i < deg; i++)
+    if (l[i] == row) return i;
+  (void)g;
+  return -1;
+}
+static void list_insert(const ora_graph *g, int32_t *l, int32_t *deg, int32_t row) {
+  if (list_find(g, l, *deg, row) >= 0) return; /* map overwrite: length unchanged */
+  int i = *deg;
+  int64_t k = g->key[row];
+  while (i > 0 && g->key[l[i - 1]] > k) {
+    l[i] = l[i - 1];
+    i--;
+  }
+  l[i] = row;
+  (*deg)++;
+}
+static void list_delete(const ora_graph *g, int32_t *l, int32_t *deg, int32_t row) {
+  int i = list_find(g, l, *deg, row);
+  if (i < 0) return;
+  for (; i + 1 < *deg; i++) l[i] = l[i + 1];
+  (*deg)--;
+}
+
+static inline float gdist(const ora_graph *g, int metric, int32_t a, const float *b) {
+  return ora_distance(metric, g->flavor, g->vec + (size_t)a * g->dim, b, g->dim);
+}
+
+static void replenish(ora_graph *g, int layer, int32_t n, int m);
+
+/* layerNode.addNeighbor -- graph.go:41-81 */
+static void add_neighbor(ora_graph *g, int layer, int32_t n, int32_t newn, int m, int metric) {
+  int32_t *deg;
+  int32_t *l = list_ptr(g, layer, n, &deg);
+  if (!l) return;
+  list_insert(g, l, deg, newn); /* graph.go:50 */
+  if (*deg <= m) return;        /* graph.go:51-53 */
+  /* graph.go:56-71: scan every neighbour (ascending key stands in for map order) for the worst */
+  float worst_dist = -INFINITY;
+  int32_t worst = -1;
+  const float *nv = g->vec + (size_t)n * g->dim;
+  for (int i = 0; i < *deg; i++) {
+    float d = gdist(g, metric, l[i], nv); /* dist(neighbor.Value, n.Value) */
+    g->ctr.evict_evals++;
+    if (d > worst_dist || worst < 0) {
+      worst_dist = d;
+      worst = l[i];
+    }
+  }
+  if (worst >= 0) { /* graph.go:73-80 */
+    g->ctr.evictions++;
+    list_delete(g, l, deg, worst);
+    int32_t *wdeg;
+    int32_t *wl = list_ptr(g, layer, worst, &wdeg);
+    if (wl) list_delete(g, wl, wdeg, n);
+    replenish(g, layer, worst, m);
+  }
+}
+
+/* layerNode.replenish -- graph.go:172-219.  Always CosineDistance (graph.go:204, 216). */
+static void replenish(ora_graph *g, int layer, int32_t n, int m) {
+  int32_t *deg;
+  int32_t *l = list_ptr(g, layer, n, &deg);
+  if (!l || *deg >= m) return; /* graph.go:173-175 */
+  ora_heap cand;
+  ora_heap_init(&cand, m * 2);
+  /* visited = {n} U neighbours(n) (graph.go:183-190); the lists are tiny, so a linear set suffices */
+  int vcap = 64, vn = 0;
+  int32_t *vis = (int32_t *)malloc(sizeof(int32_t) * (size_t)vcap);
+  vis[vn++] = n;
+  for (int i = 0; i < *deg; i++) vis[vn++] = l[i];
+  const float *nv = g->vec + (size_t)n * g->dim;
+  for (int i = 0; i < *deg; i++) { /* graph.go:193-210 */
+    int32_t *ndeg;
+    int32_t *nl = list_ptr(g, layer, l[i], &ndeg);
+    if (!nl) continue;
+    for (int j = 0; j < *ndeg; j++) {
+      int32_t c = nl[j];
+      int seen = 0;
+      for (int t = 0; t < vn; t++)
+        if (vis[t] == c) {
+          seen = 1;
+          break;
+        }
+      if (seen) continue;
+      if (vn == vcap) {
+        vcap *= 2;
+        vis = (int32_t *)realloc(vis, sizeof(int32_t) * (size_t)vcap);
+      }
+      vis[vn++] = c;
+      float d = gdist(g, ORA_COSINE, c, nv); /* CosineDistance(candidate.Value, n.Value) */
+      g->ctr.replenish_evals++;
+      ora_heap_push(&cand, d, c);
+    }
+  }
+  while (cand.len > 0 && *deg < m) { /* graph.go:213-218 */
+    float d;
+    int32_t best;
+    ora_heap_pop(&cand, &d, &best);
+    add_neighbor(g, layer, n, best, m, ORA_COSINE);
+  }
+  free(vis);
+  ora_heap_free(&cand);
+}
+
+/* ---- layerNode.search -- graph.go:94-170 ----------------------------------------------------- */
+static int layer_search(const ora_graph *g, visited_t *vis, ora_counters *ctr, int layer, int32_t entry, int k,
+                        int ef, const float *target, int mode, int32_t *out_rows, float *out_dists) {
+  if (entry < 0) return 0; /* graph.go:101-103 */
+  ora_heap cand, res;
+  ora_heap_init(&cand, ef + 1);
+  ora_heap_init(&res, k + 1);
+  if (++vis->epoch == 0) { /* stamp wrap */
+    memset(vis->stamp, 0, sizeof(uint32_t) * (size_t)vis->cap);
+    vis->epoch = 1;
+  }
+  float d0 = gdist(g, g->metric, entry, target);
+  ctr->dist_evals++;
+  ora_heap_push(&cand, d0, entry);           /* graph.go:109-114 */
+  ora_heap_push(&res, cand.dist[0], cand.id[0]); /* graph.go:122 */
+  vis->stamp[entry] = vis->epoch;            /* graph.go:123 */
+
+  if (mode == ORA_MODE_REFERENCE) {
+    while (cand.len > 0) { /* graph.go:125 */
+      int32_t cur;
+      ora_heap_pop(&cand, NULL, &cur); /* graph.go:127 */
+      int improved = 0;
+      int32_t *deg;
+      int32_t *l = list_ptr(g, layer, cur, &deg);
+      if (!l) continue; /* graph.go:131-133 */
+      ctr->expansions++;
+      for (int i = 0; i < *deg; i++) { /* graph.go:137-160, keys already ascending */
+        int32_t nb = l[i];
+        ctr->nbr_reads++;
+        if (vis->stamp[nb] == vis->epoch) continue;
+        vis->stamp[nb] = vis->epoch;
+        float d = gdist(g, g->metric, nb, target);
+        ctr->dist_evals++;
+        improved = improved || (res.len > 0 && d < res.dist[0]); /* graph.go:147 */
+        if (res.len < k) {
+          ora_heap_push(&res, d, nb);
+        } else if (d < res.dist[res.len - 1]) { /* result.Max() == last slot */
+          ora_heap_poplast(&res, NULL, NULL);
+          ora_heap_push(&res, d, nb);
+        }
+        ora_heap_push(&cand, d, nb);
+        if (cand.len > ef) ora_heap_poplast(&cand, NULL, NULL); /* graph.go:157-159 */
+      }
+      if (!improved && res.len >= k) break; /* graph.go:164-166 */
+    }
+  } else {
+    /* ORA_MODE_EXTENDED: NOT the reference.  Textbook HNSW layer search (Malkov & Yashunin, Alg. 2):
+     * W is a true bounded max-set of size max(ef,k); stop when the nearest candidate is farther than
+     * the farthest element of W.  `res` is used as a max-heap by storing negated distances. */
+    int efk = ef > k ? ef : k;
+    res.len = 0;
+    ora_heap_push(&res, -d0, entry);
+    while (cand.len > 0) {
+      float cd;
+      int32_t cur;
+      ora_heap_pop(&cand, &cd, &cur);
+      if (res.len >= efk && cd > -res.dist[0]) break;
+      int32_t *deg;
+      int32_t *l = list_ptr(g, layer, cur, &deg);
+      if (!l) continue;
+      ctr->expansions++;
+      for (int i = 0; i < *deg; i++) {
+        int32_t nb = l[i];
+        ctr->nbr_reads++;
+        if (vis->stamp[nb] == vis->epoch) continue;
+        vis->stamp[nb] = vis->epoch;
+        float d = gdist(g, g->metric, nb, target);
+        ctr->dist_evals++;
+        if (res.len < efk || d < -res.dist[0]) {
+          ora_heap_push(&cand, d, nb);
+          ora_heap_push(&res, -d, nb);
+          if (res.len > efk) ora_heap_pop(&res, NULL, NULL);
+        }
+      }
+    }
+    /* emit the k nearest, ascending distance (ties: as popped) */
+    while (res.len > k) ora_heap_pop(&res, NULL, NULL);
+    int n = res.len;
+    for (int i = n - 1; i >= 0; i--) {
+      float d;
+      int32_t id;
+      ora_heap_pop(&res, &d, &id);
+      out_rows[i] = id;
+      out_dists[i] = -d;
+    }
+    ora_heap_free(&cand);
+    ora_heap_free(&res);
+    return n;
+  }
+  int n = res.len; /* graph.go:169: Slice() = raw heap array */
+  for (int i = 0; i < n; i++) {
+    out_rows[i] = res.id[i];
+    out_dists[i] = res.dist[i];
+  }
+  ora_heap_free(&cand);
+  ora_heap_free(&res);
+  return n;
+}
+
+int ora_layer_search(ora_graph *g, int layer, int32_t entry, int k, int ef, const float *target, int mode,
+                     int32_t *out_rows, float *out_dists) {
+  visited_t v = {g->stamp, g->epoch, g->cap};
+  int n = layer_search(g, &v, &g->ctr, layer, entry, k, ef, target, mode, out_rows, out_dists);
+  g->epoch = v.epoch;
+  return n;
+}
+
+/* Graph.Search body -- graph.go:571-593 (== BatchSearch body, graph.go:1081-1106) */
+static int graph_search(const ora_graph *g, visited_t *vis, ora_counters *ctr, const float *q, int k, int ef,
+                        int mode, const int32_t *entries, int32_t *out_rows, float *out_dists) {
+  int32_t elevator = -1;
+  for (int layer = g->n_layers - 1; layer >= 0; layer--) {
+    int32_t sp = entries ? entries[layer] : g->entry[layer];
+    if (elevator >= 0) sp = elevator;
+    if (layer > 0) {
+      int32_t r;
+      float d;
+      /* extended mode keeps the reference's greedy k=1 descent on upper layers with ef=1 */
+      int n = layer_search(g, vis, ctr, layer, sp, 1, mode == ORA_MODE_EXTENDED ? 1 : ef, q, mode, &r, &d);
+      if (n == 0) continue; /* graph.go:580-583 */
+      elevator = r;
+      continue;
+    }
+    return layer_search(g, vis, ctr, 0, sp, k, ef, q, mode, out_rows, out_dists);
+  }
+  return 0;
+}
+
+int ora_graph_search(ora_graph *g, const float *query, int k, int ef, int mode, const int32_t *entries,
+                     int32_t *out_rows, float *out_dists) {
+  visited_t v = {g->stamp, g->epoch, g->cap};
+  int n = graph_search(g, &v, &g->ctr, query, k, ef, mode, entries, out_rows, out_dists);
+  g->epoch = v.epoch;
+  return n;
+}
+
+typedef struct {
+  const ora_graph *g;
+  const float *queries;
+  int64_t q0, q1;
+  int k, ef, mode;
+  int32_t *out_rows;
+  float *out_dists;
+  int32_t *out_counts;
+  ora_counters ctr;
+} bs_job;
+
+static void *bs_worker(void *arg) {
+  bs_job *j = (bs_job *)arg;
+  visited_t v;
+  v.cap = j->g->cap;
+  v.stamp = (uint32_t *)calloc((size_t)(v.cap ? v.cap : 1), sizeof(uint32_t));
+  v.epoch = 0;
+  for (int64_t i = j->q0; i < j->q1; i++) {
+    int n = graph_search(j->g, &v, &j->ctr, j->queries + (size_t)i * j->g->dim, j->k, j->ef, j->mode, NULL,
+                         j->out_rows + (size_t)i * j->k, j->out_dists + (size_t)i * j->k);
+    j->out_counts[i] = n;
+  }
+  free(v.stamp);
+  return NULL;
+}
+
+void ora_graph_batch_search(ora_graph *g, const float *queries, int64_t nq, int k, int ef, int mode, int n_threads,
+                            int32_t *out_rows, float *out_dists, int32_t *out_counts, ora_counters *total) {
+  if (n_threads < 1) n_threads = 1;
+  if (n_threads > nq) n_threads = nq > 0 ? (int)nq : 1;
+  bs_job *jobs = (bs_job *)calloc((size_t)n_threads, sizeof *jobs);
+  pthread_t *th = (pthread_t *)calloc((size_t)n_threads, sizeof *th);
+  for (int t = 0; t < n_threads; t++) {
+    jobs[t].g = g;
+    jobs[t].queries = queries;
+    jobs[t].q0 = nq * t / n_threads;
+    jobs[t].q1 = nq * (t + 1) / n_threads;
+    jobs[t].k = k;
+    jobs[t].ef = ef;
+    jobs[t].mode = mode;
+    jobs[t].out_rows = out_rows;
+    jobs[t].out_dists = out_dists;
+    jobs[t].out_counts = out_counts;
+    if (n_threads == 1) bs_worker(&jobs[t]);
+    else pthread_create(&th[t], NULL, bs_worker, &jobs[t]);
+  }
+  ora_counters sum;
+  memset(&sum, 0, sizeof sum);
+  for (int t = 0; t < n_threads; t++) {
+    if (n_threads > 1) pthread_join(th[t], NULL);
+    sum.dist_evals += jobs[t].ctr.dist_evals;
+    sum.expansions += jobs[t].ctr.expansions;
+    sum.nbr_reads += jobs[t].ctr.nbr_reads;
+  }
+  if (total) *total = sum;
+  free(jobs);
+  free(th);
+}
+
+/* ---- Graph.Add for one node -- graph.go:445-528 ----------------------------------------------- */
+int32_t ora_graph_add(ora_graph *g, int64_t key, const float *vec, int level, int ef) {
+  if (level < 0 || level >= ORA_MAX_LAYERS) return -1;
+  int32_t row = new_row(g, key, vec, level);
+  while (level >= g->n_layers) { /* graph.go:462-464 */
+    g->entry[g->n_layers] = -1;
+    g->layer_size[g->n_layers] = 0;
+    g->n_layers++;
+  }
+  int32_t elevator = -1;
+  int M = g->M;
+  int32_t *nb_rows = (int32_t *)malloc(sizeof(int32_t) * (size_t)M);
+  float *nb_d = (float *)malloc(sizeof(float) * (size_t)M);
+  for (int i = g->n_layers - 1; i >= 0; i--) { /* graph.go:475 */
+    if (g->layer_size[i] == 0) {               /* graph.go:485-488 */
+      if (i > level) {
+        /* An empty layer above the drawn level only arises after deletions; the row has no list
+         * there.  Out of scope with Delete. */
+        continue;
+      }
+      g->entry[i] = row;
+      g->layer_size[i] = 1;
+      continue;
+    }
+    int32_t sp = g->entry[i]; /* graph.go:492 */
+    if (elevator >= 0) sp = elevator; /* graph.go:496-498 */
+    int cnt = ora_layer_search(g, i, sp, M, ef, vec, ORA_MODE_REFERENCE, nb_rows, nb_d); /* graph.go:500 */
+    if (cnt == 0) {
+      free(nb_rows);
+      free(nb_d);
+      return -2;
+    }
+    elevator = nb_rows[0]; /* graph.go:508 */
+    if (level >= i) {      /* graph.go:510 */
+      g->layer_size[i]++;  /* graph.go:515 */
+      for (int t = 0; t < cnt; t++) { /* graph.go:516-520, heap-array order */
+        add_neighbor(g, i, nb_rows[t], row, M, g->metric);
+        add_neighbor(g, i, row, nb_rows[t], M, g->metric);
+      }
+    }
+  }
+  free(nb_rows);
+  free(nb_d);
+  return row;
+}
+
+int32_t ora_graph_put_node(ora_graph *g, int64_t key, const float *vec, int level) {
+  int32_t row = new_row(g, key, vec, level);
+  while (level >= g->n_layers) {
+    g->entry[g->n_layers] = -1;
+    g->layer_size[g->n_layers] = 0;
+    g->n_layers++;
+  }
+  for (int l = 0; l <= level; l++) {
+    if (g->entry[l] < 0) g->entry[l] = row;
+    g->layer_size[l]++;
+  }
+  return row;
+}
+
+int ora_graph_link(ora_graph *g, int layer, int32_t from, int32_t to) {
+  int32_t *deg;
+  int32_t *l = list_ptr(g, layer, from, &deg);
+  if (!l || *deg >= g->stride) return -1;
+  list_insert(g, l, deg, to);
+  return 0;
+}
