@@ -3,11 +3,12 @@
  * (see hnsw_oracle.h for the parity status and who may load this).
  *
  * Citations are file:line into the reference tree (TFMV/hnsw).  Nothing here is shipped.
- * Build: see oracle/Makefile (gcc -O3 -march=native -ffp-contract=off).
+ * Build: see oracle/Makefile (gcc -O3 -march=x86-64-v3 -ffp-contract=off).
  */
 #define _GNU_SOURCE
 #include "hnsw_oracle.h"
 
+#include <immintrin.h>
 #include <math.h>
 #include <pthread.h>
 #include <stdlib.h>
@@ -24,18 +25,54 @@
  * over its elements in index order; the 32 partial sums are combined by an xor butterfly with
  * offsets 16, 8, 4, 2, 1 (float addition is commutative, so every lane holds the same bits). */
 static inline float butterfly32(float *acc) {
-  for (int off = 16; off >= 1; off >>= 1) {
-    float t[32];
-    for (int i = 0; i < 32; i++) t[i] = acc[i] + acc[i ^ off];
-    memcpy(acc, t, sizeof t);
-  }
+  /* lane 0 of the butterfly only ever reads lanes < off, so a halving reduction gives the same bits */
+  for (int off = 16; off >= 1; off >>= 1)
+    for (int i = 0; i < off; i++) acc[i] = acc[i] + acc[i + off];
   return acc[0];
 }
 
-static float l2sq_canonical(const float *a, const float *b, int d) {
-  float acc[32];
-  for (int i = 0; i < 32; i++) acc[i] = 0.0f;
-  for (int i = 0; i < d; i++) {
+/* AVX2 form of the same order.  A block of 128 floats touches each of the 32 accumulators once, four
+ * elements in a row.  For 8 consecutive chunks held in 4 registers r0..r3 (r_i = [chunk 2i | chunk 2i+1]) a
+ * 4x4 transpose inside each 128-bit half gives X = [c0.x c2.x c4.x c6.x | c1.x c3.x c5.x c7.x] (likewise Y, Z,
+ * W), so one register of 8 accumulators advances by fma(X), fma(Y), fma(Z), fma(W): the per-accumulator chain
+ * is still x, y, z, w in index order.  Bit-identical to the scalar definition (tests/test_oracle_kat.py). */
+static inline void transpose8(__m256 r0, __m256 r1, __m256 r2, __m256 r3, __m256 *x, __m256 *y, __m256 *z,
+                              __m256 *w) {
+  __m256 t0 = _mm256_unpacklo_ps(r0, r1), t1 = _mm256_unpackhi_ps(r0, r1);
+  __m256 t2 = _mm256_unpacklo_ps(r2, r3), t3 = _mm256_unpackhi_ps(r2, r3);
+  *x = _mm256_shuffle_ps(t0, t2, 0x44);
+  *y = _mm256_shuffle_ps(t0, t2, 0xEE);
+  *z = _mm256_shuffle_ps(t1, t3, 0x44);
+  *w = _mm256_shuffle_ps(t1, t3, 0xEE);
+}
+/* register lane j of group g holds accumulator 8g + perm[j] */
+static const int kLanePerm[8] = {0, 2, 4, 6, 1, 3, 5, 7};
+static inline void unpermute(const __m256 v[4], float *acc) {
+  float t[8] __attribute__((aligned(32)));
+  for (int g = 0; g < 4; g++) {
+    _mm256_store_ps(t, v[g]);
+    for (int j = 0; j < 8; j++) acc[8 * g + kLanePerm[j]] = t[j];
+  }
+}
+
+static float l2sq_canonical(const float *restrict a, const float *restrict b, int d) {
+  float acc[32] __attribute__((aligned(64)));
+  __m256 v[4] = {_mm256_setzero_ps(), _mm256_setzero_ps(), _mm256_setzero_ps(), _mm256_setzero_ps()};
+  int i = 0;
+  for (; i + 128 <= d; i += 128) {
+    for (int g = 0; g < 4; g++) {
+      const float *pa = a + i + 32 * g, *pb = b + i + 32 * g;
+      __m256 r0 = _mm256_sub_ps(_mm256_loadu_ps(pa), _mm256_loadu_ps(pb));
+      __m256 r1 = _mm256_sub_ps(_mm256_loadu_ps(pa + 8), _mm256_loadu_ps(pb + 8));
+      __m256 r2 = _mm256_sub_ps(_mm256_loadu_ps(pa + 16), _mm256_loadu_ps(pb + 16));
+      __m256 r3 = _mm256_sub_ps(_mm256_loadu_ps(pa + 24), _mm256_loadu_ps(pb + 24));
+      __m256 x, y, z, w;
+      transpose8(r0, r1, r2, r3, &x, &y, &z, &w);
+      v[g] = _mm256_fmadd_ps(w, w, _mm256_fmadd_ps(z, z, _mm256_fmadd_ps(y, y, _mm256_fmadd_ps(x, x, v[g]))));
+    }
+  }
+  unpermute(v, acc);
+  for (; i < d; i++) {
     float diff = a[i] - b[i];
     int lane = (i >> 2) & 31;
     acc[lane] = fmaf(diff, diff, acc[lane]);
@@ -43,10 +80,30 @@ static float l2sq_canonical(const float *a, const float *b, int d) {
   return butterfly32(acc);
 }
 
-static void dot3_canonical(const float *a, const float *b, int d, float *dot, float *na, float *nb) {
-  float accd[32], acca[32], accb[32];
-  for (int i = 0; i < 32; i++) accd[i] = acca[i] = accb[i] = 0.0f;
-  for (int i = 0; i < d; i++) {
+static void dot3_canonical(const float *restrict a, const float *restrict b, int d, float *dot, float *na,
+                           float *nb) {
+  float accd[32] __attribute__((aligned(64))), acca[32] __attribute__((aligned(64))),
+      accb[32] __attribute__((aligned(64)));
+  __m256 vd[4], va[4], vb[4];
+  for (int g = 0; g < 4; g++) vd[g] = va[g] = vb[g] = _mm256_setzero_ps();
+  int i = 0;
+  for (; i + 128 <= d; i += 128) {
+    for (int g = 0; g < 4; g++) {
+      const float *pa = a + i + 32 * g, *pb = b + i + 32 * g;
+      __m256 ax, ay, az, aw, bx, by, bz, bw;
+      transpose8(_mm256_loadu_ps(pa), _mm256_loadu_ps(pa + 8), _mm256_loadu_ps(pa + 16), _mm256_loadu_ps(pa + 24),
+                 &ax, &ay, &az, &aw);
+      transpose8(_mm256_loadu_ps(pb), _mm256_loadu_ps(pb + 8), _mm256_loadu_ps(pb + 16), _mm256_loadu_ps(pb + 24),
+                 &bx, &by, &bz, &bw);
+      vd[g] = _mm256_fmadd_ps(aw, bw, _mm256_fmadd_ps(az, bz, _mm256_fmadd_ps(ay, by, _mm256_fmadd_ps(ax, bx, vd[g]))));
+      va[g] = _mm256_fmadd_ps(aw, aw, _mm256_fmadd_ps(az, az, _mm256_fmadd_ps(ay, ay, _mm256_fmadd_ps(ax, ax, va[g]))));
+      vb[g] = _mm256_fmadd_ps(bw, bw, _mm256_fmadd_ps(bz, bz, _mm256_fmadd_ps(by, by, _mm256_fmadd_ps(bx, bx, vb[g]))));
+    }
+  }
+  unpermute(vd, accd);
+  unpermute(va, acca);
+  unpermute(vb, accb);
+  for (; i < d; i++) {
     int lane = (i >> 2) & 31;
     accd[lane] = fmaf(a[i], b[i], accd[lane]);
     acca[lane] = fmaf(a[i], a[i], acca[lane]);
@@ -80,50 +137,61 @@ static void dot3_sequential(const float *a, const float *b, int d, float *dot, f
   *nb = sb;
 }
 
-/* ORA_FLAVOR_SIMD: 16 independent accumulators so gcc vectorises it (AVX2/AVX-512 + FMA), the
- * shape of vek32's assembly path.  Used only for the timed CPU baseline. */
-#define SIMD_W 16
+/* ORA_FLAVOR_SIMD: four 8-wide FMA accumulators, the shape of vek32's AVX2 assembly path.
+ * Used only for the timed CPU baseline. */
+static inline float hsum8(__m256 v) {
+  __m128 lo = _mm256_castps256_ps128(v), hi = _mm256_extractf128_ps(v, 1);
+  lo = _mm_add_ps(lo, hi);
+  lo = _mm_add_ps(lo, _mm_movehl_ps(lo, lo));
+  lo = _mm_add_ss(lo, _mm_shuffle_ps(lo, lo, 1));
+  return _mm_cvtss_f32(lo);
+}
 static float l2sq_simd(const float *a, const float *b, int d) {
-  float acc[SIMD_W] = {0};
+  __m256 s0 = _mm256_setzero_ps(), s1 = s0, s2 = s0, s3 = s0;
   int i = 0;
-  for (; i + SIMD_W <= d; i += SIMD_W)
-    for (int j = 0; j < SIMD_W; j++) {
-      float diff = a[i + j] - b[i + j];
-      acc[j] = fmaf(diff, diff, acc[j]);
-    }
-  float s = 0.0f;
+  for (; i + 32 <= d; i += 32) {
+    __m256 d0 = _mm256_sub_ps(_mm256_loadu_ps(a + i), _mm256_loadu_ps(b + i));
+    __m256 d1 = _mm256_sub_ps(_mm256_loadu_ps(a + i + 8), _mm256_loadu_ps(b + i + 8));
+    __m256 d2 = _mm256_sub_ps(_mm256_loadu_ps(a + i + 16), _mm256_loadu_ps(b + i + 16));
+    __m256 d3 = _mm256_sub_ps(_mm256_loadu_ps(a + i + 24), _mm256_loadu_ps(b + i + 24));
+    s0 = _mm256_fmadd_ps(d0, d0, s0);
+    s1 = _mm256_fmadd_ps(d1, d1, s1);
+    s2 = _mm256_fmadd_ps(d2, d2, s2);
+    s3 = _mm256_fmadd_ps(d3, d3, s3);
+  }
+  for (; i + 8 <= d; i += 8) {
+    __m256 d0 = _mm256_sub_ps(_mm256_loadu_ps(a + i), _mm256_loadu_ps(b + i));
+    s0 = _mm256_fmadd_ps(d0, d0, s0);
+  }
+  float s = hsum8(_mm256_add_ps(_mm256_add_ps(s0, s1), _mm256_add_ps(s2, s3)));
   for (; i < d; i++) {
     float diff = a[i] - b[i];
     s = fmaf(diff, diff, s);
   }
-  for (int w = SIMD_W / 2; w >= 1; w >>= 1)
-    for (int j = 0; j < w; j++) acc[j] += acc[j + w];
-  return acc[0] + s;
+  return s;
 }
 static void dot3_simd(const float *a, const float *b, int d, float *dot, float *na, float *nb) {
-  float ad[SIMD_W] = {0}, aa[SIMD_W] = {0}, ab[SIMD_W] = {0};
+  __m256 sd0 = _mm256_setzero_ps(), sd1 = sd0, sa0 = sd0, sa1 = sd0, sb0 = sd0, sb1 = sd0;
   int i = 0;
-  for (; i + SIMD_W <= d; i += SIMD_W)
-    for (int j = 0; j < SIMD_W; j++) {
-      ad[j] = fmaf(a[i + j], b[i + j], ad[j]);
-      aa[j] = fmaf(a[i + j], a[i + j], aa[j]);
-      ab[j] = fmaf(b[i + j], b[i + j], ab[j]);
-    }
-  float sd = 0, sa = 0, sb = 0;
+  for (; i + 16 <= d; i += 16) {
+    __m256 a0 = _mm256_loadu_ps(a + i), a1 = _mm256_loadu_ps(a + i + 8);
+    __m256 b0 = _mm256_loadu_ps(b + i), b1 = _mm256_loadu_ps(b + i + 8);
+    sd0 = _mm256_fmadd_ps(a0, b0, sd0);
+    sd1 = _mm256_fmadd_ps(a1, b1, sd1);
+    sa0 = _mm256_fmadd_ps(a0, a0, sa0);
+    sa1 = _mm256_fmadd_ps(a1, a1, sa1);
+    sb0 = _mm256_fmadd_ps(b0, b0, sb0);
+    sb1 = _mm256_fmadd_ps(b1, b1, sb1);
+  }
+  float sd = hsum8(_mm256_add_ps(sd0, sd1)), sa = hsum8(_mm256_add_ps(sa0, sa1)), sb = hsum8(_mm256_add_ps(sb0, sb1));
   for (; i < d; i++) {
     sd = fmaf(a[i], b[i], sd);
     sa = fmaf(a[i], a[i], sa);
     sb = fmaf(b[i], b[i], sb);
   }
-  for (int w = SIMD_W / 2; w >= 1; w >>= 1)
-    for (int j = 0; j < w; j++) {
-      ad[j] += ad[j + w];
-      aa[j] += aa[j + w];
-      ab[j] += ab[j + w];
-    }
-  *dot = ad[0] + sd;
-  *na = aa[0] + sa;
-  *nb = ab[0] + sb;
+  *dot = sd;
+  *na = sa;
+  *nb = sb;
 }
 
 float ora_distance(int metric, int flavor, const float *a, const float *b, int d) {

@@ -208,11 +208,13 @@ static void replenish(ora_graph *g, int layer, int32_t n, int m) {
   if (!l || *deg >= m) return; /* graph.go:173-175 */
   ora_heap cand;
   ora_heap_init(&cand, m * 2);
-  /* visited = {n} U neighbours(n) (graph.go:183-190); the lists are tiny, so a linear set suffices */
-  int vcap = 64, vn = 0;
-  int32_t *vis = (int32_t *)malloc(sizeof(int32_t) * (size_t)vcap);
-  vis[vn++] = n;
-  for (int i = 0; i < *deg; i++) vis[vn++] = l[i];
+  /* visited = {n} U neighbours(n) (graph.go:183-190); epoch stamps play the map[K]bool */
+  if (++g->epoch == 0) {
+    memset(g->stamp, 0, sizeof(uint32_t) * (size_t)g->cap);
+    g->epoch = 1;
+  }
+  g->stamp[n] = g->epoch;
+  for (int i = 0; i < *deg; i++) g->stamp[l[i]] = g->epoch;
   const float *nv = g->vec + (size_t)n * g->dim;
   for (int i = 0; i < *deg; i++) { /* graph.go:193-210 */
     int32_t *ndeg;
@@ -220,18 +222,8 @@ static void replenish(ora_graph *g, int layer, int32_t n, int m) {
     if (!nl) continue;
     for (int j = 0; j < *ndeg; j++) {
       int32_t c = nl[j];
-      int seen = 0;
-      for (int t = 0; t < vn; t++)
-        if (vis[t] == c) {
-          seen = 1;
-          break;
-        }
-      if (seen) continue;
-      if (vn == vcap) {
-        vcap *= 2;
-        vis = (int32_t *)realloc(vis, sizeof(int32_t) * (size_t)vcap);
-      }
-      vis[vn++] = c;
+      if (g->stamp[c] == g->epoch) continue;
+      g->stamp[c] = g->epoch;
       float d = gdist(g, ORA_COSINE, c, nv); /* CosineDistance(candidate.Value, n.Value) */
       g->ctr.replenish_evals++;
       ora_heap_push(&cand, d, c);
@@ -243,7 +235,6 @@ static void replenish(ora_graph *g, int layer, int32_t n, int m) {
     ora_heap_pop(&cand, &d, &best);
     add_neighbor(g, layer, n, best, m, ORA_COSINE);
   }
-  free(vis);
   ora_heap_free(&cand);
 }
 
