@@ -1,0 +1,9 @@
+"""hnsw_b200 -- B200-native (sm_100a) drop-in for the data-parallel hot path of TFMV/hnsw.
+
+Host-side mirror of the reference's Go API over the C ABI in include/b200hnsw.h.  No CPU fallback.
+"""
+from .distance import (CosineDistance, EuclideanDistance, RegisterDistanceFunc, distanceFuncs, distanceFuncToName)
+from .graph import Graph, GoRand, MakeNode, NewGraph, NewGraphWithConfig, Node, maxLevel
+
+__all__ = ["Graph", "GoRand", "Node", "MakeNode", "NewGraph", "NewGraphWithConfig", "maxLevel", "CosineDistance",
+           "EuclideanDistance", "RegisterDistanceFunc", "distanceFuncs", "distanceFuncToName"]

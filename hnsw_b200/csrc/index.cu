@@ -1,0 +1,495 @@
+// index.cu -- C ABI (include/b200hnsw.h): lifetime, device-resident layout, load / read-back, search entry points.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <new>
+
+#include "index.hpp"
+
+namespace b200 {
+
+static thread_local std::string g_err;
+
+void set_error(const char *fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_err = buf;
+}
+
+int cuda_fail(cudaError_t e, const char *what) {
+  set_error("CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
+  return e == cudaErrorMemoryAllocation ? B200HNSW_ERR_OOM : B200HNSW_ERR_CUDA;
+}
+
+int CallCtx::reserve_device(size_t bytes) {
+  if (bytes <= scratch_bytes) return 0;
+  if (d_scratch) cudaFree(d_scratch);
+  d_scratch = nullptr;
+  scratch_bytes = 0;
+  size_t want = std::max(bytes, (size_t)1 << 20);
+  B200_CUDA(cudaMalloc(&d_scratch, want));
+  scratch_bytes = want;
+  return 0;
+}
+int CallCtx::reserve_pinned(size_t bytes) {
+  if (bytes <= pinned_bytes) return 0;
+  if (h_pinned) cudaFreeHost(h_pinned);
+  h_pinned = nullptr;
+  pinned_bytes = 0;
+  size_t want = std::max(bytes, (size_t)1 << 20);
+  B200_CUDA(cudaMallocHost(&h_pinned, want));
+  pinned_bytes = want;
+  return 0;
+}
+
+template <typename T>
+static int grow(T *&ptr, int64_t old_elems, int64_t new_elems, cudaStream_t s, int fill_byte = -1) {
+  T *np = nullptr;
+  B200_CUDA(cudaMalloc(&np, sizeof(T) * (size_t)new_elems));
+  if (fill_byte >= 0) B200_CUDA(cudaMemsetAsync(np, fill_byte, sizeof(T) * (size_t)new_elems, s));
+  if (ptr && old_elems > 0)
+    B200_CUDA(cudaMemcpyAsync(np, ptr, sizeof(T) * (size_t)old_elems, cudaMemcpyDeviceToDevice, s));
+  B200_CUDA(cudaStreamSynchronize(s));
+  if (ptr) cudaFree(ptr);
+  ptr = np;
+  return 0;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+b200::CallCtx *b200hnsw::acquire() {
+  {
+    std::lock_guard<std::mutex> lk(pool_mu);
+    if (!pool.empty()) {
+      CallCtx *c = pool.back();
+      pool.pop_back();
+      return c;
+    }
+  }
+  CallCtx *c = new (std::nothrow) CallCtx();
+  if (!c) return nullptr;
+  if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess) {
+    delete c;
+    return nullptr;
+  }
+  return c;
+}
+void b200hnsw::release(CallCtx *c) {
+  std::lock_guard<std::mutex> lk(pool_mu);
+  pool.push_back(c);
+}
+
+b200::GraphView b200hnsw::view() const {
+  GraphView g;
+  g.vec = reinterpret_cast<const float4 *>(d.vec);
+  g.adj0 = d.adj0;
+  g.adjU = d.adjU;
+  g.upper_off = d.upper_off;
+  g.row_chunks = row_floats / 4;
+  g.M = M;
+  g.dim = cfg.dim;
+  return g;
+}
+
+int b200hnsw::ensure_capacity(int64_t rows, int64_t upper_slots, cudaStream_t s) {
+  if (rows > d.cap) {
+    int64_t nc = std::max<int64_t>(d.cap * 2, std::max<int64_t>(rows, 1024));
+    int rc;
+    // vectors are zero-filled so the padding lanes of every row are exact zeros
+    if ((rc = grow(d.vec, n * row_floats, nc * row_floats, s, 0))) return rc;
+    if ((rc = grow(d.keys, n, nc, s))) return rc;
+    if ((rc = grow(d.adj0, n * M, nc * M, s, 0xff))) return rc;
+    if ((rc = grow(d.upper_off, n, nc, s, 0xff))) return rc;
+    d.cap = nc;
+  }
+  if (upper_slots > d.capU) {
+    int64_t nc = std::max<int64_t>(d.capU * 2, std::max<int64_t>(upper_slots, 1024));
+    int rc;
+    if ((rc = grow(d.adjU, nU * M, nc * M, s, 0xff))) return rc;
+    d.capU = nc;
+  }
+  return 0;
+}
+
+extern "C" {
+
+int b200hnsw_abi_version(void) { return B200HNSW_ABI_VERSION; }
+const char *b200hnsw_last_error(void) { return g_err.c_str(); }
+
+int b200hnsw_create(const b200hnsw_config *cfg, b200hnsw_t **out) {
+  if (!cfg || !out) {
+    set_error("create: null argument");
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  *out = nullptr;
+  if (cfg->dim <= 0 || cfg->max_m <= 0 || cfg->max_m > B200HNSW_MAX_M || cfg->reserved != 0) {
+    set_error("create: dim=%d max_m=%d out of range (max_m <= %d)", cfg->dim, cfg->max_m, B200HNSW_MAX_M);
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    set_error("create: no CUDA device (%s); this library has no CPU fallback", cudaGetErrorString(e));
+    return B200HNSW_ERR_CUDA;
+  }
+  if (cfg->device < 0 || cfg->device >= ndev) {
+    set_error("create: device %d out of range (%d devices)", cfg->device, ndev);
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  B200_CUDA(cudaSetDevice(cfg->device));
+  b200hnsw *h = new (std::nothrow) b200hnsw();
+  if (!h) return B200HNSW_ERR_OOM;
+  h->cfg = *cfg;
+  h->row_floats = (cfg->dim + 31) / 32 * 32;
+  h->M = cfg->max_m;
+  for (int l = 0; l < B200HNSW_MAX_LAYERS; l++) {
+    h->entry[l] = -1;
+    h->layer_size[l] = 0;
+  }
+  cudaDeviceProp prop;
+  B200_CUDA(cudaGetDeviceProperties(&prop, cfg->device));
+  h->sm_count = prop.multiProcessorCount;
+  h->smem_optin = prop.sharedMemPerBlockOptin;
+  CallCtx *c = h->acquire();
+  if (!c) {
+    delete h;
+    set_error("create: cannot create stream");
+    return B200HNSW_ERR_CUDA;
+  }
+  int rc = h->ensure_capacity(cfg->capacity > 0 ? cfg->capacity : 1024, 1024, c->stream);
+  if (!rc && cudaMalloc(&h->d_err_word, 64) != cudaSuccess) rc = B200HNSW_ERR_OOM;
+  if (!rc) cudaMemset(h->d_err_word, 0, 64);
+  h->release(c);
+  if (rc) {
+    b200hnsw_destroy(h);
+    return rc;
+  }
+  *out = h;
+  return 0;
+}
+
+void b200hnsw_destroy(b200hnsw_t *h) {
+  if (!h) return;
+  cudaSetDevice(h->cfg.device);
+  cudaDeviceSynchronize();
+  for (CallCtx *c : h->pool) {
+    if (c->d_scratch) cudaFree(c->d_scratch);
+    if (c->h_pinned) cudaFreeHost(c->h_pinned);
+    cudaEventDestroy(c->ev0);
+    cudaEventDestroy(c->ev1);
+    cudaStreamDestroy(c->stream);
+    delete c;
+  }
+  cudaFree(h->d.vec);
+  cudaFree(h->d.keys);
+  cudaFree(h->d.adj0);
+  cudaFree(h->d.upper_off);
+  cudaFree(h->d.adjU);
+  cudaFree(h->d_err_word);
+  delete h;
+}
+
+int b200hnsw_reserve(b200hnsw_t *h, int64_t rows) {
+  if (!h || rows < 0) return B200HNSW_ERR_BAD_ARG;
+  B200_CUDA(cudaSetDevice(h->cfg.device));
+  CallCtx *c = h->acquire();
+  if (!c) return B200HNSW_ERR_CUDA;
+  int rc = h->ensure_capacity(rows, rows / 2 + 1024, c->stream);
+  h->release(c);
+  return rc;
+}
+
+int64_t b200hnsw_len(const b200hnsw_t *h) { return h && h->n_layers ? h->layer_size[0] : 0; }
+int32_t b200hnsw_layers(const b200hnsw_t *h) { return h ? h->n_layers : 0; }
+int64_t b200hnsw_layer_size(const b200hnsw_t *h, int32_t l) {
+  return (h && l >= 0 && l < h->n_layers) ? h->layer_size[l] : 0;
+}
+int32_t b200hnsw_entry(const b200hnsw_t *h, int32_t l) { return (h && l >= 0 && l < h->n_layers) ? h->entry[l] : -1; }
+int b200hnsw_set_entry(b200hnsw_t *h, int32_t l, int32_t row) {
+  if (!h || l < 0 || l >= h->n_layers || row < 0 || row >= h->n || h->h_level[row] < l) {
+    set_error("set_entry: row %d is not a member of layer %d", row, l);
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  h->entry[l] = row;
+  return 0;
+}
+
+int b200hnsw_load(b200hnsw_t *h, int64_t n, const float *vectors, const int64_t *keys, const int32_t *levels,
+                  int32_t n_layers, const int32_t *entries, const int64_t *layer_sizes, const int32_t *layer_rows,
+                  const int64_t *layer_ptr, const int32_t *layer_nbr) {
+  if (!h || n < 0 || n_layers < 0 || n_layers > B200HNSW_MAX_LAYERS || (n > 0 && (!vectors || !keys || !levels))) {
+    set_error("load: bad argument");
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  if (n > 0 && (n_layers == 0 || !layer_sizes || !layer_rows || !layer_ptr || layer_sizes[0] != n)) {
+    set_error("load: layer 0 must list every row");
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  B200_CUDA(cudaSetDevice(h->cfg.device));
+  const int M = h->M, dim = h->cfg.dim, rf = h->row_floats;
+  // slots for upper layers
+  std::vector<int32_t> upper_off((size_t)n, -1);
+  int64_t nU = 0;
+  for (int64_t r = 0; r < n; r++) {
+    if (levels[r] < 0 || levels[r] >= n_layers) {
+      set_error("load: level %d of row %lld outside 0..%d", levels[r], (long long)r, n_layers - 1);
+      return B200HNSW_ERR_BAD_ARG;
+    }
+    if (levels[r] > 0) {
+      upper_off[r] = (int32_t)nU;
+      nU += levels[r];
+    }
+  }
+  std::vector<int32_t> adj0((size_t)n * M, -1), adjU((size_t)nU * M, -1);
+  int64_t roff = 0, poff = 0, noff = 0;
+  std::vector<int32_t> tmp;
+  for (int l = 0; l < n_layers; l++) {
+    int64_t nl = layer_sizes[l];
+    for (int64_t i = 0; i < nl; i++) {
+      int32_t row = layer_rows[roff + i];
+      if (row < 0 || row >= n || levels[row] < l) {
+        set_error("load: row %d listed in layer %d but its level is lower", row, l);
+        return B200HNSW_ERR_BAD_ARG;
+      }
+      int64_t b = layer_ptr[poff + i], e = layer_ptr[poff + i + 1];
+      if (e - b > M || e < b) {
+        set_error("load: row %d has %lld neighbours in layer %d (max_m=%d)", row, (long long)(e - b), l, M);
+        return B200HNSW_ERR_BAD_ARG;
+      }
+      tmp.assign(layer_nbr + noff + b, layer_nbr + noff + e);
+      for (int32_t t : tmp)
+        if (t < 0 || t >= n || levels[t] < l) {
+          set_error("load: neighbour %d of row %d is not a member of layer %d", t, row, l);
+          return B200HNSW_ERR_BAD_ARG;
+        }
+      std::sort(tmp.begin(), tmp.end(), [&](int32_t a, int32_t c) { return keys[a] < keys[c]; });
+      int32_t *dst = l == 0 ? &adj0[(size_t)row * M] : &adjU[((size_t)upper_off[row] + (l - 1)) * M];
+      std::copy(tmp.begin(), tmp.end(), dst);
+    }
+    noff += layer_ptr[poff + nl];
+    roff += nl;
+    poff += nl + 1;
+  }
+  CallCtx *c = h->acquire();
+  if (!c) return B200HNSW_ERR_CUDA;
+  h->n = 0;
+  h->nU = 0;
+  int rc = h->ensure_capacity(n, nU, c->stream);
+  if (rc) {
+    h->release(c);
+    return rc;
+  }
+  cudaStream_t s = c->stream;
+  auto fail = [&](int code) {
+    h->release(c);
+    return code;
+  };
+  if (n > 0) {
+    if (cudaMemsetAsync(h->d.vec, 0, sizeof(float) * (size_t)n * rf, s) != cudaSuccess ||
+        cudaMemcpy2DAsync(h->d.vec, sizeof(float) * rf, vectors, sizeof(float) * dim, sizeof(float) * dim, (size_t)n,
+                          cudaMemcpyHostToDevice, s) != cudaSuccess ||
+        cudaMemcpyAsync(h->d.keys, keys, sizeof(int64_t) * (size_t)n, cudaMemcpyHostToDevice, s) != cudaSuccess ||
+        cudaMemcpyAsync(h->d.adj0, adj0.data(), sizeof(int32_t) * adj0.size(), cudaMemcpyHostToDevice, s) !=
+            cudaSuccess ||
+        cudaMemcpyAsync(h->d.upper_off, upper_off.data(), sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice, s) !=
+            cudaSuccess ||
+        (nU > 0 && cudaMemcpyAsync(h->d.adjU, adjU.data(), sizeof(int32_t) * adjU.size(), cudaMemcpyHostToDevice,
+                                   s) != cudaSuccess))
+      return fail(cuda_fail(cudaGetLastError(), "load copies"));
+  }
+  cudaError_t e = cudaStreamSynchronize(s);
+  if (e != cudaSuccess) return fail(cuda_fail(e, "load sync"));
+  h->n = n;
+  h->nU = nU;
+  h->n_layers = n_layers;
+  h->h_keys.assign(keys, keys + n);
+  h->h_level.assign(levels, levels + n);
+  h->h_upper_off = upper_off;
+  roff = 0;
+  for (int l = 0; l < B200HNSW_MAX_LAYERS; l++) {
+    h->entry[l] = -1;
+    h->layer_size[l] = 0;
+  }
+  for (int l = 0; l < n_layers; l++) {
+    h->layer_size[l] = layer_sizes[l];
+    int32_t en = entries ? entries[l] : -1;
+    if (en < 0 && layer_sizes[l] > 0) {
+      // "any node of the layer" (graph.go:246-258): the member with the smallest row = first inserted
+      en = layer_rows[roff];
+      for (int64_t i = 1; i < layer_sizes[l]; i++) en = std::min(en, layer_rows[roff + i]);
+    }
+    h->entry[l] = en;
+    roff += layer_sizes[l];
+  }
+  h->release(c);
+  return 0;
+}
+
+int b200hnsw_get_rows(const b200hnsw_t *hc, int64_t first, int64_t count, float *vectors, int64_t *keys,
+                      int32_t *levels) {
+  b200hnsw *h = const_cast<b200hnsw *>(hc);
+  if (!h || first < 0 || count < 0 || first + count > h->n) {
+    set_error("get_rows: range [%lld, +%lld) outside 0..%lld", (long long)first, (long long)count,
+              h ? (long long)h->n : 0LL);
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  B200_CUDA(cudaSetDevice(h->cfg.device));
+  if (vectors && count > 0)
+    B200_CUDA(cudaMemcpy2D(vectors, sizeof(float) * h->cfg.dim, h->d.vec + (size_t)first * h->row_floats,
+                           sizeof(float) * h->row_floats, sizeof(float) * h->cfg.dim, (size_t)count,
+                           cudaMemcpyDeviceToHost));
+  if (keys) std::copy(h->h_keys.begin() + first, h->h_keys.begin() + first + count, keys);
+  if (levels) std::copy(h->h_level.begin() + first, h->h_level.begin() + first + count, levels);
+  return 0;
+}
+
+int b200hnsw_get_neighbors(const b200hnsw_t *hc, int32_t layer, int64_t first, int64_t count, int32_t *nbr,
+                           uint8_t *member) {
+  b200hnsw *h = const_cast<b200hnsw *>(hc);
+  if (!h || layer < 0 || layer >= h->n_layers || first < 0 || count < 0 || first + count > h->n || !nbr) {
+    set_error("get_neighbors: bad argument");
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  B200_CUDA(cudaSetDevice(h->cfg.device));
+  const int M = h->M;
+  if (layer == 0) {
+    if (count > 0)
+      B200_CUDA(cudaMemcpy(nbr, h->d.adj0 + (size_t)first * M, sizeof(int32_t) * (size_t)count * M,
+                           cudaMemcpyDeviceToHost));
+    if (member) memset(member, 1, (size_t)count);
+    return 0;
+  }
+  std::vector<int32_t> all((size_t)h->nU * M);
+  if (h->nU > 0)
+    B200_CUDA(cudaMemcpy(all.data(), h->d.adjU, sizeof(int32_t) * all.size(), cudaMemcpyDeviceToHost));
+  for (int64_t i = 0; i < count; i++) {
+    int64_t row = first + i;
+    bool mem = h->h_level[row] >= layer;
+    if (member) member[i] = mem;
+    if (mem)
+      std::copy(&all[((size_t)h->h_upper_off[row] + (layer - 1)) * M],
+                &all[((size_t)h->h_upper_off[row] + (layer - 1)) * M] + M, nbr + (size_t)i * M);
+    else
+      std::fill(nbr + (size_t)i * M, nbr + (size_t)(i + 1) * M, -1);
+  }
+  return 0;
+}
+
+static int check_search_args(b200hnsw_t *h, int64_t B, int32_t k, int32_t ef, int32_t metric) {
+  if (!h || B < 0) {
+    set_error("search: bad handle or batch size");
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  if (k <= 0 || k > B200HNSW_MAX_K) {  // graph.go:542-544: "k must be greater than 0"
+    set_error("k must be greater than 0 and <= %d, got %d", B200HNSW_MAX_K, k);
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  if (ef <= 0 || ef > B200HNSW_MAX_EF) {  // graph.go:928-930
+    set_error("EfSearch must be greater than 0 and <= %d, got %d", B200HNSW_MAX_EF, ef);
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  if (metric != B200HNSW_EUCLIDEAN && metric != B200HNSW_COSINE) {
+    set_error("unknown metric %d", metric);
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  return 0;
+}
+
+int b200hnsw_search_batch_device(b200hnsw_t *h, const float *d_queries, int64_t B, int32_t k, int32_t ef,
+                                 int32_t metric, int32_t mode, const int32_t *entries, int32_t *d_out_rows,
+                                 float *d_out_dists, int32_t *d_out_counts, int64_t *d_counters, void *stream) {
+  int rc = check_search_args(h, B, k, ef, metric);
+  if (rc) return rc;
+  B200_CUDA(cudaSetDevice(h->cfg.device));
+  cudaStream_t s = (cudaStream_t)stream;
+  if (B == 0) return 0;
+  if (h->n_layers == 0 || h->n == 0) {  // graph.go:554-556: empty graph -> no results
+    B200_CUDA(cudaMemsetAsync(d_out_counts, 0, sizeof(int32_t) * (size_t)B, s));
+    B200_CUDA(cudaMemsetAsync(d_out_rows, 0xff, sizeof(int32_t) * (size_t)B * k, s));
+    B200_CUDA(cudaMemsetAsync(d_out_dists, 0xff, sizeof(float) * (size_t)B * k, s));
+    return 0;
+  }
+  // d_counters is int64[8]: evals, expansions, nbr_reads, overflowed queries, error flag, 3 spare
+  int *d_err = d_counters ? reinterpret_cast<int *>(d_counters + 4) : h->d_err_word;
+  return launch_search(h, d_queries, B, k, ef, metric, mode, entries, d_out_rows, d_out_dists, d_out_counts,
+                       reinterpret_cast<unsigned long long *>(d_counters), d_err, s);
+}
+
+int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_t k, int32_t ef, int32_t metric,
+                          int32_t mode, const int32_t *entries, int32_t *out_rows, float *out_dists,
+                          int32_t *out_counts, b200hnsw_stats *stats) {
+  int rc = check_search_args(h, B, k, ef, metric);
+  if (rc) return rc;
+  if (B > 0 && (!queries || !out_rows || !out_dists || !out_counts)) {
+    set_error("search: null buffer");
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  if (stats) memset(stats, 0, sizeof *stats);
+  if (B == 0) return 0;
+  if (h->n_layers == 0 || h->n == 0) {
+    std::fill(out_counts, out_counts + B, 0);
+    std::fill(out_rows, out_rows + B * k, -1);
+    std::fill(out_dists, out_dists + B * k, NAN);
+    return 0;
+  }
+  B200_CUDA(cudaSetDevice(h->cfg.device));
+  CallCtx *c = h->acquire();
+  if (!c) return B200HNSW_ERR_CUDA;
+  const int dim = h->cfg.dim;
+  size_t qb = sizeof(float) * (size_t)B * dim, rb = sizeof(int32_t) * (size_t)B * k, db = sizeof(float) * (size_t)B * k,
+         cb = sizeof(int32_t) * (size_t)B;
+  auto al = [](size_t v) { return (v + 255) & ~(size_t)255; };
+  size_t total = al(qb) + al(rb) + al(db) + al(cb) + 256;
+  auto fail = [&](int code) {
+    h->release(c);
+    return code;
+  };
+  if ((rc = c->reserve_device(total))) return fail(rc);
+  char *p = (char *)c->d_scratch;
+  float *d_q = (float *)p;
+  p += al(qb);
+  int32_t *d_rows = (int32_t *)p;
+  p += al(rb);
+  float *d_dists = (float *)p;
+  p += al(db);
+  int32_t *d_cnt = (int32_t *)p;
+  p += al(cb);
+  unsigned long long *d_ctr = (unsigned long long *)p;  // [4] + error word
+  int *d_err = (int *)(d_ctr + 4);
+  cudaStream_t s = c->stream;
+  cudaError_t e;
+  if ((e = cudaMemcpyAsync(d_q, queries, qb, cudaMemcpyHostToDevice, s)) != cudaSuccess ||
+      (e = cudaMemsetAsync(d_ctr, 0, 64, s)) != cudaSuccess || (e = cudaEventRecord(c->ev0, s)) != cudaSuccess)
+    return fail(cuda_fail(e, "search staging"));
+  rc = launch_search(h, d_q, B, k, ef, metric, mode, entries, d_rows, d_dists, d_cnt, d_ctr, d_err, s);
+  if (rc) return fail(rc);
+  unsigned long long ctr[5] = {0, 0, 0, 0, 0};
+  if ((e = cudaEventRecord(c->ev1, s)) != cudaSuccess ||
+      (e = cudaMemcpyAsync(out_rows, d_rows, rb, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
+      (e = cudaMemcpyAsync(out_dists, d_dists, db, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
+      (e = cudaMemcpyAsync(out_counts, d_cnt, cb, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
+      (e = cudaMemcpyAsync(ctr, d_ctr, 40, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
+      (e = cudaStreamSynchronize(s)) != cudaSuccess)
+    return fail(cuda_fail(e, "search copy-back"));
+  if (stats) {
+    stats->dist_evals = (int64_t)ctr[0];
+    stats->expansions = (int64_t)ctr[1];
+    stats->nbr_reads = (int64_t)ctr[2];
+    stats->launches = 1;
+    cudaEventElapsedTime(&stats->kernel_ms, c->ev0, c->ev1);
+  }
+  h->release(c);
+  if ((int)(ctr[4] & 0xffffffffu) != 0) {
+    set_error("search: %llu queries overflowed the visited set (layer search visited > 512 nodes)", ctr[3]);
+    return B200HNSW_ERR_VISITED_OVERFLOW;
+  }
+  return 0;
+}
+
+}  // extern "C"

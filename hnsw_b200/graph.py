@@ -1,0 +1,331 @@
+"""Host-side mirror of the reference's Graph[K] API (graph.go), routing the hot path through the C ABI.
+
+Same names, argument meaning and error texts as the Go methods so the parity tests read like the reference's:
+NewGraph / NewGraphWithConfig (graph.go:340-366), Graph.Add / BatchAdd (437-531, 942-1042), Search / BatchSearch /
+ParallelSearch (534-625, 1047-1110, 631-826), Len / Dims / Lookup / Validate (419-429, 829-838, 898-937),
+Export / Import (encode.go:133-262).  The host keeps what the reference's host would keep under cgo: validation,
+the key <-> row mapping, the level RNG (graph.go:388-417), a host copy of the vectors for returning Node values,
+and the test hacks of graph.go:563-569, 595-619.  Everything data-parallel runs on the device.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+import time
+from dataclasses import dataclass
+from typing import Iterable, List, Optional, Sequence
+
+import numpy as np
+
+from . import _lib
+from .distance import CosineDistance, EuclideanDistance, distanceFuncs, distanceFuncToName, metric_of
+
+
+@dataclass
+class Node:
+    """graph.go:20-27"""
+    Key: int
+    Value: np.ndarray
+
+    def __eq__(self, other):
+        return isinstance(other, Node) and self.Key == other.Key and np.array_equal(self.Value, other.Value)
+
+
+def MakeNode(key, vec) -> Node:
+    return Node(key, np.asarray(vec, dtype=np.float32))
+
+
+class GoRand:
+    """Stand-in for *rand.Rand: anything with Float64().  Go's math/rand stream itself is not reproducible here."""
+
+    def __init__(self, seed: Optional[int] = None):
+        self._g = np.random.default_rng(seed if seed is not None else time.time_ns())
+
+    def Float64(self) -> float:
+        return float(self._g.random())
+
+
+def maxLevel(ml: float, numNodes: int) -> int:
+    """graph.go:370-385"""
+    if ml == 0:
+        raise ValueError("ml must be greater than 0")
+    if numNodes == 0:
+        return 1
+    l = math.log(float(numNodes)) / math.log(1 / ml)
+    # Go math.Round: half away from zero
+    return int(math.floor(l + 0.5) if l >= 0 else math.ceil(l - 0.5)) + 1
+
+
+class Graph:
+    """graph.go:305-332.  Public mutable fields: Distance, Rng, M, Ml, EfSearch."""
+
+    def __init__(self, M=16, Ml=0.25, EfSearch=20, Distance=CosineDistance, Rng=None, device: int = 0,
+                 capacity: int = 0):
+        self.M, self.Ml, self.EfSearch, self.Distance = M, Ml, EfSearch, Distance
+        self.Rng = Rng if Rng is not None else GoRand()
+        self.device = device
+        self._capacity = capacity
+        self._h = None          # b200hnsw_t*
+        self._dim = 0
+        self._max_m = 0
+        self._keys: List[int] = []          # row -> key
+        self._row_of = {}                   # key -> row
+        self._vecs = np.zeros((0, 0), np.float32)  # host copy, grows by doubling
+        self.last_stats = None
+
+    # ---- lifetime -------------------------------------------------------------------------------------------
+    def _ensure_device(self, dim: int):
+        if self._h is not None:
+            return
+        cfg = _lib.Config(dim=dim, max_m=min(max(self.M, 1), _lib.MAX_M), device=self.device, reserved=0,
+                          capacity=self._capacity)
+        h = C.c_void_p()
+        _lib.check(_lib.lib().b200hnsw_create(C.byref(cfg), C.byref(h)))
+        self._h, self._dim, self._max_m = h, dim, cfg.max_m
+        self._vecs = np.zeros((max(self._capacity, 1024), dim), np.float32)
+
+    def close(self):
+        if self._h is not None:
+            _lib.lib().b200hnsw_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- graph.go:916-937 ---------------------------------------------------------------------------------------
+    def Validate(self):
+        if self.M <= 0:
+            raise ValueError(f"M must be greater than 0, got {self.M}")
+        if self.Ml <= 0 or self.Ml >= 1:
+            raise ValueError(f"Ml must be between 0 and 1 (exclusive), got {self.Ml:f}")
+        if self.EfSearch <= 0:
+            raise ValueError(f"EfSearch must be greater than 0, got {self.EfSearch}")
+        if self.Distance is None:
+            raise ValueError("Distance function must be set")
+
+    def Len(self) -> int:
+        return 0 if self._h is None else int(_lib.lib().b200hnsw_len(self._h))
+
+    def Dims(self) -> int:
+        return self._dim if self.Len() > 0 else 0
+
+    def Lookup(self, key):
+        row = self._row_of.get(key)
+        if row is None:
+            return None, False
+        return self._vecs[row], True
+
+    def Topography(self) -> List[int]:
+        """analyzer.go: nodes per layer."""
+        if self._h is None:
+            return []
+        L = _lib.lib()
+        return [int(L.b200hnsw_layer_size(self._h, l)) for l in range(L.b200hnsw_layers(self._h))]
+
+    # ---- graph.go:388-417 -----------------------------------------------------------------------------------------
+    def randomLevel(self) -> int:
+        mx = 1
+        if self._h is not None and _lib.lib().b200hnsw_layers(self._h) > 0:
+            if self.Ml == 0:
+                raise ValueError("(*Graph).Ml must be greater than 0")
+            mx = maxLevel(self.Ml, self.Len())
+        for level in range(mx):
+            if self.Rng is None:
+                self.Rng = GoRand()
+            if self.Rng.Float64() > self.Ml:
+                return level
+        return mx
+
+    # ---- Add / BatchAdd ---------------------------------------------------------------------------------------------
+    def _store_host(self, keys: Sequence[int], vecs: np.ndarray):
+        n0 = len(self._keys)
+        need = n0 + len(keys)
+        if need > self._vecs.shape[0]:
+            grown = np.zeros((max(need, 2 * self._vecs.shape[0]), self._dim), np.float32)
+            grown[:n0] = self._vecs[:n0]
+            self._vecs = grown
+        self._vecs[n0:need] = vecs
+        for i, k in enumerate(keys):
+            self._row_of[k] = n0 + i
+            self._keys.append(k)
+
+    def _draw_levels(self, n: int) -> np.ndarray:
+        """randomLevel() for n consecutive insertions: the bound maxLevel(Ml, len(layer0)) grows as nodes land."""
+        out = np.empty(n, dtype=np.int32)
+        have_layers = self._h is not None and _lib.lib().b200hnsw_layers(self._h) > 0
+        size0 = self.Len()
+        for i in range(n):
+            mx = maxLevel(self.Ml, size0) if have_layers else 1
+            lvl = mx
+            for level in range(mx):
+                if self.Rng.Float64() > self.Ml:
+                    lvl = level
+                    break
+            out[i] = lvl
+            have_layers = True
+            size0 += 1
+        return out
+
+    def BatchAdd(self, nodes: Iterable[Node], levels: Optional[Sequence[int]] = None):
+        """graph.go:942-1042.  `levels` (testing hook) replaces the Rng draws."""
+        self.Validate()
+        nodes = list(nodes)
+        if not nodes:
+            return
+        metric = metric_of(self.Distance)
+        vecs = [np.asarray(nd.Value, dtype=np.float32).reshape(-1) for nd in nodes]
+        dim0 = self._dim if self.Len() > 0 else len(vecs[0])
+        for v in vecs:
+            if len(v) != dim0:  # graph.go:450-455
+                raise ValueError(f"embedding dimension mismatch: {dim0} != {len(v)}")
+        self._ensure_device(dim0)
+        if self.M > self._max_m:
+            raise ValueError(f"M={self.M} exceeds the device list stride {self._max_m} fixed at the first Add")
+        keys = []
+        for nd in nodes:
+            k = nd.Key
+            if not isinstance(k, (int, np.integer)):
+                raise TypeError("device path orders neighbours by int64 keys; non-integer keys are not supported")
+            if k in self._row_of or k in keys:
+                # graph.go:1016-1024 deletes the old node first; Delete is SURVEY.md row N3 (not built yet)
+                raise NotImplementedError(f"key {k} already present: replacing a node needs Delete (not built yet)")
+            keys.append(int(k))
+        lv = np.asarray(levels, dtype=np.int32) if levels is not None else self._draw_levels(len(nodes))
+        V = np.ascontiguousarray(np.stack(vecs), dtype=np.float32)
+        K = np.asarray(keys, dtype=np.int64)
+        st = _lib.Stats()
+        _lib.check(_lib.lib().b200hnsw_add_batch(self._h, V.ctypes.data_as(_lib.f32p), K.ctypes.data_as(_lib.i64p),
+                                                 lv.ctypes.data_as(_lib.i32p), len(keys), self.M, self.EfSearch,
+                                                 metric, C.byref(st)))
+        self.last_stats = st.as_dict()
+        self._store_host(keys, V)
+
+    def Add(self, *nodes: Node, levels: Optional[Sequence[int]] = None):
+        """graph.go:437-531 (same body as BatchAdd; the reference's Add deadlocks on a duplicate key, F9)."""
+        self.BatchAdd(nodes, levels=levels)
+
+    # ---- load a graph built elsewhere (Import, or the oracle in tests) ----------------------------------------------
+    def load_flat(self, vectors, keys, levels, layer_lists, entries=None):
+        """layer_lists[l] = (rows[N_l], ptr[N_l+1], nbr[...]) CSR of layer l.  Replaces the content."""
+        vectors = np.ascontiguousarray(vectors, dtype=np.float32)
+        n, dim = vectors.shape
+        self._ensure_device(dim)
+        keys = np.ascontiguousarray(keys, dtype=np.int64)
+        levels = np.ascontiguousarray(levels, dtype=np.int32)
+        nl = len(layer_lists)
+        sizes = np.array([len(r) for r, _, _ in layer_lists], dtype=np.int64)
+        rows = np.ascontiguousarray(np.concatenate([np.asarray(r, np.int32) for r, _, _ in layer_lists])
+                                    if nl else np.zeros(0, np.int32))
+        ptr = np.ascontiguousarray(np.concatenate([np.asarray(p, np.int64) for _, p, _ in layer_lists])
+                                   if nl else np.zeros(0, np.int64))
+        nbr = np.ascontiguousarray(np.concatenate([np.asarray(b, np.int32) for _, _, b in layer_lists])
+                                   if nl else np.zeros(0, np.int32))
+        ent = None
+        if entries is not None:
+            ent = np.ascontiguousarray(entries, dtype=np.int32)
+        _lib.check(_lib.lib().b200hnsw_load(
+            self._h, n, vectors.ctypes.data_as(_lib.f32p), keys.ctypes.data_as(_lib.i64p),
+            levels.ctypes.data_as(_lib.i32p), nl, ent.ctypes.data_as(_lib.i32p) if ent is not None else None,
+            sizes.ctypes.data_as(_lib.i64p), rows.ctypes.data_as(_lib.i32p), ptr.ctypes.data_as(_lib.i64p),
+            nbr.ctypes.data_as(_lib.i32p)))
+        self._keys = [int(k) for k in keys]
+        self._row_of = {k: i for i, k in enumerate(self._keys)}
+        self._vecs = vectors.copy()
+
+    def entries(self) -> np.ndarray:
+        L = _lib.lib()
+        return np.array([L.b200hnsw_entry(self._h, l) for l in range(L.b200hnsw_layers(self._h))], dtype=np.int32)
+
+    def set_entry(self, layer: int, row: int):
+        _lib.check(_lib.lib().b200hnsw_set_entry(self._h, layer, row))
+
+    def neighbors(self, layer: int):
+        """(nbr[N][max_m] rows padded with -1, member[N]) for a layer -- used by Export / Analyzer / parity tests."""
+        n = len(self._keys)
+        nbr = np.empty((n, self._max_m), dtype=np.int32)
+        mem = np.empty(n, dtype=np.uint8)
+        _lib.check(_lib.lib().b200hnsw_get_neighbors(self._h, layer, 0, n, nbr.ctypes.data_as(_lib.i32p),
+                                                     mem.ctypes.data_as(_lib.u8p)))
+        return nbr, mem.astype(bool)
+
+    # ---- Search / BatchSearch -----------------------------------------------------------------------------------------
+    def search_rows(self, queries, k: int, ef: Optional[int] = None, mode: int = _lib.MODE_REFERENCE, entries=None):
+        """Raw device call: (rows[B,k], dists[B,k], counts[B]) in the reference's heap-array order."""
+        q = np.ascontiguousarray(queries, dtype=np.float32)
+        if q.ndim == 1:
+            q = q.reshape(1, -1)
+        B = q.shape[0]
+        rows = np.empty((B, k), dtype=np.int32)
+        dists = np.empty((B, k), dtype=np.float32)
+        counts = np.empty(B, dtype=np.int32)
+        st = _lib.Stats()
+        ent = None if entries is None else np.ascontiguousarray(entries, dtype=np.int32)
+        _lib.check(_lib.lib().b200hnsw_search_batch(
+            self._h, q.ctypes.data_as(_lib.f32p), B, k, ef if ef is not None else self.EfSearch,
+            metric_of(self.Distance), mode, ent.ctypes.data_as(_lib.i32p) if ent is not None else None,
+            rows.ctypes.data_as(_lib.i32p), dists.ctypes.data_as(_lib.f32p), counts.ctypes.data_as(_lib.i32p),
+            C.byref(st)))
+        self.last_stats = st.as_dict()
+        return rows, dists, counts
+
+    def _nodes(self, rows, count) -> List[Node]:
+        return [Node(self._keys[r], self._vecs[r]) for r in rows[:count]]
+
+    def Search(self, near, k: int) -> List[Node]:
+        """graph.go:534-625"""
+        self.Validate()
+        if k <= 0:
+            raise ValueError(f"k must be greater than 0, got {k}")
+        near = np.asarray(near, dtype=np.float32).reshape(-1)
+        if self.Len() > 0 and self.Dims() != len(near):
+            raise ValueError(f"embedding dimension mismatch: {self.Dims()} != {len(near)}")
+        if self.Len() == 0:
+            return None  # graph.go:554-556: (nil, nil)
+        ef = self.EfSearch
+        # graph.go:563-569: the reference's hard-wired "dog query" test hack doubles efSearch
+        is_dog = len(near) == 3 and near[0] == np.float32(1.0) and near[1] == np.float32(0.2) and \
+            near[2] == np.float32(0.1)
+        if is_dog:
+            ef *= 2
+        rows, _, counts = self.search_rows(near, k, ef)
+        out = self._nodes(rows[0], counts[0])
+        if is_dog and len(out) == 3 and all(nd.Key != 3 for nd in out) and 3 in self._row_of:
+            out[2] = Node(3, self._vecs[self._row_of[3]])  # graph.go:595-619
+        return out
+
+    def BatchSearch(self, queries, k: int) -> List[List[Node]]:
+        """graph.go:1047-1110 (no dog hack in the reference's batch loop)."""
+        self.Validate()
+        if k <= 0:
+            raise ValueError(f"k must be greater than 0, got {k}")
+        qs = [np.asarray(q, dtype=np.float32).reshape(-1) for q in queries]
+        if self.Len() > 0:
+            for i, q in enumerate(qs):
+                if self.Dims() != len(q):
+                    raise ValueError(f"embedding dimension mismatch for query {i}: {self.Dims()} != {len(q)}")
+        if self.Len() == 0:
+            return [None] * len(qs)
+        if not qs:
+            return []
+        rows, _, counts = self.search_rows(np.stack(qs), k)
+        return [self._nodes(rows[i], counts[i]) for i in range(len(qs))]
+
+    def ParallelSearch(self, near, k: int, numWorkers: int = 0) -> List[Node]:
+        """graph.go:631-826.  The reference's goroutine fan-out consumes results in channel-arrival order
+        (non-deterministic); the deterministic branch (graph.go:791-809) is Search, which is what runs here."""
+        return self.Search(near, k)
+
+
+def NewGraph(**kw) -> Graph:
+    """graph.go:340-349: M=16, Ml=0.25, CosineDistance, EfSearch=20."""
+    return Graph(M=16, Ml=0.25, EfSearch=20, Distance=CosineDistance, **kw)
+
+
+def NewGraphWithConfig(m: int, ml: float, efSearch: int, distance, **kw) -> Graph:
+    """graph.go:352-366: validates and returns the error."""
+    g = Graph(M=m, Ml=ml, EfSearch=efSearch, Distance=distance, **kw)
+    g.Validate()
+    return g

@@ -1,0 +1,166 @@
+/*
+ * b200hnsw.h -- C ABI of the B200-native replacement for TFMV/hnsw's data-parallel hot path.
+ *
+ * The reference has no FFI seam; the seam is its exported Go API.  Each entry point below names the Go
+ * method(s) whose body it replaces (file:line into the reference tree).  The Go host keeps validation,
+ * locking (sync.RWMutex), the key <-> row mapping, the level RNG and the test hacks (graph.go:563-569,
+ * 595-619); see INTEGRATION.md for the cgo binding.  Signatures use plain pointers and sizes only.
+ *
+ * Conventions
+ *   - A node is a dense int32 ROW (insertion order).  keys[row] is an int64 that orders rows exactly as the
+ *     reference's K orders keys (cmp.Ordered); neighbour lists are kept sorted by it because the reference
+ *     expands neighbours in ascending key order (graph.go:137-138).
+ *   - A node added with level L is a member of layers 0..L (graph.go:510-515).
+ *   - Every function returns 0 on success or a negative B200HNSW_ERR_*; b200hnsw_last_error() gives text.
+ *     Nothing aborts or throws across the boundary.  There is NO CPU fallback: without a CUDA device every
+ *     compute call fails with B200HNSW_ERR_CUDA.
+ *   - Host-pointer calls copy inputs before returning (cgo may not retain Go pointers).  *_device variants
+ *     take device pointers plus a cudaStream_t (as void*) and are asynchronous on that stream.
+ *   - Search calls may run concurrently from several host threads (they only read the index); calls that
+ *     mutate (add, load, reserve) must be serialised by the caller, as the reference's write lock does.
+ */
+#ifndef B200HNSW_H
+#define B200HNSW_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200HNSW_ABI_VERSION 1
+
+enum {
+  B200HNSW_OK = 0,
+  B200HNSW_ERR_BAD_ARG = -1,
+  B200HNSW_ERR_OOM = -2,
+  B200HNSW_ERR_CUDA = -3,
+  B200HNSW_ERR_UNSUPPORTED = -4,
+  B200HNSW_ERR_VISITED_OVERFLOW = -5, /* a layer search visited more nodes than the scratch allows */
+  B200HNSW_ERR_STATE = -6
+};
+
+/* distance.go:25-28: the two registered DistanceFuncs.  Any other Go func => the host returns an error. */
+enum { B200HNSW_EUCLIDEAN = 0, B200HNSW_COSINE = 1 };
+
+/* B200HNSW_MODE_REFERENCE reproduces layerNode.search bit for bit (graph.go:94-170, including its
+ * first-non-improving-hop termination).  B200HNSW_MODE_EXTENDED is NOT the reference: textbook HNSW
+ * termination with a true ef-bounded result set, offered because the reference's rule cannot reach high
+ * recall on high-dimensional data.  Results of the two modes are never mixed. */
+enum { B200HNSW_MODE_REFERENCE = 0, B200HNSW_MODE_EXTENDED = 1 };
+
+#define B200HNSW_MAX_LAYERS 64
+#define B200HNSW_MAX_M 64
+#define B200HNSW_MAX_K 256
+#define B200HNSW_MAX_EF 1024
+
+typedef struct b200hnsw b200hnsw_t;
+typedef struct b200exact b200exact_t;
+
+typedef struct {
+  int32_t dim;      /* len(Vector); fixed by the first Add in the reference (graph.go:450-455)            */
+  int32_t max_m;    /* largest Graph.M that will be used; neighbour lists have this many slots (<=64)      */
+  int32_t device;   /* CUDA device ordinal                                                                 */
+  int32_t reserved; /* must be 0                                                                           */
+  int64_t capacity; /* rows to reserve up front (grows by doubling when exceeded); 0 = default             */
+} b200hnsw_config;
+
+/* counters of one search batch; E and H are the quantities the roofline bytes are computed from */
+typedef struct {
+  int64_t dist_evals;  /* E: distance evaluations (graph.go:146)                      */
+  int64_t expansions;  /* H: candidates popped and expanded (graph.go:127-139)        */
+  int64_t nbr_reads;   /* neighbour ids read                                           */
+  float kernel_ms;     /* device time of the traversal kernel (host-pointer calls)     */
+  int32_t launches;    /* kernels launched by the call                                 */
+} b200hnsw_stats;
+
+int b200hnsw_abi_version(void);
+/* text of the last error raised on the calling thread ("" if none) */
+const char *b200hnsw_last_error(void);
+
+/* ---- lifetime: NewGraph / NewGraphWithConfig (graph.go:340-366) create the host object; this creates its
+ *      device mirror ------------------------------------------------------------------------------------ */
+int b200hnsw_create(const b200hnsw_config *cfg, b200hnsw_t **out);
+void b200hnsw_destroy(b200hnsw_t *h);
+int b200hnsw_reserve(b200hnsw_t *h, int64_t rows);
+
+/* Graph.Len (graph.go:829-838), len(g.layers), layer.size (graph.go:260-265), layer.entry (graph.go:246-258:
+ * "any node of the layer"; here the first node inserted into it unless overridden). */
+int64_t b200hnsw_len(const b200hnsw_t *h);
+int32_t b200hnsw_layers(const b200hnsw_t *h);
+int64_t b200hnsw_layer_size(const b200hnsw_t *h, int32_t layer);
+int32_t b200hnsw_entry(const b200hnsw_t *h, int32_t layer);
+int b200hnsw_set_entry(b200hnsw_t *h, int32_t layer, int32_t row);
+
+/* ---- Graph.Import (encode.go:180-262) / a graph built by the reference, flattened by the host ------------
+ * n rows; vectors[n][dim]; keys[n]; levels[n]; entries[n_layers] (-1 = first member).
+ * Per layer l (0..n_layers-1), lists are given as CSR over ALL n rows of that layer's members:
+ *   layer_rows  : concatenated member rows, layer_sizes[l] per layer (layer 0 must list every row)
+ *   layer_ptr   : concatenated offsets, layer_sizes[l]+1 per layer, each starting at 0 for its layer
+ *   layer_nbr   : concatenated neighbour rows
+ * Lists longer than max_m are rejected; lists are re-sorted by key on load. Replaces the current content. */
+int b200hnsw_load(b200hnsw_t *h, int64_t n, const float *vectors, const int64_t *keys, const int32_t *levels,
+                  int32_t n_layers, const int32_t *entries, const int64_t *layer_sizes, const int32_t *layer_rows,
+                  const int64_t *layer_ptr, const int32_t *layer_nbr);
+
+/* ---- Graph.Export (encode.go:133-174) / Analyzer: read the device graph back ------------------------------ */
+int b200hnsw_get_rows(const b200hnsw_t *h, int64_t first, int64_t count, float *vectors, int64_t *keys,
+                      int32_t *levels);
+/* neighbour rows of `count` rows starting at `first` in `layer`, padded with -1 to max_m per row; rows that are
+ * not members of the layer get all -1 and member[i]=0. */
+int b200hnsw_get_neighbors(const b200hnsw_t *h, int32_t layer, int64_t first, int64_t count, int32_t *nbr,
+                           uint8_t *member);
+
+/* ---- Graph.Search / Graph.BatchSearch / Graph.ParallelSearch (graph.go:534-625, 1047-1110, 631-826) ---------
+ * One traversal per query, all B in one launch.  out_rows/out_dists are [B][k] in the reference's order, i.e.
+ * the raw heap array of the layer-0 result queue (graph.go:169, 588-593: index 0 is the nearest, the rest in
+ * binary-heap layout); unused slots are -1 / NaN; out_counts[b] = len(result).  entries may be NULL.
+ * k <= B200HNSW_MAX_K, ef <= B200HNSW_MAX_EF.  An empty graph yields counts of 0 (graph.go:554-556). */
+int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_t k, int32_t ef, int32_t metric,
+                          int32_t mode, const int32_t *entries, int32_t *out_rows, float *out_dists,
+                          int32_t *out_counts, b200hnsw_stats *stats);
+int b200hnsw_search_batch_device(b200hnsw_t *h, const float *d_queries, int64_t B, int32_t k, int32_t ef,
+                                 int32_t metric, int32_t mode, const int32_t *entries, int32_t *d_out_rows,
+                                 float *d_out_dists, int32_t *d_out_counts, int64_t *d_counters /*[8] or NULL*/,
+                                 void *stream);
+
+/* ---- Graph.Add / Graph.BatchAdd (graph.go:437-531, 942-1042) ------------------------------------------------
+ * Inserts n nodes in input order with the reference's semantics: per layer top->0 search(k=M, ef) from the
+ * elevator, then for every result (heap-array order) addNeighbor both ways with evict-worst + replenish
+ * (graph.go:41-81, 172-219; replenish always scores with cosine).  levels[i] is the host's randomLevel() draw
+ * (graph.go:388-417).  Keys must be new (the host deletes an existing key first, graph.go:1016-1024).
+ * Rows are assigned len()..len()+n-1. */
+int b200hnsw_add_batch(b200hnsw_t *h, const float *vectors, const int64_t *keys, const int32_t *levels, int64_t n,
+                       int32_t m, int32_t ef, int32_t metric, b200hnsw_stats *stats);
+
+/* ---- multi-GPU: merge G per-shard result lists per query into one top-k (no reference counterpart; tie order =
+ *      lower shard first, the stable order of hybrid/adapter.go:264-292).  Inputs [G][B][k] ascending-sorted
+ *      per shard or heap-ordered (sorted_in=0); ids are int64 global ids.  Device pointers. ----------------- */
+int b200hnsw_merge_topk_device(int32_t device, int32_t G, int64_t B, int32_t k, const float *d_dists,
+                               const int64_t *d_ids, const int32_t *d_counts, int32_t sorted_in, float *d_out_dists,
+                               int64_t *d_out_ids, int32_t *d_out_counts, void *stream);
+
+/* ---- hybrid.ExactIndex (hnsw-extensions/hybrid/exact.go:13-160) --------------------------------------------- */
+int b200exact_create(int32_t dim, int32_t metric, int32_t device, int64_t capacity, b200exact_t **out);
+void b200exact_destroy(b200exact_t *x);
+int64_t b200exact_len(const b200exact_t *x); /* rows ever added minus removed */
+/* ExactIndex.Add / BatchAdd (exact.go:27-58): copies n vectors; rows are assigned in order; *first_row out */
+int b200exact_add_batch(b200exact_t *x, const float *vectors, int64_t n, int64_t *first_row);
+/* ExactIndex.Delete / BatchDelete (exact.go:114-145): tombstones rows */
+int b200exact_remove(b200exact_t *x, const int64_t *rows, int64_t n);
+/* ExactIndex.Search (exact.go:61-111) for B queries: out_rows/out_dists [B][k] ascending by distance, ties in
+ * row order (the reference's order among ties is Go map order, i.e. unspecified); out_counts = min(k, len). */
+int b200exact_search_batch(b200exact_t *x, const float *queries, int64_t B, int32_t k, int64_t *out_rows,
+                           float *out_dists, int32_t *out_counts, b200hnsw_stats *stats);
+int b200exact_search_batch_device(b200exact_t *x, const float *d_queries, int64_t B, int32_t k, int64_t *d_out_rows,
+                                  float *d_out_dists, int32_t *d_out_counts, void *stream);
+
+/* EuclideanDistance / CosineDistance (distance.go:15-23) on the device, pairs (a[i], b[i]); host pointers.
+ * Exists so the distance KATs (distance_test.go:9-31) run through the same arithmetic as the kernels. */
+int b200hnsw_distance_batch(int32_t device, int32_t metric, const float *a, const float *b, int64_t n, int32_t dim,
+                            float *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,116 @@
+"""K1 parity: device Graph.Search / BatchSearch vs the oracle on identical graphs and queries.
+
+Bit-exact bar: rows, their heap-array order, counts AND distances (the device reproduces the oracle's canonical
+summation order), plus equal E/H counters ("device counters must equal them").
+"""
+import numpy as np
+import pytest
+
+from util import build_oracle_graph, flatten_oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def _device_graph(oracle, g, M, ef, metric):
+    import hnsw_b200
+    dist = hnsw_b200.EuclideanDistance if metric == oracle.EUCLIDEAN else hnsw_b200.CosineDistance
+    dg = hnsw_b200.Graph(M=M, Ml=0.25, EfSearch=ef, Distance=dist)
+    dg.load_flat(*flatten_oracle(g))
+    return dg
+
+
+def _assert_same(oracle, g, dg, Q, k, ef):
+    g.reset_counters()
+    o_rows, o_d, o_cnt, o_ctr = g.batch_search(Q, k, ef)
+    d_rows, d_d, d_cnt = dg.search_rows(Q, k, ef)
+    assert np.array_equal(o_cnt, d_cnt)
+    assert np.array_equal(o_rows, d_rows)
+    assert np.array_equal(o_d.view(np.uint32), d_d.view(np.uint32))  # bit-identical distances (NaN padding too)
+    st = dg.last_stats
+    assert st["dist_evals"] == o_ctr["dist_evals"]
+    assert st["expansions"] == o_ctr["expansions"]
+    assert st["nbr_reads"] == o_ctr["nbr_reads"]
+
+
+@pytest.mark.parametrize("n,d,M,ef,k,metric", [
+    (2000, 128, 16, 20, 10, 0),   # BASELINE config C1 shape (graph_benchmark_test.go), reduced N
+    (2000, 128, 16, 64, 10, 0),   # C2 parameters
+    (1500, 96, 16, 64, 10, 0),    # C4 dimension (24 chunks: partial warp)
+    (800, 768, 32, 64, 10, 1),    # C3 shape: cosine, M=32, 6 chunks per lane
+    (600, 1024, 16, 20, 5, 1),    # C5 dimension
+    (500, 3, 6, 20, 4, 0),        # tiny dims like the reference's unit tests
+    (300, 1, 6, 20, 4, 0),        # 1-D line graph (graph_test.go:86-133 shape)
+    (400, 200, 48, 30, 64, 0),    # M > 32 (two list rounds), k > ef
+])
+def test_batch_search_matches_oracle(oracle, n, d, M, ef, k, metric):
+    rng = np.random.default_rng(42)
+    X = rng.uniform(-1, 1, (n, d)).astype(np.float32)
+    g, _, _ = build_oracle_graph(oracle, X, M, 0.25, ef, metric)
+    dg = _device_graph(oracle, g, M, ef, metric)
+    Q = np.random.default_rng(43).uniform(-1, 1, (257, d)).astype(np.float32)
+    _assert_same(oracle, g, dg, Q, k, ef)
+    # stored points as queries: exact-zero distances and ties
+    _assert_same(oracle, g, dg, X[:64], k, ef)
+
+
+def test_layer_search_kat_on_device(oracle):
+    # graph_test.go:27-74 through the device: rows [4, 3] == Keys [5, 3]
+    import hnsw_b200
+    g = oracle.Graph(1, 6, oracle.EUCLIDEAN)
+    for mk in range(6):
+        g.put_node(mk, [float(mk)])
+    for nb in (1, 2, 3):
+        g.link(0, 0, nb)
+    for nb in (4, 5):
+        g.link(0, 3, nb)
+    dg = hnsw_b200.Graph(M=6, Ml=0.5, EfSearch=4, Distance=hnsw_b200.EuclideanDistance)
+    dg.load_flat(*flatten_oracle(g))
+    rows, dists, cnt = dg.search_rows([[4.0]], 2, 4)
+    assert cnt[0] == 2 and list(rows[0]) == [4, 3] and list(dists[0]) == [0.0, 1.0]
+
+
+def test_entry_override_and_k_larger_than_graph(oracle):
+    rng = np.random.default_rng(1)
+    X = rng.uniform(-1, 1, (50, 16)).astype(np.float32)
+    g, _, _ = build_oracle_graph(oracle, X, 8, 0.25, 20, 0)
+    dg = _device_graph(oracle, g, 8, 20, 0)
+    Q = rng.uniform(-1, 1, (16, 16)).astype(np.float32)
+    _assert_same(oracle, g, dg, Q, 100, 20)  # k > N: fewer than k results
+    # explicit entries (F5: the reference's entry is a random map element)
+    ent = g.entries().copy()
+    top = g.n_layers - 1
+    members = [r for r in range(50) if g.level(r) >= top]
+    ent[top] = members[-1]
+    for q in Q:
+        o_rows, o_d = g.search(q, 5, 20, entries=ent)
+        d_rows, d_d, d_cnt = dg.search_rows(q, 5, 20, entries=ent)
+        assert list(o_rows) == list(d_rows[0][:d_cnt[0]])
+
+
+def test_distance_kats_on_device():
+    # distance_test.go:9-31 through the device arithmetic
+    import hnsw_b200
+    assert hnsw_b200.EuclideanDistance([1, 2, 3], [4, 5, 6]) == np.float32(5.196152)
+    assert abs(hnsw_b200.CosineDistance([1, 1, 1], [0.8, 0.8, 0.8])) <= 1e-6
+    assert abs(hnsw_b200.CosineDistance([1, 0], [0, 1]) - 1) <= 1e-6
+    assert abs(hnsw_b200.CosineDistance([1, 0], [1, 0])) <= 1e-6
+
+
+def test_distance_bits_match_oracle(oracle):
+    from hnsw_b200.distance import distance_batch
+    rng = np.random.default_rng(9)
+    for d in (1, 3, 96, 128, 130, 768, 1024, 1536):
+        a = rng.standard_normal((64, d)).astype(np.float32)
+        b = rng.standard_normal((64, d)).astype(np.float32)
+        for metric in (0, 1):
+            dev = distance_batch(metric, a, b)
+            ref = np.array([oracle.distance(metric, a[i], b[i]) for i in range(64)], dtype=np.float32)
+            assert np.array_equal(dev.view(np.uint32), ref.view(np.uint32)), (d, metric)
+
+
+def test_empty_graph_and_errors():
+    import hnsw_b200
+    g = hnsw_b200.NewGraph()
+    assert g.Search([0.5, 0.5], 1) is None  # graph.go:554-556
+    with pytest.raises(ValueError, match="k must be greater than 0"):
+        g.Search([0.5], 0)

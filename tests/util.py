@@ -1,0 +1,57 @@
+"""Shared helpers for the parity tests: build graphs with the oracle, flatten them for the device."""
+import numpy as np
+
+
+def has_cuda():
+    try:
+        import torch
+        return torch.cuda.is_available()
+    except Exception:
+        return False
+
+
+def draw_levels(oracle, n, ml, seed):
+    """Level sequence with the reference's rule (graph.go:388-417) from a numpy stream."""
+    rng = np.random.default_rng(seed)
+    levels = np.empty(n, dtype=np.int32)
+    n_layers, size0 = 0, 0
+    for i in range(n):
+        lvl, _ = oracle.random_level(ml, n_layers, size0, rng.random(64))
+        levels[i] = lvl
+        n_layers = max(n_layers, lvl + 1)
+        size0 += 1
+    return levels
+
+
+def build_oracle_graph(oracle, X, M, ml, ef, metric, seed=44, keys=None, flavor=0):
+    n, d = X.shape
+    g = oracle.Graph(d, M, metric, flavor)
+    levels = draw_levels(oracle, n, ml, seed)
+    keys = np.arange(n, dtype=np.int64) if keys is None else np.asarray(keys, dtype=np.int64)
+    g.add_many(keys, X, levels, ef)
+    return g, keys, levels
+
+
+def flatten_oracle(g):
+    """Oracle graph -> (vectors, keys, levels, layer_lists, entries) as hnsw_b200.Graph.load_flat expects."""
+    n = len(g)
+    vec, keys, levels = g.dump()
+    layer_lists = []
+    for l in range(g.n_layers):
+        rows = np.nonzero(levels >= l)[0].astype(np.int32)
+        ptr = [0]
+        nbr = []
+        for r in rows:
+            nb = g.neighbors(l, int(r))
+            nbr.extend(nb.tolist())
+            ptr.append(len(nbr))
+        layer_lists.append((rows, np.asarray(ptr, np.int64), np.asarray(nbr, np.int32)))
+    return vec, keys, levels, layer_lists, g.entries()
+
+
+def recall_at_k(found_rows, truth_rows):
+    k = truth_rows.shape[1]
+    hits = 0
+    for f, t in zip(found_rows, truth_rows):
+        hits += len(set(int(x) for x in f if x >= 0) & set(int(x) for x in t))
+    return hits / (k * len(truth_rows))
