@@ -3,8 +3,8 @@
 // Max() is the LAST ARRAY SLOT (heap.go:89-91) and PopLast() == Remove(len-1) is a truncation (heap.go:73-75),
 // so both membership and order of the result depend on reproducing Go's sift sequences exactly.
 //
-// Every lane of the warp executes these functions with identical arguments (uniform control flow, broadcast
-// shared-memory reads, same-value writes), so no intra-warp synchronisation is needed around them.
+// One lane (lane 0) of the owning warp executes these; other lanes read the array only after a __syncwarp().
+// (Redundant execution by all 32 lanes is NOT safe: lanes are not guaranteed to stay in lockstep.)
 // Elements are (dist, id) packed in a uint2.  `less` is strict '<' on dist (graph.go:88-90).
 #pragma once
 #include <cuda_runtime.h>

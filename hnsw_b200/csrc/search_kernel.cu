@@ -47,7 +47,8 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) search_kernel(GraphView 
       if (layer > 0) {
         n = layer_search_ref<CPL, U>(g, layer, sp, 1, p.ef, p.metric, Q, C, R, V, ctr, lane);
         if (n < 0) break;
-        if (n > 0) elevator = R.id(0);    // graph.go:584
+        if (n > 0) elevator = R.id(0);    // graph.go:584 (array published by the __syncwarp in layer_search_ref)
+        __syncwarp();                     // all lanes have read R before lane 0 reuses it
         n = 0;
         continue;
       }
