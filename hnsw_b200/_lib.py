@@ -30,6 +30,7 @@ class Config(C.Structure):
 
 class Stats(C.Structure):
     _fields_ = [("dist_evals", C.c_int64), ("expansions", C.c_int64), ("nbr_reads", C.c_int64),
+                ("evict_evals", C.c_int64), ("replenish_evals", C.c_int64), ("evictions", C.c_int64),
                 ("kernel_ms", C.c_float), ("launches", C.c_int32)]
 
     def as_dict(self):

@@ -290,8 +290,14 @@ int b200hnsw_load(b200hnsw_t *h, int64_t n, const float *vectors, const int64_t 
     h->release(c);
     return code;
   };
+  // wipe the whole reserved area: later Adds rely on untouched rows being zero vectors / empty lists
+  if (cudaMemsetAsync(h->d.vec, 0, sizeof(float) * (size_t)h->d.cap * rf, s) != cudaSuccess ||
+      cudaMemsetAsync(h->d.adj0, 0xff, sizeof(int32_t) * (size_t)h->d.cap * M, s) != cudaSuccess ||
+      cudaMemsetAsync(h->d.upper_off, 0xff, sizeof(int32_t) * (size_t)h->d.cap, s) != cudaSuccess ||
+      cudaMemsetAsync(h->d.adjU, 0xff, sizeof(int32_t) * (size_t)h->d.capU * M, s) != cudaSuccess)
+    return fail(cuda_fail(cudaGetLastError(), "load wipe"));
   if (n > 0) {
-    if (cudaMemsetAsync(h->d.vec, 0, sizeof(float) * (size_t)n * rf, s) != cudaSuccess ||
+    if (
         cudaMemcpy2DAsync(h->d.vec, sizeof(float) * rf, vectors, sizeof(float) * dim, sizeof(float) * dim, (size_t)n,
                           cudaMemcpyHostToDevice, s) != cudaSuccess ||
         cudaMemcpyAsync(h->d.keys, keys, sizeof(int64_t) * (size_t)n, cudaMemcpyHostToDevice, s) != cudaSuccess ||

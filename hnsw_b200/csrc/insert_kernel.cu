@@ -1,0 +1,675 @@
+// insert_kernel.cu -- K2: Graph.Add / Graph.BatchAdd (graph.go:437-531, 942-1042) with the reference's exact
+// sequential semantics: nodes are inserted one after the other, each seeing every link of its predecessors.
+//
+// One persistent CTA walks the batch in input order.  Per node and per layer (top -> 0):
+//   warp 0   : layerNode.search(k=M, ef) from the elevator -- the same device function as K1 (layer_search.cuh)
+//   all warps: for every result in heap-array order, addNeighbor both ways (graph.go:516-520):
+//              sorted insert; on overflow the M+1 distances of the eviction scan (graph.go:60-71) are evaluated
+//              one per warp, the worst is dropped with its back-link, and replenish (graph.go:172-219) scores
+//              the neighbours-of-neighbours with CosineDistance, all warps gathering rows in parallel.
+// Order-dependent decisions (scan order, tie rule `d > worst || worst == nil`, heap pop order) are taken by one
+// thread over the values the warps produced, so the result equals the oracle's bit for bit.
+// Bound: latency of dependent gathers (serial dependency between insertions), not bandwidth.
+#include <algorithm>
+#include <cstring>
+#include <vector>
+
+#include "index.hpp"
+
+namespace b200 {
+
+constexpr int INS_WARPS = 16;
+constexpr int INS_THREADS = INS_WARPS * 32;
+
+struct InsertParams {
+  long long first_row;
+  int n;                   // nodes in this batch
+  const int32_t *levels;   // [n] device
+  int m, ef, metric;
+  int n_layers;
+  int entries[B200HNSW_MAX_LAYERS];
+  int *state_out;                 // [1 + MAX_LAYERS]: n_layers, entries
+  unsigned long long *counters;   // [8]: evals, expansions, nbr_reads, evict_evals, replenish_evals, evictions
+  int *error;
+  int heap_c, heap_r, vis_cap;    // search scratch (uint2 slots, uint2 slots, u32 entries)
+  int cand_cap, rep_cap;          // replenish candidates (<= M*M) and its visited table (power of two)
+};
+
+struct MutGraph {
+  float4 *vec;
+  int64_t *keys;
+  int32_t *adj0;
+  int32_t *adjU;
+  int32_t *upper_off;
+  int32_t row_chunks, M, dim;
+  __device__ __forceinline__ int32_t *list(int layer, int row) const {
+    if (layer == 0) return adj0 + (size_t)row * M;
+    return adjU + ((size_t)upper_off[row] + (layer - 1)) * M;
+  }
+};
+
+// shared-memory control block
+struct InsCtl {
+  int n_layers;
+  int elevator;
+  int cnt;        // neighbourhood size of the current layer search, -1 on overflow
+  int flag;       // overflow / continue flag of the current block-wide step
+  int tmp_len;    // entries in tmp list
+  int worst;      // evicted neighbour
+  int wl_len;     // degree of the node being replenished
+  int ncand;      // replenish candidates
+  int need_heap;  // replenish needs the exact heap (NaN present or more than one pop)
+  int abort_;
+  int entries[B200HNSW_MAX_LAYERS];
+};
+
+// ---- warp-level list helpers (lists: stride M, sorted by key, -1 padded) -----------------------------------------
+
+// load a list into shared memory; returns its degree (uniform over the warp)
+__device__ __forceinline__ int warp_load_list(const int32_t *lp, int M, int *dst, int lane) {
+  int deg = 0;
+  for (int base = 0; base < M; base += 32) {
+    int v = -1;
+    if (base + lane < M) v = lp[base + lane];
+    unsigned mk = __ballot_sync(FULL, v >= 0);
+    if (base + lane < M) dst[base + lane] = v;
+    deg += __popc(mk);
+    if (mk != FULL) break;
+  }
+  __syncwarp();
+  return deg;
+}
+
+// write `len` entries from shared memory, pad the rest of the stride with -1
+__device__ __forceinline__ void warp_store_list(int32_t *lp, int M, const int *src, int len, int lane) {
+  for (int i = lane; i < M; i += 32) lp[i] = i < len ? src[i] : -1;
+}
+
+// sorted insert of x into the shared-memory list l[0..deg): returns new degree (unchanged if x is present: Go map
+// overwrite, graph.go:50).  Executed by one warp; the result is in l[].
+__device__ __forceinline__ int warp_sorted_insert(int *l, int deg, int x, const int64_t *keys, int lane) {
+  long long kx = keys[x];
+  int pos = 0;
+  bool present = false;
+  for (int base = 0; base < deg; base += 32) {
+    int i = base + lane;
+    int v = i < deg ? l[i] : -1;
+    bool lt = false;
+    if (v >= 0) {
+      present = present || (v == x);
+      lt = keys[v] < kx;
+    }
+    pos += __popc(__ballot_sync(FULL, lt));
+  }
+  if (__any_sync(FULL, present)) return deg;
+  // shift right from the end (single pass, each lane moves its element after all have read)
+  int moved[2];
+  int cntm = 0;
+  for (int i = pos + lane; i < deg; i += 32) moved[cntm++] = l[i];
+  __syncwarp();
+  cntm = 0;
+  for (int i = pos + lane; i < deg; i += 32) l[i + 1] = moved[cntm++];
+  if (lane == 0) l[pos] = x;
+  __syncwarp();
+  return deg + 1;
+}
+
+// remove x from l[0..deg) if present; returns new degree
+__device__ __forceinline__ int warp_list_remove(int *l, int deg, int x, int lane) {
+  int pos = -1;
+  for (int base = 0; base < deg; base += 32) {
+    int i = base + lane;
+    bool hit = i < deg && l[i] == x;
+    unsigned mk = __ballot_sync(FULL, hit);
+    if (mk) {
+      pos = base + __ffs(mk) - 1;
+      break;
+    }
+  }
+  if (pos < 0) return deg;
+  int moved[2];
+  int cntm = 0;
+  for (int i = pos + 1 + lane; i < deg; i += 32) moved[cntm++] = l[i];
+  __syncwarp();
+  cntm = 0;
+  for (int i = pos + 1 + lane; i < deg; i += 32) l[i - 1] = moved[cntm++];
+  __syncwarp();
+  return deg - 1;
+}
+
+// ---- block-wide state -------------------------------------------------------------------------------------------
+template <int CPL, int U>
+struct Inserter {
+  MutGraph g;
+  InsertParams p;
+  InsCtl *ctl;
+  int *nbh;        // [M]   neighbourhood rows (heap-array order)
+  int *tmp;        // [M+1] list being edited
+  float *tmpd;     // [M+1] eviction-scan distances
+  int *wl;         // [M+1] list of the node being replenished
+  int *cand;       // [cand_cap] replenish candidates in push order
+  float *candd;    // [cand_cap]
+  uint32_t *rep;   // [rep_cap] replenish visited table
+  GoHeap C, R;
+  Visited V;
+  int tid, lane, warp;
+  unsigned long long c_evict, c_repl, c_evictions;  // thread-local counters (summed at the end)
+
+  // distance(row = a, query = b) for a set of rows against one "query" row, warps striding over the items
+  __device__ __forceinline__ void block_distances(const int *ids, int n, int qrow, int metric, float *out) {
+    QueryRegs<CPL> Q;
+    load_query<CPL>(Q, reinterpret_cast<const float *>(g.vec + (size_t)qrow * g.row_chunks), g.dim, g.row_chunks,
+                    lane);
+    for (int base = warp * U; base < n; base += INS_WARPS * U) {
+      float4 rows[U][CPL];
+#pragma unroll
+      for (int u = 0; u < U; u++)
+        if (base + u < n) load_row<CPL>(rows[u], g.vec + (size_t)ids[base + u] * g.row_chunks, g.row_chunks, lane);
+#pragma unroll
+      for (int u = 0; u < U; u++)
+        if (base + u < n) {
+          float d = finish_distance<CPL>(rows[u], Q, metric);
+          if (lane == 0) out[base + u] = d;
+        }
+    }
+  }
+
+  // layerNode.replenish(m) -- graph.go:172-219; always CosineDistance.  Block-wide; ends with a barrier.
+  __device__ void replenish(int layer, int w) {
+    const int m = p.m, M = g.M;
+    int32_t *lw = g.list(layer, w);
+    __syncthreads();  // every thread has finished reading the control block of the previous step
+    for (int i = tid; i < p.rep_cap; i += INS_THREADS) rep[i] = ~0u;
+    if (warp == 0) {
+      int deg = warp_load_list(lw, M, wl, lane);
+      if (lane == 0) {
+        ctl->wl_len = deg;
+        ctl->flag = deg < m;  // graph.go:173-175
+        ctl->ncand = 0;
+      }
+    }
+    __syncthreads();
+    if (!ctl->flag) return;
+    if (warp == 0) {
+      Visited RV{rep, (uint32_t)p.rep_cap - 1, 0};
+      const int deg = ctl->wl_len;
+      // graph.go:183-190: visited = {w} U neighbours(w)
+      if (lane == 0) RV.insert((uint32_t)w);
+      for (int i = lane; i < deg; i += 32) RV.insert((uint32_t)wl[i]);
+      __syncwarp();
+      // graph.go:193-210: neighbours of neighbours, ascending key order at both levels
+      int nc = 0;
+      for (int i = 0; i < deg; i++) {
+        const int32_t *ln = g.list(layer, wl[i]);
+        for (int base = 0; base < M; base += 32) {
+          int v = -1;
+          if (base + lane < M) v = ln[base + lane];
+          unsigned vm = __ballot_sync(FULL, v >= 0);
+          if (!vm) break;
+          bool fresh = v >= 0 && RV.insert((uint32_t)v);
+          unsigned fm = __ballot_sync(FULL, fresh);
+          if (fresh) cand[nc + __popc(fm & ((1u << lane) - 1))] = v;
+          nc += __popc(fm);
+          if (vm != FULL) break;
+        }
+      }
+      if (lane == 0) ctl->ncand = nc;
+    }
+    __syncthreads();
+    const int nc = ctl->ncand;
+    if (nc == 0) return;
+    block_distances(cand, nc, w, 1 /*cosine*/, candd);  // CosineDistance(candidate.Value, n.Value)
+    if (tid == 0) c_repl += nc;
+    __syncthreads();
+    if (warp == 0) {
+      // graph.go:213-218: pop best-first until the list is full.  The first pop of a min-heap filled by pushes is
+      // the first-pushed global minimum; that shortcut is exact when one pop suffices and no distance is NaN.
+      int deg = ctl->wl_len;
+      const int need = m - deg;
+      bool nan = false;
+      for (int i = lane; i < nc; i += 32) nan = nan || (candd[i] != candd[i]);
+      nan = __any_sync(FULL, nan);
+      if (need == 1 && !nan) {
+        float bd = __int_as_float(0x7f800000);
+        int bi = 0x7fffffff;
+        for (int i = lane; i < nc; i += 32) {
+          float d = candd[i];
+          if (d < bd || (d == bd && i < bi)) {
+            bd = d;
+            bi = i;
+          }
+        }
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) {
+          float od = __shfl_xor_sync(FULL, bd, off);
+          int oi = __shfl_xor_sync(FULL, bi, off);
+          if (od < bd || (od == bd && oi < bi)) {
+            bd = od;
+            bi = oi;
+          }
+        }
+        deg = warp_sorted_insert(wl, deg, cand[bi], g.keys, lane);
+      } else {
+        // exact heap emulation (lane 0) in the search heap C's storage is too small in general: use candd/cand
+        // in place as a binary heap built by successive pushes.
+        if (lane == 0) {
+          // build: push i-th element into heap of size i (arrays themselves are the heap storage)
+          for (int i = 1; i < nc; i++) {
+            float d = candd[i];
+            int id_ = cand[i];
+            int j = i;
+            while (j > 0) {
+              int pi = (j - 1) >> 1;
+              if (!(d < candd[pi])) break;
+              candd[j] = candd[pi];
+              cand[j] = cand[pi];
+              j = pi;
+            }
+            candd[j] = d;
+            cand[j] = id_;
+          }
+        }
+        __syncwarp();
+        int hn = nc;
+        while (hn > 0 && deg < m) {
+          int best = cand[0];
+          __syncwarp();
+          if (lane == 0) {  // container/heap.Pop
+            int n = --hn;
+            float md = candd[n];
+            int mid = cand[n];
+            int i = 0;
+            for (;;) {
+              int j1 = 2 * i + 1;
+              if (j1 >= n) break;
+              int j = j1;
+              if (j1 + 1 < n && candd[j1 + 1] < candd[j1]) j = j1 + 1;
+              if (!(candd[j] < md)) break;
+              candd[i] = candd[j];
+              cand[i] = cand[j];
+              i = j;
+            }
+            if (n > 0) {
+              candd[i] = md;
+              cand[i] = mid;
+            }
+          }
+          hn = __shfl_sync(FULL, hn, 0);
+          __syncwarp();
+          deg = warp_sorted_insert(wl, deg, best, g.keys, lane);  // addNeighbor(best): len <= m, no overflow
+        }
+      }
+      warp_store_list(lw, M, wl, deg, lane);
+    }
+    __syncthreads();
+  }
+
+  // layerNode.addNeighbor(newNode, m, dist) on node n -- graph.go:41-81.  Block-wide; ends with a barrier.
+  __device__ void add_neighbor(int layer, int n, int x, int metric) {
+    const int m = p.m, M = g.M;
+    int32_t *ln = g.list(layer, n);
+    __syncthreads();  // every thread has finished reading the control block of the previous step
+    if (warp == 0) {
+      int deg = warp_load_list(ln, M, tmp, lane);
+      int nd = warp_sorted_insert(tmp, deg, x, g.keys, lane);  // graph.go:50
+      bool over = nd > m;                                      // graph.go:51-53
+      if (!over && nd != deg) warp_store_list(ln, M, tmp, nd, lane);
+      if (lane == 0) {
+        ctl->flag = over;
+        ctl->tmp_len = nd;
+      }
+    }
+    __syncthreads();
+    if (!ctl->flag) return;
+    const int len = ctl->tmp_len;  // m + 1
+    // graph.go:60-71: dist(neighbor.Value, n.Value) for every neighbour
+    block_distances(tmp, len, n, metric, tmpd);
+    __syncthreads();
+    if (tid == 0) {
+      c_evict += len;
+      float worst_d = __int_as_float(0xff800000);  // -Inf
+      int worst = -1, wpos = -1;
+      for (int i = 0; i < len; i++) {  // ascending key order stands in for Go's map order
+        float d = tmpd[i];
+        if (d > worst_d || worst < 0) {
+          worst_d = d;
+          worst = tmp[i];
+          wpos = i;
+        }
+      }
+      for (int i = wpos; i + 1 < len; i++) tmp[i] = tmp[i + 1];  // delete(n.neighbors, worst.Key)
+      ctl->worst = worst;
+      ctl->tmp_len = len - 1;
+      c_evictions++;
+    }
+    __syncthreads();
+    const int worst = ctl->worst;
+    if (warp == 0) warp_store_list(ln, M, tmp, ctl->tmp_len, lane);
+    if (warp == 1) {  // graph.go:75-78: delete the back-link
+      int32_t *lwp = g.list(layer, worst);
+      int dw = warp_load_list(lwp, M, wl, lane);
+      int nd = warp_list_remove(wl, dw, n, lane);
+      if (nd != dw) warp_store_list(lwp, M, wl, nd, lane);
+    }
+    __syncthreads();
+    replenish(layer, worst);  // graph.go:79
+  }
+};
+
+static __host__ __device__ inline size_t al16(size_t v) { return (v + 15) & ~(size_t)15; }
+
+struct InsLayout {
+  size_t ctl, heapC, heapR, vis, nbh, tmp, tmpd, wl, cand, candd, rep, total;
+  __host__ __device__ InsLayout(const InsertParams &p, int M) {
+    size_t o = 0;
+    ctl = o;   o += al16(sizeof(InsCtl));
+    heapC = o; o += al16(sizeof(uint2) * p.heap_c);
+    heapR = o; o += al16(sizeof(uint2) * p.heap_r);
+    vis = o;   o += al16(sizeof(uint32_t) * p.vis_cap);
+    nbh = o;   o += al16(sizeof(int) * (M + 1));
+    tmp = o;   o += al16(sizeof(int) * (M + 1));
+    tmpd = o;  o += al16(sizeof(float) * (M + 1));
+    wl = o;    o += al16(sizeof(int) * (M + 1));
+    cand = o;  o += al16(sizeof(int) * p.cand_cap);
+    candd = o; o += al16(sizeof(float) * p.cand_cap);
+    rep = o;   o += al16(sizeof(uint32_t) * p.rep_cap);
+    total = o;
+  }
+};
+
+template <int CPL, int U>
+__global__ void __launch_bounds__(INS_THREADS) insert_kernel(MutGraph g, InsertParams p) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const InsLayout lay(p, g.M);
+  Inserter<CPL, U> I;
+  I.g = g;
+  I.p = p;
+  I.ctl = reinterpret_cast<InsCtl *>(smem + lay.ctl);
+  I.nbh = reinterpret_cast<int *>(smem + lay.nbh);
+  I.tmp = reinterpret_cast<int *>(smem + lay.tmp);
+  I.tmpd = reinterpret_cast<float *>(smem + lay.tmpd);
+  I.wl = reinterpret_cast<int *>(smem + lay.wl);
+  I.cand = reinterpret_cast<int *>(smem + lay.cand);
+  I.candd = reinterpret_cast<float *>(smem + lay.candd);
+  I.rep = reinterpret_cast<uint32_t *>(smem + lay.rep);
+  I.C = GoHeap{reinterpret_cast<uint2 *>(smem + lay.heapC), 0};
+  I.R = GoHeap{reinterpret_cast<uint2 *>(smem + lay.heapR), 0};
+  I.V = Visited{reinterpret_cast<uint32_t *>(smem + lay.vis), (uint32_t)p.vis_cap - 1, 0};
+  I.tid = threadIdx.x;
+  I.lane = threadIdx.x & 31;
+  I.warp = threadIdx.x >> 5;
+  I.c_evict = I.c_repl = I.c_evictions = 0;
+  InsCtl *ctl = I.ctl;
+  const int tid = I.tid, lane = I.lane, warp = I.warp;
+  if (tid == 0) {
+    ctl->n_layers = p.n_layers;
+    ctl->abort_ = 0;
+    for (int l = 0; l < B200HNSW_MAX_LAYERS; l++) ctl->entries[l] = p.entries[l];
+  }
+  __syncthreads();
+  GraphView gv;
+  gv.vec = g.vec;
+  gv.adj0 = g.adj0;
+  gv.adjU = g.adjU;
+  gv.upper_off = g.upper_off;
+  gv.row_chunks = g.row_chunks;
+  gv.M = g.M;
+  gv.dim = g.dim;
+  SearchCounters sc{0, 0, 0};
+  bool aborted = false;
+  for (int j = 0; j < p.n && !aborted; j++) {
+    const int row = (int)(p.first_row + j);
+    const int L = p.levels[j];                          // randomLevel() drawn by the host (graph.go:457)
+    const int old_layers = ctl->n_layers;
+    const int top = (old_layers > L + 1 ? old_layers : L + 1) - 1;  // graph.go:462-464
+    if (tid == 0) ctl->elevator = -1;
+    __syncthreads();
+    for (int l = top; l >= 0 && !aborted; l--) {        // graph.go:475
+      if (l >= old_layers) {                            // graph.go:485-488: empty layer takes the node
+        if (tid == 0) ctl->entries[l] = row;
+        continue;
+      }
+      if (warp == 0) {
+        int sp = ctl->elevator >= 0 ? ctl->elevator : ctl->entries[l];  // graph.go:492-498
+        QueryRegs<CPL> Q;
+        load_query<CPL>(Q, reinterpret_cast<const float *>(g.vec + (size_t)row * g.row_chunks), g.dim, g.row_chunks,
+                        lane);
+        int cnt = layer_search_ref<CPL, U>(gv, l, sp, p.m, p.ef, p.metric, Q, I.C, I.R, I.V, sc, lane);  // :500
+        for (int i = lane; i < cnt; i += 32) I.nbh[i] = I.R.id(i);
+        if (lane == 0) {
+          ctl->cnt = cnt;
+          if (cnt > 0) ctl->elevator = I.R.id(0);       // graph.go:508
+        }
+      }
+      __syncthreads();
+      const int cnt = ctl->cnt;
+      if (cnt <= 0) {  // visited overflow (or the impossible empty neighbourhood, graph.go:501-505)
+        aborted = true;
+        if (tid == 0) *p.error = cnt < 0 ? 1 : 2;
+        break;
+      }
+      if (L >= l) {  // graph.go:510-521
+        for (int t = 0; t < cnt; t++) {
+          const int nb = I.nbh[t];
+          I.add_neighbor(l, nb, row, p.metric);
+          I.add_neighbor(l, row, nb, p.metric);
+        }
+      }
+      __syncthreads();
+    }
+    if (tid == 0 && L + 1 > old_layers) ctl->n_layers = L + 1;
+    __syncthreads();
+  }
+  if (tid == 0) {
+    p.state_out[0] = ctl->n_layers;
+    for (int l = 0; l < B200HNSW_MAX_LAYERS; l++) p.state_out[1 + l] = ctl->entries[l];
+    atomicAdd(&p.counters[3], I.c_evict);
+    atomicAdd(&p.counters[4], I.c_repl);
+    atomicAdd(&p.counters[5], I.c_evictions);
+  }
+  if (warp == 0 && lane == 0) {
+    atomicAdd(&p.counters[0], sc.evals);
+    atomicAdd(&p.counters[1], sc.expansions);
+    atomicAdd(&p.counters[2], sc.nbr_reads);
+  }
+}
+
+static int pow2_at_least(int v) {
+  int r = 1;
+  while (r < v) r <<= 1;
+  return r;
+}
+
+template <int CPL, int U>
+static int launch_insert_t(b200hnsw *h, const MutGraph &g, InsertParams &p, cudaStream_t s) {
+  auto kern = insert_kernel<CPL, U>;
+  InsLayout lay(p, g.M);
+  if (lay.total > h->smem_optin) {
+    set_error("add: M=%d ef=%d need %zu B of shared memory (> %zu)", p.m, p.ef, lay.total, h->smem_optin);
+    return B200HNSW_ERR_UNSUPPORTED;
+  }
+  B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lay.total));
+  kern<<<1, INS_THREADS, lay.total, s>>>(g, p);
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
+static int launch_insert(b200hnsw *h, InsertParams &p, cudaStream_t s) {
+  MutGraph g;
+  g.vec = reinterpret_cast<float4 *>(h->d.vec);
+  g.keys = h->d.keys;
+  g.adj0 = h->d.adj0;
+  g.adjU = h->d.adjU;
+  g.upper_off = h->d.upper_off;
+  g.row_chunks = h->row_floats / 4;
+  g.M = h->M;
+  g.dim = h->cfg.dim;
+  p.heap_c = (p.ef + 2) & ~1;
+  p.heap_r = (p.m + 2) & ~1;
+  p.vis_cap = 1024;
+  p.cand_cap = p.m * p.m + 4;
+  p.rep_cap = pow2_at_least(2 * (p.m * p.m + p.m + 2));
+  int cpl = (g.row_chunks + 31) / 32;
+  switch (cpl) {
+    case 1: return launch_insert_t<1, 4>(h, g, p, s);
+    case 2: return launch_insert_t<2, 4>(h, g, p, s);
+    case 3: return launch_insert_t<3, 2>(h, g, p, s);
+    case 4: return launch_insert_t<4, 2>(h, g, p, s);
+    case 5:
+    case 6: return launch_insert_t<6, 2>(h, g, p, s);
+    case 7:
+    case 8: return launch_insert_t<8, 1>(h, g, p, s);
+    case 9:
+    case 10:
+    case 11:
+    case 12: return launch_insert_t<12, 1>(h, g, p, s);
+    case 13:
+    case 14:
+    case 15:
+    case 16: return launch_insert_t<16, 1>(h, g, p, s);
+    default:
+      set_error("add: dim %d > 2048 not supported", g.dim);
+      return B200HNSW_ERR_UNSUPPORTED;
+  }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200hnsw_add_batch(b200hnsw_t *h, const float *vectors, const int64_t *keys, const int32_t *levels,
+                                  int64_t n, int32_t m, int32_t ef, int32_t metric, b200hnsw_stats *stats) {
+  if (stats) memset(stats, 0, sizeof *stats);
+  if (!h || n < 0 || (n > 0 && (!vectors || !keys || !levels))) {
+    set_error("add: bad argument");
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  if (m <= 0 || m > h->M) {  // graph.go:918-920
+    set_error("M must be greater than 0 and <= max_m=%d, got %d", h->M, m);
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  if (ef <= 0 || ef > B200HNSW_MAX_EF) {
+    set_error("EfSearch must be greater than 0 and <= %d, got %d", B200HNSW_MAX_EF, ef);
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  if (metric != B200HNSW_EUCLIDEAN && metric != B200HNSW_COSINE) {
+    set_error("unknown metric %d", metric);
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  if (n == 0) return 0;
+  if (h->n + n > 0x7fffffffLL) {
+    set_error("add: more than 2^31-1 rows");
+    return B200HNSW_ERR_UNSUPPORTED;
+  }
+  int64_t add_slots = 0;
+  for (int64_t i = 0; i < n; i++) {
+    if (levels[i] < 0 || levels[i] >= B200HNSW_MAX_LAYERS) {  // graph.go:466-468 "invalid level"
+      set_error("invalid level: %d", levels[i]);
+      return B200HNSW_ERR_BAD_ARG;
+    }
+    add_slots += levels[i];
+  }
+  B200_CUDA(cudaSetDevice(h->cfg.device));
+  CallCtx *c = h->acquire();
+  if (!c) return B200HNSW_ERR_CUDA;
+  cudaStream_t s = c->stream;
+  auto fail = [&](int code) {
+    h->release(c);
+    return code;
+  };
+  int rc = h->ensure_capacity(h->n + n, h->nU + add_slots, s);
+  if (rc) return fail(rc);
+  const int dim = h->cfg.dim, rf = h->row_floats;
+  std::vector<int32_t> upper_off((size_t)n, -1);
+  int64_t nU = h->nU;
+  for (int64_t i = 0; i < n; i++)
+    if (levels[i] > 0) {
+      upper_off[i] = (int32_t)nU;
+      nU += levels[i];
+    }
+  const int64_t CH = 1 << 16;  // insertions per launch
+  size_t scratch = sizeof(int32_t) * (size_t)std::min(n, CH) + 256 + 64 * 8 + sizeof(int) * (2 + B200HNSW_MAX_LAYERS);
+  if ((rc = c->reserve_device(scratch + 1024))) return fail(rc);
+  char *sp = (char *)c->d_scratch;
+  int32_t *d_levels = (int32_t *)sp;
+  sp += (sizeof(int32_t) * (size_t)std::min(n, CH) + 255) & ~(size_t)255;
+  unsigned long long *d_ctr = (unsigned long long *)sp;
+  sp += 64;
+  int *d_err = (int *)sp;
+  sp += 64;
+  int *d_state = (int *)sp;
+  cudaError_t e;
+  if ((e = cudaMemcpy2DAsync(h->d.vec + (size_t)h->n * rf, sizeof(float) * rf, vectors, sizeof(float) * dim,
+                             sizeof(float) * dim, (size_t)n, cudaMemcpyHostToDevice, s)) != cudaSuccess ||
+      (e = cudaMemcpyAsync(h->d.keys + h->n, keys, sizeof(int64_t) * (size_t)n, cudaMemcpyHostToDevice, s)) !=
+          cudaSuccess ||
+      (e = cudaMemcpyAsync(h->d.upper_off + h->n, upper_off.data(), sizeof(int32_t) * (size_t)n,
+                           cudaMemcpyHostToDevice, s)) != cudaSuccess ||
+      (e = cudaMemsetAsync(d_ctr, 0, 128, s)) != cudaSuccess)
+    return fail(cuda_fail(e, "add staging"));
+  if ((e = cudaEventRecord(c->ev0, s)) != cudaSuccess) return fail(cuda_fail(e, "event"));
+  int launches = 0;
+  int n_layers = h->n_layers;
+  int32_t entries[B200HNSW_MAX_LAYERS];
+  memcpy(entries, h->entry, sizeof entries);
+  for (int64_t off = 0; off < n; off += CH) {
+    int64_t cnt = std::min(CH, n - off);
+    if ((e = cudaMemcpyAsync(d_levels, levels + off, sizeof(int32_t) * (size_t)cnt, cudaMemcpyHostToDevice, s)) !=
+        cudaSuccess)
+      return fail(cuda_fail(e, "levels copy"));
+    InsertParams p{};
+    p.first_row = h->n + off;
+    p.n = (int)cnt;
+    p.levels = d_levels;
+    p.m = m;
+    p.ef = ef;
+    p.metric = metric;
+    p.n_layers = n_layers;
+    memcpy(p.entries, entries, sizeof entries);
+    p.state_out = d_state;
+    p.counters = d_ctr;
+    p.error = d_err;
+    if ((rc = launch_insert(h, p, s))) return fail(rc);
+    launches++;
+    int state[1 + B200HNSW_MAX_LAYERS];
+    int err = 0;
+    if ((e = cudaMemcpyAsync(state, d_state, sizeof state, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
+        (e = cudaMemcpyAsync(&err, d_err, sizeof err, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
+        (e = cudaStreamSynchronize(s)) != cudaSuccess)
+      return fail(cuda_fail(e, "add kernel"));
+    if (err) {
+      set_error(err == 1 ? "add: a layer search overflowed the visited set" : "no nodes found in neighborhood search");
+      return fail(err == 1 ? B200HNSW_ERR_VISITED_OVERFLOW : B200HNSW_ERR_STATE);
+    }
+    n_layers = state[0];
+    memcpy(entries, state + 1, sizeof entries);
+  }
+  unsigned long long ctr[8];
+  if ((e = cudaEventRecord(c->ev1, s)) != cudaSuccess ||
+      (e = cudaMemcpyAsync(ctr, d_ctr, sizeof ctr, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
+      (e = cudaStreamSynchronize(s)) != cudaSuccess)
+    return fail(cuda_fail(e, "add counters"));
+  // commit host mirrors
+  for (int64_t i = 0; i < n; i++) {
+    h->h_keys.push_back(keys[i]);
+    h->h_level.push_back(levels[i]);
+    h->h_upper_off.push_back(upper_off[i]);
+    for (int l = 0; l <= levels[i]; l++) h->layer_size[l]++;
+  }
+  h->n += n;
+  h->nU = nU;
+  h->n_layers = n_layers;
+  memcpy(h->entry, entries, sizeof entries);
+  if (stats) {
+    stats->dist_evals = (int64_t)ctr[0];
+    stats->evict_evals = (int64_t)ctr[3];
+    stats->replenish_evals = (int64_t)ctr[4];
+    stats->evictions = (int64_t)ctr[5];
+    stats->expansions = (int64_t)ctr[1];
+    stats->nbr_reads = (int64_t)ctr[2];
+    stats->launches = launches;
+    cudaEventElapsedTime(&stats->kernel_ms, c->ev0, c->ev1);
+  }
+  h->release(c);
+  return 0;
+}

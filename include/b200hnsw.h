@@ -70,6 +70,9 @@ typedef struct {
   int64_t dist_evals;  /* E: distance evaluations (graph.go:146)                      */
   int64_t expansions;  /* H: candidates popped and expanded (graph.go:127-139)        */
   int64_t nbr_reads;   /* neighbour ids read                                           */
+  int64_t evict_evals;     /* add: distances in addNeighbor overflow scans (graph.go:60-71)   */
+  int64_t replenish_evals; /* add: cosine distances in replenish (graph.go:204)               */
+  int64_t evictions;       /* add: neighbours evicted (graph.go:73-80)                         */
   float kernel_ms;     /* device time of the traversal kernel (host-pointer calls)     */
   int32_t launches;    /* kernels launched by the call                                 */
 } b200hnsw_stats;

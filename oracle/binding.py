@@ -22,6 +22,7 @@ MODE_REFERENCE, MODE_EXTENDED = 0, 1
 f32p = C.POINTER(C.c_float)
 i32p = C.POINTER(C.c_int32)
 u8p = C.POINTER(C.c_uint8)
+i64p = C.POINTER(C.c_int64)
 f64p = C.POINTER(C.c_double)
 
 
@@ -105,6 +106,11 @@ def lib():
     L.ora_exact_search.argtypes = [f32p, C.c_int64, C.c_int, C.c_int, C.c_int, f32p, C.c_int, C.c_int, i32p, f32p]
     L.ora_exact_batch_search.argtypes = [f32p, C.c_int64, C.c_int, C.c_int, C.c_int, f32p, C.c_int64, C.c_int,
                                          C.c_int, C.c_int, i32p, f32p]
+    L.ora_graph_dump_layer.restype = C.c_int64
+    L.ora_graph_dump_layer.argtypes = [C.c_void_p, C.c_int, i32p, i64p, i32p]
+    L.ora_graph_dump_rows.argtypes = [C.c_void_p, f32p, i64p, i32p]
+    L.ora_graph_add_many.restype = C.c_int64
+    L.ora_graph_add_many.argtypes = [C.c_void_p, i64p, f32p, i32p, C.c_int64, C.c_int]
     L.ora_heap_init.argtypes = [C.POINTER(_Heap), C.c_int]
     L.ora_heap_free.argtypes = [C.POINTER(_Heap)]
     L.ora_heap_push.argtypes = [C.POINTER(_Heap), C.c_float, C.c_int32]
@@ -212,10 +218,23 @@ class Graph:
 
     def add_many(self, keys, vecs, levels, ef):
         vecs = np.ascontiguousarray(vecs, dtype=np.float32)
-        for i in range(len(keys)):
-            row = self.L.ora_graph_add(self.h, int(keys[i]), vecs[i].ctypes.data_as(f32p), int(levels[i]), int(ef))
-            if row < 0:
-                raise RuntimeError(f"ora_graph_add failed: {row}")
+        keys = np.ascontiguousarray(keys, dtype=np.int64)
+        levels = np.ascontiguousarray(levels, dtype=np.int32)
+        done = self.L.ora_graph_add_many(self.h, keys.ctypes.data_as(i64p), vecs.ctypes.data_as(f32p),
+                                         levels.ctypes.data_as(i32p), len(keys), int(ef))
+        if done != len(keys):
+            raise RuntimeError(f"ora_graph_add failed at node {done}")
+
+    def dump_layer(self, layer):
+        """CSR of one layer over its member rows: (rows, ptr, nbr)."""
+        n = int(self.L.ora_graph_layer_size(self.h, layer))
+        nn = self.L.ora_graph_dump_layer(self.h, layer, None, None, None)
+        rows = np.empty(n, dtype=np.int32)
+        ptr = np.empty(n + 1, dtype=np.int64)
+        nbr = np.empty(max(nn, 1), dtype=np.int32)
+        self.L.ora_graph_dump_layer(self.h, layer, rows.ctypes.data_as(i32p), ptr.ctypes.data_as(i64p),
+                                    nbr.ctypes.data_as(i32p))
+        return rows, ptr, nbr[:nn]
 
     def put_node(self, key, vec, level=0):
         v, pv = _f32(vec)
@@ -299,9 +318,12 @@ class Graph:
         """(vectors[N,d], keys[N], levels[N], lists per layer as {layer: (rows[N_l], adj[N_l,M], deg[N_l])})."""
         n = int(self.L.ora_graph_len(self.h)) if self.n_layers else 0
         # rows are dense 0..n-1 when nothing was deleted
-        vec = np.stack([self.vector(r) for r in range(n)]) if n else np.zeros((0, self.dim), np.float32)
-        keys = np.array([self.key(r) for r in range(n)], dtype=np.int64)
-        levels = np.array([self.level(r) for r in range(n)], dtype=np.int32)
+        vec = np.zeros((n, self.dim), np.float32)
+        keys = np.zeros(n, dtype=np.int64)
+        levels = np.zeros(n, dtype=np.int32)
+        if n:
+            self.L.ora_graph_dump_rows(self.h, vec.ctypes.data_as(f32p), keys.ctypes.data_as(i64p),
+                                       levels.ctypes.data_as(i32p))
         return vec, keys, levels
 
 

@@ -125,3 +125,15 @@ void ora_exact_batch_search(const float *vecs, int64_t n, int dim, int metric, i
 }
 #endif
 #endif
+
+/* bulk helpers for the test harness (not part of the restated API) */
+#ifdef __cplusplus
+extern "C" {
+#endif
+int64_t ora_graph_dump_layer(const ora_graph *g, int layer, int32_t *rows, int64_t *ptr, int32_t *nbr);
+void ora_graph_dump_rows(const ora_graph *g, float *vec, int64_t *keys, int32_t *levels);
+int64_t ora_graph_add_many(ora_graph *g, const int64_t *keys, const float *vecs, const int32_t *levels, int64_t n,
+                           int ef);
+#ifdef __cplusplus
+}
+#endif

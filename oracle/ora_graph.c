@@ -500,3 +500,32 @@ int ora_graph_link(ora_graph *g, int layer, int32_t from, int32_t to) {
   list_insert(g, l, deg, to);
   return 0;
 }
+
+/* bulk read-back for the test harness: CSR of one layer over its member rows (ascending row) */
+int64_t ora_graph_dump_layer(const ora_graph *g, int layer, int32_t *rows, int64_t *ptr, int32_t *nbr) {
+  int64_t nm = 0, nn = 0;
+  for (int32_t r = 0; r < (int32_t)g->n; r++) {
+    if (g->level[r] < layer) continue;
+    int32_t *deg;
+    int32_t *l = list_ptr(g, layer, r, &deg);
+    if (rows) rows[nm] = r;
+    if (ptr) ptr[nm] = nn;
+    if (nbr) memcpy(nbr + nn, l, sizeof(int32_t) * (size_t)*deg);
+    nn += *deg;
+    nm++;
+  }
+  if (ptr) ptr[nm] = nn;
+  return nn;
+}
+void ora_graph_dump_rows(const ora_graph *g, float *vec, int64_t *keys, int32_t *levels) {
+  memcpy(vec, g->vec, sizeof(float) * (size_t)g->n * g->dim);
+  memcpy(keys, g->key, sizeof(int64_t) * (size_t)g->n);
+  memcpy(levels, g->level, sizeof(int32_t) * (size_t)g->n);
+}
+/* Graph.Add for n nodes in input order (the serial loop of graph.go:445) */
+int64_t ora_graph_add_many(ora_graph *g, const int64_t *keys, const float *vecs, const int32_t *levels, int64_t n,
+                           int ef) {
+  for (int64_t i = 0; i < n; i++)
+    if (ora_graph_add(g, keys[i], vecs + (size_t)i * g->dim, levels[i], ef) < 0) return i;
+  return n;
+}

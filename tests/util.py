@@ -34,18 +34,8 @@ def build_oracle_graph(oracle, X, M, ml, ef, metric, seed=44, keys=None, flavor=
 
 def flatten_oracle(g):
     """Oracle graph -> (vectors, keys, levels, layer_lists, entries) as hnsw_b200.Graph.load_flat expects."""
-    n = len(g)
     vec, keys, levels = g.dump()
-    layer_lists = []
-    for l in range(g.n_layers):
-        rows = np.nonzero(levels >= l)[0].astype(np.int32)
-        ptr = [0]
-        nbr = []
-        for r in rows:
-            nb = g.neighbors(l, int(r))
-            nbr.extend(nb.tolist())
-            ptr.append(len(nbr))
-        layer_lists.append((rows, np.asarray(ptr, np.int64), np.asarray(nbr, np.int32)))
+    layer_lists = [g.dump_layer(l) for l in range(g.n_layers)]
     return vec, keys, levels, layer_lists, g.entries()
 
 
