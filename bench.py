@@ -1,0 +1,421 @@
+#!/usr/bin/env python
+"""bench.py -- batched Graph.Search QPS on 1M x 128 L2 (BASELINE.json configs[1]) + build rate, on N B200s.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+  torchrun ... bench.py --gpus N ...   (one rank per GPU; RANK / LOCAL_RANK / WORLD_SIZE from the env)
+
+A "step" is one BatchSearch of `--batch` synthetic queries (k=10, EfSearch=64) against the device-resident graph.
+  value      : whole-job queries/s, queries already resident in HBM, CUDA events around the K steps, max over ranks
+  e2e        : the same through the reference-facing C-ABI call with HOST buffers (H2D + kernel + D2H per step)
+  roofline   : traversal kernel's algorithmic bytes (E*4d + neighbour ids + query + results) / its event time,
+               against the measured HBM copy bandwidth in MEASURED_PEAKS.json
+  cpu_baseline: the oracle (CPU port of the reference's Go algorithm) on all host cores, same graph, same queries
+  --impl reference: only the CPU port is built and timed (no GPU code on that path)
+
+Multi-GPU (north_star): every rank owns an independent sub-graph of --n rows (weak scaling), the query batch is
+the same on all ranks, per-shard top-k lists are all-gathered over NCCL and merged by the K4 kernel.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--n", type=int, default=1_000_000, help="rows per GPU (BASELINE configs[1]: 1M)")
+    ap.add_argument("--dim", type=int, default=128)
+    ap.add_argument("--batch", type=int, default=10_000)
+    ap.add_argument("--m", type=int, default=16)
+    ap.add_argument("--ef", type=int, default=64)
+    ap.add_argument("--k", type=int, default=10)
+    ap.add_argument("--ml", type=float, default=0.25)
+    ap.add_argument("--cpu-seconds", type=float, default=10.0, help="target length of the cpu_baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def synth_rows(n, dim, seed):
+    # graph_benchmark_test.go:12-18: rand.Float32()*2-1, i.e. uniform [-1, 1)
+    return np.random.default_rng(seed).uniform(-1.0, 1.0, (n, dim)).astype(np.float32)
+
+
+def draw_levels(n, ml, seed):
+    """graph.go:388-417 with a numpy stream: level draws for n consecutive insertions into an empty graph."""
+    rng = np.random.default_rng(seed)
+    go = rng.random((n, 32)) <= ml  # the loop continues while r <= Ml (graph.go:411 stops on r > Ml)
+    run = np.where(go.all(axis=1), go.shape[1], go.argmin(axis=1))  # leading run of "continue" = level
+    size0 = np.arange(n, dtype=np.float64)  # len(layer 0) seen by the i-th insertion
+    with np.errstate(divide="ignore"):
+        mx = np.floor(np.log(np.maximum(size0, 1.0)) / np.log(1.0 / ml) + 0.5).astype(np.int64) + 1  # maxLevel
+    mx[0] = 1  # graph.go:395: no layers yet -> max = 1 (and maxLevel(ml, 0) == 1 as well)
+    return np.minimum(run, mx).astype(np.int32)
+
+
+class ClockSampler(threading.Thread):
+    """Samples nvidia-smi clocks / throttle reasons of one GPU while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.proc = index, [], None
+
+    def run(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.index), "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            for line in self.proc.stdout:
+                self.rows.append([c.strip() for c in line.split(",")])
+        except Exception:
+            pass
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+        self.join(timeout=2)
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            for name, col in (("hw_slowdown", 3), ("hw_thermal_slowdown", 4), ("sw_thermal_slowdown", 5),
+                              ("sw_power_cap", 6)):
+                if len(r) > col and r[col].lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def load_peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        try:
+            return float(json.loads(p.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def load_traffic():
+    """dram bytes per launch of the traversal kernel from the committed ncu --set full capture, if any."""
+    p = ROOT / "profiles" / "k1_traffic.json"
+    if p.exists():
+        try:
+            return json.loads(p.read_text())
+        except Exception:
+            return None
+    return None
+
+
+def algorithmic_bytes(evals, nbr_reads, queries, dim, k):
+    """E rows of 4*dim bytes + the neighbour ids read + the query + the (id, dist) results."""
+    return evals * 4 * dim + nbr_reads * 4 + queries * (4 * dim + 8 * k + 4)
+
+
+# ------------------------------------------------------------------------------------------------ reference arm
+def run_reference(args, rank, world):
+    """The reference's own CPU path (its C port: oracle/), all host threads, same config.  No GPU code here."""
+    if rank != 0:
+        return 0
+    from oracle import binding as oracle
+    oracle.build()
+    cores = os.cpu_count() or 1
+    X = synth_rows(args.n, args.dim, 42)
+    levels = draw_levels(args.n, args.ml, 44)
+    g = oracle.Graph(args.dim, args.m, oracle.EUCLIDEAN, oracle.SIMD)
+    t0 = time.perf_counter()
+    g.add_many(np.arange(args.n, dtype=np.int64), X, levels, args.ef)
+    build_s = time.perf_counter() - t0
+    nb = args.warmup + args.steps
+    Q = synth_rows(nb * args.batch, args.dim, 43).reshape(nb, args.batch, args.dim)
+    for i in range(args.warmup):
+        g.batch_search(Q[i], args.k, args.ef, n_threads=cores)
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        g.batch_search(Q[args.warmup + i], args.k, args.ef, n_threads=cores)
+    dt = time.perf_counter() - t0
+    qps = args.steps * args.batch / dt
+    line = {
+        "impl": "reference", "metric": "batched Search QPS (Graph.BatchSearch, k=10)", "value": qps,
+        "unit": "queries/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, 1),
+        "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": cores, "kind": "port",
+                         "sample": f"{args.steps} x {args.batch} queries, one query per thread over {cores} threads, "
+                                   f"AVX2 distance; graph built by the same port in {build_s:.1f} s (single thread, "
+                                   f"{args.n / build_s:.0f} vec/s)"},
+        "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "build_vec_per_s": args.n / build_s, "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def workload_config(args, world):
+    return {"workload": f"{args.n}x{args.dim} uniform[-1,1) f32 rows per GPU, L2 (EuclideanDistance), M={args.m} "
+                        f"Ml={args.ml} EfSearch={args.ef}, {args.batch}-query batch, k={args.k} "
+                        f"(BASELINE.json configs[1])",
+            "rows_per_gpu": args.n, "dim": args.dim, "M": args.m, "EfSearch": args.ef, "k": args.k,
+            "batch": args.batch, "mode": "reference (bit-faithful layerNode.search termination)",
+            "layout": "1 graph" if world == 1 else
+            f"{world} independent sub-graphs (one per GPU), queries broadcast, NCCL all-gather + top-k merge",
+            "l2_policy": "inputs larger than L2: 576 MB of graph per GPU gathered at random, a fresh query batch "
+                         "every step"}
+
+
+# ------------------------------------------------------------------------------------------------------ our arm
+def run_ours(args, rank, local_rank, world):
+    import ctypes as C
+
+    import torch
+
+    import hnsw_b200
+    from hnsw_b200 import _lib
+
+    _lib.lib()  # fail loudly if the CUDA extension is missing
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; hnsw_b200 has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    n, dim, B, k, ef = args.n, args.dim, args.batch, args.k, args.ef
+
+    # ---- build this rank's sub-graph with the device Add path (exact reference order) -------------------------
+    X = synth_rows(n, dim, 42 + rank)
+    levels = draw_levels(n, args.ml, 44 + rank)
+    g = hnsw_b200.Graph(M=args.m, Ml=args.ml, EfSearch=ef, Distance=hnsw_b200.EuclideanDistance, device=local_rank,
+                        capacity=n)
+    keys = np.arange(n, dtype=np.int64) + rank * n  # global ids
+    t0 = time.perf_counter()
+    g.add_arrays(keys, X, levels)
+    build_wall = time.perf_counter() - t0
+    bst = g.last_stats
+    build_kernel_s = bst["kernel_ms"] / 1e3
+
+    # ---- synthetic queries: a fresh batch per step, identical on every rank (the "broadcast" of north_star) ----
+    nb = args.warmup + args.steps
+    Qh = torch.from_numpy(synth_rows(nb * B, dim, 43).reshape(nb, B, dim)).pin_memory()
+    Qd = Qh.to(dev)
+    rows = torch.empty((B, k), dtype=torch.int32, device=dev)
+    dists = torch.empty((B, k), dtype=torch.float32, device=dev)
+    counts = torch.empty((B,), dtype=torch.int32, device=dev)
+    counters = torch.zeros(8, dtype=torch.int64, device=dev)
+    stream = torch.cuda.current_stream(dev)
+    if world > 1:
+        ids = torch.empty((B, k), dtype=torch.int64, device=dev)
+        all_d = torch.empty((world, B, k), dtype=torch.float32, device=dev)
+        all_i = torch.empty((world, B, k), dtype=torch.int64, device=dev)
+        all_c = torch.empty((world, B), dtype=torch.int32, device=dev)
+    m_d = torch.empty((B, k), dtype=torch.float32, device=dev)
+    m_i = torch.empty((B, k), dtype=torch.int64, device=dev)
+    m_c = torch.empty((B,), dtype=torch.int32, device=dev)
+
+    def search_step(qd):
+        g.search_device(qd.data_ptr(), B, k, rows.data_ptr(), dists.data_ptr(), counts.data_ptr(),
+                        counters.data_ptr(), stream.cuda_stream)
+
+    def merge_step():
+        torch.add(rows, rank * n, out=ids)  # shard row -> global id (-1 stays negative only for rank 0; masked by counts)
+        dist.all_gather_into_tensor(all_d, dists)
+        dist.all_gather_into_tensor(all_i, ids)
+        dist.all_gather_into_tensor(all_c, counts)
+        _lib.check(_lib.lib().b200hnsw_merge_topk_device(
+            local_rank, world, B, k, C.c_void_p(all_d.data_ptr()), C.c_void_p(all_i.data_ptr()),
+            C.c_void_p(all_c.data_ptr()), 0, C.c_void_p(m_d.data_ptr()), C.c_void_p(m_i.data_ptr()),
+            C.c_void_p(m_c.data_ptr()), C.c_void_p(stream.cuda_stream)))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+
+    # ---- device-resident timing: W warm-up steps, then exactly K steps between events ---------------------------
+    for i in range(args.warmup):
+        search_step(Qd[i])
+        if world > 1:
+            merge_step()
+    barrier()
+    counters.zero_()
+    ka = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    kb = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record(stream)
+    for i in range(args.steps):
+        ka[i].record(stream)
+        search_step(Qd[args.warmup + i])
+        kb[i].record(stream)
+        if world > 1:
+            merge_step()
+    ev1.record(stream)
+    barrier()
+    total_ms = ev0.elapsed_time(ev1)
+    kernel_ms = [a.elapsed_time(b) for a, b in zip(ka, kb)]
+    ctr = counters.cpu().numpy().copy()
+    last_rows, last_dists, last_counts = rows.cpu().numpy(), dists.cpu().numpy(), counts.cpu().numpy()
+    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms = float(t.item())
+
+    # ---- end to end: host buffers in, host buffers out, every step ---------------------------------------------------
+    h_rows = torch.empty((B, k), dtype=torch.int32).pin_memory()
+    h_dists = torch.empty((B, k), dtype=torch.float32).pin_memory()
+    h_counts = torch.empty((B,), dtype=torch.int32).pin_memory()
+    h_mi = torch.empty((B, k), dtype=torch.int64).pin_memory()
+    h_md = torch.empty((B, k), dtype=torch.float32).pin_memory()
+    qtmp = torch.empty((B, dim), dtype=torch.float32, device=dev)
+
+    def e2e_step(i):
+        if world == 1:  # the drop-in call itself: b200hnsw_search_batch(host pointers)
+            g.search_host_ptrs(Qh[i].data_ptr(), B, k, h_rows.data_ptr(), h_dists.data_ptr(), h_counts.data_ptr())
+        else:
+            qtmp.copy_(Qh[i], non_blocking=True)
+            search_step(qtmp)
+            merge_step()
+            h_mi.copy_(m_i, non_blocking=True)
+            h_md.copy_(m_d, non_blocking=True)
+            torch.cuda.synchronize(dev)
+
+    for i in range(min(args.warmup, 3)):
+        e2e_step(i)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        e2e_step(args.warmup + i)
+    torch.cuda.synchronize(dev)
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_s = float(t.item())
+    clocks = sampler.stop()
+
+    # ---- numbers ----------------------------------------------------------------------------------------------------
+    units = args.steps * B * world  # (query, shard) traversals done by all ranks
+    value = units / (total_ms / 1e3)
+    e2e_value = units / e2e_s
+    peak, peak_src = load_peaks()
+    kern_avg_ms = float(np.mean(kernel_ms))
+    alg_bytes = algorithmic_bytes(int(ctr[0]), int(ctr[2]), args.steps * B, dim, k) / args.steps
+    achieved = alg_bytes / (kern_avg_ms / 1e3) / 1e9
+    traffic = load_traffic()
+    line = {
+        "metric": "batched Search QPS (Graph.BatchSearch, k=10)", "value": value, "unit": "queries/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, world),
+        "e2e": {"value": e2e_value, "unit": "queries/s", "h2d_bytes_per_step": B * dim * 4,
+                "d2h_bytes_per_step": B * k * 8 + B * 4 + 40 if world == 1 else B * k * 12},
+        "gpu_launches": args.steps * (1 if world == 1 else 2),
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": (traffic or {}).get("dram_bytes_per_launch"),
+                     "kernel": "b200::search_kernel<1,8>", "kernel_ms": kern_avg_ms,
+                     "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
+                     "dist_evals_per_query": float(ctr[0]) / (args.steps * B),
+                     "expansions_per_query": float(ctr[1]) / (args.steps * B)},
+        "clocks": clocks,
+        "build": {"vec_per_s": n * world / build_wall, "kernel_vec_per_s": n / build_kernel_s, "wall_s": build_wall,
+                  "semantics": "exact sequential Graph.Add order (bit-identical to the oracle)",
+                  "evals_per_insert": (bst["dist_evals"] + bst["evict_evals"] + bst["replenish_evals"]) / n},
+    }
+
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        line.update(cpu_baseline_and_parity(args, g, Qh, last_rows, last_dists, last_counts, torch, dev, X))
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def cpu_baseline_and_parity(args, g, Qh, last_rows, last_dists, last_counts, torch, dev, X):
+    """Rank 0, N=1: time the CPU port on the SAME graph (read back from the device) and check the GPU's last batch
+    against it.  The oracle is the checker and the reported baseline here, never the thing measured above."""
+    from oracle import binding as oracle
+    oracle.build()
+    cores = os.cpu_count() or 1
+    flat = g.dump_flat()
+    B, k, ef = args.batch, args.k, args.ef
+    out = {}
+    # parity: canonical-order oracle vs the device results of the last timed step (bit-exact bar)
+    oc = oracle.Graph(args.dim, args.m, oracle.EUCLIDEAN, oracle.CANONICAL)
+    oc.load_flat(*flat)
+    last = args.warmup + args.steps - 1
+    o_rows, o_d, o_cnt, o_ctr = oc.batch_search(Qh[last].numpy(), k, ef, n_threads=cores)
+    out["parity"] = {"checked_queries": int(B), "rows_equal": bool(np.array_equal(o_rows, last_rows)),
+                     "dists_bit_equal": bool(np.array_equal(o_d.view(np.uint32), last_dists.view(np.uint32))),
+                     "counts_equal": bool(np.array_equal(o_cnt, last_counts))}
+    del oc
+    # recall@10 of the bit-faithful mode against float32 brute force on the GPU (measurement only)
+    nq = min(1000, B)
+    q = Qh[last][:nq].to(dev)
+    xd = torch.from_numpy(X).to(dev)
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    d2 = (xd * xd).sum(1)[None, :] - 2.0 * (q @ xd.T)
+    torch.backends.cuda.matmul.allow_tf32 = prev
+    truth = d2.topk(k, dim=1, largest=False).indices.cpu().numpy()
+    hits = sum(len(set(int(v) for v in last_rows[i] if v >= 0) & set(int(v) for v in truth[i])) for i in range(nq))
+    out["recall_at_10"] = hits / (nq * k)
+    del xd, d2
+    # timing: AVX2-distance flavour, one query per thread on all cores, bounded sample
+    os_ = oracle.Graph(args.dim, args.m, oracle.EUCLIDEAN, oracle.SIMD)
+    os_.load_flat(*flat)
+    nb = Qh.shape[0]
+    os_.batch_search(Qh[0].numpy(), k, ef, n_threads=cores)
+    done, t0 = 0, time.perf_counter()
+    i = 0
+    while True:
+        os_.batch_search(Qh[i % nb].numpy(), k, ef, n_threads=cores)
+        done += B
+        i += 1
+        el = time.perf_counter() - t0
+        if el >= args.cpu_seconds or i >= 2000:
+            break
+    t1 = time.perf_counter()
+    os_.batch_search(Qh[0].numpy()[: max(B // 10, 1)], k, ef, n_threads=1)
+    single = max(B // 10, 1) / (time.perf_counter() - t1)
+    out["cpu_baseline"] = {"value": done / el, "unit": "queries/s", "cores": cores, "kind": "port",
+                           "sample": f"{done} queries ({i} batches of {B}) in {el:.1f} s, one query per thread, AVX2 "
+                                     f"distance, same graph read back from the device",
+                           "single_thread_value": single}
+    return out
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        return run_reference(args, rank, world)
+    return run_ours(args, rank, local_rank, world)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

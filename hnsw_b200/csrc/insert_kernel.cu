@@ -190,6 +190,16 @@ struct Inserter {
     }
     __syncthreads();
     if (!ctl->flag) return;
+    // all neighbours' lists are fetched at once (independent gathers), one list per warp, into shared memory
+    int *nl = reinterpret_cast<int *>(candd);  // [deg][M], free until the distances are written
+    {
+      const int deg = ctl->wl_len;
+      for (int i = warp; i < deg; i += INS_WARPS) {
+        const int32_t *ln = g.list(layer, wl[i]);
+        for (int j = lane; j < M; j += 32) nl[i * M + j] = ln[j];
+      }
+    }
+    __syncthreads();
     if (warp == 0) {
       Visited RV{rep, (uint32_t)p.rep_cap - 1, 0};
       const int deg = ctl->wl_len;
@@ -200,7 +210,7 @@ struct Inserter {
       // graph.go:193-210: neighbours of neighbours, ascending key order at both levels
       int nc = 0;
       for (int i = 0; i < deg; i++) {
-        const int32_t *ln = g.list(layer, wl[i]);
+        const int *ln = nl + i * M;
         for (int base = 0; base < M; base += 32) {
           int v = -1;
           if (base + lane < M) v = ln[base + lane];
@@ -507,8 +517,8 @@ static int launch_insert(b200hnsw *h, InsertParams &p, cudaStream_t s) {
   p.heap_c = (p.ef + 2) & ~1;
   p.heap_r = (p.m + 2) & ~1;
   p.vis_cap = 1024;
-  p.cand_cap = p.m * p.m + 4;
-  p.rep_cap = pow2_at_least(2 * (p.m * p.m + p.m + 2));
+  p.cand_cap = g.M * g.M + 4;  // also holds the [deg][M] staging of the neighbours' lists
+  p.rep_cap = pow2_at_least(2 * (g.M * g.M + g.M + 2));
   int cpl = (g.row_chunks + 31) / 32;
   switch (cpl) {
     case 1: return launch_insert_t<1, 4>(h, g, p, s);

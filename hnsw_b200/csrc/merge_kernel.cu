@@ -1,0 +1,98 @@
+// merge_kernel.cu -- K4: merge G per-shard result lists per query into one top-k (multi-GPU search and exact search).
+// No reference counterpart (the reference is single-process); the tie rule mirrors the stable
+// concatenate-then-sort of hnsw-extensions/hybrid/adapter.go:264-292: equal distances keep shard order, then the
+// position inside the shard's list.  One CTA per query: the G*k candidates are bitonic-sorted in shared memory on
+// a 64-bit key (order-preserving distance bits << 32 | shard*k + position); NaN distances sort last.
+// Bound: launch latency / NVLink all-gather latency (G*k*12 bytes per query).
+#include "index.hpp"
+
+namespace b200 {
+
+__device__ __forceinline__ uint32_t ordered_bits(float d) {
+  uint32_t u = __float_as_uint(d);
+  if (d != d) return 0xffffffffu;                      // NaN last
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);   // total order of the finite/inf floats
+}
+
+__global__ void merge_topk_kernel(int G, long long B, int k, const float *__restrict__ dists,
+                                  const int64_t *__restrict__ ids, const int32_t *__restrict__ counts, int n_pow2,
+                                  float *__restrict__ out_d, int64_t *__restrict__ out_id,
+                                  int32_t *__restrict__ out_cnt) {
+  extern __shared__ unsigned long long keys[];
+  const long long q = blockIdx.x;
+  const int total = G * k;
+  for (int i = threadIdx.x; i < n_pow2; i += blockDim.x) {
+    unsigned long long key = ~0ull;
+    if (i < total) {
+      int g = i / k, pos = i - g * k;
+      int cnt = counts[(long long)g * B + q];
+      if (pos < cnt) {
+        float d = dists[((long long)g * B + q) * k + pos];
+        key = ((unsigned long long)ordered_bits(d) << 32) | (unsigned)i;
+      }
+    }
+    keys[i] = key;
+  }
+  __syncthreads();
+  for (int size = 2; size <= n_pow2; size <<= 1) {
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      for (int i = threadIdx.x; i < n_pow2 / 2; i += blockDim.x) {
+        int lo = 2 * i - (i & (stride - 1));
+        int hi = lo + stride;
+        bool up = (lo & size) == 0;
+        unsigned long long a = keys[lo], b = keys[hi];
+        if ((a > b) == up) {
+          keys[lo] = b;
+          keys[hi] = a;
+        }
+      }
+      __syncthreads();
+    }
+  }
+  int valid = 0;
+  for (int i = threadIdx.x; i < k; i += blockDim.x) {
+    unsigned long long key = keys[i];
+    bool ok = key != ~0ull;
+    int src = (int)(key & 0xffffffffu);
+    int g = ok ? src / k : 0, pos = ok ? src - g * k : 0;
+    long long off = ((long long)g * B + q) * k + pos;
+    out_d[q * k + i] = ok ? dists[off] : __int_as_float(0x7fc00000);
+    out_id[q * k + i] = ok ? ids[off] : -1;
+    valid += ok;
+  }
+  // count = min(k, sum of counts)
+  if (threadIdx.x == 0) {
+    long long s = 0;
+    for (int g = 0; g < G; g++) s += counts[(long long)g * B + q];
+    out_cnt[q] = (int)(s < k ? s : k);
+  }
+  (void)valid;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200hnsw_merge_topk_device(int32_t device, int32_t G, int64_t B, int32_t k, const float *d_dists,
+                                          const int64_t *d_ids, const int32_t *d_counts, int32_t sorted_in,
+                                          float *d_out_dists, int64_t *d_out_ids, int32_t *d_out_counts,
+                                          void *stream) {
+  (void)sorted_in;  // both input orders go through the same sort
+  if (G <= 0 || B < 0 || k <= 0 || k > B200HNSW_MAX_K || (long long)G * k > 8192 ||
+      (B > 0 && (!d_dists || !d_ids || !d_counts || !d_out_dists || !d_out_ids || !d_out_counts))) {
+    set_error("merge_topk: bad argument (G=%d k=%d; G*k <= 8192)", G, k);
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  if (B == 0) return 0;
+  B200_CUDA(cudaSetDevice(device));
+  int n_pow2 = 2;
+  while (n_pow2 < G * k) n_pow2 <<= 1;
+  int threads = n_pow2 / 2 < 32 ? 32 : (n_pow2 / 2 > 256 ? 256 : n_pow2 / 2);
+  size_t smem = sizeof(unsigned long long) * (size_t)n_pow2;
+  if (smem > 48 * 1024)
+    B200_CUDA(cudaFuncSetAttribute(merge_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  merge_topk_kernel<<<(unsigned)B, threads, smem, (cudaStream_t)stream>>>(G, B, k, d_dists, d_ids, d_counts, n_pow2,
+                                                                          d_out_dists, d_out_ids, d_out_counts);
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}

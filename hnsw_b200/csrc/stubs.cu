@@ -5,8 +5,6 @@ using namespace b200;
   set_error(name ": not implemented in this build"); \
   return B200HNSW_ERR_UNSUPPORTED
 extern "C" {
-int b200hnsw_merge_topk_device(int32_t, int32_t, int64_t, int32_t, const float *, const int64_t *, const int32_t *,
-                               int32_t, float *, int64_t *, int32_t *, void *) { STUB("merge_topk_device"); }
 int b200exact_create(int32_t, int32_t, int32_t, int64_t, b200exact_t **) { STUB("exact_create"); }
 void b200exact_destroy(b200exact_t *) {}
 int64_t b200exact_len(const b200exact_t *) { return 0; }

@@ -193,15 +193,36 @@ class Graph:
                 # graph.go:1016-1024 deletes the old node first; Delete is SURVEY.md row N3 (not built yet)
                 raise NotImplementedError(f"key {k} already present: replacing a node needs Delete (not built yet)")
             keys.append(int(k))
-        lv = np.asarray(levels, dtype=np.int32) if levels is not None else self._draw_levels(len(nodes))
-        V = np.ascontiguousarray(np.stack(vecs), dtype=np.float32)
-        K = np.asarray(keys, dtype=np.int64)
+        self._add_arrays(keys, np.stack(vecs), levels, metric)
+
+    def _add_arrays(self, keys, V, levels, metric):
+        lv = np.ascontiguousarray(levels, dtype=np.int32) if levels is not None else self._draw_levels(len(keys))
+        V = np.ascontiguousarray(V, dtype=np.float32)
+        K = np.ascontiguousarray(keys, dtype=np.int64)
         st = _lib.Stats()
         _lib.check(_lib.lib().b200hnsw_add_batch(self._h, V.ctypes.data_as(_lib.f32p), K.ctypes.data_as(_lib.i64p),
-                                                 lv.ctypes.data_as(_lib.i32p), len(keys), self.M, self.EfSearch,
+                                                 lv.ctypes.data_as(_lib.i32p), len(K), self.M, self.EfSearch,
                                                  metric, C.byref(st)))
         self.last_stats = st.as_dict()
-        self._store_host(keys, V)
+        self._store_host([int(k) for k in K], V)
+
+    def add_arrays(self, keys, vectors, levels: Optional[Sequence[int]] = None):
+        """BatchAdd for array inputs (keys[n] int64, vectors[n, dim] float32): same semantics, no per-node objects.
+        Keys must be new and distinct."""
+        self.Validate()
+        vectors = np.asarray(vectors, dtype=np.float32)
+        if vectors.ndim != 2 or len(keys) != vectors.shape[0]:
+            raise ValueError("keys and vectors must have the same length")
+        if len(keys) == 0:
+            return
+        dim0 = self._dim if self.Len() > 0 else vectors.shape[1]
+        if vectors.shape[1] != dim0:
+            raise ValueError(f"embedding dimension mismatch: {dim0} != {vectors.shape[1]}")
+        metric = metric_of(self.Distance)
+        self._ensure_device(dim0)
+        if self.M > self._max_m:
+            raise ValueError(f"M={self.M} exceeds the device list stride {self._max_m} fixed at the first Add")
+        self._add_arrays(keys, vectors, levels, metric)
 
     def Add(self, *nodes: Node, levels: Optional[Sequence[int]] = None):
         """graph.go:437-531 (same body as BatchAdd; the reference's Add deadlocks on a duplicate key, F9)."""
@@ -251,6 +272,25 @@ class Graph:
                                                      mem.ctypes.data_as(_lib.u8p)))
         return nbr, mem.astype(bool)
 
+    def dump_flat(self):
+        """Inverse of load_flat: (vectors, keys, levels, layer_lists, entries) read back from the device."""
+        L = _lib.lib()
+        n = len(self._keys)
+        vec = np.empty((n, self._dim), dtype=np.float32)
+        keys = np.empty(n, dtype=np.int64)
+        levels = np.empty(n, dtype=np.int32)
+        _lib.check(L.b200hnsw_get_rows(self._h, 0, n, vec.ctypes.data_as(_lib.f32p), keys.ctypes.data_as(_lib.i64p),
+                                       levels.ctypes.data_as(_lib.i32p)))
+        layer_lists = []
+        for l in range(L.b200hnsw_layers(self._h)):
+            nbr, member = self.neighbors(l)
+            rows = np.nonzero(member)[0].astype(np.int32)
+            sub = nbr[rows]
+            deg = (sub >= 0).sum(axis=1)
+            ptr = np.concatenate([[0], np.cumsum(deg)]).astype(np.int64)
+            layer_lists.append((rows, ptr, sub[sub >= 0].astype(np.int32)))
+        return vec, keys, levels, layer_lists, self.entries()
+
     # ---- Search / BatchSearch -----------------------------------------------------------------------------------------
     def search_rows(self, queries, k: int, ef: Optional[int] = None, mode: int = _lib.MODE_REFERENCE, entries=None):
         """Raw device call: (rows[B,k], dists[B,k], counts[B]) in the reference's heap-array order."""
@@ -270,6 +310,27 @@ class Graph:
             C.byref(st)))
         self.last_stats = st.as_dict()
         return rows, dists, counts
+
+    def search_device(self, d_queries: int, B: int, k: int, d_rows: int, d_dists: int, d_counts: int,
+                      d_counters: int = 0, stream: int = 0, ef: Optional[int] = None,
+                      mode: int = _lib.MODE_REFERENCE):
+        """Device-pointer variant (b200hnsw_search_batch_device): inputs already resident in HBM, asynchronous on
+        `stream` (a cudaStream_t as int).  d_counters: int64[8] or 0."""
+        _lib.check(_lib.lib().b200hnsw_search_batch_device(
+            self._h, C.c_void_p(d_queries), B, k, ef if ef is not None else self.EfSearch, metric_of(self.Distance),
+            mode, None, C.c_void_p(d_rows), C.c_void_p(d_dists), C.c_void_p(d_counts),
+            C.c_void_p(d_counters) if d_counters else None, C.c_void_p(stream) if stream else None))
+
+    def search_host_ptrs(self, q_ptr: int, B: int, k: int, rows_ptr: int, dists_ptr: int, counts_ptr: int,
+                         ef: Optional[int] = None, mode: int = _lib.MODE_REFERENCE):
+        """b200hnsw_search_batch on caller-owned HOST buffers given as addresses (e.g. pinned torch tensors): the
+        call a cgo host makes.  H2D copy, traversal kernel and D2H copy all happen inside; returns the stats."""
+        st = _lib.Stats()
+        _lib.check(_lib.lib().b200hnsw_search_batch(
+            self._h, C.cast(q_ptr, _lib.f32p), B, k, ef if ef is not None else self.EfSearch,
+            metric_of(self.Distance), mode, None, C.cast(rows_ptr, _lib.i32p), C.cast(dists_ptr, _lib.f32p),
+            C.cast(counts_ptr, _lib.i32p), C.byref(st)))
+        return st.as_dict()
 
     def _nodes(self, rows, count) -> List[Node]:
         return [Node(self._keys[r], self._vecs[r]) for r in rows[:count]]

@@ -111,6 +111,8 @@ def lib():
     L.ora_graph_dump_rows.argtypes = [C.c_void_p, f32p, i64p, i32p]
     L.ora_graph_add_many.restype = C.c_int64
     L.ora_graph_add_many.argtypes = [C.c_void_p, i64p, f32p, i32p, C.c_int64, C.c_int]
+    L.ora_graph_load_flat.restype = C.c_int
+    L.ora_graph_load_flat.argtypes = [C.c_void_p, C.c_int64, f32p, i64p, i32p, C.c_int, i32p, i64p, i32p, i64p, i32p]
     L.ora_heap_init.argtypes = [C.POINTER(_Heap), C.c_int]
     L.ora_heap_free.argtypes = [C.POINTER(_Heap)]
     L.ora_heap_push.argtypes = [C.POINTER(_Heap), C.c_float, C.c_int32]
@@ -224,6 +226,26 @@ class Graph:
                                          levels.ctypes.data_as(i32p), len(keys), int(ef))
         if done != len(keys):
             raise RuntimeError(f"ora_graph_add failed at node {done}")
+
+    def load_flat(self, vectors, keys, levels, layer_lists, entries=None):
+        """Fill an empty graph from (vectors, keys, levels, [(rows, ptr, nbr) per layer], entries)."""
+        vectors = np.ascontiguousarray(vectors, dtype=np.float32)
+        keys = np.ascontiguousarray(keys, dtype=np.int64)
+        levels = np.ascontiguousarray(levels, dtype=np.int32)
+        nl = len(layer_lists)
+        sizes = np.array([len(r) for r, _, _ in layer_lists], dtype=np.int64)
+        rows = np.ascontiguousarray(np.concatenate([np.asarray(r, np.int32) for r, _, _ in layer_lists]))
+        ptr = np.ascontiguousarray(np.concatenate([np.asarray(p, np.int64) for _, p, _ in layer_lists]))
+        nbr = np.ascontiguousarray(np.concatenate([np.asarray(b, np.int32) for _, _, b in layer_lists] +
+                                                  [np.zeros(1, np.int32)]))
+        ent = None if entries is None else np.ascontiguousarray(entries, dtype=np.int32)
+        rc = self.L.ora_graph_load_flat(self.h, len(keys), vectors.ctypes.data_as(f32p), keys.ctypes.data_as(i64p),
+                                        levels.ctypes.data_as(i32p), nl,
+                                        ent.ctypes.data_as(i32p) if ent is not None else None,
+                                        sizes.ctypes.data_as(i64p), rows.ctypes.data_as(i32p),
+                                        ptr.ctypes.data_as(i64p), nbr.ctypes.data_as(i32p))
+        if rc:
+            raise RuntimeError(f"ora_graph_load_flat failed: {rc}")
 
     def dump_layer(self, layer):
         """CSR of one layer over its member rows: (rows, ptr, nbr)."""

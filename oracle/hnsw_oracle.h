@@ -134,6 +134,9 @@ int64_t ora_graph_dump_layer(const ora_graph *g, int layer, int32_t *rows, int64
 void ora_graph_dump_rows(const ora_graph *g, float *vec, int64_t *keys, int32_t *levels);
 int64_t ora_graph_add_many(ora_graph *g, const int64_t *keys, const float *vecs, const int32_t *levels, int64_t n,
                            int ef);
+int ora_graph_load_flat(ora_graph *g, int64_t n, const float *vecs, const int64_t *keys, const int32_t *levels,
+                        int n_layers, const int32_t *entries, const int64_t *layer_sizes, const int32_t *layer_rows,
+                        const int64_t *layer_ptr, const int32_t *layer_nbr);
 #ifdef __cplusplus
 }
 #endif

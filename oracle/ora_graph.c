@@ -529,3 +529,32 @@ int64_t ora_graph_add_many(ora_graph *g, const int64_t *keys, const float *vecs,
     if (ora_graph_add(g, keys[i], vecs + (size_t)i * g->dim, levels[i], ef) < 0) return i;
   return n;
 }
+
+/* Fill an EMPTY graph from flat arrays (the shape the device library dumps): rows 0..n-1 with vectors, keys and
+ * levels; per layer a CSR over its member rows (rows[], ptr[], nbr[] concatenated layer after layer, each layer's
+ * ptr starting at 0).  Lists are re-sorted by key.  Returns 0 or a negative error. */
+int ora_graph_load_flat(ora_graph *g, int64_t n, const float *vecs, const int64_t *keys, const int32_t *levels,
+                        int n_layers, const int32_t *entries, const int64_t *layer_sizes, const int32_t *layer_rows,
+                        const int64_t *layer_ptr, const int32_t *layer_nbr) {
+  if (g->n != 0) return -1;
+  for (int64_t i = 0; i < n; i++) new_row(g, keys[i], vecs + (size_t)i * g->dim, levels[i]);
+  g->n_layers = n_layers;
+  int64_t roff = 0, poff = 0, noff = 0;
+  for (int l = 0; l < n_layers; l++) {
+    int64_t nl = layer_sizes[l];
+    g->layer_size[l] = nl;
+    g->entry[l] = entries ? entries[l] : (nl ? layer_rows[roff] : -1);
+    for (int64_t i = 0; i < nl; i++) {
+      int32_t row = layer_rows[roff + i];
+      if (row < 0 || row >= n || levels[row] < l) return -2;
+      int64_t b = layer_ptr[poff + i], e = layer_ptr[poff + i + 1];
+      if (e - b > g->M) return -3;
+      for (int64_t t = b; t < e; t++)
+        if (ora_graph_link(g, l, row, layer_nbr[noff + t])) return -4;
+    }
+    noff += layer_ptr[poff + nl];
+    roff += nl;
+    poff += nl + 1;
+  }
+  return 0;
+}
