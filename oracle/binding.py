@@ -113,6 +113,10 @@ def lib():
     L.ora_graph_add_many.argtypes = [C.c_void_p, i64p, f32p, i32p, C.c_int64, C.c_int]
     L.ora_graph_load_flat.restype = C.c_int
     L.ora_graph_load_flat.argtypes = [C.c_void_p, C.c_int64, f32p, i64p, i32p, C.c_int, i32p, i64p, i32p, i64p, i32p]
+    L.ora_wave_len.restype = C.c_int64
+    L.ora_wave_len.argtypes = [C.c_int64, C.c_int, i32p, C.c_int64, C.c_int64]
+    L.ora_graph_add_waves.restype = C.c_int64
+    L.ora_graph_add_waves.argtypes = [C.c_void_p, i64p, f32p, i32p, C.c_int64, C.c_int, C.c_int64, C.c_int]
     L.ora_heap_init.argtypes = [C.POINTER(_Heap), C.c_int]
     L.ora_heap_free.argtypes = [C.POINTER(_Heap)]
     L.ora_heap_push.argtypes = [C.POINTER(_Heap), C.c_float, C.c_int32]
@@ -226,6 +230,17 @@ class Graph:
                                          levels.ctypes.data_as(i32p), len(keys), int(ef))
         if done != len(keys):
             raise RuntimeError(f"ora_graph_add failed at node {done}")
+
+    def add_waves(self, keys, vecs, levels, ef, wave_max=4096, n_threads=1):
+        """Wave-batched Add (NOT the reference's algorithm; restates the device library's batched construction)."""
+        vecs = np.ascontiguousarray(vecs, dtype=np.float32)
+        keys = np.ascontiguousarray(keys, dtype=np.int64)
+        levels = np.ascontiguousarray(levels, dtype=np.int32)
+        done = self.L.ora_graph_add_waves(self.h, keys.ctypes.data_as(i64p), vecs.ctypes.data_as(f32p),
+                                          levels.ctypes.data_as(i32p), len(keys), int(ef), int(wave_max),
+                                          int(n_threads))
+        if done != len(keys):
+            raise RuntimeError(f"ora_graph_add_waves failed at node {done}")
 
     def load_flat(self, vectors, keys, levels, layer_lists, entries=None):
         """Fill an empty graph from (vectors, keys, levels, [(rows, ptr, nbr) per layer], entries)."""

@@ -140,3 +140,15 @@ int ora_graph_load_flat(ora_graph *g, int64_t n, const float *vecs, const int64_
 #ifdef __cplusplus
 }
 #endif
+
+/* Wave-batched Add: NOT the reference's algorithm; the CPU restatement of the device library's batched
+ * construction (see the banner in ora_graph.c). */
+#ifdef __cplusplus
+extern "C" {
+#endif
+int64_t ora_wave_len(int64_t cur_rows, int n_layers, const int32_t *levels, int64_t remaining, int64_t wave_max);
+int64_t ora_graph_add_waves(ora_graph *g, const int64_t *keys, const float *vecs, const int32_t *levels, int64_t n,
+                            int ef, int64_t wave_max, int n_threads);
+#ifdef __cplusplus
+}
+#endif

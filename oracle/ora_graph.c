@@ -558,3 +558,363 @@ int ora_graph_load_flat(ora_graph *g, int64_t n, const float *vecs, const int64_
   }
   return 0;
 }
+
+/* ================================================================================================
+ * WAVE-BATCHED ADD -- NOT the reference's algorithm.
+ *
+ * The reference inserts strictly one node after the other (graph.go:445, one write lock).  The device
+ * library also offers a batched construction (north_star: "Batched Add evaluates candidates in parallel
+ * in the same kernels and applies the same neighbor-selection heuristic"): nodes are inserted in WAVES;
+ * all nodes of a wave search the graph as it was before the wave, then their links are committed in
+ * deterministic phases that apply the reference's heuristic (link to every search result, evict the
+ * farthest on overflow, delete the back-link, replenish the evicted node with CosineDistance).
+ * This function is the CPU restatement of THAT specification, so the device path can be checked bit for
+ * bit.  It is pinned to nothing in the reference; what it borrows from the reference is cited inline.
+ *
+ *   schedule  : ora_wave_len() below (identical formula in hnsw_b200/csrc/wave_insert.cu)
+ *   phase S   : per new node, per layer top->0: search(k=M, ef) from the elevator (graph.go:475-508)
+ *   phase A   : the new node's own list at each of its layers = its search results (graph.go:519)
+ *   phase B   : per (layer, target): insert the new rows in input order; on overflow evict the farthest
+ *               (graph.go:50-73, scan in ascending key order, rule `d > worst || worst == nil`)
+ *   phase C   : per eviction (n, worst): delete n from worst's list (graph.go:75-78)
+ *   phase D   : per evicted node with fewer than M links: replenish from the lists as they are after
+ *               phase C (graph.go:172-219), results staged
+ *   phase E   : staged lists replace the old ones
+ * ================================================================================================ */
+int64_t ora_wave_len(int64_t cur_rows, int n_layers, const int32_t *levels, int64_t remaining, int64_t wave_max) {
+  if (remaining <= 0) return 0;
+  if (n_layers == 0) return 1; /* the very first node */
+  int64_t cap = cur_rows / 16;
+  if (cap < 1) cap = 1;
+  if (cap > wave_max) cap = wave_max;
+  int64_t w = 0;
+  while (w < remaining && w < cap) {
+    if (levels[w] >= n_layers) { /* a node that opens new layers is inserted alone */
+      if (w == 0) w = 1;
+      break;
+    }
+    w++;
+  }
+  return w;
+}
+
+typedef struct {
+  int32_t row, layer, cnt;
+  int32_t *rows; /* [M] heap-array order */
+  float *dists;  /* [M] */
+} wave_slot;
+
+typedef struct {
+  ora_graph *g;
+  wave_slot *slots;
+  const int64_t *slot_off; /* first slot of node j */
+  int32_t first_row;
+  int64_t j0, j1;
+  int ef, old_layers, fail;
+  ora_counters ctr;
+} waveS_job;
+
+static void *waveS_worker(void *arg) {
+  waveS_job *J = (waveS_job *)arg;
+  ora_graph *g = J->g;
+  visited_t v;
+  v.cap = g->cap;
+  v.stamp = (uint32_t *)calloc((size_t)v.cap, sizeof(uint32_t));
+  v.epoch = 0;
+  int M = g->M;
+  int32_t *rows = (int32_t *)malloc(sizeof(int32_t) * (size_t)M);
+  float *d = (float *)malloc(sizeof(float) * (size_t)M);
+  for (int64_t j = J->j0; j < J->j1; j++) {
+    int32_t row = J->first_row + (int32_t)j;
+    int level = g->level[row];
+    const float *vec = g->vec + (size_t)row * g->dim;
+    int32_t elevator = -1;
+    for (int i = J->old_layers - 1; i >= 0; i--) {
+      int32_t sp = elevator >= 0 ? elevator : g->entry[i];
+      int cnt = layer_search(g, &v, &J->ctr, i, sp, M, J->ef, vec, ORA_MODE_REFERENCE, rows, d);
+      if (cnt == 0) {
+        J->fail = 1;
+        break;
+      }
+      elevator = rows[0];
+      if (level >= i) {
+        wave_slot *s = &J->slots[J->slot_off[j] + i];
+        s->row = row;
+        s->layer = i;
+        s->cnt = cnt;
+        memcpy(s->rows, rows, sizeof(int32_t) * (size_t)cnt);
+        memcpy(s->dists, d, sizeof(float) * (size_t)cnt);
+      }
+    }
+  }
+  free(rows);
+  free(d);
+  free(v.stamp);
+  return NULL;
+}
+
+typedef struct {
+  int32_t layer, n, worst;
+} wave_evict;
+
+typedef struct {
+  int32_t layer, row, deg; /* deg after replenish */
+  int32_t *list;           /* [M+1] staged list */
+} wave_rep;
+
+typedef struct {
+  ora_graph *g;
+  wave_rep *reps;
+  int64_t r0, r1;
+  ora_counters ctr;
+} waveD_job;
+
+/* graph.go:172-219 on the lists as they stand (read-only), result written to rep->list */
+static void wave_replenish(const ora_graph *g, wave_rep *rep, ora_counters *ctr, uint32_t *tab, uint32_t mask) {
+  int32_t *deg;
+  const int32_t *l = list_ptr(g, rep->layer, rep->row, &deg);
+  int m = g->M, dg = *deg;
+  memcpy(rep->list, l, sizeof(int32_t) * (size_t)dg);
+  rep->deg = dg;
+  if (dg >= m) return;
+  memset(tab, 0xff, sizeof(uint32_t) * (size_t)(mask + 1));
+#define TAB_INSERT(idv, fresh)                                   \
+  do {                                                           \
+    uint32_t h__ = ((uint32_t)(idv) * 2654435761u) >> 7;         \
+    for (;;) {                                                   \
+      h__ &= mask;                                               \
+      if (tab[h__] == 0xffffffffu) {                             \
+        tab[h__] = (uint32_t)(idv);                              \
+        fresh = 1;                                               \
+        break;                                                   \
+      }                                                          \
+      if (tab[h__] == (uint32_t)(idv)) {                         \
+        fresh = 0;                                               \
+        break;                                                   \
+      }                                                          \
+      h__++;                                                     \
+    }                                                            \
+  } while (0)
+  int fresh;
+  TAB_INSERT(rep->row, fresh);
+  for (int i = 0; i < dg; i++) TAB_INSERT(l[i], fresh);
+  ora_heap cand;
+  ora_heap_init(&cand, m * 2);
+  const float *nv = g->vec + (size_t)rep->row * g->dim;
+  for (int i = 0; i < dg; i++) {
+    int32_t *ndeg;
+    const int32_t *nl = list_ptr(g, rep->layer, l[i], &ndeg);
+    if (!nl) continue;
+    for (int j = 0; j < *ndeg; j++) {
+      int32_t c = nl[j];
+      TAB_INSERT(c, fresh);
+      if (!fresh) continue;
+      float d = gdist(g, ORA_COSINE, c, nv);
+      ctr->replenish_evals++;
+      ora_heap_push(&cand, d, c);
+    }
+  }
+#undef TAB_INSERT
+  while (cand.len > 0 && rep->deg < m) {
+    float d;
+    int32_t best;
+    ora_heap_pop(&cand, &d, &best);
+    list_insert(g, rep->list, &rep->deg, best);
+  }
+  ora_heap_free(&cand);
+}
+
+static void *waveD_worker(void *arg) {
+  waveD_job *J = (waveD_job *)arg;
+  int M = J->g->M;
+  uint32_t cap = 1;
+  while (cap < (uint32_t)(2 * (M * M + M + 2))) cap <<= 1;
+  uint32_t *tab = (uint32_t *)malloc(sizeof(uint32_t) * cap);
+  for (int64_t r = J->r0; r < J->r1; r++) wave_replenish(J->g, &J->reps[r], &J->ctr, tab, cap - 1);
+  free(tab);
+  return NULL;
+}
+
+static void ctr_add(ora_counters *a, const ora_counters *b) {
+  a->dist_evals += b->dist_evals;
+  a->expansions += b->expansions;
+  a->nbr_reads += b->nbr_reads;
+  a->evict_evals += b->evict_evals;
+  a->replenish_evals += b->replenish_evals;
+  a->evictions += b->evictions;
+}
+
+static int evict_cmp(const void *a, const void *b) {
+  const wave_evict *x = (const wave_evict *)a, *y = (const wave_evict *)b;
+  if (x->layer != y->layer) return x->layer < y->layer ? -1 : 1;
+  if (x->worst != y->worst) return x->worst < y->worst ? -1 : 1;
+  return 0;
+}
+
+/* one wave: rows first_row .. first_row+w-1 are already stored (new_row) but not linked */
+static int wave_commit(ora_graph *g, int32_t first_row, int64_t w, int ef, int n_threads) {
+  const int M = g->M, old_layers = g->n_layers;
+  int64_t *slot_off = (int64_t *)malloc(sizeof(int64_t) * (size_t)(w + 1));
+  int64_t ns = 0;
+  for (int64_t j = 0; j < w; j++) {
+    slot_off[j] = ns;
+    ns += g->level[first_row + j] + 1;
+  }
+  slot_off[w] = ns;
+  wave_slot *slots = (wave_slot *)calloc((size_t)ns, sizeof *slots);
+  int32_t *srows = (int32_t *)malloc(sizeof(int32_t) * (size_t)ns * M);
+  float *sd = (float *)malloc(sizeof(float) * (size_t)ns * M);
+  for (int64_t s = 0; s < ns; s++) {
+    slots[s].rows = srows + (size_t)s * M;
+    slots[s].dists = sd + (size_t)s * M;
+    slots[s].layer = -1;
+  }
+  /* ---- phase S ---- */
+  if (n_threads < 1) n_threads = 1;
+  int nt = (int)(w < n_threads ? w : n_threads);
+  waveS_job *sj = (waveS_job *)calloc((size_t)nt, sizeof *sj);
+  pthread_t *th = (pthread_t *)calloc((size_t)n_threads, sizeof *th);
+  int fail = 0;
+  for (int t = 0; t < nt; t++) {
+    sj[t].g = g;
+    sj[t].slots = slots;
+    sj[t].slot_off = slot_off;
+    sj[t].first_row = first_row;
+    sj[t].j0 = w * t / nt;
+    sj[t].j1 = w * (t + 1) / nt;
+    sj[t].ef = ef;
+    sj[t].old_layers = old_layers;
+    if (nt == 1) waveS_worker(&sj[t]);
+    else pthread_create(&th[t], NULL, waveS_worker, &sj[t]);
+  }
+  for (int t = 0; t < nt; t++) {
+    if (nt > 1) pthread_join(th[t], NULL);
+    ctr_add(&g->ctr, &sj[t].ctr);
+    fail |= sj[t].fail;
+  }
+  free(sj);
+  /* ---- phase A: own lists; layer membership ---- */
+  int64_t nreq = 0;
+  for (int64_t s = 0; s < ns && !fail; s++) {
+    wave_slot *S = &slots[s];
+    if (S->layer < 0) continue; /* a layer this wave opens: no links there */
+    int32_t *deg;
+    int32_t *l = list_ptr(g, S->layer, S->row, &deg);
+    for (int t = 0; t < S->cnt; t++) list_insert(g, l, deg, S->rows[t]);
+    nreq += S->cnt;
+  }
+  /* ---- phase B: targets take the new rows in input order; evictions recorded ---- */
+  wave_evict *ev = (wave_evict *)malloc(sizeof(wave_evict) * (size_t)(nreq + 1));
+  int64_t nev = 0;
+  for (int64_t s = 0; s < ns && !fail; s++) {
+    wave_slot *S = &slots[s];
+    if (S->layer < 0) continue;
+    for (int t = 0; t < S->cnt; t++) {
+      int32_t n = S->rows[t];
+      int32_t *deg;
+      int32_t *l = list_ptr(g, S->layer, n, &deg);
+      list_insert(g, l, deg, S->row);
+      if (*deg <= M) continue;
+      float worst_dist = -INFINITY;
+      int32_t worst = -1;
+      const float *nv = g->vec + (size_t)n * g->dim;
+      for (int i = 0; i < *deg; i++) {
+        float d = gdist(g, g->metric, l[i], nv);
+        g->ctr.evict_evals++;
+        if (d > worst_dist || worst < 0) {
+          worst_dist = d;
+          worst = l[i];
+        }
+      }
+      g->ctr.evictions++;
+      list_delete(g, l, deg, worst);
+      ev[nev].layer = S->layer;
+      ev[nev].n = n;
+      ev[nev].worst = worst;
+      nev++;
+    }
+  }
+  /* ---- phase C: back-links.  A row of this wave that a target evicted keeps its own (now one-directional) link,
+   * as the reference's newNode.addNeighbor(n) re-adds it right after n.addNeighbor(newNode) (graph.go:518-519),
+   * and is not replenished. ---- */
+  {
+    int64_t kept = 0;
+    for (int64_t e = 0; e < nev; e++)
+      if (ev[e].worst < first_row) ev[kept++] = ev[e];
+    nev = kept;
+  }
+  for (int64_t e = 0; e < nev; e++) {
+    int32_t *deg;
+    int32_t *l = list_ptr(g, ev[e].layer, ev[e].worst, &deg);
+    if (l) list_delete(g, l, deg, ev[e].n);
+  }
+  /* ---- phase D: replenish every distinct evicted node from the post-C lists, staged ---- */
+  qsort(ev, (size_t)nev, sizeof *ev, evict_cmp);
+  int64_t nrep = 0;
+  for (int64_t e = 0; e < nev; e++)
+    if (e == 0 || evict_cmp(&ev[e - 1], &ev[e]) != 0) ev[nrep++] = ev[e];
+  wave_rep *reps = (wave_rep *)calloc((size_t)(nrep + 1), sizeof *reps);
+  int32_t *rl = (int32_t *)malloc(sizeof(int32_t) * (size_t)(nrep + 1) * (M + 1));
+  for (int64_t r = 0; r < nrep; r++) {
+    reps[r].layer = ev[r].layer;
+    reps[r].row = ev[r].worst;
+    reps[r].list = rl + (size_t)r * (M + 1);
+  }
+  nt = (int)(nrep < n_threads ? nrep : n_threads);
+  if (nt < 1) nt = 1;
+  waveD_job *dj = (waveD_job *)calloc((size_t)nt, sizeof *dj);
+  for (int t = 0; t < nt; t++) {
+    dj[t].g = g;
+    dj[t].reps = reps;
+    dj[t].r0 = nrep * t / nt;
+    dj[t].r1 = nrep * (t + 1) / nt;
+    if (nt == 1) waveD_worker(&dj[t]);
+    else pthread_create(&th[t], NULL, waveD_worker, &dj[t]);
+  }
+  for (int t = 0; t < nt; t++) {
+    if (nt > 1) pthread_join(th[t], NULL);
+    ctr_add(&g->ctr, &dj[t].ctr);
+  }
+  free(dj);
+  free(th);
+  /* ---- phase E ---- */
+  for (int64_t r = 0; r < nrep; r++) {
+    int32_t *deg;
+    int32_t *l = list_ptr(g, reps[r].layer, reps[r].row, &deg);
+    memcpy(l, reps[r].list, sizeof(int32_t) * (size_t)reps[r].deg);
+    *deg = reps[r].deg;
+  }
+  free(reps);
+  free(rl);
+  free(ev);
+  free(slots);
+  free(srows);
+  free(sd);
+  free(slot_off);
+  return fail ? -1 : 0;
+}
+
+/* Batched Add in waves (see the banner above).  Returns the number of nodes inserted. */
+int64_t ora_graph_add_waves(ora_graph *g, const int64_t *keys, const float *vecs, const int32_t *levels, int64_t n,
+                            int ef, int64_t wave_max, int n_threads) {
+  int64_t i = 0;
+  while (i < n) {
+    int64_t w = ora_wave_len(g->n, g->n_layers, levels + i, n - i, wave_max);
+    int32_t first_row = (int32_t)g->n;
+    int top = g->n_layers;
+    for (int64_t j = 0; j < w; j++) {
+      if (levels[i + j] < 0 || levels[i + j] >= ORA_MAX_LAYERS) return i;
+      new_row(g, keys[i + j], vecs + (size_t)(i + j) * g->dim, levels[i + j]);
+      if (levels[i + j] + 1 > top) top = levels[i + j] + 1;
+    }
+    if (g->n_layers > 0 && wave_commit(g, first_row, w, ef, n_threads)) return i;
+    for (int64_t j = 0; j < w; j++)
+      for (int l = 0; l <= levels[i + j]; l++) {
+        if (l >= g->n_layers || g->layer_size[l] == 0) g->entry[l] = first_row + (int32_t)j;
+        g->layer_size[l]++;
+      }
+    if (top > g->n_layers) g->n_layers = top;
+    i += w;
+  }
+  return n;
+}
