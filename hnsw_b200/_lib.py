@@ -65,6 +65,8 @@ SYMBOLS = {
                                                C.c_void_p]),
     "b200hnsw_add_batch": (C.c_int, [C.c_void_p, f32p, i64p, i32p, C.c_int64, C.c_int32, C.c_int32, C.c_int32,
                                      C.POINTER(Stats)]),
+    "b200hnsw_add_batch_waves": (C.c_int, [C.c_void_p, f32p, i64p, i32p, C.c_int64, C.c_int32, C.c_int32, C.c_int32,
+                                           C.c_int64, C.POINTER(Stats)]),
     "b200hnsw_merge_topk_device": (C.c_int, [C.c_int32, C.c_int32, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p,
                                              C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "b200exact_create": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.POINTER(C.c_void_p)]),

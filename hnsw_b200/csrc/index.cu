@@ -117,6 +117,22 @@ int b200hnsw::ensure_capacity(int64_t rows, int64_t upper_slots, cudaStream_t s)
   return 0;
 }
 
+int b200hnsw::ensure_inboxes(cudaStream_t s) {
+  const int64_t want = d.cap + d.capU;
+  if (d.inbox && d.inbox_n == want) return 0;  // inboxes are left empty by every wave
+  if (d.inbox) cudaFree(d.inbox);
+  d.inbox = nullptr;
+  d.inbox_n = 0;
+  B200_CUDA(cudaMalloc(&d.inbox, sizeof(int32_t) * 4 * (size_t)want));
+  // heads = -1 (empty list), owners = 0x7f7f7f7f (larger than any request id)
+  B200_CUDA(cudaMemsetAsync(d.inbox, 0xff, sizeof(int32_t) * (size_t)want, s));
+  B200_CUDA(cudaMemsetAsync(d.inbox + want, 0x7f, sizeof(int32_t) * (size_t)want, s));
+  B200_CUDA(cudaMemsetAsync(d.inbox + 2 * want, 0xff, sizeof(int32_t) * (size_t)want, s));
+  B200_CUDA(cudaMemsetAsync(d.inbox + 3 * want, 0x7f, sizeof(int32_t) * (size_t)want, s));
+  d.inbox_n = want;
+  return 0;
+}
+
 extern "C" {
 
 int b200hnsw_abi_version(void) { return B200HNSW_ABI_VERSION; }
@@ -191,6 +207,7 @@ void b200hnsw_destroy(b200hnsw_t *h) {
   cudaFree(h->d.adj0);
   cudaFree(h->d.upper_off);
   cudaFree(h->d.adjU);
+  cudaFree(h->d.inbox);
   cudaFree(h->d_err_word);
   delete h;
 }
@@ -424,7 +441,7 @@ int b200hnsw_search_batch_device(b200hnsw_t *h, const float *d_queries, int64_t 
   // d_counters is int64[8]: evals, expansions, nbr_reads, overflowed queries, error flag, 3 spare
   int *d_err = d_counters ? reinterpret_cast<int *>(d_counters + 4) : h->d_err_word;
   return launch_search(h, d_queries, B, k, ef, metric, mode, entries, d_out_rows, d_out_dists, d_out_counts,
-                       reinterpret_cast<unsigned long long *>(d_counters), d_err, s);
+                       reinterpret_cast<unsigned long long *>(d_counters), d_err, h->vis_hint, s);
 }
 
 int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_t k, int32_t ef, int32_t metric,
@@ -470,31 +487,42 @@ int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_
   int *d_err = (int *)(d_ctr + 4);
   cudaStream_t s = c->stream;
   cudaError_t e;
-  if ((e = cudaMemcpyAsync(d_q, queries, qb, cudaMemcpyHostToDevice, s)) != cudaSuccess ||
-      (e = cudaMemsetAsync(d_ctr, 0, 64, s)) != cudaSuccess || (e = cudaEventRecord(c->ev0, s)) != cudaSuccess)
+  if ((e = cudaMemcpyAsync(d_q, queries, qb, cudaMemcpyHostToDevice, s)) != cudaSuccess)
     return fail(cuda_fail(e, "search staging"));
-  rc = launch_search(h, d_q, B, k, ef, metric, mode, entries, d_rows, d_dists, d_cnt, d_ctr, d_err, s);
-  if (rc) return fail(rc);
   unsigned long long ctr[5] = {0, 0, 0, 0, 0};
-  if ((e = cudaEventRecord(c->ev1, s)) != cudaSuccess ||
-      (e = cudaMemcpyAsync(out_rows, d_rows, rb, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
+  int launches = 0;
+  // A layer search that visits more nodes than the shared-memory visited table holds fails loudly in the kernel;
+  // the whole batch is then redone with a table 4x the size (sticky for later calls), so results are always exact.
+  for (int vis = h->vis_hint;; vis *= 4) {
+    if ((e = cudaMemsetAsync(d_ctr, 0, 64, s)) != cudaSuccess || (e = cudaEventRecord(c->ev0, s)) != cudaSuccess)
+      return fail(cuda_fail(e, "search staging"));
+    rc = launch_search(h, d_q, B, k, ef, metric, mode, entries, d_rows, d_dists, d_cnt, d_ctr, d_err, vis, s);
+    if (rc) return fail(rc);
+    launches++;
+    if ((e = cudaEventRecord(c->ev1, s)) != cudaSuccess ||
+        (e = cudaMemcpyAsync(ctr, d_ctr, 40, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
+        (e = cudaStreamSynchronize(s)) != cudaSuccess)
+      return fail(cuda_fail(e, "search kernel"));
+    if ((int)(ctr[4] & 0xffffffffu) == 0) break;
+    if (vis >= 16384) {
+      set_error("search: %llu queries overflowed the visited set (a layer search visited > %d nodes)", ctr[3], vis / 2);
+      return fail(B200HNSW_ERR_VISITED_OVERFLOW);
+    }
+    h->vis_hint = vis * 4;
+  }
+  if ((e = cudaMemcpyAsync(out_rows, d_rows, rb, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
       (e = cudaMemcpyAsync(out_dists, d_dists, db, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
       (e = cudaMemcpyAsync(out_counts, d_cnt, cb, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
-      (e = cudaMemcpyAsync(ctr, d_ctr, 40, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
       (e = cudaStreamSynchronize(s)) != cudaSuccess)
     return fail(cuda_fail(e, "search copy-back"));
   if (stats) {
     stats->dist_evals = (int64_t)ctr[0];
     stats->expansions = (int64_t)ctr[1];
     stats->nbr_reads = (int64_t)ctr[2];
-    stats->launches = 1;
+    stats->launches = launches;
     cudaEventElapsedTime(&stats->kernel_ms, c->ev0, c->ev1);
   }
   h->release(c);
-  if ((int)(ctr[4] & 0xffffffffu) != 0) {
-    set_error("search: %llu queries overflowed the visited set (layer search visited > 512 nodes)", ctr[3]);
-    return B200HNSW_ERR_VISITED_OVERFLOW;
-  }
   return 0;
 }
 

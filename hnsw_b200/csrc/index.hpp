@@ -43,6 +43,8 @@ struct DeviceGraph {
   int32_t *upper_off = nullptr; // [cap]
   int32_t *adjU = nullptr;      // [capU][M]
   int64_t cap = 0, capU = 0;
+  int32_t *inbox = nullptr;     // 4 x inbox_n: request heads/owners and eviction heads/owners per list slot (wave Add)
+  int64_t inbox_n = 0;
 };
 
 }  // namespace b200
@@ -61,6 +63,7 @@ struct b200hnsw {
   std::vector<int32_t> h_level;
   std::vector<int32_t> h_upper_off;
   int *d_err_word = nullptr;  // error flag for device-pointer calls that pass no counters
+  int vis_hint = 512;  // visited-table entries per traversal; raised (sticky) when a search overflows it
   int sm_count = 148;
   size_t smem_optin = 0;
   std::mutex pool_mu;
@@ -69,6 +72,7 @@ struct b200hnsw {
   b200::CallCtx *acquire();
   void release(b200::CallCtx *c);
   int ensure_capacity(int64_t rows, int64_t upper_slots, cudaStream_t s);
+  int ensure_inboxes(cudaStream_t s);
   b200::GraphView view() const;
 };
 
@@ -76,5 +80,7 @@ namespace b200 {
 // launchers implemented in the .cu files
 int launch_search(b200hnsw *h, const float *d_queries, int64_t B, int k, int ef, int metric, int mode,
                   const int32_t *entries, int32_t *d_rows, float *d_dists, int32_t *d_counts,
-                  unsigned long long *d_counters, int *d_error, cudaStream_t s);
+                  unsigned long long *d_counters, int *d_error, int vis_cap, cudaStream_t s);
+struct TraverseParams;
+int launch_traverse(b200hnsw *h, TraverseParams &p, int vis_cap, cudaStream_t s);
 }  // namespace b200

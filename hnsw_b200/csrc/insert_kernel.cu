@@ -15,6 +15,7 @@
 #include <vector>
 
 #include "index.hpp"
+#include "listops.cuh"
 
 namespace b200 {
 
@@ -62,80 +63,6 @@ struct InsCtl {
   int abort_;
   int entries[B200HNSW_MAX_LAYERS];
 };
-
-// ---- warp-level list helpers (lists: stride M, sorted by key, -1 padded) -----------------------------------------
-
-// load a list into shared memory; returns its degree (uniform over the warp)
-__device__ __forceinline__ int warp_load_list(const int32_t *lp, int M, int *dst, int lane) {
-  int deg = 0;
-  for (int base = 0; base < M; base += 32) {
-    int v = -1;
-    if (base + lane < M) v = lp[base + lane];
-    unsigned mk = __ballot_sync(FULL, v >= 0);
-    if (base + lane < M) dst[base + lane] = v;
-    deg += __popc(mk);
-    if (mk != FULL) break;
-  }
-  __syncwarp();
-  return deg;
-}
-
-// write `len` entries from shared memory, pad the rest of the stride with -1
-__device__ __forceinline__ void warp_store_list(int32_t *lp, int M, const int *src, int len, int lane) {
-  for (int i = lane; i < M; i += 32) lp[i] = i < len ? src[i] : -1;
-}
-
-// sorted insert of x into the shared-memory list l[0..deg): returns new degree (unchanged if x is present: Go map
-// overwrite, graph.go:50).  Executed by one warp; the result is in l[].
-__device__ __forceinline__ int warp_sorted_insert(int *l, int deg, int x, const int64_t *keys, int lane) {
-  long long kx = keys[x];
-  int pos = 0;
-  bool present = false;
-  for (int base = 0; base < deg; base += 32) {
-    int i = base + lane;
-    int v = i < deg ? l[i] : -1;
-    bool lt = false;
-    if (v >= 0) {
-      present = present || (v == x);
-      lt = keys[v] < kx;
-    }
-    pos += __popc(__ballot_sync(FULL, lt));
-  }
-  if (__any_sync(FULL, present)) return deg;
-  // shift right from the end (single pass, each lane moves its element after all have read)
-  int moved[2];
-  int cntm = 0;
-  for (int i = pos + lane; i < deg; i += 32) moved[cntm++] = l[i];
-  __syncwarp();
-  cntm = 0;
-  for (int i = pos + lane; i < deg; i += 32) l[i + 1] = moved[cntm++];
-  if (lane == 0) l[pos] = x;
-  __syncwarp();
-  return deg + 1;
-}
-
-// remove x from l[0..deg) if present; returns new degree
-__device__ __forceinline__ int warp_list_remove(int *l, int deg, int x, int lane) {
-  int pos = -1;
-  for (int base = 0; base < deg; base += 32) {
-    int i = base + lane;
-    bool hit = i < deg && l[i] == x;
-    unsigned mk = __ballot_sync(FULL, hit);
-    if (mk) {
-      pos = base + __ffs(mk) - 1;
-      break;
-    }
-  }
-  if (pos < 0) return deg;
-  int moved[2];
-  int cntm = 0;
-  for (int i = pos + 1 + lane; i < deg; i += 32) moved[cntm++] = l[i];
-  __syncwarp();
-  cntm = 0;
-  for (int i = pos + 1 + lane; i < deg; i += 32) l[i - 1] = moved[cntm++];
-  __syncwarp();
-  return deg - 1;
-}
 
 // ---- block-wide state -------------------------------------------------------------------------------------------
 template <int CPL, int U>

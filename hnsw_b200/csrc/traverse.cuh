@@ -1,0 +1,261 @@
+// traverse.cuh -- K1: the layer descent of Graph.Search / BatchSearch (graph.go:571-593, 1075-1106) and of the search
+// half of Graph.Add (graph.go:475-508) as a STEP MACHINE.
+//
+// A warp serves 32/G traversals at once, one per group of G lanes.  Every iteration of the warp-uniform loop lets each
+// group do one step of its own traversal, whatever layer it is in:
+//     INIT   : evaluate the layer's entry point (graph.go:107-123)
+//     EXPAND : read the popped node's neighbour list (ascending key order, graph.go:137-138), drop the visited ones,
+//              evaluate the rest U rows at a time (16 B loads, all U rows in flight before the first reduction)
+// then the group's leader lane replays the order-dependent part (graph.go:146-166) on the Go-exact shared-memory
+// heaps (goheap.cuh).  The leaders of all groups run that serial code together, so its cost is shared by 32/G
+// traversals, and a group never waits for another group's layer to end.
+#pragma once
+#include "gdist.cuh"
+#include "goheap.cuh"
+#include "layer_search.cuh"
+
+namespace b200 {
+
+struct TraverseParams {
+  const float *queries;   // query t starts at queries + t * q_stride
+  long long q_stride;
+  long long B;
+  int k;         // result size on layer 0
+  int k_upper;   // result size on layers > 0: 1 for Search (graph.go:579), M for Add (graph.go:500)
+  int ef, metric, n_layers;
+  int entries[B200HNSW_MAX_LAYERS];
+  // Search sink: layer-0 results in heap-array order
+  int32_t *out_rows;    // [B][k]
+  float *out_dists;     // [B][k]
+  int32_t *out_counts;  // [B]
+  // Add sink (out_rows == nullptr): results of every layer <= levels[t] go to slot slot_off[t] + layer
+  const int32_t *levels;     // [B]
+  const long long *slot_off; // [B]
+  int32_t *slot_cnt;         // [slots]
+  int32_t *slot_rows;        // [slots][sink_stride]
+  float *slot_dists;         // [slots][sink_stride]
+  int sink_stride;
+  unsigned long long *counters;  // [4]: evals, expansions, nbr_reads, overflowed traversals (may be null)
+  int *error;                    // set to 1 on visited overflow
+  int vis_cap;                   // visited-table entries per group (power of two)
+  int heap_c, heap_r, fresh_cap; // per-group slots: uint2, uint2, int
+};
+
+__host__ __device__ inline size_t traverse_group_bytes(const TraverseParams &p) {
+  return (size_t)(p.heap_c + p.heap_r) * 8 + (size_t)p.fresh_cap * 4 + (size_t)p.vis_cap * 4;
+}
+
+constexpr int TRAV_WARPS = 4;
+
+enum { ST_NEED = 0, ST_INIT = 1, ST_EXPAND = 2, ST_IDLE = 3 };
+
+template <int G, int CH, int U>
+__global__ void __launch_bounds__(TRAV_WARPS * 32) traverse_kernel(GraphView g, TraverseParams p) {
+  constexpr int NG = 32 / G;
+  constexpr unsigned GBITS = G == 32 ? 0xffffffffu : ((1u << G) - 1u);
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const int gl = lane & (G - 1);
+  const int grp = lane / G;
+  const int gshift = grp * G;
+  const int leader_lane = gshift;
+  const bool leader = gl == 0;
+  const size_t gbytes = traverse_group_bytes(p);
+  unsigned char *base = smem + gbytes * (size_t)(warp * NG + grp);
+  GoHeap C{reinterpret_cast<uint2 *>(base), 0};
+  GoHeap R{reinterpret_cast<uint2 *>(base) + p.heap_c, 0};
+  int *fresh = reinterpret_cast<int *>(base + (size_t)(p.heap_c + p.heap_r) * 8);
+  uint32_t *vtab = reinterpret_cast<uint32_t *>(base + (size_t)(p.heap_c + p.heap_r) * 8 + (size_t)p.fresh_cap * 4);
+  const uint32_t vmask = (uint32_t)p.vis_cap - 1;
+  const int M = g.M;
+
+  __shared__ int s_entries[B200HNSW_MAX_LAYERS];
+  for (int i = threadIdx.x; i < B200HNSW_MAX_LAYERS; i += blockDim.x) s_entries[i] = p.entries[i];
+  __syncthreads();
+
+  const long long n_groups = (long long)gridDim.x * TRAV_WARPS * NG;
+  long long q = ((long long)blockIdx.x * TRAV_WARPS + warp) * NG + grp - n_groups;  // advanced before first use
+  int st = ST_NEED, layer = 0, cur = -1, elevator = -1, kcur = 1, vcount = 0, lvl = -1;
+  GQuery<CH> Q;
+#pragma unroll
+  for (int t = 0; t < CH; t++) Q.q[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+  Q.qq = 0.f;
+  unsigned long long c_evals = 0, c_exp = 0, c_nbr = 0, c_over = 0;  // meaningful in leader lanes
+
+  for (;;) {
+    // ---- fetch the next traversal for groups that finished one --------------------------------------------------
+    const bool need = st == ST_NEED;
+    if (__any_sync(FULL, need)) {
+      if (need) {
+        q += n_groups;
+        if (q >= p.B) st = ST_IDLE;
+      }
+      const bool on = need && st != ST_IDLE;
+      GQuery<CH> NQ;
+      group_load_query<G, CH>(NQ, p.queries + (on ? q : 0) * p.q_stride, on, g.dim, g.row_chunks, gl);
+      if (on) {
+        Q = NQ;
+        layer = p.n_layers - 1;
+        elevator = -1;
+        lvl = p.levels ? p.levels[q] : -1;
+        st = ST_INIT;
+      }
+    }
+    if (__all_sync(FULL, st == ST_IDLE)) break;
+    const bool init = st == ST_INIT, expand = st == ST_EXPAND;
+    bool improved = false;  // leader
+    int nfresh = 0;
+    // ---- INIT: reset the queues and the visited set, the entry point is the only row to evaluate -----------------
+    if (init) {
+      cur = elevator >= 0 ? elevator : s_entries[layer];  // graph.go:572-575 / 492-498
+      kcur = layer > 0 ? p.k_upper : p.k;
+      C.len = 0;
+      R.len = 0;
+      uint4 e4 = make_uint4(~0u, ~0u, ~0u, ~0u);
+      uint4 *t4 = reinterpret_cast<uint4 *>(vtab);
+      for (uint32_t i = gl; i < (vmask + 1) / 4; i += G) t4[i] = e4;
+      vcount = 0;
+      if (cur >= 0) {
+        if (leader) fresh[0] = cur;
+        nfresh = 1;
+      }
+    }
+    __syncwarp();
+    // ---- EXPAND: neighbour list of `cur`, ascending key order, unvisited only (graph.go:137-144) ----------------
+    if (__any_sync(FULL, expand)) {
+      const int32_t *list = nullptr;
+      if (expand) {
+        if (layer == 0) list = g.adj0 + (size_t)cur * M;
+        else list = g.adjU + ((size_t)g.upper_off[cur] + (layer - 1)) * M;
+        if (leader) c_exp++;
+      }
+      bool more = expand;
+      for (int b0 = 0; b0 < M; b0 += G) {
+        int nb = -1;
+        if (more && b0 + gl < M) nb = list[b0 + gl];
+        const bool valid = nb >= 0;
+        const unsigned gv = (__ballot_sync(FULL, valid) >> gshift) & GBITS;
+        bool fr = false;
+        if (valid) {  // exact visited set: open addressing, empty = 0xffffffff
+          uint32_t h = ((uint32_t)nb * 2654435761u) >> 7;
+          for (;;) {
+            h &= vmask;
+            uint32_t old = atomicCAS(&vtab[h], ~0u, (uint32_t)nb);
+            if (old == ~0u) {
+              fr = true;
+              break;
+            }
+            if (old == (uint32_t)nb) break;
+            h++;
+          }
+        }
+        const unsigned gf = (__ballot_sync(FULL, fr) >> gshift) & GBITS;
+        if (fr) fresh[nfresh + __popc(gf & ((1u << gl) - 1u))] = nb;
+        nfresh += __popc(gf);
+        if (leader) c_nbr += __popc(gv);
+        if (gv != GBITS) more = false;  // lists are -1 padded at the end
+        if (!__any_sync(FULL, more)) break;
+      }
+      vcount += nfresh;
+    }
+    __syncwarp();
+    const bool overflow = vcount * 2 > (int)vmask;  // load factor > 1/2: fail loudly, never approximate
+    if (overflow) nfresh = 0;
+    // ---- evaluate the fresh rows, U at a time; the leader replays graph.go:146-159 in key order -------------------
+    for (int b0 = 0; __any_sync(FULL, b0 < nfresh); b0 += U) {
+      int ids[U];
+#pragma unroll
+      for (int u = 0; u < U; u++) ids[u] = b0 + u < nfresh ? fresh[b0 + u] : -1;
+      const float dmine = group_distances<G, CH, U>(g.vec, g.row_chunks, ids, Q, p.metric, gl);
+      float d[U];
+#pragma unroll
+      for (int u = 0; u < U; u++) d[u] = __shfl_sync(FULL, dmine, leader_lane + u * (G / U));
+      if (leader) {
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+          if (ids[u] < 0) continue;
+          c_evals++;
+          if (init) {  // graph.go:109-123
+            C.push(d[u], ids[u]);
+            R.push(d[u], ids[u]);
+            uint32_t h = ((uint32_t)ids[u] * 2654435761u) >> 7;
+            vtab[h & vmask] = (uint32_t)ids[u];
+            continue;
+          }
+          improved = improved || (R.len > 0 && d[u] < R.min_dist());  // graph.go:147
+          if (R.len < kcur) {
+            R.push(d[u], ids[u]);
+          } else if (d[u] < R.max_dist()) {  // result.Max() is the last array slot
+            R.pop_last();
+            R.push(d[u], ids[u]);
+          }
+          C.push(d[u], ids[u]);
+          if (C.len > p.ef) C.pop_last();  // graph.go:157-159
+        }
+      }
+    }
+    if (init && nfresh > 0) vcount = 1;
+    // ---- leader decides: next node, end of layer ---------------------------------------------------------------------
+    int next = -1;
+    if (leader && (init || expand) && !overflow) {
+      if (init) {
+        if (nfresh > 0) next = (int)C.pop().y;                     // graph.go:125-127, first iteration
+      } else if (!(!improved && R.len >= kcur) && C.len > 0) {      // graph.go:164-166, 125
+        next = (int)C.pop().y;
+      }
+    }
+    next = __shfl_sync(FULL, next, leader_lane);
+    const int rlen = __shfl_sync(FULL, R.len, leader_lane);
+    __syncwarp();  // the leader's heap writes are visible to its group
+    if (init || expand) {
+      if (overflow) {
+        if (leader) {
+          *p.error = 1;
+          c_over++;
+          if (p.out_counts) p.out_counts[q] = -1;
+          else p.slot_cnt[p.slot_off[q]] = -1;
+        }
+        st = ST_NEED;
+      } else if (next >= 0) {
+        cur = next;
+        st = ST_EXPAND;
+      } else {
+        // ---- end of this layer: results are the raw heap array (graph.go:169) ----------------------------------
+        if (p.out_rows) {
+          if (layer == 0) {  // graph.go:588-593
+            for (int i = gl; i < p.k; i += G) {
+              const bool ok = i < rlen;
+              p.out_rows[q * p.k + i] = ok ? R.id(i) : -1;
+              p.out_dists[q * p.k + i] = ok ? R.dist(i) : __int_as_float(0x7fc00000);
+            }
+            if (leader) p.out_counts[q] = rlen;
+          }
+        } else if (layer <= lvl) {  // graph.go:510: this layer takes the new node
+          const long long slot = p.slot_off[q] + layer;
+          for (int i = gl; i < rlen; i += G) {
+            p.slot_rows[slot * p.sink_stride + i] = R.id(i);
+            p.slot_dists[slot * p.sink_stride + i] = R.dist(i);
+          }
+          if (leader) p.slot_cnt[slot] = rlen;
+        }
+        if (rlen > 0) elevator = R.id(0);  // graph.go:584 / 508
+        if (layer == 0) {
+          st = ST_NEED;
+        } else {
+          layer--;
+          st = ST_INIT;
+        }
+      }
+    }
+    __syncwarp();  // every lane has read R before the leader reuses it
+  }
+  if (p.counters && leader) {
+    if (c_evals) atomicAdd(&p.counters[0], c_evals);
+    if (c_exp) atomicAdd(&p.counters[1], c_exp);
+    if (c_nbr) atomicAdd(&p.counters[2], c_nbr);
+    if (c_over) atomicAdd(&p.counters[3], c_over);
+  }
+}
+
+}  // namespace b200

@@ -195,20 +195,26 @@ class Graph:
             keys.append(int(k))
         self._add_arrays(keys, np.stack(vecs), levels, metric)
 
-    def _add_arrays(self, keys, V, levels, metric):
+    def _add_arrays(self, keys, V, levels, metric, wave_max=0):
         lv = np.ascontiguousarray(levels, dtype=np.int32) if levels is not None else self._draw_levels(len(keys))
         V = np.ascontiguousarray(V, dtype=np.float32)
         K = np.ascontiguousarray(keys, dtype=np.int64)
         st = _lib.Stats()
-        _lib.check(_lib.lib().b200hnsw_add_batch(self._h, V.ctypes.data_as(_lib.f32p), K.ctypes.data_as(_lib.i64p),
-                                                 lv.ctypes.data_as(_lib.i32p), len(K), self.M, self.EfSearch,
-                                                 metric, C.byref(st)))
+        if wave_max and wave_max > 0:  # batched construction in waves (not the reference's sequential order)
+            _lib.check(_lib.lib().b200hnsw_add_batch_waves(
+                self._h, V.ctypes.data_as(_lib.f32p), K.ctypes.data_as(_lib.i64p), lv.ctypes.data_as(_lib.i32p),
+                len(K), self.M, self.EfSearch, metric, int(wave_max), C.byref(st)))
+        else:
+            _lib.check(_lib.lib().b200hnsw_add_batch(self._h, V.ctypes.data_as(_lib.f32p),
+                                                     K.ctypes.data_as(_lib.i64p), lv.ctypes.data_as(_lib.i32p),
+                                                     len(K), self.M, self.EfSearch, metric, C.byref(st)))
         self.last_stats = st.as_dict()
         self._store_host([int(k) for k in K], V)
 
-    def add_arrays(self, keys, vectors, levels: Optional[Sequence[int]] = None):
+    def add_arrays(self, keys, vectors, levels: Optional[Sequence[int]] = None, wave_max: int = 0):
         """BatchAdd for array inputs (keys[n] int64, vectors[n, dim] float32): same semantics, no per-node objects.
-        Keys must be new and distinct."""
+        Keys must be new and distinct.  wave_max > 0 selects the wave-batched construction
+        (b200hnsw_add_batch_waves): parallel, deterministic, NOT the reference's sequential graph."""
         self.Validate()
         vectors = np.asarray(vectors, dtype=np.float32)
         if vectors.ndim != 2 or len(keys) != vectors.shape[0]:
@@ -222,7 +228,7 @@ class Graph:
         self._ensure_device(dim0)
         if self.M > self._max_m:
             raise ValueError(f"M={self.M} exceeds the device list stride {self._max_m} fixed at the first Add")
-        self._add_arrays(keys, vectors, levels, metric)
+        self._add_arrays(keys, vectors, levels, metric, wave_max)
 
     def Add(self, *nodes: Node, levels: Optional[Sequence[int]] = None):
         """graph.go:437-531 (same body as BatchAdd; the reference's Add deadlocks on a duplicate key, F9)."""

@@ -136,6 +136,18 @@ int b200hnsw_search_batch_device(b200hnsw_t *h, const float *d_queries, int64_t 
 int b200hnsw_add_batch(b200hnsw_t *h, const float *vectors, const int64_t *keys, const int32_t *levels, int64_t n,
                        int32_t m, int32_t ef, int32_t metric, b200hnsw_stats *stats);
 
+/* Batched construction in WAVES.  NOT the reference's order: the nodes of a wave (at most wave_max, never more than
+ * 1/16 of the rows already present) all search the graph as it was before the wave (K1 kernel, k = M on every layer,
+ * graph.go:475-508) and their links are then committed in deterministic parallel phases that apply the reference's
+ * heuristic (link to every result, evict the farthest on overflow, delete the back-link, replenish the evicted node
+ * with CosineDistance: graph.go:41-81, 172-219).  The result is independent of scheduling and is restated on the CPU
+ * by the oracle (ora_graph_add_waves) for bit-exact checks; it is NOT the graph b200hnsw_add_batch builds.  This is
+ * the throughput path north_star calls "batched Add"; use b200hnsw_add_batch when the reference's exact graph is
+ * required. */
+int b200hnsw_add_batch_waves(b200hnsw_t *h, const float *vectors, const int64_t *keys, const int32_t *levels,
+                             int64_t n, int32_t m, int32_t ef, int32_t metric, int64_t wave_max,
+                             b200hnsw_stats *stats);
+
 /* ---- multi-GPU: merge G per-shard result lists per query into one top-k (no reference counterpart; tie order =
  *      lower shard first, the stable order of hybrid/adapter.go:264-292).  Inputs [G][B][k] ascending-sorted
  *      per shard or heap-ordered (sorted_in=0); ids are int64 global ids.  Device pointers. ----------------- */
