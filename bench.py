@@ -35,7 +35,7 @@ sys.path.insert(0, str(ROOT))
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--n", type=int, default=1_000_000, help="rows per GPU (BASELINE configs[1]: 1M)")
@@ -45,6 +45,9 @@ def parse_args():
     ap.add_argument("--ef", type=int, default=64)
     ap.add_argument("--k", type=int, default=10)
     ap.add_argument("--ml", type=float, default=0.25)
+    ap.add_argument("--wave-max", type=int, default=4096,
+                    help="nodes per construction wave (b200hnsw_add_batch_waves); 0 = exact sequential Graph.Add")
+    ap.add_argument("--pool", type=int, default=16, help="distinct query batches cycled through the steps")
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="target length of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -68,38 +71,63 @@ def draw_levels(n, ml, seed):
 
 
 class ClockSampler(threading.Thread):
-    """Samples nvidia-smi clocks / throttle reasons of one GPU while the timed region runs."""
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """Samples SM clock / power / throttle reasons of one GPU through NVML while the timed region runs."""
 
-    def __init__(self, index):
+    def __init__(self, index, period_s=0.002):
         super().__init__(daemon=True)
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.period, self.rows, self._stop_ev = index, period_s, [], threading.Event()
+        self.max_mhz, self.ok = None, False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.ok = True
+        except Exception:
+            self.ok = False
+
+    def sample(self):
+        nv = self.nv
+        mhz = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+        try:
+            reasons = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+        except Exception:
+            reasons = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+        try:
+            power = nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0
+        except Exception:
+            power = None
+        self.rows.append((float(mhz), int(reasons), power))
 
     def run(self):
-        try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-i", str(self.index), "-lms", "100"], stdout=subprocess.PIPE, text=True)
-            for line in self.proc.stdout:
-                self.rows.append([c.strip() for c in line.split(",")])
-        except Exception:
-            pass
+        if not self.ok:
+            return
+        while not self._stop_ev.is_set():
+            try:
+                self.sample()
+            except Exception:
+                break
+            time.sleep(self.period)
 
     def stop(self):
-        if self.proc is not None:
-            self.proc.terminate()
+        self._stop_ev.set()
         self.join(timeout=2)
-        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
-        reasons = set()
-        for r in self.rows:
-            for name, col in (("hw_slowdown", 3), ("hw_thermal_slowdown", 4), ("sw_thermal_slowdown", 5),
-                              ("sw_power_cap", 6)):
-                if len(r) > col and r[col].lower().startswith("active"):
-                    reasons.add(name)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        if not self.ok or not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "samples": 0}
+        nv = self.nv
+        bits = {"hw_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8),
+                "hw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40),
+                "sw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20),
+                "sw_power_cap": getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4)}
+        seen = set()
+        for _, r, _ in self.rows:
+            for name, bit in bits.items():
+                if r & bit:
+                    seen.add(name)
+        pw = [p for _, _, p in self.rows if p is not None]
+        return {"sm_mhz": float(np.median([m for m, _, _ in self.rows])), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(seen), "samples": len(self.rows), "power_w_max": max(pw) if pw else None}
 
 
 def load_peaks():
@@ -138,17 +166,29 @@ def run_reference(args, rank, world):
     cores = os.cpu_count() or 1
     X = synth_rows(args.n, args.dim, 42)
     levels = draw_levels(args.n, args.ml, 44)
+    keys = np.arange(args.n, dtype=np.int64)
+    # Graph.Add exactly as the reference does it (serial, graph.go:445) on a bounded sample: the build rate reported
+    ns = min(args.n, 20000)
+    gs = oracle.Graph(args.dim, args.m, oracle.EUCLIDEAN, oracle.SIMD)
+    t0 = time.perf_counter()
+    gs.add_many(keys[:ns], X[:ns], levels[:ns], args.ef)
+    serial_rate = ns / (time.perf_counter() - t0)
+    del gs
+    # the graph that is searched: the same one our arm builds (wave schedule, deterministic), built on all cores
     g = oracle.Graph(args.dim, args.m, oracle.EUCLIDEAN, oracle.SIMD)
     t0 = time.perf_counter()
-    g.add_many(np.arange(args.n, dtype=np.int64), X, levels, args.ef)
+    if args.wave_max > 0:
+        g.add_waves(keys, X, levels, args.ef, args.wave_max, n_threads=cores)
+    else:
+        g.add_many(keys, X, levels, args.ef)
     build_s = time.perf_counter() - t0
-    nb = args.warmup + args.steps
+    nb = min(args.warmup + args.steps, args.pool)
     Q = synth_rows(nb * args.batch, args.dim, 43).reshape(nb, args.batch, args.dim)
     for i in range(args.warmup):
-        g.batch_search(Q[i], args.k, args.ef, n_threads=cores)
+        g.batch_search(Q[i % nb], args.k, args.ef, n_threads=cores)
     t0 = time.perf_counter()
     for i in range(args.steps):
-        g.batch_search(Q[args.warmup + i], args.k, args.ef, n_threads=cores)
+        g.batch_search(Q[(args.warmup + i) % nb], args.k, args.ef, n_threads=cores)
     dt = time.perf_counter() - t0
     qps = args.steps * args.batch / dt
     line = {
@@ -159,10 +199,11 @@ def run_reference(args, rank, world):
         "config": workload_config(args, 1),
         "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": cores, "kind": "port",
                          "sample": f"{args.steps} x {args.batch} queries, one query per thread over {cores} threads, "
-                                   f"AVX2 distance; graph built by the same port in {build_s:.1f} s (single thread, "
-                                   f"{args.n / build_s:.0f} vec/s)"},
+                                   f"AVX2 distance; graph = the wave-scheduled construction our arm uses, built by the "
+                                   f"port on {cores} threads in {build_s:.1f} s; the reference's serial Graph.Add runs "
+                                   f"at {serial_rate:.0f} vec/s here (first {ns} rows)"},
         "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "build_vec_per_s": args.n / build_s, "gpu_launches": 0,
+        "build_vec_per_s": serial_rate, "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
     return 0
@@ -176,8 +217,8 @@ def workload_config(args, world):
             "batch": args.batch, "mode": "reference (bit-faithful layerNode.search termination)",
             "layout": "1 graph" if world == 1 else
             f"{world} independent sub-graphs (one per GPU), queries broadcast, NCCL all-gather + top-k merge",
-            "l2_policy": "inputs larger than L2: 576 MB of graph per GPU gathered at random, a fresh query batch "
-                         "every step"}
+            "l2_policy": f"inputs larger than L2: {args.n * (args.dim * 4 + args.m * 4) / 1e6:.0f} MB of graph per GPU "
+                         f"gathered at random; a pool of {args.pool} distinct query batches cycled through the steps"}
 
 
 # ------------------------------------------------------------------------------------------------------ our arm
@@ -200,20 +241,28 @@ def run_ours(args, rank, local_rank, world):
         dist.init_process_group("nccl", device_id=dev)
     n, dim, B, k, ef = args.n, args.dim, args.batch, args.k, args.ef
 
-    # ---- build this rank's sub-graph with the device Add path (exact reference order) -------------------------
+    # ---- build this rank's sub-graph on the device -------------------------------------------------------------------
     X = synth_rows(n, dim, 42 + rank)
     levels = draw_levels(n, args.ml, 44 + rank)
     g = hnsw_b200.Graph(M=args.m, Ml=args.ml, EfSearch=ef, Distance=hnsw_b200.EuclideanDistance, device=local_rank,
                         capacity=n)
     keys = np.arange(n, dtype=np.int64) + rank * n  # global ids
     t0 = time.perf_counter()
-    g.add_arrays(keys, X, levels)
+    g.add_arrays(keys, X, levels, wave_max=args.wave_max)
     build_wall = time.perf_counter() - t0
     bst = g.last_stats
     build_kernel_s = bst["kernel_ms"] / 1e3
+    seq_rate = None
+    if rank == 0 and world == 1:  # the reference's exact sequential order on a bounded sample (K2, insert_kernel.cu)
+        ns = min(n, 4000)
+        gs = hnsw_b200.Graph(M=args.m, Ml=args.ml, EfSearch=ef, Distance=hnsw_b200.EuclideanDistance,
+                             device=local_rank, capacity=ns)
+        gs.add_arrays(keys[:ns], X[:ns], levels[:ns])
+        seq_rate = ns / (gs.last_stats["kernel_ms"] / 1e3)
+        gs.close()
 
-    # ---- synthetic queries: a fresh batch per step, identical on every rank (the "broadcast" of north_star) ----
-    nb = args.warmup + args.steps
+    # ---- synthetic queries: a pool of distinct batches cycled through the steps, identical on every rank ----------
+    nb = max(1, min(args.warmup + args.steps, args.pool))
     Qh = torch.from_numpy(synth_rows(nb * B, dim, 43).reshape(nb, B, dim)).pin_memory()
     Qd = Qh.to(dev)
     rows = torch.empty((B, k), dtype=torch.int32, device=dev)
@@ -235,7 +284,7 @@ def run_ours(args, rank, local_rank, world):
                         counters.data_ptr(), stream.cuda_stream)
 
     def merge_step():
-        torch.add(rows, rank * n, out=ids)  # shard row -> global id (-1 stays negative only for rank 0; masked by counts)
+        torch.add(rows, rank * n, out=ids)  # shard row -> global id (unused slots are masked by counts)
         dist.all_gather_into_tensor(all_d, dists)
         dist.all_gather_into_tensor(all_i, ids)
         dist.all_gather_into_tensor(all_c, counts)
@@ -254,7 +303,7 @@ def run_ours(args, rank, local_rank, world):
 
     # ---- device-resident timing: W warm-up steps, then exactly K steps between events ---------------------------
     for i in range(args.warmup):
-        search_step(Qd[i])
+        search_step(Qd[i % nb])
         if world > 1:
             merge_step()
     barrier()
@@ -266,7 +315,7 @@ def run_ours(args, rank, local_rank, world):
     ev0.record(stream)
     for i in range(args.steps):
         ka[i].record(stream)
-        search_step(Qd[args.warmup + i])
+        search_step(Qd[(args.warmup + i) % nb])
         kb[i].record(stream)
         if world > 1:
             merge_step()
@@ -275,6 +324,9 @@ def run_ours(args, rank, local_rank, world):
     total_ms = ev0.elapsed_time(ev1)
     kernel_ms = [a.elapsed_time(b) for a, b in zip(ka, kb)]
     ctr = counters.cpu().numpy().copy()
+    if int(ctr[4]) != 0:
+        raise SystemExit("bench.py: a traversal overflowed the visited set in the device-pointer path")
+    last = (args.warmup + args.steps - 1) % nb
     last_rows, last_dists, last_counts = rows.cpu().numpy(), dists.cpu().numpy(), counts.cpu().numpy()
     t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
     if world > 1:
@@ -300,12 +352,12 @@ def run_ours(args, rank, local_rank, world):
             h_md.copy_(m_d, non_blocking=True)
             torch.cuda.synchronize(dev)
 
-    for i in range(min(args.warmup, 3)):
-        e2e_step(i)
+    for i in range(max(args.warmup, 3)):
+        e2e_step(i % nb)
     barrier()
     t0 = time.perf_counter()
     for i in range(args.steps):
-        e2e_step(args.warmup + i)
+        e2e_step((args.warmup + i) % nb)
     torch.cuda.synchronize(dev)
     e2e_s = time.perf_counter() - t0
     t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
@@ -333,18 +385,23 @@ def run_ours(args, rank, local_rank, world):
         "gpu_launches": args.steps * (1 if world == 1 else 2),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": (traffic or {}).get("dram_bytes_per_launch"),
-                     "kernel": "b200::search_kernel<1,8>", "kernel_ms": kern_avg_ms,
+                     "kernel": "b200::traverse_kernel (K1, traverse.cuh)", "kernel_ms": kern_avg_ms,
                      "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
                      "dist_evals_per_query": float(ctr[0]) / (args.steps * B),
                      "expansions_per_query": float(ctr[1]) / (args.steps * B)},
         "clocks": clocks,
         "build": {"vec_per_s": n * world / build_wall, "kernel_vec_per_s": n / build_kernel_s, "wall_s": build_wall,
-                  "semantics": "exact sequential Graph.Add order (bit-identical to the oracle)",
-                  "evals_per_insert": (bst["dist_evals"] + bst["evict_evals"] + bst["replenish_evals"]) / n},
+                  "semantics": (f"wave-batched Add, waves of <= {args.wave_max} nodes (b200hnsw_add_batch_waves; "
+                                "bit-identical to the oracle's restatement of the same schedule, NOT the reference's "
+                                "sequential graph)") if args.wave_max > 0 else
+                  "exact sequential Graph.Add order (bit-identical to the oracle)",
+                  "launches": bst["launches"],
+                  "evals_per_insert": (bst["dist_evals"] + bst["evict_evals"] + bst["replenish_evals"]) / n,
+                  "exact_sequential_vec_per_s": seq_rate},
     }
 
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        line.update(cpu_baseline_and_parity(args, g, Qh, last_rows, last_dists, last_counts, torch, dev, X))
+        line.update(cpu_baseline_and_parity(args, g, Qh, last, last_rows, last_dists, last_counts, torch, dev, X))
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -353,7 +410,7 @@ def run_ours(args, rank, local_rank, world):
     return 0
 
 
-def cpu_baseline_and_parity(args, g, Qh, last_rows, last_dists, last_counts, torch, dev, X):
+def cpu_baseline_and_parity(args, g, Qh, last, last_rows, last_dists, last_counts, torch, dev, X):
     """Rank 0, N=1: time the CPU port on the SAME graph (read back from the device) and check the GPU's last batch
     against it.  The oracle is the checker and the reported baseline here, never the thing measured above."""
     from oracle import binding as oracle
@@ -365,7 +422,6 @@ def cpu_baseline_and_parity(args, g, Qh, last_rows, last_dists, last_counts, tor
     # parity: canonical-order oracle vs the device results of the last timed step (bit-exact bar)
     oc = oracle.Graph(args.dim, args.m, oracle.EUCLIDEAN, oracle.CANONICAL)
     oc.load_flat(*flat)
-    last = args.warmup + args.steps - 1
     o_rows, o_d, o_cnt, o_ctr = oc.batch_search(Qh[last].numpy(), k, ef, n_threads=cores)
     out["parity"] = {"checked_queries": int(B), "rows_equal": bool(np.array_equal(o_rows, last_rows)),
                      "dists_bit_equal": bool(np.array_equal(o_d.view(np.uint32), last_dists.view(np.uint32))),

@@ -8,9 +8,9 @@
 
 namespace b200 {
 
-template <int G, int CH, int U>
+template <int G, int CH, int U, int MINB = 1>
 static int launch_t(b200hnsw *h, const GraphView &g, TraverseParams &p, cudaStream_t s) {
-  auto kern = traverse_kernel<G, CH, U>;
+  auto kern = traverse_kernel<G, CH, U, MINB>;
   constexpr int NG = 32 / G;
   size_t smem = traverse_group_bytes(p) * TRAV_WARPS * NG;
   if (smem > h->smem_optin - 512) {
@@ -39,7 +39,7 @@ static int round_pow2(int v) {
 
 // group width: the fewest lanes that keep a row within 4 chunks per lane (overridable for tuning)
 static int pick_group(int row_chunks) {
-  static const char *env = getenv("B200HNSW_K1_G");
+  const char *env = getenv("B200HNSW_K1_G");
   if (env) {
     int v = atoi(env);
     if (v == 8 || v == 16 || v == 32) return v;
@@ -61,11 +61,28 @@ int launch_traverse(b200hnsw *h, TraverseParams &p, int vis_cap, cudaStream_t s)
   // a large visited table (retry after overflow) only fits with one traversal per warp
   if (traverse_group_bytes(p) * TRAV_WARPS * (32 / G) > h->smem_optin - 512) G = 32;
   int ch = (g.row_chunks + G - 1) / G;
-#define K1(G_, CH_, U_) return launch_t<G_, CH_, U_>(h, g, p, s)
+  if (const char *v = getenv("B200HNSW_K1_VARIANT")) {  // tuning experiments (dim 128 only)
+    int id = atoi(v);
+    if (g.row_chunks == 32) {
+      if (id == 1) return launch_t<8, 4, 4, 5>(h, g, p, s);
+      if (id == 2) return launch_t<8, 4, 8, 1>(h, g, p, s);
+      if (id == 3) return launch_t<16, 2, 8, 1>(h, g, p, s);
+      if (id == 4) return launch_t<16, 2, 4, 4>(h, g, p, s);
+      if (id == 5) return launch_t<32, 1, 16, 1>(h, g, p, s);
+      if (id == 6) return launch_t<16, 2, 8, 3>(h, g, p, s);
+      if (id == 7) return launch_t<8, 4, 2, 5>(h, g, p, s);
+      if (id == 8) return launch_t<8, 4, 1, 6>(h, g, p, s);
+      if (id == 9) return launch_t<8, 4, 2, 6>(h, g, p, s);
+      if (id == 10) return launch_t<16, 2, 2, 6>(h, g, p, s);
+      if (id == 11) return launch_t<16, 2, 4, 6>(h, g, p, s);
+      if (id == 12) return launch_t<8, 4, 1, 8>(h, g, p, s);
+    }
+  }
+#define K1(G_, CH_, U_) return launch_t<G_, CH_, U_, ((CH_) >= 12 ? 2 : ((CH_) * (U_) <= 8 ? 5 : 4))>(h, g, p, s)
   if (G == 8) {
     if (ch <= 1) K1(8, 1, 8);
     if (ch <= 2) K1(8, 2, 4);
-    if (ch <= 4) K1(8, 4, 4);
+    if (ch <= 4) K1(8, 4, 2);
     G = 16;
     ch = (g.row_chunks + 15) / 16;
   }

@@ -49,8 +49,8 @@ constexpr int TRAV_WARPS = 4;
 
 enum { ST_NEED = 0, ST_INIT = 1, ST_EXPAND = 2, ST_IDLE = 3 };
 
-template <int G, int CH, int U>
-__global__ void __launch_bounds__(TRAV_WARPS * 32) traverse_kernel(GraphView g, TraverseParams p) {
+template <int G, int CH, int U, int MINB>
+__global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphView g, TraverseParams p) {
   constexpr int NG = 32 / G;
   constexpr unsigned GBITS = G == 32 ? 0xffffffffu : ((1u << G) - 1u);
   extern __shared__ __align__(16) unsigned char smem[];
