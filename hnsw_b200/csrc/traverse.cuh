@@ -83,6 +83,9 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
   Q.qq = 0.f;
   unsigned long long c_evals = 0, c_exp = 0, c_nbr = 0, c_over = 0;  // meaningful in leader lanes
 
+  float best_d = 0.f;  // leader: the one-element result queue of a k = 1 layer lives in registers
+  int best_id = -1, r1 = 0;
+
   for (;;) {
     // ---- fetch the next traversal for groups that finished one --------------------------------------------------
     const bool need = st == ST_NEED;
@@ -106,12 +109,13 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
     const bool init = st == ST_INIT, expand = st == ST_EXPAND;
     bool improved = false;  // leader
     int nfresh = 0;
-    // ---- INIT: reset the queues and the visited set, the entry point is the only row to evaluate -----------------
+    // ---- INIT (top layer, or a layer reached without an elevator): the entry point is the only row to evaluate ----
     if (init) {
       cur = elevator >= 0 ? elevator : s_entries[layer];  // graph.go:572-575 / 492-498
       kcur = layer > 0 ? p.k_upper : p.k;
       C.len = 0;
       R.len = 0;
+      r1 = 0;
       uint4 e4 = make_uint4(~0u, ~0u, ~0u, ~0u);
       uint4 *t4 = reinterpret_cast<uint4 *>(vtab);
       for (uint32_t i = gl; i < (vmask + 1) / 4; i += G) t4[i] = e4;
@@ -176,19 +180,36 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
         for (int u = 0; u < U; u++) {
           if (ids[u] < 0) continue;
           c_evals++;
-          if (init) {  // graph.go:109-123
-            C.push(d[u], ids[u]);
-            R.push(d[u], ids[u]);
+          if (init) {
+            // graph.go:109-127: candidates.Push(entry); result.Push(entry); visited[entry]; the first Pop takes the
+            // entry back out, so the candidate queue stays empty and the entry is the first node expanded
+            if (kcur == 1) {
+              best_d = d[u];
+              best_id = ids[u];
+              r1 = 1;
+            } else {
+              R.push(d[u], ids[u]);
+            }
             uint32_t h = ((uint32_t)ids[u] * 2654435761u) >> 7;
             vtab[h & vmask] = (uint32_t)ids[u];
             continue;
           }
-          improved = improved || (R.len > 0 && d[u] < R.min_dist());  // graph.go:147
-          if (R.len < kcur) {
-            R.push(d[u], ids[u]);
-          } else if (d[u] < R.max_dist()) {  // result.Max() is the last array slot
-            R.pop_last();
-            R.push(d[u], ids[u]);
+          if (kcur == 1) {
+            // a full one-element queue: `improved` (graph.go:147) and the replacement test (graph.go:150,
+            // result.Max() is that element) are the same comparison
+            if (d[u] < best_d) {
+              improved = true;
+              best_d = d[u];
+              best_id = ids[u];
+            }
+          } else {
+            improved = improved || (R.len > 0 && d[u] < R.min_dist());  // graph.go:147
+            if (R.len < kcur) {
+              R.push(d[u], ids[u]);
+            } else if (d[u] < R.max_dist()) {  // result.Max() is the last array slot
+              R.pop_last();
+              R.push(d[u], ids[u]);
+            }
           }
           C.push(d[u], ids[u]);
           if (C.len > p.ef) C.pop_last();  // graph.go:157-159
@@ -199,15 +220,20 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
     // ---- leader decides: next node, end of layer ---------------------------------------------------------------------
     int next = -1;
     if (leader && (init || expand) && !overflow) {
+      const int rl = kcur == 1 ? r1 : R.len;
       if (init) {
-        if (nfresh > 0) next = (int)C.pop().y;                     // graph.go:125-127, first iteration
-      } else if (!(!improved && R.len >= kcur) && C.len > 0) {      // graph.go:164-166, 125
+        if (nfresh > 0) next = cur;                                 // graph.go:125-127, first iteration
+      } else if (!(!improved && rl >= kcur) && C.len > 0) {        // graph.go:164-166, 125
         next = (int)C.pop().y;
       }
     }
     next = __shfl_sync(FULL, next, leader_lane);
-    const int rlen = __shfl_sync(FULL, R.len, leader_lane);
+    const int rlen = __shfl_sync(FULL, kcur == 1 ? r1 : R.len, leader_lane);
+    const int r0_id = __shfl_sync(FULL, best_id, leader_lane);    // k = 1 layers: the result itself
+    const float r0_d = __shfl_sync(FULL, best_d, leader_lane);
     __syncwarp();  // the leader's heap writes are visible to its group
+    bool chain = false;
+    float elev_d = 0.f;
     if (init || expand) {
       if (overflow) {
         if (leader) {
@@ -222,33 +248,67 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
         st = ST_EXPAND;
       } else {
         // ---- end of this layer: results are the raw heap array (graph.go:169) ----------------------------------
+        const bool one = kcur == 1;
         if (p.out_rows) {
           if (layer == 0) {  // graph.go:588-593
             for (int i = gl; i < p.k; i += G) {
               const bool ok = i < rlen;
-              p.out_rows[q * p.k + i] = ok ? R.id(i) : -1;
-              p.out_dists[q * p.k + i] = ok ? R.dist(i) : __int_as_float(0x7fc00000);
+              p.out_rows[q * p.k + i] = ok ? (one ? r0_id : R.id(i)) : -1;
+              p.out_dists[q * p.k + i] = ok ? (one ? r0_d : R.dist(i)) : __int_as_float(0x7fc00000);
             }
             if (leader) p.out_counts[q] = rlen;
           }
         } else if (layer <= lvl) {  // graph.go:510: this layer takes the new node
           const long long slot = p.slot_off[q] + layer;
           for (int i = gl; i < rlen; i += G) {
-            p.slot_rows[slot * p.sink_stride + i] = R.id(i);
-            p.slot_dists[slot * p.sink_stride + i] = R.dist(i);
+            p.slot_rows[slot * p.sink_stride + i] = one ? r0_id : R.id(i);
+            p.slot_dists[slot * p.sink_stride + i] = one ? r0_d : R.dist(i);
           }
           if (leader) p.slot_cnt[slot] = rlen;
         }
-        if (rlen > 0) elevator = R.id(0);  // graph.go:584 / 508
+        if (rlen > 0) {  // graph.go:584 / 508: the nearest result is the next layer's entry point
+          elevator = one ? r0_id : R.id(0);
+          elev_d = one ? r0_d : R.dist(0);
+        }
         if (layer == 0) {
           st = ST_NEED;
         } else {
           layer--;
-          st = ST_INIT;
+          chain = rlen > 0;
+          st = chain ? ST_EXPAND : ST_INIT;
         }
       }
     }
     __syncwarp();  // every lane has read R before the leader reuses it
+    // ---- the next layer starts at the elevator.  Its distance to the query was just computed in the layer above
+    //      (same row, same query, same arithmetic), so graph.go:107-127 needs no new evaluation: the queues are
+    //      {entry} and {} after the first Pop, and the entry is the node expanded next. --------------------------------
+    if (chain) {
+      cur = elevator;
+      kcur = layer > 0 ? p.k_upper : p.k;
+      uint4 e4 = make_uint4(~0u, ~0u, ~0u, ~0u);
+      uint4 *t4 = reinterpret_cast<uint4 *>(vtab);
+      for (uint32_t i = gl; i < (vmask + 1) / 4; i += G) t4[i] = e4;
+      vcount = 1;
+      if (leader) {
+        c_evals++;  // the reference evaluates the entry again; counted so E equals the oracle's
+        C.len = 0;
+        if (kcur == 1) {
+          best_d = elev_d;
+          best_id = elevator;
+          r1 = 1;
+        } else {
+          R.len = 0;
+          R.push(elev_d, elevator);
+        }
+      }
+    }
+    __syncwarp();
+    if (chain && leader) {
+      uint32_t h = ((uint32_t)elevator * 2654435761u) >> 7;
+      vtab[h & vmask] = (uint32_t)elevator;
+    }
+    __syncwarp();
   }
   if (p.counters && leader) {
     if (c_evals) atomicAdd(&p.counters[0], c_evals);

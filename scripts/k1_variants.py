@@ -9,7 +9,9 @@ Bs = [int(x) for x in sys.argv[3].split(',')]
 X = synth_rows(N, d, 42); lv = draw_levels(N, 0.25, 44)
 g = hnsw_b200.Graph(M=M, Ml=0.25, EfSearch=ef, Distance=hnsw_b200.EuclideanDistance, capacity=N)
 g.add_arrays(np.arange(N, dtype=np.int64), X, lv, wave_max=4096)
-print("built", g.Topography(), flush=True)
+print("built", g.Topography(), "build launches", g.last_stats["launches"], flush=True)
+import torch
+torch.cuda.cudart().cudaProfilerStart()
 ref = {}
 for v in variants:
     os.environ.pop("B200HNSW_K1_VARIANT", None); os.environ.pop("B200HNSW_K1_G", None)
