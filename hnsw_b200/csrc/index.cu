@@ -1,6 +1,7 @@
 // index.cu -- C ABI (include/b200hnsw.h): lifetime, device-resident layout, load / read-back, search entry points.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -32,6 +33,14 @@ int CallCtx::reserve_device(size_t bytes) {
   size_t want = std::max(bytes, (size_t)1 << 20);
   B200_CUDA(cudaMalloc(&d_scratch, want));
   scratch_bytes = want;
+  return 0;
+}
+int CallCtx::ensure_sub(int n) {
+  while (n_sub < n && n_sub < MAX_SUB) {
+    B200_CUDA(cudaStreamCreateWithFlags(&sub[n_sub], cudaStreamNonBlocking));
+    B200_CUDA(cudaEventCreateWithFlags(&sub_ev[n_sub], cudaEventDisableTiming));
+    n_sub++;
+  }
   return 0;
 }
 int CallCtx::reserve_pinned(size_t bytes) {
@@ -195,6 +204,10 @@ void b200hnsw_destroy(b200hnsw_t *h) {
   cudaSetDevice(h->cfg.device);
   cudaDeviceSynchronize();
   for (CallCtx *c : h->pool) {
+    for (int i = 0; i < c->n_sub; i++) {
+      cudaEventDestroy(c->sub_ev[i]);
+      cudaStreamDestroy(c->sub[i]);
+    }
     if (c->d_scratch) cudaFree(c->d_scratch);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     cudaEventDestroy(c->ev0);
@@ -487,18 +500,52 @@ int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_
   int *d_err = (int *)(d_ctr + 4);
   cudaStream_t s = c->stream;
   cudaError_t e;
-  if ((e = cudaMemcpyAsync(d_q, queries, qb, cudaMemcpyHostToDevice, s)) != cudaSuccess)
-    return fail(cuda_fail(e, "search staging"));
+  // The batch is cut in chunks that run on their own streams: the H2D copy of chunk i+1 and the D2H copy of chunk
+  // i-1 overlap the traversal kernel of chunk i, and the kernels of different chunks share the SMs.
+  int nchunk = B >= 4096 ? 4 : (B >= 1024 ? 2 : 1);
+  if (const char *v = getenv("B200HNSW_E2E_CHUNKS")) {
+    int t = atoi(v);
+    if (t >= 1 && t <= CallCtx::MAX_SUB) nchunk = t;
+  }
+  if ((rc = c->ensure_sub(nchunk))) return fail(rc);
   unsigned long long ctr[5] = {0, 0, 0, 0, 0};
   int launches = 0;
+  bool staged = false;
+  if (nchunk == 1) {  // one chunk: copy first, so that kernel_ms (ev0..ev1) is the traversal kernel alone
+    if ((e = cudaMemcpyAsync(d_q, queries, qb, cudaMemcpyHostToDevice, s)) != cudaSuccess)
+      return fail(cuda_fail(e, "search staging"));
+    staged = true;
+  }
   // A layer search that visits more nodes than the shared-memory visited table holds fails loudly in the kernel;
   // the whole batch is then redone with a table 4x the size (sticky for later calls), so results are always exact.
   for (int vis = h->vis_hint;; vis *= 4) {
     if ((e = cudaMemsetAsync(d_ctr, 0, 64, s)) != cudaSuccess || (e = cudaEventRecord(c->ev0, s)) != cudaSuccess)
       return fail(cuda_fail(e, "search staging"));
-    rc = launch_search(h, d_q, B, k, ef, metric, mode, entries, d_rows, d_dists, d_cnt, d_ctr, d_err, vis, s);
-    if (rc) return fail(rc);
-    launches++;
+    for (int ci = 0; ci < nchunk; ci++) {
+      const int64_t q0 = B * ci / nchunk, q1 = B * (ci + 1) / nchunk, nq = q1 - q0;
+      if (nq <= 0) continue;
+      cudaStream_t sc = nchunk == 1 ? s : c->sub[ci];
+      if (nchunk > 1 && (e = cudaStreamWaitEvent(sc, c->ev0, 0)) != cudaSuccess)
+        return fail(cuda_fail(e, "search chunk wait"));
+      if (!staged && (e = cudaMemcpyAsync(d_q + q0 * dim, queries + q0 * dim, sizeof(float) * (size_t)nq * dim,
+                                          cudaMemcpyHostToDevice, sc)) != cudaSuccess)
+        return fail(cuda_fail(e, "search staging"));
+      rc = launch_search(h, d_q + q0 * dim, nq, k, ef, metric, mode, entries, d_rows + q0 * k, d_dists + q0 * k,
+                         d_cnt + q0, d_ctr, d_err, vis, sc);
+      if (rc) return fail(rc);
+      launches++;
+      if ((e = cudaMemcpyAsync(out_rows + q0 * k, d_rows + q0 * k, sizeof(int32_t) * (size_t)nq * k,
+                               cudaMemcpyDeviceToHost, sc)) != cudaSuccess ||
+          (e = cudaMemcpyAsync(out_dists + q0 * k, d_dists + q0 * k, sizeof(float) * (size_t)nq * k,
+                               cudaMemcpyDeviceToHost, sc)) != cudaSuccess ||
+          (e = cudaMemcpyAsync(out_counts + q0, d_cnt + q0, sizeof(int32_t) * (size_t)nq, cudaMemcpyDeviceToHost,
+                               sc)) != cudaSuccess)
+        return fail(cuda_fail(e, "search copy-back"));
+      if (nchunk > 1 && ((e = cudaEventRecord(c->sub_ev[ci], sc)) != cudaSuccess ||
+                         (e = cudaStreamWaitEvent(s, c->sub_ev[ci], 0)) != cudaSuccess))
+        return fail(cuda_fail(e, "search chunk join"));
+    }
+    staged = true;
     if ((e = cudaEventRecord(c->ev1, s)) != cudaSuccess ||
         (e = cudaMemcpyAsync(ctr, d_ctr, 40, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
         (e = cudaStreamSynchronize(s)) != cudaSuccess)
@@ -510,11 +557,6 @@ int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_
     }
     h->vis_hint = vis * 4;
   }
-  if ((e = cudaMemcpyAsync(out_rows, d_rows, rb, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
-      (e = cudaMemcpyAsync(out_dists, d_dists, db, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
-      (e = cudaMemcpyAsync(out_counts, d_cnt, cb, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
-      (e = cudaStreamSynchronize(s)) != cudaSuccess)
-    return fail(cuda_fail(e, "search copy-back"));
   if (stats) {
     stats->dist_evals = (int64_t)ctr[0];
     stats->expansions = (int64_t)ctr[1];

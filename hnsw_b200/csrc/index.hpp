@@ -32,6 +32,11 @@ struct CallCtx {
   size_t scratch_bytes = 0;
   void *h_pinned = nullptr;    // pinned host staging
   size_t pinned_bytes = 0;
+  static constexpr int MAX_SUB = 8;
+  cudaStream_t sub[MAX_SUB] = {};   // chunk streams of a host-pointer search (copy / kernel overlap)
+  cudaEvent_t sub_ev[MAX_SUB] = {};
+  int n_sub = 0;
+  int ensure_sub(int n);
   int reserve_device(size_t bytes);
   int reserve_pinned(size_t bytes);
 };

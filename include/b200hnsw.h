@@ -73,7 +73,8 @@ typedef struct {
   int64_t evict_evals;     /* add: distances in addNeighbor overflow scans (graph.go:60-71)   */
   int64_t replenish_evals; /* add: cosine distances in replenish (graph.go:204)               */
   int64_t evictions;       /* add: neighbours evicted (graph.go:73-80)                         */
-  float kernel_ms;     /* device time of the traversal kernel (host-pointer calls)     */
+  float kernel_ms;     /* device time of the call's kernels; for a search cut in chunks (B >= 1024) it spans
+                          the overlapped copy-in / traversal / copy-out pipeline                             */
   int32_t launches;    /* kernels launched by the call                                 */
 } b200hnsw_stats;
 

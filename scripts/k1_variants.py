@@ -1,6 +1,8 @@
 """Exploration: K1 variants (B200HNSW_K1_VARIANT / B200HNSW_K1_G) on a wave-built graph."""
 import os, sys, time, numpy as np
 sys.path.insert(0, '.')
+import os
+os.environ.setdefault('B200HNSW_E2E_CHUNKS', '1')  # kernel_ms = the traversal kernel alone
 import hnsw_b200
 from bench import synth_rows, draw_levels
 N = int(sys.argv[1]); d = 128; M = 16; ef = 64

@@ -1,6 +1,8 @@
 """Exploration: wave-batched Add rate on the device and K1 timing on the resulting graph."""
 import sys, time, numpy as np
 sys.path.insert(0, '.')
+import os
+os.environ.setdefault('B200HNSW_E2E_CHUNKS', '1')  # kernel_ms = the traversal kernel alone
 import hnsw_b200
 from bench import synth_rows, draw_levels
 N = int(sys.argv[1]); d = int(sys.argv[2]); M = int(sys.argv[3]); ef = int(sys.argv[4]); wm = int(sys.argv[5])
