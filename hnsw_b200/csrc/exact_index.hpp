@@ -1,0 +1,37 @@
+// exact_index.hpp -- host object behind b200exact_t (hybrid.ExactIndex, hnsw-extensions/hybrid/exact.go:13-25).
+#pragma once
+#include <cuda_bf16.h>
+
+#include "gdist.cuh"
+#include "index.hpp"
+
+struct b200exact {
+  int dim = 0, metric = 0, device = 0;
+  int row_floats = 0;   // dim padded to a multiple of 32 floats
+  int kpad = 0;         // dim padded to a multiple of 64 (bf16 K extent of the tensor path)
+  int64_t n = 0, cap = 0, live = 0;
+  float *d_vec = nullptr;            // [cap][row_floats] fp32, zero padded (what results are computed from)
+  uint8_t *d_alive = nullptr;        // [cap] 0 = deleted (exact.go:114-145)
+  __nv_bfloat16 *d_vech = nullptr;   // [cap][kpad] bf16 copy for the tensor path
+  float *d_aux = nullptr;            // [cap] L2: |x|^2, cosine: 1/|x|; +inf / 0 for deleted rows
+  float max_norm = 0.f;              // max |x| over rows ever added (error bound of the tensor path)
+  std::vector<uint8_t> h_alive;
+  int sm_count = 148;
+  size_t smem_optin = 0;
+  cudaStream_t stream = nullptr;
+  void *d_scratch = nullptr;
+  size_t scratch_bytes = 0;
+  void *tmap_x = nullptr;            // CUtensorMap of d_vech (exact_gemm.cu), rebuilt when storage moves
+  int64_t tmap_rows = -1;
+  std::mutex mu;                     // searches share the scratch buffer: one at a time per index
+  int reserve(size_t bytes);
+  int ensure_capacity(int64_t rows);
+};
+
+namespace b200 {
+// exact_gemm.cu: fills cand[q][0..cand_cap) / cand_cnt[q] with rows that provably contain the k nearest of every
+// query; returns B200HNSW_ERR_UNSUPPORTED when the tensor path cannot be used (caller falls back to the scan).
+int exact_candidates_tensor(b200exact *x, const float *d_queries, int64_t B, int k, int32_t *d_cand,
+                            int32_t *d_cand_cnt, int cand_cap, cudaStream_t s);
+int exact_after_add(b200exact *x, int64_t first, int64_t count, cudaStream_t s);  // bf16 copy + norms of new rows
+}  // namespace b200
