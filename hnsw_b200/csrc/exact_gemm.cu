@@ -1,9 +1,462 @@
-// exact_gemm.cu -- K3 tensor path (placeholder until the tcgen05 kernel lands): reports "unsupported" so the
-// caller uses the exact fp32 scan.
+// exact_gemm.cu -- K3 tensor path: candidate generation for hybrid.ExactIndex.Search (hnsw-extensions/hybrid/
+// exact.go:76-108) as a bf16 tcgen05 GEMM with a fused, provably safe threshold filter.
+//
+//   D[q][row] = sum_k Qh[q][k] * Xh[row][k]          (bf16 operands, fp32 accumulation in TMEM)
+//   score     = |x|^2 - 2 D            (Euclidean: distance^2 - |q|^2, monotone in the distance)
+//             = 1 - D / (|x| |q|)      (cosine distance)
+// Every score is within eps_q of the same transform of the canonical fp32 distance the reference would sort by
+// (bf16 rounding of both operands: |D - x.q| <= gamma |x||q|, gamma ~ 2^-7; plus fp32 rounding terms).  Per query a
+// running upper bound tau_q on the k-th smallest score is kept (k slots of tile-block minima over disjoint row sets;
+// shared between CTAs through an atomicMin), and every row with score <= tau_q + 2 eps_q is appended to the query's
+// candidate list.  That list provably contains the k nearest rows; exact_index.cu re-evaluates it in canonical fp32.
+//
+// One CTA = 128 queries (UMMA M) x a range of 256-row tiles (UMMA N = 256), K in 64-element (128 B, SWIZZLE_128B)
+// blocks.  Warp 0: TMA producer; warp 1: TMEM allocator + single-thread tcgen05.mma issuer; warps 2-5: epilogue
+// (tcgen05.ld 32x32b, one query row per thread).  Accumulators are double-buffered in TMEM (2 x 256 columns).
+// Bound: tensor pipe (2*B*N*dim flop) for B >~ 300 queries, HBM (2*N*dim bytes of bf16 rows) below.
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
 #include "exact_index.hpp"
+
 namespace b200 {
-int exact_candidates_tensor(b200exact *, const float *, int64_t, int, int32_t *, int32_t *, int, cudaStream_t) {
-  return B200HNSW_ERR_UNSUPPORTED;
+
+constexpr int GM_M = 128;      // queries per CTA
+constexpr int GM_N = 256;      // rows per tile
+constexpr int GM_K = 64;       // bf16 elements per K block (128 B)
+constexpr int GM_STAGES = 3;
+constexpr int GM_A_BYTES = GM_M * GM_K * 2;   // 16 KB
+constexpr int GM_B_BYTES = GM_N * GM_K * 2;   // 32 KB
+constexpr int GM_THREADS = 192;
+constexpr int GM_MAX_K = 64;   // result size the slot table supports
+
+// ---- PTX wrappers ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
 }
-int exact_after_add(b200exact *, int64_t, int64_t, cudaStream_t) { return 0; }
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+  } while (!ok);
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const void *tmap, int c0, int c1, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          dst),
+      "l"(tmap), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(
+          tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// K-major, SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor): start address >> 4 in bits
+// [0,14), leading byte offset (unused for swizzled K-major) = 1 in [16,30), stride byte offset = 1024 B (eight 128 B
+// rows) >> 4 in [32,46), version 1 in [46,48), layout type 2 (SWIZZLE_128B) in [61,64).
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
+  return (uint64_t)((saddr & 0x3ffffu) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) |
+         ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+}
+// kind::f16 instruction descriptor: D = F32 (bits 4-5 = 1), A = B = BF16 (bits 7-9, 10-12 = 1), both K-major,
+// N >> 3 in bits 17-22, M >> 4 in bits 24-28
+constexpr uint32_t GM_IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(GM_N >> 3) << 17) |
+                              ((uint32_t)(GM_M >> 4) << 24);
+
+__device__ __forceinline__ uint32_t ord_bits(float d) {
+  uint32_t u = __float_as_uint(d);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float ord_float(uint32_t k) {
+  return __uint_as_float((k & 0x80000000u) ? (k ^ 0x80000000u) : ~k);
+}
+
+
+struct GemmParams {
+  const float *aux;        // [cap] |x|^2 (Euclidean) or 1/|x| (cosine); +inf / NaN for dead rows
+  int metric, kblocks, tiles_total, tiles_per_split, warm_tiles, k;
+  long long B;
+  const float *q_inv;      // [Bpad] 1/|q| (cosine)
+  const float *q_margin;   // [Bpad] 2 * eps_q
+  uint32_t *tau_g;         // [Bpad] order-preserving bits of the shared bound on the k-th smallest score
+  int32_t *cand;           // [B][cand_cap]
+  int32_t *cand_cnt;       // [B]
+  int cand_cap;
+};
+
+struct GemmSmem {
+  static constexpr size_t stages = (size_t)GM_STAGES * (GM_A_BYTES + GM_B_BYTES);
+  static constexpr size_t slots = stages;                               // float[128][k]
+  static __host__ __device__ size_t aux(int k) { return slots + (size_t)GM_M * k * 4; }   // float[2][256]
+  static __host__ __device__ size_t bars(int k) { return aux(k) + 2 * GM_N * 4; }         // 2*S + 4 barriers, tmem ptr
+  static __host__ __device__ size_t total(int k) { return bars(k) + 16 * 8 + 1024; }       // + alignment slack
+};
+
+__global__ void __launch_bounds__(GM_THREADS, 1)
+exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x,
+                  GemmParams p) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char *smem = reinterpret_cast<unsigned char *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float *slots = reinterpret_cast<float *>(smem + GemmSmem::slots);
+  float *aux_s = reinterpret_cast<float *>(smem + GemmSmem::aux(p.k));
+  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + GemmSmem::bars(p.k));
+  uint32_t *tmem_ptr_s = reinterpret_cast<uint32_t *>(bars + 2 * GM_STAGES + 4);
+  const uint32_t bar_full = smem_u32(bars), bar_empty = smem_u32(bars + GM_STAGES);
+  const uint32_t bar_tfull = smem_u32(bars + 2 * GM_STAGES), bar_tempty = smem_u32(bars + 2 * GM_STAGES + 2);
+  const uint32_t s_base = smem_u32(smem);
+
+  const int mt = blockIdx.y, sp = blockIdx.x;
+  const int t_begin = sp * p.tiles_per_split;
+  const int t_end = min(p.tiles_total, t_begin + p.tiles_per_split);
+  const int n_tiles = t_end - t_begin;
+  const int warm = min(p.warm_tiles, n_tiles);
+  const int seq = n_tiles > 0 ? warm + n_tiles : 0;  // warm-up tiles are visited twice: first only to bound tau
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < GM_STAGES; i++) {
+      mbar_init(bar_full + 8 * i, 1);
+      mbar_init(bar_empty + 8 * i, 1);
+    }
+    for (int i = 0; i < 2; i++) {
+      mbar_init(bar_tfull + 8 * i, 1);
+      mbar_init(bar_tempty + 8 * i, 4);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {  // TMEM: 2 accumulator stages x 256 fp32 columns
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr_s)),
+                 "r"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_s;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      int stage = 0, phase = 0;
+      for (int idx = 0; idx < seq; idx++) {
+        const int tile = t_begin + (idx < warm ? idx : idx - warm);
+        for (int kb = 0; kb < p.kblocks; kb++) {
+          mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+          const uint32_t sa = s_base + stage * (GM_A_BYTES + GM_B_BYTES), sb = sa + GM_A_BYTES;
+          mbar_expect_tx(bar_full + 8 * stage, GM_A_BYTES + GM_B_BYTES);
+          tma_load_2d(sa, &tmap_q, kb * GM_K, mt * GM_M, bar_full + 8 * stage);
+          tma_load_2d(sb, &tmap_x, kb * GM_K, tile * GM_N, bar_full + 8 * stage);
+          if (++stage == GM_STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (one thread) =====
+    if (lane == 0) {
+      int stage = 0, phase = 0;
+      for (int idx = 0; idx < seq; idx++) {
+        const int as = idx & 1;
+        mbar_wait(bar_tempty + 8 * as, ((idx >> 1) & 1) ^ 1);  // epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + as * GM_N;
+        for (int kb = 0; kb < p.kblocks; kb++) {
+          mbar_wait(bar_full + 8 * stage, phase);
+          tc_fence_after();
+          const uint32_t sa = s_base + stage * (GM_A_BYTES + GM_B_BYTES), sb = sa + GM_A_BYTES;
+          const uint64_t adesc = umma_desc_sw128(sa), bdesc = umma_desc_sw128(sb);
+#pragma unroll
+          for (int k4 = 0; k4 < GM_K / 16; k4++)  // UMMA K = 16 bf16 = 32 B: advance the start address field by 2
+            umma_bf16(tmem_d, adesc + 2 * k4, bdesc + 2 * k4, GM_IDESC, (kb | k4) != 0);
+          umma_commit(bar_empty + 8 * stage);  // frees the smem stage when these MMAs retire
+          if (++stage == GM_STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(bar_tfull + 8 * as);  // accumulator ready
+      }
+    }
+  } else {
+    // ===== epilogue: one query row per thread =====
+    const int ew = warp & 3;                  // TMEM lane quarter this warp may access
+    const int r = ew * 32 + lane;             // row of the tile = TMEM lane
+    const long long q = (long long)mt * GM_M + r;
+    const bool live_q = q < p.B;
+    const int et = (warp - 2) * 32 + lane;    // 0..127 among the epilogue threads
+    float *my_slots = slots + (size_t)r * p.k;
+    for (int j = 0; j < p.k; j++) my_slots[j] = __int_as_float(0x7f800000);
+    const float margin = live_q ? p.q_margin[q] : 0.f;
+    const float qinv = (live_q && p.metric == 1) ? p.q_inv[q] : 0.f;
+    float thr = __int_as_float(0x7f800000);
+    int sub = 0;
+    for (int idx = 0; idx < seq; idx++) {
+      const int as = idx & 1;
+      const int tile = t_begin + (idx < warm ? idx : idx - warm);
+      const bool emit = live_q && idx >= warm;
+      // stage the tile's per-row terms (the previous use of this buffer ended two tiles ago)
+      float *ax = aux_s + as * GM_N;
+      ax[et] = p.aux[(long long)tile * GM_N + et];
+      ax[et + 128] = p.aux[(long long)tile * GM_N + et + 128];
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      mbar_wait(bar_tfull + 8 * as, (idx >> 1) & 1);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + as * GM_N;
+      for (int c = 0; c < GM_N / 32; c++) {
+        uint32_t v[32];
+        tmem_ld32(taddr + c * 32, v);
+        float bmin = __int_as_float(0x7f800000);
+#pragma unroll
+        for (int j = 0; j < 32; j++) {
+          const float D = __uint_as_float(v[j]);
+          const float a = ax[c * 32 + j];
+          const float s = p.metric == 0 ? fmaf(-2.f, D, a) : fmaf(-D * a, qinv, 1.f);
+          bmin = fminf(bmin, s);
+          if (emit && s <= thr && s < __int_as_float(0x7f800000)) {  // dead rows score +inf / NaN
+            const int at = atomicAdd(&p.cand_cnt[q], 1);
+            if (at < p.cand_cap) p.cand[q * p.cand_cap + at] = tile * GM_N + c * 32 + j;
+          }
+        }
+        // slot `sub mod k` holds the minimum over a set of rows disjoint from every other slot's set
+        const int sl = sub % p.k;
+        my_slots[sl] = fminf(my_slots[sl], bmin);
+        sub++;
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
+      if (sub >= p.k && live_q) {
+        // k distinct rows score <= max(slots): an upper bound on the k-th smallest score of the whole index
+        float tau = my_slots[0];
+        for (int j = 1; j < p.k; j++) tau = fmaxf(tau, my_slots[j]);
+        const uint32_t mine = ord_bits(tau);
+        const uint32_t old = atomicMin(&p.tau_g[q], mine);
+        tau = ord_float(min(old, mine));
+        thr = tau + margin;
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
+  }
+}
+
+
+// ---- preparation kernels ---------------------------------------------------------------------------------------------
+// rows [first, first+count): bf16 copy (zero padded to kpad), |x|^2 / 1/|x|, running max of |x|^2
+__global__ void exact_xprep_kernel(const float *vec, int row_floats, int dim, int kpad, long long first,
+                                   long long count, int metric, __nv_bfloat16 *vech, float *aux, uint32_t *maxn2) {
+  const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (w >= count) return;
+  const long long row = first + w;
+  const float *src = vec + row * row_floats;
+  __nv_bfloat16 *dst = vech + row * kpad;
+  float acc = 0.f;
+  for (int i = lane; i < kpad; i += 32) {
+    float v = i < dim ? src[i] : 0.f;
+    acc = fmaf(v, v, acc);
+    dst[i] = __float2bfloat16_rn(v);
+  }
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) acc += __shfl_xor_sync(FULL, acc, off);
+  if (lane == 0) {
+    aux[row] = metric == 0 ? acc : 1.0f / sqrtf(acc);  // a zero vector gives inf: its score is NaN, never a candidate
+    atomicMax(maxn2, __float_as_uint(acc));             // non-negative floats order like their bit patterns
+  }
+}
+__global__ void exact_fill_kernel(float *p, long long n, float v) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+// queries: bf16 copy into Qh[Bpad][kpad], 1/|q|, filter margin 2*eps_q, tau = +inf, candidate count = 0
+__global__ void exact_qprep_kernel(const float *q, long long B, long long Bpad, int dim, int kpad, int metric,
+                                   const uint32_t *maxn2, __nv_bfloat16 *qh, float *q_inv, float *q_margin,
+                                   uint32_t *tau_g, int32_t *cand_cnt) {
+  const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (w >= Bpad) return;
+  const bool live = w < B;
+  float acc = 0.f;
+  for (int i = lane; i < kpad; i += 32) {
+    float v = (live && i < dim) ? q[w * dim + i] : 0.f;
+    acc = fmaf(v, v, acc);
+    qh[w * kpad + i] = __float2bfloat16_rn(v);
+  }
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) acc += __shfl_xor_sync(FULL, acc, off);
+  if (lane == 0) {
+    const float qn = sqrtf(acc), xmax = sqrtf(__uint_as_float(*maxn2));
+    // |D - x.q| <= gamma |x||q|: two bf16 roundings (2^-8 each, RN) and the fp32 accumulation of kpad products
+    const float gamma = 0.0078125f * 1.01f + (float)(kpad + 64) * 2.3841858e-7f;
+    const float fp32 = (float)(dim / 8 + 64) * 5.9604645e-8f;  // canonical fp32 distance vs exact arithmetic
+    float eps;
+    if (metric == 0) eps = 2.f * gamma * xmax * qn + fp32 * (xmax + qn) * (xmax + qn);
+    else eps = gamma * 1.001f + fp32;
+    q_inv[w] = 1.0f / qn;
+    q_margin[w] = 2.f * eps * 1.001f;
+    tau_g[w] = 0xff800000u;  // ord_bits(+inf)
+    if (live) cand_cnt[w] = 0;
+  }
+}
+
+// ---- host side -------------------------------------------------------------------------------------------------------
+typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                    const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static encode_tiled_fn get_encoder() {
+  static encode_tiled_fn fn = nullptr;
+  if (!fn) {
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = (encode_tiled_fn)p;
+  }
+  return fn;
+}
+// bf16 matrix [rows][kpad], box = 64 elements (128 B) x box_rows, 128 B swizzle
+static int make_tmap(CUtensorMap *m, void *base, uint64_t rows, uint64_t kpad, uint32_t box_rows) {
+  encode_tiled_fn enc = get_encoder();
+  if (!enc) {
+    set_error("exact: cuTensorMapEncodeTiled is not available");
+    return B200HNSW_ERR_UNSUPPORTED;
+  }
+  cuuint64_t gdim[2] = {kpad, rows};
+  cuuint64_t gstride[1] = {kpad * 2};
+  cuuint32_t box[2] = {GM_K, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("exact: cuTensorMapEncodeTiled failed (%d)", (int)r);
+    return B200HNSW_ERR_CUDA;
+  }
+  return 0;
+}
+
+int exact_after_add(b200exact *x, int64_t first, int64_t count, cudaStream_t s) {
+  if (!x->d_maxn2) {
+    B200_CUDA(cudaMalloc(&x->d_maxn2, 64));
+    B200_CUDA(cudaMemsetAsync(x->d_maxn2, 0, 64, s));
+  }
+  if (x->aux_dead_cap != x->cap) {  // storage grew: rows that do not exist yet must never become candidates
+    const float dead = x->metric == 0 ? __builtin_inff() : __builtin_nanf("");
+    long long nfill = x->cap - first;
+    exact_fill_kernel<<<(unsigned)((nfill + 255) / 256), 256, 0, s>>>(x->d_aux + first, nfill, dead);
+    x->aux_dead_cap = x->cap;
+  }
+  long long threads = count * 32;
+  exact_xprep_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(x->d_vec, x->row_floats, x->dim, x->kpad, first,
+                                                                        count, x->metric, x->d_vech, x->d_aux,
+                                                                        x->d_maxn2);
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int exact_candidates_tensor(b200exact *x, const float *d_queries, int64_t B, int k, int32_t *d_cand,
+                            int32_t *d_cand_cnt, int cand_cap, cudaStream_t s) {
+  if (k > GM_MAX_K) return B200HNSW_ERR_UNSUPPORTED;  // the slot table is sized for k <= 64: the scan handles the rest
+  const size_t smem = GemmSmem::total(k);
+  if (smem > x->smem_optin) return B200HNSW_ERR_UNSUPPORTED;
+  const int64_t Bpad = (B + GM_M - 1) / GM_M * GM_M;
+  auto al = [](size_t v) { return (v + 255) & ~(size_t)255; };
+  const size_t need = al(2 * (size_t)Bpad * x->kpad) + 3 * al(4 * (size_t)Bpad);
+  if (need > x->gemm_ws_bytes) {
+    if (x->d_gemm_ws) cudaFree(x->d_gemm_ws);
+    x->d_gemm_ws = nullptr;
+    x->gemm_ws_bytes = 0;
+    B200_CUDA(cudaMalloc(&x->d_gemm_ws, need));
+    x->gemm_ws_bytes = need;
+  }
+  char *w = (char *)x->d_gemm_ws;
+  __nv_bfloat16 *qh = (__nv_bfloat16 *)w;
+  w += al(2 * (size_t)Bpad * x->kpad);
+  float *q_inv = (float *)w;
+  w += al(4 * (size_t)Bpad);
+  float *q_margin = (float *)w;
+  w += al(4 * (size_t)Bpad);
+  uint32_t *tau_g = (uint32_t *)w;
+  exact_qprep_kernel<<<(unsigned)((Bpad * 32 + 255) / 256), 256, 0, s>>>(d_queries, B, Bpad, x->dim, x->kpad, x->metric,
+                                                                          x->d_maxn2, qh, q_inv, q_margin, tau_g,
+                                                                          d_cand_cnt);
+  B200_CUDA(cudaGetLastError());
+  int rc;
+  if (!x->tmap_x) x->tmap_x = malloc(sizeof(CUtensorMap));
+  if (x->tmap_rows != x->cap) {
+    if ((rc = make_tmap((CUtensorMap *)x->tmap_x, x->d_vech, (uint64_t)x->cap, (uint64_t)x->kpad, GM_N))) return rc;
+    x->tmap_rows = x->cap;
+  }
+  CUtensorMap tq;
+  if ((rc = make_tmap(&tq, qh, (uint64_t)Bpad, (uint64_t)x->kpad, GM_M))) return rc;
+  GemmParams p{};
+  p.aux = x->d_aux;
+  p.metric = x->metric;
+  p.kblocks = x->kpad / GM_K;
+  p.tiles_total = (int)((x->n + GM_N - 1) / GM_N);
+  p.warm_tiles = (k + 7) / 8;
+  p.k = k;
+  p.B = B;
+  p.q_inv = q_inv;
+  p.q_margin = q_margin;
+  p.tau_g = tau_g;
+  p.cand = d_cand;
+  p.cand_cnt = d_cand_cnt;
+  p.cand_cap = cand_cap;
+  const int m_tiles = (int)(Bpad / GM_M);
+  // one CTA per SM (shared memory); splits of the row range so that the grid covers the SMs about once, but never so
+  // short that the warm-up tiles dominate
+  int splits = std::max(1, x->sm_count / m_tiles);
+  const int min_tiles = 4 * p.warm_tiles + 4;
+  splits = std::min(splits, std::max(1, p.tiles_total / min_tiles));
+  p.tiles_per_split = (p.tiles_total + splits - 1) / splits;
+  splits = (p.tiles_total + p.tiles_per_split - 1) / p.tiles_per_split;
+  B200_CUDA(cudaFuncSetAttribute(exact_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  dim3 grid((unsigned)splits, (unsigned)m_tiles);
+  exact_gemm_kernel<<<grid, GM_THREADS, smem, s>>>(tq, *(CUtensorMap *)x->tmap_x, p);
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
 }  // namespace b200

@@ -88,7 +88,8 @@ __global__ void __launch_bounds__(SCAN_THREADS) exact_scan_kernel(const float4 *
 template <int CH, int U>
 __global__ void __launch_bounds__(SCAN_THREADS) exact_rerank_kernel(const float4 *vec, int row_chunks, int dim,
                                                                     const float *queries, int metric, int k,
-                                                                    const int32_t *cand, const int32_t *cand_cnt,
+                                                                    const uint8_t *alive, const int32_t *cand,
+                                                                    const int32_t *cand_cnt,
                                                                     int cand_cap, int n_pow2,
                                                                     unsigned long long *out_keys) {
   extern __shared__ unsigned long long skeys[];
@@ -104,7 +105,10 @@ __global__ void __launch_bounds__(SCAN_THREADS) exact_rerank_kernel(const float4
   for (int r0 = warp * U; r0 < cnt; r0 += nw * U) {
     int ids[U];
 #pragma unroll
-    for (int u = 0; u < U; u++) ids[u] = r0 + u < cnt ? cq[r0 + u] : -1;
+    for (int u = 0; u < U; u++) {
+      int id = r0 + u < cnt ? cq[r0 + u] : -1;
+      ids[u] = (id >= 0 && alive[id]) ? id : -1;
+    }
     const float dm = group_distances<32, CH, U>(vec, row_chunks, ids, Q, metric, lane);
     if ((lane & (32 / U - 1)) == 0) {
       const int u = lane / (32 / U);
@@ -205,7 +209,7 @@ static int run_rerank(b200exact *x, const float *d_q, int64_t B, int k, const in
   auto kern = exact_rerank_kernel<CH, U>;
   B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   kern<<<(unsigned)B, SCAN_THREADS, smem, s>>>(reinterpret_cast<const float4 *>(x->d_vec), x->row_floats / 4, x->dim,
-                                               d_q, x->metric, k, cand, cnt, cand_cap, n_pow2, out);
+                                               d_q, x->metric, k, x->d_alive, cand, cnt, cand_cap, n_pow2, out);
   B200_CUDA(cudaGetLastError());
   return 0;
 }
@@ -311,7 +315,7 @@ static int exact_search_core(b200exact *x, const float *d_q, int64_t B, int k, i
       B200_CUDA(cudaMemcpyAsync(cnt.data(), d_cnt, 4 * (size_t)B, cudaMemcpyDeviceToHost, s));
       B200_CUDA(cudaStreamSynchronize(s));
       for (int64_t q = 0; q < B; q++)
-        if (cnt[q] > cand_cap || cnt[q] < 0)
+        if (cnt[q] > cand_cap || cnt[q] < std::min<int64_t>(k, x->live))
           if ((rc = scan_topk(x, d_q + q * x->dim, 1, k, d_keys + q * k, ws, ws_b, s))) return rc;
       done = true;
     } else if (rc != B200HNSW_ERR_UNSUPPORTED || (force && !strcmp(force, "tensor"))) {
@@ -378,6 +382,8 @@ void b200exact_destroy(b200exact_t *x) {
   cudaFree(x->d_vech);
   cudaFree(x->d_aux);
   cudaFree(x->d_scratch);
+  cudaFree(x->d_maxn2);
+  cudaFree(x->d_gemm_ws);
   free(x->tmap_x);
   if (x->stream) cudaStreamDestroy(x->stream);
   delete x;
@@ -426,8 +432,8 @@ int b200exact_remove(b200exact_t *x, const int64_t *rows, int64_t n) {
     x->h_alive[r] = 0;
     x->live--;
     B200_CUDA(cudaMemsetAsync(x->d_alive + r, 0, 1, x->stream));
-    // the tensor path skips the row: |x|^2 = +inf (L2) / 1/|x| = 0 scores it out of every candidate list
-    const float dead = x->metric == B200HNSW_EUCLIDEAN ? __builtin_inff() : 0.f;
+    // the tensor path skips the row: |x|^2 = +inf (L2) / 1/|x| = NaN scores it out of every candidate list
+    const float dead = x->metric == B200HNSW_EUCLIDEAN ? __builtin_inff() : __builtin_nanf("");
     B200_CUDA(cudaMemcpyAsync(x->d_aux + r, &dead, sizeof dead, cudaMemcpyHostToDevice, x->stream));
   }
   B200_CUDA(cudaStreamSynchronize(x->stream));

@@ -23,6 +23,10 @@ struct b200exact {
   size_t scratch_bytes = 0;
   void *tmap_x = nullptr;            // CUtensorMap of d_vech (exact_gemm.cu), rebuilt when storage moves
   int64_t tmap_rows = -1;
+  uint32_t *d_maxn2 = nullptr;       // bits of max |x|^2 over rows ever added
+  int64_t aux_dead_cap = -1;         // capacity up to which d_aux of unused rows holds the dead value
+  void *d_gemm_ws = nullptr;         // query-side workspace of the tensor path
+  size_t gemm_ws_bytes = 0;
   std::mutex mu;                     // searches share the scratch buffer: one at a time per index
   int reserve(size_t bytes);
   int ensure_capacity(int64_t rows);
