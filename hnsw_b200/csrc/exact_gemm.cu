@@ -55,6 +55,18 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         : "memory");
   } while (!ok);
 }
+__device__ __forceinline__ void mbar_wait_backoff(uint32_t bar, uint32_t parity) {  // off the critical path
+  uint32_t ok;
+  for (;;) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (ok) break;
+    __nanosleep(64);
+  }
+}
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const void *tmap, int c0, int c1, uint32_t bar) {
   asm volatile(
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
@@ -114,7 +126,7 @@ struct GemmParams {
   long long B;
   const float *q_inv;      // [Bpad] 1/|q| (cosine)
   const float *q_margin;   // [Bpad] 2 * eps_q
-  uint32_t *tau_g;         // [Bpad] order-preserving bits of the shared bound on the k-th smallest score
+  uint32_t *slots_g;       // [Bpad][k] order-preserving bits of the slot minima merged over all CTAs of a query
   int32_t *cand;           // [B][cand_cap]
   int32_t *cand_cnt;       // [B]
   int cand_cap;
@@ -128,6 +140,7 @@ struct GemmSmem {
   static __host__ __device__ size_t total(int k) { return bars(k) + 16 * 8 + 1024; }       // + alignment slack
 };
 
+template <int METRIC>
 __global__ void __launch_bounds__(GM_THREADS, 1)
 exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x,
                   GemmParams p) {
@@ -177,7 +190,7 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       for (int idx = 0; idx < seq; idx++) {
         const int tile = t_begin + (idx < warm ? idx : idx - warm);
         for (int kb = 0; kb < p.kblocks; kb++) {
-          mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+          mbar_wait_backoff(bar_empty + 8 * stage, phase ^ 1);
           const uint32_t sa = s_base + stage * (GM_A_BYTES + GM_B_BYTES), sb = sa + GM_A_BYTES;
           mbar_expect_tx(bar_full + 8 * stage, GM_A_BYTES + GM_B_BYTES);
           tma_load_2d(sa, &tmap_q, kb * GM_K, mt * GM_M, bar_full + 8 * stage);
@@ -225,9 +238,10 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     float *my_slots = slots + (size_t)r * p.k;
     for (int j = 0; j < p.k; j++) my_slots[j] = __int_as_float(0x7f800000);
     const float margin = live_q ? p.q_margin[q] : 0.f;
-    const float qinv = (live_q && p.metric == 1) ? p.q_inv[q] : 0.f;
-    float thr = __int_as_float(0x7f800000);
-    int sub = 0;
+    const float nqinv = (live_q && METRIC == 1) ? -p.q_inv[q] : 0.f;
+    const float INF = __int_as_float(0x7f800000);
+    float thr = INF;
+    int sub = 0, sl = 0;
     for (int idx = 0; idx < seq; idx++) {
       const int as = idx & 1;
       const int tile = t_begin + (idx < warm ? idx : idx - warm);
@@ -243,34 +257,62 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       for (int c = 0; c < GM_N / 32; c++) {
         uint32_t v[32];
         tmem_ld32(taddr + c * 32, v);
-        float bmin = __int_as_float(0x7f800000);
+        const float4 *ax4 = reinterpret_cast<const float4 *>(ax + c * 32);
+        float sc[32];
 #pragma unroll
-        for (int j = 0; j < 32; j++) {
-          const float D = __uint_as_float(v[j]);
-          const float a = ax[c * 32 + j];
-          const float s = p.metric == 0 ? fmaf(-2.f, D, a) : fmaf(-D * a, qinv, 1.f);
-          bmin = fminf(bmin, s);
-          if (emit && s <= thr && s < __int_as_float(0x7f800000)) {  // dead rows score +inf / NaN
-            const int at = atomicAdd(&p.cand_cnt[q], 1);
-            if (at < p.cand_cap) p.cand[q * p.cand_cap + at] = tile * GM_N + c * 32 + j;
+        for (int j4 = 0; j4 < 8; j4++) {  // 32 independent scores: no branch, no dependent chain
+          const float4 a = ax4[j4];
+          if (METRIC == 0) {
+            sc[4 * j4 + 0] = fmaf(-2.f, __uint_as_float(v[4 * j4 + 0]), a.x);
+            sc[4 * j4 + 1] = fmaf(-2.f, __uint_as_float(v[4 * j4 + 1]), a.y);
+            sc[4 * j4 + 2] = fmaf(-2.f, __uint_as_float(v[4 * j4 + 2]), a.z);
+            sc[4 * j4 + 3] = fmaf(-2.f, __uint_as_float(v[4 * j4 + 3]), a.w);
+          } else {
+            sc[4 * j4 + 0] = fmaf(__uint_as_float(v[4 * j4 + 0]) * a.x, nqinv, 1.f);
+            sc[4 * j4 + 1] = fmaf(__uint_as_float(v[4 * j4 + 1]) * a.y, nqinv, 1.f);
+            sc[4 * j4 + 2] = fmaf(__uint_as_float(v[4 * j4 + 2]) * a.z, nqinv, 1.f);
+            sc[4 * j4 + 3] = fmaf(__uint_as_float(v[4 * j4 + 3]) * a.w, nqinv, 1.f);
           }
         }
+        float m8[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++)
+          m8[j] = fminf(fminf(sc[j], sc[j + 8]), fminf(sc[j + 16], sc[j + 24]));  // fminf drops NaN (dead rows)
+        const float bmin = fminf(fminf(fminf(m8[0], m8[1]), fminf(m8[2], m8[3])),
+                                 fminf(fminf(m8[4], m8[5]), fminf(m8[6], m8[7])));
+        if (emit && bmin <= thr) {  // rare: some row of this block passes the filter
+#pragma unroll
+          for (int j = 0; j < 32; j++)
+            if (sc[j] <= thr && sc[j] < INF) {  // dead rows score +inf / NaN
+              const int at = atomicAdd(&p.cand_cnt[q], 1);
+              if (at < p.cand_cap) p.cand[q * p.cand_cap + at] = tile * GM_N + c * 32 + j;
+            }
+        }
         // slot `sub mod k` holds the minimum over a set of rows disjoint from every other slot's set
-        const int sl = sub % p.k;
         my_slots[sl] = fminf(my_slots[sl], bmin);
+        if (++sl == p.k) sl = 0;
         sub++;
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
       if (sub >= p.k && live_q) {
+        // Now and then (often at first, when bounds improve fast) merge the slots with those of the other CTAs that
+        // work on this query: slot j of every CTA covers rows disjoint from slot j' of any CTA, so the element-wise
+        // minimum over CTAs is again k minima over k disjoint row sets.
+        const int done = idx + 1;
+        if (sub - GM_N / 32 < p.k || (done & (done - 1)) == 0 || (done & 31) == 0 || idx == seq - 1) {
+          uint32_t *sg = p.slots_g + q * p.k;
+          for (int j = 0; j < p.k; j++) {
+            const uint32_t mine = ord_bits(my_slots[j]);
+            const uint32_t old = atomicMin(&sg[j], mine);
+            if (old < mine) my_slots[j] = ord_float(old);
+          }
+        }
         // k distinct rows score <= max(slots): an upper bound on the k-th smallest score of the whole index
         float tau = my_slots[0];
         for (int j = 1; j < p.k; j++) tau = fmaxf(tau, my_slots[j]);
-        const uint32_t mine = ord_bits(tau);
-        const uint32_t old = atomicMin(&p.tau_g[q], mine);
-        tau = ord_float(min(old, mine));
-        thr = tau + margin;
+        thr = fminf(thr, tau + margin);
       }
     }
   }
@@ -313,7 +355,7 @@ __global__ void exact_fill_kernel(float *p, long long n, float v) {
 // queries: bf16 copy into Qh[Bpad][kpad], 1/|q|, filter margin 2*eps_q, tau = +inf, candidate count = 0
 __global__ void exact_qprep_kernel(const float *q, long long B, long long Bpad, int dim, int kpad, int metric,
                                    const uint32_t *maxn2, __nv_bfloat16 *qh, float *q_inv, float *q_margin,
-                                   uint32_t *tau_g, int32_t *cand_cnt) {
+                                   uint32_t *slots_g, int k, int32_t *cand_cnt) {
   const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (w >= Bpad) return;
@@ -336,9 +378,9 @@ __global__ void exact_qprep_kernel(const float *q, long long B, long long Bpad, 
     else eps = gamma * 1.001f + fp32;
     q_inv[w] = 1.0f / qn;
     q_margin[w] = 2.f * eps * 1.001f;
-    tau_g[w] = 0xff800000u;  // ord_bits(+inf)
     if (live) cand_cnt[w] = 0;
   }
+  for (int j = lane; j < k; j += 32) slots_g[w * k + j] = 0xff800000u;  // ord_bits(+inf)
 }
 
 // ---- host side -------------------------------------------------------------------------------------------------------
@@ -402,7 +444,7 @@ int exact_candidates_tensor(b200exact *x, const float *d_queries, int64_t B, int
   if (smem > x->smem_optin) return B200HNSW_ERR_UNSUPPORTED;
   const int64_t Bpad = (B + GM_M - 1) / GM_M * GM_M;
   auto al = [](size_t v) { return (v + 255) & ~(size_t)255; };
-  const size_t need = al(2 * (size_t)Bpad * x->kpad) + 3 * al(4 * (size_t)Bpad);
+  const size_t need = al(2 * (size_t)Bpad * x->kpad) + 2 * al(4 * (size_t)Bpad) + al(4 * (size_t)Bpad * k);
   if (need > x->gemm_ws_bytes) {
     if (x->d_gemm_ws) cudaFree(x->d_gemm_ws);
     x->d_gemm_ws = nullptr;
@@ -417,10 +459,10 @@ int exact_candidates_tensor(b200exact *x, const float *d_queries, int64_t B, int
   w += al(4 * (size_t)Bpad);
   float *q_margin = (float *)w;
   w += al(4 * (size_t)Bpad);
-  uint32_t *tau_g = (uint32_t *)w;
+  uint32_t *slots_g = (uint32_t *)w;
   exact_qprep_kernel<<<(unsigned)((Bpad * 32 + 255) / 256), 256, 0, s>>>(d_queries, B, Bpad, x->dim, x->kpad, x->metric,
-                                                                          x->d_maxn2, qh, q_inv, q_margin, tau_g,
-                                                                          d_cand_cnt);
+                                                                          x->d_maxn2, qh, q_inv, q_margin, slots_g,
+                                                                          k, d_cand_cnt);
   B200_CUDA(cudaGetLastError());
   int rc;
   if (!x->tmap_x) x->tmap_x = malloc(sizeof(CUtensorMap));
@@ -440,21 +482,31 @@ int exact_candidates_tensor(b200exact *x, const float *d_queries, int64_t B, int
   p.B = B;
   p.q_inv = q_inv;
   p.q_margin = q_margin;
-  p.tau_g = tau_g;
+  p.slots_g = slots_g;
   p.cand = d_cand;
   p.cand_cnt = d_cand_cnt;
   p.cand_cap = cand_cap;
   const int m_tiles = (int)(Bpad / GM_M);
   // one CTA per SM (shared memory); splits of the row range so that the grid covers the SMs about once, but never so
   // short that the warm-up tiles dominate
-  int splits = std::max(1, x->sm_count / m_tiles);
-  const int min_tiles = 4 * p.warm_tiles + 4;
-  splits = std::min(splits, std::max(1, p.tiles_total / min_tiles));
+  const int min_tiles = 8 * p.warm_tiles + 8;
+  const int max_splits = std::max(1, std::min(p.tiles_total / min_tiles, 64));
+  int splits = 1;
+  double best_eff = 0;
+  for (int sp = 1; sp <= max_splits; sp++) {  // fill whole waves of sm_count CTAs
+    long long ctas = (long long)m_tiles * sp;
+    double eff = (double)ctas / (double)(((ctas + x->sm_count - 1) / x->sm_count) * x->sm_count);
+    if (eff > best_eff + 0.02) {
+      best_eff = eff;
+      splits = sp;
+    }
+  }
   p.tiles_per_split = (p.tiles_total + splits - 1) / splits;
   splits = (p.tiles_total + p.tiles_per_split - 1) / p.tiles_per_split;
-  B200_CUDA(cudaFuncSetAttribute(exact_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  auto kern = x->metric == 0 ? exact_gemm_kernel<0> : exact_gemm_kernel<1>;
+  B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid((unsigned)splits, (unsigned)m_tiles);
-  exact_gemm_kernel<<<grid, GM_THREADS, smem, s>>>(tq, *(CUtensorMap *)x->tmap_x, p);
+  kern<<<grid, GM_THREADS, smem, s>>>(tq, *(CUtensorMap *)x->tmap_x, p);
   B200_CUDA(cudaGetLastError());
   return 0;
 }

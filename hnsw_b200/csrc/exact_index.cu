@@ -272,8 +272,13 @@ static int scan_topk(b200exact *x, const float *d_q, int64_t B, int k, unsigned 
 
 // ExactIndex.Search for B queries resident on the device; results to device buffers.  Synchronises `s` only when the
 // tensor path has to check for candidate-list overflow.
+static thread_local int64_t g_last_cands = 0, g_last_fallbacks = 0;
+static thread_local int g_last_path = 0;  // 1 = scan, 2 = tensor
+
 static int exact_search_core(b200exact *x, const float *d_q, int64_t B, int k, int64_t *d_rows, float *d_dists,
                              int32_t *d_counts, cudaStream_t s) {
+  g_last_cands = g_last_fallbacks = 0;
+  g_last_path = 0;
   if (x->live == 0 || x->n == 0) {  // exact.go:65-67
     B200_CUDA(cudaMemsetAsync(d_counts, 0, sizeof(int32_t) * (size_t)B, s));
     B200_CUDA(cudaMemsetAsync(d_rows, 0xff, sizeof(int64_t) * (size_t)B * k, s));
@@ -282,10 +287,10 @@ static int exact_search_core(b200exact *x, const float *d_q, int64_t B, int k, i
   }
   auto al = [](size_t v) { return (v + 255) & ~(size_t)255; };
   const char *force = getenv("B200EXACT_PATH");
-  bool want_tensor = x->n >= 16384 && (double)x->n * (double)B >= 1e8;  // small problems: the scan is cheaper
+  bool want_tensor = x->n >= 16384 && (double)x->n * (double)B >= 2e6;  // small problems: the scan is cheaper
   if (force && !strcmp(force, "scan")) want_tensor = false;
   if (force && !strcmp(force, "tensor")) want_tensor = true;
-  const int cand_cap = 1024;
+  const int cand_cap = 4096;
   const size_t keys_b = al(sizeof(unsigned long long) * (size_t)B * k);
   const size_t cand_b = want_tensor ? al(4 * (size_t)B * cand_cap) + al(4 * (size_t)B) : 0;
   const int n_chunks = (int)((x->n + SCAN_ROWS - 1) / SCAN_ROWS);
@@ -314,15 +319,23 @@ static int exact_search_core(b200exact *x, const float *d_q, int64_t B, int k, i
       std::vector<int32_t> cnt((size_t)B);
       B200_CUDA(cudaMemcpyAsync(cnt.data(), d_cnt, 4 * (size_t)B, cudaMemcpyDeviceToHost, s));
       B200_CUDA(cudaStreamSynchronize(s));
-      for (int64_t q = 0; q < B; q++)
-        if (cnt[q] > cand_cap || cnt[q] < std::min<int64_t>(k, x->live))
+      for (int64_t q = 0; q < B; q++) {
+        g_last_cands += cnt[q];
+        if (cnt[q] > cand_cap || cnt[q] < std::min<int64_t>(k, x->live)) {
+          g_last_fallbacks++;
           if ((rc = scan_topk(x, d_q + q * x->dim, 1, k, d_keys + q * k, ws, ws_b, s))) return rc;
+        }
+      }
+      g_last_path = 2;
       done = true;
     } else if (rc != B200HNSW_ERR_UNSUPPORTED || (force && !strcmp(force, "tensor"))) {
       return rc;
     }
   }
-  if (!done && (rc = scan_topk(x, d_q, B, k, d_keys, ws, ws_b, s))) return rc;
+  if (!done) {
+    if ((rc = scan_topk(x, d_q, B, k, d_keys, ws, ws_b, s))) return rc;
+    g_last_path = 1;
+  }
   long long total = (long long)B * k;
   exact_emit_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(d_keys, B, k, x->live, d_rows, d_dists, d_counts);
   B200_CUDA(cudaGetLastError());
@@ -490,7 +503,12 @@ int b200exact_search_batch(b200exact_t *x, const float *queries, int64_t B, int3
                   cudaSuccess ||
               (e = cudaStreamSynchronize(s)) != cudaSuccess))
     rc = cuda_fail(e, "exact D2H");
-  if (!rc && stats) cudaEventElapsedTime(&stats->kernel_ms, e0, e1);
+  if (!rc && stats) {
+    cudaEventElapsedTime(&stats->kernel_ms, e0, e1);
+    stats->dist_evals = g_last_path == 2 ? g_last_cands : (int64_t)B * x->live;  // fp32 evaluations made
+    stats->expansions = g_last_fallbacks;                                        // queries redone by the scan
+    stats->launches = g_last_path;                                               // 1 = scan path, 2 = tensor path
+  }
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);
   cudaFree(d_q);
