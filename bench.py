@@ -228,7 +228,7 @@ def run_ours(args, rank, local_rank, world):
     import torch
 
     import hnsw_b200
-    from hnsw_b200 import _lib
+    from hnsw_b200 import _lib, sharded
 
     _lib.lib()  # fail loudly if the CUDA extension is missing
     if not torch.cuda.is_available():
@@ -270,28 +270,17 @@ def run_ours(args, rank, local_rank, world):
     counts = torch.empty((B,), dtype=torch.int32, device=dev)
     counters = torch.zeros(8, dtype=torch.int64, device=dev)
     stream = torch.cuda.current_stream(dev)
-    if world > 1:
-        ids = torch.empty((B, k), dtype=torch.int64, device=dev)
-        all_d = torch.empty((world, B, k), dtype=torch.float32, device=dev)
-        all_i = torch.empty((world, B, k), dtype=torch.int64, device=dev)
-        all_c = torch.empty((world, B), dtype=torch.int32, device=dev)
-    m_d = torch.empty((B, k), dtype=torch.float32, device=dev)
-    m_i = torch.empty((B, k), dtype=torch.int64, device=dev)
-    m_c = torch.empty((B,), dtype=torch.int32, device=dev)
 
     def search_step(qd):
         g.search_device(qd.data_ptr(), B, k, rows.data_ptr(), dists.data_ptr(), counts.data_ptr(),
                         counters.data_ptr(), stream.cuda_stream)
 
+    merged = {}
+
     def merge_step():
-        torch.add(rows, rank * n, out=ids)  # shard row -> global id (unused slots are masked by counts)
-        dist.all_gather_into_tensor(all_d, dists)
-        dist.all_gather_into_tensor(all_i, ids)
-        dist.all_gather_into_tensor(all_c, counts)
-        _lib.check(_lib.lib().b200hnsw_merge_topk_device(
-            local_rank, world, B, k, C.c_void_p(all_d.data_ptr()), C.c_void_p(all_i.data_ptr()),
-            C.c_void_p(all_c.data_ptr()), 0, C.c_void_p(m_d.data_ptr()), C.c_void_p(m_i.data_ptr()),
-            C.c_void_p(m_c.data_ptr()), C.c_void_p(stream.cuda_stream)))
+        gids = sharded.global_ids(rows, rank, n)  # shard row -> global id (unused slots stay negative)
+        all_d, all_i, all_c = sharded.gather_shard_results(dist, dists, gids, counts)
+        merged["d"], merged["i"], merged["c"] = sharded.merge_topk_device(all_d, all_i, all_c, k, stream.cuda_stream)
 
     def barrier():
         if world > 1:
@@ -348,8 +337,8 @@ def run_ours(args, rank, local_rank, world):
             qtmp.copy_(Qh[i], non_blocking=True)
             search_step(qtmp)
             merge_step()
-            h_mi.copy_(m_i, non_blocking=True)
-            h_md.copy_(m_d, non_blocking=True)
+            h_mi.copy_(merged["i"], non_blocking=True)
+            h_md.copy_(merged["d"], non_blocking=True)
             torch.cuda.synchronize(dev)
 
     for i in range(max(args.warmup, 3)):

@@ -114,3 +114,24 @@ def test_empty_graph_and_errors():
     assert g.Search([0.5, 0.5], 1) is None  # graph.go:554-556
     with pytest.raises(ValueError, match="k must be greater than 0"):
         g.Search([0.5], 0)
+
+
+def test_merge_kernel_matches_spec():
+    # K4 vs its numpy specification (tests/merge_ref.py): ties -> lower shard, then list position; NaN last
+    import torch
+    from hnsw_b200 import sharded
+    from merge_ref import merge_topk_ref
+    rng = np.random.default_rng(3)
+    for G, B, k in ((2, 50, 10), (8, 33, 10), (4, 20, 64), (3, 7, 1)):
+        d = np.round(rng.uniform(0, 4, (G, B, k)), 1).astype(np.float32)  # coarse values: many ties
+        d.sort(axis=2)
+        d[rng.uniform(size=d.shape) < 0.02] = np.nan
+        i = rng.integers(0, 1 << 40, (G, B, k)).astype(np.int64)
+        c = rng.integers(0, k + 1, (G, B)).astype(np.int32)
+        md, mi, mc = sharded.merge_topk_device(torch.from_numpy(d).cuda(), torch.from_numpy(i).cuda(),
+                                               torch.from_numpy(c).cuda(), k)
+        torch.cuda.synchronize()
+        rd, ri, rc = merge_topk_ref(d, i, c, k)
+        assert np.array_equal(mc.cpu().numpy(), rc)
+        assert np.array_equal(mi.cpu().numpy(), ri)
+        assert np.array_equal(md.cpu().numpy(), rd, equal_nan=True)
