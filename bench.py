@@ -50,6 +50,8 @@ def parse_args():
     ap.add_argument("--pool", type=int, default=16, help="distinct query batches cycled through the steps")
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="target length of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-exact", action="store_true", help="skip the ExactIndex (K3) side measurement")
+    ap.add_argument("--exact-steps", type=int, default=10)
     return ap.parse_args()
 
 
@@ -391,6 +393,8 @@ def run_ours(args, rank, local_rank, world):
 
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         line.update(cpu_baseline_and_parity(args, g, Qh, last, last_rows, last_dists, last_counts, torch, dev, X))
+    if rank == 0 and world == 1 and not args.no_exact:
+        line["exact"] = exact_measurement(args, X, Qh, Qd, torch, dev, stream, not args.no_cpu_baseline)
     if rank == 0:
         emit(line)
     if world > 1:
@@ -449,6 +453,73 @@ def cpu_baseline_and_parity(args, g, Qh, last, last_rows, last_dists, last_count
                            "sample": f"{done} queries ({i} batches of {B}) in {el:.1f} s, one query per thread, AVX2 "
                                      f"distance, same graph read back from the device",
                            "single_thread_value": single}
+    return out
+
+
+def exact_measurement(args, X, Qh, Qd, torch, dev, stream, with_cpu):
+    """hybrid.ExactIndex.Search (exact.go:61-111) over the same rows and query batches: K3, the tensor path
+    (exact_gemm.cu: bf16 tcgen05 scores + provably safe filter + canonical fp32 re-rank).  A side measurement carried
+    in the same JSON line; the headline metric above is untouched."""
+    import hnsw_b200
+    n, dim, B, k = args.n, args.dim, args.batch, args.k
+    nb = Qd.shape[0]
+    x = hnsw_b200.ExactIndex(hnsw_b200.EuclideanDistance, device=dev.index, capacity=n)
+    t0 = time.perf_counter()
+    x.add_arrays(range(n), X)
+    add_s = time.perf_counter() - t0
+    rows = torch.empty((B, k), dtype=torch.int64, device=dev)
+    dists = torch.empty((B, k), dtype=torch.float32, device=dev)
+    counts = torch.empty((B,), dtype=torch.int32, device=dev)
+    for i in range(3):
+        x.search_device(Qd[i % nb].data_ptr(), B, k, rows.data_ptr(), dists.data_ptr(), counts.data_ptr(),
+                        stream.cuda_stream)
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for i in range(args.exact_steps):
+        x.search_device(Qd[(3 + i) % nb].data_ptr(), B, k, rows.data_ptr(), dists.data_ptr(), counts.data_ptr(),
+                        stream.cuda_stream)
+    e1.record(stream)
+    torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1) / args.exact_steps
+    last = (3 + args.exact_steps - 1) % nb
+    # end to end through b200exact_search_batch (host buffers)
+    t0 = time.perf_counter()
+    h_rows, h_d, h_c = x.search_rows(Qh[last].numpy(), k)
+    e2e_s = time.perf_counter() - t0
+    st = x.last_stats
+    peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text()) if (ROOT / "MEASURED_PEAKS.json").exists() else {}
+    peak = float(peaks.get("bf16_tflops_sustained", 1414.2))
+    flops = 2.0 * n * B * dim
+    out = {"metric": "ExactIndex.Search QPS (k=10)", "value": B / (ms / 1e3), "unit": "queries/s", "ms_per_step": ms,
+           "steps": args.exact_steps, "dtype": "bf16 scores, f32 canonical re-rank",
+           "e2e": {"value": B / e2e_s, "unit": "queries/s", "h2d_bytes_per_step": B * dim * 4,
+                   "d2h_bytes_per_step": B * k * 12 + B * 4},
+           "roofline": {"bound": "tensor", "achieved": flops / (ms / 1e3) / 1e12, "peak": peak, "unit": "TFLOP/s",
+                        "frac": flops / (ms / 1e3) / 1e12 / peak, "traffic": None,
+                        "kernel": "b200::exact_gemm_kernel (K3 tensor path) + re-rank, whole call",
+                        "algorithmic_flops_per_launch": flops,
+                        "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback"},
+           "path": {0: "scan", 1: "tensor"}.get(int(st["launches"]), str(st["launches"])),
+           "candidates_per_query": st["dist_evals"] / B, "fallback_queries": int(st["expansions"]),
+           "add_vec_per_s": n / add_s,
+           "device_and_host_call_agree": bool(np.array_equal(h_rows, rows.cpu().numpy()))}
+    if with_cpu:
+        from oracle import binding as oracle
+        cores = os.cpu_count() or 1
+        nq = 64
+        o_rows, o_d = oracle.exact_batch_search(X, Qh[last].numpy()[:nq], k, oracle.EUCLIDEAN, oracle.CANONICAL,
+                                                n_threads=cores)[:2]
+        out["parity"] = {"checked_queries": nq, "rows_equal": bool(np.array_equal(o_rows, h_rows[:nq])),
+                         "dists_bit_equal": bool(np.array_equal(np.asarray(o_d).view(np.uint32),
+                                                                h_d[:nq].view(np.uint32)))}
+        nq = min(B, 16 * cores)
+        t0 = time.perf_counter()
+        oracle.exact_batch_search(X, Qh[last].numpy()[:nq], k, oracle.EUCLIDEAN, oracle.SIMD, n_threads=cores)
+        el = time.perf_counter() - t0
+        out["cpu_baseline"] = {"value": nq / el, "unit": "queries/s", "cores": cores, "kind": "port",
+                               "sample": f"{nq} queries, one per thread, AVX2 distance, in {el:.1f} s"}
+    x.Close()
     return out
 
 

@@ -146,14 +146,14 @@ template <int G, int CH, int U>
 __device__ __forceinline__ float group_distances(const float4 *vec, int row_chunks, const int (&ids)[U],
                                                  const GQuery<CH> &Q, int metric, int gl) {
   float4 r[U][CH];
+  const bool full = row_chunks == G * CH;  // every lane owns CH real chunks: no per-chunk bounds test
 #pragma unroll
   for (int u = 0; u < U; u++) {
-    const float4 *row = vec + (size_t)(ids[u] < 0 ? 0 : ids[u]) * row_chunks;
+    // a missing row (ids[u] < 0) reads row 0 instead of branching; its distance is never used
+    const float4 *row = vec + (size_t)(ids[u] < 0 ? 0 : ids[u]) * row_chunks + gl;
 #pragma unroll
-    for (int t = 0; t < CH; t++) {
-      const int chunk = gl + G * t;
-      r[u][t] = (ids[u] >= 0 && chunk < row_chunks) ? ldg_f4(row + chunk) : make_float4(0.f, 0.f, 0.f, 0.f);
-    }
+    for (int t = 0; t < CH; t++)
+      r[u][t] = (full || gl + G * t < row_chunks) ? ldg_f4(row + G * t) : make_float4(0.f, 0.f, 0.f, 0.f);
   }
   if (metric == 0) {
     float p[U];

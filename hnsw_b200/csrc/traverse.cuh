@@ -179,7 +179,6 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
 #pragma unroll
         for (int u = 0; u < U; u++) {
           if (ids[u] < 0) continue;
-          c_evals++;
           if (init) {
             // graph.go:109-127: candidates.Push(entry); result.Push(entry); visited[entry]; the first Pop takes the
             // entry back out, so the candidate queue stays empty and the entry is the first node expanded
@@ -216,6 +215,7 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
         }
       }
     }
+    if (leader) c_evals += nfresh;  // E: one per evaluated row
     if (init && nfresh > 0) vcount = 1;
     // ---- leader decides: next node, end of layer ---------------------------------------------------------------------
     int next = -1;

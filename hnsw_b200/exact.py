@@ -66,6 +66,26 @@ class ExactIndex:
             self._key_of.append(keys[i])
             self._vecs.append(Vk[j].copy())
 
+    def add_arrays(self, keys, V) -> None:
+        """Array-level BatchAdd for keys not seen before (what a cgo host calls after its own map bookkeeping)."""
+        V = np.ascontiguousarray(V, dtype=np.float32)
+        self._ensure(V.shape[1])
+        if V.shape[1] != self._dim:
+            raise ValueError(f"embedding dimension mismatch: {self._dim} != {V.shape[1]}")
+        first = C.c_int64()
+        _lib.check(_lib.lib().b200exact_add_batch(self._x, V.ctypes.data_as(_lib.f32p), V.shape[0], C.byref(first)))
+        for j, key in enumerate(keys):
+            self._row_of[key] = first.value + j
+        self._key_of.extend(keys)
+        self._vecs.extend(V)
+
+    def search_device(self, d_queries: int, B: int, k: int, d_rows: int, d_dists: int, d_counts: int,
+                      stream: int = 0) -> None:
+        """Device-pointer search (rows int64 [B,k], dists f32 [B,k], counts i32 [B]) on `stream`; no host sync."""
+        _lib.check(_lib.lib().b200exact_search_batch_device(self._x, C.c_void_p(d_queries), B, k, C.c_void_p(d_rows),
+                                                            C.c_void_p(d_dists), C.c_void_p(d_counts),
+                                                            C.c_void_p(stream)))
+
     def _remove_rows(self, rows):
         r = np.ascontiguousarray(rows, dtype=np.int64)
         _lib.check(_lib.lib().b200exact_remove(self._x, r.ctypes.data_as(_lib.i64p), len(r)))

@@ -88,6 +88,8 @@ class Graph:
         if self._h is not None:
             _lib.lib().b200hnsw_destroy(self._h)
             self._h = None
+        self._keys, self._row_of, self._dim = [], {}, 0
+        self._vecs = np.zeros((0, 0), np.float32)
 
     def __del__(self):
         try:
@@ -379,6 +381,15 @@ class Graph:
             return []
         rows, _, counts = self.search_rows(np.stack(qs), k)
         return [self._nodes(rows[i], counts[i]) for i in range(len(qs))]
+
+    # ---- encode.go:133-262 -----------------------------------------------------------------------------------------
+    def Export(self, w) -> None:
+        from .encode import export_graph
+        export_graph(self, w)
+
+    def Import(self, r) -> None:
+        from .encode import import_graph
+        import_graph(self, r)
 
     def ParallelSearch(self, near, k: int, numWorkers: int = 0) -> List[Node]:
         """graph.go:631-826.  The reference's goroutine fan-out consumes results in channel-arrival order
