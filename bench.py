@@ -500,7 +500,7 @@ def exact_measurement(args, X, Qh, Qd, torch, dev, stream, with_cpu):
                         "kernel": "b200::exact_gemm_kernel (K3 tensor path) + re-rank, whole call",
                         "algorithmic_flops_per_launch": flops,
                         "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback"},
-           "path": {0: "scan", 1: "tensor"}.get(int(st["launches"]), str(st["launches"])),
+           "path": {1: "scan", 2: "tensor"}.get(int(st["launches"]), str(st["launches"])),
            "candidates_per_query": st["dist_evals"] / B, "fallback_queries": int(st["expansions"]),
            "add_vec_per_s": n / add_s,
            "device_and_host_call_agree": bool(np.array_equal(h_rows, rows.cpu().numpy()))}
