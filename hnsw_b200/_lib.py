@@ -6,10 +6,12 @@ the call raises.  Nothing here imports the oracle.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from pathlib import Path
 
 _PKG = Path(__file__).resolve().parent
-LIB_PATH = _PKG / "lib" / "libb200hnsw.so"
+# B200HNSW_LIB: another build of the same CUDA library (kernel tuning experiments); never a CPU path
+LIB_PATH = Path(os.environ["B200HNSW_LIB"]) if os.environ.get("B200HNSW_LIB") else _PKG / "lib" / "libb200hnsw.so"
 
 OK = 0
 ERR_BAD_ARG, ERR_OOM, ERR_CUDA, ERR_UNSUPPORTED, ERR_VISITED_OVERFLOW, ERR_STATE = -1, -2, -3, -4, -5, -6

@@ -1,10 +1,13 @@
 // dist.cuh -- warp-cooperative EuclideanDistance / CosineDistance (reference: distance.go:15-23).
 //
 // Canonical summation order (shared with oracle/hnsw_oracle.c so results are bit-identical):
-//   the padded row is cut in float4 chunks; chunk c belongs to lane (c mod 32); each lane runs ONE fused
-//   multiply-add chain over its elements in index order; the 32 partial sums are combined by an xor butterfly
-//   with offsets 16, 8, 4, 2, 1.  Rows are zero-padded to a multiple of 32 floats (128 B), which adds exact
-//   zeros to the chains and therefore changes nothing.
+//   the padded row is cut in float4 chunks; chunk c belongs to lane (c mod 32); each lane runs TWO fused
+//   multiply-add chains over its chunks in index order -- the even one takes elements x then z of every chunk, the
+//   odd one y then w -- and adds them (even + odd) at the end; the 32 partial sums are then combined by an xor
+//   butterfly with offsets 16, 8, 4, 2, 1.  Two chains per lane is the shape of Blackwell's packed fp32 pipe:
+//   FADD2/FFMA2 (add/fma.rn.f32x2) advance both chains with one instruction, each half a plain IEEE rn operation,
+//   so a float4 costs 4 issue slots instead of 8.  Rows are zero-padded to a multiple of 32 floats (128 B), which
+//   adds exact zeros to the chains and therefore changes nothing.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -19,12 +22,56 @@ __device__ __forceinline__ float butterfly(float v) {
   return v;
 }
 
+// ---- packed fp32 pairs (sm_100: FADD2 / FFMA2) ------------------------------------------------------------------------
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float lo, float hi) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+// even chain + odd chain
+__device__ __forceinline__ float sum2(f32x2 v) {
+  float lo, hi;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+  return __fadd_rn(lo, hi);
+}
+// one float4 of squared differences / products onto a chain pair
+__device__ __forceinline__ f32x2 acc_l2(const float4 &r, const float4 &q, f32x2 acc) {
+  f32x2 d0 = sub2(pk2(r.x, r.y), pk2(q.x, q.y));
+  f32x2 d1 = sub2(pk2(r.z, r.w), pk2(q.z, q.w));
+  acc = fma2(d0, d0, acc);
+  return fma2(d1, d1, acc);
+}
+__device__ __forceinline__ f32x2 acc_dot(const float4 &a, const float4 &b, f32x2 acc) {
+  acc = fma2(pk2(a.x, a.y), pk2(b.x, b.y), acc);
+  return fma2(pk2(a.z, a.w), pk2(b.z, b.w), acc);
+}
+
 // read-only, streaming 16 B load (vectors are immutable once written; rows are rarely re-used by the same SM)
 __device__ __forceinline__ float4 ldg_f4(const float4 *p) {
   float4 v;
   asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
                : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
                : "l"(p));
+  return v;
+}
+
+// the same load when `ok`; otherwise nothing is loaded and the result is undefined (the empty asm only tells the compiler
+// the registers are written, so no zero fill is emitted)
+__device__ __forceinline__ float4 ldg_f4_if(const float4 *p, bool ok) {
+  float4 v;
+  asm("" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w));
+  if (ok) v = ldg_f4(p);
   return v;
 }
 
@@ -38,7 +85,7 @@ struct QueryRegs {
 template <int CPL>
 __device__ __forceinline__ void load_query(QueryRegs<CPL> &Q, const float *query, int dim, int nchunks, int lane) {
   // the caller's query is [dim] floats, unpadded and possibly unaligned for float4: scalar loads, once
-  float acc = 0.f;
+  f32x2 acc = 0ull;
 #pragma unroll
   for (int c = 0; c < CPL; c++) {
     int chunk = lane + 32 * c;
@@ -51,10 +98,9 @@ __device__ __forceinline__ void load_query(QueryRegs<CPL> &Q, const float *query
       }
     }
     Q.q[c] = make_float4(v[0], v[1], v[2], v[3]);
-#pragma unroll
-    for (int e = 0; e < 4; e++) acc = __fmaf_rn(v[e], v[e], acc);
+    acc = acc_dot(Q.q[c], Q.q[c], acc);
   }
-  Q.qq = butterfly(acc);
+  Q.qq = butterfly(sum2(acc));
 }
 
 // issue the loads of one stored row (lane's chunks); nchunks = padded_dim/4
@@ -71,32 +117,19 @@ __device__ __forceinline__ void load_row(float4 (&r)[CPL], const float4 *row, in
 template <int CPL>
 __device__ __forceinline__ float finish_distance(const float4 (&r)[CPL], const QueryRegs<CPL> &Q, int metric) {
   if (metric == 0) {
-    float acc = 0.f;
+    f32x2 acc = 0ull;
 #pragma unroll
-    for (int c = 0; c < CPL; c++) {
-      float dx = __fsub_rn(r[c].x, Q.q[c].x), dy = __fsub_rn(r[c].y, Q.q[c].y);
-      float dz = __fsub_rn(r[c].z, Q.q[c].z), dw = __fsub_rn(r[c].w, Q.q[c].w);
-      acc = __fmaf_rn(dx, dx, acc);
-      acc = __fmaf_rn(dy, dy, acc);
-      acc = __fmaf_rn(dz, dz, acc);
-      acc = __fmaf_rn(dw, dw, acc);
-    }
-    return __fsqrt_rn(butterfly(acc));
+    for (int c = 0; c < CPL; c++) acc = acc_l2(r[c], Q.q[c], acc);
+    return __fsqrt_rn(butterfly(sum2(acc)));
   }
-  float dot = 0.f, na = 0.f;
+  f32x2 dot2 = 0ull, na2 = 0ull;
 #pragma unroll
   for (int c = 0; c < CPL; c++) {
-    dot = __fmaf_rn(r[c].x, Q.q[c].x, dot);
-    dot = __fmaf_rn(r[c].y, Q.q[c].y, dot);
-    dot = __fmaf_rn(r[c].z, Q.q[c].z, dot);
-    dot = __fmaf_rn(r[c].w, Q.q[c].w, dot);
-    na = __fmaf_rn(r[c].x, r[c].x, na);
-    na = __fmaf_rn(r[c].y, r[c].y, na);
-    na = __fmaf_rn(r[c].z, r[c].z, na);
-    na = __fmaf_rn(r[c].w, r[c].w, na);
+    dot2 = acc_dot(r[c], Q.q[c], dot2);
+    na2 = acc_dot(r[c], r[c], na2);
   }
-  dot = butterfly(dot);
-  na = butterfly(na);
+  const float dot = butterfly(sum2(dot2));
+  const float na = butterfly(sum2(na2));
   // 1 - dot / sqrt(|a|^2 * |b|^2)
   return __fsub_rn(1.0f, __fdiv_rn(dot, __fsqrt_rn(__fmul_rn(na, Q.qq))));
 }
@@ -105,36 +138,20 @@ __device__ __forceinline__ float finish_distance(const float4 (&r)[CPL], const Q
 __device__ __forceinline__ float warp_distance_generic(const float4 *a, const float4 *b, int nchunks, int metric,
                                                        int lane) {
   if (metric == 0) {
-    float acc = 0.f;
-    for (int chunk = lane; chunk < nchunks; chunk += 32) {
-      float4 x = a[chunk], y = b[chunk];
-      float dx = __fsub_rn(x.x, y.x), dy = __fsub_rn(x.y, y.y), dz = __fsub_rn(x.z, y.z), dw = __fsub_rn(x.w, y.w);
-      acc = __fmaf_rn(dx, dx, acc);
-      acc = __fmaf_rn(dy, dy, acc);
-      acc = __fmaf_rn(dz, dz, acc);
-      acc = __fmaf_rn(dw, dw, acc);
-    }
-    return __fsqrt_rn(butterfly(acc));
+    f32x2 acc = 0ull;
+    for (int chunk = lane; chunk < nchunks; chunk += 32) acc = acc_l2(a[chunk], b[chunk], acc);
+    return __fsqrt_rn(butterfly(sum2(acc)));
   }
-  float dot = 0.f, na = 0.f, nb = 0.f;
+  f32x2 dot2 = 0ull, na2 = 0ull, nb2 = 0ull;
   for (int chunk = lane; chunk < nchunks; chunk += 32) {
     float4 x = a[chunk], y = b[chunk];
-    dot = __fmaf_rn(x.x, y.x, dot);
-    dot = __fmaf_rn(x.y, y.y, dot);
-    dot = __fmaf_rn(x.z, y.z, dot);
-    dot = __fmaf_rn(x.w, y.w, dot);
-    na = __fmaf_rn(x.x, x.x, na);
-    na = __fmaf_rn(x.y, x.y, na);
-    na = __fmaf_rn(x.z, x.z, na);
-    na = __fmaf_rn(x.w, x.w, na);
-    nb = __fmaf_rn(y.x, y.x, nb);
-    nb = __fmaf_rn(y.y, y.y, nb);
-    nb = __fmaf_rn(y.z, y.z, nb);
-    nb = __fmaf_rn(y.w, y.w, nb);
+    dot2 = acc_dot(x, y, dot2);
+    na2 = acc_dot(x, x, na2);
+    nb2 = acc_dot(y, y, nb2);
   }
-  dot = butterfly(dot);
-  na = butterfly(na);
-  nb = butterfly(nb);
+  const float dot = butterfly(sum2(dot2));
+  const float na = butterfly(sum2(na2));
+  const float nb = butterfly(sum2(nb2));
   return __fsub_rn(1.0f, __fdiv_rn(dot, __fsqrt_rn(__fmul_rn(na, nb))));
 }
 

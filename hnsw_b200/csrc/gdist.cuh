@@ -1,7 +1,8 @@
 // gdist.cuh -- EuclideanDistance / CosineDistance (distance.go:15-23) evaluated by a GROUP of G lanes (G = 8, 16, 32),
 // so one warp serves 32/G queries at once.  Bit-identical to the canonical order of dist.cuh / oracle/hnsw_oracle.c:
-//   chunk c (float4) belongs to chain (c mod 32); a chain is one fused-multiply-add sequence in index order; the 32
-//   chain sums are combined by an xor butterfly with offsets 16, 8, 4, 2, 1.
+//   chunk c (float4) belongs to chain pair (c mod 32): an even chain over x, z and an odd chain over y, w of its chunks
+//   in index order, added at the end (FADD2/FFMA2 advance both at once); the 32 sums are combined by an xor butterfly
+//   with offsets 16, 8, 4, 2, 1.
 // With G lanes, lane g owns chunks g, g+G, g+2G, ... and therefore the 32/G chains g, g+G, ...; butterfly steps with
 // offset >= G combine chains held by the same lane (plain adds), the remaining steps are shuffles inside the group.
 // fadd is commutative, so which lane performs an addition does not change its bits.
@@ -21,7 +22,10 @@ struct GroupGeom {
 
 // combine the chains a lane holds (butterfly offsets 16 .. G)
 template <int NCH>
-__device__ __forceinline__ float inlane_combine(const float (&a)[NCH]) {
+__device__ __forceinline__ float inlane_combine(const f32x2 (&p)[NCH]) {
+  float a[NCH];
+#pragma unroll
+  for (int i = 0; i < NCH; i++) a[i] = sum2(p[i]);  // even + odd chain
   if constexpr (NCH == 1) return a[0];
   else if constexpr (NCH == 2) return __fadd_rn(a[0], a[1]);                                    // offset 16
   else return __fadd_rn(__fadd_rn(a[0], a[2]), __fadd_rn(a[1], a[3]));                           // 16, then 8
@@ -70,9 +74,9 @@ template <int G, int CH>
 __device__ __forceinline__ void group_load_query(GQuery<CH> &Q, const float *query, bool on, int dim, int nchunks,
                                                  int gl) {
   constexpr int NCH = GroupGeom<G>::NCH;
-  float acc[NCH];
+  f32x2 acc[NCH];
 #pragma unroll
-  for (int i = 0; i < NCH; i++) acc[i] = 0.f;
+  for (int i = 0; i < NCH; i++) acc[i] = 0ull;
 #pragma unroll
   for (int t = 0; t < CH; t++) {
     const int chunk = gl + G * t;
@@ -85,10 +89,7 @@ __device__ __forceinline__ void group_load_query(GQuery<CH> &Q, const float *que
       }
     }
     Q.q[t] = make_float4(v[0], v[1], v[2], v[3]);
-    float a = acc[t % NCH];
-#pragma unroll
-    for (int e = 0; e < 4; e++) a = __fmaf_rn(v[e], v[e], a);
-    acc[t % NCH] = a;
+    acc[t % NCH] = acc_dot(Q.q[t], Q.q[t], acc[t % NCH]);
   }
   float s[1] = {inlane_combine<NCH>(acc)};
   group_reduce<G, 1>(s, gl);
@@ -99,75 +100,94 @@ __device__ __forceinline__ void group_load_query(GQuery<CH> &Q, const float *que
 template <int G, int CH>
 __device__ __forceinline__ float row_partial_l2(const float4 (&r)[CH], const GQuery<CH> &Q) {
   constexpr int NCH = GroupGeom<G>::NCH;
-  float acc[NCH];
+  f32x2 acc[NCH];
 #pragma unroll
-  for (int i = 0; i < NCH; i++) acc[i] = 0.f;
+  for (int i = 0; i < NCH; i++) acc[i] = 0ull;
 #pragma unroll
-  for (int t = 0; t < CH; t++) {
-    float dx = __fsub_rn(r[t].x, Q.q[t].x), dy = __fsub_rn(r[t].y, Q.q[t].y);
-    float dz = __fsub_rn(r[t].z, Q.q[t].z), dw = __fsub_rn(r[t].w, Q.q[t].w);
-    float a = acc[t % NCH];
-    a = __fmaf_rn(dx, dx, a);
-    a = __fmaf_rn(dy, dy, a);
-    a = __fmaf_rn(dz, dz, a);
-    a = __fmaf_rn(dw, dw, a);
-    acc[t % NCH] = a;
-  }
+  for (int t = 0; t < CH; t++) acc[t % NCH] = acc_l2(r[t], Q.q[t], acc[t % NCH]);
   return inlane_combine<NCH>(acc);
 }
 
 template <int G, int CH>
 __device__ __forceinline__ void row_partial_cos(const float4 (&r)[CH], const GQuery<CH> &Q, float &dot, float &na) {
   constexpr int NCH = GroupGeom<G>::NCH;
-  float ad[NCH], an[NCH];
+  f32x2 ad[NCH], an[NCH];
 #pragma unroll
-  for (int i = 0; i < NCH; i++) ad[i] = an[i] = 0.f;
+  for (int i = 0; i < NCH; i++) ad[i] = an[i] = 0ull;
 #pragma unroll
   for (int t = 0; t < CH; t++) {
-    float d = ad[t % NCH], n = an[t % NCH];
-    d = __fmaf_rn(r[t].x, Q.q[t].x, d);
-    d = __fmaf_rn(r[t].y, Q.q[t].y, d);
-    d = __fmaf_rn(r[t].z, Q.q[t].z, d);
-    d = __fmaf_rn(r[t].w, Q.q[t].w, d);
-    n = __fmaf_rn(r[t].x, r[t].x, n);
-    n = __fmaf_rn(r[t].y, r[t].y, n);
-    n = __fmaf_rn(r[t].z, r[t].z, n);
-    n = __fmaf_rn(r[t].w, r[t].w, n);
-    ad[t % NCH] = d;
-    an[t % NCH] = n;
+    ad[t % NCH] = acc_dot(r[t], Q.q[t], ad[t % NCH]);
+    an[t % NCH] = acc_dot(r[t], r[t], an[t % NCH]);
   }
   dot = inlane_combine<NCH>(ad);
   na = inlane_combine<NCH>(an);
 }
 
-// Distances of U rows (ids[u] < 0 = no row) to the group's query.  Returns, in every lane, the distance of row
-// (gl * U / G); the caller fetches row u from lane u * (G / U) of its group.
+// ---- the three phases of evaluating U rows (ids[u] < 0 = no row), split so a caller can issue the loads of the next
+//      batch between the multiply-adds of this one and its reduction (software pipelining, traverse.cuh) -----------
+
+// phase 1: issue the 16 B loads.  A missing row loads nothing and leaves its registers undefined; its (garbage)
+// distance is never used.  G == 8: rows are padded to 128 B (row_chunks % 8 == 0) and the launcher instantiates
+// CH == row_chunks / 8 exactly, so every lane owns CH real chunks and no bounds test is needed.
+template <int G, int CH, int U>
+__device__ __forceinline__ void group_load_rows(float4 (&r)[U][CH], const float4 *vec, int row_chunks,
+                                                const int (&ids)[U], int gl) {
+#pragma unroll
+  for (int u = 0; u < U; u++) {
+    const float4 *row = vec + (size_t)ids[u] * row_chunks + gl;
+    const bool ok = ids[u] >= 0;
+#pragma unroll
+    for (int t = 0; t < CH; t++) {
+      if constexpr (G == 8) {
+        r[u][t] = ldg_f4_if(row + G * t, ok);
+      } else {
+        r[u][t] = gl + G * t < row_chunks ? ldg_f4_if(row + G * t, ok) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+  }
+}
+
+template <int U>
+struct GPartial {
+  float a[U];  // L2: sum of squared differences; cosine: dot
+  float b[U];  // cosine: |row|^2
+};
+
+// phase 2: the lane's share of the sums (consumes the row registers)
+template <int G, int CH, int U>
+__device__ __forceinline__ void group_partials(GPartial<U> &P, const float4 (&r)[U][CH], const GQuery<CH> &Q,
+                                               int metric) {
+  if (metric == 0) {
+#pragma unroll
+    for (int u = 0; u < U; u++) P.a[u] = row_partial_l2<G, CH>(r[u], Q);
+  } else {
+#pragma unroll
+    for (int u = 0; u < U; u++) row_partial_cos<G, CH>(r[u], Q, P.a[u], P.b[u]);
+  }
+}
+
+// phase 3: cross-lane reduction and the final formula.  Returns, in every lane, the distance of row (gl * U / G);
+// the caller fetches row u from lane u * (G / U) of its group.
+template <int G, int CH, int U>
+__device__ __forceinline__ float group_finish(GPartial<U> &P, const GQuery<CH> &Q, int metric, int gl) {
+  if (metric == 0) {
+    group_reduce<G, U>(P.a, gl);
+    return __fsqrt_rn(P.a[0]);
+  }
+  group_reduce<G, U>(P.a, gl);
+  group_reduce<G, U>(P.b, gl);
+  return __fsub_rn(1.0f, __fdiv_rn(P.a[0], __fsqrt_rn(__fmul_rn(P.b[0], Q.qq))));
+}
+
+// all three at once
 template <int G, int CH, int U>
 __device__ __forceinline__ float group_distances(const float4 *vec, int row_chunks, const int (&ids)[U],
                                                  const GQuery<CH> &Q, int metric, int gl) {
   float4 r[U][CH];
-  const bool full = row_chunks == G * CH;  // every lane owns CH real chunks: no per-chunk bounds test
-#pragma unroll
-  for (int u = 0; u < U; u++) {
-    // a missing row (ids[u] < 0) reads row 0 instead of branching; its distance is never used
-    const float4 *row = vec + (size_t)(ids[u] < 0 ? 0 : ids[u]) * row_chunks + gl;
-#pragma unroll
-    for (int t = 0; t < CH; t++)
-      r[u][t] = (full || gl + G * t < row_chunks) ? ldg_f4(row + G * t) : make_float4(0.f, 0.f, 0.f, 0.f);
-  }
-  if (metric == 0) {
-    float p[U];
-#pragma unroll
-    for (int u = 0; u < U; u++) p[u] = row_partial_l2<G, CH>(r[u], Q);
-    group_reduce<G, U>(p, gl);
-    return __fsqrt_rn(p[0]);
-  }
-  float pd[U], pn[U];
-#pragma unroll
-  for (int u = 0; u < U; u++) row_partial_cos<G, CH>(r[u], Q, pd[u], pn[u]);
-  group_reduce<G, U>(pd, gl);
-  group_reduce<G, U>(pn, gl);
-  return __fsub_rn(1.0f, __fdiv_rn(pd[0], __fsqrt_rn(__fmul_rn(pn[0], Q.qq))));
+  group_load_rows<G, CH, U>(r, vec, row_chunks, ids, gl);
+  GPartial<U> P;
+  group_partials<G, CH, U>(P, r, Q, metric);
+  return group_finish<G, CH, U>(P, Q, metric, gl);
 }
 
 }  // namespace b200

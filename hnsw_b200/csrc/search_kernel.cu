@@ -80,9 +80,11 @@ int launch_traverse(b200hnsw *h, TraverseParams &p, int vis_cap, cudaStream_t s)
   }
 #define K1(G_, CH_, U_) return launch_t<G_, CH_, U_, ((CH_) >= 12 ? 2 : ((CH_) * (U_) <= 8 ? 5 : 4))>(h, g, p, s)
   if (G == 8) {
-    if (ch <= 1) K1(8, 1, 8);
-    if (ch <= 2) K1(8, 2, 4);
-    if (ch <= 4) K1(8, 4, 2);
+    // G = 8 kernels load rows without bounds tests: CH must equal row_chunks / 8 exactly (gdist.cuh)
+    if (ch == 1) K1(8, 1, 8);
+    if (ch == 2) K1(8, 2, 4);
+    if (ch == 3) K1(8, 3, 2);
+    if (ch == 4) K1(8, 4, 2);
     G = 16;
     ch = (g.row_chunks + 15) / 16;
   }

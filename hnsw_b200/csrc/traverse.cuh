@@ -135,9 +135,12 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
         if (leader) c_exp++;
       }
       bool more = expand;
+      int nb_next = -1;
+      if (more && gl < M) nb_next = list[gl];
       for (int b0 = 0; b0 < M; b0 += G) {
-        int nb = -1;
-        if (more && b0 + gl < M) nb = list[b0 + gl];
+        const int nb = nb_next;
+        nb_next = -1;  // the next G entries are requested before these are looked at
+        if (more && b0 + G + gl < M) nb_next = list[b0 + G + gl];
         const bool valid = nb >= 0;
         const unsigned gv = (__ballot_sync(FULL, valid) >> gshift) & GBITS;
         bool fr = false;
@@ -167,11 +170,23 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
     const bool overflow = vcount * 2 > (int)vmask;  // load factor > 1/2: fail loudly, never approximate
     if (overflow) nfresh = 0;
     // ---- evaluate the fresh rows, U at a time; the leader replays graph.go:146-159 in key order -------------------
+    // Software pipeline: the loads of batch b+1 are issued right after the multiply-adds of batch b, so they fly during
+    // b's reduction and the leader's serial replay.
+    int nid[U];
+    float4 rr[U][CH];
+#pragma unroll
+    for (int u = 0; u < U; u++) nid[u] = u < nfresh ? fresh[u] : -1;
+    group_load_rows<G, CH, U>(rr, g.vec, g.row_chunks, nid, gl);
     for (int b0 = 0; __any_sync(FULL, b0 < nfresh); b0 += U) {
       int ids[U];
 #pragma unroll
-      for (int u = 0; u < U; u++) ids[u] = b0 + u < nfresh ? fresh[b0 + u] : -1;
-      const float dmine = group_distances<G, CH, U>(g.vec, g.row_chunks, ids, Q, p.metric, gl);
+      for (int u = 0; u < U; u++) ids[u] = nid[u];
+      GPartial<U> P;
+      group_partials<G, CH, U>(P, rr, Q, p.metric);
+#pragma unroll
+      for (int u = 0; u < U; u++) nid[u] = b0 + U + u < nfresh ? fresh[b0 + U + u] : -1;
+      group_load_rows<G, CH, U>(rr, g.vec, g.row_chunks, nid, gl);
+      const float dmine = group_finish<G, CH, U>(P, Q, p.metric, gl);
       float d[U];
 #pragma unroll
       for (int u = 0; u < U; u++) d[u] = __shfl_sync(FULL, dmine, leader_lane + u * (G / U));
@@ -195,12 +210,17 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
           }
           if (kcur == 1) {
             // a full one-element queue: `improved` (graph.go:147) and the replacement test (graph.go:150,
-            // result.Max() is that element) are the same comparison
+            // result.Max() is that element) are the same comparison.  No candidate queue either: the new best is
+            // strictly below everything evaluated on this layer, so candidates.Push sifts it to the root, where
+            // neither a later Push of this step (strict <) nor PopLast (ef >= 1 keeps slot 0) can move it; the next
+            // Pop (graph.go:126) therefore returns exactly this node, and when nothing improved the loop ends
+            // (graph.go:164-166) without looking at the queue.
             if (d[u] < best_d) {
               improved = true;
               best_d = d[u];
               best_id = ids[u];
             }
+            continue;
           } else {
             improved = improved || (R.len > 0 && d[u] < R.min_dist());  // graph.go:147
             if (R.len < kcur) {
@@ -223,6 +243,8 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
       const int rl = kcur == 1 ? r1 : R.len;
       if (init) {
         if (nfresh > 0) next = cur;                                 // graph.go:125-127, first iteration
+      } else if (kcur == 1) {
+        if (improved) next = best_id;                               // what candidates.Pop() would return, see above
       } else if (!(!improved && rl >= kcur) && C.len > 0) {        // graph.go:164-166, 125
         next = (int)C.pop().y;
       }

@@ -21,9 +21,11 @@
  * ============================================================================================ */
 
 /* ORA_FLAVOR_CANONICAL: the order the device kernels use.  The vector is cut in float4 chunks;
- * chunk c belongs to accumulator (c mod 32); each accumulator runs one fused-multiply-add chain
- * over its elements in index order; the 32 partial sums are combined by an xor butterfly with
- * offsets 16, 8, 4, 2, 1 (float addition is commutative, so every lane holds the same bits). */
+ * chunk c belongs to accumulator pair (c mod 32): an EVEN fused-multiply-add chain over elements
+ * x then z of its chunks in index order, an ODD chain over y then w, added (even + odd) at the
+ * end; the 32 sums are combined by an xor butterfly with offsets 16, 8, 4, 2, 1 (float addition
+ * is commutative, so every lane holds the same bits).  Element i therefore goes to chain pair
+ * (i >> 2) & 31, half i & 1. */
 static inline float butterfly32(float *acc) {
   /* lane 0 of the butterfly only ever reads lanes < off, so a halving reduction gives the same bits */
   for (int off = 16; off >= 1; off >>= 1)
@@ -34,8 +36,8 @@ static inline float butterfly32(float *acc) {
 /* AVX2 form of the same order.  A block of 128 floats touches each of the 32 accumulators once, four
  * elements in a row.  For 8 consecutive chunks held in 4 registers r0..r3 (r_i = [chunk 2i | chunk 2i+1]) a
  * 4x4 transpose inside each 128-bit half gives X = [c0.x c2.x c4.x c6.x | c1.x c3.x c5.x c7.x] (likewise Y, Z,
- * W), so one register of 8 accumulators advances by fma(X), fma(Y), fma(Z), fma(W): the per-accumulator chain
- * is still x, y, z, w in index order.  Bit-identical to the scalar definition (tests/test_oracle_kat.py). */
+ * W), so one register of 8 even accumulators advances by fma(X), fma(Z) and one of 8 odd accumulators by
+ * fma(Y), fma(W).  Bit-identical to the scalar definition (tests/test_oracle_kat.py). */
 static inline void transpose8(__m256 r0, __m256 r1, __m256 r2, __m256 r3, __m256 *x, __m256 *y, __m256 *z,
                               __m256 *w) {
   __m256 t0 = _mm256_unpacklo_ps(r0, r1), t1 = _mm256_unpackhi_ps(r0, r1);
@@ -54,10 +56,16 @@ static inline void unpermute(const __m256 v[4], float *acc) {
     for (int j = 0; j < 8; j++) acc[8 * g + kLanePerm[j]] = t[j];
   }
 }
+/* even + odd per chain, then the butterfly */
+static inline float finish64(float *even, float *odd) {
+  for (int i = 0; i < 32; i++) even[i] = even[i] + odd[i];
+  return butterfly32(even);
+}
 
 static float l2sq_canonical(const float *restrict a, const float *restrict b, int d) {
-  float acc[32] __attribute__((aligned(64)));
-  __m256 v[4] = {_mm256_setzero_ps(), _mm256_setzero_ps(), _mm256_setzero_ps(), _mm256_setzero_ps()};
+  float acc[2][32] __attribute__((aligned(64)));
+  __m256 ve[4], vo[4];
+  for (int g = 0; g < 4; g++) ve[g] = vo[g] = _mm256_setzero_ps();
   int i = 0;
   for (; i + 128 <= d; i += 128) {
     for (int g = 0; g < 4; g++) {
@@ -68,24 +76,27 @@ static float l2sq_canonical(const float *restrict a, const float *restrict b, in
       __m256 r3 = _mm256_sub_ps(_mm256_loadu_ps(pa + 24), _mm256_loadu_ps(pb + 24));
       __m256 x, y, z, w;
       transpose8(r0, r1, r2, r3, &x, &y, &z, &w);
-      v[g] = _mm256_fmadd_ps(w, w, _mm256_fmadd_ps(z, z, _mm256_fmadd_ps(y, y, _mm256_fmadd_ps(x, x, v[g]))));
+      ve[g] = _mm256_fmadd_ps(z, z, _mm256_fmadd_ps(x, x, ve[g]));
+      vo[g] = _mm256_fmadd_ps(w, w, _mm256_fmadd_ps(y, y, vo[g]));
     }
   }
-  unpermute(v, acc);
+  unpermute(ve, acc[0]);
+  unpermute(vo, acc[1]);
   for (; i < d; i++) {
     float diff = a[i] - b[i];
     int lane = (i >> 2) & 31;
-    acc[lane] = fmaf(diff, diff, acc[lane]);
+    acc[i & 1][lane] = fmaf(diff, diff, acc[i & 1][lane]);
   }
-  return butterfly32(acc);
+  return finish64(acc[0], acc[1]);
 }
 
 static void dot3_canonical(const float *restrict a, const float *restrict b, int d, float *dot, float *na,
                            float *nb) {
-  float accd[32] __attribute__((aligned(64))), acca[32] __attribute__((aligned(64))),
-      accb[32] __attribute__((aligned(64)));
-  __m256 vd[4], va[4], vb[4];
-  for (int g = 0; g < 4; g++) vd[g] = va[g] = vb[g] = _mm256_setzero_ps();
+  float accd[2][32] __attribute__((aligned(64))), acca[2][32] __attribute__((aligned(64))),
+      accb[2][32] __attribute__((aligned(64)));
+  __m256 vd[2][4], va[2][4], vb[2][4];
+  for (int h = 0; h < 2; h++)
+    for (int g = 0; g < 4; g++) vd[h][g] = va[h][g] = vb[h][g] = _mm256_setzero_ps();
   int i = 0;
   for (; i + 128 <= d; i += 128) {
     for (int g = 0; g < 4; g++) {
@@ -95,23 +106,28 @@ static void dot3_canonical(const float *restrict a, const float *restrict b, int
                  &ax, &ay, &az, &aw);
       transpose8(_mm256_loadu_ps(pb), _mm256_loadu_ps(pb + 8), _mm256_loadu_ps(pb + 16), _mm256_loadu_ps(pb + 24),
                  &bx, &by, &bz, &bw);
-      vd[g] = _mm256_fmadd_ps(aw, bw, _mm256_fmadd_ps(az, bz, _mm256_fmadd_ps(ay, by, _mm256_fmadd_ps(ax, bx, vd[g]))));
-      va[g] = _mm256_fmadd_ps(aw, aw, _mm256_fmadd_ps(az, az, _mm256_fmadd_ps(ay, ay, _mm256_fmadd_ps(ax, ax, va[g]))));
-      vb[g] = _mm256_fmadd_ps(bw, bw, _mm256_fmadd_ps(bz, bz, _mm256_fmadd_ps(by, by, _mm256_fmadd_ps(bx, bx, vb[g]))));
+      vd[0][g] = _mm256_fmadd_ps(az, bz, _mm256_fmadd_ps(ax, bx, vd[0][g]));
+      vd[1][g] = _mm256_fmadd_ps(aw, bw, _mm256_fmadd_ps(ay, by, vd[1][g]));
+      va[0][g] = _mm256_fmadd_ps(az, az, _mm256_fmadd_ps(ax, ax, va[0][g]));
+      va[1][g] = _mm256_fmadd_ps(aw, aw, _mm256_fmadd_ps(ay, ay, va[1][g]));
+      vb[0][g] = _mm256_fmadd_ps(bz, bz, _mm256_fmadd_ps(bx, bx, vb[0][g]));
+      vb[1][g] = _mm256_fmadd_ps(bw, bw, _mm256_fmadd_ps(by, by, vb[1][g]));
     }
   }
-  unpermute(vd, accd);
-  unpermute(va, acca);
-  unpermute(vb, accb);
-  for (; i < d; i++) {
-    int lane = (i >> 2) & 31;
-    accd[lane] = fmaf(a[i], b[i], accd[lane]);
-    acca[lane] = fmaf(a[i], a[i], acca[lane]);
-    accb[lane] = fmaf(b[i], b[i], accb[lane]);
+  for (int h = 0; h < 2; h++) {
+    unpermute(vd[h], accd[h]);
+    unpermute(va[h], acca[h]);
+    unpermute(vb[h], accb[h]);
   }
-  *dot = butterfly32(accd);
-  *na = butterfly32(acca);
-  *nb = butterfly32(accb);
+  for (; i < d; i++) {
+    int lane = (i >> 2) & 31, h = i & 1;
+    accd[h][lane] = fmaf(a[i], b[i], accd[h][lane]);
+    acca[h][lane] = fmaf(a[i], a[i], acca[h][lane]);
+    accb[h][lane] = fmaf(b[i], b[i], accb[h][lane]);
+  }
+  *dot = finish64(accd[0], accd[1]);
+  *na = finish64(acca[0], acca[1]);
+  *nb = finish64(accb[0], accb[1]);
 }
 
 /* ORA_FLAVOR_SEQUENTIAL: vek's portable Go loops (one accumulator, index order, no fusing). */

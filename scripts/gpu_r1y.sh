@@ -1,0 +1,5 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu_r1y.log 2>&1; echo "pytest rc=$?"; tail -4 gpurun_out/pytest_gpu_r1y.log
+timeout 900 python scripts/k1_variants.py 1000000 0,1,9,11,G16 10000,100000 > gpurun_out/k1_variants_r1y.log 2>&1
+cat gpurun_out/k1_variants_r1y.log

@@ -58,17 +58,19 @@ def test_distance_flavors_agree_within_tolerance(oracle):
 
 
 def test_canonical_order_definition(oracle):
-    """The canonical order written out in numpy float32: 32 chunk-strided fma chains + xor butterfly."""
+    """The canonical order written out in numpy float32: 32 chunk-strided pairs of fma chains (even: x, z of each
+    chunk; odd: y, w), even + odd, then the xor butterfly."""
     rng = np.random.default_rng(2)
     for d in (5, 128, 200, 768):
         a = rng.standard_normal(d).astype(np.float32)
         b = rng.standard_normal(d).astype(np.float32)
-        acc = [np.float32(0)] * 32
+        half = [[np.float32(0)] * 32, [np.float32(0)] * 32]
         for i in range(d):
             diff = np.float32(a[i] - b[i])
-            lane = (i >> 2) & 31
+            lane, h = (i >> 2) & 31, i & 1
             # fma in float64 is exact for float32 products, single rounding at the end
-            acc[lane] = np.float32(np.float64(diff) * np.float64(diff) + np.float64(acc[lane]))
+            half[h][lane] = np.float32(np.float64(diff) * np.float64(diff) + np.float64(half[h][lane]))
+        acc = [np.float32(half[0][i] + half[1][i]) for i in range(32)]
         for off in (16, 8, 4, 2, 1):
             acc = [np.float32(acc[i] + acc[i ^ off]) for i in range(32)]
         assert oracle.distance(oracle.EUCLIDEAN, a, b, oracle.CANONICAL) == np.sqrt(acc[0], dtype=np.float32)
