@@ -51,7 +51,7 @@ struct WaveParams {
   int32_t *ev_next;     // [n_slots * M]
   int32_t *rep_rec;     // [n_slots * M][2]: layer, row
   int32_t *staged;      // [n_slots * M][M + 1]: new list, then its degree
-  int *wave_ctr;        // [0] evictions recorded, [1] replenish work items, [2] waves committed
+  int *wave_ctr;        // [0] evictions recorded, [1] replenish work items, [2] waves committed, [4] NaN seen
   unsigned long long *counters;  // [8]: evals, expansions, nbr_reads, evict_evals, replenish_evals, evictions
   int *error;
   int rep_cap;          // replenish visited-table entries per warp (power of two)
@@ -88,6 +88,8 @@ __global__ void __launch_bounds__(WV_WARPS * 32) link_kernel(WaveParams p) {
     int32_t *lx = p.list(l, x);
     for (int t = lane; t < cnt; t += 32) {
       const int n = rows[t];
+      const float dn = p.slot_dists[slot * M + t];
+      if (dn != dn) p.wave_ctr[4] = 1;  // phase B then takes the literal, order-dependent path
       const long long kn = p.keys[n];
       int rank = 0;
       for (int u = 0; u < cnt; u++) rank += p.keys[rows[u]] < kn;  // keys are unique
@@ -120,71 +122,248 @@ __device__ __forceinline__ void warp_distances(const WaveParams &p, const int *i
 }
 
 // ---- phase B: one warp per (layer, target) that received requests ------------------------------------------------
+// graph.go:50-73 applied to target n for every request in input order: insert x; once the list holds m + 1 rows, drop
+// the one farthest from n (`d > worst || worst == nil` scanning in ascending key order, i.e. among equal maxima the
+// smallest key).  Two ways to get there:
+//   * target_sequential: literally that, request by request (any distances, NaN included);
+//   * target_select: when no distance involved is NaN the rule is a total order (farther first, then smaller key), and
+//     "insert, then drop the maximum" repeated over any sequence leaves exactly the m smallest of list U requests:
+//     the outcome does not depend on the order, so requests are streamed as they come off the inbox.  The distance
+//     of a new row x to n is the one its own search already produced (slot_dists; both metrics are symmetric bit for
+//     bit in the canonical order), so only the rows already in the list are evaluated, once per target.
+//   evict_evals still counts what the reference would evaluate (m + 1 per eviction).
+struct TargetSmem {
+  int *kid;          // [M + 4] list / kept rows
+  float *kd;         // [M + 4] their distance to the target
+  long long *kkey;   // [M + 4] their keys
+  int *bx;           // [32] batch of requests: new row, request id
+  int *br;           // [32]
+  float *bd;         // [32]
+  long long *bkey;   // [32]
+  __host__ __device__ static size_t bytes(int M) { return (size_t)(M + 4) * 16 + 32 * 24; }
+  __device__ TargetSmem(unsigned char *base, int M) {
+    kkey = reinterpret_cast<long long *>(base);
+    bkey = kkey + (M + 4);
+    kid = reinterpret_cast<int *>(bkey + 32);
+    kd = reinterpret_cast<float *>(kid + (M + 4));
+    bx = reinterpret_cast<int *>(kd + (M + 4));
+    br = bx + 32;
+    bd = reinterpret_cast<float *>(br + 32);
+  }
+};
+
+__device__ __forceinline__ void record_eviction(const WaveParams &p, int l, int n, int worst) {
+  const int e = atomicAdd(&p.wave_ctr[0], 1);
+  p.ev_rec[3 * e] = l;
+  p.ev_rec[3 * e + 1] = n;
+  p.ev_rec[3 * e + 2] = worst;
+  if (worst < p.first_row) {  // rows of this wave keep their own link and are not replenished (see oracle)
+    const long long sw = p.lslot(l, worst);
+    p.ev_next[e] = atomicExch(&p.ev_head[sw], e);
+    atomicMin(&p.ev_owner[sw], e);
+  }
+}
+
+template <int CH, int U>
+__device__ void target_sequential(const WaveParams &p, int l, int n, long long s, const TargetSmem &T,
+                                  unsigned long long &c_evict, unsigned long long &c_evictions, int lane) {
+  const int M = p.M, m = p.m;
+  int *tmp = T.kid;
+  float *td = T.kd;
+  int32_t *ln = p.list(l, n);
+  int deg = warp_load_list(ln, M, tmp, lane);
+  GQuery<CH> Q;
+  bool have_q = false;
+  int last = -1;
+  for (;;) {  // requests in ascending order (= input order of the new nodes)
+    int best = 0x7fffffff;
+    for (int r2 = p.in_head[s]; r2 >= 0; r2 = p.req_next[r2])
+      if (r2 > last && r2 < best) best = r2;
+    if (best == 0x7fffffff) break;
+    last = best;
+    const int x = p.slot_xrow[best / M];
+    deg = warp_sorted_insert(tmp, deg, x, p.keys, lane);  // graph.go:50
+    if (deg <= m) continue;                               // graph.go:51-53
+    if (!have_q) {
+      group_load_query<32, CH>(Q, reinterpret_cast<const float *>(p.vec + (size_t)n * p.row_chunks), true, p.dim,
+                               p.row_chunks, lane);
+      have_q = true;
+    }
+    warp_distances<CH, U>(p, tmp, deg, Q, p.metric, td, lane);  // graph.go:60-63: dist(neighbor.Value, n.Value)
+    c_evict += deg;
+    int wpos = 0;
+    if (lane == 0) {  // graph.go:64-71 in ascending key order: `d > worst || worst == nil`
+      float wd = td[0];
+      for (int i = 1; i < deg; i++)
+        if (td[i] > wd) {
+          wd = td[i];
+          wpos = i;
+        }
+    }
+    wpos = __shfl_sync(FULL, wpos, 0);
+    const int worst = tmp[wpos];
+    __syncwarp();
+    deg = warp_list_remove(tmp, deg, worst, lane);  // graph.go:73
+    c_evictions++;
+    if (lane == 0) record_eviction(p, l, n, worst);
+  }
+  warp_store_list(ln, M, tmp, deg, lane);
+}
+
+// position of the row to drop next among T.k*[0..deg): farthest, then smallest key (uniform over the warp)
+__device__ __forceinline__ int kept_worst(const TargetSmem &T, int deg, int lane) {
+  float wd = -__int_as_float(0x7f800000);
+  long long wk = 0x7fffffffffffffffLL;
+  int wp = -1;
+  for (int i = lane; i < deg; i += 32) {
+    const float d = T.kd[i];
+    const long long k = T.kkey[i];
+    if (wp < 0 || d > wd || (d == wd && k < wk)) {
+      wd = d;
+      wk = k;
+      wp = i;
+    }
+  }
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+    const float od = __shfl_xor_sync(FULL, wd, off);
+    const long long ok = __shfl_xor_sync(FULL, wk, off);
+    const int op = __shfl_xor_sync(FULL, wp, off);
+    if (op >= 0 && (wp < 0 || od > wd || (od == wd && ok < wk))) {
+      wd = od;
+      wk = ok;
+      wp = op;
+    }
+  }
+  return wp;
+}
+
+template <int CH, int U>
+__device__ void target_select(const WaveParams &p, int l, int n, long long s, const TargetSmem &T,
+                              unsigned long long &c_evict, unsigned long long &c_evictions, int lane) {
+  const int M = p.M, m = p.m;
+  int32_t *ln = p.list(l, n);
+  const int deg0 = warp_load_list(ln, M, T.kid, lane);
+  int deg = deg0;
+  bool have = false;  // distances and keys of the kept rows are known, wpos is valid
+  int wpos = -1;
+  int cur = p.in_head[s];
+  while (cur >= 0) {
+    // ---- next batch of requests off the inbox: lane 0 follows the links, all lanes fetch the payloads --------------
+    int nb = 0;
+    if (lane == 0) {
+      while (cur >= 0 && nb < 32) {
+        T.br[nb++] = cur;
+        cur = p.req_next[cur];
+      }
+    }
+    nb = __shfl_sync(FULL, nb, 0);
+    cur = __shfl_sync(FULL, cur, 0);
+    __syncwarp();
+    if (lane < nb) {
+      const int r2 = T.br[lane];
+      const int x = p.slot_xrow[r2 / M];
+      T.bx[lane] = x;
+      T.bd[lane] = p.slot_dists[r2];  // d(x, n) from x's own search == dist(x.Value, n.Value), graph.go:60-63
+      T.bkey[lane] = p.keys[x];
+    }
+    __syncwarp();
+    for (int i = 0; i < nb; i++) {
+      const int x = T.bx[i];
+      const float dx = T.bd[i];
+      const long long kx = T.bkey[i];
+      if (deg < m) {  // graph.go:51-53: room left
+        if (lane == 0) {
+          T.kid[deg] = x;
+          T.kd[deg] = dx;
+          T.kkey[deg] = kx;
+        }
+        deg++;
+        __syncwarp();
+        if (have) wpos = kept_worst(T, deg, lane);
+        continue;
+      }
+      if (!have) {  // first overflow: distances of the rows that were in the list before the wave, keys of all
+        if (deg0 > 0) {
+          GQuery<CH> Q;
+          group_load_query<32, CH>(Q, reinterpret_cast<const float *>(p.vec + (size_t)n * p.row_chunks), true, p.dim,
+                                   p.row_chunks, lane);
+          warp_distances<CH, U>(p, T.kid, deg0, Q, p.metric, T.kd, lane);
+        }
+        bool nan = false;
+        for (int j = lane; j < deg; j += 32) {
+          if (j < deg0) T.kkey[j] = p.keys[T.kid[j]];
+          nan = nan || (T.kd[j] != T.kd[j]);
+        }
+        __syncwarp();
+        if (__any_sync(FULL, nan)) {  // not a total order: nothing has been recorded yet, do it the literal way
+          target_sequential<CH, U>(p, l, n, s, T, c_evict, c_evictions, lane);
+          return;
+        }
+        wpos = kept_worst(T, deg, lane);
+        have = true;
+      }
+      // the list would hold m + 1 rows: drop the maximum of kept U {x}
+      const float wd = T.kd[wpos];
+      const long long wk = T.kkey[wpos];
+      int out;
+      if (dx > wd || (dx == wd && kx < wk)) {
+        out = x;  // the newcomer itself
+      } else {
+        out = T.kid[wpos];
+        __syncwarp();
+        if (lane == 0) {
+          T.kid[wpos] = x;
+          T.kd[wpos] = dx;
+          T.kkey[wpos] = kx;
+        }
+        __syncwarp();
+        wpos = kept_worst(T, deg, lane);
+      }
+      c_evict += m + 1;
+      c_evictions++;
+      if (lane == 0) record_eviction(p, l, n, out);
+    }
+    __syncwarp();
+  }
+  // ---- the kept rows in key order --------------------------------------------------------------------------------------
+  if (!have)
+    for (int j = lane; j < deg0; j += 32) T.kkey[j] = p.keys[T.kid[j]];
+  __syncwarp();
+  int mine[2], rank[2];
+  int cnt = 0;
+  for (int j = lane; j < deg; j += 32) {
+    const long long kj = T.kkey[j];
+    int rk = 0;
+    for (int u = 0; u < deg; u++) rk += T.kkey[u] < kj;  // keys are unique
+    mine[cnt] = T.kid[j];
+    rank[cnt++] = rk;
+  }
+  __syncwarp();
+  for (int c = 0; c < cnt; c++) ln[rank[c]] = mine[c];
+  for (int j = deg + lane; j < M; j += 32) ln[j] = -1;
+}
+
 template <int CH, int U>
 __global__ void __launch_bounds__(WV_WARPS * 32) targets_kernel(WaveParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int M = p.M, m = p.m;
-  int *tmp = reinterpret_cast<int *>(smem) + (size_t)warp * 2 * (M + 4);
-  float *td = reinterpret_cast<float *>(tmp + (M + 4));
+  const int M = p.M;
+  const TargetSmem T(smem + TargetSmem::bytes(M) * warp, M);
   const long long slot = (long long)blockIdx.x * WV_WARPS + warp;
   if (*p.error || slot >= p.n_slots) return;
   const int cnt = p.slot_cnt[slot];
   const int l = p.slot_layer[slot];
+  const bool any_nan = p.wave_ctr[4] != 0;  // some search of this wave returned a NaN distance (link_kernel)
   unsigned long long c_evict = 0, c_evictions = 0;
   for (int t = 0; t < cnt; t++) {
     const int n = p.slot_rows[slot * M + t];
     const long long s = p.lslot(l, n);
     const int r = (int)(slot * M + t);
     if (p.in_owner[s] != r) continue;  // another warp owns this target (warp-uniform)
-    int32_t *ln = p.list(l, n);
-    int deg = warp_load_list(ln, M, tmp, lane);
-    GQuery<CH> Q;
-    bool have_q = false;
-    int last = -1;
-    for (;;) {  // requests in ascending order (= input order of the new nodes)
-      int best = 0x7fffffff;
-      for (int r2 = p.in_head[s]; r2 >= 0; r2 = p.req_next[r2])
-        if (r2 > last && r2 < best) best = r2;
-      if (best == 0x7fffffff) break;
-      last = best;
-      const int x = p.slot_xrow[best / M];
-      deg = warp_sorted_insert(tmp, deg, x, p.keys, lane);  // graph.go:50
-      if (deg <= m) continue;                               // graph.go:51-53
-      if (!have_q) {
-        group_load_query<32, CH>(Q, reinterpret_cast<const float *>(p.vec + (size_t)n * p.row_chunks), true, p.dim,
-                                 p.row_chunks, lane);
-        have_q = true;
-      }
-      warp_distances<CH, U>(p, tmp, deg, Q, p.metric, td, lane);  // graph.go:60-63: dist(neighbor.Value, n.Value)
-      c_evict += deg;
-      int wpos = 0;
-      if (lane == 0) {  // graph.go:64-71 in ascending key order: `d > worst || worst == nil`
-        float wd = td[0];
-        for (int i = 1; i < deg; i++)
-          if (td[i] > wd) {
-            wd = td[i];
-            wpos = i;
-          }
-      }
-      wpos = __shfl_sync(FULL, wpos, 0);
-      const int worst = tmp[wpos];
-      __syncwarp();
-      deg = warp_list_remove(tmp, deg, worst, lane);  // graph.go:73
-      c_evictions++;
-      if (lane == 0) {
-        const int e = atomicAdd(&p.wave_ctr[0], 1);
-        p.ev_rec[3 * e] = l;
-        p.ev_rec[3 * e + 1] = n;
-        p.ev_rec[3 * e + 2] = worst;
-        if (worst < p.first_row) {  // rows of this wave keep their own link and are not replenished (see oracle)
-          const long long sw = p.lslot(l, worst);
-          p.ev_next[e] = atomicExch(&p.ev_head[sw], e);
-          atomicMin(&p.ev_owner[sw], e);
-        }
-      }
-    }
-    warp_store_list(ln, M, tmp, deg, lane);
+    if (any_nan) target_sequential<CH, U>(p, l, n, s, T, c_evict, c_evictions, lane);
+    else target_select<CH, U>(p, l, n, s, T, c_evict, c_evictions, lane);
+    __syncwarp();
     if (lane == 0) {
       p.in_head[s] = -1;
       p.in_owner[s] = 0x7fffffff;
@@ -385,7 +564,10 @@ __global__ void __launch_bounds__(WV_WARPS * 32) scatter_kernel(WaveParams p) {
     const int32_t *st = p.staged + (size_t)idx * (p.M + 1);
     for (int i = lane; i < p.M; i += 32) lw[i] = st[i];
   }
-  if (blockIdx.x == 0 && threadIdx.x == 0) p.wave_ctr[2]++;
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    p.wave_ctr[2]++;
+    p.wave_ctr[4] = 0;
+  }
 }
 
 
@@ -419,8 +601,7 @@ static int launch_commit(b200hnsw *h, WaveParams &p, cudaStream_t s) {
   const int blocks_nodes = (p.w + WV_WARPS - 1) / WV_WARPS;
   const int blocks_slots = (int)((p.n_slots + WV_WARPS - 1) / WV_WARPS);
   link_kernel<<<blocks_nodes, WV_WARPS * 32, 0, s>>>(p);
-  size_t sm_t = (size_t)WV_WARPS * 2 * (M + 4) * 4;
-  targets_kernel<CH, U><<<blocks_slots, WV_WARPS * 32, sm_t, s>>>(p);
+  targets_kernel<CH, U><<<blocks_slots, WV_WARPS * 32, TargetSmem::bytes(M) * WV_WARPS, s>>>(p);
   // evictions <= requests; the grids below stride over the device-side counts
   long long max_items = p.n_slots * M;
   int grid_e = (int)std::min<long long>((max_items + WV_WARPS - 1) / WV_WARPS, (long long)h->sm_count * 8);
