@@ -133,9 +133,9 @@ int b200hnsw::ensure_inboxes(cudaStream_t s) {
   d.inbox = nullptr;
   d.inbox_n = 0;
   B200_CUDA(cudaMalloc(&d.inbox, sizeof(int32_t) * 4 * (size_t)want));
-  // heads = -1 (empty list), owners = 0x7f7f7f7f (larger than any request id)
-  B200_CUDA(cudaMemsetAsync(d.inbox, 0xff, sizeof(int32_t) * (size_t)want, s));
-  B200_CUDA(cudaMemsetAsync(d.inbox + want, 0x7f, sizeof(int32_t) * (size_t)want, s));
+  // request counts = 0 (their segment bases need no initial value); eviction heads = -1 (empty list), owners =
+  // 0x7f7f7f7f (larger than any record id)
+  B200_CUDA(cudaMemsetAsync(d.inbox, 0, sizeof(int32_t) * 2 * (size_t)want, s));
   B200_CUDA(cudaMemsetAsync(d.inbox + 2 * want, 0xff, sizeof(int32_t) * (size_t)want, s));
   B200_CUDA(cudaMemsetAsync(d.inbox + 3 * want, 0x7f, sizeof(int32_t) * (size_t)want, s));
   d.inbox_n = want;

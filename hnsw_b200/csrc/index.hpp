@@ -48,7 +48,7 @@ struct DeviceGraph {
   int32_t *upper_off = nullptr; // [cap]
   int32_t *adjU = nullptr;      // [capU][M]
   int64_t cap = 0, capU = 0;
-  int32_t *inbox = nullptr;     // 4 x inbox_n: request heads/owners and eviction heads/owners per list slot (wave Add)
+  int32_t *inbox = nullptr;     // 4 x inbox_n: request counts/segments and eviction heads/owners per list slot (wave Add)
   int64_t inbox_n = 0;
 };
 

@@ -12,8 +12,10 @@
 //   phase D  : replenish_kernel-- per evicted node short of M links: neighbours of neighbours scored with
 //              CosineDistance (graph.go:172-219), staged
 //   phase E  : scatter_kernel  -- staged lists replace the old ones
-// Work is grouped per target with lock-free inboxes (atomicExch linked lists + atomicMin owner election); the owner
-// processes its inbox in ascending request order, so the result does not depend on scheduling.
+// Requests are grouped per target without sorting: link_kernel counts them (atomicAdd per list slot), group_kernel
+// gives every target a contiguous segment of the request arena and drops each request into its place; the warp holding
+// a target's first-counted request owns the target.  Evicted rows are grouped per row the same way they were before
+// (atomicExch linked lists + atomicMin owner election).  No result depends on the scheduling (see phase B).
 // Bound: HBM gather (search + eviction scans + replenish rows), counted in the same counters as the oracle's.
 #include <algorithm>
 #include <cstring>
@@ -35,7 +37,7 @@ struct WaveParams {
   int32_t row_chunks, M, dim;
   long long cap;  // list slot of (row, 0) = row; of (row, l > 0) = cap + upper_off[row] + l - 1
   // inboxes, one entry per list slot
-  int32_t *in_head, *in_owner, *ev_head, *ev_owner;
+  int32_t *in_cnt, *in_base, *ev_head, *ev_owner;  // requests per slot / their arena segment; eviction lists
   // this wave
   int first_row, w, m, metric;
   const int32_t *levels;      // [w]
@@ -46,12 +48,14 @@ struct WaveParams {
   float *slot_dists;    // [n_slots][M]
   int32_t *slot_xrow;   // [n_slots] new row of the slot
   int32_t *slot_layer;  // [n_slots]
-  int32_t *req_next;    // [n_slots * M]
+  int32_t *req_pos;     // [n_slots * M] position of the request inside its target's segment
+  int32_t *req_arena;   // [n_slots * M] request ids grouped by target
   int32_t *ev_rec;      // [n_slots * M][3]: layer, n, worst
   int32_t *ev_next;     // [n_slots * M]
   int32_t *rep_rec;     // [n_slots * M][2]: layer, row
   int32_t *staged;      // [n_slots * M][M + 1]: new list, then its degree
-  int *wave_ctr;        // [0] evictions recorded, [1] replenish work items, [2] waves committed, [4] NaN seen
+  int *wave_ctr;        // [0] evictions recorded, [1] replenish work items, [2] waves committed, [3] arena fill,
+                        // [4] NaN seen
   unsigned long long *counters;  // [8]: evals, expansions, nbr_reads, evict_evals, replenish_evals, evictions
   int *error;
   int rep_cap;          // replenish visited-table entries per warp (power of two)
@@ -72,6 +76,7 @@ __global__ void __launch_bounds__(WV_WARPS * 32) link_kernel(WaveParams p) {
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     p.wave_ctr[0] = 0;
     p.wave_ctr[1] = 0;
+    p.wave_ctr[3] = 0;
   }
   if (*p.error || j >= p.w) return;
   const int x = p.first_row + j;
@@ -96,9 +101,23 @@ __global__ void __launch_bounds__(WV_WARPS * 32) link_kernel(WaveParams p) {
       lx[rank] = n;  // graph.go:519: newNode.addNeighbor(n), lists kept in key order
       const int r = (int)(slot * M + t);  // requests are ordered by (node, layer, position)
       const long long s = p.lslot(l, n);
-      p.req_next[r] = atomicExch(&p.in_head[s], r);
-      atomicMin(&p.in_owner[s], r);
+      p.req_pos[r] = atomicAdd(&p.in_cnt[s], 1);
     }
+  }
+}
+
+// ---- requests grouped by target: one thread per request, two passes (segment allocation, placement) ------------------
+__global__ void group_kernel(WaveParams p, int pass) {
+  const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (*p.error || r >= p.n_slots * p.M) return;
+  const long long slot = r / p.M;
+  if ((int)(r - slot * p.M) >= p.slot_cnt[slot]) return;
+  const long long s = p.lslot(p.slot_layer[slot], p.slot_rows[r]);
+  const int pos = p.req_pos[r];
+  if (pass == 0) {
+    if (pos == 0) p.in_base[s] = atomicAdd(&p.wave_ctr[3], p.in_cnt[s]);
+  } else {
+    p.req_arena[p.in_base[s] + pos] = (int)r;
   }
 }
 
@@ -136,32 +155,33 @@ struct TargetSmem {
   int *kid;          // [M + 4] list / kept rows
   float *kd;         // [M + 4] their distance to the target
   long long *kkey;   // [M + 4] their keys
-  int *bx;           // [32] batch of requests: new row, request id
-  int *br;           // [32]
-  float *bd;         // [32]
-  long long *bkey;   // [32]
-  __host__ __device__ static size_t bytes(int M) { return (size_t)(M + 4) * 16 + 32 * 24; }
+  int *ebuf;         // [64] rows evicted, not yet recorded
+  __host__ __device__ static size_t bytes(int M) { return (size_t)(M + 4) * 16 + 64 * 4; }
   __device__ TargetSmem(unsigned char *base, int M) {
     kkey = reinterpret_cast<long long *>(base);
-    bkey = kkey + (M + 4);
-    kid = reinterpret_cast<int *>(bkey + 32);
+    kid = reinterpret_cast<int *>(kkey + (M + 4));
     kd = reinterpret_cast<float *>(kid + (M + 4));
-    bx = reinterpret_cast<int *>(kd + (M + 4));
-    br = bx + 32;
-    bd = reinterpret_cast<float *>(br + 32);
+    ebuf = reinterpret_cast<int *>(kd + (M + 4));
   }
 };
 
-__device__ __forceinline__ void record_eviction(const WaveParams &p, int l, int n, int worst) {
-  const int e = atomicAdd(&p.wave_ctr[0], 1);
-  p.ev_rec[3 * e] = l;
-  p.ev_rec[3 * e + 1] = n;
-  p.ev_rec[3 * e + 2] = worst;
-  if (worst < p.first_row) {  // rows of this wave keep their own link and are not replenished (see oracle)
-    const long long sw = p.lslot(l, worst);
-    p.ev_next[e] = atomicExch(&p.ev_head[sw], e);
-    atomicMin(&p.ev_owner[sw], e);
+// rows ev[0..cnt) were dropped by target (l, n): one record each, grouped per dropped row for phase C
+__device__ __forceinline__ void record_evictions(const WaveParams &p, int l, int n, const int *ev, int cnt, int lane) {
+  int e0 = 0;
+  if (lane == 0) e0 = atomicAdd(&p.wave_ctr[0], cnt);
+  e0 = __shfl_sync(FULL, e0, 0);
+  for (int j = lane; j < cnt; j += 32) {
+    const int e = e0 + j, worst = ev[j];
+    p.ev_rec[3 * e] = l;
+    p.ev_rec[3 * e + 1] = n;
+    p.ev_rec[3 * e + 2] = worst;
+    if (worst < p.first_row) {  // rows of this wave keep their own link and are not replenished (see oracle)
+      const long long sw = p.lslot(l, worst);
+      p.ev_next[e] = atomicExch(&p.ev_head[sw], e);
+      atomicMin(&p.ev_owner[sw], e);
+    }
   }
+  __syncwarp();
 }
 
 template <int CH, int U>
@@ -172,14 +192,19 @@ __device__ void target_sequential(const WaveParams &p, int l, int n, long long s
   float *td = T.kd;
   int32_t *ln = p.list(l, n);
   int deg = warp_load_list(ln, M, tmp, lane);
+  const int r = p.in_cnt[s];
+  const int32_t *seg = p.req_arena + p.in_base[s];
   GQuery<CH> Q;
   bool have_q = false;
   int last = -1;
-  for (;;) {  // requests in ascending order (= input order of the new nodes)
+  for (int it = 0; it < r; it++) {  // requests in ascending order (= input order of the new nodes)
     int best = 0x7fffffff;
-    for (int r2 = p.in_head[s]; r2 >= 0; r2 = p.req_next[r2])
+    for (int i = lane; i < r; i += 32) {
+      const int r2 = seg[i];
       if (r2 > last && r2 < best) best = r2;
-    if (best == 0x7fffffff) break;
+    }
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) best = min(best, __shfl_xor_sync(FULL, best, off));
     last = best;
     const int x = p.slot_xrow[best / M];
     deg = warp_sorted_insert(tmp, deg, x, p.keys, lane);  // graph.go:50
@@ -205,15 +230,17 @@ __device__ void target_sequential(const WaveParams &p, int l, int n, long long s
     __syncwarp();
     deg = warp_list_remove(tmp, deg, worst, lane);  // graph.go:73
     c_evictions++;
-    if (lane == 0) record_eviction(p, l, n, worst);
+    if (lane == 0) T.ebuf[0] = worst;
+    __syncwarp();
+    record_evictions(p, l, n, T.ebuf, 1, lane);
   }
   warp_store_list(ln, M, tmp, deg, lane);
 }
 
 // position of the row to drop next among T.k*[0..deg): farthest, then smallest key (uniform over the warp)
 __device__ __forceinline__ int kept_worst(const TargetSmem &T, int deg, int lane) {
-  float wd = -__int_as_float(0x7f800000);
-  long long wk = 0x7fffffffffffffffLL;
+  float wd = 0.f;
+  long long wk = 0;
   int wp = -1;
   for (int i = lane; i < deg; i += 32) {
     const float d = T.kd[i];
@@ -238,98 +265,8 @@ __device__ __forceinline__ int kept_worst(const TargetSmem &T, int deg, int lane
   return wp;
 }
 
-template <int CH, int U>
-__device__ void target_select(const WaveParams &p, int l, int n, long long s, const TargetSmem &T,
-                              unsigned long long &c_evict, unsigned long long &c_evictions, int lane) {
-  const int M = p.M, m = p.m;
-  int32_t *ln = p.list(l, n);
-  const int deg0 = warp_load_list(ln, M, T.kid, lane);
-  int deg = deg0;
-  bool have = false;  // distances and keys of the kept rows are known, wpos is valid
-  int wpos = -1;
-  int cur = p.in_head[s];
-  while (cur >= 0) {
-    // ---- next batch of requests off the inbox: lane 0 follows the links, all lanes fetch the payloads --------------
-    int nb = 0;
-    if (lane == 0) {
-      while (cur >= 0 && nb < 32) {
-        T.br[nb++] = cur;
-        cur = p.req_next[cur];
-      }
-    }
-    nb = __shfl_sync(FULL, nb, 0);
-    cur = __shfl_sync(FULL, cur, 0);
-    __syncwarp();
-    if (lane < nb) {
-      const int r2 = T.br[lane];
-      const int x = p.slot_xrow[r2 / M];
-      T.bx[lane] = x;
-      T.bd[lane] = p.slot_dists[r2];  // d(x, n) from x's own search == dist(x.Value, n.Value), graph.go:60-63
-      T.bkey[lane] = p.keys[x];
-    }
-    __syncwarp();
-    for (int i = 0; i < nb; i++) {
-      const int x = T.bx[i];
-      const float dx = T.bd[i];
-      const long long kx = T.bkey[i];
-      if (deg < m) {  // graph.go:51-53: room left
-        if (lane == 0) {
-          T.kid[deg] = x;
-          T.kd[deg] = dx;
-          T.kkey[deg] = kx;
-        }
-        deg++;
-        __syncwarp();
-        if (have) wpos = kept_worst(T, deg, lane);
-        continue;
-      }
-      if (!have) {  // first overflow: distances of the rows that were in the list before the wave, keys of all
-        if (deg0 > 0) {
-          GQuery<CH> Q;
-          group_load_query<32, CH>(Q, reinterpret_cast<const float *>(p.vec + (size_t)n * p.row_chunks), true, p.dim,
-                                   p.row_chunks, lane);
-          warp_distances<CH, U>(p, T.kid, deg0, Q, p.metric, T.kd, lane);
-        }
-        bool nan = false;
-        for (int j = lane; j < deg; j += 32) {
-          if (j < deg0) T.kkey[j] = p.keys[T.kid[j]];
-          nan = nan || (T.kd[j] != T.kd[j]);
-        }
-        __syncwarp();
-        if (__any_sync(FULL, nan)) {  // not a total order: nothing has been recorded yet, do it the literal way
-          target_sequential<CH, U>(p, l, n, s, T, c_evict, c_evictions, lane);
-          return;
-        }
-        wpos = kept_worst(T, deg, lane);
-        have = true;
-      }
-      // the list would hold m + 1 rows: drop the maximum of kept U {x}
-      const float wd = T.kd[wpos];
-      const long long wk = T.kkey[wpos];
-      int out;
-      if (dx > wd || (dx == wd && kx < wk)) {
-        out = x;  // the newcomer itself
-      } else {
-        out = T.kid[wpos];
-        __syncwarp();
-        if (lane == 0) {
-          T.kid[wpos] = x;
-          T.kd[wpos] = dx;
-          T.kkey[wpos] = kx;
-        }
-        __syncwarp();
-        wpos = kept_worst(T, deg, lane);
-      }
-      c_evict += m + 1;
-      c_evictions++;
-      if (lane == 0) record_eviction(p, l, n, out);
-    }
-    __syncwarp();
-  }
-  // ---- the kept rows in key order --------------------------------------------------------------------------------------
-  if (!have)
-    for (int j = lane; j < deg0; j += 32) T.kkey[j] = p.keys[T.kid[j]];
-  __syncwarp();
+// T.kid[0..deg) with keys T.kkey -> the list in key order, -1 padded
+__device__ __forceinline__ void store_by_key(const TargetSmem &T, int32_t *ln, int deg, int M, int lane) {
   int mine[2], rank[2];
   int cnt = 0;
   for (int j = lane; j < deg; j += 32) {
@@ -345,6 +282,104 @@ __device__ void target_select(const WaveParams &p, int l, int n, long long s, co
 }
 
 template <int CH, int U>
+__device__ void target_select(const WaveParams &p, int l, int n, long long s, const TargetSmem &T,
+                              unsigned long long &c_evict, unsigned long long &c_evictions, int lane) {
+  const int M = p.M, m = p.m;
+  int32_t *ln = p.list(l, n);
+  const int deg0 = warp_load_list(ln, M, T.kid, lane);
+  const int r = p.in_cnt[s];
+  const int32_t *seg = p.req_arena + p.in_base[s];
+  for (int j = lane; j < deg0; j += 32) T.kkey[j] = p.keys[T.kid[j]];
+  if (deg0 + r <= m) {  // graph.go:51-53: room for everybody, no distance needed
+    for (int i = lane; i < r; i += 32) {
+      const int x = p.slot_xrow[seg[i] / M];
+      T.kid[deg0 + i] = x;
+      T.kkey[deg0 + i] = p.keys[x];
+    }
+    __syncwarp();
+    store_by_key(T, ln, deg0 + r, M, lane);
+    return;
+  }
+  if (deg0 > 0) {  // the rows that were in the list before the wave: their distance to n, once
+    GQuery<CH> Q;
+    group_load_query<32, CH>(Q, reinterpret_cast<const float *>(p.vec + (size_t)n * p.row_chunks), true, p.dim,
+                             p.row_chunks, lane);
+    warp_distances<CH, U>(p, T.kid, deg0, Q, p.metric, T.kd, lane);
+    bool nan = false;
+    for (int j = lane; j < deg0; j += 32) nan = nan || (T.kd[j] != T.kd[j]);
+    if (__any_sync(FULL, nan)) {  // not a total order: nothing has been recorded yet, do it the literal way
+      target_sequential<CH, U>(p, l, n, s, T, c_evict, c_evictions, lane);
+      return;
+    }
+  }
+  int deg = deg0, wpos = -1, nev = 0;
+  for (int b0 = 0; b0 < r; b0 += 32) {
+    bool pending = b0 + lane < r;
+    int x = -1;
+    float dx = 0.f;
+    long long kx = 0;
+    if (pending) {
+      const int r2 = seg[b0 + lane];
+      x = p.slot_xrow[r2 / M];
+      dx = p.slot_dists[r2];  // d(x, n) from x's own search == dist(x.Value, n.Value), graph.go:60-63
+      kx = p.keys[x];
+    }
+    for (;;) {
+      unsigned mask;
+      if (deg < m) {
+        mask = __ballot_sync(FULL, pending);  // room left: anybody
+      } else {
+        if (wpos < 0) wpos = kept_worst(T, deg, lane);
+        const float wd = T.kd[wpos];
+        const long long wk = T.kkey[wpos];
+        mask = __ballot_sync(FULL, pending && !(dx > wd || (dx == wd && kx < wk)));  // beats the row to drop
+      }
+      if (!mask) break;
+      const int i = __ffs(mask) - 1;
+      const int xi = __shfl_sync(FULL, x, i);
+      const float di = __shfl_sync(FULL, dx, i);
+      const long long ki = __shfl_sync(FULL, kx, i);
+      const int at = deg < m ? deg : wpos;
+      __syncwarp();
+      if (lane == 0) {
+        if (deg >= m) T.ebuf[nev] = T.kid[at];
+        T.kid[at] = xi;
+        T.kd[at] = di;
+        T.kkey[at] = ki;
+      }
+      if (deg < m) deg++;
+      else nev++;
+      wpos = -1;
+      if (lane == i) pending = false;
+      __syncwarp();
+      if (nev >= 32) {
+        record_evictions(p, l, n, T.ebuf, nev, lane);
+        c_evictions += nev;
+        c_evict += (unsigned long long)nev * (m + 1);  // what graph.go:60-63 evaluates per eviction
+        nev = 0;
+      }
+    }
+    // whoever is still pending is farther than every kept row: dropped on arrival
+    const unsigned rej = __ballot_sync(FULL, pending);
+    if (pending) T.ebuf[nev + __popc(rej & ((1u << lane) - 1u))] = x;
+    nev += __popc(rej);
+    __syncwarp();
+    if (nev >= 32) {
+      record_evictions(p, l, n, T.ebuf, nev, lane);
+      c_evictions += nev;
+      c_evict += (unsigned long long)nev * (m + 1);
+      nev = 0;
+    }
+  }
+  if (nev > 0) {
+    record_evictions(p, l, n, T.ebuf, nev, lane);
+    c_evictions += nev;
+    c_evict += (unsigned long long)nev * (m + 1);
+  }
+  store_by_key(T, ln, deg, M, lane);
+}
+
+template <int CH, int U>
 __global__ void __launch_bounds__(WV_WARPS * 32) targets_kernel(WaveParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -357,17 +392,14 @@ __global__ void __launch_bounds__(WV_WARPS * 32) targets_kernel(WaveParams p) {
   const bool any_nan = p.wave_ctr[4] != 0;  // some search of this wave returned a NaN distance (link_kernel)
   unsigned long long c_evict = 0, c_evictions = 0;
   for (int t = 0; t < cnt; t++) {
-    const int n = p.slot_rows[slot * M + t];
+    const long long r = slot * M + t;
+    if (p.req_pos[r] != 0) continue;  // another warp owns this target (warp-uniform)
+    const int n = p.slot_rows[r];
     const long long s = p.lslot(l, n);
-    const int r = (int)(slot * M + t);
-    if (p.in_owner[s] != r) continue;  // another warp owns this target (warp-uniform)
     if (any_nan) target_sequential<CH, U>(p, l, n, s, T, c_evict, c_evictions, lane);
     else target_select<CH, U>(p, l, n, s, T, c_evict, c_evictions, lane);
     __syncwarp();
-    if (lane == 0) {
-      p.in_head[s] = -1;
-      p.in_owner[s] = 0x7fffffff;
-    }
+    if (lane == 0) p.in_cnt[s] = 0;
     __syncwarp();
   }
   if (lane == 0) {
@@ -601,6 +633,9 @@ static int launch_commit(b200hnsw *h, WaveParams &p, cudaStream_t s) {
   const int blocks_nodes = (p.w + WV_WARPS - 1) / WV_WARPS;
   const int blocks_slots = (int)((p.n_slots + WV_WARPS - 1) / WV_WARPS);
   link_kernel<<<blocks_nodes, WV_WARPS * 32, 0, s>>>(p);
+  const int blocks_req = (int)((p.n_slots * M + 255) / 256);
+  group_kernel<<<blocks_req, 256, 0, s>>>(p, 0);
+  group_kernel<<<blocks_req, 256, 0, s>>>(p, 1);
   targets_kernel<CH, U><<<blocks_slots, WV_WARPS * 32, TargetSmem::bytes(M) * WV_WARPS, s>>>(p);
   // evictions <= requests; the grids below stride over the device-side counts
   long long max_items = p.n_slots * M;
@@ -729,7 +764,7 @@ extern "C" int b200hnsw_add_batch_waves(b200hnsw_t *h, const float *vectors, con
   // ---- device scratch ------------------------------------------------------------------------------------------------
   auto al = [](size_t v) { return (v + 255) & ~(size_t)255; };
   const size_t items = (size_t)max_slots * M;
-  size_t need = al(4 * (size_t)n) + al(8 * (size_t)n) + al(4 * (size_t)max_slots) * 3 + al(4 * items) * 4 +
+  size_t need = al(4 * (size_t)n) + al(8 * (size_t)n) + al(4 * (size_t)max_slots) * 3 + al(4 * items) * 5 +
                 al(12 * items) + al(8 * items) + al(4 * items * (M + 1)) + 1024;
   if ((rc = c->reserve_device(need))) return fail(rc);
   char *sp = (char *)c->d_scratch;
@@ -746,7 +781,8 @@ extern "C" int b200hnsw_add_batch_waves(b200hnsw_t *h, const float *vectors, con
   p.slot_layer = (int32_t *)carve(4 * (size_t)max_slots);
   p.slot_rows = (int32_t *)carve(4 * items);
   p.slot_dists = (float *)carve(4 * items);
-  p.req_next = (int32_t *)carve(4 * items);
+  p.req_pos = (int32_t *)carve(4 * items);
+  p.req_arena = (int32_t *)carve(4 * items);
   p.ev_next = (int32_t *)carve(4 * items);
   p.ev_rec = (int32_t *)carve(12 * items);
   p.rep_rec = (int32_t *)carve(8 * items);
@@ -776,8 +812,8 @@ extern "C" int b200hnsw_add_batch_waves(b200hnsw_t *h, const float *vectors, con
   p.M = M;
   p.dim = dim;
   p.cap = h->d.cap;
-  p.in_head = h->d.inbox;
-  p.in_owner = h->d.inbox + h->d.inbox_n;
+  p.in_cnt = h->d.inbox;
+  p.in_base = h->d.inbox + h->d.inbox_n;
   p.ev_head = h->d.inbox + 2 * h->d.inbox_n;
   p.ev_owner = h->d.inbox + 3 * h->d.inbox_n;
   p.m = m;
@@ -822,7 +858,7 @@ extern "C" int b200hnsw_add_batch_waves(b200hnsw_t *h, const float *vectors, con
     p.slot_off = d_slot_rel + wv.start;
     p.n_slots = wv.n_slots;
     if ((rc = launch_commit_any(h, p, s))) return fail(rc);
-    launches += 6;
+    launches += 8;
     kernel_waves++;
   }
   unsigned long long ctr[8];

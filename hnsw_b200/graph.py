@@ -150,9 +150,9 @@ class Graph:
             grown[:n0] = self._vecs[:n0]
             self._vecs = grown
         self._vecs[n0:need] = vecs
-        for i, k in enumerate(keys):
-            self._row_of[k] = n0 + i
-            self._keys.append(k)
+        keys = list(keys)
+        self._row_of.update(zip(keys, range(n0, need)))
+        self._keys.extend(keys)
 
     def _draw_levels(self, n: int) -> np.ndarray:
         """randomLevel() for n consecutive insertions: the bound maxLevel(Ml, len(layer0)) grows as nodes land."""
@@ -211,7 +211,7 @@ class Graph:
                                                      K.ctypes.data_as(_lib.i64p), lv.ctypes.data_as(_lib.i32p),
                                                      len(K), self.M, self.EfSearch, metric, C.byref(st)))
         self.last_stats = st.as_dict()
-        self._store_host([int(k) for k in K], V)
+        self._store_host(K.tolist(), V)
 
     def add_arrays(self, keys, vectors, levels: Optional[Sequence[int]] = None, wave_max: int = 0):
         """BatchAdd for array inputs (keys[n] int64, vectors[n, dim] float32): same semantics, no per-node objects.
