@@ -218,7 +218,8 @@ def workload_config(args, world):
             "rows_per_gpu": args.n, "dim": args.dim, "M": args.m, "EfSearch": args.ef, "k": args.k,
             "batch": args.batch, "mode": "reference (bit-faithful layerNode.search termination)",
             "layout": "1 graph" if world == 1 else
-            f"{world} independent sub-graphs (one per GPU), queries broadcast, NCCL all-gather + top-k merge",
+            f"{world} independent sub-graphs (one per GPU), queries broadcast, one NCCL all-gather of the packed per-shard "
+            f"results + K4 top-k merge on every rank",
             "l2_policy": f"inputs larger than L2: {args.n * (args.dim * 4 + args.m * 4) / 1e6:.0f} MB of graph per GPU "
                          f"gathered at random; a pool of {args.pool} distinct query batches cycled through the steps"}
 
@@ -267,9 +268,9 @@ def run_ours(args, rank, local_rank, world):
     nb = max(1, min(args.warmup + args.steps, args.pool))
     Qh = torch.from_numpy(synth_rows(nb * B, dim, 43).reshape(nb, B, dim)).pin_memory()
     Qd = Qh.to(dev)
-    rows = torch.empty((B, k), dtype=torch.int32, device=dev)
-    dists = torch.empty((B, k), dtype=torch.float32, device=dev)
-    counts = torch.empty((B,), dtype=torch.int32, device=dev)
+    # the three outputs of a search live in ONE buffer per rank, so the multi-GPU step needs one all-gather
+    packed = sharded.PackedResults(B, k, world, dev)
+    rows, dists, counts = packed.rows, packed.dists, packed.counts
     counters = torch.zeros(8, dtype=torch.int64, device=dev)
     stream = torch.cuda.current_stream(dev)
 
@@ -280,9 +281,8 @@ def run_ours(args, rank, local_rank, world):
     merged = {}
 
     def merge_step():
-        gids = sharded.global_ids(rows, rank, n)  # shard row -> global id (unused slots stay negative)
-        all_d, all_i, all_c = sharded.gather_shard_results(dist, dists, gids, counts)
-        merged["d"], merged["i"], merged["c"] = sharded.merge_topk_device(all_d, all_i, all_c, k, stream.cuda_stream)
+        packed.gather(dist)  # NCCL all-gather of B*(8k+4) bytes per rank
+        merged["d"], merged["i"], merged["c"] = packed.merge(n, stream.cuda_stream)  # K4: global id = shard*n + row
 
     def barrier():
         if world > 1:
@@ -373,7 +373,7 @@ def run_ours(args, rank, local_rank, world):
         "config": workload_config(args, world),
         "e2e": {"value": e2e_value, "unit": "queries/s", "h2d_bytes_per_step": B * dim * 4,
                 "d2h_bytes_per_step": B * k * 8 + B * 4 + 40 if world == 1 else B * k * 12},
-        "gpu_launches": args.steps * (1 if world == 1 else 2),
+        "gpu_launches": args.steps * (1 if world == 1 else 2),  # K1 (+ K4 merge); the all-gather is NCCL's
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": (traffic or {}).get("dram_bytes_per_launch"),
                      "kernel": "b200::traverse_kernel (K1, traverse.cuh)", "kernel_ms": kern_avg_ms,

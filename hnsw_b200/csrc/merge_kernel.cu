@@ -14,9 +14,15 @@ __device__ __forceinline__ uint32_t ordered_bits(float d) {
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);   // total order of the finite/inf floats
 }
 
+// PACKED = false: dists [G][B][k], ids int64 [G][B][k], counts [G][B].
+// PACKED = true : `packed` holds, per shard g at packed + g * shard_stride (int32 elements), what one K1 launch wrote:
+//                 rows int32 [B][k] | dists f32 [B][k] | counts int32 [B]; the global id of a row is g * id_stride + row.
+//                 This is the buffer an all-gather of the per-rank result buffers produces: no repacking in between.
+template <bool PACKED>
 __global__ void merge_topk_kernel(int G, long long B, int k, const float *__restrict__ dists,
-                                  const int64_t *__restrict__ ids, const int32_t *__restrict__ counts, int n_pow2,
-                                  float *__restrict__ out_d, int64_t *__restrict__ out_id,
+                                  const int64_t *__restrict__ ids, const int32_t *__restrict__ counts,
+                                  const int32_t *__restrict__ packed, long long shard_stride, long long id_stride,
+                                  int n_pow2, float *__restrict__ out_d, int64_t *__restrict__ out_id,
                                   int32_t *__restrict__ out_cnt) {
   extern __shared__ unsigned long long keys[];
   const long long q = blockIdx.x;
@@ -25,9 +31,17 @@ __global__ void merge_topk_kernel(int G, long long B, int k, const float *__rest
     unsigned long long key = ~0ull;
     if (i < total) {
       int g = i / k, pos = i - g * k;
-      int cnt = counts[(long long)g * B + q];
+      int cnt;
+      float d = 0.f;
+      if constexpr (PACKED) {
+        const int32_t *sh = packed + g * shard_stride;
+        cnt = sh[2 * B * k + q];
+        if (pos < cnt) d = __int_as_float(sh[B * k + q * k + pos]);
+      } else {
+        cnt = counts[(long long)g * B + q];
+        if (pos < cnt) d = dists[((long long)g * B + q) * k + pos];
+      }
       if (pos < cnt) {
-        float d = dists[((long long)g * B + q) * k + pos];
         key = ((unsigned long long)ordered_bits(d) << 32) | (unsigned)i;
       }
     }
@@ -55,15 +69,30 @@ __global__ void merge_topk_kernel(int G, long long B, int k, const float *__rest
     bool ok = key != ~0ull;
     int src = (int)(key & 0xffffffffu);
     int g = ok ? src / k : 0, pos = ok ? src - g * k : 0;
-    long long off = ((long long)g * B + q) * k + pos;
-    out_d[q * k + i] = ok ? dists[off] : __int_as_float(0x7fc00000);
-    out_id[q * k + i] = ok ? ids[off] : -1;
+    float d = __int_as_float(0x7fc00000);
+    long long id = -1;
+    if (ok) {
+      if constexpr (PACKED) {
+        const int32_t *sh = packed + g * shard_stride;
+        d = __int_as_float(sh[B * k + q * k + pos]);
+        id = g * id_stride + sh[q * k + pos];
+      } else {
+        const long long off = ((long long)g * B + q) * k + pos;
+        d = dists[off];
+        id = ids[off];
+      }
+    }
+    out_d[q * k + i] = d;
+    out_id[q * k + i] = id;
     valid += ok;
   }
   // count = min(k, sum of counts)
   if (threadIdx.x == 0) {
     long long s = 0;
-    for (int g = 0; g < G; g++) s += counts[(long long)g * B + q];
+    for (int g = 0; g < G; g++) {
+      int c = PACKED ? packed[g * shard_stride + 2 * B * k + q] : counts[(long long)g * B + q];
+      s += c > 0 ? c : 0;  // a failed traversal reports -1
+    }
     out_cnt[q] = (int)(s < k ? s : k);
   }
   (void)valid;
@@ -72,6 +101,23 @@ __global__ void merge_topk_kernel(int G, long long B, int k, const float *__rest
 }  // namespace b200
 
 using namespace b200;
+
+static int launch_merge(int32_t device, int32_t G, int64_t B, int32_t k, const float *d_dists, const int64_t *d_ids,
+                        const int32_t *d_counts, const int32_t *d_packed, int64_t shard_stride, int64_t id_stride,
+                        float *d_out_dists, int64_t *d_out_ids, int32_t *d_out_counts, void *stream) {
+  if (B == 0) return 0;
+  B200_CUDA(cudaSetDevice(device));
+  int n_pow2 = 2;
+  while (n_pow2 < G * k) n_pow2 <<= 1;
+  int threads = n_pow2 / 2 < 32 ? 32 : (n_pow2 / 2 > 256 ? 256 : n_pow2 / 2);
+  size_t smem = sizeof(unsigned long long) * (size_t)n_pow2;
+  auto kern = d_packed ? merge_topk_kernel<true> : merge_topk_kernel<false>;
+  if (smem > 48 * 1024) B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<(unsigned)B, threads, smem, (cudaStream_t)stream>>>(G, B, k, d_dists, d_ids, d_counts, d_packed, shard_stride,
+                                                             id_stride, n_pow2, d_out_dists, d_out_ids, d_out_counts);
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
 
 extern "C" int b200hnsw_merge_topk_device(int32_t device, int32_t G, int64_t B, int32_t k, const float *d_dists,
                                           const int64_t *d_ids, const int32_t *d_counts, int32_t sorted_in,
@@ -83,16 +129,18 @@ extern "C" int b200hnsw_merge_topk_device(int32_t device, int32_t G, int64_t B, 
     set_error("merge_topk: bad argument (G=%d k=%d; G*k <= 8192)", G, k);
     return B200HNSW_ERR_BAD_ARG;
   }
-  if (B == 0) return 0;
-  B200_CUDA(cudaSetDevice(device));
-  int n_pow2 = 2;
-  while (n_pow2 < G * k) n_pow2 <<= 1;
-  int threads = n_pow2 / 2 < 32 ? 32 : (n_pow2 / 2 > 256 ? 256 : n_pow2 / 2);
-  size_t smem = sizeof(unsigned long long) * (size_t)n_pow2;
-  if (smem > 48 * 1024)
-    B200_CUDA(cudaFuncSetAttribute(merge_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  merge_topk_kernel<<<(unsigned)B, threads, smem, (cudaStream_t)stream>>>(G, B, k, d_dists, d_ids, d_counts, n_pow2,
-                                                                          d_out_dists, d_out_ids, d_out_counts);
-  B200_CUDA(cudaGetLastError());
-  return 0;
+  return launch_merge(device, G, B, k, d_dists, d_ids, d_counts, nullptr, 0, 0, d_out_dists, d_out_ids, d_out_counts,
+                      stream);
+}
+
+extern "C" int b200hnsw_merge_shards_device(int32_t device, int32_t G, int64_t B, int32_t k, const int32_t *d_packed,
+                                            int64_t shard_stride, int64_t id_stride, float *d_out_dists,
+                                            int64_t *d_out_ids, int32_t *d_out_counts, void *stream) {
+  if (G <= 0 || B < 0 || k <= 0 || k > B200HNSW_MAX_K || (long long)G * k > 8192 ||
+      shard_stride < 2 * B * k + B || (B > 0 && (!d_packed || !d_out_dists || !d_out_ids || !d_out_counts))) {
+    set_error("merge_shards: bad argument (G=%d k=%d; G*k <= 8192; shard_stride >= 2*B*k + B)", G, k);
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  return launch_merge(device, G, B, k, nullptr, nullptr, nullptr, d_packed, shard_stride, id_stride, d_out_dists,
+                      d_out_ids, d_out_counts, stream);
 }

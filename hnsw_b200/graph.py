@@ -202,6 +202,7 @@ class Graph:
         V = np.ascontiguousarray(V, dtype=np.float32)
         K = np.ascontiguousarray(keys, dtype=np.int64)
         st = _lib.Stats()
+        t0 = time.perf_counter()
         if wave_max and wave_max > 0:  # batched construction in waves (not the reference's sequential order)
             _lib.check(_lib.lib().b200hnsw_add_batch_waves(
                 self._h, V.ctypes.data_as(_lib.f32p), K.ctypes.data_as(_lib.i64p), lv.ctypes.data_as(_lib.i32p),
@@ -211,6 +212,7 @@ class Graph:
                                                      K.ctypes.data_as(_lib.i64p), lv.ctypes.data_as(_lib.i32p),
                                                      len(K), self.M, self.EfSearch, metric, C.byref(st)))
         self.last_stats = st.as_dict()
+        self.last_stats["call_s"] = time.perf_counter() - t0  # wall time of the C call (staging + kernels)
         self._store_host(K.tolist(), V)
 
     def add_arrays(self, keys, vectors, levels: Optional[Sequence[int]] = None, wave_max: int = 0):

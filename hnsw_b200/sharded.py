@@ -52,3 +52,44 @@ def merge_topk_device(all_d, all_i, all_c, k: int, stream: int = 0):
         C.c_void_p(all_c.data_ptr()), 0, C.c_void_p(m_d.data_ptr()), C.c_void_p(m_i.data_ptr()),
         C.c_void_p(m_c.data_ptr()), C.c_void_p(stream) if stream else None))
     return m_d, m_i, m_c
+
+
+class PackedResults:
+    """One contiguous int32 buffer per rank laid out as the search kernel's three outputs (rows [B,k] | dists [B,k] |
+    counts [B]), so a step needs ONE all-gather and no repacking kernels; `merge` runs K4 on the gathered buffer and
+    turns shard rows into global ids (shard * rows_per_shard + row) inside the kernel."""
+
+    def __init__(self, B: int, k: int, world: int, device):
+        import torch
+        self.B, self.k, self.world = B, k, world
+        self.stride = 2 * B * k + B
+        self.local = torch.empty(self.stride, dtype=torch.int32, device=device)
+        self.gathered = torch.empty(world * self.stride, dtype=torch.int32, device=device)
+        self.rows = self.local[:B * k].view(B, k)
+        self.dists = self.local[B * k:2 * B * k].view(torch.float32).view(B, k)
+        self.counts = self.local[2 * B * k:]
+        dev = self.local.device
+        self.m_d = torch.empty((B, k), dtype=torch.float32, device=dev)
+        self.m_i = torch.empty((B, k), dtype=torch.int64, device=dev)
+        self.m_c = torch.empty((B,), dtype=torch.int32, device=dev)
+
+    def gather(self, dist):
+        dist.all_gather_into_tensor(self.gathered, self.local)
+        return self.gathered
+
+    def shard_views(self):
+        """(rows [G,B,k] i32, dists [G,B,k] f32, counts [G,B] i32) views of the gathered buffer (for checks)."""
+        import torch
+        g = self.gathered.view(self.world, self.stride)
+        B, k = self.B, self.k
+        return (g[:, :B * k].reshape(self.world, B, k), g[:, B * k:2 * B * k].view(torch.float32).reshape(self.world, B, k),
+                g[:, 2 * B * k:])
+
+    def merge(self, rows_per_shard: int, stream: int = 0):
+        if self.gathered.device.type != "cuda":
+            raise RuntimeError("PackedResults.merge needs CUDA tensors; hnsw_b200 has no CPU fallback")
+        _lib.check(_lib.lib().b200hnsw_merge_shards_device(
+            self.gathered.device.index or 0, self.world, self.B, self.k, C.c_void_p(self.gathered.data_ptr()),
+            self.stride, rows_per_shard, C.c_void_p(self.m_d.data_ptr()), C.c_void_p(self.m_i.data_ptr()),
+            C.c_void_p(self.m_c.data_ptr()), C.c_void_p(stream) if stream else None))
+        return self.m_d, self.m_i, self.m_c

@@ -156,6 +156,13 @@ int b200hnsw_merge_topk_device(int32_t device, int32_t G, int64_t B, int32_t k, 
                                const int64_t *d_ids, const int32_t *d_counts, int32_t sorted_in, float *d_out_dists,
                                int64_t *d_out_ids, int32_t *d_out_counts, void *stream);
 
+/* The same merge reading what the search kernel wrote, without repacking: shard g's results start at
+ * d_packed + g * shard_stride (int32 elements) as rows int32 [B][k] | dists f32 [B][k] | counts int32 [B] -- one
+ * contiguous buffer per rank, so ONE all-gather moves everything; the global id of a row is g * id_stride + row. */
+int b200hnsw_merge_shards_device(int32_t device, int32_t G, int64_t B, int32_t k, const int32_t *d_packed,
+                                 int64_t shard_stride, int64_t id_stride, float *d_out_dists, int64_t *d_out_ids,
+                                 int32_t *d_out_counts, void *stream);
+
 /* ---- hybrid.ExactIndex (hnsw-extensions/hybrid/exact.go:13-160) --------------------------------------------- */
 int b200exact_create(int32_t dim, int32_t metric, int32_t device, int64_t capacity, b200exact_t **out);
 void b200exact_destroy(b200exact_t *x);

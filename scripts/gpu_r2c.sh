@@ -1,0 +1,5 @@
+#!/bin/bash
+mkdir -p gpurun_out
+nvidia-smi -L
+timeout 600 python -m pytest tests -m gpu -x -q -k "merge" 2>&1 | tail -3
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29555 bench.py --gpus 2 --steps 50 --warmup 3 > gpurun_out/bench_g2_r2c.json 2> gpurun_out/bench_g2_r2c.err; echo "rc=$?"; cut -c1-900 gpurun_out/bench_g2_r2c.json; tail -3 gpurun_out/bench_g2_r2c.err

@@ -11,7 +11,7 @@ X = synth_rows(N, d, 42); lv = draw_levels(N, 0.25, 44)
 g = hnsw_b200.Graph(M=M, Ml=0.25, EfSearch=ef, Distance=hnsw_b200.EuclideanDistance, capacity=N)
 t = time.time(); g.add_arrays(np.arange(N, dtype=np.int64), X, lv, wave_max=wm); dt = time.time() - t
 st = g.last_stats
-print(f"wave add N={N} wall {dt:.2f}s kernel {st['kernel_ms']/1e3:.2f}s -> {N/(st['kernel_ms']/1e3):.0f} vec/s launches={st['launches']} "
+print(f"wave add N={N} wall {dt:.2f}s (C call {st.get('call_s', 0):.2f}s) kernel {st['kernel_ms']/1e3:.2f}s -> {N/(st['kernel_ms']/1e3):.0f} vec/s launches={st['launches']} "
       f"E={st['dist_evals']/N:.0f} evict={st['evict_evals']/N:.0f} repl={st['replenish_evals']/N:.0f} evictions={st['evictions']/N:.1f}", flush=True)
 print(g.Topography())
 for B in Bs:

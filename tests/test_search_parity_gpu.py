@@ -135,3 +135,30 @@ def test_merge_kernel_matches_spec():
         assert np.array_equal(mc.cpu().numpy(), rc)
         assert np.array_equal(mi.cpu().numpy(), ri)
         assert np.array_equal(md.cpu().numpy(), rd, equal_nan=True)
+
+
+@pytest.mark.gpu
+def test_packed_shard_merge_matches_spec():
+    # the same K4 reading the search kernel's own output layout (rows | dists | counts per shard), ids = g*stride + row
+    import torch
+    from hnsw_b200 import sharded
+    from merge_ref import merge_topk_ref
+    rng = np.random.default_rng(4)
+    for G, B, k, stride_ids in ((2, 50, 10, 1000), (8, 33, 10, 1 << 20), (4, 20, 64, 77), (1, 9, 3, 5)):
+        d = np.round(rng.uniform(0, 4, (G, B, k)), 1).astype(np.float32)
+        d.sort(axis=2)
+        d[rng.uniform(size=d.shape) < 0.02] = np.nan
+        rows = rng.integers(0, stride_ids, (G, B, k)).astype(np.int32)
+        c = rng.integers(0, k + 1, (G, B)).astype(np.int32)
+        pr = sharded.PackedResults(B, k, G, torch.device("cuda", 0))
+        g = pr.gathered.view(G, pr.stride)
+        g[:, :B * k] = torch.from_numpy(rows.reshape(G, -1)).cuda()
+        g[:, B * k:2 * B * k] = torch.from_numpy(d.view(np.int32).reshape(G, -1)).cuda()
+        g[:, 2 * B * k:] = torch.from_numpy(c).cuda()
+        md, mi, mc = pr.merge(stride_ids)
+        torch.cuda.synchronize()
+        ids = rows.astype(np.int64) + (np.arange(G, dtype=np.int64) * stride_ids)[:, None, None]
+        rd, ri, rc = merge_topk_ref(d, ids, c, k)
+        assert np.array_equal(mc.cpu().numpy(), rc)
+        assert np.array_equal(mi.cpu().numpy(), ri)
+        assert np.array_equal(md.cpu().numpy(), rd, equal_nan=True)

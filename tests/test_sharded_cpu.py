@@ -32,6 +32,16 @@ def _worker(rank, world, port, tmp):
     ids = sharded.global_ids(torch.from_numpy(rows), rank, n)
     all_d, all_i, all_c = sharded.gather_shard_results(dist, torch.from_numpy(dd), ids, torch.from_numpy(cnt))
     m = merge_topk_ref(all_d.numpy(), all_i.numpy(), all_c.numpy(), k)
+    # the packed layout the GPU path uses (one buffer, one collective) carries the same lists
+    pr = sharded.PackedResults(len(Q), k, world, torch.device("cpu"))
+    pr.rows.copy_(torch.from_numpy(rows))
+    pr.dists.copy_(torch.from_numpy(dd))
+    pr.counts.copy_(torch.from_numpy(cnt))
+    pr.gather(dist)
+    p_rows, p_d, p_c = pr.shard_views()
+    assert np.array_equal(p_d.numpy(), all_d.numpy(), equal_nan=True) and np.array_equal(p_c.numpy(), all_c.numpy())
+    gid = np.where(p_rows.numpy() >= 0, p_rows.numpy().astype(np.int64) + np.arange(world)[:, None, None] * n, -1)
+    assert np.array_equal(gid, all_i.numpy())
     np.savez(os.path.join(tmp, f"rank{rank}.npz"), d=m[0], i=m[1], c=m[2], rows=rows, dd=dd, cnt=cnt)
     dist.barrier()
     dist.destroy_process_group()
