@@ -66,6 +66,8 @@ __device__ __forceinline__ float4 ldg_f4(const float4 *p) {
   return v;
 }
 
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
 // the same load when `ok`; otherwise nothing is loaded and the result is undefined (the empty asm only tells the compiler
 // the registers are written, so no zero fill is emitted)
 __device__ __forceinline__ float4 ldg_f4_if(const float4 *p, bool ok) {

@@ -76,6 +76,10 @@ int launch_traverse(b200hnsw *h, TraverseParams &p, int vis_cap, cudaStream_t s)
       if (id == 10) return launch_t<16, 2, 2, 6>(h, g, p, s);
       if (id == 11) return launch_t<16, 2, 4, 6>(h, g, p, s);
       if (id == 12) return launch_t<8, 4, 1, 8>(h, g, p, s);
+      if (id == 13) return launch_t<16, 2, 2, 8>(h, g, p, s);
+      if (id == 14) return launch_t<16, 2, 4, 8>(h, g, p, s);
+      if (id == 15) return launch_t<8, 4, 2, 6>(h, g, p, s);
+      if (id == 16) return launch_t<16, 2, 2, 6>(h, g, p, s);
     }
   }
 #define K1(G_, CH_, U_) return launch_t<G_, CH_, U_, ((CH_) >= 12 ? 2 : ((CH_) * (U_) <= 8 ? 5 : 4))>(h, g, p, s)

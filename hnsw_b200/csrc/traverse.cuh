@@ -47,6 +47,12 @@ __host__ __device__ inline size_t traverse_group_bytes(const TraverseParams &p) 
 
 constexpr int TRAV_WARPS = 4;
 
+#ifdef B200_K1_TIMING  // exploration build only (scripts/): cycles per phase of warp 0 of block 0, printed at the end
+#define K1_T(i) { long long t__ = clock64(); tphase[i] += t__ - tlast; tlast = t__; }
+#else
+#define K1_T(i)
+#endif
+
 enum { ST_NEED = 0, ST_INIT = 1, ST_EXPAND = 2, ST_IDLE = 3 };
 
 template <int G, int CH, int U, int MINB>
@@ -85,8 +91,15 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
 
   float best_d = 0.f;  // leader: the one-element result queue of a k = 1 layer lives in registers
   int best_id = -1, r1 = 0;
+  int imp_id = -1;      // leader: last row that improved on result.Min() in this step
+  bool cfree = false;   // leader: the candidate queue is no longer needed on this layer (see the decision below)
 
+#ifdef B200_K1_TIMING
+  long long tphase[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tlast = clock64();
+  int tsteps = 0;
+#endif
   for (;;) {
+    K1_T(7)
     // ---- fetch the next traversal for groups that finished one --------------------------------------------------
     const bool need = st == ST_NEED;
     if (__any_sync(FULL, need)) {
@@ -116,6 +129,7 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
       C.len = 0;
       R.len = 0;
       r1 = 0;
+      cfree = false;
       uint4 e4 = make_uint4(~0u, ~0u, ~0u, ~0u);
       uint4 *t4 = reinterpret_cast<uint4 *>(vtab);
       for (uint32_t i = gl; i < (vmask + 1) / 4; i += G) t4[i] = e4;
@@ -126,6 +140,7 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
       }
     }
     __syncwarp();
+    K1_T(0)
     // ---- EXPAND: neighbour list of `cur`, ascending key order, unvisited only (graph.go:137-144) ----------------
     if (__any_sync(FULL, expand)) {
       const int32_t *list = nullptr;
@@ -158,7 +173,13 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
           }
         }
         const unsigned gf = (__ballot_sync(FULL, fr) >> gshift) & GBITS;
-        if (fr) fresh[nfresh + __popc(gf & ((1u << gl) - 1u))] = nb;
+        if (fr) {
+          fresh[nfresh + __popc(gf & ((1u << gl) - 1u))] = nb;
+          // every fresh row is requested from HBM now (into L2), so the U-at-a-time loads below find it on chip
+          // instead of paying one DRAM latency per batch
+          const float4 *row = g.vec + (size_t)nb * g.row_chunks;
+          for (int c = 0; c < g.row_chunks; c += 8) prefetch_l2(row + c);
+        }
         nfresh += __popc(gf);
         if (leader) c_nbr += __popc(gv);
         if (gv != GBITS) more = false;  // lists are -1 padded at the end
@@ -167,6 +188,7 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
       vcount += nfresh;
     }
     __syncwarp();
+    K1_T(1)
     const bool overflow = vcount * 2 > (int)vmask;  // load factor > 1/2: fail loudly, never approximate
     if (overflow) nfresh = 0;
     // ---- evaluate the fresh rows, U at a time; the leader replays graph.go:146-159 in key order -------------------
@@ -177,12 +199,24 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
 #pragma unroll
     for (int u = 0; u < U; u++) nid[u] = u < nfresh ? fresh[u] : -1;
     group_load_rows<G, CH, U>(rr, g.vec, g.row_chunks, nid, gl);
+#ifdef B200_K1_TIMING
+    if (__any_sync(FULL, nfresh > 0)) {  // wait for the first batch explicitly so that it is timed on its own
+      float tw = rr[0][0].x;
+      asm volatile("" ::"f"(tw));
+      tsteps++;
+    }
+    K1_T(2)
+#endif
     for (int b0 = 0; __any_sync(FULL, b0 < nfresh); b0 += U) {
       int ids[U];
 #pragma unroll
       for (int u = 0; u < U; u++) ids[u] = nid[u];
       GPartial<U> P;
       group_partials<G, CH, U>(P, rr, Q, p.metric);
+#ifdef B200_K1_TIMING
+      asm volatile("" ::"f"(P.a[0]));
+      K1_T(3)
+#endif
 #pragma unroll
       for (int u = 0; u < U; u++) nid[u] = b0 + U + u < nfresh ? fresh[b0 + U + u] : -1;
       group_load_rows<G, CH, U>(rr, g.vec, g.row_chunks, nid, gl);
@@ -190,6 +224,10 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
       float d[U];
 #pragma unroll
       for (int u = 0; u < U; u++) d[u] = __shfl_sync(FULL, dmine, leader_lane + u * (G / U));
+#ifdef B200_K1_TIMING
+      asm volatile("" ::"f"(d[0]));
+      K1_T(5)
+#endif
       if (leader) {
 #pragma unroll
         for (int u = 0; u < U; u++) {
@@ -208,33 +246,36 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
             vtab[h & vmask] = (uint32_t)ids[u];
             continue;
           }
+          const float du = d[u];
           if (kcur == 1) {
             // a full one-element queue: `improved` (graph.go:147) and the replacement test (graph.go:150,
-            // result.Max() is that element) are the same comparison.  No candidate queue either: the new best is
-            // strictly below everything evaluated on this layer, so candidates.Push sifts it to the root, where
-            // neither a later Push of this step (strict <) nor PopLast (ef >= 1 keeps slot 0) can move it; the next
-            // Pop (graph.go:126) therefore returns exactly this node, and when nothing improved the loop ends
-            // (graph.go:164-166) without looking at the queue.
-            if (d[u] < best_d) {
+            // result.Max() is that element) are the same comparison
+            if (du < best_d) {
               improved = true;
-              best_d = d[u];
+              imp_id = ids[u];
+              best_d = du;
               best_id = ids[u];
             }
-            continue;
           } else {
-            improved = improved || (R.len > 0 && d[u] < R.min_dist());  // graph.go:147
+            if (R.len > 0 && du < R.min_dist()) {  // graph.go:147
+              improved = true;
+              imp_id = ids[u];
+            }
             if (R.len < kcur) {
-              R.push(d[u], ids[u]);
-            } else if (d[u] < R.max_dist()) {  // result.Max() is the last array slot
+              R.push(du, ids[u]);
+            } else if (du < R.max_dist()) {  // result.Max() is the last array slot
               R.pop_last();
-              R.push(d[u], ids[u]);
+              R.push(du, ids[u]);
             }
           }
-          C.push(d[u], ids[u]);
-          if (C.len > p.ef) C.pop_last();  // graph.go:157-159
+          if (!cfree) {
+            C.push(du, ids[u]);
+            if (C.len > p.ef) C.pop_last();  // graph.go:157-159
+          }
         }
       }
     }
+    K1_T(6)
     if (leader) c_evals += nfresh;  // E: one per evaluated row
     if (init && nfresh > 0) vcount = 1;
     // ---- leader decides: next node, end of layer ---------------------------------------------------------------------
@@ -243,17 +284,24 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
       const int rl = kcur == 1 ? r1 : R.len;
       if (init) {
         if (nfresh > 0) next = cur;                                 // graph.go:125-127, first iteration
-      } else if (kcur == 1) {
-        if (improved) next = best_id;                               // what candidates.Pop() would return, see above
+      } else if (cfree) {
+        if (improved) next = imp_id;                                // what candidates.Pop() would return, see below
       } else if (!(!improved && rl >= kcur) && C.len > 0) {        // graph.go:164-166, 125
         next = (int)C.pop().y;
       }
+      // Once the result queue is full it stays full (PopLast + Push), and from then on the candidate queue is never
+      // looked at again: the loop goes on only when some row improved on result.Min() (graph.go:164-166), and that
+      // row is strictly below everything evaluated on this layer, so candidates.Push sifted it to the root, where
+      // neither a later Push of the same step (strict <) nor PopLast (ef >= 1 keeps slot 0) can move it -- the next
+      // Pop (graph.go:126) returns exactly the last improving row.  So the queue is not maintained any more.
+      if (rl >= kcur) cfree = true;
     }
     next = __shfl_sync(FULL, next, leader_lane);
     const int rlen = __shfl_sync(FULL, kcur == 1 ? r1 : R.len, leader_lane);
     const int r0_id = __shfl_sync(FULL, best_id, leader_lane);    // k = 1 layers: the result itself
     const float r0_d = __shfl_sync(FULL, best_d, leader_lane);
     __syncwarp();  // the leader's heap writes are visible to its group
+    K1_T(4)
     bool chain = false;
     float elev_d = 0.f;
     if (init || expand) {
@@ -315,6 +363,7 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
       if (leader) {
         c_evals++;  // the reference evaluates the entry again; counted so E equals the oracle's
         C.len = 0;
+        cfree = kcur == 1;  // the result queue {entry} is already full
         if (kcur == 1) {
           best_d = elev_d;
           best_id = elevator;
@@ -332,6 +381,12 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
     }
     __syncwarp();
   }
+#ifdef B200_K1_TIMING
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    printf("K1 timing (cycles, warp 0): init %lld list+visited %lld first-rows %lld wait+math %lld reduce %lld leader %lld "
+           "decide %lld tail %lld steps %d\n", tphase[0], tphase[1], tphase[2], tphase[3], tphase[5], tphase[6],
+           tphase[4], tphase[7], tsteps);
+#endif
   if (p.counters && leader) {
     if (c_evals) atomicAdd(&p.counters[0], c_evals);
     if (c_exp) atomicAdd(&p.counters[1], c_exp);
