@@ -219,7 +219,8 @@ def workload_config(args, world):
             "batch": args.batch, "mode": "reference (bit-faithful layerNode.search termination)",
             "layout": "1 graph" if world == 1 else
             f"{world} independent sub-graphs (one per GPU), queries broadcast, one NCCL all-gather of the packed per-shard "
-            f"results + K4 top-k merge on every rank",
+            f"results + K4 top-k merge on every rank, pipelined: the gather + merge of step i run on a side stream under "
+            f"the traversal of step i+1 (all inside the timed region)",
             "l2_policy": f"inputs larger than L2: {args.n * (args.dim * 4 + args.m * 4) / 1e6:.0f} MB of graph per GPU "
                          f"gathered at random; a pool of {args.pool} distinct query batches cycled through the steps"}
 
@@ -289,14 +290,20 @@ def run_ours(args, rank, local_rank, world):
             dist.barrier()
         torch.cuda.synchronize(dev)
 
+    # N > 1: traversal of step i+1 overlaps the all-gather + merge of step i (two result buffers, side stream)
+    pipe = sharded.ShardPipeline(g, dist, B, k, n, dev) if world > 1 else None
+
     sampler = ClockSampler(local_rank)
     sampler.start()
 
     # ---- device-resident timing: W warm-up steps, then exactly K steps between events ---------------------------
     for i in range(args.warmup):
-        search_step(Qd[i % nb])
         if world > 1:
-            merge_step()
+            pipe.search(Qd[i % nb].data_ptr(), counters.data_ptr())
+        else:
+            search_step(Qd[i % nb])
+    if world > 1:
+        pipe.drain()
     barrier()
     counters.zero_()
     ka = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
@@ -306,10 +313,13 @@ def run_ours(args, rank, local_rank, world):
     ev0.record(stream)
     for i in range(args.steps):
         ka[i].record(stream)
-        search_step(Qd[(args.warmup + i) % nb])
-        kb[i].record(stream)
         if world > 1:
-            merge_step()
+            last_slot = pipe.search(Qd[(args.warmup + i) % nb].data_ptr(), counters.data_ptr())
+        else:
+            search_step(Qd[(args.warmup + i) % nb])
+        kb[i].record(stream)
+    if world > 1:
+        pipe.drain()  # the timed region ends when the last merge has finished
     ev1.record(stream)
     barrier()
     total_ms = ev0.elapsed_time(ev1)
@@ -318,6 +328,8 @@ def run_ours(args, rank, local_rank, world):
     if int(ctr[4]) != 0:
         raise SystemExit("bench.py: a traversal overflowed the visited set in the device-pointer path")
     last = (args.warmup + args.steps - 1) % nb
+    if world > 1:
+        rows, dists, counts = pipe.buf[last_slot].rows, pipe.buf[last_slot].dists, pipe.buf[last_slot].counts
     last_rows, last_dists, last_counts = rows.cpu().numpy(), dists.cpu().numpy(), counts.cpu().numpy()
     t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
     if world > 1:

@@ -93,3 +93,51 @@ class PackedResults:
             self.stride, rows_per_shard, C.c_void_p(self.m_d.data_ptr()), C.c_void_p(self.m_i.data_ptr()),
             C.c_void_p(self.m_c.data_ptr()), C.c_void_p(stream) if stream else None))
         return self.m_d, self.m_i, self.m_c
+
+
+class ShardPipeline:
+    """Sharded batched search as a two-stage pipeline: the traversal of batch i+1 (main stream) runs while the
+    all-gather + K4 merge of batch i run on a side stream, over two PackedResults buffers.  `search` launches one
+    batch and returns at once; `merged(slot)` are the tensors the merge of that slot writes (valid after `drain`, or
+    after `done[slot]` has been waited on)."""
+
+    def __init__(self, graph, dist, B: int, k: int, rows_per_shard: int, device):
+        import torch
+        self.g, self.dist, self.B, self.k, self.n = graph, dist, B, k, rows_per_shard
+        self.world = dist.get_world_size() if dist is not None else 1
+        self.main = torch.cuda.current_stream(device)
+        self.side = torch.cuda.Stream(device)
+        self.buf = [PackedResults(B, k, self.world, device) for _ in range(2)]
+        self.searched = [torch.cuda.Event() for _ in range(2)]
+        self.done = [torch.cuda.Event() for _ in range(2)]
+        self.used = [False, False]
+        self.step = 0
+
+    def search(self, d_queries: int, d_counters: int = 0) -> int:
+        """Queue one batch (device pointer to [B, dim] f32); returns the slot its results will land in."""
+        import torch
+        slot = self.step & 1
+        self.step += 1
+        b = self.buf[slot]
+        if self.used[slot]:
+            self.main.wait_event(self.done[slot])  # the merge that last read this slot's buffers has finished
+        self.g.search_device(d_queries, self.B, self.k, b.rows.data_ptr(), b.dists.data_ptr(), b.counts.data_ptr(),
+                             d_counters, self.main.cuda_stream)
+        self.searched[slot].record(self.main)
+        self.side.wait_event(self.searched[slot])
+        with torch.cuda.stream(self.side):
+            b.gather(self.dist)
+            b.merge(self.n, self.side.cuda_stream)
+        self.done[slot].record(self.side)
+        self.used[slot] = True
+        return slot
+
+    def merged(self, slot: int):
+        b = self.buf[slot]
+        return b.m_d, b.m_i, b.m_c
+
+    def drain(self):
+        """Main stream waits for every queued merge."""
+        for slot in range(2):
+            if self.used[slot]:
+                self.main.wait_event(self.done[slot])

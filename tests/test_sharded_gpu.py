@@ -1,0 +1,69 @@
+"""N>1 path on GPUs (skipped with fewer than 2 devices): world_size 2 over NCCL.  Every rank builds its own sub-graph
+on its own device, the same queries go to both, and the pipelined all-gather + K4 merge (hnsw_b200.sharded.ShardPipeline)
+must return, on every rank, merge(shard results) as the numpy specification computes it in one process."""
+import os
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def _worker(rank, world, port, tmp):
+    sys.path.insert(0, str(ROOT))
+    import torch
+    import torch.distributed as dist
+    import hnsw_b200
+    from hnsw_b200 import sharded
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    n, d, k, ef, B = 3000, 64, 10, 32, 200
+    X = np.random.default_rng(100 + rank).uniform(-1, 1, (n, d)).astype(np.float32)
+    lv = np.minimum(np.random.default_rng(200 + rank).geometric(0.75, n) - 1, 5).astype(np.int32)
+    g = hnsw_b200.Graph(M=12, Ml=0.25, EfSearch=ef, Distance=hnsw_b200.EuclideanDistance, device=rank, capacity=n)
+    g.add_arrays(np.arange(n, dtype=np.int64), X, lv, wave_max=256)
+    pipe = sharded.ShardPipeline(g, dist, B, k, n, dev)
+    out = {}
+    for step in range(3):  # three batches through the two slots
+        Q = np.random.default_rng(7 + step).uniform(-1, 1, (B, d)).astype(np.float32)  # the same on every rank
+        qd = torch.from_numpy(Q).to(dev)
+        slot = pipe.search(qd.data_ptr())
+        pipe.drain()
+        torch.cuda.synchronize(dev)
+        md, mi, mc = pipe.merged(slot)
+        b = pipe.buf[slot]
+        out[f"d{step}"], out[f"i{step}"], out[f"c{step}"] = md.cpu().numpy(), mi.cpu().numpy(), mc.cpu().numpy()
+        out[f"rows{step}"], out[f"dd{step}"], out[f"cnt{step}"] = (b.rows.cpu().numpy(), b.dists.cpu().numpy(),
+                                                                 b.counts.cpu().numpy())
+    np.savez(os.path.join(tmp, f"rank{rank}.npz"), **out)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+def test_two_gpu_pipeline_matches_merge_spec(tmp_path):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+    sys.path.insert(0, str(ROOT / "tests"))
+    from merge_ref import merge_topk_ref
+    world, port = 2, 29617 + os.getpid() % 200
+    mp.spawn(_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    r = [np.load(tmp_path / f"rank{i}.npz") for i in range(world)]
+    for step in range(3):
+        all_d = np.stack([r[i][f"dd{step}"] for i in range(world)])
+        all_i = np.stack([np.where(r[i][f"rows{step}"] >= 0, r[i][f"rows{step}"].astype(np.int64) + i * 3000, -1)
+                          for i in range(world)])
+        all_c = np.stack([r[i][f"cnt{step}"] for i in range(world)])
+        m = merge_topk_ref(all_d, all_i, all_c, 10)
+        for i in range(world):  # every rank holds the same merged lists, equal to the specification's
+            assert np.array_equal(r[i][f"d{step}"], m[0], equal_nan=True)
+            assert np.array_equal(r[i][f"i{step}"], m[1])
+            assert np.array_equal(r[i][f"c{step}"], m[2])
+        assert (m[1] >= 3000).any() and (m[1][m[1] >= 0] < 3000).any()
