@@ -218,9 +218,9 @@ def workload_config(args, world):
             "rows_per_gpu": args.n, "dim": args.dim, "M": args.m, "EfSearch": args.ef, "k": args.k,
             "batch": args.batch, "mode": "reference (bit-faithful layerNode.search termination)",
             "layout": "1 graph" if world == 1 else
-            f"{world} independent sub-graphs (one per GPU), queries broadcast, one NCCL all-gather of the packed per-shard "
-            f"results + K4 top-k merge on every rank, pipelined: the gather + merge of step i run on a side stream under "
-            f"the traversal of step i+1 (all inside the timed region)",
+            f"{world} independent sub-graphs (one per GPU), queries broadcast; rank r merges queries [r*B/{world}, "
+            f"(r+1)*B/{world}): one NCCL all-to-all of the per-shard result blocks + K4 top-k merge, pipelined on a side "
+            f"stream under the traversal of the next step (all inside the timed region)",
             "l2_policy": f"inputs larger than L2: {args.n * (args.dim * 4 + args.m * 4) / 1e6:.0f} MB of graph per GPU "
                          f"gathered at random; a pool of {args.pool} distinct query batches cycled through the steps"}
 
@@ -269,21 +269,15 @@ def run_ours(args, rank, local_rank, world):
     nb = max(1, min(args.warmup + args.steps, args.pool))
     Qh = torch.from_numpy(synth_rows(nb * B, dim, 43).reshape(nb, B, dim)).pin_memory()
     Qd = Qh.to(dev)
-    # the three outputs of a search live in ONE buffer per rank, so the multi-GPU step needs one all-gather
-    packed = sharded.PackedResults(B, k, world, dev)
-    rows, dists, counts = packed.rows, packed.dists, packed.counts
+    rows = torch.empty((B, k), dtype=torch.int32, device=dev)
+    dists = torch.empty((B, k), dtype=torch.float32, device=dev)
+    counts = torch.empty((B,), dtype=torch.int32, device=dev)
     counters = torch.zeros(8, dtype=torch.int64, device=dev)
     stream = torch.cuda.current_stream(dev)
 
     def search_step(qd):
         g.search_device(qd.data_ptr(), B, k, rows.data_ptr(), dists.data_ptr(), counts.data_ptr(),
                         counters.data_ptr(), stream.cuda_stream)
-
-    merged = {}
-
-    def merge_step():
-        packed.gather(dist)  # NCCL all-gather of B*(8k+4) bytes per rank
-        merged["d"], merged["i"], merged["c"] = packed.merge(n, stream.cuda_stream)  # K4: global id = shard*n + row
 
     def barrier():
         if world > 1:
@@ -328,8 +322,6 @@ def run_ours(args, rank, local_rank, world):
     if int(ctr[4]) != 0:
         raise SystemExit("bench.py: a traversal overflowed the visited set in the device-pointer path")
     last = (args.warmup + args.steps - 1) % nb
-    if world > 1:
-        rows, dists, counts = pipe.buf[last_slot].rows, pipe.buf[last_slot].dists, pipe.buf[last_slot].counts
     last_rows, last_dists, last_counts = rows.cpu().numpy(), dists.cpu().numpy(), counts.cpu().numpy()
     t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
     if world > 1:
@@ -340,19 +332,25 @@ def run_ours(args, rank, local_rank, world):
     h_rows = torch.empty((B, k), dtype=torch.int32).pin_memory()
     h_dists = torch.empty((B, k), dtype=torch.float32).pin_memory()
     h_counts = torch.empty((B,), dtype=torch.int32).pin_memory()
-    h_mi = torch.empty((B, k), dtype=torch.int64).pin_memory()
-    h_md = torch.empty((B, k), dtype=torch.float32).pin_memory()
+    seg = pipe.buf[0].seg if pipe else B
+    h_mi = torch.empty((seg, k), dtype=torch.int64).pin_memory()
+    h_md = torch.empty((seg, k), dtype=torch.float32).pin_memory()
+    h_mc = torch.empty((seg,), dtype=torch.int32).pin_memory()
     qtmp = torch.empty((B, dim), dtype=torch.float32, device=dev)
 
     def e2e_step(i):
         if world == 1:  # the drop-in call itself: b200hnsw_search_batch(host pointers)
             g.search_host_ptrs(Qh[i].data_ptr(), B, k, h_rows.data_ptr(), h_dists.data_ptr(), h_counts.data_ptr())
         else:
+            # every rank receives the whole batch, searches its shard, and returns the merged lists of its share of the
+            # queries (B / world of them) to the host
             qtmp.copy_(Qh[i], non_blocking=True)
-            search_step(qtmp)
-            merge_step()
-            h_mi.copy_(merged["i"], non_blocking=True)
-            h_md.copy_(merged["d"], non_blocking=True)
+            slot = pipe.search(qtmp.data_ptr())
+            pipe.drain()
+            md, mi, mc = pipe.merged(slot)
+            h_mi.copy_(mi, non_blocking=True)
+            h_md.copy_(md, non_blocking=True)
+            h_mc.copy_(mc, non_blocking=True)
             torch.cuda.synchronize(dev)
 
     for i in range(max(args.warmup, 3)):
@@ -384,7 +382,7 @@ def run_ours(args, rank, local_rank, world):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args, world),
         "e2e": {"value": e2e_value, "unit": "queries/s", "h2d_bytes_per_step": B * dim * 4,
-                "d2h_bytes_per_step": B * k * 8 + B * 4 + 40 if world == 1 else B * k * 12},
+                "d2h_bytes_per_step": B * k * 8 + B * 4 + 40 if world == 1 else seg * (k * 12 + 4)},
         "gpu_launches": args.steps * (1 if world == 1 else 2),  # K1 (+ K4 merge); the all-gather is NCCL's
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": (traffic or {}).get("dram_bytes_per_launch"),

@@ -71,6 +71,9 @@ SYMBOLS = {
                                            C.c_int64, C.POINTER(Stats)]),
     "b200hnsw_merge_topk_device": (C.c_int, [C.c_int32, C.c_int32, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p,
                                              C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b200hnsw_search_batch_segmented_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32,
+                                                         C.c_int32, C.c_int32, i32p, C.c_void_p, C.c_int64, C.c_int64,
+                                                         C.c_void_p, C.c_void_p]),
     "b200hnsw_merge_shards_device": (C.c_int, [C.c_int32, C.c_int32, C.c_int64, C.c_int32, C.c_void_p, C.c_int64,
                                                C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "b200exact_create": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.POINTER(C.c_void_p)]),

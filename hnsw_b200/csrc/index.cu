@@ -457,6 +457,33 @@ int b200hnsw_search_batch_device(b200hnsw_t *h, const float *d_queries, int64_t 
                        reinterpret_cast<unsigned long long *>(d_counters), d_err, h->vis_hint, s);
 }
 
+int b200hnsw_search_batch_segmented_device(b200hnsw_t *h, const float *d_queries, int64_t B, int32_t k, int32_t ef,
+                                           int32_t metric, int32_t mode, const int32_t *entries, int32_t *d_packed,
+                                           int64_t seg_len, int64_t seg_stride, int64_t *d_counters, void *stream) {
+  int rc = check_search_args(h, B, k, ef, metric);
+  if (rc) return rc;
+  if (seg_len <= 0 || seg_stride < 2 * seg_len * k + seg_len || (B > 0 && !d_packed)) {
+    set_error("search: bad segment layout (seg_len=%lld seg_stride=%lld, need >= %lld)", (long long)seg_len,
+              (long long)seg_stride, (long long)(2 * seg_len * k + seg_len));
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  B200_CUDA(cudaSetDevice(h->cfg.device));
+  cudaStream_t s = (cudaStream_t)stream;
+  if (B == 0) return 0;
+  const int64_t nseg = (B + seg_len - 1) / seg_len;
+  if (h->n_layers == 0 || h->n == 0) {  // graph.go:554-556: empty graph -> no results
+    for (int64_t g = 0; g < nseg; g++) {
+      int32_t *base = d_packed + g * seg_stride;
+      B200_CUDA(cudaMemsetAsync(base, 0xff, sizeof(int32_t) * 2 * (size_t)seg_len * k, s));
+      B200_CUDA(cudaMemsetAsync(base + 2 * seg_len * k, 0, sizeof(int32_t) * (size_t)seg_len, s));
+    }
+    return 0;
+  }
+  int *d_err = d_counters ? reinterpret_cast<int *>(d_counters + 4) : h->d_err_word;
+  return launch_search(h, d_queries, B, k, ef, metric, mode, entries, d_packed, nullptr, nullptr,
+                       reinterpret_cast<unsigned long long *>(d_counters), d_err, h->vis_hint, s, seg_len, seg_stride);
+}
+
 int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_t k, int32_t ef, int32_t metric,
                           int32_t mode, const int32_t *entries, int32_t *out_rows, float *out_dists,
                           int32_t *out_counts, b200hnsw_stats *stats) {

@@ -113,7 +113,8 @@ int launch_traverse(b200hnsw *h, TraverseParams &p, int vis_cap, cudaStream_t s)
 
 int launch_search(b200hnsw *h, const float *d_queries, int64_t B, int k, int ef, int metric, int mode,
                   const int32_t *entries, int32_t *d_rows, float *d_dists, int32_t *d_counts,
-                  unsigned long long *d_counters, int *d_error, int vis_cap, cudaStream_t s) {
+                  unsigned long long *d_counters, int *d_error, int vis_cap, cudaStream_t s, int64_t seg_len,
+                  int64_t seg_stride) {
   if (mode != B200HNSW_MODE_REFERENCE) {
     set_error("search: mode %d not implemented yet", mode);
     return B200HNSW_ERR_UNSUPPORTED;
@@ -131,6 +132,8 @@ int launch_search(b200hnsw *h, const float *d_queries, int64_t B, int k, int ef,
   p.out_rows = d_rows;
   p.out_dists = d_dists;
   p.out_counts = d_counts;
+  p.out_seg_len = seg_len;
+  p.out_seg_stride = seg_stride;
   p.counters = d_counters;
   p.error = d_error;
   return launch_traverse(h, p, vis_cap, s);

@@ -28,6 +28,10 @@ struct TraverseParams {
   int32_t *out_rows;    // [B][k]
   float *out_dists;     // [B][k]
   int32_t *out_counts;  // [B]
+  // segmented Search sink (out_seg_len > 0): queries are cut in runs of out_seg_len; run s writes, at
+  // out_rows + s * out_seg_stride (int32 elements): rows [seg][k] | dists f32 [seg][k] | counts [seg] -- one
+  // self-contained block per destination rank of the multi-GPU all-to-all
+  long long out_seg_len, out_seg_stride;
   // Add sink (out_rows == nullptr): results of every layer <= levels[t] go to slot slot_off[t] + layer
   const int32_t *levels;     // [B]
   const long long *slot_off; // [B]
@@ -40,6 +44,19 @@ struct TraverseParams {
   int vis_cap;                   // visited-table entries per group (power of two)
   int heap_c, heap_r, fresh_cap; // per-group slots: uint2, uint2, int
 };
+
+struct OutPtrs {
+  int32_t *rows;
+  float *dists;
+  int32_t *count;
+};
+__device__ __forceinline__ OutPtrs search_out(const TraverseParams &p, long long q) {
+  if (p.out_seg_len == 0) return {p.out_rows + q * p.k, p.out_dists + q * p.k, p.out_counts + q};
+  const long long s = q / p.out_seg_len, ql = q - s * p.out_seg_len;
+  int32_t *base = p.out_rows + s * p.out_seg_stride;
+  return {base + ql * p.k, reinterpret_cast<float *>(base + p.out_seg_len * p.k) + ql * p.k,
+          base + 2 * p.out_seg_len * p.k + ql};
+}
 
 __host__ __device__ inline size_t traverse_group_bytes(const TraverseParams &p) {
   return (size_t)(p.heap_c + p.heap_r) * 8 + (size_t)p.fresh_cap * 4 + (size_t)p.vis_cap * 4;
@@ -309,7 +326,7 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
         if (leader) {
           *p.error = 1;
           c_over++;
-          if (p.out_counts) p.out_counts[q] = -1;
+          if (p.out_rows) *search_out(p, q).count = -1;
           else p.slot_cnt[p.slot_off[q]] = -1;
         }
         st = ST_NEED;
@@ -321,12 +338,13 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
         const bool one = kcur == 1;
         if (p.out_rows) {
           if (layer == 0) {  // graph.go:588-593
+            const OutPtrs o = search_out(p, q);
             for (int i = gl; i < p.k; i += G) {
               const bool ok = i < rlen;
-              p.out_rows[q * p.k + i] = ok ? (one ? r0_id : R.id(i)) : -1;
-              p.out_dists[q * p.k + i] = ok ? (one ? r0_d : R.dist(i)) : __int_as_float(0x7fc00000);
+              o.rows[i] = ok ? (one ? r0_id : R.id(i)) : -1;
+              o.dists[i] = ok ? (one ? r0_d : R.dist(i)) : __int_as_float(0x7fc00000);
             }
-            if (leader) p.out_counts[q] = rlen;
+            if (leader) *o.count = rlen;
           }
         } else if (layer <= lvl) {  // graph.go:510: this layer takes the new node
           const long long slot = p.slot_off[q] + layer;

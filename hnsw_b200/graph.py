@@ -331,6 +331,16 @@ class Graph:
             mode, None, C.c_void_p(d_rows), C.c_void_p(d_dists), C.c_void_p(d_counts),
             C.c_void_p(d_counters) if d_counters else None, C.c_void_p(stream) if stream else None))
 
+    def search_segmented_device(self, d_queries: int, B: int, k: int, d_packed: int, seg_len: int, seg_stride: int,
+                                d_counters: int = 0, stream: int = 0, ef: Optional[int] = None,
+                                mode: int = _lib.MODE_REFERENCE):
+        """b200hnsw_search_batch_segmented_device: results of queries [s*seg_len, (s+1)*seg_len) go to the block at
+        d_packed + s*seg_stride (int32 elements) as rows | dists | counts -- the send buffer of the all-to-all."""
+        _lib.check(_lib.lib().b200hnsw_search_batch_segmented_device(
+            self._h, C.c_void_p(d_queries), B, k, ef if ef is not None else self.EfSearch, metric_of(self.Distance),
+            mode, None, C.c_void_p(d_packed), seg_len, seg_stride,
+            C.c_void_p(d_counters) if d_counters else None, C.c_void_p(stream) if stream else None))
+
     def search_host_ptrs(self, q_ptr: int, B: int, k: int, rows_ptr: int, dists_ptr: int, counts_ptr: int,
                          ef: Optional[int] = None, mode: int = _lib.MODE_REFERENCE):
         """b200hnsw_search_batch on caller-owned HOST buffers given as addresses (e.g. pinned torch tensors): the

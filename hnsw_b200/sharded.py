@@ -95,19 +95,66 @@ class PackedResults:
         return self.m_d, self.m_i, self.m_c
 
 
+class SegmentedResults:
+    """Send/receive buffers of the all-to-all layout: rank r merges the queries [r*seg, (r+1)*seg) of every batch.
+    `send` is what the search kernel writes (block s = this shard's results for the queries rank s merges: rows [seg,k] |
+    dists [seg,k] | counts [seg]); after `exchange`, `recv` block g holds shard g's results for MY queries, which is the
+    packed layout K4 reads.  Each rank moves (world-1)/world of one result set instead of receiving world-1 of them."""
+
+    def __init__(self, B: int, k: int, world: int, rank: int, device):
+        import torch
+        self.B, self.k, self.world, self.rank = B, k, world, rank
+        self.seg = (B + world - 1) // world
+        self.stride = 2 * self.seg * k + self.seg
+        self.send = torch.zeros(world * self.stride, dtype=torch.int32, device=device)  # counts of unused slots stay 0
+        self.recv = torch.zeros(world * self.stride, dtype=torch.int32, device=device)
+        self.q0 = min(B, rank * self.seg)
+        self.q1 = min(B, (rank + 1) * self.seg)
+        dev = self.send.device
+        self.m_d = torch.empty((self.seg, k), dtype=torch.float32, device=dev)
+        self.m_i = torch.empty((self.seg, k), dtype=torch.int64, device=dev)
+        self.m_c = torch.empty((self.seg,), dtype=torch.int32, device=dev)
+
+    def exchange(self, dist):
+        if self.world == 1:
+            self.recv.copy_(self.send)
+        else:
+            dist.all_to_all_single(self.recv, self.send)
+        return self.recv
+
+    def block_views(self, buf):
+        """(rows [G,seg,k] i32, dists [G,seg,k] f32, counts [G,seg] i32) views of `send` or `recv` (for checks)."""
+        import torch
+        g = buf.view(self.world, self.stride)
+        n = self.seg * self.k
+        return (g[:, :n].reshape(self.world, self.seg, self.k),
+                g[:, n:2 * n].view(torch.float32).reshape(self.world, self.seg, self.k), g[:, 2 * n:])
+
+    def merge(self, rows_per_shard: int, stream: int = 0):
+        """K4 over my query range: (dists [seg,k], global ids [seg,k], counts [seg]); rows beyond q1-q0 are padding."""
+        if self.recv.device.type != "cuda":
+            raise RuntimeError("SegmentedResults.merge needs CUDA tensors; hnsw_b200 has no CPU fallback")
+        _lib.check(_lib.lib().b200hnsw_merge_shards_device(
+            self.recv.device.index or 0, self.world, self.seg, self.k, C.c_void_p(self.recv.data_ptr()),
+            self.stride, rows_per_shard, C.c_void_p(self.m_d.data_ptr()), C.c_void_p(self.m_i.data_ptr()),
+            C.c_void_p(self.m_c.data_ptr()), C.c_void_p(stream) if stream else None))
+        return self.m_d, self.m_i, self.m_c
+
+
 class ShardPipeline:
     """Sharded batched search as a two-stage pipeline: the traversal of batch i+1 (main stream) runs while the
-    all-gather + K4 merge of batch i run on a side stream, over two PackedResults buffers.  `search` launches one
-    batch and returns at once; `merged(slot)` are the tensors the merge of that slot writes (valid after `drain`, or
-    after `done[slot]` has been waited on)."""
+    all-to-all + K4 merge of batch i run on a side stream, over two SegmentedResults buffers.  `search` launches one
+    batch and returns at once; `merged(slot)` are the tensors the merge of that slot writes for THIS rank's share of
+    the queries (valid after `drain`, or after `done[slot]` has been waited on)."""
 
     def __init__(self, graph, dist, B: int, k: int, rows_per_shard: int, device):
         import torch
         self.g, self.dist, self.B, self.k, self.n = graph, dist, B, k, rows_per_shard
         self.world = dist.get_world_size() if dist is not None else 1
+        self.rank = dist.get_rank() if dist is not None else 0
         self.main = torch.cuda.current_stream(device)
         self.side = torch.cuda.Stream(device)
-        self.buf = [PackedResults(B, k, self.world, device) for _ in range(2)]
+        self.buf = [SegmentedResults(B, k, self.world, self.rank, device) for _ in range(2)]
         self.searched = [torch.cuda.Event() for _ in range(2)]
         self.done = [torch.cuda.Event() for _ in range(2)]
         self.used = [False, False]
@@ -120,13 +167,13 @@ class ShardPipeline:
         self.step += 1
         b = self.buf[slot]
         if self.used[slot]:
-            self.main.wait_event(self.done[slot])  # the merge that last read this slot's buffers has finished
-        self.g.search_device(d_queries, self.B, self.k, b.rows.data_ptr(), b.dists.data_ptr(), b.counts.data_ptr(),
-                             d_counters, self.main.cuda_stream)
+            self.main.wait_event(self.done[slot])  # the exchange that last read this slot's send buffer has finished
+        self.g.search_segmented_device(d_queries, self.B, self.k, b.send.data_ptr(), b.seg, b.stride, d_counters,
+                                       self.main.cuda_stream)
         self.searched[slot].record(self.main)
         self.side.wait_event(self.searched[slot])
         with torch.cuda.stream(self.side):
-            b.gather(self.dist)
+            b.exchange(self.dist)
             b.merge(self.n, self.side.cuda_stream)
         self.done[slot].record(self.side)
         self.used[slot] = True

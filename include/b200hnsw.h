@@ -128,6 +128,14 @@ int b200hnsw_search_batch_device(b200hnsw_t *h, const float *d_queries, int64_t 
                                  float *d_out_dists, int32_t *d_out_counts, int64_t *d_counters /*[8] or NULL*/,
                                  void *stream);
 
+/* The same search writing a SEGMENTED result buffer for the multi-GPU all-to-all: queries are cut in runs of seg_len
+ * (the share of one destination rank); run s writes, at d_packed + s * seg_stride (int32 elements),
+ * rows int32 [seg_len][k] | dists f32 [seg_len][k] | counts int32 [seg_len] -- the layout
+ * b200hnsw_merge_shards_device reads (with B = seg_len), so one all-to-all moves every rank's share into place. */
+int b200hnsw_search_batch_segmented_device(b200hnsw_t *h, const float *d_queries, int64_t B, int32_t k, int32_t ef,
+                                           int32_t metric, int32_t mode, const int32_t *entries, int32_t *d_packed,
+                                           int64_t seg_len, int64_t seg_stride, int64_t *d_counters, void *stream);
+
 /* ---- Graph.Add / Graph.BatchAdd (graph.go:437-531, 942-1042) ------------------------------------------------
  * Inserts n nodes in input order with the reference's semantics: per layer top->0 search(k=M, ef) from the
  * elevator, then for every result (heap-array order) addNeighbor both ways with evict-worst + replenish

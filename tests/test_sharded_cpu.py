@@ -42,6 +42,22 @@ def _worker(rank, world, port, tmp):
     assert np.array_equal(p_d.numpy(), all_d.numpy(), equal_nan=True) and np.array_equal(p_c.numpy(), all_c.numpy())
     gid = np.where(p_rows.numpy() >= 0, p_rows.numpy().astype(np.int64) + np.arange(world)[:, None, None] * n, -1)
     assert np.array_equal(gid, all_i.numpy())
+    # the all-to-all layout: block s of `send` = my results for the queries rank s merges; after the exchange block g
+    # of `recv` = shard g's results for MY queries
+    sr = sharded.SegmentedResults(len(Q), k, world, rank, torch.device("cpu"))
+    s_rows, s_d, s_c = sr.block_views(sr.send)
+    for s_ in range(world):
+        a, b = s_ * sr.seg, min(len(Q), (s_ + 1) * sr.seg)
+        s_rows[s_, :b - a] = torch.from_numpy(rows[a:b])
+        s_d[s_, :b - a] = torch.from_numpy(dd[a:b])
+        s_c[s_, :b - a] = torch.from_numpy(cnt[a:b])
+    sr.exchange(dist)
+    r_rows, r_d, r_c = sr.block_views(sr.recv)
+    nq = sr.q1 - sr.q0
+    assert np.array_equal(r_d.numpy()[:, :nq], all_d.numpy()[:, sr.q0:sr.q1], equal_nan=True)
+    assert np.array_equal(r_c.numpy()[:, :nq], all_c.numpy()[:, sr.q0:sr.q1])
+    gid2 = np.where(r_rows.numpy() >= 0, r_rows.numpy().astype(np.int64) + np.arange(world)[:, None, None] * n, -1)
+    assert np.array_equal(gid2[:, :nq], all_i.numpy()[:, sr.q0:sr.q1])
     np.savez(os.path.join(tmp, f"rank{rank}.npz"), d=m[0], i=m[1], c=m[2], rows=rows, dd=dd, cnt=cnt)
     dist.barrier()
     dist.destroy_process_group()

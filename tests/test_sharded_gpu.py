@@ -1,6 +1,6 @@
 """N>1 path on GPUs (skipped with fewer than 2 devices): world_size 2 over NCCL.  Every rank builds its own sub-graph
-on its own device, the same queries go to both, and the pipelined all-gather + K4 merge (hnsw_b200.sharded.ShardPipeline)
-must return, on every rank, merge(shard results) as the numpy specification computes it in one process."""
+on its own device, the same queries go to both, and the pipelined all-to-all + K4 merge (hnsw_b200.sharded.ShardPipeline)
+must return, on rank r, merge(shard results) for r's share of the queries as the numpy specification computes it."""
 import os
 import sys
 from pathlib import Path
@@ -38,8 +38,12 @@ def _worker(rank, world, port, tmp):
         md, mi, mc = pipe.merged(slot)
         b = pipe.buf[slot]
         out[f"d{step}"], out[f"i{step}"], out[f"c{step}"] = md.cpu().numpy(), mi.cpu().numpy(), mc.cpu().numpy()
-        out[f"rows{step}"], out[f"dd{step}"], out[f"cnt{step}"] = (b.rows.cpu().numpy(), b.dists.cpu().numpy(),
-                                                                 b.counts.cpu().numpy())
+        # this shard's own results for ALL queries: the blocks of the send buffer, one per destination rank
+        r_, d_, c_ = b.block_views(b.send)
+        out[f"rows{step}"] = r_.cpu().numpy().reshape(-1, k)[:B]
+        out[f"dd{step}"] = d_.cpu().numpy().reshape(-1, k)[:B]
+        out[f"cnt{step}"] = c_.cpu().numpy().reshape(-1)[:B]
+        out["q0"], out["q1"] = b.q0, b.q1
     np.savez(os.path.join(tmp, f"rank{rank}.npz"), **out)
     dist.barrier()
     dist.destroy_process_group()
@@ -62,8 +66,10 @@ def test_two_gpu_pipeline_matches_merge_spec(tmp_path):
                           for i in range(world)])
         all_c = np.stack([r[i][f"cnt{step}"] for i in range(world)])
         m = merge_topk_ref(all_d, all_i, all_c, 10)
-        for i in range(world):  # every rank holds the same merged lists, equal to the specification's
-            assert np.array_equal(r[i][f"d{step}"], m[0], equal_nan=True)
-            assert np.array_equal(r[i][f"i{step}"], m[1])
-            assert np.array_equal(r[i][f"c{step}"], m[2])
+        for i in range(world):  # rank i holds the merged lists of its share of the queries
+            q0, q1 = int(r[i]["q0"]), int(r[i]["q1"])
+            assert q1 - q0 == 100
+            assert np.array_equal(r[i][f"d{step}"][:q1 - q0], m[0][q0:q1], equal_nan=True)
+            assert np.array_equal(r[i][f"i{step}"][:q1 - q0], m[1][q0:q1])
+            assert np.array_equal(r[i][f"c{step}"][:q1 - q0], m[2][q0:q1])
         assert (m[1] >= 3000).any() and (m[1][m[1] >= 0] < 3000).any()
