@@ -28,7 +28,8 @@ namespace b200 {
 constexpr int GM_M = 128;      // queries per CTA
 constexpr int GM_N = 256;      // rows per tile
 constexpr int GM_K = 64;       // bf16 elements per K block (128 B)
-constexpr int GM_STAGES = 3;
+constexpr int GM_STAGES = 4;
+constexpr int GM_CB = 16;  // candidates a thread stages in shared memory before it appends them to the query's list
 constexpr int GM_A_BYTES = GM_M * GM_K * 2;   // 16 KB
 constexpr int GM_B_BYTES = GM_N * GM_K * 2;   // 32 KB
 constexpr int GM_THREADS = 192;
@@ -136,7 +137,8 @@ struct GemmSmem {
   static constexpr size_t stages = (size_t)GM_STAGES * (GM_A_BYTES + GM_B_BYTES);
   static constexpr size_t slots = stages;                               // float[128][k]
   static __host__ __device__ size_t aux(int k) { return slots + (size_t)GM_M * k * 4; }   // float[2][256]
-  static __host__ __device__ size_t bars(int k) { return aux(k) + 2 * GM_N * 4; }         // 2*S + 4 barriers, tmem ptr
+  static __host__ __device__ size_t cbuf(int k) { return aux(k) + 2 * GM_N * 4; }         // int[GM_CB][128] staged candidates
+  static __host__ __device__ size_t bars(int k) { return cbuf(k) + GM_CB * GM_M * 4; }    // 2*S + 4 barriers, tmem ptr
   static __host__ __device__ size_t total(int k) { return bars(k) + 16 * 8 + 1024; }       // + alignment slack
 };
 
@@ -149,13 +151,16 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float *slots = reinterpret_cast<float *>(smem + GemmSmem::slots);
   float *aux_s = reinterpret_cast<float *>(smem + GemmSmem::aux(p.k));
+  int *cbuf = reinterpret_cast<int *>(smem + GemmSmem::cbuf(p.k));
   uint64_t *bars = reinterpret_cast<uint64_t *>(smem + GemmSmem::bars(p.k));
   uint32_t *tmem_ptr_s = reinterpret_cast<uint32_t *>(bars + 2 * GM_STAGES + 4);
   const uint32_t bar_full = smem_u32(bars), bar_empty = smem_u32(bars + GM_STAGES);
   const uint32_t bar_tfull = smem_u32(bars + 2 * GM_STAGES), bar_tempty = smem_u32(bars + 2 * GM_STAGES + 2);
   const uint32_t s_base = smem_u32(smem);
 
-  const int mt = blockIdx.y, sp = blockIdx.x;
+  // x = query tile: CTAs that are scheduled together sweep the SAME row tiles in the same order, so a row tile comes
+  // from HBM once and from L2 for every other query tile
+  const int mt = blockIdx.x, sp = blockIdx.y;
   const int t_begin = sp * p.tiles_per_split;
   const int t_end = min(p.tiles_total, t_begin + p.tiles_per_split);
   const int n_tiles = t_end - t_begin;
@@ -242,6 +247,19 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     const float INF = __int_as_float(0x7f800000);
     float thr = INF;
     int sub = 0, sl = 0;
+    // Candidates are staged per thread (cbuf[i][et], conflict-free) and appended to the query's global list a batch at
+    // a time: one atomicAdd per batch instead of one per candidate, and the whole warp flushes together so that the
+    // round trip to L2 is paid once per flush, not once per lane.
+    int *mybuf = cbuf + et;
+    int ccnt = 0;
+    auto flush = [&]() {
+      if (ccnt > 0) {
+        const int at = atomicAdd(&p.cand_cnt[q], ccnt);
+        for (int i = 0; i < ccnt; i++)
+          if (at + i < p.cand_cap) p.cand[q * p.cand_cap + at + i] = mybuf[i * GM_M];
+        ccnt = 0;
+      }
+    };
     for (int idx = 0; idx < seq; idx++) {
       const int as = idx & 1;
       const int tile = t_begin + (idx < warm ? idx : idx - warm);
@@ -280,14 +298,32 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
           m8[j] = fminf(fminf(sc[j], sc[j + 8]), fminf(sc[j + 16], sc[j + 24]));  // fminf drops NaN (dead rows)
         const float bmin = fminf(fminf(fminf(m8[0], m8[1]), fminf(m8[2], m8[3])),
                                  fminf(fminf(m8[4], m8[5]), fminf(m8[6], m8[7])));
-        if (emit && bmin <= thr) {  // rare: some row of this block passes the filter
+        if (emit && bmin <= thr) {  // some row of this block passes the filter
+          unsigned pass = 0;
 #pragma unroll
-          for (int j = 0; j < 32; j++)
-            if (sc[j] <= thr && sc[j] < INF) {  // dead rows score +inf / NaN
-              const int at = atomicAdd(&p.cand_cnt[q], 1);
-              if (at < p.cand_cap) p.cand[q * p.cand_cap + at] = tile * GM_N + c * 32 + j;
+          for (int j = 0; j < 32; j++)  // branch-free; dead rows score +inf / NaN
+            pass |= (unsigned)((sc[j] <= thr) & (sc[j] < INF)) << j;
+          const int np = __popc(pass);
+          if (ccnt + np > GM_CB) flush();
+          if (np > GM_CB) {  // only while the threshold is still loose: straight to the list
+            const int at = atomicAdd(&p.cand_cnt[q], np);
+            int i = 0;
+            while (pass) {
+              const int j = __ffs(pass) - 1;
+              pass &= pass - 1;
+              if (at + i < p.cand_cap) p.cand[q * p.cand_cap + at + i] = tile * GM_N + c * 32 + j;
+              i++;
             }
+          } else {
+            while (pass) {
+              const int j = __ffs(pass) - 1;
+              pass &= pass - 1;
+              mybuf[ccnt * GM_M] = tile * GM_N + c * 32 + j;
+              ccnt++;
+            }
+          }
         }
+        if (__any_sync(FULL, ccnt >= GM_CB / 2)) flush();
         // slot `sub mod k` holds the minimum over a set of rows disjoint from every other slot's set
         my_slots[sl] = fminf(my_slots[sl], bmin);
         if (++sl == p.k) sl = 0;
@@ -315,6 +351,7 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         thr = fminf(thr, tau + margin);
       }
     }
+    flush();
   }
   tc_fence_before();
   __syncthreads();
@@ -505,7 +542,7 @@ int exact_candidates_tensor(b200exact *x, const float *d_queries, int64_t B, int
   splits = (p.tiles_total + p.tiles_per_split - 1) / p.tiles_per_split;
   auto kern = x->metric == 0 ? exact_gemm_kernel<0> : exact_gemm_kernel<1>;
   B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  dim3 grid((unsigned)splits, (unsigned)m_tiles);
+  dim3 grid((unsigned)m_tiles, (unsigned)splits);
   kern<<<grid, GM_THREADS, smem, s>>>(tq, *(CUtensorMap *)x->tmap_x, p);
   B200_CUDA(cudaGetLastError());
   return 0;

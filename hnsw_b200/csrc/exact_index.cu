@@ -97,6 +97,11 @@ __global__ void __launch_bounds__(SCAN_THREADS) exact_rerank_kernel(const float4
   const long long q = blockIdx.x;
   int cnt = cand_cnt[q];
   if (cnt > cand_cap) cnt = cand_cap;  // overflowed queries are redone by the scan path (host checks the count)
+  {  // sort only as many keys as this query has (n_pow2 is the capacity the launch reserved)
+    int need = 2;
+    while (need < cnt || need < k) need <<= 1;
+    n_pow2 = min(n_pow2, need);
+  }
   for (int i = threadIdx.x; i < n_pow2; i += blockDim.x) skeys[i] = ~0ull;
   __syncthreads();
   GQuery<CH> Q;
