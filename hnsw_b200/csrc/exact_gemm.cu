@@ -15,7 +15,7 @@
 // (tcgen05.ld 32x32b, one query row per thread).  Accumulators are double-buffered in TMEM (2 x 256 columns).
 // Bound: tensor pipe (2*B*N*dim flop) for B >~ 300 queries, HBM (2*N*dim bytes of bf16 rows) below.
 #include <cuda.h>
-#include <cuda_bf16.h>
+#include <cuda_fp16.h>
 
 #include <algorithm>
 #include <cmath>
@@ -95,7 +95,17 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
         "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
         "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
       : "r"(taddr));
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+// the loaded registers are operands of the wait, so no use of them can be scheduled ahead of it
+__device__ __forceinline__ void tmem_ld_wait(uint32_t (&v)[32]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]),
+                 "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15]),
+                 "+r"(v[16]), "+r"(v[17]), "+r"(v[18]), "+r"(v[19]), "+r"(v[20]), "+r"(v[21]), "+r"(v[22]),
+                 "+r"(v[23]), "+r"(v[24]), "+r"(v[25]), "+r"(v[26]), "+r"(v[27]), "+r"(v[28]), "+r"(v[29]),
+                 "+r"(v[30]), "+r"(v[31])
+               :
+               : "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -107,10 +117,10 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
   return (uint64_t)((saddr & 0x3ffffu) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) |
          ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
 }
-// kind::f16 instruction descriptor: D = F32 (bits 4-5 = 1), A = B = BF16 (bits 7-9, 10-12 = 1), both K-major,
-// N >> 3 in bits 17-22, M >> 4 in bits 24-28
-constexpr uint32_t GM_IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(GM_N >> 3) << 17) |
-                              ((uint32_t)(GM_M >> 4) << 24);
+// kind::f16 instruction descriptor: D = F32 (bits 4-5 = 1), A = B = F16 (bits 7-9, 10-12 = 0), both K-major,
+// N >> 3 in bits 17-22, M >> 4 in bits 24-28.  fp16, not bf16: 11 significand bits make the provable error bound of a
+// score 8x tighter, which is what decides how many candidates the fp32 re-rank has to read.
+constexpr uint32_t GM_IDESC = (1u << 4) | ((uint32_t)(GM_N >> 3) << 17) | ((uint32_t)(GM_M >> 4) << 24);
 
 __device__ __forceinline__ uint32_t ord_bits(float d) {
   uint32_t u = __float_as_uint(d);
@@ -125,7 +135,7 @@ struct GemmParams {
   const float *aux;        // [cap] |x|^2 (Euclidean) or 1/|x| (cosine); +inf / NaN for dead rows
   int metric, kblocks, tiles_total, tiles_per_split, warm_tiles, k;
   long long B;
-  const float *q_inv;      // [Bpad] 1/|q| (cosine)
+  const float *q_inv;      // [Bpad] Euclidean: -2 * 2^-(sx+sq); cosine: -2^-(sx+sq) / |q|  (sx, sq: operand scales)
   const float *q_margin;   // [Bpad] 2 * eps_q
   uint32_t *slots_g;       // [Bpad][k] order-preserving bits of the slot minima merged over all CTAs of a query
   int32_t *cand;           // [B][cand_cap]
@@ -243,7 +253,7 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     float *my_slots = slots + (size_t)r * p.k;
     for (int j = 0; j < p.k; j++) my_slots[j] = __int_as_float(0x7f800000);
     const float margin = live_q ? p.q_margin[q] : 0.f;
-    const float nqinv = (live_q && METRIC == 1) ? -p.q_inv[q] : 0.f;
+    const float qf = live_q ? p.q_inv[q] : 0.f;  // turns the accumulator into -2 q.x (Euclidean) or -q.x/|q| (cosine)
     const float INF = __int_as_float(0x7f800000);
     float thr = INF;
     int sub = 0, sl = 0;
@@ -260,36 +270,51 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         ccnt = 0;
       }
     };
+    // per-row terms of tile 0; those of tile idx+1 are fetched while tile idx is processed
+    auto tile_of = [&](int idx) { return t_begin + (idx < warm ? idx : idx - warm); };
+    if (seq > 0) {
+      aux_s[et] = p.aux[(long long)tile_of(0) * GM_N + et];
+      aux_s[et + 128] = p.aux[(long long)tile_of(0) * GM_N + et + 128];
+    }
+    asm volatile("bar.sync 1, 128;" ::: "memory");
     for (int idx = 0; idx < seq; idx++) {
       const int as = idx & 1;
-      const int tile = t_begin + (idx < warm ? idx : idx - warm);
+      const int tile = tile_of(idx);
       const bool emit = live_q && idx >= warm;
-      // stage the tile's per-row terms (the previous use of this buffer ended two tiles ago)
       float *ax = aux_s + as * GM_N;
-      ax[et] = p.aux[(long long)tile * GM_N + et];
-      ax[et + 128] = p.aux[(long long)tile * GM_N + et + 128];
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      float nx0 = 0.f, nx1 = 0.f;
+      if (idx + 1 < seq) {
+        nx0 = p.aux[(long long)tile_of(idx + 1) * GM_N + et];
+        nx1 = p.aux[(long long)tile_of(idx + 1) * GM_N + et + 128];
+      }
       mbar_wait(bar_tfull + 8 * as, (idx >> 1) & 1);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + as * GM_N;
-      for (int c = 0; c < GM_N / 32; c++) {
-        uint32_t v[32];
-        tmem_ld32(taddr + c * 32, v);
+      uint32_t va[32], vb[32];
+      tmem_ld32(taddr, va);
+#pragma unroll 1
+      for (int c2 = 0; c2 < GM_N / 64; c2++) {
+#pragma unroll
+        for (int half = 0; half < 2; half++) {
+        const int c = 2 * c2 + half;
+        uint32_t (&v)[32] = half == 0 ? va : vb;
+        tmem_ld_wait(v);  // chunk c has landed; chunk c+1 is requested before c is looked at
+        if (c + 1 < GM_N / 32) tmem_ld32(taddr + (c + 1) * 32, half == 0 ? vb : va);
         const float4 *ax4 = reinterpret_cast<const float4 *>(ax + c * 32);
         float sc[32];
 #pragma unroll
         for (int j4 = 0; j4 < 8; j4++) {  // 32 independent scores: no branch, no dependent chain
           const float4 a = ax4[j4];
           if (METRIC == 0) {
-            sc[4 * j4 + 0] = fmaf(-2.f, __uint_as_float(v[4 * j4 + 0]), a.x);
-            sc[4 * j4 + 1] = fmaf(-2.f, __uint_as_float(v[4 * j4 + 1]), a.y);
-            sc[4 * j4 + 2] = fmaf(-2.f, __uint_as_float(v[4 * j4 + 2]), a.z);
-            sc[4 * j4 + 3] = fmaf(-2.f, __uint_as_float(v[4 * j4 + 3]), a.w);
+            sc[4 * j4 + 0] = fmaf(qf, __uint_as_float(v[4 * j4 + 0]), a.x);
+            sc[4 * j4 + 1] = fmaf(qf, __uint_as_float(v[4 * j4 + 1]), a.y);
+            sc[4 * j4 + 2] = fmaf(qf, __uint_as_float(v[4 * j4 + 2]), a.z);
+            sc[4 * j4 + 3] = fmaf(qf, __uint_as_float(v[4 * j4 + 3]), a.w);
           } else {
-            sc[4 * j4 + 0] = fmaf(__uint_as_float(v[4 * j4 + 0]) * a.x, nqinv, 1.f);
-            sc[4 * j4 + 1] = fmaf(__uint_as_float(v[4 * j4 + 1]) * a.y, nqinv, 1.f);
-            sc[4 * j4 + 2] = fmaf(__uint_as_float(v[4 * j4 + 2]) * a.z, nqinv, 1.f);
-            sc[4 * j4 + 3] = fmaf(__uint_as_float(v[4 * j4 + 3]) * a.w, nqinv, 1.f);
+            sc[4 * j4 + 0] = fmaf(__uint_as_float(v[4 * j4 + 0]) * a.x, qf, 1.f);
+            sc[4 * j4 + 1] = fmaf(__uint_as_float(v[4 * j4 + 1]) * a.y, qf, 1.f);
+            sc[4 * j4 + 2] = fmaf(__uint_as_float(v[4 * j4 + 2]) * a.z, qf, 1.f);
+            sc[4 * j4 + 3] = fmaf(__uint_as_float(v[4 * j4 + 3]) * a.w, qf, 1.f);
           }
         }
         float m8[8];
@@ -328,10 +353,15 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         my_slots[sl] = fminf(my_slots[sl], bmin);
         if (++sl == p.k) sl = 0;
         sub++;
+        }
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
+      // next tile's terms into the other buffer (its previous readers finished before the barrier of the last tile)
+      aux_s[(as ^ 1) * GM_N + et] = nx0;
+      aux_s[(as ^ 1) * GM_N + et + 128] = nx1;
+      asm volatile("bar.sync 1, 128;" ::: "memory");
       if (sub >= p.k && live_q) {
         // Now and then (often at first, when bounds improve fast) merge the slots with those of the other CTAs that
         // work on this query: slot j of every CTA covers rows disjoint from slot j' of any CTA, so the element-wise
@@ -363,58 +393,105 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 
 
 // ---- preparation kernels ---------------------------------------------------------------------------------------------
-// rows [first, first+count): bf16 copy (zero padded to kpad), |x|^2 / 1/|x|, running max of |x|^2
-__global__ void exact_xprep_kernel(const float *vec, int row_floats, int dim, int kpad, long long first,
-                                   long long count, int metric, __nv_bfloat16 *vech, float *aux, uint32_t *maxn2) {
+// stats[0] = bits of max |x|^2, stats[1] = bits of min |x|^2 over rows with |x| > 0, stats[2] = bits of max |x_i|
+// rows [first, first+count): |x|^2 -> aux (Euclidean) or 1/|x| (cosine), running statistics
+__global__ void exact_xstats_kernel(const float *vec, int row_floats, int dim, long long first, long long count,
+                                    int metric, float *aux, uint32_t *stats) {
   const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (w >= count) return;
   const long long row = first + w;
   const float *src = vec + row * row_floats;
-  __nv_bfloat16 *dst = vech + row * kpad;
-  float acc = 0.f;
-  for (int i = lane; i < kpad; i += 32) {
-    float v = i < dim ? src[i] : 0.f;
+  float acc = 0.f, mx = 0.f;
+  for (int i = lane; i < dim; i += 32) {
+    const float v = src[i];
     acc = fmaf(v, v, acc);
-    dst[i] = __float2bfloat16_rn(v);
+    mx = fmaxf(mx, fabsf(v));
   }
 #pragma unroll
-  for (int off = 16; off >= 1; off >>= 1) acc += __shfl_xor_sync(FULL, acc, off);
+  for (int off = 16; off >= 1; off >>= 1) {
+    acc += __shfl_xor_sync(FULL, acc, off);
+    mx = fmaxf(mx, __shfl_xor_sync(FULL, mx, off));
+  }
   if (lane == 0) {
     aux[row] = metric == 0 ? acc : 1.0f / sqrtf(acc);  // a zero vector gives inf: its score is NaN, never a candidate
-    atomicMax(maxn2, __float_as_uint(acc));             // non-negative floats order like their bit patterns
+    atomicMax(&stats[0], __float_as_uint(acc));         // non-negative floats order like their bit patterns
+    if (acc > 0.f) atomicMin(&stats[1], __float_as_uint(acc));
+    if (mx < __int_as_float(0x7f800000)) atomicMax(&stats[2], __float_as_uint(mx));
   }
+}
+// rows [first, first+count): fp16 copy of x * 2^sx_exp, zero padded to kpad
+__global__ void exact_xconv_kernel(const float *vec, int row_floats, int dim, int kpad, long long first,
+                                   long long count, int sx_exp, __half *vech) {
+  const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (w >= count) return;
+  const long long row = first + w;
+  const float *src = vec + row * row_floats;
+  __half *dst = vech + row * kpad;
+  for (int i = lane; i < kpad; i += 32) dst[i] = __float2half_rn(i < dim ? ldexpf(src[i], sx_exp) : 0.f);
 }
 __global__ void exact_fill_kernel(float *p, long long n, float v) {
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) p[i] = v;
 }
-// queries: bf16 copy into Qh[Bpad][kpad], 1/|q|, filter margin 2*eps_q, tau = +inf, candidate count = 0
+// queries: fp16 copy of q * 2^sq (sq per query: the largest component lands in [2^13, 2^14)) into Qh[Bpad][kpad],
+// the factor that turns an accumulator into the score's dot term, the filter margin 2*eps_q, tau = +inf, count = 0.
+//
+// Error of a score.  With X = x 2^sx, Q = q 2^sq, u = 2^-11 and nu = 2^-25 (half the fp16 subnormal spacing) every
+// converted operand satisfies |fp16(X_i) - X_i| <= u |X_i| + nu, products of fp16 numbers are exact in fp32, and the
+// fp32 accumulation of kpad of them loses at most (kpad + 64) 2^-22 of sum |X_i Q_i|.  Hence, in the units of x.q:
+//   |D' 2^-(sx+sq) - x.q| <= g |x||q| + nu (1+u) sqrt(kpad) (|x| 2^-sq + |q| 2^-sx) + kpad nu^2 2^-(sx+sq),
+//   g = (2u + u^2) + (kpad + 64) 2^-22
+// (Cauchy-Schwarz for sum |x_i||q_i| and for the 1-norms).  The Euclidean score |x|^2 - 2 x.q inherits twice that with
+// |x| <= xmax; the cosine score 1 - x.q/(|x||q|) inherits it divided by |x||q| with |x| >= xmin.  `fp32` covers the
+// difference between the canonical fp32 distance and exact arithmetic, and the epilogue's own roundings.
 __global__ void exact_qprep_kernel(const float *q, long long B, long long Bpad, int dim, int kpad, int metric,
-                                   const uint32_t *maxn2, __nv_bfloat16 *qh, float *q_inv, float *q_margin,
+                                   const uint32_t *stats, int sx_exp, __half *qh, float *q_fac, float *q_margin,
                                    uint32_t *slots_g, int k, int32_t *cand_cnt) {
   const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (w >= Bpad) return;
   const bool live = w < B;
-  float acc = 0.f;
-  for (int i = lane; i < kpad; i += 32) {
-    float v = (live && i < dim) ? q[w * dim + i] : 0.f;
+  float acc = 0.f, mx = 0.f;
+  for (int i = lane; i < dim; i += 32) {
+    const float v = live ? q[w * dim + i] : 0.f;
     acc = fmaf(v, v, acc);
-    qh[w * kpad + i] = __float2bfloat16_rn(v);
+    mx = fmaxf(mx, fabsf(v));
   }
 #pragma unroll
-  for (int off = 16; off >= 1; off >>= 1) acc += __shfl_xor_sync(FULL, acc, off);
+  for (int off = 16; off >= 1; off >>= 1) {
+    acc += __shfl_xor_sync(FULL, acc, off);
+    mx = fmaxf(mx, __shfl_xor_sync(FULL, mx, off));
+  }
+  int sq_exp = 0;
+  if (mx > 0.f && mx < __int_as_float(0x7f800000)) {
+    int e;
+    frexpf(mx, &e);  // mx = m 2^e, m in [0.5, 1)
+    sq_exp = 14 - e;
+  }
+  sq_exp = max(-100 - sx_exp, min(100 - sx_exp, sq_exp));  // keep 2^-(sx+sq) a normal float
+  for (int i = lane; i < kpad; i += 32)
+    qh[w * kpad + i] = __float2half_rn((live && i < dim) ? ldexpf(q[w * dim + i], sq_exp) : 0.f);
   if (lane == 0) {
-    const float qn = sqrtf(acc), xmax = sqrtf(__uint_as_float(*maxn2));
-    // |D - x.q| <= gamma |x||q|: two bf16 roundings (2^-8 each, RN) and the fp32 accumulation of kpad products
-    const float gamma = 0.0078125f * 1.01f + (float)(kpad + 64) * 2.3841858e-7f;
-    const float fp32 = (float)(dim / 8 + 64) * 5.9604645e-8f;  // canonical fp32 distance vs exact arithmetic
+    const float qn = sqrtf(acc), xmax = sqrtf(__uint_as_float(stats[0])), xmin = sqrtf(__uint_as_float(stats[1]));
+    const float u = 4.8828125e-4f, nu = 2.9802322e-8f;
+    const float g = (2.f * u + u * u) * 1.01f + (float)(kpad + 64) * 2.3841858e-7f;
+    const float isx = ldexpf(1.f, -sx_exp), isq = ldexpf(1.f, -sq_exp);
+    const float sub = nu * (1.f + u) * sqrtf((float)kpad);  // subnormal part, per unit of |.| 2^-scale
+    const float fp32 = (float)(dim / 8 + 64) * 5.9604645e-8f;
+    const float dsc = ldexpf(1.f, -(sx_exp + sq_exp));
     float eps;
-    if (metric == 0) eps = 2.f * gamma * xmax * qn + fp32 * (xmax + qn) * (xmax + qn);
-    else eps = gamma * 1.001f + fp32;
-    q_inv[w] = 1.0f / qn;
-    q_margin[w] = 2.f * eps * 1.001f;
+    if (metric == 0) {
+      const float e_dot = g * xmax * qn + sub * (xmax * isq + qn * isx) + (float)kpad * nu * nu * dsc;
+      eps = 2.f * e_dot + fp32 * (xmax + qn) * (xmax + qn);
+      q_fac[w] = -2.f * dsc;
+    } else {
+      // divided by |x||q| with |x| >= xmin; a query of norm 0 scores NaN everywhere and selects nothing
+      eps = g + sub * (isq / qn + isx / xmin) + (float)kpad * nu * nu * dsc / (xmin * qn) + fp32;
+      q_fac[w] = -dsc / qn;
+    }
+    q_margin[w] = 2.f * eps * 1.01f;
     if (live) cand_cnt[w] = 0;
   }
   for (int j = lane; j < k; j += 32) slots_g[w * k + j] = 0xff800000u;  // ord_bits(+inf)
@@ -435,7 +512,7 @@ static encode_tiled_fn get_encoder() {
   }
   return fn;
 }
-// bf16 matrix [rows][kpad], box = 64 elements (128 B) x box_rows, 128 B swizzle
+// fp16 matrix [rows][kpad], box = 64 elements (128 B) x box_rows, 128 B swizzle
 static int make_tmap(CUtensorMap *m, void *base, uint64_t rows, uint64_t kpad, uint32_t box_rows) {
   encode_tiled_fn enc = get_encoder();
   if (!enc) {
@@ -446,7 +523,7 @@ static int make_tmap(CUtensorMap *m, void *base, uint64_t rows, uint64_t kpad, u
   cuuint64_t gstride[1] = {kpad * 2};
   cuuint32_t box[2] = {GM_K, box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, base, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("exact: cuTensorMapEncodeTiled failed (%d)", (int)r);
@@ -458,7 +535,9 @@ static int make_tmap(CUtensorMap *m, void *base, uint64_t rows, uint64_t kpad, u
 int exact_after_add(b200exact *x, int64_t first, int64_t count, cudaStream_t s) {
   if (!x->d_maxn2) {
     B200_CUDA(cudaMalloc(&x->d_maxn2, 64));
+    const uint32_t init[3] = {0u, 0x7f800000u, 0u};  // max |x|^2, min |x|^2 > 0, max |x_i|
     B200_CUDA(cudaMemsetAsync(x->d_maxn2, 0, 64, s));
+    B200_CUDA(cudaMemcpyAsync(x->d_maxn2, init, sizeof init, cudaMemcpyHostToDevice, s));
   }
   if (x->aux_dead_cap != x->cap) {  // storage grew: rows that do not exist yet must never become candidates
     const float dead = x->metric == 0 ? __builtin_inff() : __builtin_nanf("");
@@ -467,9 +546,29 @@ int exact_after_add(b200exact *x, int64_t first, int64_t count, cudaStream_t s) 
     x->aux_dead_cap = x->cap;
   }
   long long threads = count * 32;
-  exact_xprep_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(x->d_vec, x->row_floats, x->dim, x->kpad, first,
-                                                                        count, x->metric, x->d_vech, x->d_aux,
-                                                                        x->d_maxn2);
+  exact_xstats_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(x->d_vec, x->row_floats, x->dim, first, count,
+                                                                         x->metric, x->d_aux, x->d_maxn2);
+  // the fp16 copy is scaled by a power of two chosen from the largest component seen so far (three binades of
+  // headroom below fp16's 2^15); a later batch that does not fit re-converts everything under a new scale
+  uint32_t st[3];
+  B200_CUDA(cudaMemcpyAsync(st, x->d_maxn2, sizeof st, cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaStreamSynchronize(s));
+  float mx;
+  memcpy(&mx, &st[2], 4);
+  long long conv_first = first, conv_count = count;
+  if (!x->have_scale || ldexpf(mx, x->sx_exp) > 32768.f) {
+    int e = 0;
+    if (mx > 0.f) frexpf(mx, &e);  // mx = m 2^e, m in [0.5, 1)
+    x->sx_exp = mx > 0.f ? 12 - e : 0;
+    if (x->sx_exp > 100) x->sx_exp = 100;
+    if (x->sx_exp < -100) x->sx_exp = -100;
+    x->have_scale = true;
+    conv_first = 0;
+    conv_count = first + count;
+  }
+  threads = conv_count * 32;
+  exact_xconv_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(x->d_vec, x->row_floats, x->dim, x->kpad,
+                                                                        conv_first, conv_count, x->sx_exp, x->d_vech);
   B200_CUDA(cudaGetLastError());
   return 0;
 }
@@ -490,7 +589,7 @@ int exact_candidates_tensor(b200exact *x, const float *d_queries, int64_t B, int
     x->gemm_ws_bytes = need;
   }
   char *w = (char *)x->d_gemm_ws;
-  __nv_bfloat16 *qh = (__nv_bfloat16 *)w;
+  __half *qh = (__half *)w;
   w += al(2 * (size_t)Bpad * x->kpad);
   float *q_inv = (float *)w;
   w += al(4 * (size_t)Bpad);
@@ -498,7 +597,7 @@ int exact_candidates_tensor(b200exact *x, const float *d_queries, int64_t B, int
   w += al(4 * (size_t)Bpad);
   uint32_t *slots_g = (uint32_t *)w;
   exact_qprep_kernel<<<(unsigned)((Bpad * 32 + 255) / 256), 256, 0, s>>>(d_queries, B, Bpad, x->dim, x->kpad, x->metric,
-                                                                          x->d_maxn2, qh, q_inv, q_margin, slots_g,
+                                                                          x->d_maxn2, x->sx_exp, qh, q_inv, q_margin, slots_g,
                                                                           k, d_cand_cnt);
   B200_CUDA(cudaGetLastError());
   int rc;
