@@ -28,11 +28,13 @@ namespace b200 {
 constexpr int GM_M = 128;      // queries per CTA
 constexpr int GM_N = 256;      // rows per tile
 constexpr int GM_K = 64;       // bf16 elements per K block (128 B)
-constexpr int GM_STAGES = 4;
-constexpr int GM_CB = 16;  // candidates a thread stages in shared memory before it appends them to the query's list
+constexpr int GM_STAGES = 4;  // at most; 3 when k is large (GemmParams::stages)
+constexpr int GM_CB = 8;   // candidates a thread stages in shared memory before it appends them to the query's list
 constexpr int GM_A_BYTES = GM_M * GM_K * 2;   // 16 KB
 constexpr int GM_B_BYTES = GM_N * GM_K * 2;   // 32 KB
-constexpr int GM_THREADS = 192;
+constexpr int GM_EPI_WARPS = 8;  // two per TMEM lane quarter, each takes half of the tile's columns
+constexpr int GM_EPI = GM_EPI_WARPS * 32;
+constexpr int GM_THREADS = 64 + GM_EPI;
 constexpr int GM_MAX_K = 64;   // result size the slot table supports
 
 // ---- PTX wrappers ---------------------------------------------------------------------------------------------------
@@ -133,7 +135,7 @@ __device__ __forceinline__ float ord_float(uint32_t k) {
 
 struct GemmParams {
   const float *aux;        // [cap] |x|^2 (Euclidean) or 1/|x| (cosine); +inf / NaN for dead rows
-  int metric, kblocks, tiles_total, tiles_per_split, warm_tiles, k;
+  int metric, kblocks, tiles_total, tiles_per_split, warm_tiles, k, stages;
   long long B;
   const float *q_inv;      // [Bpad] Euclidean: -2 * 2^-(sx+sq); cosine: -2^-(sx+sq) / |q|  (sx, sq: operand scales)
   const float *q_margin;   // [Bpad] 2 * eps_q
@@ -143,13 +145,12 @@ struct GemmParams {
   int cand_cap;
 };
 
-struct GemmSmem {
-  static constexpr size_t stages = (size_t)GM_STAGES * (GM_A_BYTES + GM_B_BYTES);
-  static constexpr size_t slots = stages;                               // float[128][k]
-  static __host__ __device__ size_t aux(int k) { return slots + (size_t)GM_M * k * 4; }   // float[2][256]
-  static __host__ __device__ size_t cbuf(int k) { return aux(k) + 2 * GM_N * 4; }         // int[GM_CB][128] staged candidates
-  static __host__ __device__ size_t bars(int k) { return cbuf(k) + GM_CB * GM_M * 4; }    // 2*S + 4 barriers, tmem ptr
-  static __host__ __device__ size_t total(int k) { return bars(k) + 16 * 8 + 1024; }       // + alignment slack
+struct GemmSmem {  // S = number of operand stages
+  static __host__ __device__ size_t slots(int S) { return (size_t)S * (GM_A_BYTES + GM_B_BYTES); }  // float[GM_EPI][k]
+  static __host__ __device__ size_t aux(int S, int k) { return slots(S) + (size_t)GM_EPI * k * 4; }  // float[2][256]
+  static __host__ __device__ size_t cbuf(int S, int k) { return aux(S, k) + 2 * GM_N * 4; }  // int[GM_CB][GM_EPI]
+  static __host__ __device__ size_t bars(int S, int k) { return cbuf(S, k) + GM_CB * GM_EPI * 4; }  // barriers, tmem ptr
+  static __host__ __device__ size_t total(int S, int k) { return bars(S, k) + 16 * 8 + 1024; }      // + alignment slack
 };
 
 template <int METRIC>
@@ -159,10 +160,11 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
   extern __shared__ unsigned char smem_raw[];
   unsigned char *smem = reinterpret_cast<unsigned char *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float *slots = reinterpret_cast<float *>(smem + GemmSmem::slots);
-  float *aux_s = reinterpret_cast<float *>(smem + GemmSmem::aux(p.k));
-  int *cbuf = reinterpret_cast<int *>(smem + GemmSmem::cbuf(p.k));
-  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + GemmSmem::bars(p.k));
+  const int S = p.stages;
+  float *slots = reinterpret_cast<float *>(smem + GemmSmem::slots(S));
+  float *aux_s = reinterpret_cast<float *>(smem + GemmSmem::aux(S, p.k));
+  int *cbuf = reinterpret_cast<int *>(smem + GemmSmem::cbuf(S, p.k));
+  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + GemmSmem::bars(S, p.k));
   uint32_t *tmem_ptr_s = reinterpret_cast<uint32_t *>(bars + 2 * GM_STAGES + 4);
   const uint32_t bar_full = smem_u32(bars), bar_empty = smem_u32(bars + GM_STAGES);
   const uint32_t bar_tfull = smem_u32(bars + 2 * GM_STAGES), bar_tempty = smem_u32(bars + 2 * GM_STAGES + 2);
@@ -178,13 +180,13 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
   const int seq = n_tiles > 0 ? warm + n_tiles : 0;  // warm-up tiles are visited twice: first only to bound tau
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < GM_STAGES; i++) {
+    for (int i = 0; i < S; i++) {
       mbar_init(bar_full + 8 * i, 1);
       mbar_init(bar_empty + 8 * i, 1);
     }
     for (int i = 0; i < 2; i++) {
       mbar_init(bar_tfull + 8 * i, 1);
-      mbar_init(bar_tempty + 8 * i, 4);
+      mbar_init(bar_tempty + 8 * i, GM_EPI_WARPS);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -210,7 +212,7 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
           mbar_expect_tx(bar_full + 8 * stage, GM_A_BYTES + GM_B_BYTES);
           tma_load_2d(sa, &tmap_q, kb * GM_K, mt * GM_M, bar_full + 8 * stage);
           tma_load_2d(sb, &tmap_x, kb * GM_K, tile * GM_N, bar_full + 8 * stage);
-          if (++stage == GM_STAGES) {
+          if (++stage == S) {
             stage = 0;
             phase ^= 1;
           }
@@ -235,7 +237,7 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
           for (int k4 = 0; k4 < GM_K / 16; k4++)  // UMMA K = 16 bf16 = 32 B: advance the start address field by 2
             umma_bf16(tmem_d, adesc + 2 * k4, bdesc + 2 * k4, GM_IDESC, (kb | k4) != 0);
           umma_commit(bar_empty + 8 * stage);  // frees the smem stage when these MMAs retire
-          if (++stage == GM_STAGES) {
+          if (++stage == S) {
             stage = 0;
             phase ^= 1;
           }
@@ -249,8 +251,9 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     const int r = ew * 32 + lane;             // row of the tile = TMEM lane
     const long long q = (long long)mt * GM_M + r;
     const bool live_q = q < p.B;
-    const int et = (warp - 2) * 32 + lane;    // 0..127 among the epilogue threads
-    float *my_slots = slots + (size_t)r * p.k;
+    const int et = (warp - 2) * 32 + lane;    // 0..GM_EPI-1 among the epilogue threads
+    const int ch0 = ((warp - 2) >> 2) * (GM_N / 64);  // first 32-column chunk of this warp's half of the tile
+    float *my_slots = slots + (size_t)et * p.k;
     for (int j = 0; j < p.k; j++) my_slots[j] = __int_as_float(0x7f800000);
     const float margin = live_q ? p.q_margin[q] : 0.f;
     const float qf = live_q ? p.q_inv[q] : 0.f;  // turns the accumulator into -2 q.x (Euclidean) or -q.x/|q| (cosine)
@@ -266,7 +269,7 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       if (ccnt > 0) {
         const int at = atomicAdd(&p.cand_cnt[q], ccnt);
         for (int i = 0; i < ccnt; i++)
-          if (at + i < p.cand_cap) p.cand[q * p.cand_cap + at + i] = mybuf[i * GM_M];
+          if (at + i < p.cand_cap) p.cand[q * p.cand_cap + at + i] = mybuf[i * GM_EPI];
         ccnt = 0;
       }
     };
@@ -274,32 +277,28 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     auto tile_of = [&](int idx) { return t_begin + (idx < warm ? idx : idx - warm); };
     if (seq > 0) {
       aux_s[et] = p.aux[(long long)tile_of(0) * GM_N + et];
-      aux_s[et + 128] = p.aux[(long long)tile_of(0) * GM_N + et + 128];
     }
-    asm volatile("bar.sync 1, 128;" ::: "memory");
+    asm volatile("bar.sync 1, %0;" ::"n"(GM_EPI) : "memory");
     for (int idx = 0; idx < seq; idx++) {
       const int as = idx & 1;
       const int tile = tile_of(idx);
       const bool emit = live_q && idx >= warm;
       float *ax = aux_s + as * GM_N;
-      float nx0 = 0.f, nx1 = 0.f;
-      if (idx + 1 < seq) {
-        nx0 = p.aux[(long long)tile_of(idx + 1) * GM_N + et];
-        nx1 = p.aux[(long long)tile_of(idx + 1) * GM_N + et + 128];
-      }
+      float nx0 = 0.f;
+      if (idx + 1 < seq) nx0 = p.aux[(long long)tile_of(idx + 1) * GM_N + et];
       mbar_wait(bar_tfull + 8 * as, (idx >> 1) & 1);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + as * GM_N;
       uint32_t va[32], vb[32];
-      tmem_ld32(taddr, va);
+      tmem_ld32(taddr + ch0 * 32, va);
 #pragma unroll 1
-      for (int c2 = 0; c2 < GM_N / 64; c2++) {
+      for (int c2 = 0; c2 < GM_N / 128; c2++) {
 #pragma unroll
         for (int half = 0; half < 2; half++) {
-        const int c = 2 * c2 + half;
+        const int c = ch0 + 2 * c2 + half;
         uint32_t (&v)[32] = half == 0 ? va : vb;
         tmem_ld_wait(v);  // chunk c has landed; chunk c+1 is requested before c is looked at
-        if (c + 1 < GM_N / 32) tmem_ld32(taddr + (c + 1) * 32, half == 0 ? vb : va);
+        if (c + 1 < ch0 + GM_N / 64) tmem_ld32(taddr + (c + 1) * 32, half == 0 ? vb : va);
         const float4 *ax4 = reinterpret_cast<const float4 *>(ax + c * 32);
         float sc[32];
 #pragma unroll
@@ -343,7 +342,7 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
             while (pass) {
               const int j = __ffs(pass) - 1;
               pass &= pass - 1;
-              mybuf[ccnt * GM_M] = tile * GM_N + c * 32 + j;
+              mybuf[ccnt * GM_EPI] = tile * GM_N + c * 32 + j;
               ccnt++;
             }
           }
@@ -360,14 +359,13 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
       // next tile's terms into the other buffer (its previous readers finished before the barrier of the last tile)
       aux_s[(as ^ 1) * GM_N + et] = nx0;
-      aux_s[(as ^ 1) * GM_N + et + 128] = nx1;
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      asm volatile("bar.sync 1, %0;" ::"n"(GM_EPI) : "memory");
       if (sub >= p.k && live_q) {
         // Now and then (often at first, when bounds improve fast) merge the slots with those of the other CTAs that
         // work on this query: slot j of every CTA covers rows disjoint from slot j' of any CTA, so the element-wise
         // minimum over CTAs is again k minima over k disjoint row sets.
         const int done = idx + 1;
-        if (sub - GM_N / 32 < p.k || (done & (done - 1)) == 0 || (done & 31) == 0 || idx == seq - 1) {
+        if (sub - GM_N / 64 < p.k || (done & (done - 1)) == 0 || (done & 31) == 0 || idx == seq - 1) {
           uint32_t *sg = p.slots_g + q * p.k;
           for (int j = 0; j < p.k; j++) {
             const uint32_t mine = ord_bits(my_slots[j]);
@@ -576,7 +574,9 @@ int exact_after_add(b200exact *x, int64_t first, int64_t count, cudaStream_t s) 
 int exact_candidates_tensor(b200exact *x, const float *d_queries, int64_t B, int k, int32_t *d_cand,
                             int32_t *d_cand_cnt, int cand_cap, cudaStream_t s) {
   if (k > GM_MAX_K) return B200HNSW_ERR_UNSUPPORTED;  // the slot table is sized for k <= 64: the scan handles the rest
-  const size_t smem = GemmSmem::total(k);
+  int stages = GM_STAGES;
+  if (GemmSmem::total(stages, k) > x->smem_optin) stages = 3;
+  const size_t smem = GemmSmem::total(stages, k);
   if (smem > x->smem_optin) return B200HNSW_ERR_UNSUPPORTED;
   const int64_t Bpad = (B + GM_M - 1) / GM_M * GM_M;
   auto al = [](size_t v) { return (v + 255) & ~(size_t)255; };
@@ -613,7 +613,8 @@ int exact_candidates_tensor(b200exact *x, const float *d_queries, int64_t B, int
   p.metric = x->metric;
   p.kblocks = x->kpad / GM_K;
   p.tiles_total = (int)((x->n + GM_N - 1) / GM_N);
-  p.warm_tiles = (k + 7) / 8;
+  p.warm_tiles = (k + GM_N / 64 - 1) / (GM_N / 64);  // a thread fills GM_N / 64 slots per tile
+  p.stages = stages;
   p.k = k;
   p.B = B;
   p.q_inv = q_inv;
