@@ -468,7 +468,7 @@ def cpu_baseline_and_parity(args, g, Qh, last, last_rows, last_dists, last_count
 
 def exact_measurement(args, X, Qh, Qd, torch, dev, stream, with_cpu):
     """hybrid.ExactIndex.Search (exact.go:61-111) over the same rows and query batches: K3, the tensor path
-    (exact_gemm.cu: bf16 tcgen05 scores + provably safe filter + canonical fp32 re-rank).  A side measurement carried
+    (exact_gemm.cu: fp16 tcgen05 scores + provably safe filter + canonical fp32 re-rank).  A side measurement carried
     in the same JSON line; the headline metric above is untouched."""
     import hnsw_b200
     n, dim, B, k = args.n, args.dim, args.batch, args.k
@@ -502,7 +502,7 @@ def exact_measurement(args, X, Qh, Qd, torch, dev, stream, with_cpu):
     peak = float(peaks.get("bf16_tflops_sustained", 1414.2))
     flops = 2.0 * n * B * dim
     out = {"metric": "ExactIndex.Search QPS (k=10)", "value": B / (ms / 1e3), "unit": "queries/s", "ms_per_step": ms,
-           "steps": args.exact_steps, "dtype": "bf16 scores, f32 canonical re-rank",
+           "steps": args.exact_steps, "dtype": "fp16 operands / fp32 accumulate scores, f32 canonical re-rank",
            "e2e": {"value": B / e2e_s, "unit": "queries/s", "h2d_bytes_per_step": B * dim * 4,
                    "d2h_bytes_per_step": B * k * 12 + B * 4},
            "roofline": {"bound": "tensor", "achieved": flops / (ms / 1e3) / 1e12, "peak": peak, "unit": "TFLOP/s",
