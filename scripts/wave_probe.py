@@ -6,9 +6,10 @@ os.environ.setdefault('B200HNSW_E2E_CHUNKS', '1')  # kernel_ms = the traversal k
 import hnsw_b200
 from bench import synth_rows, draw_levels
 N = int(sys.argv[1]); d = int(sys.argv[2]); M = int(sys.argv[3]); ef = int(sys.argv[4]); wm = int(sys.argv[5])
+metric = sys.argv[7] if len(sys.argv) > 7 else 'l2'
 Bs = [int(x) for x in sys.argv[6].split(',')]
 X = synth_rows(N, d, 42); lv = draw_levels(N, 0.25, 44)
-g = hnsw_b200.Graph(M=M, Ml=0.25, EfSearch=ef, Distance=hnsw_b200.EuclideanDistance, capacity=N)
+g = hnsw_b200.Graph(M=M, Ml=0.25, EfSearch=ef, Distance=hnsw_b200.EuclideanDistance if metric == 'l2' else hnsw_b200.CosineDistance, capacity=N)
 t = time.time(); g.add_arrays(np.arange(N, dtype=np.int64), X, lv, wave_max=wm); dt = time.time() - t
 st = g.last_stats
 print(f"wave add N={N} wall {dt:.2f}s (C call {st.get('call_s', 0):.2f}s) kernel {st['kernel_ms']/1e3:.2f}s -> {N/(st['kernel_ms']/1e3):.0f} vec/s launches={st['launches']} "
