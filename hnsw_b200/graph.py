@@ -394,6 +394,19 @@ class Graph:
         rows, _, counts = self.search_rows(np.stack(qs), k)
         return [self._nodes(rows[i], counts[i]) for i in range(len(qs))]
 
+    # ---- graph.go:1116-1537 (host re-ranking over device searches and device distances: negatives.py) -----------------
+    def SearchWithNegative(self, near, negative, k: int, negWeight: float):
+        from .negatives import search_with_negative
+        return search_with_negative(self, near, negative, k, negWeight)
+
+    def SearchWithNegatives(self, near, negatives, k: int, negWeight: float):
+        from .negatives import search_with_negatives
+        return search_with_negatives(self, near, negatives, k, negWeight)
+
+    def BatchSearchWithNegatives(self, queries, negatives, k: int, negWeight: float):
+        from .negatives import batch_search_with_negatives
+        return batch_search_with_negatives(self, queries, negatives, k, negWeight)
+
     # ---- encode.go:133-262 -----------------------------------------------------------------------------------------
     def Export(self, w) -> None:
         from .encode import export_graph

