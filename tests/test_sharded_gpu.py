@@ -73,3 +73,67 @@ def test_two_gpu_pipeline_matches_merge_spec(tmp_path):
             assert np.array_equal(r[i][f"i{step}"][:q1 - q0], m[1][q0:q1])
             assert np.array_equal(r[i][f"c{step}"][:q1 - q0], m[2][q0:q1])
         assert (m[1] >= 3000).any() and (m[1][m[1] >= 0] < 3000).any()
+
+
+def _exact_worker(rank, world, port, tmp):
+    sys.path.insert(0, str(ROOT))
+    import torch
+    import torch.distributed as dist
+    import hnsw_b200
+    from hnsw_b200 import sharded
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    n_total, d, k, B = 40000, 256, 10, 300
+    rng = np.random.default_rng(5)
+    X = rng.standard_normal((n_total, d), dtype=np.float32)
+    X[123] = X[77]  # a tie across shards (row 77 -> shard 1, row 123 -> shard 1 ... both odd) and
+    X[200] = X[77]  # one across shards (row 200 -> shard 0)
+    Q = rng.standard_normal((B, d), dtype=np.float32)
+    mine = np.arange(rank, n_total, world)  # rows round-robin (row mod G)
+    ix = hnsw_b200.NewExactIndex(hnsw_b200.CosineDistance, device=rank, capacity=len(mine))
+    ix.add_arrays(mine.tolist(), X[mine])
+    rows = torch.empty((B, k), dtype=torch.int64, device=dev)
+    dd = torch.empty((B, k), dtype=torch.float32, device=dev)
+    cnt = torch.empty((B,), dtype=torch.int32, device=dev)
+    qd = torch.from_numpy(Q).to(dev)
+    ix.search_device(qd.data_ptr(), B, k, rows.data_ptr(), dd.data_ptr(), cnt.data_ptr())
+    gids = torch.where(rows >= 0, rows * world + rank, rows)  # shard row -> global row
+    all_d, all_i, all_c = sharded.gather_shard_results(dist, dd, gids, cnt)
+    md, mi, mc = sharded.merge_topk_device(all_d, all_i, all_c, k)
+    torch.cuda.synchronize(dev)
+    np.savez(os.path.join(tmp, f"exact{rank}.npz"), d=md.cpu().numpy(), i=mi.cpu().numpy(), c=mc.cpu().numpy())
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+def test_two_gpu_sharded_exact_matches_oracle(tmp_path):
+    # BASELINE config 5 shape (cosine, rows sharded over the GPUs, K3 per shard, K4 merge), reduced: the merged top-k
+    # must be the oracle's exact top-k over ALL rows, distance bits included
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+    from oracle import binding as oracle
+    oracle.build()
+    world, port = 2, 29717 + os.getpid() % 200
+    mp.spawn(_exact_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    r = [np.load(tmp_path / f"exact{i}.npz") for i in range(world)]
+    rng = np.random.default_rng(5)
+    X = rng.standard_normal((40000, 256), dtype=np.float32)
+    X[123] = X[77]
+    X[200] = X[77]
+    Q = rng.standard_normal((300, 256), dtype=np.float32)
+    o_idx, o_d = oracle.exact_batch_search(X, Q, 10, oracle.COSINE, n_threads=8)
+    for i in range(world):
+        assert np.array_equal(r[i]["d"].view(np.uint32), np.asarray(o_d).view(np.uint32))
+        # ids equal except inside groups of bit-equal distances (ties: the sharded merge orders them by shard, the
+        # single index by row)
+        same = r[i]["i"] == o_idx.astype(np.int64)
+        for q, j in zip(*np.nonzero(~same)):
+            tied = np.nonzero(o_d[q].view(np.uint32) == o_d[q, j].view(np.uint32))[0]
+            assert set(r[i]["i"][q, tied].tolist()) == set(o_idx[q, tied].astype(np.int64).tolist())
+        assert (r[i]["c"] == 10).all()
