@@ -484,6 +484,16 @@ int b200hnsw_search_batch_segmented_device(b200hnsw_t *h, const float *d_queries
                        reinterpret_cast<unsigned long long *>(d_counters), d_err, h->vis_hint, s, seg_len, seg_stride);
 }
 
+// device alias of a page-locked, mapped host buffer (cudaHostAlloc / cudaHostRegister under UVA), or nullptr
+static void *mapped_host(const void *p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  return a.type == cudaMemoryTypeHost ? a.devicePointer : nullptr;
+}
+
 int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_t k, int32_t ef, int32_t metric,
                           int32_t mode, const int32_t *entries, int32_t *out_rows, float *out_dists,
                           int32_t *out_counts, b200hnsw_stats *stats) {
@@ -527,6 +537,18 @@ int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_
   int *d_err = (int *)(d_ctr + 4);
   cudaStream_t s = c->stream;
   cudaError_t e;
+  // Page-locked result buffers are written by the kernel itself (80 B of posted PCIe writes per query at the end of
+  // its traversal): no device staging, no D2H copies behind the kernel.
+  bool direct_out = false;
+  if (!getenv("B200HNSW_NO_DIRECT_OUT")) {
+    void *zr = mapped_host(out_rows), *zd = mapped_host(out_dists), *zc = mapped_host(out_counts);
+    if (zr && zd && zc) {
+      d_rows = (int32_t *)zr;
+      d_dists = (float *)zd;
+      d_cnt = (int32_t *)zc;
+      direct_out = true;
+    }
+  }
   // The batch is cut in chunks that run on their own streams: the H2D copy of chunk i+1 and the D2H copy of chunk
   // i-1 overlap the traversal kernel of chunk i, and the kernels of different chunks share the SMs.
   int nchunk = B >= 4096 ? 4 : (B >= 1024 ? 2 : 1);
@@ -561,12 +583,13 @@ int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_
                          d_cnt + q0, d_ctr, d_err, vis, sc);
       if (rc) return fail(rc);
       launches++;
-      if ((e = cudaMemcpyAsync(out_rows + q0 * k, d_rows + q0 * k, sizeof(int32_t) * (size_t)nq * k,
+      if (!direct_out &&
+          ((e = cudaMemcpyAsync(out_rows + q0 * k, d_rows + q0 * k, sizeof(int32_t) * (size_t)nq * k,
                                cudaMemcpyDeviceToHost, sc)) != cudaSuccess ||
           (e = cudaMemcpyAsync(out_dists + q0 * k, d_dists + q0 * k, sizeof(float) * (size_t)nq * k,
                                cudaMemcpyDeviceToHost, sc)) != cudaSuccess ||
           (e = cudaMemcpyAsync(out_counts + q0, d_cnt + q0, sizeof(int32_t) * (size_t)nq, cudaMemcpyDeviceToHost,
-                               sc)) != cudaSuccess)
+                               sc)) != cudaSuccess))
         return fail(cuda_fail(e, "search copy-back"));
       if (nchunk > 1 && ((e = cudaEventRecord(c->sub_ev[ci], sc)) != cudaSuccess ||
                          (e = cudaStreamWaitEvent(s, c->sub_ev[ci], 0)) != cudaSuccess))
