@@ -5,7 +5,8 @@ Host-side mirror of the reference's Go API over the C ABI in include/b200hnsw.h.
 from .distance import (CosineDistance, EuclideanDistance, RegisterDistanceFunc, distanceFuncs, distanceFuncToName)
 from .encode import LoadSavedGraph, SavedGraph
 from .exact import ExactIndex, NewExactIndex
+from ._lib import B200Error
 from .graph import Graph, GoRand, MakeNode, NewGraph, NewGraphWithConfig, Node, maxLevel
 
-__all__ = ["LoadSavedGraph", "SavedGraph", "ExactIndex", "NewExactIndex", "Graph", "GoRand", "Node", "MakeNode", "NewGraph", "NewGraphWithConfig", "maxLevel", "CosineDistance",
+__all__ = ["B200Error", "LoadSavedGraph", "SavedGraph", "ExactIndex", "NewExactIndex", "Graph", "GoRand", "Node", "MakeNode", "NewGraph", "NewGraphWithConfig", "maxLevel", "CosineDistance",
            "EuclideanDistance", "RegisterDistanceFunc", "distanceFuncs", "distanceFuncToName"]

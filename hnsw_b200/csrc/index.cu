@@ -115,6 +115,7 @@ int b200hnsw::ensure_capacity(int64_t rows, int64_t upper_slots, cudaStream_t s)
     if ((rc = grow(d.keys, n, nc, s))) return rc;
     if ((rc = grow(d.adj0, n * M, nc * M, s, 0xff))) return rc;
     if ((rc = grow(d.upper_off, n, nc, s, 0xff))) return rc;
+    if ((rc = grow(d.dead, n, nc, s, 0))) return rc;
     d.cap = nc;
   }
   if (upper_slots > d.capU) {
@@ -219,6 +220,7 @@ void b200hnsw_destroy(b200hnsw_t *h) {
   cudaFree(h->d.keys);
   cudaFree(h->d.adj0);
   cudaFree(h->d.upper_off);
+  cudaFree(h->d.dead);
   cudaFree(h->d.adjU);
   cudaFree(h->d.inbox);
   cudaFree(h->d_err_word);
@@ -236,6 +238,7 @@ int b200hnsw_reserve(b200hnsw_t *h, int64_t rows) {
 }
 
 int64_t b200hnsw_len(const b200hnsw_t *h) { return h && h->n_layers ? h->layer_size[0] : 0; }
+int64_t b200hnsw_rows(const b200hnsw_t *h) { return h ? h->n : 0; }
 int32_t b200hnsw_layers(const b200hnsw_t *h) { return h ? h->n_layers : 0; }
 int64_t b200hnsw_layer_size(const b200hnsw_t *h, int32_t l) {
   return (h && l >= 0 && l < h->n_layers) ? h->layer_size[l] : 0;
@@ -339,6 +342,8 @@ int b200hnsw_load(b200hnsw_t *h, int64_t n, const float *vectors, const int64_t 
                                    s) != cudaSuccess))
       return fail(cuda_fail(cudaGetLastError(), "load copies"));
   }
+  if (h->d.dead && cudaMemsetAsync(h->d.dead, 0, (size_t)h->d.cap, s) != cudaSuccess)
+    return fail(cuda_fail(cudaGetLastError(), "load: clearing the deleted flags"));
   cudaError_t e = cudaStreamSynchronize(s);
   if (e != cudaSuccess) return fail(cuda_fail(e, "load sync"));
   h->n = n;
@@ -346,6 +351,8 @@ int b200hnsw_load(b200hnsw_t *h, int64_t n, const float *vectors, const int64_t 
   h->n_layers = n_layers;
   h->h_keys.assign(keys, keys + n);
   h->h_level.assign(levels, levels + n);
+  h->h_dead.assign((size_t)n, 0);
+  h->n_dead = 0;
   h->h_upper_off = upper_off;
   roff = 0;
   for (int l = 0; l < B200HNSW_MAX_LAYERS; l++) {
@@ -445,7 +452,7 @@ int b200hnsw_search_batch_device(b200hnsw_t *h, const float *d_queries, int64_t 
   B200_CUDA(cudaSetDevice(h->cfg.device));
   cudaStream_t s = (cudaStream_t)stream;
   if (B == 0) return 0;
-  if (h->n_layers == 0 || h->n == 0) {  // graph.go:554-556: empty graph -> no results
+  if (h->live_layers() == 0) {  // graph.go:554-556: empty graph -> no results
     B200_CUDA(cudaMemsetAsync(d_out_counts, 0, sizeof(int32_t) * (size_t)B, s));
     B200_CUDA(cudaMemsetAsync(d_out_rows, 0xff, sizeof(int32_t) * (size_t)B * k, s));
     B200_CUDA(cudaMemsetAsync(d_out_dists, 0xff, sizeof(float) * (size_t)B * k, s));
@@ -471,7 +478,7 @@ int b200hnsw_search_batch_segmented_device(b200hnsw_t *h, const float *d_queries
   cudaStream_t s = (cudaStream_t)stream;
   if (B == 0) return 0;
   const int64_t nseg = (B + seg_len - 1) / seg_len;
-  if (h->n_layers == 0 || h->n == 0) {  // graph.go:554-556: empty graph -> no results
+  if (h->live_layers() == 0) {  // graph.go:554-556: empty graph -> no results
     for (int64_t g = 0; g < nseg; g++) {
       int32_t *base = d_packed + g * seg_stride;
       B200_CUDA(cudaMemsetAsync(base, 0xff, sizeof(int32_t) * 2 * (size_t)seg_len * k, s));
@@ -505,7 +512,7 @@ int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_
   }
   if (stats) memset(stats, 0, sizeof *stats);
   if (B == 0) return 0;
-  if (h->n_layers == 0 || h->n == 0) {
+  if (h->live_layers() == 0) {
     std::fill(out_counts, out_counts + B, 0);
     std::fill(out_rows, out_rows + B * k, -1);
     std::fill(out_dists, out_dists + B * k, NAN);

@@ -48,6 +48,7 @@ struct DeviceGraph {
   int32_t *upper_off = nullptr; // [cap]
   int32_t *adjU = nullptr;      // [capU][M]
   int64_t cap = 0, capU = 0;
+  uint8_t *dead = nullptr;      // [cap] 1 = removed from its layers by Delete (graph.go:843-866); row and lists stay
   int32_t *inbox = nullptr;     // 4 x inbox_n: request counts/segments and eviction heads/owners per list slot (wave Add)
   int64_t inbox_n = 0;
 };
@@ -67,6 +68,8 @@ struct b200hnsw {
   std::vector<int64_t> h_keys;
   std::vector<int32_t> h_level;
   std::vector<int32_t> h_upper_off;
+  std::vector<uint8_t> h_dead;
+  int64_t n_dead = 0;
   int *d_err_word = nullptr;  // error flag for device-pointer calls that pass no counters
   int vis_hint = 512;  // visited-table entries per traversal; raised (sticky) when a search overflows it
   int sm_count = 148;
@@ -79,6 +82,13 @@ struct b200hnsw {
   int ensure_capacity(int64_t rows, int64_t upper_slots, cudaStream_t s);
   int ensure_inboxes(cudaStream_t s);
   b200::GraphView view() const;
+  // layers that still have a member: Delete can empty the top ones, which Search then passes through without an
+  // elevator (graph.go:571-583), i.e. exactly as if they were not there
+  int32_t live_layers() const {
+    int32_t l = n_layers;
+    while (l > 0 && layer_size[l - 1] == 0) l--;
+    return l;
+  }
 };
 
 namespace b200 {

@@ -34,6 +34,11 @@ struct InsertParams {
   int *error;
   int heap_c, heap_r, vis_cap;    // search scratch (uint2 slots, uint2 slots, u32 entries)
   int cand_cap, rep_cap;          // replenish candidates (<= M*M) and its visited table (power of two)
+  const uint8_t *dead;            // [rows] deleted flags, null while nothing was deleted
+  // Delete (delete_kernel): rows to isolate, in call order
+  const int32_t *del_rows;
+  const int32_t *del_levels;
+  uint8_t *dead_set;              // deleted flags, written by the delete kernel
 };
 
 struct MutGraph {
@@ -62,6 +67,7 @@ struct InsCtl {
   int need_heap;  // replenish needs the exact heap (NaN present or more than one pop)
   int abort_;
   int entries[B200HNSW_MAX_LAYERS];
+  int cnts[B200HNSW_MAX_LAYERS];  // neighbourhood sizes of the node being inserted, -1 = the layer was empty
 };
 
 // ---- block-wide state -------------------------------------------------------------------------------------------
@@ -70,7 +76,7 @@ struct Inserter {
   MutGraph g;
   InsertParams p;
   InsCtl *ctl;
-  int *nbh;        // [M]   neighbourhood rows (heap-array order)
+  int *nbh;        // [MAX_LAYERS][M] neighbourhood rows per layer (heap-array order)
   int *tmp;        // [M+1] list being edited
   float *tmpd;     // [M+1] eviction-scan distances
   int *wl;         // [M+1] list of the node being replenished
@@ -291,6 +297,29 @@ struct Inserter {
     __syncthreads();
     replenish(layer, worst);  // graph.go:79
   }
+
+  // layerNode.isolate(m) -- graph.go:223-235: every neighbour drops its link to n and is replenished at once, in
+  // ascending key order (the stand-in for Go's map order).  n's own list is left as it is, as in the reference.
+  __device__ void isolate(int layer, int n) {
+    const int M = g.M;
+    __syncthreads();
+    if (warp == 0) {
+      int deg = warp_load_list(g.list(layer, n), M, nbh, lane);
+      if (lane == 0) ctl->cnt = deg;
+    }
+    __syncthreads();
+    const int deg = ctl->cnt;
+    for (int i = 0; i < deg; i++) {
+      const int nb = nbh[i];
+      if (warp == 1) {  // graph.go:232: delete(neighbor.neighbors, n.Key)
+        int32_t *l = g.list(layer, nb);
+        int d = warp_load_list(l, M, wl, lane);
+        int nd = warp_list_remove(wl, d, n, lane);
+        if (nd != d) warp_store_list(l, M, wl, nd, lane);
+      }
+      replenish(layer, nb);  // graph.go:233 (starts with a barrier)
+    }
+  }
 };
 
 static __host__ __device__ inline size_t al16(size_t v) { return (v + 15) & ~(size_t)15; }
@@ -303,7 +332,7 @@ struct InsLayout {
     heapC = o; o += al16(sizeof(uint2) * p.heap_c);
     heapR = o; o += al16(sizeof(uint2) * p.heap_r);
     vis = o;   o += al16(sizeof(uint32_t) * p.vis_cap);
-    nbh = o;   o += al16(sizeof(int) * (M + 1));
+    nbh = o;   o += al16(sizeof(int) * (size_t)B200HNSW_MAX_LAYERS * M);
     tmp = o;   o += al16(sizeof(int) * (M + 1));
     tmpd = o;  o += al16(sizeof(float) * (M + 1));
     wl = o;    o += al16(sizeof(int) * (M + 1));
@@ -359,41 +388,59 @@ __global__ void __launch_bounds__(INS_THREADS) insert_kernel(MutGraph g, InsertP
     const int L = p.levels[j];                          // randomLevel() drawn by the host (graph.go:457)
     const int old_layers = ctl->n_layers;
     const int top = (old_layers > L + 1 ? old_layers : L + 1) - 1;  // graph.go:462-464
-    if (tid == 0) ctl->elevator = -1;
+    // Every layer search first, then the linking.  A layer's search reads that layer's lists only and linking at
+    // layer l writes layer-l lists only, so the neighbourhoods equal those of the reference's interleaved loop
+    // (graph.go:475-522); a failed Add (deleted elevator) then leaves the graph untouched.
+    if (warp == 0) {
+      QueryRegs<CPL> Q;
+      load_query<CPL>(Q, reinterpret_cast<const float *>(g.vec + (size_t)row * g.row_chunks), g.dim, g.row_chunks,
+                      lane);
+      int elevator = -1, bad = 0;
+      for (int l = top; l >= 0; l--) {                  // graph.go:475
+        int cnt = -1;
+        if (l < old_layers && ctl->entries[l] >= 0) {   // else graph.go:485-488: an empty layer takes the node
+          int sp = elevator >= 0 ? elevator : ctl->entries[l];  // graph.go:492-498
+          if (elevator >= 0 && p.dead && p.dead[elevator]) {
+            cnt = 0;  // layer.nodes[*elevator] == nil: the search returns nothing (graph.go:101-103)
+          } else {
+            cnt = layer_search_ref<CPL, U>(gv, l, sp, p.m, p.ef, p.metric, Q, I.C, I.R, I.V, sc, lane);  // :500
+            for (int i = lane; i < cnt; i += 32) I.nbh[l * g.M + i] = I.R.id(i);
+            if (cnt > 0) elevator = I.R.id(0);          // graph.go:508
+          }
+          if (cnt <= 0) {  // visited overflow (< 0) or "no nodes found in neighborhood search" (graph.go:501-505)
+            bad = cnt < 0 ? 1 : 2;
+            break;
+          }
+        }
+        if (lane == 0) ctl->cnts[l] = cnt;
+        __syncwarp();
+      }
+      if (lane == 0) ctl->flag = bad;
+    }
     __syncthreads();
-    for (int l = top; l >= 0 && !aborted; l--) {        // graph.go:475
-      if (l >= old_layers) {                            // graph.go:485-488: empty layer takes the node
+    if (ctl->flag) {
+      aborted = true;
+      if (tid == 0) {
+        *p.error = ctl->flag;
+        p.state_out[1 + B200HNSW_MAX_LAYERS] = j;  // nodes before j are in
+      }
+      break;
+    }
+    for (int l = top; l >= 0; l--) {
+      const int cnt = ctl->cnts[l];
+      if (cnt < 0) {
         if (tid == 0) ctl->entries[l] = row;
         continue;
       }
-      if (warp == 0) {
-        int sp = ctl->elevator >= 0 ? ctl->elevator : ctl->entries[l];  // graph.go:492-498
-        QueryRegs<CPL> Q;
-        load_query<CPL>(Q, reinterpret_cast<const float *>(g.vec + (size_t)row * g.row_chunks), g.dim, g.row_chunks,
-                        lane);
-        int cnt = layer_search_ref<CPL, U>(gv, l, sp, p.m, p.ef, p.metric, Q, I.C, I.R, I.V, sc, lane);  // :500
-        for (int i = lane; i < cnt; i += 32) I.nbh[i] = I.R.id(i);
-        if (lane == 0) {
-          ctl->cnt = cnt;
-          if (cnt > 0) ctl->elevator = I.R.id(0);       // graph.go:508
-        }
-      }
-      __syncthreads();
-      const int cnt = ctl->cnt;
-      if (cnt <= 0) {  // visited overflow (or the impossible empty neighbourhood, graph.go:501-505)
-        aborted = true;
-        if (tid == 0) *p.error = cnt < 0 ? 1 : 2;
-        break;
-      }
       if (L >= l) {  // graph.go:510-521
         for (int t = 0; t < cnt; t++) {
-          const int nb = I.nbh[t];
+          const int nb = I.nbh[l * g.M + t];
           I.add_neighbor(l, nb, row, p.metric);
           I.add_neighbor(l, row, nb, p.metric);
         }
       }
-      __syncthreads();
     }
+    __syncthreads();
     if (tid == 0 && L + 1 > old_layers) ctl->n_layers = L + 1;
     __syncthreads();
   }
@@ -411,6 +458,40 @@ __global__ void __launch_bounds__(INS_THREADS) insert_kernel(MutGraph g, InsertP
   }
 }
 
+// K2d: Graph.Delete / Graph.BatchDelete (graph.go:843-895).  One CTA walks the rows in call order; per row, base layer
+// first (the order of h.layers), isolate() on every layer the row is a member of.  The host has already taken the
+// rows out of its layer bookkeeping and set their deleted flags.  Bound: latency of dependent gathers.
+template <int CPL, int U>
+__global__ void __launch_bounds__(INS_THREADS) delete_kernel(MutGraph g, InsertParams p) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const InsLayout lay(p, g.M);
+  Inserter<CPL, U> I;
+  I.g = g;
+  I.p = p;
+  I.ctl = reinterpret_cast<InsCtl *>(smem + lay.ctl);
+  I.nbh = reinterpret_cast<int *>(smem + lay.nbh);
+  I.tmp = reinterpret_cast<int *>(smem + lay.tmp);
+  I.tmpd = reinterpret_cast<float *>(smem + lay.tmpd);
+  I.wl = reinterpret_cast<int *>(smem + lay.wl);
+  I.cand = reinterpret_cast<int *>(smem + lay.cand);
+  I.candd = reinterpret_cast<float *>(smem + lay.candd);
+  I.rep = reinterpret_cast<uint32_t *>(smem + lay.rep);
+  I.C = GoHeap{reinterpret_cast<uint2 *>(smem + lay.heapC), 0};
+  I.R = GoHeap{reinterpret_cast<uint2 *>(smem + lay.heapR), 0};
+  I.V = Visited{reinterpret_cast<uint32_t *>(smem + lay.vis), (uint32_t)p.vis_cap - 1, 0};
+  I.tid = threadIdx.x;
+  I.lane = threadIdx.x & 31;
+  I.warp = threadIdx.x >> 5;
+  I.c_evict = I.c_repl = I.c_evictions = 0;
+  for (int j = 0; j < p.n; j++) {
+    const int row = p.del_rows[j];
+    const int L = p.del_levels[j];
+    if (I.tid == 0) p.dead_set[row] = 1;  // read by Search / Add when they look an elevator up
+    for (int l = 0; l <= L; l++) I.isolate(l, row);
+  }
+  if (I.tid == 0) atomicAdd(&p.counters[4], I.c_repl);
+}
+
 static int pow2_at_least(int v) {
   int r = 1;
   while (r < v) r <<= 1;
@@ -419,7 +500,7 @@ static int pow2_at_least(int v) {
 
 template <int CPL, int U>
 static int launch_insert_t(b200hnsw *h, const MutGraph &g, InsertParams &p, cudaStream_t s) {
-  auto kern = insert_kernel<CPL, U>;
+  auto kern = p.del_rows ? delete_kernel<CPL, U> : insert_kernel<CPL, U>;
   InsLayout lay(p, g.M);
   if (lay.total > h->smem_optin) {
     set_error("add: M=%d ef=%d need %zu B of shared memory (> %zu)", p.m, p.ef, lay.total, h->smem_optin);
@@ -506,6 +587,25 @@ extern "C" int b200hnsw_add_batch(b200hnsw_t *h, const float *vectors, const int
     }
     add_slots += levels[i];
   }
+  if (h->n_dead) {
+    // A layer emptied by Delete above a node's drawn level: the reference parks the node there without the layers
+    // in between (graph.go:485-488), after which every Search loses its elevator.  Not reproduced: refused.
+    int top_empty = -1;  // highest empty layer below n_layers
+    for (int l = h->n_layers - 1; l >= 0; l--)
+      if (h->layer_size[l] == 0) {
+        top_empty = l;
+        break;
+      }
+    for (int64_t i = 0; i < n && top_empty >= 0; i++) {
+      if (levels[i] < top_empty) {
+        set_error("add: layer %d was emptied by Delete and node %lld of the batch draws level %d below it; the "
+                  "reference's behaviour here (graph.go:485-488) is not reproduced", top_empty, (long long)i,
+                  levels[i]);
+        return B200HNSW_ERR_UNSUPPORTED;
+      }
+      top_empty = -1;  // this node fills every empty layer up to its level, which is >= top_empty
+    }
+  }
   B200_CUDA(cudaSetDevice(h->cfg.device));
   CallCtx *c = h->acquire();
   if (!c) return B200HNSW_ERR_CUDA;
@@ -549,6 +649,21 @@ extern "C" int b200hnsw_add_batch(b200hnsw_t *h, const float *vectors, const int
   int n_layers = h->n_layers;
   int32_t entries[B200HNSW_MAX_LAYERS];
   memcpy(entries, h->entry, sizeof entries);
+  auto commit = [&](int64_t count) {  // host mirrors of the first `count` nodes of the batch
+    int64_t used = h->nU;
+    for (int64_t i = 0; i < count; i++) {
+      h->h_keys.push_back(keys[i]);
+      h->h_level.push_back(levels[i]);
+      h->h_dead.push_back(0);
+      h->h_upper_off.push_back(upper_off[i]);
+      for (int l = 0; l <= levels[i]; l++) h->layer_size[l]++;
+      used += levels[i];
+    }
+    h->n += count;
+    h->nU = used;
+    h->n_layers = n_layers;
+    memcpy(h->entry, entries, sizeof entries);
+  };
   for (int64_t off = 0; off < n; off += CH) {
     int64_t cnt = std::min(CH, n - off);
     if ((e = cudaMemcpyAsync(d_levels, levels + off, sizeof(int32_t) * (size_t)cnt, cudaMemcpyHostToDevice, s)) !=
@@ -566,37 +681,32 @@ extern "C" int b200hnsw_add_batch(b200hnsw_t *h, const float *vectors, const int
     p.state_out = d_state;
     p.counters = d_ctr;
     p.error = d_err;
+    p.dead = h->n_dead ? h->d.dead : nullptr;
     if ((rc = launch_insert(h, p, s))) return fail(rc);
     launches++;
-    int state[1 + B200HNSW_MAX_LAYERS];
+    int state[2 + B200HNSW_MAX_LAYERS];
     int err = 0;
     if ((e = cudaMemcpyAsync(state, d_state, sizeof state, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
         (e = cudaMemcpyAsync(&err, d_err, sizeof err, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
         (e = cudaStreamSynchronize(s)) != cudaSuccess)
       return fail(cuda_fail(e, "add kernel"));
-    if (err) {
-      set_error(err == 1 ? "add: a layer search overflowed the visited set" : "no nodes found in neighborhood search");
-      return fail(err == 1 ? B200HNSW_ERR_VISITED_OVERFLOW : B200HNSW_ERR_STATE);
-    }
     n_layers = state[0];
     memcpy(entries, state + 1, sizeof entries);
+    if (err) {
+      // the kernel stopped in front of node `bad` with the graph as its predecessors left it: keep those
+      const int64_t bad = off + state[1 + B200HNSW_MAX_LAYERS];
+      commit(bad);
+      set_error(err == 1 ? "add: a layer search overflowed the visited set (node %lld of the batch)"
+                         : "no nodes found in neighborhood search (node %lld of the batch)", (long long)bad);
+      return fail(err == 1 ? B200HNSW_ERR_VISITED_OVERFLOW : B200HNSW_ERR_STATE);
+    }
   }
   unsigned long long ctr[8];
   if ((e = cudaEventRecord(c->ev1, s)) != cudaSuccess ||
       (e = cudaMemcpyAsync(ctr, d_ctr, sizeof ctr, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
       (e = cudaStreamSynchronize(s)) != cudaSuccess)
     return fail(cuda_fail(e, "add counters"));
-  // commit host mirrors
-  for (int64_t i = 0; i < n; i++) {
-    h->h_keys.push_back(keys[i]);
-    h->h_level.push_back(levels[i]);
-    h->h_upper_off.push_back(upper_off[i]);
-    for (int l = 0; l <= levels[i]; l++) h->layer_size[l]++;
-  }
-  h->n += n;
-  h->nU = nU;
-  h->n_layers = n_layers;
-  memcpy(h->entry, entries, sizeof entries);
+  commit(n);
   if (stats) {
     stats->dist_evals = (int64_t)ctr[0];
     stats->evict_evals = (int64_t)ctr[3];
@@ -609,4 +719,92 @@ extern "C" int b200hnsw_add_batch(b200hnsw_t *h, const float *vectors, const int
   }
   h->release(c);
   return 0;
+}
+
+// Graph.Delete / Graph.BatchDelete -- graph.go:843-895.  rows[i] is the row the caller's key map holds for the i-th
+// key (-1 for a key it does not know); out_deleted[i] mirrors the reference's []bool.
+extern "C" int b200hnsw_delete_batch(b200hnsw_t *h, const int32_t *rows, int64_t n, int32_t m, uint8_t *out_deleted,
+                                     b200hnsw_stats *stats) {
+  if (stats) memset(stats, 0, sizeof *stats);
+  if (!h || n < 0 || (n > 0 && !rows)) {
+    set_error("delete: bad argument");
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  if (m <= 0 || m > h->M) {  // graph.go:918-920
+    set_error("M must be greater than 0 and <= max_m=%d, got %d", h->M, m);
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  if (out_deleted) memset(out_deleted, 0, (size_t)n);
+  if (n == 0 || h->n_layers == 0) return 0;  // graph.go:847-849
+  std::vector<int32_t> del, lev;
+  for (int64_t i = 0; i < n; i++) {
+    const int32_t r = rows[i];
+    if (r < 0 || r >= h->n || h->h_dead[(size_t)r]) continue;  // unknown key, or deleted earlier (in this batch too)
+    h->h_dead[(size_t)r] = 1;
+    h->n_dead++;
+    if (out_deleted) out_deleted[i] = 1;
+    del.push_back(r);
+    lev.push_back(h->h_level[(size_t)r]);
+    for (int l = 0; l <= h->h_level[(size_t)r]; l++) {  // delete(layer.nodes, key)
+      h->layer_size[l]--;
+      if (h->entry[l] == r) {  // layer.entry(): the lowest live member row takes over (documented stand-in)
+        int32_t en = -1;
+        if (h->layer_size[l] > 0)
+          for (int64_t x = 0; x < h->n; x++)
+            if (!h->h_dead[(size_t)x] && h->h_level[(size_t)x] >= l) {
+              en = (int32_t)x;
+              break;
+            }
+        h->entry[l] = en;
+      }
+    }
+  }
+  if (del.empty()) return 0;
+  B200_CUDA(cudaSetDevice(h->cfg.device));
+  CallCtx *c = h->acquire();
+  if (!c) return B200HNSW_ERR_CUDA;
+  cudaStream_t s = c->stream;
+  auto fail = [&](int code) {
+    h->release(c);
+    return code;
+  };
+  const size_t nd = del.size();
+  const size_t lev_off = (sizeof(int32_t) * nd + 255) & ~(size_t)255;
+  int rc = c->reserve_device(2 * lev_off + nd + 512);
+  if (rc) return fail(rc);
+  char *sp = (char *)c->d_scratch;
+  int32_t *d_rows = (int32_t *)sp;
+  int32_t *d_lev = (int32_t *)(sp + lev_off);
+  unsigned long long *d_ctr = (unsigned long long *)(sp + 2 * lev_off);
+  cudaError_t e;
+  if ((e = cudaMemcpyAsync(d_rows, del.data(), sizeof(int32_t) * nd, cudaMemcpyHostToDevice, s)) != cudaSuccess ||
+      (e = cudaMemcpyAsync(d_lev, lev.data(), sizeof(int32_t) * nd, cudaMemcpyHostToDevice, s)) != cudaSuccess ||
+      (e = cudaMemsetAsync(d_ctr, 0, 128, s)) != cudaSuccess)
+    return fail(cuda_fail(e, "delete staging"));
+  if ((e = cudaEventRecord(c->ev0, s)) != cudaSuccess) return fail(cuda_fail(e, "event"));
+  InsertParams p{};
+  p.n = (int)nd;
+  p.m = m;
+  p.ef = 1;
+  p.del_rows = d_rows;
+  p.del_levels = d_lev;
+  p.dead_set = h->d.dead;
+  p.counters = d_ctr;
+  if ((rc = launch_insert(h, p, s))) return fail(rc);
+  unsigned long long ctr[8];
+  if ((e = cudaEventRecord(c->ev1, s)) != cudaSuccess ||
+      (e = cudaMemcpyAsync(ctr, d_ctr, sizeof ctr, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
+      (e = cudaStreamSynchronize(s)) != cudaSuccess)
+    return fail(cuda_fail(e, "delete kernel"));
+  if (stats) {
+    stats->replenish_evals = (int64_t)ctr[4];
+    stats->launches = 1;
+    cudaEventElapsedTime(&stats->kernel_ms, c->ev0, c->ev1);
+  }
+  h->release(c);
+  return 0;
+}
+
+extern "C" int32_t b200hnsw_is_deleted(const b200hnsw_t *h, int32_t row) {
+  return (h && row >= 0 && row < h->n) ? (int32_t)h->h_dead[(size_t)row] : -1;
 }

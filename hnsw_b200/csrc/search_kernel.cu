@@ -51,7 +51,7 @@ static int pick_group(int row_chunks) {
 
 int launch_traverse(b200hnsw *h, TraverseParams &p, int vis_cap, cudaStream_t s) {
   GraphView g = h->view();
-  p.n_layers = h->n_layers;
+  if (p.n_layers == 0) p.n_layers = h->n_layers;
   int kr = p.k > p.k_upper ? p.k : p.k_upper;
   p.heap_c = (p.ef + 2) & ~1;
   p.heap_r = (kr + 1) & ~1;
@@ -136,6 +136,8 @@ int launch_search(b200hnsw *h, const float *d_queries, int64_t B, int k, int ef,
   p.out_seg_stride = seg_stride;
   p.counters = d_counters;
   p.error = d_error;
+  p.dead = h->n_dead ? h->d.dead : nullptr;
+  p.n_layers = h->live_layers();  // layers Delete emptied at the top are passed through without an elevator
   return launch_traverse(h, p, vis_cap, s);
 }
 

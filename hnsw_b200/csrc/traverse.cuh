@@ -43,6 +43,7 @@ struct TraverseParams {
   int *error;                    // set to 1 on visited overflow
   int vis_cap;                   // visited-table entries per group (power of two)
   int heap_c, heap_r, fresh_cap; // per-group slots: uint2, uint2, int
+  const uint8_t *dead;           // [rows] rows Delete removed from layer.nodes; null while nothing was deleted
 };
 
 struct OutPtrs {
@@ -364,6 +365,23 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
           layer--;
           chain = rlen > 0;
           st = chain ? ST_EXPAND : ST_INIT;
+          if (chain && p.dead && p.dead[elevator]) {
+            // layer.nodes[*elevator] is nil once the key was deleted (graph.go:573-575): the search from a nil node
+            // returns nothing on this and, the elevator never changing again, on every layer below -- Search
+            // answers with an empty list (graph.go:580-593).
+            chain = false;
+            st = ST_NEED;
+            if (p.out_rows) {
+              const OutPtrs o = search_out(p, q);
+              for (int i = gl; i < p.k; i += G) {
+                o.rows[i] = -1;
+                o.dists[i] = __int_as_float(0x7fc00000);
+              }
+              if (leader) *o.count = 0;
+            } else if (leader) {
+              *p.error = 2;  // Add: "no nodes found in neighborhood search" (graph.go:501-505)
+            }
+          }
         }
       }
     }

@@ -693,6 +693,10 @@ extern "C" int b200hnsw_add_batch_waves(b200hnsw_t *h, const float *vectors, con
     set_error("unknown metric %d", metric);
     return B200HNSW_ERR_BAD_ARG;
   }
+  if (h->n_dead) {
+    set_error("add_batch_waves: the graph holds deleted rows; Add after Delete goes through b200hnsw_add_batch");
+    return B200HNSW_ERR_UNSUPPORTED;
+  }
   if (n == 0) return 0;
   if (h->n + n > 0x7fffffffLL) {
     set_error("add: more than 2^31-1 rows");
@@ -883,6 +887,7 @@ extern "C" int b200hnsw_add_batch_waves(b200hnsw_t *h, const float *vectors, con
       int L = levels[i];
       h->h_keys.push_back(keys[i]);
       h->h_level.push_back(L);
+      h->h_dead.push_back(0);
       h->h_upper_off.push_back(upper_off[i]);
       for (int l = 0; l <= L; l++) {
         if (h->layer_size[l] == 0) h->entry[l] = (int32_t)(h->n + i);

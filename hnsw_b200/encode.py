@@ -80,6 +80,10 @@ def export_graph(g, w: BinaryIO) -> None:
         raise ValueError(f"distance function {g.Distance!r} must be registered with RegisterDistanceFunc")
     w.write(put_varint(encodingVersion) + put_varint(g.M) + struct.pack("<d", float(g.Ml)) +
             put_varint(g.EfSearch) + put_string(name))
+    if getattr(g, "_retired", None):
+        # the reference would write live nodes whose neighbour lists still name deleted keys (replenish re-links
+        # isolated nodes, graph.go:172-219); Import turns those into nil neighbours.  Not reproduced.
+        raise NotImplementedError("Export after Delete is not supported")
     if g.Len() == 0:
         w.write(put_varint(0))
         return

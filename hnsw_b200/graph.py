@@ -69,7 +69,8 @@ class Graph:
         self._dim = 0
         self._max_m = 0
         self._keys: List[int] = []          # row -> key
-        self._row_of = {}                   # key -> row
+        self._row_of = {}                   # key -> row (live keys only)
+        self._retired = set()               # keys removed by Delete
         self._vecs = np.zeros((0, 0), np.float32)  # host copy, grows by doubling
         self.last_stats = None
 
@@ -89,6 +90,7 @@ class Graph:
             _lib.lib().b200hnsw_destroy(self._h)
             self._h = None
         self._keys, self._row_of, self._dim = [], {}, 0
+        self._retired = set()
         self._vecs = np.zeros((0, 0), np.float32)
 
     def __del__(self):
@@ -192,8 +194,13 @@ class Graph:
             if not isinstance(k, (int, np.integer)):
                 raise TypeError("device path orders neighbours by int64 keys; non-integer keys are not supported")
             if k in self._row_of or k in keys:
-                # graph.go:1016-1024 deletes the old node first; Delete is SURVEY.md row N3 (not built yet)
-                raise NotImplementedError(f"key {k} already present: replacing a node needs Delete (not built yet)")
+                # graph.go:1016-1024 isolates the old node in the middle of the insertion and then links the new
+                # one into maps keyed by the same key; lists keyed by row cannot hold that state
+                raise NotImplementedError(f"key {k} already present: replacing a node in place is not supported; "
+                                          f"Delete it and Add it under a new key")
+            if k in self._retired:
+                raise NotImplementedError(f"key {k} was deleted: its node can still be linked under that key "
+                                          f"(graph.go:172-219 re-links isolated nodes); use a new key")
             keys.append(int(k))
         self._add_arrays(keys, np.stack(vecs), levels, metric)
 
@@ -202,15 +209,23 @@ class Graph:
         V = np.ascontiguousarray(V, dtype=np.float32)
         K = np.ascontiguousarray(keys, dtype=np.int64)
         st = _lib.Stats()
+        L = _lib.lib()
+        rows0 = int(L.b200hnsw_rows(self._h))
         t0 = time.perf_counter()
-        if wave_max and wave_max > 0:  # batched construction in waves (not the reference's sequential order)
-            _lib.check(_lib.lib().b200hnsw_add_batch_waves(
-                self._h, V.ctypes.data_as(_lib.f32p), K.ctypes.data_as(_lib.i64p), lv.ctypes.data_as(_lib.i32p),
-                len(K), self.M, self.EfSearch, metric, int(wave_max), C.byref(st)))
-        else:
-            _lib.check(_lib.lib().b200hnsw_add_batch(self._h, V.ctypes.data_as(_lib.f32p),
-                                                     K.ctypes.data_as(_lib.i64p), lv.ctypes.data_as(_lib.i32p),
-                                                     len(K), self.M, self.EfSearch, metric, C.byref(st)))
+        try:
+            if wave_max and wave_max > 0:  # batched construction in waves (not the reference's sequential order)
+                _lib.check(L.b200hnsw_add_batch_waves(
+                    self._h, V.ctypes.data_as(_lib.f32p), K.ctypes.data_as(_lib.i64p), lv.ctypes.data_as(_lib.i32p),
+                    len(K), self.M, self.EfSearch, metric, int(wave_max), C.byref(st)))
+            else:
+                _lib.check(L.b200hnsw_add_batch(self._h, V.ctypes.data_as(_lib.f32p), K.ctypes.data_as(_lib.i64p),
+                                                lv.ctypes.data_as(_lib.i32p), len(K), self.M, self.EfSearch, metric,
+                                                C.byref(st)))
+        except _lib.B200Error:
+            done = int(L.b200hnsw_rows(self._h)) - rows0  # nodes in front of the failing one are in
+            if done > 0:
+                self._store_host(K[:done].tolist(), V[:done])
+            raise
         self.last_stats = st.as_dict()
         self.last_stats["call_s"] = time.perf_counter() - t0  # wall time of the C call (staging + kernels)
         self._store_host(K.tolist(), V)
@@ -233,6 +248,30 @@ class Graph:
         if self.M > self._max_m:
             raise ValueError(f"M={self.M} exceeds the device list stride {self._max_m} fixed at the first Add")
         self._add_arrays(keys, vectors, levels, metric, wave_max)
+
+    # ---- Delete / BatchDelete -------------------------------------------------------------------------------------
+    def BatchDelete(self, keys) -> List[bool]:
+        """graph.go:871-895.  The reference's quirks are kept (see b200hnsw_delete_batch in include/b200hnsw.h): a
+        deleted node can stay linked one-way and Search can still return it; Lookup and Len stop seeing it."""
+        keys = list(keys)
+        if self._h is None or _lib.lib().b200hnsw_layers(self._h) == 0 or not keys:
+            return [False] * len(keys)
+        rows = np.array([self._row_of.get(k, -1) if isinstance(k, (int, np.integer)) else -1 for k in keys],
+                        dtype=np.int32)
+        out = np.zeros(len(keys), dtype=np.uint8)
+        st = _lib.Stats()
+        _lib.check(_lib.lib().b200hnsw_delete_batch(self._h, rows.ctypes.data_as(_lib.i32p), len(keys), self.M,
+                                                    out.ctypes.data_as(_lib.u8p), C.byref(st)))
+        self.last_stats = st.as_dict()
+        for k, ok in zip(keys, out):
+            if ok:
+                del self._row_of[k]
+                self._retired.add(k)
+        return [bool(x) for x in out]
+
+    def Delete(self, key) -> bool:
+        """graph.go:843-866."""
+        return self.BatchDelete([key])[0]
 
     def Add(self, *nodes: Node, levels: Optional[Sequence[int]] = None):
         """graph.go:437-531 (same body as BatchAdd; the reference's Add deadlocks on a duplicate key, F9)."""
@@ -363,8 +402,10 @@ class Graph:
         near = np.asarray(near, dtype=np.float32).reshape(-1)
         if self.Len() > 0 and self.Dims() != len(near):
             raise ValueError(f"embedding dimension mismatch: {self.Dims()} != {len(near)}")
-        if self.Len() == 0:
+        if self._h is None or _lib.lib().b200hnsw_layers(self._h) == 0:
             return None  # graph.go:554-556: (nil, nil)
+        if self.Len() == 0:
+            return []    # every node deleted: the layers are still there, their entry points are nil
         ef = self.EfSearch
         # graph.go:563-569: the reference's hard-wired "dog query" test hack doubles efSearch
         is_dog = len(near) == 3 and near[0] == np.float32(1.0) and near[1] == np.float32(0.2) and \

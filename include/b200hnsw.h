@@ -91,6 +91,7 @@ int b200hnsw_reserve(b200hnsw_t *h, int64_t rows);
 /* Graph.Len (graph.go:829-838), len(g.layers), layer.size (graph.go:260-265), layer.entry (graph.go:246-258:
  * "any node of the layer"; here the first node inserted into it unless overridden). */
 int64_t b200hnsw_len(const b200hnsw_t *h);
+int64_t b200hnsw_rows(const b200hnsw_t *h);   /* rows ever stored (deleted ones included): the next Add starts here */
 int32_t b200hnsw_layers(const b200hnsw_t *h);
 int64_t b200hnsw_layer_size(const b200hnsw_t *h, int32_t layer);
 int32_t b200hnsw_entry(const b200hnsw_t *h, int32_t layer);
@@ -156,6 +157,19 @@ int b200hnsw_add_batch(b200hnsw_t *h, const float *vectors, const int64_t *keys,
 int b200hnsw_add_batch_waves(b200hnsw_t *h, const float *vectors, const int64_t *keys, const int32_t *levels,
                              int64_t n, int32_t m, int32_t ef, int32_t metric, int64_t wave_max,
                              b200hnsw_stats *stats);
+
+/* Graph.Delete / Graph.BatchDelete (graph.go:843-895; layerNode.isolate graph.go:223-235, replenish graph.go:172-219).
+ * rows[i] = the row the caller's key map holds for the i-th key, -1 for an unknown key; processed in call order, as
+ * the reference's loop under one lock.  out_deleted[i] (may be null) mirrors the reference's []bool: 1 iff the row
+ * was a live member.  m = Graph.M.  As in the reference the node's storage survives: it leaves layer.nodes (entry
+ * point, elevator lookup, len), every neighbour drops its link and is replenished (which can link the node again
+ * one-way), its own list is kept, traversals still walk through it and Search can still return its row.  A Search
+ * whose elevator is a deleted row returns 0 results (graph.go:573-583); an Add in that situation fails with
+ * "no nodes found in neighborhood search" (graph.go:501-505) and, unlike the reference, leaves the graph untouched. */
+int b200hnsw_delete_batch(b200hnsw_t *h, const int32_t *rows, int64_t n, int32_t m, uint8_t *out_deleted,
+                          b200hnsw_stats *stats);
+/* 1 if `row` was deleted, 0 if live, -1 if out of range */
+int32_t b200hnsw_is_deleted(const b200hnsw_t *h, int32_t row);
 
 /* ---- multi-GPU: merge G per-shard result lists per query into one top-k (no reference counterpart; tie order =
  *      lower shard first, the stable order of hybrid/adapter.go:264-292).  Inputs [G][B][k] ascending-sorted

@@ -82,6 +82,18 @@ def lib():
     L.ora_graph_neighbors.argtypes = [C.c_void_p, C.c_int, C.c_int32, i32p]
     L.ora_graph_counters.argtypes = [C.c_void_p, C.POINTER(Counters)]
     L.ora_graph_reset_counters.argtypes = [C.c_void_p]
+    L.ora_graph_layer_rows.restype = C.c_int64
+    L.ora_graph_layer_rows.argtypes = [C.c_void_p, C.c_int]
+    L.ora_graph_delete.restype = C.c_int
+    L.ora_graph_delete.argtypes = [C.c_void_p, C.c_int64]
+    L.ora_graph_delete_row.restype = C.c_int
+    L.ora_graph_delete_row.argtypes = [C.c_void_p, C.c_int32]
+    L.ora_graph_is_dead.restype = C.c_int
+    L.ora_graph_is_dead.argtypes = [C.c_void_p, C.c_int32]
+    L.ora_graph_dead_count.restype = C.c_int64
+    L.ora_graph_dead_count.argtypes = [C.c_void_p]
+    L.ora_graph_set_build_mode.restype = None
+    L.ora_graph_set_build_mode.argtypes = [C.c_void_p, C.c_int]
     L.ora_graph_add.restype = C.c_int32
     L.ora_graph_add.argtypes = [C.c_void_p, C.c_int64, f32p, C.c_int, C.c_int]
     L.ora_graph_put_node.restype = C.c_int32
@@ -222,6 +234,20 @@ class Graph:
             raise RuntimeError(f"ora_graph_add failed: {row}")
         return row
 
+    def delete(self, key) -> bool:
+        """Graph.Delete (graph.go:843-866)."""
+        return bool(self.L.ora_graph_delete(self.h, int(key)))
+
+    def batch_delete(self, keys):
+        """Graph.BatchDelete (graph.go:871-895): the same loop under one lock."""
+        return [self.delete(k) for k in keys]
+
+    def is_dead(self, row) -> bool:
+        return self.L.ora_graph_is_dead(self.h, int(row)) == 1
+
+    def set_build_mode(self, mode):
+        self.L.ora_graph_set_build_mode(self.h, int(mode))
+
     def add_many(self, keys, vecs, levels, ef):
         vecs = np.ascontiguousarray(vecs, dtype=np.float32)
         keys = np.ascontiguousarray(keys, dtype=np.int64)
@@ -264,7 +290,7 @@ class Graph:
 
     def dump_layer(self, layer):
         """CSR of one layer over its member rows: (rows, ptr, nbr)."""
-        n = int(self.L.ora_graph_layer_size(self.h, layer))
+        n = int(self.L.ora_graph_layer_rows(self.h, layer))  # deleted rows keep their lists
         nn = self.L.ora_graph_dump_layer(self.h, layer, None, None, None)
         rows = np.empty(n, dtype=np.int32)
         ptr = np.empty(n + 1, dtype=np.int64)

@@ -91,6 +91,14 @@ void ora_graph_reset_counters(ora_graph *g);
 
 /* Graph.Add for one node (graph.go:445-528); `level` is randomLevel()'s draw. Returns row or <0. */
 int32_t ora_graph_add(ora_graph *g, int64_t key, const float *vec, int level, int ef);
+/* Graph.Delete (graph.go:843-866): 1 if the key was present.  The row stays addressable (see ora_graph.c). */
+int64_t ora_graph_layer_rows(const ora_graph *g, int layer);
+int ora_graph_delete(ora_graph *g, int64_t key);
+int ora_graph_delete_row(ora_graph *g, int32_t row);
+int ora_graph_is_dead(const ora_graph *g, int32_t row);
+int64_t ora_graph_dead_count(const ora_graph *g);
+/* NOT the reference: layer search used by Add (ORA_MODE_*); only for the recall study in scripts/ext_recall.py */
+void ora_graph_set_build_mode(ora_graph *g, int mode);
 /* Hand-build a layer (test fixtures such as graph_test.go:27-74): appends a node to `layer`
  * without linking; ora_graph_link adds a one-directional edge. */
 int32_t ora_graph_put_node(ora_graph *g, int64_t key, const float *vec, int level);

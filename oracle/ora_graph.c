@@ -23,6 +23,9 @@ struct ora_graph {
   float *vec;
   int64_t *key;
   int32_t *level;
+  uint8_t *dead; /* 1 = removed from layer.nodes by Delete (graph.go:843-866); the row and its list stay */
+  int64_t n_dead;
+  int build_mode; /* ORA_MODE_* of the layer search used by Add (reference: ORA_MODE_REFERENCE) */
   int32_t *adj0;
   int32_t *deg0;
   int32_t *upper_off;
@@ -59,6 +62,7 @@ void ora_graph_free(ora_graph *g) {
   free(g->vec);
   free(g->key);
   free(g->level);
+  free(g->dead);
   free(g->adj0);
   free(g->deg0);
   free(g->upper_off);
@@ -110,6 +114,8 @@ static void grow_rows(ora_graph *g) {
   g->vec = (float *)realloc(g->vec, sizeof(float) * (size_t)cap * g->dim);
   g->key = (int64_t *)realloc(g->key, sizeof(int64_t) * (size_t)cap);
   g->level = (int32_t *)realloc(g->level, sizeof(int32_t) * (size_t)cap);
+  g->dead = (uint8_t *)realloc(g->dead, (size_t)cap);
+  memset(g->dead + g->cap, 0, (size_t)(cap - g->cap));
   g->adj0 = (int32_t *)realloc(g->adj0, sizeof(int32_t) * (size_t)cap * g->stride);
   g->deg0 = (int32_t *)realloc(g->deg0, sizeof(int32_t) * (size_t)cap);
   g->upper_off = (int32_t *)realloc(g->upper_off, sizeof(int32_t) * (size_t)cap);
@@ -351,7 +357,7 @@ static int graph_search(const ora_graph *g, visited_t *vis, ora_counters *ctr, c
   int32_t elevator = -1;
   for (int layer = g->n_layers - 1; layer >= 0; layer--) {
     int32_t sp = entries ? entries[layer] : g->entry[layer];
-    if (elevator >= 0) sp = elevator;
+    if (elevator >= 0) sp = g->dead[elevator] ? -1 : elevator; /* layer.nodes[*elevator]: nil once deleted */
     if (layer > 0) {
       int32_t r;
       float d;
@@ -436,47 +442,105 @@ void ora_graph_batch_search(ora_graph *g, const float *queries, int64_t nq, int 
 /* ---- Graph.Add for one node -- graph.go:445-528 ----------------------------------------------- */
 int32_t ora_graph_add(ora_graph *g, int64_t key, const float *vec, int level, int ef) {
   if (level < 0 || level >= ORA_MAX_LAYERS) return -1;
-  int32_t row = new_row(g, key, vec, level);
-  while (level >= g->n_layers) { /* graph.go:462-464 */
-    g->entry[g->n_layers] = -1;
-    g->layer_size[g->n_layers] = 0;
-    g->n_layers++;
-  }
-  int32_t elevator = -1;
-  int M = g->M;
-  int32_t *nb_rows = (int32_t *)malloc(sizeof(int32_t) * (size_t)M);
+  /* A layer emptied by deletions above the drawn level: the reference parks the node there without the layers
+   * in between (graph.go:485-488), after which every Search loses its elevator.  Not reproduced: refused. */
+  for (int i = level + 1; i < g->n_layers; i++)
+    if (g->layer_size[i] == 0) return -3;
+  /* The reference interleaves search and linking per layer (graph.go:475-522).  A layer's search reads that
+   * layer's lists only and linking at layer i writes layer-i lists only, so running every search first gives the
+   * same neighbourhoods; it lets a failed Add (deleted elevator, graph.go:501-505) leave the graph untouched,
+   * where the reference leaves the node half inserted. */
+  const int M = g->M;
+  const int top = (g->n_layers > level + 1 ? g->n_layers : level + 1) - 1; /* graph.go:462-464 */
+  int32_t *nb_rows = (int32_t *)malloc(sizeof(int32_t) * (size_t)M * (size_t)(top + 1));
   float *nb_d = (float *)malloc(sizeof(float) * (size_t)M);
-  for (int i = g->n_layers - 1; i >= 0; i--) { /* graph.go:475 */
-    if (g->layer_size[i] == 0) {               /* graph.go:485-488 */
-      if (i > level) {
-        /* An empty layer above the drawn level only arises after deletions; the row has no list
-         * there.  Out of scope with Delete. */
-        continue;
-      }
-      g->entry[i] = row;
-      g->layer_size[i] = 1;
-      continue;
-    }
-    int32_t sp = g->entry[i]; /* graph.go:492 */
-    if (elevator >= 0) sp = elevator; /* graph.go:496-498 */
-    int cnt = ora_layer_search(g, i, sp, M, ef, vec, ORA_MODE_REFERENCE, nb_rows, nb_d); /* graph.go:500 */
-    if (cnt == 0) {
+  int cnts[ORA_MAX_LAYERS];
+  int32_t elevator = -1;
+  for (int i = top; i >= 0; i--) { /* graph.go:475 */
+    cnts[i] = -1;
+    if (i >= g->n_layers || g->layer_size[i] == 0) continue; /* graph.go:485-488 */
+    int32_t sp = g->entry[i];                                 /* graph.go:492 */
+    if (elevator >= 0) sp = g->dead[elevator] ? -1 : elevator; /* graph.go:496-498: layer.nodes[*elevator] */
+    int cnt = ora_layer_search(g, i, sp, M, ef, vec, g->build_mode, nb_rows + (size_t)i * M, nb_d); /* :500 */
+    if (cnt == 0) { /* graph.go:501-505 "no nodes found in neighborhood search" */
       free(nb_rows);
       free(nb_d);
       return -2;
     }
-    elevator = nb_rows[0]; /* graph.go:508 */
-    if (level >= i) {      /* graph.go:510 */
-      g->layer_size[i]++;  /* graph.go:515 */
-      for (int t = 0; t < cnt; t++) { /* graph.go:516-520, heap-array order */
-        add_neighbor(g, i, nb_rows[t], row, M, g->metric);
-        add_neighbor(g, i, row, nb_rows[t], M, g->metric);
+    cnts[i] = cnt;
+    elevator = nb_rows[(size_t)i * M]; /* graph.go:508 */
+  }
+  int32_t row = new_row(g, key, vec, level);
+  while (level >= g->n_layers) {
+    g->entry[g->n_layers] = -1;
+    g->layer_size[g->n_layers] = 0;
+    g->n_layers++;
+  }
+  for (int i = top; i >= 0; i--) {
+    if (cnts[i] < 0) { /* empty layer takes the node as its only member */
+      g->entry[i] = row;
+      g->layer_size[i] = 1;
+      continue;
+    }
+    if (level >= i) {     /* graph.go:510 */
+      g->layer_size[i]++; /* graph.go:515 */
+      for (int t = 0; t < cnts[i]; t++) { /* graph.go:516-520, heap-array order */
+        add_neighbor(g, i, nb_rows[(size_t)i * M + t], row, M, g->metric);
+        add_neighbor(g, i, row, nb_rows[(size_t)i * M + t], M, g->metric);
       }
     }
   }
   free(nb_rows);
   free(nb_d);
   return row;
+}
+
+/* ---- Graph.Delete -- graph.go:843-866; layerNode.isolate -- graph.go:223-235 ------------------
+ * The key leaves layer.nodes of every layer it is in (base layer first, the order of h.layers); per layer every
+ * neighbour drops its link to the node and is replenished at once, in ascending key order (the stand-in for
+ * Go's map order).  As in the reference the node object survives: its own list is untouched, a replenish can
+ * link it again one-way through a neighbour that still lists it, traversals walk through it and can return it;
+ * only layer.nodes lookups (entry point, elevator, Lookup, Len) stop seeing it. */
+void ora_graph_set_build_mode(ora_graph *g, int mode) { g->build_mode = mode; }
+int ora_graph_is_dead(const ora_graph *g, int32_t row) { return row >= 0 && row < g->n ? g->dead[row] : -1; }
+int64_t ora_graph_dead_count(const ora_graph *g) { return g->n_dead; }
+
+int ora_graph_delete_row(ora_graph *g, int32_t row) {
+  if (row < 0 || row >= g->n || g->dead[row]) return 0;
+  g->dead[row] = 1;
+  g->n_dead++;
+  int32_t *nb = (int32_t *)malloc(sizeof(int32_t) * (size_t)g->stride);
+  for (int layer = 0; layer <= g->level[row] && layer < g->n_layers; layer++) {
+    g->layer_size[layer]--; /* delete(layer.nodes, key) */
+    if (g->entry[layer] == row) { /* entry(): lowest live member row takes over */
+      int32_t e = -1;
+      for (int32_t r = 0; r < (int32_t)g->n; r++)
+        if (!g->dead[r] && g->level[r] >= layer) {
+          e = r;
+          break;
+        }
+      g->entry[layer] = e;
+    }
+    int32_t *deg;
+    int32_t *l = list_ptr(g, layer, row, &deg);
+    int n = *deg;
+    memcpy(nb, l, sizeof(int32_t) * (size_t)n); /* the node's own map is not modified by isolate */
+    for (int i = 0; i < n; i++) {
+      int32_t *ndeg;
+      int32_t *nl = list_ptr(g, layer, nb[i], &ndeg);
+      if (!nl) continue;
+      list_delete(g, nl, ndeg, row); /* graph.go:232 */
+      replenish(g, layer, nb[i], g->M); /* graph.go:233 */
+    }
+  }
+  free(nb);
+  return 1;
+}
+
+int ora_graph_delete(ora_graph *g, int64_t key) {
+  for (int32_t r = (int32_t)g->n - 1; r >= 0; r--)
+    if (!g->dead[r] && g->key[r] == key) return ora_graph_delete_row(g, r);
+  return 0;
 }
 
 int32_t ora_graph_put_node(ora_graph *g, int64_t key, const float *vec, int level) {
@@ -501,7 +565,13 @@ int ora_graph_link(ora_graph *g, int layer, int32_t from, int32_t to) {
   return 0;
 }
 
-/* bulk read-back for the test harness: CSR of one layer over its member rows (ascending row) */
+/* rows that own a list in `layer` (members, and former members removed by Delete) */
+int64_t ora_graph_layer_rows(const ora_graph *g, int layer) {
+  int64_t nm = 0;
+  for (int32_t r = 0; r < (int32_t)g->n; r++) nm += g->level[r] >= layer;
+  return nm;
+}
+/* bulk read-back for the test harness: CSR of one layer over the rows that own a list in it (ascending row) */
 int64_t ora_graph_dump_layer(const ora_graph *g, int layer, int32_t *rows, int64_t *ptr, int32_t *nbr) {
   int64_t nm = 0, nn = 0;
   for (int32_t r = 0; r < (int32_t)g->n; r++) {
@@ -631,7 +701,7 @@ static void *waveS_worker(void *arg) {
     int32_t elevator = -1;
     for (int i = J->old_layers - 1; i >= 0; i--) {
       int32_t sp = elevator >= 0 ? elevator : g->entry[i];
-      int cnt = layer_search(g, &v, &J->ctr, i, sp, M, J->ef, vec, ORA_MODE_REFERENCE, rows, d);
+      int cnt = layer_search(g, &v, &J->ctr, i, sp, M, J->ef, vec, g->build_mode, rows, d);
       if (cnt == 0) {
         J->fail = 1;
         break;
@@ -898,6 +968,7 @@ static int wave_commit(ora_graph *g, int32_t first_row, int64_t w, int ef, int n
 int64_t ora_graph_add_waves(ora_graph *g, const int64_t *keys, const float *vecs, const int32_t *levels, int64_t n,
                             int ef, int64_t wave_max, int n_threads) {
   int64_t i = 0;
+  if (g->n_dead) return 0; /* after a Delete, Add goes through the sequential path (ora_graph_add) */
   while (i < n) {
     int64_t w = ora_wave_len(g->n, g->n_layers, levels + i, n - i, wave_max);
     int32_t first_row = (int32_t)g->n;
