@@ -32,10 +32,17 @@ constexpr int GM_STAGES = 4;  // at most; 3 when k is large (GemmParams::stages)
 constexpr int GM_CB = 8;   // candidates a thread stages in shared memory before it appends them to the query's list
 constexpr int GM_A_BYTES = GM_M * GM_K * 2;   // 16 KB
 constexpr int GM_B_BYTES = GM_N * GM_K * 2;   // 32 KB
-constexpr int GM_EPI_WARPS = 8;  // two per TMEM lane quarter, each takes half of the tile's columns
-constexpr int GM_EPI = GM_EPI_WARPS * 32;
-constexpr int GM_THREADS = 64 + GM_EPI;
+// Epilogue warps: EW = 16 (four per TMEM lane quarter, each takes 64 of the tile's 256 columns) when the per-thread slot
+// tables fit beside the operand stages, else 8 (128 columns each).  Four epilogue warps per scheduler hide the
+// fixed-latency stalls that two cannot (ncu: issue slots 32 % busy with 8 warps).
 constexpr int GM_MAX_K = 64;   // result size the slot table supports
+template <int EW>
+struct GemmShape {
+  static constexpr int EPI = EW * 32;             // epilogue threads
+  static constexpr int THREADS = 64 + EPI;        // + TMA producer warp + MMA warp
+  static constexpr int COLS_W = GM_N / (EW / 4);  // columns of a tile one warp scans
+  static constexpr int CHUNKS = COLS_W / 32;      // 32-column tcgen05.ld chunks per warp and tile
+};
 
 // ---- PTX wrappers ---------------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -145,27 +152,63 @@ struct GemmParams {
   int cand_cap;
 };
 
-struct GemmSmem {  // S = number of operand stages
-  static __host__ __device__ size_t slots(int S) { return (size_t)S * (GM_A_BYTES + GM_B_BYTES); }  // float[GM_EPI][k]
-  static __host__ __device__ size_t aux(int S, int k) { return slots(S) + (size_t)GM_EPI * k * 4; }  // float[2][256]
-  static __host__ __device__ size_t cbuf(int S, int k) { return aux(S, k) + 2 * GM_N * 4; }  // int[GM_CB][GM_EPI]
-  static __host__ __device__ size_t bars(int S, int k) { return cbuf(S, k) + GM_CB * GM_EPI * 4; }  // barriers, tmem ptr
-  static __host__ __device__ size_t total(int S, int k) { return bars(S, k) + 16 * 8 + 1024; }      // + alignment slack
+// Operand region: `stages` ring slots of one K block each.  When the whole query tile (kblocks K blocks of A) fits in
+// 64 KB it is loaded once and stays (a_res): the ring then carries row tiles only, and a third of the L2 -> SM
+// traffic of a short-K problem disappears (ncu, dim 128: 30.6 GB of TMA loads per 10 k x 1 M search, 10 GB of it A).
+__host__ __device__ inline bool gm_a_resident(int kblocks) { return kblocks * GM_A_BYTES <= 64 * 1024; }
+__host__ __device__ inline int gm_operand_bytes(int kblocks, int stages) {
+  return gm_a_resident(kblocks) ? kblocks * GM_A_BYTES + stages * GM_B_BYTES : stages * (GM_A_BYTES + GM_B_BYTES);
+}
+template <int EW>
+struct GemmSmem {  // S = bytes of the operand region (gm_operand_bytes)
+  using Sh = GemmShape<EW>;
+  static __host__ __device__ size_t slots(int S) { return (size_t)S; }                              // float[EPI][k]
+  static __host__ __device__ size_t aux(int S, int k) { return slots(S) + (size_t)Sh::EPI * k * 4; }  // float[EW][2][COLS_W]
+  static __host__ __device__ size_t cbuf(int S, int k) { return aux(S, k) + (size_t)EW * 2 * Sh::COLS_W * 4; }  // int[GM_CB][EPI]
+  static __host__ __device__ size_t bars(int S, int k) { return cbuf(S, k) + (size_t)GM_CB * Sh::EPI * 4; }  // barriers, tmem ptr
+  static __host__ __device__ size_t total(int S, int k) { return bars(S, k) + 16 * 8 + 1024; }        // + alignment slack
 };
 
+__device__ __forceinline__ float4 lds_f4(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ float lds_f1(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts_f1(uint32_t addr, float v) {
+  asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+// score of one row from its accumulator: |x|^2 - 2 q.x (Euclidean, a = |x|^2) or 1 - q.x / (|x||q|) (cosine, a = 1/|x|)
 template <int METRIC>
-__global__ void __launch_bounds__(GM_THREADS, 1)
+__device__ __forceinline__ float gm_score(float acc, float a, float qf) {
+  return METRIC == 0 ? fmaf(qf, acc, a) : fmaf(acc * a, qf, 1.f);
+}
+
+template <int METRIC, int EW>
+__global__ void __launch_bounds__(GemmShape<EW>::THREADS, 1)
 exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x,
                   GemmParams p) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char *smem = reinterpret_cast<unsigned char *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  using Sh = GemmShape<EW>;
+  using Sm = GemmSmem<EW>;
+  constexpr int EPI = Sh::EPI, COLS_W = Sh::COLS_W, CHUNKS = Sh::CHUNKS;
   const int S = p.stages;
-  float *slots = reinterpret_cast<float *>(smem + GemmSmem::slots(S));
-  float *aux_s = reinterpret_cast<float *>(smem + GemmSmem::aux(S, p.k));
-  int *cbuf = reinterpret_cast<int *>(smem + GemmSmem::cbuf(S, p.k));
-  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + GemmSmem::bars(S, p.k));
-  uint32_t *tmem_ptr_s = reinterpret_cast<uint32_t *>(bars + 2 * GM_STAGES + 4);
+  const bool a_res = gm_a_resident(p.kblocks);
+  const int OB = gm_operand_bytes(p.kblocks, S);
+  const uint32_t a_bytes = a_res ? (uint32_t)p.kblocks * GM_A_BYTES : 0u;   // resident query tile, in front of the ring
+  const uint32_t st_bytes = a_res ? GM_B_BYTES : GM_A_BYTES + GM_B_BYTES;   // one ring slot
+  const uint32_t b_off = a_res ? 0u : (uint32_t)GM_A_BYTES;                 // row tile inside a ring slot
+  float *slots = reinterpret_cast<float *>(smem + Sm::slots(OB));
+  int *cbuf = reinterpret_cast<int *>(smem + Sm::cbuf(OB, p.k));
+  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + Sm::bars(OB, p.k));
+  uint32_t *tmem_ptr_s = reinterpret_cast<uint32_t *>(bars + 2 * GM_STAGES + 5);
+  const uint32_t bar_a = smem_u32(bars + 2 * GM_STAGES + 4);
   const uint32_t bar_full = smem_u32(bars), bar_empty = smem_u32(bars + GM_STAGES);
   const uint32_t bar_tfull = smem_u32(bars + 2 * GM_STAGES), bar_tempty = smem_u32(bars + 2 * GM_STAGES + 2);
   const uint32_t s_base = smem_u32(smem);
@@ -186,8 +229,9 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     }
     for (int i = 0; i < 2; i++) {
       mbar_init(bar_tfull + 8 * i, 1);
-      mbar_init(bar_tempty + 8 * i, GM_EPI_WARPS);
+      mbar_init(bar_tempty + 8 * i, EW);
     }
+    mbar_init(bar_a, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {  // TMEM: 2 accumulator stages x 256 fp32 columns
@@ -204,13 +248,18 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     // ===== TMA producer =====
     if (lane == 0) {
       int stage = 0, phase = 0;
+      if (a_res && seq > 0) {
+        mbar_expect_tx(bar_a, a_bytes);
+        for (int kb = 0; kb < p.kblocks; kb++)
+          tma_load_2d(s_base + kb * GM_A_BYTES, &tmap_q, kb * GM_K, mt * GM_M, bar_a);
+      }
       for (int idx = 0; idx < seq; idx++) {
         const int tile = t_begin + (idx < warm ? idx : idx - warm);
         for (int kb = 0; kb < p.kblocks; kb++) {
           mbar_wait_backoff(bar_empty + 8 * stage, phase ^ 1);
-          const uint32_t sa = s_base + stage * (GM_A_BYTES + GM_B_BYTES), sb = sa + GM_A_BYTES;
-          mbar_expect_tx(bar_full + 8 * stage, GM_A_BYTES + GM_B_BYTES);
-          tma_load_2d(sa, &tmap_q, kb * GM_K, mt * GM_M, bar_full + 8 * stage);
+          const uint32_t sa = s_base + a_bytes + stage * st_bytes, sb = sa + b_off;
+          mbar_expect_tx(bar_full + 8 * stage, st_bytes);
+          if (!a_res) tma_load_2d(sa, &tmap_q, kb * GM_K, mt * GM_M, bar_full + 8 * stage);
           tma_load_2d(sb, &tmap_x, kb * GM_K, tile * GM_N, bar_full + 8 * stage);
           if (++stage == S) {
             stage = 0;
@@ -223,6 +272,7 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     // ===== MMA issuer (one thread) =====
     if (lane == 0) {
       int stage = 0, phase = 0;
+      if (a_res && seq > 0) mbar_wait(bar_a, 0);
       for (int idx = 0; idx < seq; idx++) {
         const int as = idx & 1;
         mbar_wait(bar_tempty + 8 * as, ((idx >> 1) & 1) ^ 1);  // epilogue has drained this accumulator
@@ -231,7 +281,8 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         for (int kb = 0; kb < p.kblocks; kb++) {
           mbar_wait(bar_full + 8 * stage, phase);
           tc_fence_after();
-          const uint32_t sa = s_base + stage * (GM_A_BYTES + GM_B_BYTES), sb = sa + GM_A_BYTES;
+          const uint32_t ring = s_base + a_bytes + stage * st_bytes;
+          const uint32_t sa = a_res ? s_base + kb * GM_A_BYTES : ring, sb = ring + b_off;
           const uint64_t adesc = umma_desc_sw128(sa), bdesc = umma_desc_sw128(sb);
 #pragma unroll
           for (int k4 = 0; k4 < GM_K / 16; k4++)  // UMMA K = 16 bf16 = 32 B: advance the start address field by 2
@@ -246,13 +297,14 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       }
     }
   } else {
-    // ===== epilogue: one query row per thread =====
+    // ===== epilogue: one query row per thread, COLS_W columns of every tile per warp =====
     const int ew = warp & 3;                  // TMEM lane quarter this warp may access
     const int r = ew * 32 + lane;             // row of the tile = TMEM lane
     const long long q = (long long)mt * GM_M + r;
     const bool live_q = q < p.B;
-    const int et = (warp - 2) * 32 + lane;    // 0..GM_EPI-1 among the epilogue threads
-    const int ch0 = ((warp - 2) >> 2) * (GM_N / 64);  // first 32-column chunk of this warp's half of the tile
+    const int e = warp - 2;                   // 0..EW-1 among the epilogue warps
+    const int et = e * 32 + lane;             // 0..EPI-1 among the epilogue threads
+    const int ch0 = (e >> 2) * CHUNKS;        // first 32-column chunk of this warp's share of the tile
     float *my_slots = slots + (size_t)et * p.k;
     for (int j = 0; j < p.k; j++) my_slots[j] = __int_as_float(0x7f800000);
     const float margin = live_q ? p.q_margin[q] : 0.f;
@@ -269,65 +321,69 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       if (ccnt > 0) {
         const int at = atomicAdd(&p.cand_cnt[q], ccnt);
         for (int i = 0; i < ccnt; i++)
-          if (at + i < p.cand_cap) p.cand[q * p.cand_cap + at + i] = mybuf[i * GM_EPI];
+          if (at + i < p.cand_cap) p.cand[q * p.cand_cap + at + i] = mybuf[i * EPI];
         ccnt = 0;
       }
     };
-    // per-row terms of tile 0; those of tile idx+1 are fetched while tile idx is processed
+    // Per-row terms (|x|^2 or 1/|x|) of this warp's columns: staged in a buffer only this warp touches (two tiles
+    // deep), fetched one tile ahead, so no barrier between the epilogue warps is needed.
+    constexpr int AV = COLS_W / 32;           // floats per lane and tile
+    const uint32_t aux_w = s_base + (uint32_t)Sm::aux(OB, p.k) + (uint32_t)(e * 2 * COLS_W) * 4u;
     auto tile_of = [&](int idx) { return t_begin + (idx < warm ? idx : idx - warm); };
+    auto aux_fetch = [&](int idx, float (&nx)[AV]) {
+      const float *src = p.aux + (long long)tile_of(idx) * GM_N + ch0 * 32 + lane * AV;
+#pragma unroll
+      for (int i = 0; i < AV; i++) nx[i] = __ldg(src + i);
+    };
+    auto aux_store = [&](int buf, const float (&nx)[AV]) {
+#pragma unroll
+      for (int i = 0; i < AV; i++) sts_f1(aux_w + (uint32_t)(buf * COLS_W + lane * AV + i) * 4u, nx[i]);
+    };
     if (seq > 0) {
-      aux_s[et] = p.aux[(long long)tile_of(0) * GM_N + et];
+      float n0[AV];
+      aux_fetch(0, n0);
+      aux_store(0, n0);
     }
-    asm volatile("bar.sync 1, %0;" ::"n"(GM_EPI) : "memory");
+    __syncwarp();
     for (int idx = 0; idx < seq; idx++) {
       const int as = idx & 1;
       const int tile = tile_of(idx);
       const bool emit = live_q && idx >= warm;
-      float *ax = aux_s + as * GM_N;
-      float nx0 = 0.f;
-      if (idx + 1 < seq) nx0 = p.aux[(long long)tile_of(idx + 1) * GM_N + et];
+      const uint32_t ax = aux_w + (uint32_t)(as * COLS_W) * 4u;
+      float nx[AV];
+      if (idx + 1 < seq) aux_fetch(idx + 1, nx);
       mbar_wait(bar_tfull + 8 * as, (idx >> 1) & 1);
       tc_fence_after();
-      const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + as * GM_N;
+      const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + as * GM_N + ch0 * 32;
       uint32_t va[32], vb[32];
-      tmem_ld32(taddr + ch0 * 32, va);
-#pragma unroll 1
-      for (int c2 = 0; c2 < GM_N / 128; c2++) {
+      tmem_ld32(taddr, va);
 #pragma unroll
-        for (int half = 0; half < 2; half++) {
-        const int c = ch0 + 2 * c2 + half;
-        uint32_t (&v)[32] = half == 0 ? va : vb;
-        tmem_ld_wait(v);  // chunk c has landed; chunk c+1 is requested before c is looked at
-        if (c + 1 < ch0 + GM_N / 64) tmem_ld32(taddr + (c + 1) * 32, half == 0 ? vb : va);
-        const float4 *ax4 = reinterpret_cast<const float4 *>(ax + c * 32);
-        float sc[32];
-#pragma unroll
-        for (int j4 = 0; j4 < 8; j4++) {  // 32 independent scores: no branch, no dependent chain
-          const float4 a = ax4[j4];
-          if (METRIC == 0) {
-            sc[4 * j4 + 0] = fmaf(qf, __uint_as_float(v[4 * j4 + 0]), a.x);
-            sc[4 * j4 + 1] = fmaf(qf, __uint_as_float(v[4 * j4 + 1]), a.y);
-            sc[4 * j4 + 2] = fmaf(qf, __uint_as_float(v[4 * j4 + 2]), a.z);
-            sc[4 * j4 + 3] = fmaf(qf, __uint_as_float(v[4 * j4 + 3]), a.w);
-          } else {
-            sc[4 * j4 + 0] = fmaf(__uint_as_float(v[4 * j4 + 0]) * a.x, qf, 1.f);
-            sc[4 * j4 + 1] = fmaf(__uint_as_float(v[4 * j4 + 1]) * a.y, qf, 1.f);
-            sc[4 * j4 + 2] = fmaf(__uint_as_float(v[4 * j4 + 2]) * a.z, qf, 1.f);
-            sc[4 * j4 + 3] = fmaf(__uint_as_float(v[4 * j4 + 3]) * a.w, qf, 1.f);
-          }
-        }
+      for (int cl = 0; cl < CHUNKS; cl++) {
+        uint32_t (&v)[32] = (cl & 1) == 0 ? va : vb;
+        tmem_ld_wait(v);  // chunk cl has landed; chunk cl+1 is requested before cl is looked at
+        if (cl + 1 < CHUNKS) tmem_ld32(taddr + (cl + 1) * 32, (cl & 1) == 0 ? vb : va);
+        const uint32_t axc = ax + (uint32_t)(cl * 32) * 4u;
         float m8[8];
 #pragma unroll
-        for (int j = 0; j < 8; j++)
-          m8[j] = fminf(fminf(sc[j], sc[j + 8]), fminf(sc[j + 16], sc[j + 24]));  // fminf drops NaN (dead rows)
+        for (int j4 = 0; j4 < 8; j4++) {  // 32 independent scores: no branch, no dependent chain
+          const float4 a = lds_f4(axc + j4 * 16);
+          const float s0 = gm_score<METRIC>(__uint_as_float(v[4 * j4 + 0]), a.x, qf);
+          const float s1 = gm_score<METRIC>(__uint_as_float(v[4 * j4 + 1]), a.y, qf);
+          const float s2 = gm_score<METRIC>(__uint_as_float(v[4 * j4 + 2]), a.z, qf);
+          const float s3 = gm_score<METRIC>(__uint_as_float(v[4 * j4 + 3]), a.w, qf);
+          m8[j4] = fminf(fminf(s0, s1), fminf(s2, s3));  // fminf drops NaN (dead rows)
+        }
         const float bmin = fminf(fminf(fminf(m8[0], m8[1]), fminf(m8[2], m8[3])),
                                  fminf(fminf(m8[4], m8[5]), fminf(m8[6], m8[7])));
-        if (emit && bmin <= thr) {  // some row of this block passes the filter
+        if (emit && bmin <= thr) {  // some row of this block passes the filter: score the block again, row by row
           unsigned pass = 0;
 #pragma unroll
-          for (int j = 0; j < 32; j++)  // branch-free; dead rows score +inf / NaN
-            pass |= (unsigned)((sc[j] <= thr) & (sc[j] < INF)) << j;
+          for (int j = 0; j < 32; j++) {  // branch-free; dead rows score +inf / NaN
+            const float sj = gm_score<METRIC>(__uint_as_float(v[j]), lds_f1(axc + j * 4), qf);
+            pass |= (unsigned)((sj <= thr) & (sj < INF)) << j;
+          }
           const int np = __popc(pass);
+          const int row0 = tile * GM_N + (ch0 + cl) * 32;
           if (ccnt + np > GM_CB) flush();
           if (np > GM_CB) {  // only while the threshold is still loose: straight to the list
             const int at = atomicAdd(&p.cand_cnt[q], np);
@@ -335,14 +391,14 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
             while (pass) {
               const int j = __ffs(pass) - 1;
               pass &= pass - 1;
-              if (at + i < p.cand_cap) p.cand[q * p.cand_cap + at + i] = tile * GM_N + c * 32 + j;
+              if (at + i < p.cand_cap) p.cand[q * p.cand_cap + at + i] = row0 + j;
               i++;
             }
           } else {
             while (pass) {
               const int j = __ffs(pass) - 1;
               pass &= pass - 1;
-              mybuf[ccnt * GM_EPI] = tile * GM_N + c * 32 + j;
+              mybuf[ccnt * EPI] = row0 + j;
               ccnt++;
             }
           }
@@ -352,20 +408,19 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         my_slots[sl] = fminf(my_slots[sl], bmin);
         if (++sl == p.k) sl = 0;
         sub++;
-        }
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
-      // next tile's terms into the other buffer (its previous readers finished before the barrier of the last tile)
-      aux_s[(as ^ 1) * GM_N + et] = nx0;
-      asm volatile("bar.sync 1, %0;" ::"n"(GM_EPI) : "memory");
+      // next tile's terms into the other buffer (this warp's reads of it ended one tile ago)
+      if (idx + 1 < seq) aux_store(as ^ 1, nx);
+      __syncwarp();
       if (sub >= p.k && live_q) {
         // Now and then (often at first, when bounds improve fast) merge the slots with those of the other CTAs that
         // work on this query: slot j of every CTA covers rows disjoint from slot j' of any CTA, so the element-wise
         // minimum over CTAs is again k minima over k disjoint row sets.
         const int done = idx + 1;
-        if (sub - GM_N / 64 < p.k || (done & (done - 1)) == 0 || (done & 31) == 0 || idx == seq - 1) {
+        if (sub - CHUNKS < p.k || (done & (done - 1)) == 0 || (done & 31) == 0 || idx == seq - 1) {
           uint32_t *sg = p.slots_g + q * p.k;
           for (int j = 0; j < p.k; j++) {
             const uint32_t mine = ord_bits(my_slots[j]);
@@ -571,13 +626,35 @@ int exact_after_add(b200exact *x, int64_t first, int64_t count, cudaStream_t s) 
   return 0;
 }
 
+template <int EW>
+static int launch_gemm(b200exact *x, GemmParams &p, int k, const CUtensorMap &tq, int m_tiles, int splits,
+                       cudaStream_t s) {
+  const size_t smem = GemmSmem<EW>::total(gm_operand_bytes(p.kblocks, p.stages), k);
+  auto kern = x->metric == 0 ? exact_gemm_kernel<0, EW> : exact_gemm_kernel<1, EW>;
+  B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  dim3 grid((unsigned)m_tiles, (unsigned)splits);
+  kern<<<grid, GemmShape<EW>::THREADS, smem, s>>>(tq, *(CUtensorMap *)x->tmap_x, p);
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+
 int exact_candidates_tensor(b200exact *x, const float *d_queries, int64_t B, int k, int32_t *d_cand,
                             int32_t *d_cand_cnt, int cand_cap, cudaStream_t s) {
   if (k > GM_MAX_K) return B200HNSW_ERR_UNSUPPORTED;  // the slot table is sized for k <= 64: the scan handles the rest
-  int stages = GM_STAGES;
-  if (GemmSmem::total(stages, k) > x->smem_optin) stages = 3;
-  const size_t smem = GemmSmem::total(stages, k);
-  if (smem > x->smem_optin) return B200HNSW_ERR_UNSUPPORTED;
+  // widest epilogue whose slot tables leave room for at least three operand stages
+  // (measured: 16 warps win while the epilogue is the bottleneck, dim <= 256; at dim 1024 the tensor pipe is, and the
+  // looser per-thread bounds of 16 warps only add candidates: 2.6 vs 2.4 ms on 250 k x 1024)
+  const int kblocks = x->kpad / GM_K;
+  int ew = kblocks <= 4 ? 16 : 8, stages = GM_STAGES;
+  if (const char *v = getenv("B200EXACT_EPI_WARPS")) ew = atoi(v) == 8 ? 8 : 16;  // tuning experiments
+  auto total = [&](int w, int st) {
+    const int ob = gm_operand_bytes(kblocks, st);
+    return w == 16 ? GemmSmem<16>::total(ob, k) : GemmSmem<8>::total(ob, k);
+  };
+  if (ew == 16 && total(16, 3) > x->smem_optin) ew = 8;
+  if (total(ew, stages) > x->smem_optin) stages = 3;
+  if (total(ew, stages) > x->smem_optin) return B200HNSW_ERR_UNSUPPORTED;
+  const int chunks = ew == 16 ? GemmShape<16>::CHUNKS : GemmShape<8>::CHUNKS;
   const int64_t Bpad = (B + GM_M - 1) / GM_M * GM_M;
   auto al = [](size_t v) { return (v + 255) & ~(size_t)255; };
   const size_t need = al(2 * (size_t)Bpad * x->kpad) + 2 * al(4 * (size_t)Bpad) + al(4 * (size_t)Bpad * k);
@@ -613,7 +690,7 @@ int exact_candidates_tensor(b200exact *x, const float *d_queries, int64_t B, int
   p.metric = x->metric;
   p.kblocks = x->kpad / GM_K;
   p.tiles_total = (int)((x->n + GM_N - 1) / GM_N);
-  p.warm_tiles = (k + GM_N / 64 - 1) / (GM_N / 64);  // a thread fills GM_N / 64 slots per tile
+  p.warm_tiles = (k + chunks - 1) / chunks;  // a thread fills `chunks` slots per tile
   p.stages = stages;
   p.k = k;
   p.B = B;
@@ -640,12 +717,7 @@ int exact_candidates_tensor(b200exact *x, const float *d_queries, int64_t B, int
   }
   p.tiles_per_split = (p.tiles_total + splits - 1) / splits;
   splits = (p.tiles_total + p.tiles_per_split - 1) / p.tiles_per_split;
-  auto kern = x->metric == 0 ? exact_gemm_kernel<0> : exact_gemm_kernel<1>;
-  B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  dim3 grid((unsigned)m_tiles, (unsigned)splits);
-  kern<<<grid, GM_THREADS, smem, s>>>(tq, *(CUtensorMap *)x->tmap_x, p);
-  B200_CUDA(cudaGetLastError());
-  return 0;
+  return ew == 16 ? launch_gemm<16>(x, p, k, tq, m_tiles, splits, s) : launch_gemm<8>(x, p, k, tq, m_tiles, splits, s);
 }
 
 }  // namespace b200

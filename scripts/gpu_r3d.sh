@@ -1,0 +1,4 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_exact_gpu.py -m gpu -x -q 2>&1 | tail -4
+timeout 600 python scripts/exact_probe.py 1000000,128,10000,10,0 1000000,128,10000,10,1 500000,256,8192,10,0 250000,1024,4096,10,1 2>&1 | grep -v "it=0" | tail -14
