@@ -305,13 +305,16 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     const int e = warp - 2;                   // 0..EW-1 among the epilogue warps
     const int et = e * 32 + lane;             // 0..EPI-1 among the epilogue threads
     const int ch0 = (e >> 2) * CHUNKS;        // first 32-column chunk of this warp's share of the tile
-    float *my_slots = slots + (size_t)et * p.k;
-    for (int j = 0; j < p.k; j++) my_slots[j] = __int_as_float(0x7f800000);
+    const int kk = p.k;
+    const uint32_t slots_a = smem_u32(slots) + (uint32_t)(et * kk) * 4u;  // this thread's k slot minima
+    const uint32_t slots_end = slots_a + (uint32_t)kk * 4u;
+    for (int j = 0; j < kk; j++) sts_f1(slots_a + j * 4, __int_as_float(0x7f800000));
     const float margin = live_q ? p.q_margin[q] : 0.f;
     const float qf = live_q ? p.q_inv[q] : 0.f;  // turns the accumulator into -2 q.x (Euclidean) or -q.x/|q| (cosine)
     const float INF = __int_as_float(0x7f800000);
     float thr = INF;
-    int sub = 0, sl = 0;
+    int sub = 0;
+    uint32_t sl_a = slots_a;                   // slot the next block minimum goes to
     // Candidates are staged per thread (cbuf[i][et], conflict-free) and appended to the query's global list a batch at
     // a time: one atomicAdd per batch instead of one per candidate, and the whole warp flushes together so that the
     // round trip to L2 is paid once per flush, not once per lane.
@@ -329,9 +332,9 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     // deep), fetched one tile ahead, so no barrier between the epilogue warps is needed.
     constexpr int AV = COLS_W / 32;           // floats per lane and tile
     const uint32_t aux_w = s_base + (uint32_t)Sm::aux(OB, p.k) + (uint32_t)(e * 2 * COLS_W) * 4u;
-    auto tile_of = [&](int idx) { return t_begin + (idx < warm ? idx : idx - warm); };
-    auto aux_fetch = [&](int idx, float (&nx)[AV]) {
-      const float *src = p.aux + (long long)tile_of(idx) * GM_N + ch0 * 32 + lane * AV;
+    const float *aux_g = p.aux + ch0 * 32 + lane * AV;
+    auto aux_fetch = [&](int tile, float (&nx)[AV]) {
+      const float *src = aux_g + (long long)tile * GM_N;
 #pragma unroll
       for (int i = 0; i < AV; i++) nx[i] = __ldg(src + i);
     };
@@ -341,17 +344,20 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     };
     if (seq > 0) {
       float n0[AV];
-      aux_fetch(0, n0);
+      aux_fetch(t_begin, n0);
       aux_store(0, n0);
     }
     __syncwarp();
+    int tile = t_begin;
+#pragma unroll 1
     for (int idx = 0; idx < seq; idx++) {
       const int as = idx & 1;
-      const int tile = tile_of(idx);
+      const int ntile = idx + 1 == warm ? t_begin : tile + 1;  // warm-up tiles are visited twice
       const bool emit = live_q && idx >= warm;
       const uint32_t ax = aux_w + (uint32_t)(as * COLS_W) * 4u;
+      bool changed = false;
       float nx[AV];
-      if (idx + 1 < seq) aux_fetch(idx + 1, nx);
+      if (idx + 1 < seq) aux_fetch(ntile, nx);
       mbar_wait(bar_tfull + 8 * as, (idx >> 1) & 1);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + as * GM_N + ch0 * 32;
@@ -405,8 +411,12 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         }
         if (__any_sync(FULL, ccnt >= GM_CB / 2)) flush();
         // slot `sub mod k` holds the minimum over a set of rows disjoint from every other slot's set
-        my_slots[sl] = fminf(my_slots[sl], bmin);
-        if (++sl == p.k) sl = 0;
+        if (bmin < lds_f1(sl_a)) {
+          sts_f1(sl_a, bmin);
+          changed = true;
+        }
+        sl_a += 4;
+        if (sl_a == slots_end) sl_a = slots_a;
         sub++;
       }
       tc_fence_before();
@@ -415,24 +425,28 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       // next tile's terms into the other buffer (this warp's reads of it ended one tile ago)
       if (idx + 1 < seq) aux_store(as ^ 1, nx);
       __syncwarp();
-      if (sub >= p.k && live_q) {
-        // Now and then (often at first, when bounds improve fast) merge the slots with those of the other CTAs that
-        // work on this query: slot j of every CTA covers rows disjoint from slot j' of any CTA, so the element-wise
-        // minimum over CTAs is again k minima over k disjoint row sets.
+      if (sub >= kk && live_q) {
+        // Now and then (often at first, when bounds improve fast) merge the slots with those of the other threads
+        // and CTAs that work on this query: slot j of each covers rows disjoint from slot j' of any other, so the
+        // element-wise minimum is again k minima over k disjoint row sets.
         const int done = idx + 1;
-        if (sub - CHUNKS < p.k || (done & (done - 1)) == 0 || (done & 31) == 0 || idx == seq - 1) {
-          uint32_t *sg = p.slots_g + q * p.k;
-          for (int j = 0; j < p.k; j++) {
-            const uint32_t mine = ord_bits(my_slots[j]);
+        if (sub - CHUNKS < kk || (done & (done - 1)) == 0 || (done & 31) == 0 || idx == seq - 1) {
+          uint32_t *sg = p.slots_g + q * kk;
+          for (int j = 0; j < kk; j++) {
+            const uint32_t mine = ord_bits(lds_f1(slots_a + j * 4));
             const uint32_t old = atomicMin(&sg[j], mine);
-            if (old < mine) my_slots[j] = ord_float(old);
+            if (old < mine) sts_f1(slots_a + j * 4, ord_float(old));
           }
+          changed = true;
         }
-        // k distinct rows score <= max(slots): an upper bound on the k-th smallest score of the whole index
-        float tau = my_slots[0];
-        for (int j = 1; j < p.k; j++) tau = fmaxf(tau, my_slots[j]);
-        thr = fminf(thr, tau + margin);
+        if (changed) {
+          // k distinct rows score <= max(slots): an upper bound on the k-th smallest score of the whole index
+          float tau = lds_f1(slots_a);
+          for (int j = 1; j < kk; j++) tau = fmaxf(tau, lds_f1(slots_a + j * 4));
+          thr = fminf(thr, tau + margin);
+        }
       }
+      tile = ntile;
     }
     flush();
   }
