@@ -405,6 +405,14 @@ def run_ours(args, rank, local_rank, world):
         line.update(cpu_baseline_and_parity(args, g, Qh, last, last_rows, last_dists, last_counts, torch, dev, X))
     if rank == 0 and world == 1 and not args.no_exact:
         line["exact"] = exact_measurement(args, X, Qh, Qd, torch, dev, stream, not args.no_cpu_baseline)
+        # BASELINE.json words its metric "QPS @ recall@10 >= 0.95".  The reference's graph search cannot reach that on
+        # this data; of the paths the reference has, its hybrid package's exact index is the one
+        # that does, so that clause is answered by K3 on the same rows and queries, reported beside the headline.
+        ex = line["exact"]
+        line["at_recall_ge_0.95"] = {"path": "hybrid.ExactIndex.Search (K3, exact: recall@10 = 1.0 by construction, "
+                                             "results bit-identical to the oracle)",
+                                     "value": ex["value"], "unit": ex["unit"], "e2e": ex["e2e"]["value"],
+                                     "recall_at_10": 1.0}
     if rank == 0:
         emit(line)
     if world > 1:
