@@ -1,0 +1,102 @@
+"""BASELINE.json configs[2] / configs[3] at full shape on ONE GPU: wave-batched Add on the device, batched Search on the
+result, bit-exact parity of the search against the oracle on the SAME graph (read back from the device), and the
+traversal kernel's algorithmic HBM rate.  One JSON line per run on stdout.
+
+  python scripts/config_probe.py N dim M ef metric(l2|cosine) batch [steps] [parity_queries]
+"""
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+sys.path.insert(0, '.')
+import hnsw_b200  # noqa: E402
+from bench import algorithmic_bytes, draw_levels, load_peaks  # noqa: E402
+
+N, d, M, ef = (int(x) for x in sys.argv[1:5])
+metric = sys.argv[5]
+B = int(sys.argv[6])
+steps = int(sys.argv[7]) if len(sys.argv) > 7 else 20
+pq = int(sys.argv[8]) if len(sys.argv) > 8 else 2000
+k = 10
+
+import torch  # noqa: E402
+
+dev = torch.device("cuda", 0)
+rng = np.random.default_rng(42)
+if metric == "cosine":  # N(0,1) then L2-normalised
+    X = rng.standard_normal((N, d), dtype=np.float32)
+    X /= np.linalg.norm(X, axis=1, keepdims=True)
+    Qall = np.random.default_rng(43).standard_normal((4 * B, d), dtype=np.float32)
+    Qall /= np.linalg.norm(Qall, axis=1, keepdims=True)
+    dist = hnsw_b200.CosineDistance
+else:
+    X = rng.uniform(-1.0, 1.0, (N, d)).astype(np.float32)
+    Qall = np.random.default_rng(43).uniform(-1.0, 1.0, (4 * B, d)).astype(np.float32)
+    dist = hnsw_b200.EuclideanDistance
+lv = draw_levels(N, 0.25, 44)
+g = hnsw_b200.Graph(M=M, Ml=0.25, EfSearch=ef, Distance=dist, capacity=N)
+t0 = time.perf_counter()
+g.add_arrays(np.arange(N, dtype=np.int64), X, lv, wave_max=4096)
+wall = time.perf_counter() - t0
+bst = dict(g.last_stats)
+
+Qd = torch.from_numpy(Qall.reshape(4, B, d)).to(dev)
+rows = torch.empty((B, k), dtype=torch.int32, device=dev)
+dists = torch.empty((B, k), dtype=torch.float32, device=dev)
+counts = torch.empty((B,), dtype=torch.int32, device=dev)
+ctr = torch.zeros(8, dtype=torch.int64, device=dev)
+s = torch.cuda.current_stream(dev)
+
+
+def step(i):
+    g.search_device(Qd[i % 4].data_ptr(), B, k, rows.data_ptr(), dists.data_ptr(), counts.data_ptr(), ctr.data_ptr(),
+                    s.cuda_stream)
+
+
+for i in range(3):
+    step(i)
+torch.cuda.synchronize()
+ctr.zero_()
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record(s)
+for i in range(steps):
+    step(3 + i)
+e1.record(s)
+torch.cuda.synchronize()
+ms = e0.elapsed_time(e1) / steps
+c = ctr.cpu().numpy()
+last = (3 + steps - 1) % 4
+peak, src = load_peaks()
+alg = algorithmic_bytes(int(c[0]), int(c[2]), steps * B, d, k) / steps
+
+# parity on the same graph: oracle (canonical order) loads what the device built
+from oracle import binding as oracle  # noqa: E402
+
+oracle.build()
+oc = oracle.Graph(d, M, oracle.COSINE if metric == "cosine" else oracle.EUCLIDEAN, oracle.CANONICAL)
+oc.load_flat(*g.dump_flat())
+o_rows, o_d, o_cnt, _ = oc.batch_search(Qall.reshape(4, B, d)[last][:pq], k, ef, n_threads=os.cpu_count())
+r, dd, cc = rows.cpu().numpy()[:pq], dists.cpu().numpy()[:pq], counts.cpu().numpy()[:pq]
+t1 = time.perf_counter()
+oracle_s = oracle.Graph(d, M, oracle.COSINE if metric == "cosine" else oracle.EUCLIDEAN, oracle.SIMD)
+oracle_s.load_flat(*g.dump_flat())
+t1 = time.perf_counter()
+oracle_s.batch_search(Qall.reshape(4, B, d)[0][:pq], k, ef, n_threads=os.cpu_count())
+cpu_qps = pq / (time.perf_counter() - t1)
+print(json.dumps({
+    "workload": f"{N}x{d} {metric} M={M} ef={ef} batch={B} k={k}",
+    "build": {"wall_s": wall, "kernel_s": bst["kernel_ms"] / 1e3, "vec_per_s_kernel": N / (bst["kernel_ms"] / 1e3),
+              "vec_per_s_wall": N / wall, "launches": bst["launches"],
+              "evals_per_insert": (bst["dist_evals"] + bst["evict_evals"] + bst["replenish_evals"]) / N,
+              "semantics": "wave-batched Add (waves <= 4096)"},
+    "topography": g.Topography(),
+    "search": {"ms_per_step": ms, "qps": B / ms * 1e3, "E_per_query": float(c[0]) / (steps * B),
+               "H_per_query": float(c[1]) / (steps * B), "algorithmic_GBps": alg / ms / 1e6, "peak_GBps": peak,
+               "frac": alg / ms / 1e6 / peak, "peak_source": src},
+    "parity": {"checked_queries": pq, "rows_equal": bool(np.array_equal(o_rows, r)),
+               "dists_bit_equal": bool(np.array_equal(o_d.view(np.uint32), dd.view(np.uint32))),
+               "counts_equal": bool(np.array_equal(o_cnt, cc))},
+    "cpu_port_qps_all_cores": cpu_qps, "cores": os.cpu_count()}))
