@@ -52,7 +52,10 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-exact", action="store_true", help="skip the ExactIndex (K3) side measurement")
     ap.add_argument("--exact-steps", type=int, default=10)
-    ap.add_argument("--e2e-callers", type=int, default=2,
+    ap.add_argument("--inflight", type=int, default=2,
+                    help="batches in flight in the device-resident measurement (traversal streams taking the steps in "
+                         "turn); 1 = strictly one launch after the other")
+    ap.add_argument("--e2e-callers", type=int, default=4,
                     help="host threads making the synchronous host-pointer call concurrently in the e2e measurement "
                          "(the reference admits concurrent BatchSearch callers under its RWMutex read lock)")
     return ap.parse_args()
@@ -224,6 +227,9 @@ def workload_config(args, world):
             f"{world} independent sub-graphs (one per GPU), queries broadcast; rank r merges queries [r*B/{world}, "
             f"(r+1)*B/{world}): one NCCL all-to-all of the per-shard result blocks + K4 top-k merge, pipelined on a side "
             f"stream under the traversal of the next step (all inside the timed region)",
+            "batches_in_flight": max(1, args.inflight),
+            "pipelining": f"steps are issued in turn on {max(1, args.inflight)} traversal stream(s): each step is one K1 "
+                          f"launch over one {args.batch}-query batch, at most {max(1, args.inflight)} of them in flight",
             "l2_policy": f"inputs larger than L2: {args.n * (args.dim * 4 + args.m * 4) / 1e6:.0f} MB of graph per GPU "
                          f"gathered at random; a pool of {args.pool} distinct query batches cycled through the steps"}
 
@@ -272,23 +278,38 @@ def run_ours(args, rank, local_rank, world):
     nb = max(1, min(args.warmup + args.steps, args.pool))
     Qh = torch.from_numpy(synth_rows(nb * B, dim, 43).reshape(nb, B, dim)).pin_memory()
     Qd = Qh.to(dev)
-    rows = torch.empty((B, k), dtype=torch.int32, device=dev)
-    dists = torch.empty((B, k), dtype=torch.float32, device=dev)
-    counts = torch.empty((B,), dtype=torch.int32, device=dev)
     counters = torch.zeros(8, dtype=torch.int64, device=dev)
     stream = torch.cuda.current_stream(dev)
+    # `depth` batches in flight: a 10k-query launch lasts as long as its slowest traversal and leaves SMs idle towards
+    # its end; the next batch's launch, on a second stream, fills them.  Every step is still one launch over one batch.
+    depth = max(1, args.inflight)
+    tstreams = [torch.cuda.Stream(dev) for _ in range(depth)]
+    outs_d = [(torch.empty((B, k), dtype=torch.int32, device=dev), torch.empty((B, k), dtype=torch.float32, device=dev),
+               torch.empty((B,), dtype=torch.int32, device=dev)) for _ in range(depth)]
 
-    def search_step(qd):
-        g.search_device(qd.data_ptr(), B, k, rows.data_ptr(), dists.data_ptr(), counts.data_ptr(),
-                        counters.data_ptr(), stream.cuda_stream)
+    def search_step(i, qd, t0=None, t1=None):
+        """step i on traversal stream i % depth (N = 1): b200hnsw_search_batch_device, one K1 launch"""
+        ts = tstreams[i % depth]
+        r, d_, c = outs_d[i % depth]
+        ts.wait_stream(stream)
+        if t0 is not None:
+            t0.record(ts)
+        g.search_device(qd.data_ptr(), B, k, r.data_ptr(), d_.data_ptr(), c.data_ptr(), counters.data_ptr(),
+                        ts.cuda_stream)
+        if t1 is not None:
+            t1.record(ts)
+
+    def join():
+        for ts in tstreams:
+            stream.wait_stream(ts)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    # N > 1: traversal of step i+1 overlaps the all-gather + merge of step i (two result buffers, side stream)
-    pipe = sharded.ShardPipeline(g, dist, B, k, n, dev) if world > 1 else None
+    # N > 1: the all-to-all + merge of a batch run on a side stream under the traversals of the batches behind it
+    pipe = sharded.ShardPipeline(g, dist, B, k, n, dev, depth=depth) if world > 1 else None
 
     sampler = ClockSampler(local_rank)
     sampler.start()
@@ -298,9 +319,11 @@ def run_ours(args, rank, local_rank, world):
         if world > 1:
             pipe.search(Qd[i % nb].data_ptr(), counters.data_ptr())
         else:
-            search_step(Qd[i % nb])
+            search_step(i, Qd[i % nb])
     if world > 1:
         pipe.drain()
+    else:
+        join()
     barrier()
     counters.zero_()
     ka = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
@@ -309,14 +332,14 @@ def run_ours(args, rank, local_rank, world):
     barrier()
     ev0.record(stream)
     for i in range(args.steps):
-        ka[i].record(stream)
         if world > 1:
-            last_slot = pipe.search(Qd[(args.warmup + i) % nb].data_ptr(), counters.data_ptr())
+            pipe.search(Qd[(args.warmup + i) % nb].data_ptr(), counters.data_ptr(), timing=(ka[i], kb[i]))
         else:
-            search_step(Qd[(args.warmup + i) % nb])
-        kb[i].record(stream)
+            search_step(i, Qd[(args.warmup + i) % nb], ka[i], kb[i])
     if world > 1:
         pipe.drain()  # the timed region ends when the last merge has finished
+    else:
+        join()
     ev1.record(stream)
     barrier()
     total_ms = ev0.elapsed_time(ev1)
@@ -325,43 +348,80 @@ def run_ours(args, rank, local_rank, world):
     if int(ctr[4]) != 0:
         raise SystemExit("bench.py: a traversal overflowed the visited set in the device-pointer path")
     last = (args.warmup + args.steps - 1) % nb
-    last_rows, last_dists, last_counts = rows.cpu().numpy(), dists.cpu().numpy(), counts.cpu().numpy()
+    lo = outs_d[(args.steps - 1) % depth]
+    last_rows, last_dists, last_counts = lo[0].cpu().numpy(), lo[1].cpu().numpy(), lo[2].cpu().numpy()
     t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     total_ms = float(t.item())
+    # the same launch alone on the device (nothing else in flight): the per-kernel figure earlier rounds reported
+    solo_ms = None
+    if world == 1:
+        sa = [torch.cuda.Event(enable_timing=True) for _ in range(8)]
+        sb = [torch.cuda.Event(enable_timing=True) for _ in range(8)]
+        r, d_, c = outs_d[0]
+        for i in range(8):
+            sa[i].record(stream)
+            g.search_device(Qd[i % nb].data_ptr(), B, k, r.data_ptr(), d_.data_ptr(), c.data_ptr(), 0,
+                            stream.cuda_stream)
+            sb[i].record(stream)
+        torch.cuda.synchronize(dev)
+        solo_ms = float(np.mean([x.elapsed_time(y) for x, y in zip(sa, sb)][2:]))
 
     # ---- end to end: host buffers in, host buffers out, every step ---------------------------------------------------
     h_rows = torch.empty((B, k), dtype=torch.int32).pin_memory()
     h_dists = torch.empty((B, k), dtype=torch.float32).pin_memory()
     h_counts = torch.empty((B,), dtype=torch.int32).pin_memory()
-    seg = pipe.buf[0].seg if pipe else B
-    h_mi = torch.empty((seg, k), dtype=torch.int64).pin_memory()
-    h_md = torch.empty((seg, k), dtype=torch.float32).pin_memory()
-    h_mc = torch.empty((seg,), dtype=torch.int32).pin_memory()
-    qtmp = torch.empty((B, dim), dtype=torch.float32, device=dev)
-
-    def e2e_step(i):
-        if world == 1:  # the drop-in call itself: b200hnsw_search_batch(host pointers)
+    if world == 1:
+        def e2e_step(i):  # the drop-in call itself: b200hnsw_search_batch(host pointers), one caller, one call at a time
             g.search_host_ptrs(Qh[i].data_ptr(), B, k, h_rows.data_ptr(), h_dists.data_ptr(), h_counts.data_ptr())
-        else:
-            # every rank receives the whole batch, searches its shard, and returns the merged lists of its share of the
-            # queries (B / world of them) to the host
-            qtmp.copy_(Qh[i], non_blocking=True)
-            slot = pipe.search(qtmp.data_ptr())
-            pipe.drain()
-            md, mi, mc = pipe.merged(slot)
-            h_mi.copy_(mi, non_blocking=True)
-            h_md.copy_(md, non_blocking=True)
-            h_mc.copy_(mc, non_blocking=True)
-            torch.cuda.synchronize(dev)
+
+        def e2e_finish():
+            pass
+    else:
+        # every rank receives the whole batch from ITS host (H2D in front of the traversal, on the traversal's stream),
+        # searches its shard, and returns the merged lists of its share of the queries (B / world of them) to page-
+        # locked host memory behind the merge (side stream).  The host takes a slot's results (waits for that copy)
+        # before it queues the slot again, nbuf steps later: the serving loop a caller of ShardPipeline runs.
+        seg = pipe.buf[0].seg
+        nbuf = pipe.nbuf
+        qtmp = [torch.empty((B, dim), dtype=torch.float32, device=dev) for _ in range(nbuf)]
+        h_m = [(torch.empty((seg, k), dtype=torch.int64).pin_memory(), torch.empty((seg, k), dtype=torch.float32).pin_memory(),
+                torch.empty((seg,), dtype=torch.int32).pin_memory()) for _ in range(nbuf)]
+        back = [torch.cuda.Event() for _ in range(nbuf)]
+        queued = [False] * nbuf
+
+        def e2e_step(i):
+            slot = pipe.step % nbuf
+            if queued[slot]:
+                back[slot].synchronize()  # the host has this slot's previous results
+
+            def before(st_, sl_):
+                qtmp[sl_].copy_(Qh[i], non_blocking=True)
+
+            def after(st_, sl_):
+                md, mi, mc = pipe.merged(sl_)
+                h_m[sl_][0].copy_(mi, non_blocking=True)
+                h_m[sl_][1].copy_(md, non_blocking=True)
+                h_m[sl_][2].copy_(mc, non_blocking=True)
+                back[sl_].record(st_)
+
+            pipe.search(qtmp[slot].data_ptr(), before=before, after=after)
+            queued[slot] = True
+
+        def e2e_finish():
+            for sl_ in range(nbuf):
+                if queued[sl_]:
+                    back[sl_].synchronize()
 
     for i in range(max(args.warmup, 3)):
         e2e_step(i % nb)
+    e2e_finish()
     barrier()
     t0 = time.perf_counter()
     for i in range(args.steps):
         e2e_step((args.warmup + i) % nb)
+    e2e_finish()
     torch.cuda.synchronize(dev)
     e2e_s = time.perf_counter() - t0
     e2e_single_s = e2e_s
@@ -419,17 +479,28 @@ def run_ours(args, rank, local_rank, world):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args, world),
         "e2e": {"value": e2e_value, "unit": "queries/s", "h2d_bytes_per_step": B * dim * 4,
-                "d2h_bytes_per_step": B * k * 8 + B * 4 + 40 if world == 1 else seg * (k * 12 + 4),
+                "d2h_bytes_per_step": B * k * 8 + B * 4 + 40 if world == 1 else pipe.buf[0].seg * (k * 12 + 4),
                 "callers": callers, "single_caller_value": units / e2e_single_s,
-                "call": "b200hnsw_search_batch (host pointers, synchronous)" if world == 1 else
-                        "ShardPipeline.search + merged() per rank"},
+                "call": (f"b200hnsw_search_batch (host pointers, synchronous) from {callers} host threads; "
+                         "single_caller_value = one thread, one call at a time") if world == 1 else
+                        (f"ShardPipeline.search per rank with the H2D copy of the batch in front of the traversal and "
+                         f"the D2H copy of the merged lists behind the merge, {pipe.nbuf} batches in flight")},
         "gpu_launches": args.steps * (1 if world == 1 else 2),  # K1 (+ K4 merge); the all-gather is NCCL's
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": (traffic or {}).get("dram_bytes_per_launch"),
                      "kernel": "b200::traverse_kernel (K1, traverse.cuh)", "kernel_ms": kern_avg_ms,
                      "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src,
                      "dist_evals_per_query": float(ctr[0]) / (args.steps * B),
-                     "expansions_per_query": float(ctr[1]) / (args.steps * B)},
+                     "expansions_per_query": float(ctr[1]) / (args.steps * B),
+                     # `achieved` follows the contract (bytes of one launch / that launch's event time on its own
+                     # stream); with `launches_in_flight` kernels sharing the SMs a launch lasts longer than alone.
+                     # aggregate = all launches' bytes / the timed region (it can pass the DRAM copy peak: `traffic`
+                     # shows that most of the algorithmic bytes are served by L2); solo = the launch alone.
+                     "launches_in_flight": depth,
+                     "aggregate_achieved": alg_bytes * args.steps / (total_ms / 1e3) / 1e9,
+                     "solo_kernel_ms": solo_ms,
+                     "solo_achieved": (alg_bytes / (solo_ms / 1e3) / 1e9) if solo_ms else None,
+                     "solo_frac": (alg_bytes / (solo_ms / 1e3) / 1e9 / peak) if solo_ms else None},
         "clocks": clocks,
         "build": {"vec_per_s": n * world / build_wall, "kernel_vec_per_s": n / build_kernel_s, "wall_s": build_wall,
                   "semantics": (f"wave-batched Add, waves of <= {args.wave_max} nodes (b200hnsw_add_batch_waves; "

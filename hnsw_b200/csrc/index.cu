@@ -558,13 +558,16 @@ int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_
   }
   // The batch is cut in chunks that run on their own streams: the H2D copy of chunk i+1 and the D2H copy of chunk
   // i-1 overlap the traversal kernel of chunk i, and the kernels of different chunks share the SMs.
-  int nchunk = B >= 4096 ? 4 : (B >= 1024 ? 2 : 1);
+  int nchunk = B >= 1024 ? 2 : 1;  // measured (profiles/r3h_e2e_callers.log): 2 beats 4 alone and with callers in flight
   if (const char *v = getenv("B200HNSW_E2E_CHUNKS")) {
     int t = atoi(v);
     if (t >= 1 && t <= CallCtx::MAX_SUB) nchunk = t;
   }
-  if ((rc = c->ensure_sub(nchunk))) return fail(rc);
-  unsigned long long ctr[5] = {0, 0, 0, 0, 0};
+  if ((rc = c->ensure_sub(nchunk)) || (rc = c->reserve_pinned(64))) return fail(rc);
+  // counters come back into page-locked memory: a copy into pageable memory would go through the driver's staging
+  // path, which serialises against the other calls in flight
+  volatile unsigned long long *ctr = (volatile unsigned long long *)c->h_pinned;
+  for (int i = 0; i < 5; i++) ctr[i] = 0;
   int launches = 0;
   bool staged = false;
   if (nchunk == 1) {  // one chunk: copy first, so that kernel_ms (ev0..ev1) is the traversal kernel alone
@@ -604,7 +607,7 @@ int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_
     }
     staged = true;
     if ((e = cudaEventRecord(c->ev1, s)) != cudaSuccess ||
-        (e = cudaMemcpyAsync(ctr, d_ctr, 40, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
+        (e = cudaMemcpyAsync((void *)ctr, d_ctr, 40, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
         (e = cudaStreamSynchronize(s)) != cudaSuccess)
       return fail(cuda_fail(e, "search kernel"));
     if ((int)(ctr[4] & 0xffffffffu) == 0) break;

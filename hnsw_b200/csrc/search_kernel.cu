@@ -2,6 +2,7 @@
 // and for the search half of the batched Add (wave_insert.cu).  Bound: HBM gather (E rows of 4*dim bytes per
 // traversal; E is counted per launch in d_counters).
 #include <cstdlib>
+#include <mutex>
 
 #include "index.hpp"
 #include "traverse.cuh"
@@ -18,7 +19,18 @@ static int launch_t(b200hnsw *h, const GraphView &g, TraverseParams &p, cudaStre
               smem, h->smem_optin);
     return B200HNSW_ERR_UNSUPPORTED;
   }
-  B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  {
+    // the opt-in limit of a kernel is per device and shared by every call in flight: it is only ever raised, under a
+    // lock, so a concurrent call that needs less can never lower it between another call's test and its launch
+    static std::mutex mu;
+    static size_t raised[64] = {};
+    const int dv = h->cfg.device & 63;
+    std::lock_guard<std::mutex> lk(mu);
+    if (smem > raised[dv]) {
+      B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      raised[dv] = smem;
+    }
+  }
   int per_sm = 0;
   B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, TRAV_WARPS * 32, smem));
   if (per_sm < 1) per_sm = 1;

@@ -6,6 +6,7 @@ the shard's list -- the stable concatenate-then-sort of hnsw-extensions/hybrid/a
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -142,39 +143,60 @@ class SegmentedResults:
 
 
 class ShardPipeline:
-    """Sharded batched search as a two-stage pipeline: the traversal of batch i+1 (main stream) runs while the
-    all-to-all + K4 merge of batch i run on a side stream, over two SegmentedResults buffers.  `search` launches one
-    batch and returns at once; `merged(slot)` are the tensors the merge of that slot writes for THIS rank's share of
-    the queries (valid after `drain`, or after `done[slot]` has been waited on)."""
+    """Sharded batched search as a pipeline.  `depth` traversal streams take the batches in turn (two traversal kernels
+    in flight fill the SMs that one kernel's tail leaves idle: a 10k-query launch lasts as long as its slowest
+    traversal), and the all-to-all + K4 merge of every batch run on ONE side stream (so the collectives are issued in
+    the same order on every rank) under the traversals of the batches behind it.  2 * depth SegmentedResults buffers.
+    `search` queues one batch and returns at once; `merged(slot)` are the tensors the merge of that slot writes for
+    THIS rank's share of the queries (valid after `drain`, or after `done[slot]` has been waited on)."""
 
-    def __init__(self, graph, dist, B: int, k: int, rows_per_shard: int, device):
+    def __init__(self, graph, dist, B: int, k: int, rows_per_shard: int, device, depth: int = 2):
         import torch
         self.g, self.dist, self.B, self.k, self.n = graph, dist, B, k, rows_per_shard
         self.world = dist.get_world_size() if dist is not None else 1
         self.rank = dist.get_rank() if dist is not None else 0
+        self.depth = max(1, int(depth))
+        self.nbuf = 2 * self.depth
         self.main = torch.cuda.current_stream(device)
-        self.side = torch.cuda.Stream(device)
-        self.buf = [SegmentedResults(B, k, self.world, self.rank, device) for _ in range(2)]
-        self.searched = [torch.cuda.Event() for _ in range(2)]
-        self.done = [torch.cuda.Event() for _ in range(2)]
-        self.used = [False, False]
+        self.trav = [torch.cuda.Stream(device) for _ in range(self.depth)]
+        # the exchange and the merge are short and on the critical path of slot reuse: their blocks go in front of the
+        # traversal blocks that are waiting for an SM
+        self.side = torch.cuda.Stream(device, priority=int(os.environ.get('B200HNSW_SIDE_PRIORITY', '-1')))
+        self.buf = [SegmentedResults(B, k, self.world, self.rank, device) for _ in range(self.nbuf)]
+        self.searched = [torch.cuda.Event() for _ in range(self.nbuf)]
+        self.done = [torch.cuda.Event() for _ in range(self.nbuf)]
+        self.used = [False] * self.nbuf
         self.step = 0
 
-    def search(self, d_queries: int, d_counters: int = 0) -> int:
-        """Queue one batch (device pointer to [B, dim] f32); returns the slot its results will land in."""
+    def search(self, d_queries: int, d_counters: int = 0, timing=None, before=None, after=None) -> int:
+        """Queue one batch (device pointer to [B, dim] f32); returns the slot its results will land in.
+        timing = (start, end) CUDA events recorded around the traversal kernel on the stream it runs on;
+        before(stream, slot) / after(stream, slot) queue the caller's own work in front of the traversal (e.g. the H2D
+        copy of the queries) and behind the merge (e.g. the D2H copy of the merged lists)."""
         import torch
-        slot = self.step & 1
+        slot = self.step % self.nbuf
+        t = self.trav[self.step % self.depth]
         self.step += 1
         b = self.buf[slot]
+        t.wait_stream(self.main)  # ordered behind whatever the caller queued on its stream (inputs, timing events)
         if self.used[slot]:
-            self.main.wait_event(self.done[slot])  # the exchange that last read this slot's send buffer has finished
+            t.wait_event(self.done[slot])  # the exchange + merge that last used this slot's buffers have finished
+        if before is not None:
+            with torch.cuda.stream(t):
+                before(t, slot)
+        if timing is not None:
+            timing[0].record(t)
         self.g.search_segmented_device(d_queries, self.B, self.k, b.send.data_ptr(), b.seg, b.stride, d_counters,
-                                       self.main.cuda_stream)
-        self.searched[slot].record(self.main)
+                                       t.cuda_stream)
+        if timing is not None:
+            timing[1].record(t)
+        self.searched[slot].record(t)
         self.side.wait_event(self.searched[slot])
         with torch.cuda.stream(self.side):
             b.exchange(self.dist)
             b.merge(self.n, self.side.cuda_stream)
+            if after is not None:
+                after(self.side, slot)
         self.done[slot].record(self.side)
         self.used[slot] = True
         return slot
@@ -185,6 +207,6 @@ class ShardPipeline:
 
     def drain(self):
         """Main stream waits for every queued merge."""
-        for slot in range(2):
+        for slot in range(self.nbuf):
             if self.used[slot]:
                 self.main.wait_event(self.done[slot])

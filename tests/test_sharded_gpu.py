@@ -44,6 +44,29 @@ def _worker(rank, world, port, tmp):
         out[f"dd{step}"] = d_.cpu().numpy().reshape(-1, k)[:B]
         out[f"cnt{step}"] = c_.cpu().numpy().reshape(-1)[:B]
         out["q0"], out["q1"] = b.q0, b.q1
+    # six batches queued back to back (no drain in between): both traversal streams busy, every slot reused, the merged
+    # lists of each batch copied out behind its merge on the side stream
+    nq = 6
+    Qs = [np.random.default_rng(70 + s_).uniform(-1, 1, (B, d)).astype(np.float32) for s_ in range(nq)]
+    qds = [torch.from_numpy(Q).to(dev) for Q in Qs]
+    seg = pipe.buf[0].seg
+    keep_d = torch.empty((nq, seg, k), dtype=torch.float32, device=dev)
+    keep_i = torch.empty((nq, seg, k), dtype=torch.int64, device=dev)
+    keep_c = torch.empty((nq, seg), dtype=torch.int32, device=dev)
+    torch.cuda.synchronize(dev)
+    for s_ in range(nq):
+        def after(stream, slot, s_=s_):
+            md, mi, mc = pipe.merged(slot)
+            keep_d[s_].copy_(md, non_blocking=True)
+            keep_i[s_].copy_(mi, non_blocking=True)
+            keep_c[s_].copy_(mc, non_blocking=True)
+        pipe.search(qds[s_].data_ptr(), after=after)
+    pipe.drain()
+    torch.cuda.synchronize(dev)
+    out["pd"], out["pi"], out["pc"] = keep_d.cpu().numpy(), keep_i.cpu().numpy(), keep_c.cpu().numpy()
+    for s_ in range(nq):  # this shard's own lists for all queries, through the plain host call
+        r_, d_, c_ = g.search_rows(Qs[s_], k, ef)
+        out[f"prows{s_}"], out[f"pdd{s_}"], out[f"pcnt{s_}"] = r_, d_, c_
     np.savez(os.path.join(tmp, f"rank{rank}.npz"), **out)
     dist.barrier()
     dist.destroy_process_group()
@@ -73,6 +96,17 @@ def test_two_gpu_pipeline_matches_merge_spec(tmp_path):
             assert np.array_equal(r[i][f"i{step}"][:q1 - q0], m[1][q0:q1])
             assert np.array_equal(r[i][f"c{step}"][:q1 - q0], m[2][q0:q1])
         assert (m[1] >= 3000).any() and (m[1][m[1] >= 0] < 3000).any()
+    for step in range(6):  # the back-to-back phase
+        all_d = np.stack([r[i][f"pdd{step}"] for i in range(world)])
+        all_i = np.stack([np.where(r[i][f"prows{step}"] >= 0, r[i][f"prows{step}"].astype(np.int64) + i * 3000, -1)
+                          for i in range(world)])
+        all_c = np.stack([r[i][f"pcnt{step}"] for i in range(world)])
+        m = merge_topk_ref(all_d, all_i, all_c, 10)
+        for i in range(world):
+            q0, q1 = int(r[i]["q0"]), int(r[i]["q1"])
+            assert np.array_equal(r[i]["pd"][step][:q1 - q0], m[0][q0:q1], equal_nan=True)
+            assert np.array_equal(r[i]["pi"][step][:q1 - q0], m[1][q0:q1])
+            assert np.array_equal(r[i]["pc"][step][:q1 - q0], m[2][q0:q1])
 
 
 def _exact_worker(rank, world, port, tmp):
