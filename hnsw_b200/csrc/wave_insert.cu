@@ -796,9 +796,32 @@ extern "C" int b200hnsw_add_batch_waves(b200hnsw_t *h, const float *vectors, con
   int *d_err = (int *)(ctl + 64);
   int *d_wave_ctr = (int *)(ctl + 128);
   cudaError_t e;
-  if ((e = cudaMemcpy2DAsync(h->d.vec + (size_t)h->n * rf, sizeof(float) * rf, vectors, sizeof(float) * dim,
-                             sizeof(float) * dim, (size_t)n, cudaMemcpyHostToDevice, s)) != cudaSuccess ||
-      (e = cudaMemcpyAsync(h->d.keys + h->n, keys, sizeof(int64_t) * (size_t)n, cudaMemcpyHostToDevice, s)) !=
+  // The vectors go up in chunks on a copy stream, one chunk ahead of the waves that need them: the host stages chunk
+  // j+1 (pageable memory goes through the driver's bounce buffers) while the device runs the waves of chunk j.  Chunks
+  // start small, because the first waves are (a wave never exceeds 1/16 of the rows already present).
+  if ((rc = c->ensure_sub(2))) return fail(rc);
+  cudaStream_t cs = c->sub[0];
+  std::vector<int64_t> cut{0};
+  {
+    const int64_t big = std::max<int64_t>(4096, ((int64_t)32 << 20) / ((int64_t)sizeof(float) * dim));
+    int64_t len = std::min<int64_t>(big, 8192);
+    while (cut.back() < n) {
+      cut.push_back(std::min<int64_t>(n, cut.back() + len));
+      len = std::min<int64_t>(big, len * 2);
+    }
+  }
+  const int n_chunks = (int)cut.size() - 1;
+  auto upload = [&](int j) -> cudaError_t {
+    cudaError_t r = cudaMemcpy2DAsync(h->d.vec + (size_t)(h->n + cut[j]) * rf, sizeof(float) * rf,
+                                      vectors + (size_t)cut[j] * dim, sizeof(float) * dim, sizeof(float) * dim,
+                                      (size_t)(cut[j + 1] - cut[j]), cudaMemcpyHostToDevice, cs);
+    return r != cudaSuccess ? r : cudaEventRecord(c->sub_ev[j & 1], cs);
+  };
+  // the slab may have just been grown on s (ensure_capacity): the copy stream starts behind that
+  if ((e = cudaEventRecord(c->ev0, s)) != cudaSuccess || (e = cudaStreamWaitEvent(cs, c->ev0, 0)) != cudaSuccess ||
+      (e = upload(0)) != cudaSuccess)
+    return fail(cuda_fail(e, "add_waves staging"));
+  if ((e = cudaMemcpyAsync(h->d.keys + h->n, keys, sizeof(int64_t) * (size_t)n, cudaMemcpyHostToDevice, s)) !=
           cudaSuccess ||
       (e = cudaMemcpyAsync(h->d.upper_off + h->n, upper_off.data(), sizeof(int32_t) * (size_t)n,
                            cudaMemcpyHostToDevice, s)) != cudaSuccess ||
@@ -828,7 +851,13 @@ extern "C" int b200hnsw_add_batch_waves(b200hnsw_t *h, const float *vectors, con
   p.rep_cap = pow2_ge(2 * (M * M + M + 2));
   int launches = 0, kernel_waves = 0;
   const int n_layers_before = h->n_layers;
-  for (const Wave &wv : waves) {
+  size_t wi = 0;
+  for (int j = 0; j < n_chunks; j++) {
+   if (j + 1 < n_chunks && (e = upload(j + 1)) != cudaSuccess) return fail(cuda_fail(e, "add_waves staging"));
+   if ((e = cudaStreamWaitEvent(s, c->sub_ev[j & 1], 0)) != cudaSuccess)  // rows below cut[j + 1] are in HBM
+     return fail(cuda_fail(e, "add_waves staging"));
+   for (; wi < waves.size() && waves[wi].start + waves[wi].w <= cut[j + 1]; wi++) {
+    const Wave &wv = waves[wi];
     if (!wv.kernels) continue;
     // phase S: K1 with the Add sink; it must see exactly the layers that exist before the wave
     h->n_layers = wv.n_layers;
@@ -864,6 +893,7 @@ extern "C" int b200hnsw_add_batch_waves(b200hnsw_t *h, const float *vectors, con
     if ((rc = launch_commit_any(h, p, s))) return fail(rc);
     launches += 8;
     kernel_waves++;
+   }
   }
   unsigned long long ctr[8];
   int err = 0, wave_ctr[4] = {0, 0, 0, 0};

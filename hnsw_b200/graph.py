@@ -11,6 +11,7 @@ from __future__ import annotations
 
 import ctypes as C
 import math
+import threading
 import time
 from dataclasses import dataclass
 from typing import Iterable, List, Optional, Sequence
@@ -211,7 +212,12 @@ class Graph:
         st = _lib.Stats()
         L = _lib.lib()
         rows0 = int(L.b200hnsw_rows(self._h))
+        n0 = len(self._keys)
         t0 = time.perf_counter()
+        # the host mirror (keys, key -> row, vectors: what Search hands back as Node.Value) is filled while the device
+        # call runs; the call does not hold the interpreter lock
+        mirror = threading.Thread(target=lambda: self._store_host(K.tolist(), V))
+        mirror.start()
         try:
             if wave_max and wave_max > 0:  # batched construction in waves (not the reference's sequential order)
                 _lib.check(L.b200hnsw_add_batch_waves(
@@ -221,14 +227,16 @@ class Graph:
                 _lib.check(L.b200hnsw_add_batch(self._h, V.ctypes.data_as(_lib.f32p), K.ctypes.data_as(_lib.i64p),
                                                 lv.ctypes.data_as(_lib.i32p), len(K), self.M, self.EfSearch, metric,
                                                 C.byref(st)))
-        except _lib.B200Error:
+        except BaseException:
+            mirror.join()
             done = int(L.b200hnsw_rows(self._h)) - rows0  # nodes in front of the failing one are in
-            if done > 0:
-                self._store_host(K[:done].tolist(), V[:done])
+            for key in self._keys[n0 + done:]:
+                del self._row_of[key]
+            del self._keys[n0 + done:]
             raise
         self.last_stats = st.as_dict()
         self.last_stats["call_s"] = time.perf_counter() - t0  # wall time of the C call (staging + kernels)
-        self._store_host(K.tolist(), V)
+        mirror.join()
 
     def add_arrays(self, keys, vectors, levels: Optional[Sequence[int]] = None, wave_max: int = 0):
         """BatchAdd for array inputs (keys[n] int64, vectors[n, dim] float32): same semantics, no per-node objects.
