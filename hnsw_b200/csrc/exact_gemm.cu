@@ -188,6 +188,13 @@ __device__ __forceinline__ float gm_score(float acc, float a, float qf) {
   return METRIC == 0 ? fmaf(qf, acc, a) : fmaf(acc * a, qf, 1.f);
 }
 
+// min.f32 with three inputs (sm_100: one FMNMX3); a NaN input is dropped unless all are NaN, as with fminf
+__device__ __forceinline__ float fmin3(float a, float b, float c) {
+  float r;
+  asm("min.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+  return r;
+}
+
 template <int METRIC, int EW>
 __global__ void __launch_bounds__(GemmShape<EW>::THREADS, 1)
 exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x,
@@ -369,18 +376,18 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         tmem_ld_wait(v);  // chunk cl has landed; chunk cl+1 is requested before cl is looked at
         if (cl + 1 < CHUNKS) tmem_ld32(taddr + (cl + 1) * 32, (cl & 1) == 0 ? vb : va);
         const uint32_t axc = ax + (uint32_t)(cl * 32) * 4u;
-        float m8[8];
+        float m8[8], r8[8];
 #pragma unroll
         for (int j4 = 0; j4 < 8; j4++) {  // 32 independent scores: no branch, no dependent chain
           const float4 a = lds_f4(axc + j4 * 16);
           const float s0 = gm_score<METRIC>(__uint_as_float(v[4 * j4 + 0]), a.x, qf);
           const float s1 = gm_score<METRIC>(__uint_as_float(v[4 * j4 + 1]), a.y, qf);
           const float s2 = gm_score<METRIC>(__uint_as_float(v[4 * j4 + 2]), a.z, qf);
-          const float s3 = gm_score<METRIC>(__uint_as_float(v[4 * j4 + 3]), a.w, qf);
-          m8[j4] = fminf(fminf(s0, s1), fminf(s2, s3));  // fminf drops NaN (dead rows)
-        }
-        const float bmin = fminf(fminf(fminf(m8[0], m8[1]), fminf(m8[2], m8[3])),
-                                 fminf(fminf(m8[4], m8[5]), fminf(m8[6], m8[7])));
+          r8[j4] = gm_score<METRIC>(__uint_as_float(v[4 * j4 + 3]), a.w, qf);
+          m8[j4] = fmin3(s0, s1, s2);  // three-input minimum (FMNMX3): 16 instructions per 32 scores instead of 31;
+        }                              // like fminf it drops NaN (dead rows)
+        const float bmin = fmin3(fmin3(fmin3(m8[0], m8[1], m8[2]), fmin3(m8[3], m8[4], m8[5]), fmin3(m8[6], m8[7], r8[0])),
+                                 fmin3(r8[1], r8[2], r8[3]), fmin3(fmin3(r8[4], r8[5], r8[6]), r8[7], r8[7]));
         if (emit && bmin <= thr) {  // some row of this block passes the filter: score the block again, row by row
           unsigned pass = 0;
 #pragma unroll

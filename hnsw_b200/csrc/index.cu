@@ -1,4 +1,5 @@
 // index.cu -- C ABI (include/b200hnsw.h): lifetime, device-resident layout, load / read-back, search entry points.
+#include <chrono>
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
@@ -519,8 +520,13 @@ int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_
     return 0;
   }
   B200_CUDA(cudaSetDevice(h->cfg.device));
+  static const bool trace_slow = getenv("B200HNSW_TRACE_SLOW") != nullptr;  // diagnostics: report calls over 5 ms
+  const auto w0 = std::chrono::steady_clock::now();
+  auto since = [&]() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - w0).count(); };
+  double w_acq = 0, w_queued = 0;
   CallCtx *c = h->acquire();
   if (!c) return B200HNSW_ERR_CUDA;
+  w_acq = since();
   const int dim = h->cfg.dim;
   size_t qb = sizeof(float) * (size_t)B * dim, rb = sizeof(int32_t) * (size_t)B * k, db = sizeof(float) * (size_t)B * k,
          cb = sizeof(int32_t) * (size_t)B;
@@ -606,6 +612,7 @@ int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_
         return fail(cuda_fail(e, "search chunk join"));
     }
     staged = true;
+    w_queued = since();
     if ((e = cudaEventRecord(c->ev1, s)) != cudaSuccess ||
         (e = cudaMemcpyAsync((void *)ctr, d_ctr, 40, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
         (e = cudaStreamSynchronize(s)) != cudaSuccess)
@@ -623,6 +630,13 @@ int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_
     stats->nbr_reads = (int64_t)ctr[2];
     stats->launches = launches;
     cudaEventElapsedTime(&stats->kernel_ms, c->ev0, c->ev1);
+  }
+  if (trace_slow && since() > 5.0) {
+    float kms = 0.f;
+    cudaEventElapsedTime(&kms, c->ev0, c->ev1);
+    fprintf(stderr, "b200hnsw_search_batch slow call: total %.2f ms (context %.2f, queued at %.2f), device ev0..ev1 %.2f ms, "
+                    "B=%lld chunks=%d visited table %d direct_out=%d\n", since(), w_acq, w_queued, kms, (long long)B,
+            nchunk, h->vis_hint, (int)direct_out);
   }
   h->release(c);
   return 0;
