@@ -52,9 +52,12 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-exact", action="store_true", help="skip the ExactIndex (K3) side measurement")
     ap.add_argument("--exact-steps", type=int, default=10)
-    ap.add_argument("--inflight", type=int, default=2,
+    ap.add_argument("--inflight", type=int, default=3,
                     help="batches in flight in the device-resident measurement (traversal streams taking the steps in "
                          "turn); 1 = strictly one launch after the other")
+    ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
+                    help="N > 1: how per-shard results reach the rank that merges them: p2p = the traversal kernel "
+                         "stores them into peer memory itself (fused search + exchange); nccl = one all-to-all")
     ap.add_argument("--e2e-callers", type=int, default=4,
                     help="host threads making the synchronous host-pointer call concurrently in the e2e measurement "
                          "(the reference admits concurrent BatchSearch callers under its RWMutex read lock)")
@@ -111,11 +114,12 @@ class ClockSampler(threading.Thread):
     def run(self):
         if not self.ok:
             return
-        while not self._stop_ev.is_set():
+        errors = 0
+        while not self._stop_ev.is_set() and errors < 100:
             try:
                 self.sample()
             except Exception:
-                break
+                errors += 1  # a transient NVML error must not end the sampling of the timed region
             time.sleep(self.period)
 
     def stop(self):
@@ -225,8 +229,11 @@ def workload_config(args, world):
             "batch": args.batch, "mode": "reference (bit-faithful layerNode.search termination)",
             "layout": "1 graph" if world == 1 else
             f"{world} independent sub-graphs (one per GPU), queries broadcast; rank r merges queries [r*B/{world}, "
-            f"(r+1)*B/{world}): one NCCL all-to-all of the per-shard result blocks + K4 top-k merge, pipelined on a side "
-            f"stream under the traversal of the next step (all inside the timed region)",
+            f"(r+1)*B/{world}): " + (
+                "the traversal kernel stores each rank's share of its results into that rank's receive buffer over "
+                "NVLink (CUDA IPC peer memory; ready/freed flags, no collective)" if args.exchange == "p2p" else
+                "one NCCL all-to-all of the per-shard result blocks") +
+            " + K4 top-k merge on a side stream under the traversals of the next steps (all inside the timed region)",
             "batches_in_flight": max(1, args.inflight),
             "pipelining": f"steps are issued in turn on {max(1, args.inflight)} traversal stream(s): each step is one K1 "
                           f"launch over one {args.batch}-query batch, at most {max(1, args.inflight)} of them in flight",
@@ -309,7 +316,12 @@ def run_ours(args, rank, local_rank, world):
         torch.cuda.synchronize(dev)
 
     # N > 1: the all-to-all + merge of a batch run on a side stream under the traversals of the batches behind it
-    pipe = sharded.ShardPipeline(g, dist, B, k, n, dev, depth=depth) if world > 1 else None
+    pipe = None
+    if world > 1:
+        # p2p: K1 stores each rank's share of its results into that rank's receive buffer over NVLink (search and
+        # exchange are one kernel, flags instead of a collective); nccl: K1 + one NCCL all-to-all
+        Pipe = sharded.P2PShardPipeline if args.exchange == "p2p" else sharded.ShardPipeline
+        pipe = Pipe(g, dist, B, k, n, dev, depth=depth)
 
     sampler = ClockSampler(local_rank)
     sampler.start()
@@ -325,23 +337,28 @@ def run_ours(args, rank, local_rank, world):
     else:
         join()
     barrier()
+    if pipe is not None:
+        pipe.prof = []
     counters.zero_()
     ka = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     kb = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     ev0.record(stream)
+    t_issue = time.perf_counter()
     for i in range(args.steps):
         if world > 1:
             pipe.search(Qd[(args.warmup + i) % nb].data_ptr(), counters.data_ptr(), timing=(ka[i], kb[i]))
         else:
             search_step(i, Qd[(args.warmup + i) % nb], ka[i], kb[i])
+    t_issue = (time.perf_counter() - t_issue) / args.steps * 1e3  # host time to queue one step (launch-bound check)
     if world > 1:
         pipe.drain()  # the timed region ends when the last merge has finished
     else:
         join()
     ev1.record(stream)
     barrier()
+    pipe_prof = pipe.profile_summary() if pipe is not None and pipe.profile else None
     total_ms = ev0.elapsed_time(ev1)
     kernel_ms = [a.elapsed_time(b) for a, b in zip(ka, kb)]
     ctr = counters.cpu().numpy().copy()
@@ -386,7 +403,7 @@ def run_ours(args, rank, local_rank, world):
         # searches its shard, and returns the merged lists of its share of the queries (B / world of them) to page-
         # locked host memory behind the merge (side stream).  The host takes a slot's results (waits for that copy)
         # before it queues the slot again, nbuf steps later: the serving loop a caller of ShardPipeline runs.
-        seg = pipe.buf[0].seg
+        seg = pipe.seg
         nbuf = pipe.nbuf
         qtmp = [torch.empty((B, dim), dtype=torch.float32, device=dev) for _ in range(nbuf)]
         h_m = [(torch.empty((seg, k), dtype=torch.int64).pin_memory(), torch.empty((seg, k), dtype=torch.float32).pin_memory(),
@@ -488,10 +505,10 @@ def run_ours(args, rank, local_rank, world):
     line = {
         "metric": "batched Search QPS (Graph.BatchSearch, k=10)", "value": value, "unit": "queries/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "host_issue_ms_per_step": t_issue, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args, world),
         "e2e": {"value": e2e_value, "unit": "queries/s", "h2d_bytes_per_step": B * dim * 4,
-                "d2h_bytes_per_step": B * k * 8 + B * 4 + 40 if world == 1 else pipe.buf[0].seg * (k * 12 + 4),
+                "d2h_bytes_per_step": B * k * 8 + B * 4 + 40 if world == 1 else pipe.seg * (k * 12 + 4),
                 "callers": callers, "single_caller_value": units / e2e_single_s,
                 "passes": [units / x for x in e2e_passes] if e2e_passes else None,
                 "call": (f"b200hnsw_search_batch (host pointers, synchronous) from {callers} host threads, median of "
@@ -526,6 +543,8 @@ def run_ours(args, rank, local_rank, world):
                   "exact_sequential_vec_per_s": seq_rate},
     }
 
+    if pipe_prof:
+        line["pipeline_profile"] = pipe_prof
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         line.update(cpu_baseline_and_parity(args, g, Qh, last, last_rows, last_dists, last_counts, torch, dev, X))
     if rank == 0 and world == 1 and not args.no_exact:

@@ -79,6 +79,15 @@ SYMBOLS = {
                                                          C.c_void_p, C.c_void_p]),
     "b200hnsw_merge_shards_device": (C.c_int, [C.c_int32, C.c_int32, C.c_int64, C.c_int32, C.c_void_p, C.c_int64,
                                                C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b200hnsw_search_batch_scatter_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32,
+                                                       C.c_int32, C.c_int32, i32p, C.POINTER(C.c_void_p), C.c_int32,
+                                                       C.c_int64, C.c_void_p, C.c_void_p]),
+    "b200hnsw_peer_alloc": (C.c_int, [C.c_int32, C.c_int64, C.POINTER(C.c_void_p), u8p]),
+    "b200hnsw_peer_open": (C.c_int, [C.c_int32, u8p, C.POINTER(C.c_void_p)]),
+    "b200hnsw_peer_close": (C.c_int, [C.c_void_p]),
+    "b200hnsw_peer_free": (C.c_int, [C.c_void_p]),
+    "b200hnsw_peer_signal_device": (C.c_int, [C.c_int32, C.POINTER(C.c_void_p), C.c_int32, C.c_int32, C.c_void_p]),
+    "b200hnsw_peer_wait_device": (C.c_int, [C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
     "b200exact_create": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.POINTER(C.c_void_p)]),
     "b200exact_destroy": (None, [C.c_void_p]),
     "b200exact_len": (C.c_int64, [C.c_void_p]),

@@ -492,6 +492,39 @@ int b200hnsw_search_batch_segmented_device(b200hnsw_t *h, const float *d_queries
                        reinterpret_cast<unsigned long long *>(d_counters), d_err, h->vis_hint, s, seg_len, seg_stride);
 }
 
+int b200hnsw_search_batch_scatter_device(b200hnsw_t *h, const float *d_queries, int64_t B, int32_t k, int32_t ef,
+                                         int32_t metric, int32_t mode, const int32_t *entries,
+                                         int32_t *const *seg_ptrs, int32_t n_seg, int64_t seg_len,
+                                         int64_t *d_counters, void *stream) {
+  int rc = check_search_args(h, B, k, ef, metric);
+  if (rc) return rc;
+  if (seg_len <= 0 || n_seg <= 0 || n_seg > B200HNSW_MAX_PEERS || !seg_ptrs || (int64_t)n_seg * seg_len < B) {
+    set_error("search: bad scatter layout (seg_len=%lld n_seg=%d for B=%lld; n_seg <= %d)", (long long)seg_len, n_seg,
+              (long long)B, B200HNSW_MAX_PEERS);
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  for (int i = 0; i < n_seg; i++)
+    if (!seg_ptrs[i]) {
+      set_error("search: scatter pointer %d is null", i);
+      return B200HNSW_ERR_BAD_ARG;
+    }
+  B200_CUDA(cudaSetDevice(h->cfg.device));
+  cudaStream_t s = (cudaStream_t)stream;
+  if (B == 0) return 0;
+  if (h->live_layers() == 0) {  // graph.go:554-556: empty graph -> no results
+    for (int g = 0; g < n_seg; g++) {
+      B200_CUDA(cudaMemsetAsync(seg_ptrs[g], 0xff, sizeof(int32_t) * 2 * (size_t)seg_len * k, s));
+      B200_CUDA(cudaMemsetAsync(seg_ptrs[g] + 2 * seg_len * k, 0, sizeof(int32_t) * (size_t)seg_len, s));
+    }
+    return 0;
+  }
+  int *d_err = d_counters ? reinterpret_cast<int *>(d_counters + 4) : h->d_err_word;
+  // out_rows doubles as the "Search sink" marker of the kernel: any non-null value
+  return launch_search(h, d_queries, B, k, ef, metric, mode, entries, seg_ptrs[0], nullptr, nullptr,
+                       reinterpret_cast<unsigned long long *>(d_counters), d_err, h->vis_hint, s, seg_len, 0, seg_ptrs,
+                       n_seg);
+}
+
 // device alias of a page-locked, mapped host buffer (cudaHostAlloc / cudaHostRegister under UVA), or nullptr
 static void *mapped_host(const void *p) {
   cudaPointerAttributes a;

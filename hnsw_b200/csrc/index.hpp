@@ -96,7 +96,7 @@ namespace b200 {
 int launch_search(b200hnsw *h, const float *d_queries, int64_t B, int k, int ef, int metric, int mode,
                   const int32_t *entries, int32_t *d_rows, float *d_dists, int32_t *d_counts,
                   unsigned long long *d_counters, int *d_error, int vis_cap, cudaStream_t s, int64_t seg_len = 0,
-                  int64_t seg_stride = 0);
+                  int64_t seg_stride = 0, int32_t *const *seg_ptrs = nullptr, int n_seg_ptrs = 0);
 struct TraverseParams;
 int launch_traverse(b200hnsw *h, TraverseParams &p, int vis_cap, cudaStream_t s);
 }  // namespace b200

@@ -1,5 +1,6 @@
 // misc_kernels.cu -- b200hnsw_distance_batch: EuclideanDistance / CosineDistance (distance.go:15-23) on pairs,
 // one warp per pair, canonical order (dist.cuh).
+#include <cstring>
 #include <vector>
 
 #include "index.hpp"
@@ -15,9 +16,95 @@ __global__ void distance_pairs_kernel(const float4 *a, const float4 *b, long lon
   if (lane == 0) out[w] = d;
 }
 
+// ---- flags of the fused search + exchange (sharded.py P2PShardPipeline) -------------------------------------------------
+struct PeerFlagPtrs {
+  int32_t *p[B200HNSW_MAX_PEERS];
+};
+// everything this GPU wrote before (the traversal kernel's peer stores) is made visible system-wide, then the flags
+__global__ void peer_signal_kernel(PeerFlagPtrs f, int n, int value) {
+  __threadfence_system();
+  if ((int)threadIdx.x < n)
+    asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(f.p[threadIdx.x]), "r"(value) : "memory");
+}
+__global__ void peer_wait_kernel(const int32_t *flags, int n, int value) {
+  if ((int)threadIdx.x < n) {
+    int v;
+    do {
+      asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(flags + threadIdx.x) : "memory");
+      if (v < value) __nanosleep(200);
+    } while (v < value);
+  }
+  __syncthreads();
+  __threadfence_system();
+}
+
 }  // namespace b200
 
 using namespace b200;
+
+extern "C" int b200hnsw_peer_alloc(int32_t device, int64_t bytes, void **d_ptr, uint8_t handle[64]) {
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  if (bytes <= 0 || !d_ptr || !handle) {
+    set_error("peer_alloc: bad argument");
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  B200_CUDA(cudaSetDevice(device));
+  void *p = nullptr;
+  B200_CUDA(cudaMalloc(&p, (size_t)bytes));
+  cudaError_t e = cudaMemset(p, 0, (size_t)bytes);
+  cudaIpcMemHandle_t hd;
+  if (e == cudaSuccess) e = cudaIpcGetMemHandle(&hd, p);
+  if (e != cudaSuccess) {
+    cudaFree(p);
+    return cuda_fail(e, "peer_alloc");
+  }
+  memcpy(handle, &hd, 64);
+  *d_ptr = p;
+  return 0;
+}
+extern "C" int b200hnsw_peer_open(int32_t device, const uint8_t handle[64], void **d_ptr) {
+  if (!d_ptr || !handle) {
+    set_error("peer_open: bad argument");
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  B200_CUDA(cudaSetDevice(device));
+  cudaIpcMemHandle_t hd;
+  memcpy(&hd, handle, 64);
+  B200_CUDA(cudaIpcOpenMemHandle(d_ptr, hd, cudaIpcMemLazyEnablePeerAccess));
+  return 0;
+}
+extern "C" int b200hnsw_peer_close(void *d_ptr) {
+  if (d_ptr) B200_CUDA(cudaIpcCloseMemHandle(d_ptr));
+  return 0;
+}
+extern "C" int b200hnsw_peer_free(void *d_ptr) {
+  if (d_ptr) B200_CUDA(cudaFree(d_ptr));
+  return 0;
+}
+extern "C" int b200hnsw_peer_signal_device(int32_t device, int32_t *const *flag_ptrs, int32_t n, int32_t value,
+                                           void *stream) {
+  if (n <= 0 || n > B200HNSW_MAX_PEERS || !flag_ptrs) {
+    set_error("peer_signal: bad argument (n=%d, at most %d)", n, B200HNSW_MAX_PEERS);
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  B200_CUDA(cudaSetDevice(device));
+  PeerFlagPtrs f{};
+  for (int i = 0; i < n; i++) f.p[i] = flag_ptrs[i];
+  peer_signal_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(f, n, value);
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+extern "C" int b200hnsw_peer_wait_device(int32_t device, const int32_t *d_flags, int32_t n, int32_t value,
+                                         void *stream) {
+  if (n <= 0 || n > 32 || !d_flags) {
+    set_error("peer_wait: bad argument (n=%d, at most 32)", n);
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  B200_CUDA(cudaSetDevice(device));
+  peer_wait_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(d_flags, n, value);
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
 
 extern "C" int b200hnsw_distance_batch(int32_t device, int32_t metric, const float *a, const float *b, int64_t n,
                                        int32_t dim, float *out) {

@@ -126,7 +126,7 @@ int launch_traverse(b200hnsw *h, TraverseParams &p, int vis_cap, cudaStream_t s)
 int launch_search(b200hnsw *h, const float *d_queries, int64_t B, int k, int ef, int metric, int mode,
                   const int32_t *entries, int32_t *d_rows, float *d_dists, int32_t *d_counts,
                   unsigned long long *d_counters, int *d_error, int vis_cap, cudaStream_t s, int64_t seg_len,
-                  int64_t seg_stride) {
+                  int64_t seg_stride, int32_t *const *seg_ptrs, int n_seg_ptrs) {
   if (mode != B200HNSW_MODE_REFERENCE) {
     set_error("search: mode %d not implemented yet", mode);
     return B200HNSW_ERR_UNSUPPORTED;
@@ -146,6 +146,8 @@ int launch_search(b200hnsw *h, const float *d_queries, int64_t B, int k, int ef,
   p.out_counts = d_counts;
   p.out_seg_len = seg_len;
   p.out_seg_stride = seg_stride;
+  p.n_seg_ptr = n_seg_ptrs;
+  for (int i = 0; i < n_seg_ptrs && i < B200HNSW_MAX_PEERS; i++) p.seg_ptr[i] = seg_ptrs[i];
   p.counters = d_counters;
   p.error = d_error;
   p.dead = h->n_dead ? h->d.dead : nullptr;

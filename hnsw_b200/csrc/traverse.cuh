@@ -32,6 +32,11 @@ struct TraverseParams {
   // out_rows + s * out_seg_stride (int32 elements): rows [seg][k] | dists f32 [seg][k] | counts [seg] -- one
   // self-contained block per destination rank of the multi-GPU all-to-all
   long long out_seg_len, out_seg_stride;
+  // scattered segmented sink (n_seg_ptr > 0): block s starts at seg_ptr[s] instead of out_rows + s * out_seg_stride --
+  // the pointers may name PEER memory (another GPU's receive buffer, mapped over NVLink), so the traversal kernel
+  // delivers each rank's share of the results itself and no collective follows it
+  int n_seg_ptr;
+  int32_t *seg_ptr[B200HNSW_MAX_PEERS];
   // Add sink (out_rows == nullptr): results of every layer <= levels[t] go to slot slot_off[t] + layer
   const int32_t *levels;     // [B]
   const long long *slot_off; // [B]
@@ -54,7 +59,7 @@ struct OutPtrs {
 __device__ __forceinline__ OutPtrs search_out(const TraverseParams &p, long long q) {
   if (p.out_seg_len == 0) return {p.out_rows + q * p.k, p.out_dists + q * p.k, p.out_counts + q};
   const long long s = q / p.out_seg_len, ql = q - s * p.out_seg_len;
-  int32_t *base = p.out_rows + s * p.out_seg_stride;
+  int32_t *base = p.n_seg_ptr ? p.seg_ptr[s] : p.out_rows + s * p.out_seg_stride;
   return {base + ql * p.k, reinterpret_cast<float *>(base + p.out_seg_len * p.k) + ql * p.k,
           base + 2 * p.out_seg_len * p.k + ql};
 }

@@ -11,6 +11,9 @@ import os
 import numpy as np
 
 from . import _lib
+from .distance import metric_of as _metric_of
+
+_MAX_PEERS = 16  # B200HNSW_MAX_PEERS
 
 
 def shard_of_row(row: int, world: int) -> int:
@@ -163,10 +166,14 @@ class ShardPipeline:
         # traversal blocks that are waiting for an SM
         self.side = torch.cuda.Stream(device, priority=int(os.environ.get('B200HNSW_SIDE_PRIORITY', '-1')))
         self.buf = [SegmentedResults(B, k, self.world, self.rank, device) for _ in range(self.nbuf)]
+        self.seg, self.q0, self.q1 = self.buf[0].seg, self.buf[0].q0, self.buf[0].q1
         self.searched = [torch.cuda.Event() for _ in range(self.nbuf)]
         self.done = [torch.cuda.Event() for _ in range(self.nbuf)]
         self.used = [False] * self.nbuf
         self.step = 0
+        # optional per-stage timing (B200HNSW_PIPE_PROFILE=1): events around the exchange and the merge on the side stream
+        self.profile = os.environ.get("B200HNSW_PIPE_PROFILE") == "1"
+        self.prof = []
 
     def search(self, d_queries: int, d_counters: int = 0, timing=None, before=None, after=None) -> int:
         """Queue one batch (device pointer to [B, dim] f32); returns the slot its results will land in.
@@ -193,8 +200,16 @@ class ShardPipeline:
         self.searched[slot].record(t)
         self.side.wait_event(self.searched[slot])
         with torch.cuda.stream(self.side):
+            if self.profile:
+                e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+                e[0].record(self.side)
             b.exchange(self.dist)
+            if self.profile:
+                e[1].record(self.side)
             b.merge(self.n, self.side.cuda_stream)
+            if self.profile:
+                e[2].record(self.side)
+                self.prof.append(e)
             if after is not None:
                 after(self.side, slot)
         self.done[slot].record(self.side)
@@ -210,3 +225,176 @@ class ShardPipeline:
         for slot in range(self.nbuf):
             if self.used[slot]:
                 self.main.wait_event(self.done[slot])
+
+    def profile_summary(self):
+        """Mean device time of the exchange and of the merge on the side stream (ms), over the steps profiled so far."""
+        import torch
+        torch.cuda.synchronize()
+        if not self.prof:
+            return None
+        x = [e[0].elapsed_time(e[1]) for e in self.prof]
+        m = [e[1].elapsed_time(e[2]) for e in self.prof]
+        self.prof = []
+        return {"exchange_ms": sum(x) / len(x), "merge_ms": sum(m) / len(m), "steps": len(x)}
+
+
+class P2PShardPipeline:
+    """The sharded batched search with search and exchange FUSED: the traversal kernel writes every rank's share of its
+    results straight into that rank's receive buffer (peer memory over NVLink / NVSwitch, mapped through CUDA IPC), so
+    no collective and no extra kernel moves data.  What is left of the exchange is two flags per (slot, peer):
+
+        ready[slot][src] = step + 1   set by src, in every peer, behind its traversal of `step`  (data has landed)
+        freed[slot][dst] = step + 1   set by dst, in every peer, behind its merge of `step`      (slot may be reused)
+
+    Per step i (slot = i mod nbuf), on one of `depth` traversal streams: wait freed[slot][*] >= i + 1 - nbuf, K1 with
+    per-destination base pointers (b200hnsw_search_batch_scatter_device), signal ready[slot][me] = i + 1 everywhere;
+    on the merge stream: wait ready[slot][*] >= i + 1, K4 over the local receive buffer, signal freed.  Same results as
+    ShardPipeline (NCCL all-to-all); `merged(slot)`, `drain()`, `search(..., timing, before, after)` are the same."""
+
+    def __init__(self, graph, dist, B: int, k: int, rows_per_shard: int, device, depth: int = 2):
+        import torch
+        self.g, self.dist, self.B, self.k, self.n = graph, dist, B, k, rows_per_shard
+        self.world = dist.get_world_size() if dist is not None else 1
+        self.rank = dist.get_rank() if dist is not None else 0
+        if self.world > _MAX_PEERS:
+            raise ValueError(f"at most {_MAX_PEERS} ranks")
+        self.dev = torch.device(device)
+        self.devi = self.dev.index or 0
+        self.depth = max(1, int(depth))
+        self.nbuf = 2 * self.depth
+        self.seg = (B + self.world - 1) // self.world
+        self.stride = 2 * self.seg * k + self.seg          # int32 elements of one block (rows | dists | counts)
+        self.q0, self.q1 = min(B, self.rank * self.seg), min(B, (self.rank + 1) * self.seg)
+        # one peer-visible allocation per rank: nbuf receive buffers of world blocks, then the two flag arrays
+        self.recv_elems = self.world * self.stride
+        flag_off = self.nbuf * self.recv_elems
+        self.flag_elems = self.nbuf * _MAX_PEERS
+        total = (flag_off + 2 * self.flag_elems) * 4
+        L = _lib.lib()
+        mine, handle = C.c_void_p(), (C.c_uint8 * 64)()
+        _lib.check(L.b200hnsw_peer_alloc(self.devi, total, C.byref(mine), handle))
+        self._mine = mine.value
+        handles = [None] * self.world
+        if self.world > 1:
+            dist.all_gather_object(handles, bytes(handle))
+        else:
+            handles[0] = bytes(handle)
+        self._opened = []
+        self.base = []
+        for r in range(self.world):
+            if r == self.rank:
+                self.base.append(self._mine)
+            else:
+                ptr = C.c_void_p()
+                hb = (C.c_uint8 * 64).from_buffer_copy(handles[r])
+                _lib.check(L.b200hnsw_peer_open(self.devi, hb, C.byref(ptr)))
+                self._opened.append(ptr.value)
+                self.base.append(ptr.value)
+        self._flag_off = flag_off
+        # host arrays of device pointers, one per slot: where my block lands in each rank, and the flags I set there
+        self._seg_ptrs, self._ready_ptrs, self._freed_ptrs = [], [], []
+        for slot in range(self.nbuf):
+            VP = C.c_void_p * self.world
+            self._seg_ptrs.append(VP(*[self.base[r] + 4 * (slot * self.recv_elems + self.rank * self.stride)
+                                       for r in range(self.world)]))
+            self._ready_ptrs.append(VP(*[self.base[r] + 4 * (flag_off + slot * _MAX_PEERS + self.rank)
+                                         for r in range(self.world)]))
+            self._freed_ptrs.append(VP(*[self.base[r] + 4 * (flag_off + self.flag_elems + slot * _MAX_PEERS + self.rank)
+                                         for r in range(self.world)]))
+        self.main = torch.cuda.current_stream(self.dev)
+        self.trav = [torch.cuda.Stream(self.dev) for _ in range(self.depth)]
+        self.side = torch.cuda.Stream(self.dev, priority=-1)
+        self.m_d = [torch.empty((self.seg, k), dtype=torch.float32, device=self.dev) for _ in range(self.nbuf)]
+        self.m_i = [torch.empty((self.seg, k), dtype=torch.int64, device=self.dev) for _ in range(self.nbuf)]
+        self.m_c = [torch.empty((self.seg,), dtype=torch.int32, device=self.dev) for _ in range(self.nbuf)]
+        self.searched = [torch.cuda.Event() for _ in range(self.nbuf)]
+        self.done = [torch.cuda.Event() for _ in range(self.nbuf)]
+        self.used = [False] * self.nbuf
+        self.step = 0
+        self.profile = False
+        self.prof = []
+        if dist is not None and self.world > 1:
+            dist.barrier()  # every rank has opened every buffer before anyone writes
+
+    # addresses inside my own allocation
+    def _recv_ptr(self, slot):
+        return self._mine + 4 * slot * self.recv_elems
+
+    def _ready_flags(self, slot):
+        return self._mine + 4 * (self._flag_off + slot * _MAX_PEERS)
+
+    def _freed_flags(self, slot):
+        return self._mine + 4 * (self._flag_off + self.flag_elems + slot * _MAX_PEERS)
+
+    def search(self, d_queries: int, d_counters: int = 0, timing=None, before=None, after=None) -> int:
+        import torch
+        L = _lib.lib()
+        i = self.step
+        slot = i % self.nbuf
+        t = self.trav[i % self.depth]
+        self.step += 1
+        t.wait_stream(self.main)
+        if self.used[slot]:
+            t.wait_event(self.done[slot])  # my own merge of the slot's previous step (its m_* tensors are rewritten)
+        if i >= self.nbuf:  # every peer has merged what I wrote into this slot nbuf steps ago
+            _lib.check(L.b200hnsw_peer_wait_device(self.devi, C.c_void_p(self._freed_flags(slot)), self.world,
+                                                   i + 1 - self.nbuf, C.c_void_p(t.cuda_stream)))
+        if before is not None:
+            with torch.cuda.stream(t):
+                before(t, slot)
+        if timing is not None:
+            timing[0].record(t)
+        g = self.g
+        _lib.check(L.b200hnsw_search_batch_scatter_device(
+            g._h, C.c_void_p(d_queries), self.B, self.k, g.EfSearch, _metric_of(g.Distance), _lib.MODE_REFERENCE, None,
+            self._seg_ptrs[slot], self.world, self.seg, C.c_void_p(d_counters) if d_counters else None,
+            C.c_void_p(t.cuda_stream)))
+        if timing is not None:
+            timing[1].record(t)
+        _lib.check(L.b200hnsw_peer_signal_device(self.devi, self._ready_ptrs[slot], self.world, i + 1,
+                                                 C.c_void_p(t.cuda_stream)))
+        self.searched[slot].record(t)
+        self.side.wait_event(self.searched[slot])
+        s = self.side
+        _lib.check(L.b200hnsw_peer_wait_device(self.devi, C.c_void_p(self._ready_flags(slot)), self.world, i + 1,
+                                               C.c_void_p(s.cuda_stream)))
+        _lib.check(L.b200hnsw_merge_shards_device(
+            self.devi, self.world, self.seg, self.k, C.c_void_p(self._recv_ptr(slot)), self.stride, self.n,
+            C.c_void_p(self.m_d[slot].data_ptr()), C.c_void_p(self.m_i[slot].data_ptr()),
+            C.c_void_p(self.m_c[slot].data_ptr()), C.c_void_p(s.cuda_stream)))
+        _lib.check(L.b200hnsw_peer_signal_device(self.devi, self._freed_ptrs[slot], self.world, i + 1,
+                                                 C.c_void_p(s.cuda_stream)))
+        if after is not None:
+            with torch.cuda.stream(s):
+                after(s, slot)
+        self.done[slot].record(s)
+        self.used[slot] = True
+        return slot
+
+    def merged(self, slot: int):
+        return self.m_d[slot], self.m_i[slot], self.m_c[slot]
+
+    def drain(self):
+        for slot in range(self.nbuf):
+            if self.used[slot]:
+                self.main.wait_event(self.done[slot])
+
+    def profile_summary(self):
+        return None
+
+    def close(self):
+        """Collective: every rank stops using the buffers, then unmaps and frees."""
+        import torch
+        if self._mine is None:
+            return
+        torch.cuda.synchronize(self.dev)
+        if self.dist is not None and self.world > 1:
+            self.dist.barrier()
+        L = _lib.lib()
+        for p in self._opened:
+            L.b200hnsw_peer_close(C.c_void_p(p))
+        self._opened = []
+        if self.dist is not None and self.world > 1:
+            self.dist.barrier()
+        L.b200hnsw_peer_free(C.c_void_p(self._mine))
+        self._mine = None

@@ -53,6 +53,7 @@ enum { B200HNSW_MODE_REFERENCE = 0, B200HNSW_MODE_EXTENDED = 1 };
 #define B200HNSW_MAX_M 64
 #define B200HNSW_MAX_K 256
 #define B200HNSW_MAX_EF 1024
+#define B200HNSW_MAX_PEERS 16
 
 typedef struct b200hnsw b200hnsw_t;
 typedef struct b200exact b200exact_t;
@@ -136,6 +137,29 @@ int b200hnsw_search_batch_device(b200hnsw_t *h, const float *d_queries, int64_t 
 int b200hnsw_search_batch_segmented_device(b200hnsw_t *h, const float *d_queries, int64_t B, int32_t k, int32_t ef,
                                            int32_t metric, int32_t mode, const int32_t *entries, int32_t *d_packed,
                                            int64_t seg_len, int64_t seg_stride, int64_t *d_counters, void *stream);
+
+/* The segmented search with one base pointer PER destination rank (host array of n_seg device pointers, n_seg =
+ * ceil(B / seg_len) <= B200HNSW_MAX_PEERS): block s is written at seg_ptrs[s] in the same rows | dists | counts layout.
+ * The pointers may be peer memory opened with b200hnsw_peer_open (another GPU's receive buffer over NVLink): the
+ * traversal kernel then delivers every rank's share of the results itself -- search and exchange are ONE kernel, no
+ * collective follows (no reference counterpart). */
+int b200hnsw_search_batch_scatter_device(b200hnsw_t *h, const float *d_queries, int64_t B, int32_t k, int32_t ef,
+                                         int32_t metric, int32_t mode, const int32_t *entries,
+                                         int32_t *const *seg_ptrs, int32_t n_seg, int64_t seg_len,
+                                         int64_t *d_counters, void *stream);
+
+/* ---- peer memory for the fused search + exchange (one process per GPU; handles travel over any host channel) -------
+ * b200hnsw_peer_alloc: zero-filled device memory on `device` plus its 64-byte IPC handle; b200hnsw_peer_open maps
+ * another process's allocation into this process (peer access over NVLink is enabled on demand); _close / _free undo
+ * them.  b200hnsw_peer_signal_device: after everything queued on `stream` so far, store `value` (release, system
+ * scope) into each of the n int32 flags flag_ptrs[i] (local or peer).  b200hnsw_peer_wait_device: `stream` stalls
+ * until each of the n local int32 flags d_flags[i] is >= value (acquire, system scope). */
+int b200hnsw_peer_alloc(int32_t device, int64_t bytes, void **d_ptr, uint8_t handle[64]);
+int b200hnsw_peer_open(int32_t device, const uint8_t handle[64], void **d_ptr);
+int b200hnsw_peer_close(void *d_ptr);
+int b200hnsw_peer_free(void *d_ptr);
+int b200hnsw_peer_signal_device(int32_t device, int32_t *const *flag_ptrs, int32_t n, int32_t value, void *stream);
+int b200hnsw_peer_wait_device(int32_t device, const int32_t *d_flags, int32_t n, int32_t value, void *stream);
 
 /* ---- Graph.Add / Graph.BatchAdd (graph.go:437-531, 942-1042) ------------------------------------------------
  * Inserts n nodes in input order with the reference's semantics: per layer top->0 search(k=M, ef) from the

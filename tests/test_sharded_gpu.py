@@ -11,7 +11,7 @@ import pytest
 ROOT = Path(__file__).resolve().parent.parent
 
 
-def _worker(rank, world, port, tmp):
+def _worker(rank, world, port, tmp, kind="nccl"):
     sys.path.insert(0, str(ROOT))
     import torch
     import torch.distributed as dist
@@ -27,9 +27,14 @@ def _worker(rank, world, port, tmp):
     lv = np.minimum(np.random.default_rng(200 + rank).geometric(0.75, n) - 1, 5).astype(np.int32)
     g = hnsw_b200.Graph(M=12, Ml=0.25, EfSearch=ef, Distance=hnsw_b200.EuclideanDistance, device=rank, capacity=n)
     g.add_arrays(np.arange(n, dtype=np.int64), X, lv, wave_max=256)
-    pipe = sharded.ShardPipeline(g, dist, B, k, n, dev)
-    out = {}
-    for step in range(3):  # three batches through the two slots
+    if kind == "p2p":  # search + exchange fused: the traversal kernel stores into the peers' receive buffers
+        pipe = sharded.P2PShardPipeline(g, dist, B, k, n, dev)
+        seg, q0, q1 = pipe.seg, pipe.q0, pipe.q1
+    else:
+        pipe = sharded.ShardPipeline(g, dist, B, k, n, dev)
+        seg, q0, q1 = pipe.buf[0].seg, pipe.buf[0].q0, pipe.buf[0].q1
+    out = {"q0": q0, "q1": q1}
+    for step in range(3 if kind == "nccl" else 0):  # three batches, drained one by one
         Q = np.random.default_rng(7 + step).uniform(-1, 1, (B, d)).astype(np.float32)  # the same on every rank
         qd = torch.from_numpy(Q).to(dev)
         slot = pipe.search(qd.data_ptr())
@@ -46,10 +51,9 @@ def _worker(rank, world, port, tmp):
         out["q0"], out["q1"] = b.q0, b.q1
     # six batches queued back to back (no drain in between): both traversal streams busy, every slot reused, the merged
     # lists of each batch copied out behind its merge on the side stream
-    nq = 6
+    nq = 11 if kind == "p2p" else 6
     Qs = [np.random.default_rng(70 + s_).uniform(-1, 1, (B, d)).astype(np.float32) for s_ in range(nq)]
     qds = [torch.from_numpy(Q).to(dev) for Q in Qs]
-    seg = pipe.buf[0].seg
     keep_d = torch.empty((nq, seg, k), dtype=torch.float32, device=dev)
     keep_i = torch.empty((nq, seg, k), dtype=torch.int64, device=dev)
     keep_c = torch.empty((nq, seg), dtype=torch.int32, device=dev)
@@ -68,6 +72,8 @@ def _worker(rank, world, port, tmp):
         r_, d_, c_ = g.search_rows(Qs[s_], k, ef)
         out[f"prows{s_}"], out[f"pdd{s_}"], out[f"pcnt{s_}"] = r_, d_, c_
     np.savez(os.path.join(tmp, f"rank{rank}.npz"), **out)
+    if kind == "p2p":
+        pipe.close()
     dist.barrier()
     dist.destroy_process_group()
 
@@ -96,7 +102,11 @@ def test_two_gpu_pipeline_matches_merge_spec(tmp_path):
             assert np.array_equal(r[i][f"i{step}"][:q1 - q0], m[1][q0:q1])
             assert np.array_equal(r[i][f"c{step}"][:q1 - q0], m[2][q0:q1])
         assert (m[1] >= 3000).any() and (m[1][m[1] >= 0] < 3000).any()
-    for step in range(6):  # the back-to-back phase
+    _check_back_to_back(r, world, 6, merge_topk_ref)
+
+
+def _check_back_to_back(r, world, nq, merge_topk_ref):
+    for step in range(nq):  # the back-to-back phase
         all_d = np.stack([r[i][f"pdd{step}"] for i in range(world)])
         all_i = np.stack([np.where(r[i][f"prows{step}"] >= 0, r[i][f"prows{step}"].astype(np.int64) + i * 3000, -1)
                           for i in range(world)])
@@ -171,3 +181,19 @@ def test_two_gpu_sharded_exact_matches_oracle(tmp_path):
             tied = np.nonzero(o_d[q].view(np.uint32) == o_d[q, j].view(np.uint32))[0]
             assert set(r[i]["i"][q, tied].tolist()) == set(o_idx[q, tied].astype(np.int64).tolist())
         assert (r[i]["c"] == 10).all()
+
+
+@pytest.mark.gpu
+def test_two_gpu_fused_search_exchange_matches_merge_spec(tmp_path):
+    """P2PShardPipeline: K1 writes each rank's share of its results into that rank's receive buffer over NVLink (CUDA
+    IPC peer memory), flags instead of a collective; eleven batches back to back (every slot reused twice)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+    sys.path.insert(0, str(ROOT / "tests"))
+    from merge_ref import merge_topk_ref
+    world, port = 2, 29817 + os.getpid() % 200
+    mp.spawn(_worker, args=(world, port, str(tmp_path), "p2p"), nprocs=world, join=True)
+    r = [np.load(tmp_path / f"rank{i}.npz") for i in range(world)]
+    _check_back_to_back(r, world, 11, merge_topk_ref)
