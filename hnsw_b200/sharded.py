@@ -261,7 +261,7 @@ class P2PShardPipeline:
         self.dev = torch.device(device)
         self.devi = self.dev.index or 0
         self.depth = max(1, int(depth))
-        self.nbuf = 2 * self.depth
+        self.nbuf = int(os.environ.get("B200HNSW_PIPE_NBUF", 2 * self.depth))
         self.seg = (B + self.world - 1) // self.world
         self.stride = 2 * self.seg * k + self.seg          # int32 elements of one block (rows | dists | counts)
         self.q0, self.q1 = min(B, self.rank * self.seg), min(B, (self.rank + 1) * self.seg)

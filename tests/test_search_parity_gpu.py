@@ -122,7 +122,7 @@ def test_merge_kernel_matches_spec():
     from hnsw_b200 import sharded
     from merge_ref import merge_topk_ref
     rng = np.random.default_rng(3)
-    for G, B, k in ((2, 50, 10), (8, 33, 10), (4, 20, 64), (3, 7, 1)):
+    for G, B, k in ((2, 50, 10), (8, 33, 10), (4, 20, 64), (3, 7, 1), (4, 29, 10), (2, 9, 64), (8, 17, 16), (16, 5, 8)):
         d = np.round(rng.uniform(0, 4, (G, B, k)), 1).astype(np.float32)  # coarse values: many ties
         d.sort(axis=2)
         d[rng.uniform(size=d.shape) < 0.02] = np.nan
