@@ -1,5 +1,8 @@
 // misc_kernels.cu -- b200hnsw_distance_batch: EuclideanDistance / CosineDistance (distance.go:15-23) on pairs,
 // one warp per pair, canonical order (dist.cuh).
+#include <cuda.h>
+
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -81,6 +84,26 @@ extern "C" int b200hnsw_peer_free(void *d_ptr) {
   if (d_ptr) B200_CUDA(cudaFree(d_ptr));
   return 0;
 }
+// Stream memory operations (cuStreamBatchMemOp): the flag writes and waits are executed by the stream's front end, not by
+// a kernel, so they need no SM slot.  That matters here: with three traversal launches in flight a one-block flag kernel
+// queues behind every block of the launches issued before it.  B200HNSW_PEER_FLAGS=kernel selects the kernels.
+typedef CUresult (*BatchMemOpFn)(CUstream, unsigned int, CUstreamBatchMemOpParams *, unsigned int);
+static BatchMemOpFn batch_memop() {
+  static BatchMemOpFn fn = []() -> BatchMemOpFn {
+    const char *v = getenv("B200HNSW_PEER_FLAGS");
+    if (v && strcmp(v, "kernel") == 0) return nullptr;
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuStreamBatchMemOp", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess) {
+      cudaGetLastError();
+      return nullptr;
+    }
+    return (BatchMemOpFn)p;
+  }();
+  return fn;
+}
+
 extern "C" int b200hnsw_peer_signal_device(int32_t device, int32_t *const *flag_ptrs, int32_t n, int32_t value,
                                            void *stream) {
   if (n <= 0 || n > B200HNSW_MAX_PEERS || !flag_ptrs) {
@@ -88,6 +111,22 @@ extern "C" int b200hnsw_peer_signal_device(int32_t device, int32_t *const *flag_
     return B200HNSW_ERR_BAD_ARG;
   }
   B200_CUDA(cudaSetDevice(device));
+  if (BatchMemOpFn op = batch_memop()) {
+    CUstreamBatchMemOpParams ops[B200HNSW_MAX_PEERS];
+    memset(ops, 0, sizeof ops);
+    for (int i = 0; i < n; i++) {
+      ops[i].writeValue.operation = CU_STREAM_MEM_OP_WRITE_VALUE_32;
+      ops[i].writeValue.address = (CUdeviceptr)(uintptr_t)flag_ptrs[i];
+      ops[i].writeValue.value = (cuuint32_t)value;
+      ops[i].writeValue.flags = CU_STREAM_WRITE_VALUE_DEFAULT;  // preceded by a system-wide memory fence
+    }
+    CUresult r = op((CUstream)stream, (unsigned)n, ops, 0);
+    if (r != CUDA_SUCCESS) {
+      set_error("peer_signal: cuStreamBatchMemOp failed (%d)", (int)r);
+      return B200HNSW_ERR_CUDA;
+    }
+    return 0;
+  }
   PeerFlagPtrs f{};
   for (int i = 0; i < n; i++) f.p[i] = flag_ptrs[i];
   peer_signal_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(f, n, value);
@@ -101,6 +140,22 @@ extern "C" int b200hnsw_peer_wait_device(int32_t device, const int32_t *d_flags,
     return B200HNSW_ERR_BAD_ARG;
   }
   B200_CUDA(cudaSetDevice(device));
+  if (BatchMemOpFn op = batch_memop()) {
+    CUstreamBatchMemOpParams ops[32];
+    memset(ops, 0, sizeof ops);
+    for (int i = 0; i < n; i++) {
+      ops[i].waitValue.operation = CU_STREAM_MEM_OP_WAIT_VALUE_32;
+      ops[i].waitValue.address = (CUdeviceptr)(uintptr_t)(d_flags + i);
+      ops[i].waitValue.value = (cuuint32_t)value;
+      ops[i].waitValue.flags = CU_STREAM_WAIT_VALUE_GEQ;
+    }
+    CUresult r = op((CUstream)stream, (unsigned)n, ops, 0);
+    if (r != CUDA_SUCCESS) {
+      set_error("peer_wait: cuStreamBatchMemOp failed (%d)", (int)r);
+      return B200HNSW_ERR_CUDA;
+    }
+    return 0;
+  }
   peer_wait_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(d_flags, n, value);
   B200_CUDA(cudaGetLastError());
   return 0;
