@@ -323,7 +323,9 @@ def run_ours(args, rank, local_rank, world):
         Pipe = sharded.P2PShardPipeline if args.exchange == "p2p" else sharded.ShardPipeline
         pipe = Pipe(g, dist, B, k, n, dev, depth=depth)
 
-    sampler = ClockSampler(local_rank)
+    # NVML serialises its callers system-wide: rank 0 (whose samples go into the JSON line) samples every 2 ms, the
+    # other ranks every 20 ms
+    sampler = ClockSampler(local_rank, 0.002 if rank == 0 else 0.02)
     sampler.start()
 
     # ---- device-resident timing: W warm-up steps, then exactly K steps between events ---------------------------

@@ -153,7 +153,9 @@ int b200hnsw_search_batch_scatter_device(b200hnsw_t *h, const float *d_queries, 
  * another process's allocation into this process (peer access over NVLink is enabled on demand); _close / _free undo
  * them.  b200hnsw_peer_signal_device: after everything queued on `stream` so far, store `value` (release, system
  * scope) into each of the n int32 flags flag_ptrs[i] (local or peer).  b200hnsw_peer_wait_device: `stream` stalls
- * until each of the n local int32 flags d_flags[i] is >= value (acquire, system scope). */
+ * until each of the n local int32 flags d_flags[i] is >= value (acquire, system scope).  Both are stream memory
+ * operations (cuStreamBatchMemOp) executed by the stream's front end, with one-warp kernels as the alternative
+ * (environment B200HNSW_PEER_FLAGS=kernel, or a driver without the entry point). */
 int b200hnsw_peer_alloc(int32_t device, int64_t bytes, void **d_ptr, uint8_t handle[64]);
 int b200hnsw_peer_open(int32_t device, const uint8_t handle[64], void **d_ptr);
 int b200hnsw_peer_close(void *d_ptr);
