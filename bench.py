@@ -12,8 +12,13 @@ A "step" is one BatchSearch of `--batch` synthetic queries (k=10, EfSearch=64) a
   cpu_baseline: the oracle (CPU port of the reference's Go algorithm) on all host cores, same graph, same queries
   --impl reference: only the CPU port is built and timed (no GPU code on that path)
 
+Steps are issued in turn on --inflight traversal streams (default 3): every step is one K1 launch over one batch, and
+the launches in flight fill the SMs that a single launch's tail leaves idle.  e2e: --e2e-callers host threads each
+make the synchronous host-pointer call (the reference admits concurrent BatchSearch callers under its read lock).
+
 Multi-GPU (north_star): every rank owns an independent sub-graph of --n rows (weak scaling), the query batch is
-the same on all ranks, per-shard top-k lists are all-gathered over NCCL and merged by the K4 kernel.
+the same on all ranks; the traversal kernel stores each rank's share of the per-shard top-k lists straight into that
+rank's receive buffer over NVLink (--exchange p2p; `nccl` = one all-to-all instead) and the K4 kernel merges them.
 """
 from __future__ import annotations
 
@@ -538,6 +543,9 @@ def run_ours(args, rank, local_rank, world):
                      # that ~90% of them are served by L2 (the traversals of a batch share the upper layers and the hub
                      # rows); the kernel's real bound is traversal latency x resident traversals.
                      # event_frac = one launch's bytes / its event time while sharing the SMs; solo = the launch alone.
+                     "note": ("bytes are algorithmic (SURVEY 8d); frac > 1 means L2 reuse, not an error: see traffic "
+                              "(DRAM bytes of one cold launch, ncu) and DESIGN.md 4/K1 (the kernel is bound by traversal "
+                              "latency x resident traversals)"),
                      "launches_in_flight": depth,
                      "event_frac": alg_bytes / (kern_avg_ms / 1e3) / 1e9 / peak,
                      "solo_kernel_ms": solo_ms,
@@ -571,6 +579,8 @@ def run_ours(args, rank, local_rank, world):
     if rank == 0:
         emit(line)
     if world > 1:
+        if hasattr(pipe, "close"):
+            pipe.close()  # collective: unmap the peers' receive buffers, then free mine
         dist.barrier()
         dist.destroy_process_group()
     return 0
