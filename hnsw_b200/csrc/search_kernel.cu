@@ -69,6 +69,10 @@ int launch_traverse(b200hnsw *h, TraverseParams &p, int vis_cap, cudaStream_t s)
   p.heap_r = (kr + 1) & ~1;
   p.fresh_cap = (g.M + 3) & ~3;
   p.vis_cap = round_pow2(vis_cap < 256 ? 256 : vis_cap);
+  p.off_r = p.heap_c * 8;
+  p.off_fresh = (p.heap_c + p.heap_r) * 8;
+  p.off_vis = p.off_fresh + p.fresh_cap * 4;
+  p.group_bytes = (int)traverse_group_bytes(p);
   int G = pick_group(g.row_chunks);
   // a large visited table (retry after overflow) only fits with one traversal per warp
   if (traverse_group_bytes(p) * TRAV_WARPS * (32 / G) > h->smem_optin - 512) G = 32;

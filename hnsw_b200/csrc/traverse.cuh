@@ -48,6 +48,9 @@ struct TraverseParams {
   int *error;                    // set to 1 on visited overflow
   int vis_cap;                   // visited-table entries per group (power of two)
   int heap_c, heap_r, fresh_cap; // per-group slots: uint2, uint2, int
+  // byte layout of one group's shared memory, computed once by the launcher (the kernel re-derives these addresses
+  // wherever it runs out of registers, so they should cost one constant load, not a chain of multiplies)
+  int group_bytes, off_r, off_fresh, off_vis;
   const uint8_t *dead;           // [rows] rows Delete removed from layer.nodes; null while nothing was deleted
 };
 
@@ -90,12 +93,11 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
   const int gshift = grp * G;
   const int leader_lane = gshift;
   const bool leader = gl == 0;
-  const size_t gbytes = traverse_group_bytes(p);
-  unsigned char *base = smem + gbytes * (size_t)(warp * NG + grp);
+  unsigned char *base = smem + (unsigned)(p.group_bytes * (warp * NG + grp));
   GoHeap C{reinterpret_cast<uint2 *>(base), 0};
-  GoHeap R{reinterpret_cast<uint2 *>(base) + p.heap_c, 0};
-  int *fresh = reinterpret_cast<int *>(base + (size_t)(p.heap_c + p.heap_r) * 8);
-  uint32_t *vtab = reinterpret_cast<uint32_t *>(base + (size_t)(p.heap_c + p.heap_r) * 8 + (size_t)p.fresh_cap * 4);
+  GoHeap R{reinterpret_cast<uint2 *>(base + p.off_r), 0};
+  int *fresh = reinterpret_cast<int *>(base + p.off_fresh);
+  uint32_t *vtab = reinterpret_cast<uint32_t *>(base + p.off_vis);
   const uint32_t vmask = (uint32_t)p.vis_cap - 1;
   const int M = g.M;
 
