@@ -1,0 +1,155 @@
+// host_test.cpp -- the C++ host mirror (include/b200hnsw_host.hpp) exercised the way the reference's own tests exercise
+// the Go API, plus parity against the CPU oracle (oracle/hnsw_oracle.h: test infrastructure, linked here only).
+//   host_test --cpu : what needs no device -- validation texts (graph_test.go:415-459), maxLevel (graph_test.go:14-25),
+//                     the loud failure of a compute call without a CUDA device
+//   host_test --gpu : distance KATs (distance_test.go:9-31), TestGraph_DefaultCosine (graph_test.go:253-275), and a random
+//                     graph built through Graph.Add / BatchAddWaves whose Search / BatchSearch keys, in order, equal the
+//                     oracle's on the same rows and levels
+#include <cstdio>
+#include <cstdlib>
+#include <string>
+#include <vector>
+
+#include "b200hnsw_host.hpp"
+#include "hnsw_oracle.h"
+
+static int failures = 0;
+#define CHECK(cond)                                                           \
+  do {                                                                        \
+    if (!(cond)) {                                                            \
+      std::printf("FAIL %s:%d: %s\n", __FILE__, __LINE__, #cond);             \
+      failures++;                                                             \
+    }                                                                         \
+  } while (0)
+
+template <class F>
+static std::string error_of(F &&f) {
+  try {
+    f();
+  } catch (const hnsw::Error &e) {
+    return e.what();
+  }
+  return "";
+}
+static bool contains(const std::string &s, const char *sub) { return s.find(sub) != std::string::npos; }
+
+static void cpu_tests() {
+  using namespace hnsw;
+  // graph_test.go:14-25
+  CHECK(maxLevel(0.5, 10) == 4);
+  CHECK(maxLevel(0.5, 1000) == 11);
+  CHECK(contains(error_of([] { maxLevel(0, 10); }), "ml must be greater than 0"));
+  // graph_test.go:415-459
+  CHECK(error_of([] { NewGraphWithConfig<int>(16, 0.25, 20, CosineDistance); }).empty());
+  CHECK(contains(error_of([] { NewGraphWithConfig<int>(0, 0.25, 20, CosineDistance); }), "M must be greater than 0"));
+  CHECK(contains(error_of([] { NewGraphWithConfig<int>(16, 0, 20, CosineDistance); }), "Ml must be between 0 and 1"));
+  CHECK(contains(error_of([] { NewGraphWithConfig<int>(16, 1.5, 20, CosineDistance); }), "Ml must be between 0 and 1"));
+  CHECK(contains(error_of([] { NewGraphWithConfig<int>(16, 0.25, 0, CosineDistance); }),
+                 "EfSearch must be greater than 0"));
+  CHECK(contains(error_of([] { NewGraphWithConfig<int>(16, 0.25, 20, nullptr); }), "Distance function must be set"));
+  {
+    auto g = NewGraph<int>();
+    CHECK(contains(error_of([&] { g.Search({1, 2, 3}, 0); }), "k must be greater than 0"));
+    CHECK(contains(error_of([&] { g.ParallelSearch({1, 2, 3}, -1, 4); }), "k must be greater than 0"));
+    CHECK(g.Search({1, 2, 3}, 1).empty());  // graph.go:554-556: empty graph -> (nil, nil)
+    CHECK(g.Len() == 0 && g.Dims() == 0 && !g.Lookup(1).second);
+    CHECK(g.M == 16 && g.Ml == 0.25 && g.EfSearch == 20 && g.Distance == CosineDistance);  // graph.go:340-349
+  }
+  // distance.go:25-46
+  CHECK(distanceFuncToName(EuclideanDistance).first == "euclidean" && distanceFuncToName(CosineDistance).second);
+  CHECK(!distanceFuncToName(nullptr).second);
+}
+
+static void no_device_test() {
+  using namespace hnsw;
+  auto g = NewGraph<int>();
+  std::string e = error_of([&] { g.Add(MakeNode(1, {1, 1})); });
+  CHECK(contains(e, "b200hnsw:"));  // B200HNSW_ERR_CUDA surfaced as an error: no CPU fallback
+  CHECK(g.Len() == 0);
+}
+
+static void gpu_tests() {
+  using namespace hnsw;
+  // distance_test.go:9-31
+  CHECK(EuclideanDistance({1, 2, 3}, {4, 5, 6}) == 5.196152f);
+  CHECK(std::fabs(CosineDistance({1, 1, 1}, {0.8f, 0.8f, 0.8f})) < 1e-6f);
+  CHECK(std::fabs(CosineDistance({1, 0}, {0, 1}) - 1.f) < 1e-6f);
+  CHECK(std::fabs(CosineDistance({1, 0}, {1, 0})) < 1e-6f);
+  {  // graph_test.go:253-275
+    auto g = NewGraph<int>();
+    g.Add(MakeNode(1, {1, 1}), MakeNode(2, {0, 1}), MakeNode(3, {1, -1}));
+    auto nb = g.Search({0.5f, 0.5f}, 1);
+    CHECK(nb.size() == 1 && nb[0].Key == 1 && nb[0].Value == Vector({1, 1}));
+    CHECK(g.Len() == 3 && g.Dims() == 2 && g.Lookup(2).second && g.Lookup(2).first == Vector({0, 1}));
+    CHECK(contains(error_of([&] { g.Search({0.5f}, 1); }), "embedding dimension mismatch: 2 != 1"));
+    CHECK(contains(error_of([&] { g.Add(MakeNode(9, {1, 2, 3})); }), "embedding dimension mismatch: 2 != 3"));
+  }
+  // random graph: host Graph.Add (exact sequential order) and BatchAddWaves vs the oracle on the same rows and levels
+  for (int waves = 0; waves < 2; waves++) {
+    const int n = waves ? 3000 : 1200, d = 24, M = 8, ef = 32, k = 5, nq = 100;
+    std::mt19937 rng(7 + waves);
+    std::uniform_real_distribution<float> U(-1.f, 1.f);
+    std::vector<Node<int64_t>> nodes;
+    for (int i = 0; i < n; i++) {
+      Vector v(d);
+      for (auto &x : v) x = U(rng);
+      nodes.push_back(MakeNode<int64_t>(1000 - 3 * i, v));  // descending keys: list order != insertion order
+    }
+    auto g = NewGraphWithConfig<int64_t>(M, 0.25, ef, EuclideanDistance);
+    g.Rng.emplace((uint64_t)(99 + waves));
+    if (waves) g.BatchAddWaves(nodes, 256);
+    else g.BatchAdd(nodes);
+    CHECK(g.Len() == n);
+    // the levels the host drew, read back from the device
+    std::vector<float> vec((size_t)n * d);
+    std::vector<int64_t> keys(n);
+    std::vector<int32_t> levels(n);
+    CHECK(b200hnsw_get_rows(g.Handle(), 0, n, vec.data(), keys.data(), levels.data()) == 0);
+    ora_graph *og = ora_graph_new(d, M, ORA_EUCLIDEAN, ORA_FLAVOR_CANONICAL);
+    if (waves) ora_graph_add_waves(og, keys.data(), vec.data(), levels.data(), n, ef, 256, 2);
+    else ora_graph_add_many(og, keys.data(), vec.data(), levels.data(), n, ef);
+    auto topo = g.Topography();
+    CHECK((int)topo.size() == ora_graph_layers(og));
+    for (size_t l = 0; l < topo.size(); l++) CHECK(topo[l] == (int)ora_graph_layer_size(og, (int)l));
+    std::vector<Vector> qs;
+    for (int i = 0; i < nq; i++) {
+      Vector q(d);
+      for (auto &x : q) x = U(rng);
+      qs.push_back(q);
+    }
+    auto batch = g.BatchSearch(qs, k);
+    int mismatched = 0;
+    for (int i = 0; i < nq; i++) {
+      int32_t rows[16];
+      float dist[16];
+      int cnt = ora_graph_search(og, qs[i].data(), k, ef, ORA_MODE_REFERENCE, nullptr, rows, dist);
+      auto one = g.Search(qs[i], k);
+      bool ok = (int)one.size() == cnt && (int)batch[i].size() == cnt;
+      for (int j = 0; ok && j < cnt; j++)
+        ok = one[j].Key == ora_graph_key(og, rows[j]) && batch[i][j].Key == one[j].Key &&
+             one[j].Value == Vector(ora_graph_vector(og, rows[j]), ora_graph_vector(og, rows[j]) + d);
+      mismatched += !ok;
+    }
+    CHECK(mismatched == 0);
+    // Delete through the host: the key leaves Lookup / Len, a second Delete reports false (graph.go:843-866)
+    CHECK(g.Delete(nodes[5].Key) && !g.Delete(nodes[5].Key) && g.Len() == n - 1 && !g.Lookup(nodes[5].Key).second);
+    CHECK(ora_graph_delete(og, nodes[5].Key) == 1);
+    auto after = g.Search(qs[0], k);
+    int32_t rows[16];
+    float dist[16];
+    int cnt = ora_graph_search(og, qs[0].data(), k, ef, ORA_MODE_REFERENCE, nullptr, rows, dist);
+    CHECK((int)after.size() == cnt);
+    for (int j = 0; j < cnt && j < (int)after.size(); j++) CHECK(after[j].Key == ora_graph_key(og, rows[j]));
+    CHECK(contains(error_of([&] { g.Add(nodes[7]); }), "already present"));
+    ora_graph_free(og);
+  }
+}
+
+int main(int argc, char **argv) {
+  const std::string mode = argc > 1 ? argv[1] : "--cpu";
+  cpu_tests();
+  if (mode == "--gpu") gpu_tests();
+  else if (mode == "--cpu-nodevice") no_device_test();
+  std::printf("%s: %d failure(s)\n", mode.c_str(), failures);
+  return failures ? 1 : 0;
+}
