@@ -325,8 +325,14 @@ def run_ours(args, rank, local_rank, world):
     if world > 1:
         # p2p: K1 stores each rank's share of its results into that rank's receive buffer over NVLink (search and
         # exchange are one kernel, flags instead of a collective); nccl: K1 + one NCCL all-to-all
-        Pipe = sharded.P2PShardPipeline if args.exchange == "p2p" else sharded.ShardPipeline
-        pipe = Pipe(g, dist, B, k, n, dev, depth=depth)
+        if args.exchange == "p2p":
+            try:
+                pipe = sharded.P2PShardPipeline(g, dist, B, k, n, dev, depth=depth)
+            except RuntimeError as e:  # raised on every rank together; the collective variant needs no peer mapping
+                print(f"bench.py: {e}; using the NCCL all-to-all exchange", file=sys.stderr)
+                args.exchange = "nccl"
+        if pipe is None:
+            pipe = sharded.ShardPipeline(g, dist, B, k, n, dev, depth=depth)
 
     # NVML serialises its callers system-wide: rank 0 (whose samples go into the JSON line) samples every 2 ms, the
     # other ranks every 20 ms

@@ -281,15 +281,35 @@ class P2PShardPipeline:
             handles[0] = bytes(handle)
         self._opened = []
         self.base = []
-        for r in range(self.world):
-            if r == self.rank:
-                self.base.append(self._mine)
-            else:
-                ptr = C.c_void_p()
-                hb = (C.c_uint8 * 64).from_buffer_copy(handles[r])
-                _lib.check(L.b200hnsw_peer_open(self.devi, hb, C.byref(ptr)))
-                self._opened.append(ptr.value)
-                self.base.append(ptr.value)
+        problem = None
+        try:
+            if os.environ.get("B200HNSW_TEST_P2P_FAIL") == str(self.rank):
+                raise RuntimeError("peer mapping refused (test hook)")
+            for r in range(self.world):
+                if r == self.rank:
+                    self.base.append(self._mine)
+                else:
+                    ptr = C.c_void_p()
+                    hb = (C.c_uint8 * 64).from_buffer_copy(handles[r])
+                    _lib.check(L.b200hnsw_peer_open(self.devi, hb, C.byref(ptr)))
+                    self._opened.append(ptr.value)
+                    self.base.append(ptr.value)
+        except Exception as e:  # e.g. no peer access between two devices
+            problem = e
+        if dist is not None and self.world > 1:
+            # every rank learns whether EVERY rank mapped its peers, so that all of them give up together
+            ok = torch.tensor([0 if problem else 1], dtype=torch.int32, device=device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if int(ok.item()) == 0 and problem is None:
+                problem = RuntimeError("another rank could not map its peers' buffers")
+        if problem is not None:
+            for q in self._opened:
+                L.b200hnsw_peer_close(C.c_void_p(q))
+            if dist is not None and self.world > 1:
+                dist.barrier()
+            L.b200hnsw_peer_free(C.c_void_p(self._mine))
+            self._mine = None
+            raise RuntimeError(f"P2PShardPipeline: peer memory is not available ({problem})")
         self._flag_off = flag_off
         # host arrays of device pointers, one per slot: where my block lands in each rank, and the flags I set there
         self._seg_ptrs, self._ready_ptrs, self._freed_ptrs = [], [], []
