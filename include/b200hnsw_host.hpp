@@ -391,4 +391,114 @@ Graph<K> NewGraphWithConfig(int m, double ml, int efSearch, DistanceFunc distanc
   return g;
 }
 
+// ---- hnsw-extensions/hybrid/exact.go:13-160: ExactIndex[K], brute force on the device (b200exact_*) --------------------
+// The key type only has to be hashable here (exact.go's map[K][]float32).  Go's map iteration order (random) is replaced
+// by insertion order wherever exact.go iterates the map, so ties resolve to the earlier-added key.
+namespace hybrid {
+
+template <class K>
+class ExactIndex {
+ public:
+  explicit ExactIndex(DistanceFunc distance, int device = 0)
+      : distance_(distance), metric_(detail::metric_of(distance)), device_(device) {}
+  ExactIndex(const ExactIndex &) = delete;
+  ExactIndex &operator=(const ExactIndex &) = delete;
+  ~ExactIndex() { Close(); }
+
+  // exact.go:27-38
+  void Add(const K &key, const Vector &vector) { BatchAdd({key}, {vector}); }
+
+  // exact.go:41-58
+  void BatchAdd(const std::vector<K> &keys, const std::vector<Vector> &vectors) {
+    if (keys.size() != vectors.size())
+      throw Error(detail::fmt("number of keys (%zu) does not match number of vectors (%zu)", keys.size(),
+                              vectors.size()));
+    if (keys.empty()) return;
+    const int dim = (int)vectors[0].size();
+    if (!x_) {
+      detail::check(b200exact_create(dim, metric_, device_, 0, &x_));
+      dim_ = dim;
+    }
+    for (auto &v : vectors)
+      if ((int)v.size() != dim_)
+        throw Error(detail::fmt("embedding dimension mismatch: %d != %d", dim_, (int)v.size()));
+    // map assignment overwrites an existing key (exact.go:36, 54): its old row is tombstoned; a key repeated inside the
+    // batch keeps its last vector
+    std::unordered_map<K, size_t> last;
+    for (size_t i = 0; i < keys.size(); i++) last[keys[i]] = i;
+    std::vector<size_t> keep;
+    std::vector<int64_t> stale;
+    for (size_t i = 0; i < keys.size(); i++)
+      if (last[keys[i]] == i) {
+        keep.push_back(i);
+        auto it = row_of_.find(keys[i]);
+        if (it != row_of_.end()) stale.push_back(it->second);
+      }
+    if (!stale.empty()) detail::check(b200exact_remove(x_, stale.data(), (int64_t)stale.size()));
+    std::vector<float> flat(keep.size() * (size_t)dim_);
+    for (size_t j = 0; j < keep.size(); j++)
+      std::memcpy(&flat[j * dim_], vectors[keep[j]].data(), sizeof(float) * dim_);
+    int64_t first = 0;
+    detail::check(b200exact_add_batch(x_, flat.data(), (int64_t)keep.size(), &first));
+    for (size_t j = 0; j < keep.size(); j++) {
+      row_of_[keys[keep[j]]] = first + (int64_t)j;
+      key_of_.push_back(keys[keep[j]]);
+      vecs_.push_back(vectors[keep[j]]);  // exact.go:32-36 stores a copy
+    }
+  }
+
+  // exact.go:61-111: ascending by distance, the first min(k, len) nodes
+  std::vector<Node<K>> Search(const Vector &query, int k) {
+    std::vector<Node<K>> out;
+    if (Len() == 0 || k <= 0) return out;  // exact.go:65-67
+    if ((int)query.size() != dim_)
+      throw Error(detail::fmt("embedding dimension mismatch: %d != %d", dim_, (int)query.size()));
+    std::vector<int64_t> rows((size_t)k);
+    std::vector<float> dists((size_t)k);
+    int32_t count = 0;
+    detail::check(b200exact_search_batch(x_, query.data(), 1, k, rows.data(), dists.data(), &count, nullptr));
+    for (int i = 0; i < count; i++) out.push_back(Node<K>{key_of_[(size_t)rows[i]], vecs_[(size_t)rows[i]]});
+    return out;
+  }
+
+  // exact.go:114-145
+  bool Delete(const K &key) { return BatchDelete({key})[0]; }
+  std::vector<bool> BatchDelete(const std::vector<K> &keys) {
+    std::vector<bool> res;
+    std::vector<int64_t> rows;
+    for (auto &k : keys) {
+      auto it = row_of_.find(k);
+      res.push_back(it != row_of_.end());
+      if (it != row_of_.end()) {
+        rows.push_back(it->second);
+        row_of_.erase(it);
+      }
+    }
+    if (!rows.empty()) detail::check(b200exact_remove(x_, rows.data(), (int64_t)rows.size()));
+    return res;
+  }
+
+  int Len() const { return x_ ? (int)b200exact_len(x_) : 0; }  // exact.go:148-153
+  void Close() {                                               // exact.go:156-160
+    if (x_) b200exact_destroy(x_);
+    x_ = nullptr;
+    row_of_.clear(), key_of_.clear(), vecs_.clear();
+  }
+
+ private:
+  DistanceFunc distance_;
+  int metric_, device_, dim_ = 0;
+  b200exact_t *x_ = nullptr;
+  std::unordered_map<K, int64_t> row_of_;
+  std::vector<K> key_of_;
+  std::vector<Vector> vecs_;
+};
+
+// exact.go:20-25
+template <class K>
+std::unique_ptr<ExactIndex<K>> NewExactIndex(DistanceFunc distance) {
+  return std::make_unique<ExactIndex<K>>(distance);
+}
+
+}  // namespace hybrid
 }  // namespace hnsw

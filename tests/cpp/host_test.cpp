@@ -145,10 +145,61 @@ static void gpu_tests() {
   }
 }
 
+// hybrid.ExactIndex (exact.go:13-160) through the C++ host against the oracle's restatement of ExactIndex.Search
+static void gpu_exact_tests() {
+  using namespace hnsw;
+  for (int metric = 0; metric < 2; metric++) {
+    const int n = 5000, d = 48, k = 7, nq = 60;
+    std::mt19937 rng(21 + metric);
+    std::uniform_real_distribution<float> U(-1.f, 1.f);
+    std::vector<std::string> keys;
+    std::vector<Vector> vecs;
+    std::vector<float> flat;
+    for (int i = 0; i < n; i++) {
+      Vector v(d);
+      for (auto &x : v) x = U(rng);
+      keys.push_back("k" + std::to_string(i));  // string keys: the exact index only hashes them
+      vecs.push_back(v);
+      flat.insert(flat.end(), v.begin(), v.end());
+    }
+    auto x = hybrid::NewExactIndex<std::string>(metric ? CosineDistance : EuclideanDistance);
+    CHECK(x->Search(vecs[0], 3).empty());  // exact.go:65-67
+    x->BatchAdd(keys, vecs);
+    CHECK(x->Len() == n);
+    int bad = 0;
+    for (int i = 0; i < nq; i++) {
+      Vector q(d);
+      for (auto &v : q) v = U(rng);
+      int32_t idx[16];
+      float dist[16];
+      int cnt = ora_exact_search(flat.data(), n, d, metric, ORA_FLAVOR_CANONICAL, q.data(), k, 0, idx, dist);
+      auto got = x->Search(q, k);
+      bool ok = (int)got.size() == cnt;
+      for (int j = 0; ok && j < cnt; j++) ok = got[j].Key == keys[(size_t)idx[j]] && got[j].Value == vecs[(size_t)idx[j]];
+      bad += !ok;
+    }
+    CHECK(bad == 0);
+    // overwrite (exact.go:36) and delete (exact.go:114-126)
+    x->Add("k3", vecs[10]);
+    CHECK(x->Len() == n);
+    auto hit = x->Search(vecs[10], 2);
+    CHECK(hit.size() == 2 && hit[0].Key == "k10" && hit[1].Key == "k3");  // equal distance: the earlier row first
+    CHECK(x->Delete("k10") && !x->Delete("k10") && x->Len() == n - 1);
+    hit = x->Search(vecs[10], 1);
+    CHECK(hit.size() == 1 && hit[0].Key == "k3");
+    CHECK(contains(error_of([&] { x->BatchAdd({"a", "b"}, {vecs[0]}); }), "number of keys (2) does not match"));
+    x->Close();
+    CHECK(x->Len() == 0);
+  }
+}
+
 int main(int argc, char **argv) {
   const std::string mode = argc > 1 ? argv[1] : "--cpu";
   cpu_tests();
-  if (mode == "--gpu") gpu_tests();
+  if (mode == "--gpu") {
+    gpu_tests();
+    gpu_exact_tests();
+  }
   else if (mode == "--cpu-nodevice") no_device_test();
   std::printf("%s: %d failure(s)\n", mode.c_str(), failures);
   return failures ? 1 : 0;
