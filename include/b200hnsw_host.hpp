@@ -188,6 +188,29 @@ class Graph {
     return t;
   }
   const b200hnsw_t *Handle() const { return h_; }  // for parity harnesses (levels, neighbour lists)
+  int ListStride() const { return max_m_; }         // neighbour slots per list on the device
+
+  // Import (b200hnsw_encode.hpp): drop the content, then install a flattened graph (rows, CSR lists per layer)
+  void LoadFlatBegin() {
+    close();
+    dim_ = max_m_ = 0;
+    keys_.clear(), row_of_.clear(), retired_.clear(), vecs_.clear();
+  }
+  void LoadFlat(int64_t n, int dim, const std::vector<float> &flat, const std::vector<int64_t> &keys,
+                const std::vector<int32_t> &levels, int nLayers, const std::vector<int32_t> &entries,
+                const std::vector<int64_t> &layerSizes, const std::vector<int32_t> &layerRows,
+                const std::vector<int64_t> &layerPtr, const std::vector<int32_t> &layerNbr,
+                const std::vector<Vector> &vecs) {
+    b200hnsw_config cfg{};
+    cfg.dim = dim, cfg.max_m = M < B200HNSW_MAX_M ? M : B200HNSW_MAX_M, cfg.device = Device, cfg.capacity = n;
+    detail::check(b200hnsw_create(&cfg, &h_));
+    dim_ = dim, max_m_ = cfg.max_m;
+    detail::check(b200hnsw_load(h_, n, flat.data(), keys.data(), levels.data(), nLayers, entries.data(),
+                                layerSizes.data(), layerRows.data(), layerPtr.data(), layerNbr.data()));
+    keys_ = keys;
+    vecs_ = vecs;
+    for (int64_t i = 0; i < n; i++) row_of_[keys[(size_t)i]] = (int32_t)i;
+  }
 
   // graph.go:388-417
   int randomLevel() {

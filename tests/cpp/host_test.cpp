@@ -10,6 +10,9 @@
 #include <string>
 #include <vector>
 
+#include <sstream>
+
+#include "b200hnsw_encode.hpp"
 #include "b200hnsw_host.hpp"
 #include "hnsw_oracle.h"
 
@@ -54,6 +57,26 @@ static void cpu_tests() {
     CHECK(g.Search({1, 2, 3}, 1).empty());  // graph.go:554-556: empty graph -> (nil, nil)
     CHECK(g.Len() == 0 && g.Dims() == 0 && !g.Lookup(1).second);
     CHECK(g.M == 16 && g.Ml == 0.25 && g.EfSearch == 20 && g.Distance == CosineDistance);  // graph.go:340-349
+  }
+  {  // encode_test.go:11-50
+    std::string b;
+    enc::putVarint(b, 1337);
+    CHECK(b.size() == 2);
+    std::istringstream is(b);
+    CHECK(enc::readVarint(is) == 1337);
+    std::string s;
+    enc::putString(s, "hello");
+    CHECK(s.size() == 6);
+    std::istringstream is2(s);
+    CHECK(enc::readString(is2) == "hello");
+    for (int64_t v : {0LL, -1LL, 1LL, -64LL, 63LL, 64LL, (long long)INT64_MAX, (long long)INT64_MIN}) {
+      std::string t;
+      enc::putVarint(t, v);
+      uint8_t ref[16];
+      CHECK(ora_put_varint(ref, v) == (int)t.size() && std::memcmp(ref, t.data(), t.size()) == 0);
+      std::istringstream is3(t);
+      CHECK(enc::readVarint(is3) == v);
+    }
   }
   // distance.go:25-46
   CHECK(distanceFuncToName(EuclideanDistance).first == "euclidean" && distanceFuncToName(CosineDistance).second);
@@ -131,6 +154,29 @@ static void gpu_tests() {
       mismatched += !ok;
     }
     CHECK(mismatched == 0);
+    {  // Export (encode.go:133-174) is byte-identical to the oracle's; Import of that stream searches identically
+      std::ostringstream os;
+      Export(g, os);
+      const std::string mine = os.str();
+      std::vector<uint8_t> buf(mine.size() + 1024);
+      int64_t olen = ora_graph_export(og, 0.25, ef, buf.data(), (int64_t)buf.size());
+      CHECK(olen == (int64_t)mine.size() && std::memcmp(buf.data(), mine.data(), mine.size()) == 0);
+      auto g2 = NewGraph<int64_t>();
+      std::istringstream is(mine);
+      Import(g2, is);
+      CHECK(g2.M == M && g2.Ml == 0.25 && g2.EfSearch == ef && g2.Distance == EuclideanDistance && g2.Len() == n);
+      CHECK(g2.Topography() == g.Topography());
+      int diff = 0;
+      for (int i = 0; i < 20; i++) {
+        auto a = g.Search(qs[i], k), b = g2.Search(qs[i], k);
+        bool ok = a.size() == b.size();
+        for (size_t j = 0; ok && j < a.size(); j++) ok = a[j].Key == b[j].Key && a[j].Value == b[j].Value;
+        diff += !ok;
+      }
+      CHECK(diff == 0);
+      std::istringstream bad(std::string("\x04\x10"));  // version 2
+      CHECK(!error_of([&] { auto g3 = NewGraph<int64_t>(); Import(g3, bad); }).empty());
+    }
     // Delete through the host: the key leaves Lookup / Len, a second Delete reports false (graph.go:843-866)
     CHECK(g.Delete(nodes[5].Key) && !g.Delete(nodes[5].Key) && g.Len() == n - 1 && !g.Lookup(nodes[5].Key).second);
     CHECK(ora_graph_delete(og, nodes[5].Key) == 1);
