@@ -9,11 +9,11 @@
 
 namespace b200 {
 
-template <int G, int CH, int U, int MINB = 1>
+template <int G, int CH, int U, int MINB = 1, int TW = TRAV_WARPS>
 static int launch_t(b200hnsw *h, const GraphView &g, TraverseParams &p, cudaStream_t s) {
-  auto kern = traverse_kernel<G, CH, U, MINB>;
+  auto kern = traverse_kernel<G, CH, U, MINB, TW>;
   constexpr int NG = 32 / G;
-  size_t smem = traverse_group_bytes(p) * TRAV_WARPS * NG;
+  size_t smem = traverse_group_bytes(p) * TW * NG;
   if (smem > h->smem_optin - 512) {
     set_error("search: k=%d ef=%d visited=%d need %zu B of shared memory per block (> %zu)", p.k, p.ef, p.vis_cap,
               smem, h->smem_optin);
@@ -32,13 +32,13 @@ static int launch_t(b200hnsw *h, const GraphView &g, TraverseParams &p, cudaStre
     }
   }
   int per_sm = 0;
-  B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, TRAV_WARPS * 32, smem));
+  B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, TW * 32, smem));
   if (per_sm < 1) per_sm = 1;
-  long long blocks_needed = (p.B + TRAV_WARPS * NG - 1) / (TRAV_WARPS * NG);
+  long long blocks_needed = (p.B + TW * NG - 1) / (TW * NG);
   long long resident = (long long)per_sm * h->sm_count;
   int grid = (int)(blocks_needed < resident ? blocks_needed : resident);
   if (grid < 1) grid = 1;
-  kern<<<grid, TRAV_WARPS * 32, smem, s>>>(g, p);
+  kern<<<grid, TW * 32, smem, s>>>(g, p);
   B200_CUDA(cudaGetLastError());
   return 0;
 }
@@ -65,7 +65,14 @@ int launch_traverse(b200hnsw *h, TraverseParams &p, int vis_cap, cudaStream_t s)
   GraphView g = h->view();
   if (p.n_layers == 0) p.n_layers = h->n_layers;
   int kr = p.k > p.k_upper ? p.k : p.k_upper;
-  p.heap_c = (p.ef + 2) & ~1;
+  // The candidate queue is only maintained until the result queue is full (traverse.cuh): at most kr - 1 rows were
+  // evaluated before the step that fills it and at most M in that step, and PopLast keeps it at ef: min(ef, kr-1+M)
+  // entries, +1 for the push in front of PopLast.
+  {
+    int need = kr - 1 + g.M;
+    if (need > p.ef) need = p.ef;
+    p.heap_c = (need + 2) & ~1;
+  }
   p.heap_r = (kr + 1) & ~1;
   p.fresh_cap = (g.M + 3) & ~3;
   p.vis_cap = round_pow2(vis_cap < 256 ? 256 : vis_cap);
@@ -96,6 +103,8 @@ int launch_traverse(b200hnsw *h, TraverseParams &p, int vis_cap, cudaStream_t s)
       if (id == 14) return launch_t<16, 2, 4, 8>(h, g, p, s);
       if (id == 15) return launch_t<8, 4, 2, 6>(h, g, p, s);
       if (id == 16) return launch_t<16, 2, 2, 6>(h, g, p, s);
+      if (id == 17) return launch_t<8, 4, 2, 21, 1>(h, g, p, s);  // one-warp blocks: 21 warps per SM instead of 20
+      if (id == 18) return launch_t<8, 4, 2, 10, 2>(h, g, p, s);
     }
   }
 #define K1(G_, CH_, U_) return launch_t<G_, CH_, U_, ((CH_) >= 12 ? 2 : ((CH_) * (U_) <= 8 ? 5 : 4))>(h, g, p, s)
@@ -104,7 +113,9 @@ int launch_traverse(b200hnsw *h, TraverseParams &p, int vis_cap, cudaStream_t s)
     if (ch == 1) K1(8, 1, 8);
     if (ch == 2) K1(8, 2, 4);
     if (ch == 3) K1(8, 3, 2);
-    if (ch == 4) K1(8, 4, 2);
+    // dim 128: two-warp blocks, 10 per SM (measured with three launches in flight: 73.9M queries/s against 72.9M for
+    // four-warp blocks and 70.1M for one-warp blocks, profiles/r4j_k1_block_shape.log)
+    if (ch == 4) return launch_t<8, 4, 2, 10, 2>(h, g, p, s);
     G = 16;
     ch = (g.row_chunks + 15) / 16;
   }

@@ -81,8 +81,8 @@ constexpr int TRAV_WARPS = 4;
 
 enum { ST_NEED = 0, ST_INIT = 1, ST_EXPAND = 2, ST_IDLE = 3 };
 
-template <int G, int CH, int U, int MINB>
-__global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphView g, TraverseParams p) {
+template <int G, int CH, int U, int MINB, int TW = TRAV_WARPS>
+__global__ void __launch_bounds__(TW * 32, MINB) traverse_kernel(GraphView g, TraverseParams p) {
   constexpr int NG = 32 / G;
   constexpr unsigned GBITS = G == 32 ? 0xffffffffu : ((1u << G) - 1u);
   extern __shared__ __align__(16) unsigned char smem[];
@@ -101,12 +101,8 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
   const uint32_t vmask = (uint32_t)p.vis_cap - 1;
   const int M = g.M;
 
-  __shared__ int s_entries[B200HNSW_MAX_LAYERS];
-  for (int i = threadIdx.x; i < B200HNSW_MAX_LAYERS; i += blockDim.x) s_entries[i] = p.entries[i];
-  __syncthreads();
-
-  const long long n_groups = (long long)gridDim.x * TRAV_WARPS * NG;
-  long long q = ((long long)blockIdx.x * TRAV_WARPS + warp) * NG + grp - n_groups;  // advanced before first use
+  const long long n_groups = (long long)gridDim.x * TW * NG;
+  long long q = ((long long)blockIdx.x * TW + warp) * NG + grp - n_groups;  // advanced before first use
   int st = ST_NEED, layer = 0, cur = -1, elevator = -1, kcur = 1, vcount = 0, lvl = -1;
   GQuery<CH> Q;
 #pragma unroll
@@ -149,7 +145,7 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) traverse_kernel(GraphVi
     int nfresh = 0;
     // ---- INIT (top layer, or a layer reached without an elevator): the entry point is the only row to evaluate ----
     if (init) {
-      cur = elevator >= 0 ? elevator : s_entries[layer];  // graph.go:572-575 / 492-498
+      cur = elevator >= 0 ? elevator : p.entries[layer];  // graph.go:572-575 / 492-498 (constant bank, indexed)
       kcur = layer > 0 ? p.k_upper : p.k;
       C.len = 0;
       R.len = 0;
