@@ -59,6 +59,7 @@ SYMBOLS = {
     "b200hnsw_set_entry": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32]),
     "b200hnsw_load": (C.c_int, [C.c_void_p, C.c_int64, f32p, i64p, i32p, C.c_int32, i32p, i64p, i32p, i64p, i32p]),
     "b200hnsw_get_rows": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, f32p, i64p, i32p]),
+    "b200hnsw_set_keys": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, i64p]),
     "b200hnsw_get_neighbors": (C.c_int, [C.c_void_p, C.c_int32, C.c_int64, C.c_int64, i32p, u8p]),
     "b200hnsw_search_batch": (C.c_int, [C.c_void_p, f32p, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32, i32p,
                                         i32p, f32p, i32p, C.POINTER(Stats)]),

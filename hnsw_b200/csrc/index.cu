@@ -393,6 +393,32 @@ int b200hnsw_get_rows(const b200hnsw_t *hc, int64_t first, int64_t count, float 
   return 0;
 }
 
+int b200hnsw_set_keys(b200hnsw_t *h, int64_t first, int64_t count, const int64_t *keys) {
+  if (!h || first < 0 || count < 0 || first + count > h->n || (count > 0 && !keys)) {
+    set_error("set_keys: range [%lld, +%lld) outside 0..%lld", (long long)first, (long long)count,
+              h ? (long long)h->n : 0LL);
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  if (count == 0) return 0;
+  // the new keys must order the rows exactly as the old ones do, or the lists (kept sorted by key) would no longer be
+  // in the reference's expansion order: checked on the range given (strictly, as keys are unique)
+  {
+    std::vector<int64_t> idx((size_t)count);
+    for (int64_t i = 0; i < count; i++) idx[(size_t)i] = i;
+    std::sort(idx.begin(), idx.end(), [&](int64_t a, int64_t b) { return h->h_keys[first + a] < h->h_keys[first + b]; });
+    for (int64_t i = 1; i < count; i++)
+      if (!(keys[idx[(size_t)i - 1]] < keys[idx[(size_t)i]])) {
+        set_error("set_keys: the new keys do not preserve the order of rows %lld and %lld",
+                  (long long)(first + idx[(size_t)i - 1]), (long long)(first + idx[(size_t)i]));
+        return B200HNSW_ERR_BAD_ARG;
+      }
+  }
+  B200_CUDA(cudaSetDevice(h->cfg.device));
+  B200_CUDA(cudaMemcpy(h->d.keys + first, keys, sizeof(int64_t) * (size_t)count, cudaMemcpyHostToDevice));
+  std::copy(keys, keys + count, h->h_keys.begin() + first);
+  return 0;
+}
+
 int b200hnsw_get_neighbors(const b200hnsw_t *hc, int32_t layer, int64_t first, int64_t count, int32_t *nbr,
                            uint8_t *member) {
   b200hnsw *h = const_cast<b200hnsw *>(hc);

@@ -84,6 +84,10 @@ def export_graph(g, w: BinaryIO) -> None:
         # the reference would write live nodes whose neighbour lists still name deleted keys (replenish re-links
         # isolated nodes, graph.go:172-219); Import turns those into nil neighbours.  Not reproduced.
         raise NotImplementedError("Export after Delete is not supported")
+    if getattr(getattr(g, "_codec", None), "kind", None) not in (None, "int"):
+        # encode.go:40-75 writes a string key length-prefixed and any other K through binary.Write; only the int form is
+        # restated here (and in the oracle)
+        raise NotImplementedError("Export is implemented for integer keys only")
     if g.Len() == 0:
         w.write(put_varint(0))
         return

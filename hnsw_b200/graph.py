@@ -20,6 +20,7 @@ import numpy as np
 
 from . import _lib
 from .distance import CosineDistance, EuclideanDistance, distanceFuncs, distanceFuncToName, metric_of
+from .keys import KeyCodec
 
 
 @dataclass
@@ -73,6 +74,7 @@ class Graph:
         self._row_of = {}                   # key -> row (live keys only)
         self._retired = set()               # keys removed by Delete
         self._vecs = np.zeros((0, 0), np.float32)  # host copy, grows by doubling
+        self._codec = KeyCodec()            # K (cmp.Ordered) -> the int64 the device orders neighbour lists by
         self.last_stats = None
 
     # ---- lifetime -------------------------------------------------------------------------------------------
@@ -91,6 +93,7 @@ class Graph:
             _lib.lib().b200hnsw_destroy(self._h)
             self._h = None
         self._keys, self._row_of, self._dim = [], {}, 0
+        self._codec = KeyCodec()
         self._retired = set()
         self._vecs = np.zeros((0, 0), np.float32)
 
@@ -192,8 +195,11 @@ class Graph:
         keys = []
         for nd in nodes:
             k = nd.Key
-            if not isinstance(k, (int, np.integer)):
-                raise TypeError("device path orders neighbours by int64 keys; non-integer keys are not supported")
+            self._codec.check(k)  # int, float, str or bytes, the same kind for the whole graph (Go: the type parameter K)
+            if isinstance(k, (int, np.integer)):
+                k = int(k)
+            elif isinstance(k, (float, np.floating)):
+                k = float(k)
             if k in self._row_of or k in keys:
                 # graph.go:1016-1024 isolates the old node in the middle of the insertion and then links the new
                 # one into maps keyed by the same key; lists keyed by row cannot hold that state
@@ -202,10 +208,24 @@ class Graph:
             if k in self._retired:
                 raise NotImplementedError(f"key {k} was deleted: its node can still be linked under that key "
                                           f"(graph.go:172-219 re-links isolated nodes); use a new key")
-            keys.append(int(k))
-        self._add_arrays(keys, np.stack(vecs), levels, metric)
+            keys.append(k)
+        if self._codec.kind == "int":
+            self._add_arrays(keys, np.stack(vecs), levels, metric)
+            return
+        # other ordered key types: the device sees order-preserving int64 codes (hnsw_b200/keys.py)
+        codes, respaced = self._codec.assign(keys)
+        try:
+            if respaced:  # a gap between codes ran out: every stored row gets its new code
+                allc = np.asarray([respaced[k] for k in self._keys], dtype=np.int64)
+                _lib.check(_lib.lib().b200hnsw_set_keys(self._h, 0, len(allc), allc.ctypes.data_as(_lib.i64p)))
+            self._add_arrays(codes, np.stack(vecs), levels, metric, user_keys=keys)
+        except BaseException:
+            self._codec.forget_new([k for k in keys if k not in self._row_of])  # nodes in front of a failing one are in
+            raise
 
-    def _add_arrays(self, keys, V, levels, metric, wave_max=0):
+    def _add_arrays(self, keys, V, levels, metric, wave_max=0, user_keys=None):
+        """keys: the int64 order keys the device gets; user_keys: what the host mirror stores for them (the same unless
+        K is not an integer type)."""
         lv = np.ascontiguousarray(levels, dtype=np.int32) if levels is not None else self._draw_levels(len(keys))
         V = np.ascontiguousarray(V, dtype=np.float32)
         K = np.ascontiguousarray(keys, dtype=np.int64)
@@ -216,7 +236,8 @@ class Graph:
         t0 = time.perf_counter()
         # the host mirror (keys, key -> row, vectors: what Search hands back as Node.Value) is filled while the device
         # call runs; the call does not hold the interpreter lock
-        mirror = threading.Thread(target=lambda: self._store_host(K.tolist(), V))
+        host_keys = list(user_keys) if user_keys is not None else K.tolist()
+        mirror = threading.Thread(target=lambda: self._store_host(host_keys, V))
         mirror.start()
         try:
             if wave_max and wave_max > 0:  # batched construction in waves (not the reference's sequential order)
@@ -252,6 +273,9 @@ class Graph:
         if vectors.shape[1] != dim0:
             raise ValueError(f"embedding dimension mismatch: {dim0} != {vectors.shape[1]}")
         metric = metric_of(self.Distance)
+        if self._codec.kind not in (None, "int"):
+            raise TypeError("add_arrays takes int64 keys; this graph's key type is " + self._codec.kind)
+        self._codec.kind = "int"
         self._ensure_device(dim0)
         if self.M > self._max_m:
             raise ValueError(f"M={self.M} exceeds the device list stride {self._max_m} fixed at the first Add")
@@ -264,8 +288,12 @@ class Graph:
         keys = list(keys)
         if self._h is None or _lib.lib().b200hnsw_layers(self._h) == 0 or not keys:
             return [False] * len(keys)
-        rows = np.array([self._row_of.get(k, -1) if isinstance(k, (int, np.integer)) else -1 for k in keys],
-                        dtype=np.int32)
+        def row_of(k):
+            try:
+                return self._row_of.get(k, -1)
+            except TypeError:  # unhashable: cannot be a key
+                return -1
+        rows = np.array([row_of(k) for k in keys], dtype=np.int32)
         out = np.zeros(len(keys), dtype=np.uint8)
         st = _lib.Stats()
         _lib.check(_lib.lib().b200hnsw_delete_batch(self._h, rows.ctypes.data_as(_lib.i32p), len(keys), self.M,
@@ -309,6 +337,8 @@ class Graph:
             levels.ctypes.data_as(_lib.i32p), nl, ent.ctypes.data_as(_lib.i32p) if ent is not None else None,
             sizes.ctypes.data_as(_lib.i64p), rows.ctypes.data_as(_lib.i32p), ptr.ctypes.data_as(_lib.i64p),
             nbr.ctypes.data_as(_lib.i32p)))
+        self._codec = KeyCodec()
+        self._codec.kind = "int"
         self._keys = [int(k) for k in keys]
         self._row_of = {k: i for i, k in enumerate(self._keys)}
         self._vecs = vectors.copy()

@@ -112,6 +112,11 @@ int b200hnsw_load(b200hnsw_t *h, int64_t n, const float *vectors, const int64_t 
 /* ---- Graph.Export (encode.go:133-174) / Analyzer: read the device graph back ------------------------------ */
 int b200hnsw_get_rows(const b200hnsw_t *h, int64_t first, int64_t count, float *vectors, int64_t *keys,
                       int32_t *levels);
+/* Replace the order keys of rows [first, first + count).  For hosts whose K is not an integer (string, float: any
+ * cmp.Ordered) and who map keys to order-preserving int64 codes: when the gaps between codes run out the host re-spaces
+ * them and tells the device.  The new keys must order the rows exactly as the old ones do (checked); nothing else
+ * changes.  A mutating call: serialise it with Add / Delete. */
+int b200hnsw_set_keys(b200hnsw_t *h, int64_t first, int64_t count, const int64_t *keys);
 /* neighbour rows of `count` rows starting at `first` in `layer`, padded with -1 to max_m per row; rows that are
  * not members of the layer get all -1 and member[i]=0. */
 int b200hnsw_get_neighbors(const b200hnsw_t *h, int32_t layer, int64_t first, int64_t count, int32_t *nbr,
