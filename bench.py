@@ -50,7 +50,7 @@ def parse_args():
     ap.add_argument("--ef", type=int, default=64)
     ap.add_argument("--k", type=int, default=10)
     ap.add_argument("--ml", type=float, default=0.25)
-    ap.add_argument("--wave-max", type=int, default=4096,
+    ap.add_argument("--wave-max", type=int, default=16384,
                     help="nodes per construction wave (b200hnsw_add_batch_waves); 0 = exact sequential Graph.Add")
     ap.add_argument("--pool", type=int, default=16, help="distinct query batches cycled through the steps")
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="target length of the cpu_baseline sample")

@@ -3,7 +3,7 @@ restatement of the same schedule (ora_graph_add_waves, all host threads): every 
 topography, the entries and the counters must be identical.  (tests/test_wave_add_gpu.py does this at sizes the oracle
 finishes in seconds; this is the same check at 1M rows, ~20 s of CPU.)  One JSON line on stdout.
 
-  python scripts/full_size_build_parity.py [N] [dim] [M] [ef]
+  python scripts/full_size_build_parity.py [N] [dim] [M] [ef] [wave_max]
 """
 import json
 import os
@@ -21,19 +21,20 @@ N = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000
 d = int(sys.argv[2]) if len(sys.argv) > 2 else 128
 M = int(sys.argv[3]) if len(sys.argv) > 3 else 16
 ef = int(sys.argv[4]) if len(sys.argv) > 4 else 64
+WM = int(sys.argv[5]) if len(sys.argv) > 5 else 4096
 oracle.build()
 X = synth_rows(N, d, 42)
 lv = draw_levels(N, 0.25, 44)
 keys = np.arange(N, dtype=np.int64)
 dg = hnsw_b200.Graph(M=M, Ml=0.25, EfSearch=ef, Distance=hnsw_b200.EuclideanDistance, capacity=N)
 t0 = time.perf_counter()
-dg.add_arrays(keys, X, lv, wave_max=4096)
+dg.add_arrays(keys, X, lv, wave_max=WM)
 dev_s = time.perf_counter() - t0
 dst = dict(dg.last_stats)
 cores = os.cpu_count() or 1
 og = oracle.Graph(d, M, oracle.EUCLIDEAN)
 t0 = time.perf_counter()
-og.add_waves(keys, X, lv, ef, 4096, n_threads=cores)
+og.add_waves(keys, X, lv, ef, WM, n_threads=cores)
 cpu_s = time.perf_counter() - t0
 same_topo = og.topography() == dg.Topography()
 same_entries = list(og.entries()) == list(dg.entries())
@@ -55,7 +56,7 @@ for l in range(og.n_layers):
 c = og.counters()
 ctr_equal = all(int(dst[k]) == int(c[k]) for k in ("dist_evals", "expansions", "nbr_reads", "evict_evals",
                                                    "replenish_evals", "evictions"))
-print(json.dumps({"workload": f"{N}x{d} L2 M={M} ef={ef}, waves <= 4096", "lists_compared": lists,
+print(json.dumps({"workload": f"{N}x{d} L2 M={M} ef={ef}, waves <= {WM}", "lists_compared": lists,
                   "lists_different": mism, "topography_equal": same_topo, "entries_equal": same_entries,
                   "counters_equal": ctr_equal, "topography": dg.Topography(),
                   "device_wall_s": dev_s, "device_kernel_s": dst["kernel_ms"] / 1e3,
