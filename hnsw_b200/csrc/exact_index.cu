@@ -284,6 +284,15 @@ static int exact_search_core(b200exact *x, const float *d_q, int64_t B, int k, i
                              int32_t *d_counts, cudaStream_t s) {
   g_last_cands = g_last_fallbacks = 0;
   g_last_path = 0;
+  // the scratch (and the tensor path's query workspace) belongs to one search at a time: order this call behind the
+  // previous one on the device, whatever stream that one ran on
+  if (!x->scratch_ev) B200_CUDA(cudaEventCreateWithFlags(&x->scratch_ev, cudaEventDisableTiming));
+  else B200_CUDA(cudaStreamWaitEvent(s, x->scratch_ev, 0));
+  struct Release {
+    b200exact *x;
+    cudaStream_t s;
+    ~Release() { cudaEventRecord(x->scratch_ev, s); }
+  } release{x, s};
   if (x->live == 0 || x->n == 0) {  // exact.go:65-67
     B200_CUDA(cudaMemsetAsync(d_counts, 0, sizeof(int32_t) * (size_t)B, s));
     B200_CUDA(cudaMemsetAsync(d_rows, 0xff, sizeof(int64_t) * (size_t)B * k, s));
@@ -402,6 +411,7 @@ void b200exact_destroy(b200exact_t *x) {
   cudaFree(x->d_scratch);
   cudaFree(x->d_maxn2);
   cudaFree(x->d_gemm_ws);
+  if (x->scratch_ev) cudaEventDestroy(x->scratch_ev);
   free(x->tmap_x);
   if (x->stream) cudaStreamDestroy(x->stream);
   delete x;

@@ -29,6 +29,9 @@ struct b200exact {
   void *d_gemm_ws = nullptr;         // query-side workspace of the tensor path
   size_t gemm_ws_bytes = 0;
   std::mutex mu;                     // searches share the scratch buffer: one at a time per index
+  // recorded on the caller's stream behind the last kernel of a search; the next search (possibly on another stream)
+  // waits for it before it touches d_scratch / d_gemm_ws, so two device-pointer calls in flight never share them
+  cudaEvent_t scratch_ev = nullptr;
   int reserve(size_t bytes);
   int ensure_capacity(int64_t rows);
 };

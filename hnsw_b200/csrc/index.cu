@@ -191,7 +191,10 @@ int b200hnsw_create(const b200hnsw_config *cfg, b200hnsw_t **out) {
   }
   int rc = h->ensure_capacity(cfg->capacity > 0 ? cfg->capacity : 1024, 1024, c->stream);
   if (!rc && cudaMalloc(&h->d_err_word, 64) != cudaSuccess) rc = B200HNSW_ERR_OOM;
-  if (!rc) cudaMemset(h->d_err_word, 0, 64);
+  if (!rc) {
+    cudaMemset(h->d_err_word, 0, 64);
+    h->d_row_flags = h->d_err_word + 8;
+  }
   h->release(c);
   if (rc) {
     b200hnsw_destroy(h);
@@ -312,8 +315,20 @@ int b200hnsw_load(b200hnsw_t *h, int64_t n, const float *vectors, const int64_t 
   }
   CallCtx *c = h->acquire();
   if (!c) return B200HNSW_ERR_CUDA;
+  // Load replaces the content: from here on the old graph is gone.  Whatever fails below leaves a consistent EMPTY
+  // graph (host mirrors and device agree), never a half-reset handle.
   h->n = 0;
   h->nU = 0;
+  h->n_layers = 0;
+  h->n_dead = 0;
+  h->h_keys.clear();
+  h->h_level.clear();
+  h->h_dead.clear();
+  h->h_upper_off.clear();
+  for (int l = 0; l < B200HNSW_MAX_LAYERS; l++) {
+    h->entry[l] = -1;
+    h->layer_size[l] = 0;
+  }
   int rc = h->ensure_capacity(n, nU, c->stream);
   if (rc) {
     h->release(c);
@@ -324,6 +339,8 @@ int b200hnsw_load(b200hnsw_t *h, int64_t n, const float *vectors, const int64_t 
     h->release(c);
     return code;
   };
+  if (cudaMemsetAsync(h->d_row_flags, 0, sizeof(int), s) != cudaSuccess) return fail(cuda_fail(cudaGetLastError(), "load"));
+  h->row_flags.store(0);
   // wipe the whole reserved area: later Adds rely on untouched rows being zero vectors / empty lists
   if (cudaMemsetAsync(h->d.vec, 0, sizeof(float) * (size_t)h->d.cap * rf, s) != cudaSuccess ||
       cudaMemsetAsync(h->d.adj0, 0xff, sizeof(int32_t) * (size_t)h->d.cap * M, s) != cudaSuccess ||
@@ -345,8 +362,7 @@ int b200hnsw_load(b200hnsw_t *h, int64_t n, const float *vectors, const int64_t 
   }
   if (h->d.dead && cudaMemsetAsync(h->d.dead, 0, (size_t)h->d.cap, s) != cudaSuccess)
     return fail(cuda_fail(cudaGetLastError(), "load: clearing the deleted flags"));
-  cudaError_t e = cudaStreamSynchronize(s);
-  if (e != cudaSuccess) return fail(cuda_fail(e, "load sync"));
+  if ((rc = h->flag_rows(0, n, s)) || (rc = h->refresh_row_flags(s))) return fail(rc);  // synchronises s
   h->n = n;
   h->nU = nU;
   h->n_layers = n_layers;
@@ -451,6 +467,21 @@ int b200hnsw_get_neighbors(const b200hnsw_t *hc, int32_t layer, int64_t first, i
   return 0;
 }
 
+int32_t b200hnsw_get_visited_capacity(const b200hnsw_t *h) { return h ? h->vis_hint.load() : 0; }
+int b200hnsw_set_visited_capacity(b200hnsw_t *h, int32_t entries) {
+  if (!h || entries < 256 || (entries & (entries - 1))) {
+    set_error("set_visited_capacity: %d is not a power of two >= 256", entries);
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  const int mx = max_visited_cap(h, 1, 1);
+  if (entries > mx) {
+    set_error("set_visited_capacity: %d exceeds what the device can give a traversal (%d)", entries, mx);
+    return B200HNSW_ERR_UNSUPPORTED;
+  }
+  h->vis_hint.store(entries);
+  return 0;
+}
+
 static int check_search_args(b200hnsw_t *h, int64_t B, int32_t k, int32_t ef, int32_t metric) {
   if (!h || B < 0) {
     set_error("search: bad handle or batch size");
@@ -488,7 +519,7 @@ int b200hnsw_search_batch_device(b200hnsw_t *h, const float *d_queries, int64_t 
   // d_counters is int64[8]: evals, expansions, nbr_reads, overflowed queries, error flag, 3 spare
   int *d_err = d_counters ? reinterpret_cast<int *>(d_counters + 4) : h->d_err_word;
   return launch_search(h, d_queries, B, k, ef, metric, mode, entries, d_out_rows, d_out_dists, d_out_counts,
-                       reinterpret_cast<unsigned long long *>(d_counters), d_err, h->vis_hint, s);
+                       reinterpret_cast<unsigned long long *>(d_counters), d_err, h->vis_hint.load(), s);
 }
 
 int b200hnsw_search_batch_segmented_device(b200hnsw_t *h, const float *d_queries, int64_t B, int32_t k, int32_t ef,
@@ -515,7 +546,7 @@ int b200hnsw_search_batch_segmented_device(b200hnsw_t *h, const float *d_queries
   }
   int *d_err = d_counters ? reinterpret_cast<int *>(d_counters + 4) : h->d_err_word;
   return launch_search(h, d_queries, B, k, ef, metric, mode, entries, d_packed, nullptr, nullptr,
-                       reinterpret_cast<unsigned long long *>(d_counters), d_err, h->vis_hint, s, seg_len, seg_stride);
+                       reinterpret_cast<unsigned long long *>(d_counters), d_err, h->vis_hint.load(), s, seg_len, seg_stride);
 }
 
 int b200hnsw_search_batch_scatter_device(b200hnsw_t *h, const float *d_queries, int64_t B, int32_t k, int32_t ef,
@@ -547,7 +578,7 @@ int b200hnsw_search_batch_scatter_device(b200hnsw_t *h, const float *d_queries, 
   int *d_err = d_counters ? reinterpret_cast<int *>(d_counters + 4) : h->d_err_word;
   // out_rows doubles as the "Search sink" marker of the kernel: any non-null value
   return launch_search(h, d_queries, B, k, ef, metric, mode, entries, seg_ptrs[0], nullptr, nullptr,
-                       reinterpret_cast<unsigned long long *>(d_counters), d_err, h->vis_hint, s, seg_len, 0, seg_ptrs,
+                       reinterpret_cast<unsigned long long *>(d_counters), d_err, h->vis_hint.load(), s, seg_len, 0, seg_ptrs,
                        n_seg);
 }
 
@@ -641,8 +672,19 @@ int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_
     staged = true;
   }
   // A layer search that visits more nodes than the shared-memory visited table holds fails loudly in the kernel;
-  // the whole batch is then redone with a table 4x the size (sticky for later calls), so results are always exact.
-  for (int vis = h->vis_hint;; vis *= 4) {
+  // the whole batch is then redone with a table 4x the size, so results are always exact.  The larger size becomes
+  // the handle's hint only AFTER a retry with it has succeeded, and never exceeds what the device can give a
+  // traversal: past that the call fails with B200HNSW_ERR_VISITED_OVERFLOW and leaves the handle as it was.
+  // Error 3 (NaN distances met with the short candidate queue, traverse.cuh) is retried once with the full queue.
+  int vis0 = h->vis_hint.load(), vis_max = max_visited_cap(h, k, ef);
+  if (mode == B200HNSW_MODE_EXTENDED) {  // the extended walk visits ~10x the nodes: its own default and its own ceiling
+    const int efk = ef > k ? ef : k;
+    vis_max = max_visited_cap_ext(h, efk);
+    vis0 = ext_visited_default(efk, h->M);
+    if (h->vis_hint_ext.load() > vis0) vis0 = h->vis_hint_ext.load();
+  }
+  int vis = vis0 < vis_max ? vis0 : vis_max, full_queue = 0;
+  for (;;) {
     if ((e = cudaMemsetAsync(d_ctr, 0, 64, s)) != cudaSuccess || (e = cudaEventRecord(c->ev0, s)) != cudaSuccess)
       return fail(cuda_fail(e, "search staging"));
     for (int ci = 0; ci < nchunk; ci++) {
@@ -655,7 +697,7 @@ int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_
                                           cudaMemcpyHostToDevice, sc)) != cudaSuccess)
         return fail(cuda_fail(e, "search staging"));
       rc = launch_search(h, d_q + q0 * dim, nq, k, ef, metric, mode, entries, d_rows + q0 * k, d_dists + q0 * k,
-                         d_cnt + q0, d_ctr, d_err, vis, sc);
+                         d_cnt + q0, d_ctr, d_err, vis, sc, 0, 0, nullptr, 0, full_queue);
       if (rc) return fail(rc);
       launches++;
       if (!direct_out &&
@@ -676,12 +718,24 @@ int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_
         (e = cudaMemcpyAsync((void *)ctr, d_ctr, 40, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
         (e = cudaStreamSynchronize(s)) != cudaSuccess)
       return fail(cuda_fail(e, "search kernel"));
-    if ((int)(ctr[4] & 0xffffffffu) == 0) break;
-    if (vis >= 16384) {
-      set_error("search: %llu queries overflowed the visited set (a layer search visited > %d nodes)", ctr[3], vis / 2);
+    const int err = (int)(ctr[4] & 0xffffffffu);
+    if (err == 0) break;
+    if (err == 3 && !full_queue) {  // the kernel writes the most recent code: an overflow may hide behind it, see below
+      full_queue = 1;
+      continue;
+    }
+    if (vis >= vis_max) {
+      set_error("search: %llu queries overflowed the visited set (a layer search visited > %d nodes, the largest table "
+                "this device can give a traversal)", ctr[3], vis / 2);
       return fail(B200HNSW_ERR_VISITED_OVERFLOW);
     }
-    h->vis_hint = vis * 4;
+    vis = vis * 4 < vis_max ? vis * 4 : vis_max;
+  }
+  if (vis > vis0) {  // sticky, but only now that a search with this table has succeeded; concurrent callers keep the largest
+    std::atomic<int> &hint = mode == B200HNSW_MODE_EXTENDED ? h->vis_hint_ext : h->vis_hint;
+    int cur = hint.load();
+    while (vis > cur && !hint.compare_exchange_weak(cur, vis)) {
+    }
   }
   if (stats) {
     stats->dist_evals = (int64_t)ctr[0];
@@ -695,7 +749,7 @@ int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_
     cudaEventElapsedTime(&kms, c->ev0, c->ev1);
     fprintf(stderr, "b200hnsw_search_batch slow call: total %.2f ms (context %.2f, queued at %.2f), device ev0..ev1 %.2f ms, "
                     "B=%lld chunks=%d visited table %d direct_out=%d\n", since(), w_acq, w_queued, kms, (long long)B,
-            nchunk, h->vis_hint, (int)direct_out);
+            nchunk, h->vis_hint.load(), (int)direct_out);
   }
   h->release(c);
   return 0;

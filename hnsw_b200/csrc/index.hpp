@@ -3,6 +3,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <cstdarg>
 #include <cstdint>
 #include <cstdio>
@@ -71,7 +72,16 @@ struct b200hnsw {
   std::vector<uint8_t> h_dead;
   int64_t n_dead = 0;
   int *d_err_word = nullptr;  // error flag for device-pointer calls that pass no counters
-  int vis_hint = 512;  // visited-table entries per traversal; raised (sticky) when a search overflows it
+  // visited-table entries per traversal; raised (sticky) only after a retry with the larger table has succeeded
+  std::atomic<int> vis_hint{512};
+  std::atomic<int> vis_hint_ext{0};  // the same for the extended mode (its walks visit ~10x the nodes; 0 = sized from ef)
+  // bit 0: some stored row has |x|^2 = 0, non-finite or outside [1e-18, 1e18] (NaN distances possible: traverse.cuh).
+  // d_row_flags is the device word the upload paths OR into (flag_rows); row_flags its host mirror, refreshed at the end
+  // of every mutating call.
+  int *d_row_flags = nullptr;
+  std::atomic<int> row_flags{0};
+  int flag_rows(int64_t first, int64_t count, cudaStream_t s);   // queue the scan of rows [first, first + count)
+  int refresh_row_flags(cudaStream_t s);                         // synchronises s
   int sm_count = 148;
   size_t smem_optin = 0;
   std::mutex pool_mu;
@@ -96,7 +106,13 @@ namespace b200 {
 int launch_search(b200hnsw *h, const float *d_queries, int64_t B, int k, int ef, int metric, int mode,
                   const int32_t *entries, int32_t *d_rows, float *d_dists, int32_t *d_counts,
                   unsigned long long *d_counters, int *d_error, int vis_cap, cudaStream_t s, int64_t seg_len = 0,
-                  int64_t seg_stride = 0, int32_t *const *seg_ptrs = nullptr, int n_seg_ptrs = 0);
+                  int64_t seg_stride = 0, int32_t *const *seg_ptrs = nullptr, int n_seg_ptrs = 0, int full_queue = 0);
+// largest visited table (entries, power of two) a traversal can be given on this device
+int max_visited_cap(const b200hnsw *h, int k, int ef);
 struct TraverseParams;
 int launch_traverse(b200hnsw *h, TraverseParams &p, int vis_cap, cudaStream_t s);
+// extended mode (traverse_ext.cuh): ef_upper = ef of the layers above 0 (1 for Search, EfSearch for Add)
+int launch_traverse_ext(b200hnsw *h, TraverseParams &p, int ef_upper, int vis_cap, cudaStream_t s);
+int ext_visited_default(int efk, int M);
+int max_visited_cap_ext(const b200hnsw *h, int efk_max);
 }  // namespace b200

@@ -644,6 +644,7 @@ extern "C" int b200hnsw_add_batch(b200hnsw_t *h, const float *vectors, const int
                            cudaMemcpyHostToDevice, s)) != cudaSuccess ||
       (e = cudaMemsetAsync(d_ctr, 0, 128, s)) != cudaSuccess)
     return fail(cuda_fail(e, "add staging"));
+  if ((rc = h->flag_rows(h->n, n, s))) return fail(rc);
   if ((e = cudaEventRecord(c->ev0, s)) != cudaSuccess) return fail(cuda_fail(e, "event"));
   int launches = 0;
   int n_layers = h->n_layers;
@@ -706,6 +707,7 @@ extern "C" int b200hnsw_add_batch(b200hnsw_t *h, const float *vectors, const int
       (e = cudaMemcpyAsync(ctr, d_ctr, sizeof ctr, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
       (e = cudaStreamSynchronize(s)) != cudaSuccess)
     return fail(cuda_fail(e, "add counters"));
+  if ((rc = h->refresh_row_flags(s))) return fail(rc);
   commit(n);
   if (stats) {
     stats->dist_evals = (int64_t)ctr[0];
@@ -736,26 +738,33 @@ extern "C" int b200hnsw_delete_batch(b200hnsw_t *h, const int32_t *rows, int64_t
   }
   if (out_deleted) memset(out_deleted, 0, (size_t)n);
   if (n == 0 || h->n_layers == 0) return 0;  // graph.go:847-849
+  // The new host state (deleted flags, layer sizes, entry points, the caller's []bool) is built in temporaries and
+  // committed only after the delete kernel has finished: a failure on the way leaves host and device agreeing.
   std::vector<int32_t> del, lev;
+  std::vector<uint8_t> t_dead(h->h_dead);
+  std::vector<uint8_t> t_out((size_t)n, 0);
+  int64_t t_size[B200HNSW_MAX_LAYERS];
+  int32_t t_entry[B200HNSW_MAX_LAYERS];
+  memcpy(t_size, h->layer_size, sizeof t_size);
+  memcpy(t_entry, h->entry, sizeof t_entry);
   for (int64_t i = 0; i < n; i++) {
     const int32_t r = rows[i];
-    if (r < 0 || r >= h->n || h->h_dead[(size_t)r]) continue;  // unknown key, or deleted earlier (in this batch too)
-    h->h_dead[(size_t)r] = 1;
-    h->n_dead++;
-    if (out_deleted) out_deleted[i] = 1;
+    if (r < 0 || r >= h->n || t_dead[(size_t)r]) continue;  // unknown key, or deleted earlier (in this batch too)
+    t_dead[(size_t)r] = 1;
+    t_out[(size_t)i] = 1;
     del.push_back(r);
     lev.push_back(h->h_level[(size_t)r]);
     for (int l = 0; l <= h->h_level[(size_t)r]; l++) {  // delete(layer.nodes, key)
-      h->layer_size[l]--;
-      if (h->entry[l] == r) {  // layer.entry(): the lowest live member row takes over (documented stand-in)
+      t_size[l]--;
+      if (t_entry[l] == r) {  // layer.entry(): the lowest live member row takes over (documented stand-in)
         int32_t en = -1;
-        if (h->layer_size[l] > 0)
+        if (t_size[l] > 0)
           for (int64_t x = 0; x < h->n; x++)
-            if (!h->h_dead[(size_t)x] && h->h_level[(size_t)x] >= l) {
+            if (!t_dead[(size_t)x] && h->h_level[(size_t)x] >= l) {
               en = (int32_t)x;
               break;
             }
-        h->entry[l] = en;
+        t_entry[l] = en;
       }
     }
   }
@@ -801,6 +810,11 @@ extern "C" int b200hnsw_delete_batch(b200hnsw_t *h, const int32_t *rows, int64_t
     stats->launches = 1;
     cudaEventElapsedTime(&stats->kernel_ms, c->ev0, c->ev1);
   }
+  h->h_dead.swap(t_dead);
+  h->n_dead += (int64_t)nd;
+  memcpy(h->layer_size, t_size, sizeof t_size);
+  memcpy(h->entry, t_entry, sizeof t_entry);
+  if (out_deleted) memcpy(out_deleted, t_out.data(), (size_t)n);
   h->release(c);
   return 0;
 }

@@ -19,6 +19,22 @@ __global__ void distance_pairs_kernel(const float4 *a, const float4 *b, long lon
   if (lane == 0) out[w] = d;
 }
 
+// One warp per row: |x|^2 (any summation order will do: the test is a coarse range check).  Rows whose squared norm is
+// zero, non-finite or outside [1e-18, 1e18] can produce NaN distances (distance.go:15-17: 0/0 under cosine; inf - inf).
+__global__ void flag_rows_kernel(const float4 *vec, long long first, long long count, int nchunks, int *flags) {
+  long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (w >= count) return;
+  const float4 *row = vec + (first + w) * nchunks;
+  float s = 0.f;
+  for (int c = lane; c < nchunks; c += 32) {
+    float4 v = row[c];
+    s += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+  }
+  for (int off = 16; off >= 1; off >>= 1) s += __shfl_xor_sync(FULL, s, off);
+  if (lane == 0 && !(s >= 1e-18f && s <= 1e18f)) atomicOr(flags, 1);
+}
+
 // ---- flags of the fused search + exchange (sharded.py P2PShardPipeline) -------------------------------------------------
 struct PeerFlagPtrs {
   int32_t *p[B200HNSW_MAX_PEERS];
@@ -44,6 +60,22 @@ __global__ void peer_wait_kernel(const int32_t *flags, int n, int value) {
 }  // namespace b200
 
 using namespace b200;
+
+int b200hnsw::flag_rows(int64_t first, int64_t count, cudaStream_t s) {
+  if (count <= 0) return 0;
+  const long long blocks = (count * 32 + 255) / 256;
+  flag_rows_kernel<<<(unsigned)blocks, 256, 0, s>>>(reinterpret_cast<const float4 *>(d.vec), first, count,
+                                                     row_floats / 4, d_row_flags);
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}
+int b200hnsw::refresh_row_flags(cudaStream_t s) {
+  int v = 0;
+  B200_CUDA(cudaMemcpyAsync(&v, d_row_flags, sizeof v, cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaStreamSynchronize(s));
+  row_flags.store(v);
+  return 0;
+}
 
 extern "C" int b200hnsw_peer_alloc(int32_t device, int64_t bytes, void **d_ptr, uint8_t handle[64]) {
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");

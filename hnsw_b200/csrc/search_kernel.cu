@@ -61,6 +61,14 @@ static int pick_group(int row_chunks) {
   return 32;
 }
 
+int max_visited_cap(const b200hnsw *h, int k, int ef) {
+  // one traversal per warp (G = 32), TRAV_WARPS warps per block, full-length queues
+  const size_t fixed = ((size_t)((ef + 2) & ~1) + (size_t)((k + 1) & ~1)) * 8 + (size_t)((h->M + 3) & ~3) * 4;
+  int cap = 256;
+  while ((fixed + (size_t)cap * 2 * 4) * TRAV_WARPS <= h->smem_optin - 512) cap *= 2;
+  return cap;
+}
+
 int launch_traverse(b200hnsw *h, TraverseParams &p, int vis_cap, cudaStream_t s) {
   GraphView g = h->view();
   if (p.n_layers == 0) p.n_layers = h->n_layers;
@@ -68,11 +76,17 @@ int launch_traverse(b200hnsw *h, TraverseParams &p, int vis_cap, cudaStream_t s)
   // The candidate queue is only maintained until the result queue is full (traverse.cuh): at most kr - 1 rows were
   // evaluated before the step that fills it and at most M in that step, and PopLast keeps it at ef: min(ef, kr-1+M)
   // entries, +1 for the push in front of PopLast.
+  // With NaN distances possible (rows flagged at Add time, or a retry after the kernel reported error 3) the queue is
+  // kept for the whole layer and needs its full ef + 1 entries.
   {
     int need = kr - 1 + g.M;
-    if (need > p.ef) need = p.ef;
+    if (need > p.ef || p.heap_c_full || (h->row_flags.load() & 1)) {
+      need = p.ef;
+      p.heap_c_full = 1;
+    }
     p.heap_c = (need + 2) & ~1;
   }
+  p.row_flags = h->d_row_flags;
   p.heap_r = (kr + 1) & ~1;
   p.fresh_cap = (g.M + 3) & ~3;
   p.vis_cap = round_pow2(vis_cap < 256 ? 256 : vis_cap);
@@ -141,10 +155,10 @@ int launch_traverse(b200hnsw *h, TraverseParams &p, int vis_cap, cudaStream_t s)
 int launch_search(b200hnsw *h, const float *d_queries, int64_t B, int k, int ef, int metric, int mode,
                   const int32_t *entries, int32_t *d_rows, float *d_dists, int32_t *d_counts,
                   unsigned long long *d_counters, int *d_error, int vis_cap, cudaStream_t s, int64_t seg_len,
-                  int64_t seg_stride, int32_t *const *seg_ptrs, int n_seg_ptrs) {
-  if (mode != B200HNSW_MODE_REFERENCE) {
-    set_error("search: mode %d not implemented yet", mode);
-    return B200HNSW_ERR_UNSUPPORTED;
+                  int64_t seg_stride, int32_t *const *seg_ptrs, int n_seg_ptrs, int full_queue) {
+  if (mode != B200HNSW_MODE_REFERENCE && mode != B200HNSW_MODE_EXTENDED) {
+    set_error("search: unknown mode %d", mode);
+    return B200HNSW_ERR_BAD_ARG;
   }
   TraverseParams p{};
   p.queries = d_queries;
@@ -166,7 +180,20 @@ int launch_search(b200hnsw *h, const float *d_queries, int64_t B, int k, int ef,
   p.counters = d_counters;
   p.error = d_error;
   p.dead = h->n_dead ? h->d.dead : nullptr;
+  p.heap_c_full = full_queue;
   p.n_layers = h->live_layers();  // layers Delete emptied at the top are passed through without an elevator
+  if (mode == B200HNSW_MODE_EXTENDED) {
+    // textbook layer search (traverse_ext.cuh): greedy k = ef = 1 descent on the upper layers, W of max(ef, k) on layer 0
+    const int efk = ef > k ? ef : k;
+    int want = ext_visited_default(efk, h->M);
+    const int mx = max_visited_cap_ext(h, efk);
+    if (want > mx) want = mx;
+    // the host-pointer call passes its own (retry-grown) size; device-pointer calls pass the reference mode's hint, which
+    // is smaller than `want` unless an extended retry raised vis_hint_ext
+    const int hint = h->vis_hint_ext.load();
+    if (hint > want) want = hint;
+    return launch_traverse_ext(h, p, 1, vis_cap > want ? vis_cap : want, s);
+  }
   return launch_traverse(h, p, vis_cap, s);
 }
 

@@ -52,6 +52,12 @@ struct TraverseParams {
   // wherever it runs out of registers, so they should cost one constant load, not a chain of multiplies)
   int group_bytes, off_r, off_fresh, off_vis;
   const uint8_t *dead;           // [rows] rows Delete removed from layer.nodes; null while nothing was deleted
+  // NaN distances (cosine against a zero-norm row, non-finite components) break the argument that lets the kernel stop
+  // maintaining the candidate queue once the result queue is full (Go's up()/down() never move an element past a NaN).
+  // *row_flags bit 0 = the slab holds a row whose |x|^2 is 0, non-finite or outside [1e-18, 1e18]; such graphs, and
+  // queries whose |q|^2 is outside [1e-20, 1e20] under cosine, keep the full Go-exact queue for the whole layer.
+  const int *row_flags;
+  int heap_c_full;               // the candidate queue has room for ef + 1 entries (else min(ef, k-1+M) + 1)
 };
 
 struct OutPtrs {
@@ -114,6 +120,8 @@ __global__ void __launch_bounds__(TW * 32, MINB) traverse_kernel(GraphView g, Tr
   int best_id = -1, r1 = 0;
   int imp_id = -1;      // leader: last row that improved on result.Min() in this step
   bool cfree = false;   // leader: the candidate queue is no longer needed on this layer (see the decision below)
+  const bool nan_rows = p.row_flags != nullptr && (__ldg(p.row_flags) & 1);
+  bool keepc = nan_rows;  // this traversal may meet NaN distances: never drop the candidate queue
 
 #ifdef B200_K1_TIMING
   long long tphase[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tlast = clock64();
@@ -136,12 +144,14 @@ __global__ void __launch_bounds__(TW * 32, MINB) traverse_kernel(GraphView g, Tr
         layer = p.n_layers - 1;
         elevator = -1;
         lvl = p.levels ? p.levels[q] : -1;
+        keepc = nan_rows || (p.metric != 0 && !(NQ.qq >= 1e-20f && NQ.qq <= 1e20f));
         st = ST_INIT;
       }
     }
     if (__all_sync(FULL, st == ST_IDLE)) break;
     const bool init = st == ST_INIT, expand = st == ST_EXPAND;
     bool improved = false;  // leader
+    bool cerr = false;      // leader: the candidate queue would outgrow its (short) allocation
     int nfresh = 0;
     // ---- INIT (top layer, or a layer reached without an elevator): the entry point is the only row to evaluate ----
     if (init) {
@@ -290,8 +300,12 @@ __global__ void __launch_bounds__(TW * 32, MINB) traverse_kernel(GraphView g, Tr
             }
           }
           if (!cfree) {
-            C.push(du, ids[u]);
-            if (C.len > p.ef) C.pop_last();  // graph.go:157-159
+            if (C.len >= p.heap_c) {
+              cerr = true;  // only with NaN distances in play and the short queue: reported, the host retries in full
+            } else {
+              C.push(du, ids[u]);
+              if (C.len > p.ef) C.pop_last();  // graph.go:157-159
+            }
           }
         }
       }
@@ -301,7 +315,8 @@ __global__ void __launch_bounds__(TW * 32, MINB) traverse_kernel(GraphView g, Tr
     if (init && nfresh > 0) vcount = 1;
     // ---- leader decides: next node, end of layer ---------------------------------------------------------------------
     int next = -1;
-    if (leader && (init || expand) && !overflow) {
+    const bool cfail = __shfl_sync(FULL, cerr, leader_lane);
+    if (leader && (init || expand) && !overflow && !cerr) {
       const int rl = kcur == 1 ? r1 : R.len;
       if (init) {
         if (nfresh > 0) next = cur;                                 // graph.go:125-127, first iteration
@@ -315,7 +330,8 @@ __global__ void __launch_bounds__(TW * 32, MINB) traverse_kernel(GraphView g, Tr
       // row is strictly below everything evaluated on this layer, so candidates.Push sifted it to the root, where
       // neither a later Push of the same step (strict <) nor PopLast (ef >= 1 keeps slot 0) can move it -- the next
       // Pop (graph.go:126) returns exactly the last improving row.  So the queue is not maintained any more.
-      if (rl >= kcur) cfree = true;
+      // With NaN distances possible the argument fails (a NaN can sit at the root after a Pop): keep the queue.
+      if (rl >= kcur && !keepc) cfree = true;
     }
     next = __shfl_sync(FULL, next, leader_lane);
     const int rlen = __shfl_sync(FULL, kcur == 1 ? r1 : R.len, leader_lane);
@@ -326,9 +342,9 @@ __global__ void __launch_bounds__(TW * 32, MINB) traverse_kernel(GraphView g, Tr
     bool chain = false;
     float elev_d = 0.f;
     if (init || expand) {
-      if (overflow) {
+      if (overflow || cfail) {
         if (leader) {
-          *p.error = 1;
+          *p.error = overflow ? 1 : 3;
           c_over++;
           if (p.out_rows) *search_out(p, q).count = -1;
           else p.slot_cnt[p.slot_off[q]] = -1;
@@ -402,7 +418,7 @@ __global__ void __launch_bounds__(TW * 32, MINB) traverse_kernel(GraphView g, Tr
       if (leader) {
         c_evals++;  // the reference evaluates the entry again; counted so E equals the oracle's
         C.len = 0;
-        cfree = kcur == 1;  // the result queue {entry} is already full
+        cfree = kcur == 1 && !keepc;  // the result queue {entry} is already full
         if (kcur == 1) {
           best_d = elev_d;
           best_id = elevator;

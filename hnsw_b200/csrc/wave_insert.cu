@@ -815,6 +815,8 @@ extern "C" int b200hnsw_add_batch_waves(b200hnsw_t *h, const float *vectors, con
     cudaError_t r = cudaMemcpy2DAsync(h->d.vec + (size_t)(h->n + cut[j]) * rf, sizeof(float) * rf,
                                       vectors + (size_t)cut[j] * dim, sizeof(float) * dim, sizeof(float) * dim,
                                       (size_t)(cut[j + 1] - cut[j]), cudaMemcpyHostToDevice, cs);
+    // rows that can yield NaN distances are flagged as they land (traverse.cuh reads the device word)
+    if (r == cudaSuccess && h->flag_rows(h->n + cut[j], cut[j + 1] - cut[j], cs)) r = cudaGetLastError();
     return r != cudaSuccess ? r : cudaEventRecord(c->sub_ev[j & 1], cs);
   };
   // the slab may have just been grown on s (ensure_capacity): the copy stream starts behind that
@@ -903,6 +905,7 @@ extern "C" int b200hnsw_add_batch_waves(b200hnsw_t *h, const float *vectors, con
       (e = cudaMemcpyAsync(wave_ctr, d_wave_ctr, sizeof wave_ctr, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
       (e = cudaStreamSynchronize(s)) != cudaSuccess)
     return fail(cuda_fail(e, "add_waves kernels"));
+  if ((rc = h->refresh_row_flags(s))) return fail(rc);
   // ---- commit the host mirrors for the waves that completed -----------------------------------------------------------
   int done_kernel_waves = wave_ctr[2];
   int64_t done_nodes = 0;
@@ -940,6 +943,14 @@ extern "C" int b200hnsw_add_batch_waves(b200hnsw_t *h, const float *vectors, con
     cudaEventElapsedTime(&stats->kernel_ms, c->ev0, c->ev1);
   }
   h->release(c);
+  if (err == 3) {
+    // rows that can yield NaN distances (zero norm under cosine, non-finite components) entered the graph with this
+    // batch and a later wave met them with the short candidate queue: the handle now knows (row_flags), so the caller
+    // adds the remaining nodes again and they run with the full queue
+    set_error("add_waves: rows with zero or non-finite norm entered the graph; %lld of %lld nodes were inserted, add the "
+              "rest again", (long long)done_nodes, (long long)n);
+    return B200HNSW_ERR_STATE;
+  }
   if (err || done_nodes != n) {
     set_error("add_waves: a layer search overflowed the visited set; %lld of %lld nodes were inserted",
               (long long)done_nodes, (long long)n);

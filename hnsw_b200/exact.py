@@ -81,7 +81,8 @@ class ExactIndex:
 
     def search_device(self, d_queries: int, B: int, k: int, d_rows: int, d_dists: int, d_counts: int,
                       stream: int = 0) -> None:
-        """Device-pointer search (rows int64 [B,k], dists f32 [B,k], counts i32 [B]) on `stream`; no host sync."""
+        """Device-pointer search (rows int64 [B,k], dists f32 [B,k], counts i32 [B]) on `stream`.  The scan path is
+        asynchronous; the tensor path synchronises the stream once inside the call (candidate-overflow check)."""
         _lib.check(_lib.lib().b200exact_search_batch_device(self._x, C.c_void_p(d_queries), B, k, C.c_void_p(d_rows),
                                                             C.c_void_p(d_dists), C.c_void_p(d_counts),
                                                             C.c_void_p(stream)))

@@ -185,7 +185,9 @@ class Graph:
             return
         metric = metric_of(self.Distance)
         vecs = [np.asarray(nd.Value, dtype=np.float32).reshape(-1) for nd in nodes]
-        dim0 = self._dim if self.Len() > 0 else len(vecs[0])
+        # graph.go:450-455 checks against Dims() (0 for an empty graph).  The device slab keeps its row width once it
+        # exists, so a graph whose nodes were all deleted still takes vectors of that width only.
+        dim0 = self._dim if self._h is not None else len(vecs[0])
         for v in vecs:
             if len(v) != dim0:  # graph.go:450-455
                 raise ValueError(f"embedding dimension mismatch: {dim0} != {len(v)}")
@@ -229,7 +231,6 @@ class Graph:
         lv = np.ascontiguousarray(levels, dtype=np.int32) if levels is not None else self._draw_levels(len(keys))
         V = np.ascontiguousarray(V, dtype=np.float32)
         K = np.ascontiguousarray(keys, dtype=np.int64)
-        st = _lib.Stats()
         L = _lib.lib()
         rows0 = int(L.b200hnsw_rows(self._h))
         n0 = len(self._keys)
@@ -237,27 +238,55 @@ class Graph:
         # the host mirror (keys, key -> row, vectors: what Search hands back as Node.Value) is filled while the device
         # call runs; the call does not hold the interpreter lock
         host_keys = list(user_keys) if user_keys is not None else K.tolist()
-        mirror = threading.Thread(target=lambda: self._store_host(host_keys, V))
+        mirror_err = []
+
+        def fill_mirror():
+            try:
+                self._store_host(host_keys, V)
+            except BaseException as e:  # a thread does not propagate exceptions: hand it to the caller
+                mirror_err.append(e)
+
+        mirror = threading.Thread(target=fill_mirror)
         mirror.start()
+        total = None
         try:
-            if wave_max and wave_max > 0:  # batched construction in waves (not the reference's sequential order)
-                _lib.check(L.b200hnsw_add_batch_waves(
-                    self._h, V.ctypes.data_as(_lib.f32p), K.ctypes.data_as(_lib.i64p), lv.ctypes.data_as(_lib.i32p),
-                    len(K), self.M, self.EfSearch, metric, int(wave_max), C.byref(st)))
-            else:
-                _lib.check(L.b200hnsw_add_batch(self._h, V.ctypes.data_as(_lib.f32p), K.ctypes.data_as(_lib.i64p),
-                                                lv.ctypes.data_as(_lib.i32p), len(K), self.M, self.EfSearch, metric,
-                                                C.byref(st)))
+            off = 0
+            while True:
+                st = _lib.Stats()
+                try:
+                    if wave_max and wave_max > 0:  # batched construction in waves (not the reference's sequential order)
+                        _lib.check(L.b200hnsw_add_batch_waves(
+                            self._h, V[off:].ctypes.data_as(_lib.f32p), K[off:].ctypes.data_as(_lib.i64p),
+                            lv[off:].ctypes.data_as(_lib.i32p), len(K) - off, self.M, self.EfSearch, metric,
+                            int(wave_max), C.byref(st)))
+                    else:
+                        _lib.check(L.b200hnsw_add_batch(
+                            self._h, V[off:].ctypes.data_as(_lib.f32p), K[off:].ctypes.data_as(_lib.i64p),
+                            lv[off:].ctypes.data_as(_lib.i32p), len(K) - off, self.M, self.EfSearch, metric,
+                            C.byref(st)))
+                except _lib.B200Error as e:
+                    done = int(L.b200hnsw_rows(self._h)) - rows0
+                    # rows that can yield NaN distances entered the graph with this batch: the handle now runs the full
+                    # candidate queue; the nodes that were not inserted go in again (include/b200hnsw.h)
+                    if e.code == _lib.ERR_STATE and "add the rest again" in str(e) and done > off:
+                        off = done
+                        continue
+                    raise
+                d = st.as_dict()
+                total = d if total is None else {k: total[k] + d[k] for k in d}
+                break
         except BaseException:
             mirror.join()
             done = int(L.b200hnsw_rows(self._h)) - rows0  # nodes in front of the failing one are in
             for key in self._keys[n0 + done:]:
-                del self._row_of[key]
+                self._row_of.pop(key, None)
             del self._keys[n0 + done:]
             raise
-        self.last_stats = st.as_dict()
+        self.last_stats = total
         self.last_stats["call_s"] = time.perf_counter() - t0  # wall time of the C call (staging + kernels)
         mirror.join()
+        if mirror_err:
+            raise mirror_err[0]
 
     def add_arrays(self, keys, vectors, levels: Optional[Sequence[int]] = None, wave_max: int = 0):
         """BatchAdd for array inputs (keys[n] int64, vectors[n, dim] float32): same semantics, no per-node objects.
@@ -269,7 +298,7 @@ class Graph:
             raise ValueError("keys and vectors must have the same length")
         if len(keys) == 0:
             return
-        dim0 = self._dim if self.Len() > 0 else vectors.shape[1]
+        dim0 = self._dim if self._h is not None else vectors.shape[1]  # see BatchAdd
         if vectors.shape[1] != dim0:
             raise ValueError(f"embedding dimension mismatch: {dim0} != {vectors.shape[1]}")
         metric = metric_of(self.Distance)

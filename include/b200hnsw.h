@@ -104,7 +104,8 @@ int b200hnsw_set_entry(b200hnsw_t *h, int32_t layer, int32_t row);
  *   layer_rows  : concatenated member rows, layer_sizes[l] per layer (layer 0 must list every row)
  *   layer_ptr   : concatenated offsets, layer_sizes[l]+1 per layer, each starting at 0 for its layer
  *   layer_nbr   : concatenated neighbour rows
- * Lists longer than max_m are rejected; lists are re-sorted by key on load. Replaces the current content. */
+ * Lists longer than max_m are rejected; lists are re-sorted by key on load. Replaces the current content; a load that
+ * fails after its arguments were accepted leaves an EMPTY graph (never a half-loaded one). */
 int b200hnsw_load(b200hnsw_t *h, int64_t n, const float *vectors, const int64_t *keys, const int32_t *levels,
                   int32_t n_layers, const int32_t *entries, const int64_t *layer_sizes, const int32_t *layer_rows,
                   const int64_t *layer_ptr, const int32_t *layer_nbr);
@@ -134,6 +135,15 @@ int b200hnsw_search_batch_device(b200hnsw_t *h, const float *d_queries, int64_t 
                                  int32_t metric, int32_t mode, const int32_t *entries, int32_t *d_out_rows,
                                  float *d_out_dists, int32_t *d_out_counts, int64_t *d_counters /*[8] or NULL*/,
                                  void *stream);
+
+/* Visited-set capacity (entries per traversal, a power of two >= 256).  The host-pointer call grows it by itself: a
+ * batch in which a layer search visits more than half the table is redone with a table 4x the size, and the larger size
+ * is kept for later calls once that retry has succeeded.  Device-pointer calls cannot retry (they are asynchronous):
+ * they report the overflow in d_counters[4] (1 = visited set, 3 = NaN distances met with the short candidate queue),
+ * mark the affected queries with count -1, and leave it to the caller to raise the capacity here and issue the batch
+ * again (hnsw_b200/sharded.py does).  set fails with B200HNSW_ERR_UNSUPPORTED past what the device can give. */
+int32_t b200hnsw_get_visited_capacity(const b200hnsw_t *h);
+int b200hnsw_set_visited_capacity(b200hnsw_t *h, int32_t entries);
 
 /* The same search writing a SEGMENTED result buffer for the multi-GPU all-to-all: queries are cut in runs of seg_len
  * (the share of one destination rank); run s writes, at d_packed + s * seg_stride (int32 elements),
@@ -228,6 +238,10 @@ int b200exact_remove(b200exact_t *x, const int64_t *rows, int64_t n);
  * row order (the reference's order among ties is Go map order, i.e. unspecified); out_counts = min(k, len). */
 int b200exact_search_batch(b200exact_t *x, const float *queries, int64_t B, int32_t k, int64_t *out_rows,
                            float *out_dists, int32_t *out_counts, b200hnsw_stats *stats);
+/* Device-pointer variant.  The scan path (small n or few queries) is asynchronous on `stream`; the tensor path
+ * synchronises `stream` ONCE inside the call (the host reads the per-query candidate counts and redoes, exactly, any
+ * query whose list overflowed) and queues the rest.  Calls in flight on different streams are ordered on the device
+ * where they share the index's scratch (an event recorded behind each call), so they never see each other's workspace. */
 int b200exact_search_batch_device(b200exact_t *x, const float *d_queries, int64_t B, int32_t k, int64_t *d_out_rows,
                                   float *d_out_dists, int32_t *d_out_counts, void *stream);
 

@@ -244,6 +244,22 @@ static void replenish(ora_graph *g, int layer, int32_t n, int m) {
   ora_heap_free(&cand);
 }
 
+/* order-preserving image of a distance for the extended mode's keys: ascending unsigned order == ascending float
+ * order; -0 is taken as +0, a NaN (any sign) as the canonical positive NaN, which sorts after +inf */
+static inline uint32_t ord_bits(float d) {
+  if (d != d) return 0x7fc00000u | 0x80000000u;
+  d = d + 0.0f;
+  uint32_t u;
+  memcpy(&u, &d, 4);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+static inline float ord_float(uint32_t o) {
+  uint32_t u = (o & 0x80000000u) ? (o & 0x7fffffffu) : ~o;
+  float d;
+  memcpy(&d, &u, 4);
+  return d;
+}
+
 /* ---- layerNode.search -- graph.go:94-170 ----------------------------------------------------- */
 static int layer_search(const ora_graph *g, visited_t *vis, ora_counters *ctr, int layer, int32_t entry, int k,
                         int ef, const float *target, int mode, int32_t *out_rows, float *out_dists) {
@@ -290,17 +306,35 @@ static int layer_search(const ora_graph *g, visited_t *vis, ora_counters *ctr, i
       if (!improved && res.len >= k) break; /* graph.go:164-166 */
     }
   } else {
-    /* ORA_MODE_EXTENDED: NOT the reference.  Textbook HNSW layer search (Malkov & Yashunin, Alg. 2):
-     * W is a true bounded max-set of size max(ef,k); stop when the nearest candidate is farther than
-     * the farthest element of W.  `res` is used as a max-heap by storing negated distances. */
+    /* ORA_MODE_EXTENDED: NOT the reference.  Textbook HNSW layer search (Malkov & Yashunin, Alg. 2), stated so
+     * that its result is a function of the graph and the query only (no heap-layout or arrival-order effects):
+     *
+     *   key(d, row) orders candidates by distance, ties by row; -0 counts as +0; a NaN distance never enters W
+     *   (the entry point is always taken, a NaN distance there sorts last).
+     *   W = the efk = max(ef, k) smallest keys among the nodes evaluated so far, each with an `expanded` flag.
+     *   Repeat: take the smallest unexpanded element of W, mark it, evaluate its unvisited neighbours, merge them
+     *   into W.  Stop when every element of W is expanded.  (Alg. 2's candidate queue C only ever adds elements
+     *   that are farther than W's worst at the time they leave W, and W's worst never grows, so "nearest element
+     *   of C, stop when it is farther than W's worst" visits exactly the unexpanded elements of W in key order.)
+     *   Result: the first min(k, |W|) elements of W, ascending.
+     * The device kernel (hnsw_b200/csrc/traverse_ext.cuh) implements the same statement and is held to it bit
+     * for bit, E / H / neighbour-read counters included. */
+    ora_heap_free(&cand);
+    ora_heap_free(&res);
     int efk = ef > k ? ef : k;
-    res.len = 0;
-    ora_heap_push(&res, -d0, entry);
-    while (cand.len > 0) {
-      float cd;
-      int32_t cur;
-      ora_heap_pop(&cand, &cd, &cur);
-      if (res.len >= efk && cd > -res.dist[0]) break;
+    uint64_t *W = (uint64_t *)malloc(sizeof(uint64_t) * (size_t)(efk + 1));
+    unsigned char *ex = (unsigned char *)malloc((size_t)(efk + 1));
+    int wn = 0;
+#define ORD_KEY(dv, rowv) ((((uint64_t)ord_bits(dv)) << 32) | (uint32_t)(rowv))
+    W[0] = ORD_KEY(d0, entry);
+    ex[0] = 0;
+    wn = 1;
+    for (;;) {
+      int ci = 0;
+      while (ci < wn && ex[ci]) ci++;
+      if (ci == wn) break;
+      ex[ci] = 1;
+      int32_t cur = (int32_t)(W[ci] & 0xffffffffu);
       int32_t *deg;
       int32_t *l = list_ptr(g, layer, cur, &deg);
       if (!l) continue;
@@ -312,25 +346,31 @@ static int layer_search(const ora_graph *g, visited_t *vis, ora_counters *ctr, i
         vis->stamp[nb] = vis->epoch;
         float d = gdist(g, g->metric, nb, target);
         ctr->dist_evals++;
-        if (res.len < efk || d < -res.dist[0]) {
-          ora_heap_push(&cand, d, nb);
-          ora_heap_push(&res, -d, nb);
-          if (res.len > efk) ora_heap_pop(&res, NULL, NULL);
+        if (d != d) continue;
+        uint64_t key = ORD_KEY(d, nb);
+        if (wn == efk) {
+          if (!(key < W[wn - 1])) continue;
+          wn--;
         }
+        int pos = wn;
+        while (pos > 0 && W[pos - 1] > key) {
+          W[pos] = W[pos - 1];
+          ex[pos] = ex[pos - 1];
+          pos--;
+        }
+        W[pos] = key;
+        ex[pos] = 0;
+        wn++;
       }
     }
-    /* emit the k nearest, ascending distance (ties: as popped) */
-    while (res.len > k) ora_heap_pop(&res, NULL, NULL);
-    int n = res.len;
-    for (int i = n - 1; i >= 0; i--) {
-      float d;
-      int32_t id;
-      ora_heap_pop(&res, &d, &id);
-      out_rows[i] = id;
-      out_dists[i] = -d;
+#undef ORD_KEY
+    int n = wn < k ? wn : k;
+    for (int i = 0; i < n; i++) {
+      out_rows[i] = (int32_t)(W[i] & 0xffffffffu);
+      out_dists[i] = ord_float((uint32_t)(W[i] >> 32));
     }
-    ora_heap_free(&cand);
-    ora_heap_free(&res);
+    free(W);
+    free(ex);
     return n;
   }
   int n = res.len; /* graph.go:169: Slice() = raw heap array */

@@ -12,7 +12,7 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 
-def _check(oracle, X, Q, k, metric, path):
+def _check(oracle, X, Q, k, metric, path, expect_no_fallback=True):
     import hnsw_b200
     os.environ["B200EXACT_PATH"] = path
     try:
@@ -22,6 +22,14 @@ def _check(oracle, X, Q, k, metric, path):
         ix.BatchAdd(list(range(half)), X[:half])
         ix.BatchAdd(list(range(half, len(X))), X[half:])
         rows, dists, counts = ix.search_rows(Q, k)
+        st = ix.last_stats
+        # the path that was asked for is the path that answered (launches: 1 = scan, 2 = tensor), and on the tensor
+        # path no query fell back to the scan (expansions = queries redone because their candidate list overflowed
+        # or came up short): a filter bug that sent every query to the scan would otherwise stay green
+        assert st["launches"] == {"scan": 1, "tensor": 2}[path], st
+        if path == "tensor" and expect_no_fallback:
+            assert st["expansions"] == 0, st
+            assert k <= st["dist_evals"] / len(Q) < 4096, st   # candidates per query: a real filter, not everything
         o_idx, o_d = oracle.exact_batch_search(X, Q, k, metric, n_threads=8)
         kk = min(k, len(X))
         assert (counts == kk).all()
