@@ -106,6 +106,8 @@ def lib():
     L.ora_graph_search.argtypes = [C.c_void_p, f32p, C.c_int, C.c_int, C.c_int, i32p, i32p, f32p]
     L.ora_graph_batch_search.argtypes = [C.c_void_p, f32p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, i32p, f32p,
                                          i32p, C.POINTER(Counters)]
+    L.ora_graph_batch_search_trace.argtypes = [C.c_void_p, f32p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, i32p,
+                                               f32p, i32p, C.POINTER(Counters), i32p, f32p, i64p, C.c_int64]
     L.ora_put_varint.restype = C.c_int
     L.ora_put_varint.argtypes = [u8p, C.c_int64]
     L.ora_get_varint.restype = C.c_int
@@ -359,6 +361,24 @@ class Graph:
                                       rows.ctypes.data_as(i32p), d.ctypes.data_as(f32p), cnt.ctypes.data_as(i32p),
                                       C.byref(c))
         return rows, d, cnt, c.as_dict()
+
+    def batch_search_trace(self, queries, k, ef, mode=MODE_REFERENCE, n_threads=1, trace_cap=1024):
+        """batch_search plus, per query, the rows it evaluated in evaluation order with this flavour's distances:
+        (rows, dists, counts, trace_rows[nq, cap], trace_dists[nq, cap], trace_len[nq])."""
+        q = np.ascontiguousarray(queries, dtype=np.float32)
+        nq = q.shape[0]
+        rows = np.full((nq, k), -1, dtype=np.int32)
+        d = np.full((nq, k), np.nan, dtype=np.float32)
+        cnt = np.zeros(nq, dtype=np.int32)
+        tr = np.full((nq, trace_cap), -1, dtype=np.int32)
+        td = np.full((nq, trace_cap), np.nan, dtype=np.float32)
+        tl = np.zeros(nq, dtype=np.int64)
+        c = Counters()
+        self.L.ora_graph_batch_search_trace(self.h, q.ctypes.data_as(f32p), nq, k, ef, mode, n_threads,
+                                            rows.ctypes.data_as(i32p), d.ctypes.data_as(f32p),
+                                            cnt.ctypes.data_as(i32p), C.byref(c), tr.ctypes.data_as(i32p),
+                                            td.ctypes.data_as(f32p), tl.ctypes.data_as(i64p), trace_cap)
+        return rows, d, cnt, tr, td, tl
 
     def export(self, ml, ef) -> bytes:
         n = self.L.ora_graph_export(self.h, ml, ef, None, 0)

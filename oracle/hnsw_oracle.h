@@ -115,6 +115,13 @@ void ora_graph_batch_search(ora_graph *g, const float *queries, int64_t nq, int 
                             int n_threads, int32_t *out_rows, float *out_dists, int32_t *out_counts,
                             ora_counters *total);
 
+/* the same, recording per query the rows it evaluated, in evaluation order, with the distances this flavour computed:
+ * trace_rows / trace_dists [nq][trace_cap], trace_len[nq] = evaluations made (> trace_cap: truncated) */
+void ora_graph_batch_search_trace(ora_graph *g, const float *queries, int64_t nq, int k, int ef, int mode,
+                                  int n_threads, int32_t *out_rows, float *out_dists, int32_t *out_counts,
+                                  ora_counters *total, int32_t *trace_rows, float *trace_dists, int64_t *trace_len,
+                                  int64_t trace_cap);
+
 /* ---- encode.go wire format v1 (int keys) ----------------------------------------------------- */
 int ora_put_varint(uint8_t *buf, int64_t v);                 /* binary.PutVarint  */
 int ora_get_varint(const uint8_t *buf, size_t len, int64_t *v); /* binary.ReadVarint; bytes used or <0 */

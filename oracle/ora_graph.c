@@ -47,6 +47,25 @@ typedef struct {
   int64_t cap;
 } visited_t;
 
+/* Evaluation trace of a search (rows in evaluation order with the distance this flavour computed): what the flavour
+ * divergence report compares.  Off unless a caller installs a buffer for its thread. */
+typedef struct {
+  int32_t *rows;
+  float *dists;
+  int64_t cap, n;
+} ora_trace;
+static __thread ora_trace *tls_trace;
+#define TRACE_EVAL(r, d)                                     \
+  do {                                                       \
+    if (tls_trace) {                                         \
+      if (tls_trace->n < tls_trace->cap) {                   \
+        tls_trace->rows[tls_trace->n] = (r);                 \
+        tls_trace->dists[tls_trace->n] = (d);                \
+      }                                                      \
+      tls_trace->n++;                                        \
+    }                                                        \
+  } while (0)
+
 ora_graph *ora_graph_new(int dim, int M, int metric, int flavor) {
   ora_graph *g = (ora_graph *)calloc(1, sizeof *g);
   g->dim = dim;
@@ -273,6 +292,7 @@ static int layer_search(const ora_graph *g, visited_t *vis, ora_counters *ctr, i
   }
   float d0 = gdist(g, g->metric, entry, target);
   ctr->dist_evals++;
+  TRACE_EVAL(entry, d0);
   ora_heap_push(&cand, d0, entry);           /* graph.go:109-114 */
   ora_heap_push(&res, cand.dist[0], cand.id[0]); /* graph.go:122 */
   vis->stamp[entry] = vis->epoch;            /* graph.go:123 */
@@ -293,6 +313,7 @@ static int layer_search(const ora_graph *g, visited_t *vis, ora_counters *ctr, i
         vis->stamp[nb] = vis->epoch;
         float d = gdist(g, g->metric, nb, target);
         ctr->dist_evals++;
+        TRACE_EVAL(nb, d);
         improved = improved || (res.len > 0 && d < res.dist[0]); /* graph.go:147 */
         if (res.len < k) {
           ora_heap_push(&res, d, nb);
@@ -346,6 +367,7 @@ static int layer_search(const ora_graph *g, visited_t *vis, ora_counters *ctr, i
         vis->stamp[nb] = vis->epoch;
         float d = gdist(g, g->metric, nb, target);
         ctr->dist_evals++;
+        TRACE_EVAL(nb, d);
         if (d != d) continue;
         uint64_t key = ORD_KEY(d, nb);
         if (wn == efk) {
@@ -429,6 +451,10 @@ typedef struct {
   float *out_dists;
   int32_t *out_counts;
   ora_counters ctr;
+  int32_t *trace_rows; /* [nq][trace_cap] or NULL */
+  float *trace_dists;
+  int64_t *trace_len;  /* [nq]: evaluations made (may exceed trace_cap: truncated) */
+  int64_t trace_cap;
 } bs_job;
 
 static void *bs_worker(void *arg) {
@@ -438,9 +464,21 @@ static void *bs_worker(void *arg) {
   v.stamp = (uint32_t *)calloc((size_t)(v.cap ? v.cap : 1), sizeof(uint32_t));
   v.epoch = 0;
   for (int64_t i = j->q0; i < j->q1; i++) {
+    ora_trace tr;
+    if (j->trace_rows) {
+      tr.rows = j->trace_rows + (size_t)i * j->trace_cap;
+      tr.dists = j->trace_dists + (size_t)i * j->trace_cap;
+      tr.cap = j->trace_cap;
+      tr.n = 0;
+      tls_trace = &tr;
+    }
     int n = graph_search(j->g, &v, &j->ctr, j->queries + (size_t)i * j->g->dim, j->k, j->ef, j->mode, NULL,
                          j->out_rows + (size_t)i * j->k, j->out_dists + (size_t)i * j->k);
     j->out_counts[i] = n;
+    if (j->trace_rows) {
+      j->trace_len[i] = tr.n;
+      tls_trace = NULL;
+    }
   }
   free(v.stamp);
   return NULL;
@@ -448,6 +486,15 @@ static void *bs_worker(void *arg) {
 
 void ora_graph_batch_search(ora_graph *g, const float *queries, int64_t nq, int k, int ef, int mode, int n_threads,
                             int32_t *out_rows, float *out_dists, int32_t *out_counts, ora_counters *total) {
+  ora_graph_batch_search_trace(g, queries, nq, k, ef, mode, n_threads, out_rows, out_dists, out_counts, total, NULL,
+                               NULL, NULL, 0);
+}
+
+/* the same, also recording per query the rows it evaluated, in order, with their distances (flavour report) */
+void ora_graph_batch_search_trace(ora_graph *g, const float *queries, int64_t nq, int k, int ef, int mode,
+                                  int n_threads, int32_t *out_rows, float *out_dists, int32_t *out_counts,
+                                  ora_counters *total, int32_t *trace_rows, float *trace_dists, int64_t *trace_len,
+                                  int64_t trace_cap) {
   if (n_threads < 1) n_threads = 1;
   if (n_threads > nq) n_threads = nq > 0 ? (int)nq : 1;
   bs_job *jobs = (bs_job *)calloc((size_t)n_threads, sizeof *jobs);
@@ -463,6 +510,10 @@ void ora_graph_batch_search(ora_graph *g, const float *queries, int64_t nq, int 
     jobs[t].out_rows = out_rows;
     jobs[t].out_dists = out_dists;
     jobs[t].out_counts = out_counts;
+    jobs[t].trace_rows = trace_rows;
+    jobs[t].trace_dists = trace_dists;
+    jobs[t].trace_len = trace_len;
+    jobs[t].trace_cap = trace_cap;
     if (n_threads == 1) bs_worker(&jobs[t]);
     else pthread_create(&th[t], NULL, bs_worker, &jobs[t]);
   }

@@ -4,7 +4,7 @@ oracle through them, and a failed or retried call must leave the handle usable."
 import numpy as np
 import pytest
 
-from util import build_oracle_graph, flatten_oracle
+from util import build_oracle_graph, flatten_oracle, same_float_bits
 
 pytestmark = pytest.mark.gpu
 
@@ -23,7 +23,7 @@ def _same(g, dg, Q, k, ef):
     d_rows, d_d, d_cnt = dg.search_rows(Q, k, ef)
     assert np.array_equal(o_cnt, d_cnt)
     assert np.array_equal(o_rows, d_rows)
-    assert np.array_equal(o_d.view(np.uint32), d_d.view(np.uint32))
+    assert same_float_bits(o_d, d_d)
     st = dg.last_stats
     assert (st["dist_evals"], st["expansions"], st["nbr_reads"]) == (
         o_ctr["dist_evals"], o_ctr["expansions"], o_ctr["nbr_reads"])

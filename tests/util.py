@@ -45,3 +45,15 @@ def recall_at_k(found_rows, truth_rows):
     for f, t in zip(found_rows, truth_rows):
         hits += len(set(int(x) for x in f if x >= 0) & set(int(x) for x in t))
     return hits / (k * len(truth_rows))
+
+
+def same_float_bits(a, b):
+    """Bit equality of two float32 arrays with every NaN counted as the same value: the sign and payload of a computed
+    NaN are the platform's (x86 0/0 = 0xFFC00000, CUDA 0x7FFFFFFF, arm64 0x7FC00000), not the algorithm's."""
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    b = np.ascontiguousarray(b, dtype=np.float32)
+    if a.shape != b.shape:
+        return False
+    ua = np.where(np.isnan(a), np.uint32(0x7FC00000), a.view(np.uint32))
+    ub = np.where(np.isnan(b), np.uint32(0x7FC00000), b.view(np.uint32))
+    return bool(np.array_equal(ua, ub))
