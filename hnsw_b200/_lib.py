@@ -73,6 +73,8 @@ SYMBOLS = {
     "b200hnsw_delete_batch": (C.c_int, [C.c_void_p, i32p, C.c_int64, C.c_int32, u8p, C.POINTER(Stats)]),
     "b200hnsw_is_deleted": (C.c_int32, [C.c_void_p, C.c_int32]),
     "b200hnsw_rows": (C.c_int64, [C.c_void_p]),
+    "b200hnsw_set_build_mode": (C.c_int, [C.c_void_p, C.c_int32]),
+    "b200hnsw_get_build_mode": (C.c_int32, [C.c_void_p]),
     "b200hnsw_get_visited_capacity": (C.c_int32, [C.c_void_p]),
     "b200hnsw_set_visited_capacity": (C.c_int, [C.c_void_p, C.c_int32]),
     "b200hnsw_merge_topk_device": (C.c_int, [C.c_int32, C.c_int32, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p,

@@ -467,6 +467,16 @@ int b200hnsw_get_neighbors(const b200hnsw_t *hc, int32_t layer, int64_t first, i
   return 0;
 }
 
+int b200hnsw_set_build_mode(b200hnsw_t *h, int32_t mode) {
+  if (!h || (mode != B200HNSW_MODE_REFERENCE && mode != B200HNSW_MODE_EXTENDED)) {
+    set_error("set_build_mode: unknown mode %d", mode);
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  h->build_mode = mode;
+  return 0;
+}
+int32_t b200hnsw_get_build_mode(const b200hnsw_t *h) { return h ? h->build_mode : 0; }
+
 int32_t b200hnsw_get_visited_capacity(const b200hnsw_t *h) { return h ? h->vis_hint.load() : 0; }
 int b200hnsw_set_visited_capacity(b200hnsw_t *h, int32_t entries) {
   if (!h || entries < 256 || (entries & (entries - 1))) {

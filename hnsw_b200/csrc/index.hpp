@@ -78,6 +78,7 @@ struct b200hnsw {
   // bit 0: some stored row has |x|^2 = 0, non-finite or outside [1e-18, 1e18] (NaN distances possible: traverse.cuh).
   // d_row_flags is the device word the upload paths OR into (flag_rows); row_flags its host mirror, refreshed at the end
   // of every mutating call.
+  int build_mode = 0;  // B200HNSW_MODE_*: the layer search the wave Add runs (b200hnsw_set_build_mode)
   int *d_row_flags = nullptr;
   std::atomic<int> row_flags{0};
   int flag_rows(int64_t first, int64_t count, cudaStream_t s);   // queue the scan of rows [first, first + count)

@@ -575,6 +575,11 @@ extern "C" int b200hnsw_add_batch(b200hnsw_t *h, const float *vectors, const int
     return B200HNSW_ERR_BAD_ARG;
   }
   if (n == 0) return 0;
+  if (h->build_mode != B200HNSW_MODE_REFERENCE) {
+    set_error("add: the extended build mode exists for the wave-batched Add only (b200hnsw_add_batch_waves); the "
+              "sequential Add is the reference's and uses the reference's layer search");
+    return B200HNSW_ERR_UNSUPPORTED;
+  }
   if (h->n + n > 0x7fffffffLL) {
     set_error("add: more than 2^31-1 rows");
     return B200HNSW_ERR_UNSUPPORTED;

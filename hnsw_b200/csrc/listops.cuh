@@ -32,19 +32,29 @@ __device__ __forceinline__ void warp_store_list(int32_t *lp, int M, const int *s
 // overwrite, graph.go:50).  Executed by one warp; the result is in l[].
 __device__ __forceinline__ int warp_sorted_insert(int *l, int deg, int x, const int64_t *keys, int lane) {
   long long kx = keys[x];
-  int pos = 0;
+  int pos = 0, eqpos = -1;
   bool present = false;
   for (int base = 0; base < deg; base += 32) {
     int i = base + lane;
     int v = i < deg ? l[i] : -1;
-    bool lt = false;
+    bool lt = false, eq = false;
     if (v >= 0) {
       present = present || (v == x);
-      lt = keys[v] < kx;
+      const long long kv = keys[v];
+      lt = kv < kx;
+      eq = kv == kx && v != x;  // another row under the same key: the stale row of a key that was deleted and added again
     }
     pos += __popc(__ballot_sync(FULL, lt));
+    const unsigned em = __ballot_sync(FULL, eq);
+    if (em && eqpos < 0) eqpos = base + __ffs(em) - 1;
   }
   if (__any_sync(FULL, present)) return deg;
+  if (eqpos >= 0) {  // n.neighbors[key] = newNode overwrites the entry the map holds under that key (graph.go:50)
+    __syncwarp();
+    if (lane == 0) l[eqpos] = x;
+    __syncwarp();
+    return deg;
+  }
   // shift right from the end (single pass, each lane moves its element after all have read)
   int moved[2];
   int cntm = 0;

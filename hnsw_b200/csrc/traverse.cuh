@@ -314,8 +314,8 @@ __global__ void __launch_bounds__(TW * 32, MINB) traverse_kernel(GraphView g, Tr
     if (leader) c_evals += nfresh;  // E: one per evaluated row
     if (init && nfresh > 0) vcount = 1;
     // ---- leader decides: next node, end of layer ---------------------------------------------------------------------
-    int next = -1;
-    const bool cfail = __shfl_sync(FULL, cerr, leader_lane);
+    int next = -1;  // leader: row to expand next; -1 = the layer ends; -2 = the short candidate queue would overflow
+    if (leader && cerr) next = -2;
     if (leader && (init || expand) && !overflow && !cerr) {
       const int rl = kcur == 1 ? r1 : R.len;
       if (init) {
@@ -334,6 +334,7 @@ __global__ void __launch_bounds__(TW * 32, MINB) traverse_kernel(GraphView g, Tr
       if (rl >= kcur && !keepc) cfree = true;
     }
     next = __shfl_sync(FULL, next, leader_lane);
+    const bool cfail = next == -2;
     const int rlen = __shfl_sync(FULL, kcur == 1 ? r1 : R.len, leader_lane);
     const int r0_id = __shfl_sync(FULL, best_id, leader_lane);    // k = 1 layers: the result itself
     const float r0_d = __shfl_sync(FULL, best_d, leader_lane);

@@ -15,8 +15,10 @@
 //   * the fresh rows are evaluated 32/G * U at a time: every group of G lanes takes U rows (16 B loads, every row of
 //     the round in flight before the first reduction; canonical-order arithmetic of gdist.cuh, so distances are the
 //     bits the oracle computes);
-//   * W is a sorted array of 64-bit keys (order-preserving distance bits << 32 | row, bit 31 = expanded) in shared
-//     memory; a new key is ranked by all lanes at once (ballot + popc) and the tail shifted by all lanes at once;
+//   * W is a sorted array of 64-bit keys (order-preserving distance bits << 32 | row, bit 31 = expanded) held in
+//     REGISTERS, EPL entries per lane (position p lives in lane p % 32, slot p / 32): a new key is ranked by all lanes
+//     at once (compare + ballot + popc per slot) and the tail moves up by one with a shuffle per slot -- no shared
+//     memory traffic and no serial section (v1 kept W in shared memory: 40 % of its instructions were this insertion);
 //   * the neighbour list of every row that enters W on layer 0 is prefetched into L2: it is the list a later
 //     expansion reads.
 // Bound: HBM gather (E rows of 4*dim bytes per traversal; E is ~10x the reference mode's and rows are shared far less
@@ -44,14 +46,12 @@ constexpr unsigned long long EXT_FLAG = 1ull << 31;            // expanded
 constexpr unsigned long long EXT_MASK = ~EXT_FLAG;             // compare keys with the flag removed
 
 struct ExtLayout {  // per-warp shared memory, in bytes
-  int w_off, fresh_off, vis_off, warp_bytes;
+  int fresh_off, vis_off, warp_bytes;
 };
-__host__ __device__ inline ExtLayout ext_layout(int efk_max, int M, int vis_cap) {
+__host__ __device__ inline ExtLayout ext_layout(int M, int vis_cap) {
   ExtLayout L;
-  L.w_off = 0;
-  int o = ((efk_max + 1 + 1) & ~1) * 8;
-  L.fresh_off = o;
-  o += ((M + 3) & ~3) * 4;
+  L.fresh_off = 0;
+  int o = ((M + 3) & ~3) * 4;
   o = (o + 15) & ~15;
   L.vis_off = o;
   o += vis_cap * 4;
@@ -59,30 +59,44 @@ __host__ __device__ inline ExtLayout ext_layout(int efk_max, int M, int vis_cap)
   return L;
 }
 
-template <int G, int CH, int U, int TW>
-__global__ void __launch_bounds__(TW * 32) traverse_ext_kernel(GraphView g, TraverseParams p, int ef_upper,
-                                                               int efk_max) {
+// W[idx] for a warp-uniform idx: slot idx / 32 of lane idx % 32.  The slot is picked by a binary tree of selects over
+// statically indexed registers (an equality chain `if (e == slot) v = w[e]` is folded back into an indexed load by the
+// compiler, which sends the whole array to local memory).
+template <int EPL>
+__device__ __forceinline__ unsigned long long ext_w_at(const unsigned long long (&w)[EPL], int idx) {
+  static_assert((EPL & (EPL - 1)) == 0, "EPL is a power of two");
+  unsigned long long t[EPL];
+#pragma unroll
+  for (int e = 0; e < EPL; e++) t[e] = w[e];
+  const int slot = idx >> 5;
+#pragma unroll
+  for (int stride = 1; stride < EPL; stride <<= 1) {
+#pragma unroll
+    for (int i = 0; i + stride < EPL; i += 2 * stride) t[i] = (slot & stride) ? t[i + stride] : t[i];
+  }
+  return __shfl_sync(FULL, t[0], idx & 31);
+}
+
+template <int G, int CH, int U, int EPL, int MINB>
+__global__ void __launch_bounds__(32, MINB) traverse_ext_kernel(GraphView g, TraverseParams p, int ef_upper) {
   constexpr int NG = 32 / G;
   constexpr int RPR = NG * U;  // rows per round
   static_assert(U <= G, "a group returns row u in lane u * (G / U)");
   extern __shared__ __align__(16) unsigned char smem[];
   const int lane = threadIdx.x & 31;
-  const int warp = threadIdx.x >> 5;
   const int gl = lane & (G - 1);
   const int grp = lane / G;
-  const ExtLayout lay = ext_layout(efk_max, g.M, p.vis_cap);
-  unsigned char *base = smem + (size_t)lay.warp_bytes * warp;
-  unsigned long long *W = reinterpret_cast<unsigned long long *>(base + lay.w_off);
-  int *fresh = reinterpret_cast<int *>(base + lay.fresh_off);
-  uint32_t *vtab = reinterpret_cast<uint32_t *>(base + lay.vis_off);
+  const ExtLayout lay = ext_layout(g.M, p.vis_cap);
+  int *fresh = reinterpret_cast<int *>(smem + lay.fresh_off);
+  uint32_t *vtab = reinterpret_cast<uint32_t *>(smem + lay.vis_off);
   const uint32_t vmask = (uint32_t)p.vis_cap - 1;
+  const int vlimit = (p.vis_cap >> 2) * 3;  // load factor 3/4: past it the layer search fails loudly
   const int M = g.M;
   const bool holder = (gl % (G / U)) == 0;  // this lane receives the distance of row gl / (G / U) of its group
   const int my_u = gl / (G / U);
 
   unsigned long long c_evals = 0, c_exp = 0, c_nbr = 0, c_over = 0;  // warp-uniform; lane 0 reports
-  const long long n_warps = (long long)gridDim.x * TW;
-  for (long long q = (long long)blockIdx.x * TW + warp; q < p.B; q += n_warps) {
+  for (long long q = blockIdx.x; q < p.B; q += gridDim.x) {
     GQuery<CH> Q;
     group_load_query<G, CH>(Q, p.queries + q * p.q_stride, true, g.dim, g.row_chunks, gl);
     const int lvl = p.levels ? p.levels[q] : -1;
@@ -90,6 +104,7 @@ __global__ void __launch_bounds__(TW * 32) traverse_ext_kernel(GraphView g, Trav
     unsigned long long elev_key = 0;
     bool failed = false, empty_out = false;
     int wn = 0;
+    unsigned long long w[EPL];
     for (int layer = p.n_layers - 1; layer >= 0 && !failed; layer--) {
       const int kcur = layer > 0 ? p.k_upper : p.k;
       const int efl = layer > 0 ? ef_upper : p.ef;
@@ -108,40 +123,43 @@ __global__ void __launch_bounds__(TW * 32) traverse_ext_kernel(GraphView g, Trav
         uint4 *t4 = reinterpret_cast<uint4 *>(vtab);
         for (uint32_t i = lane; i < (vmask + 1) / 4; i += 32) t4[i] = e4;
       }
-      __syncwarp();
+#pragma unroll
+      for (int e = 0; e < EPL; e++) w[e] = ~0ull;
+      unsigned long long k0;
       if (elevator >= 0) {
         // the elevator's distance to this query was computed on the layer above (same row, same arithmetic)
-        if (lane == 0) W[0] = elev_key & EXT_MASK;
+        k0 = elev_key & EXT_MASK;
       } else {
         int ids[U];
 #pragma unroll
         for (int u = 0; u < U; u++) ids[u] = (u == 0 && grp == 0) ? cur : -1;
         const float d = group_distances<G, CH, U>(g.vec, g.row_chunks, ids, Q, p.metric, gl);
         const float d0 = __shfl_sync(FULL, d, 0);
-        if (lane == 0) W[0] = ((unsigned long long)ext_ord_bits(d0) << 32) | (unsigned)cur;
+        k0 = ((unsigned long long)ext_ord_bits(d0) << 32) | (unsigned)cur;
       }
+      if (lane == 0) w[0] = k0;
       c_evals++;  // the oracle evaluates the entry on every layer
+      __syncwarp();
       if (lane == 0) vtab[(((uint32_t)cur * 2654435761u) >> 7) & vmask] = (uint32_t)cur;
       wn = 1;
-      int vcount = 1, cursor = 0;
+      int vcount = 1;
       __syncwarp();
       // ---- the walk -----------------------------------------------------------------------------------------------------
       for (;;) {
         int ci = -1;
-        for (int b0 = cursor & ~31; b0 < wn; b0 += 32) {
-          const int i = b0 + lane;
-          const bool un = i < wn && i >= cursor && !(W[i] & EXT_FLAG);
-          const unsigned m = __ballot_sync(FULL, un);
-          if (m) {
-            ci = b0 + __ffs(m) - 1;
-            break;
+#pragma unroll
+        for (int e = 0; e < EPL; e++) {
+          if (ci < 0 && e * 32 < wn) {
+            const bool un = e * 32 + lane < wn && !(w[e] & EXT_FLAG);
+            const unsigned m = __ballot_sync(FULL, un);
+            if (m) ci = e * 32 + __ffs(m) - 1;
           }
         }
         if (ci < 0) break;
-        cur = (int)(W[ci] & 0x7fffffffull);
-        __syncwarp();
-        if (lane == 0) W[ci] |= EXT_FLAG;
-        cursor = ci + 1;
+        cur = (int)(ext_w_at<EPL>(w, ci) & 0x7fffffffull);
+#pragma unroll
+        for (int e = 0; e < EPL; e++)  // every slot is rewritten (see ext_w_at on why not `if (e == slot)`)
+          w[e] |= (unsigned long long)(lane == (ci & 31) && ((ci >> 5) ^ e) == 0) << 31;
         c_exp++;
         const int32_t *list = layer == 0 ? g.adj0 + (size_t)cur * M
                                          : g.adjU + ((size_t)g.upper_off[cur] + (layer - 1)) * M;
@@ -177,12 +195,13 @@ __global__ void __launch_bounds__(TW * 32) traverse_ext_kernel(GraphView g, Trav
           if (__popc(gv) != in_range) break;  // lists are -1 padded at the end
         }
         vcount += nfresh;
-        if (vcount * 2 > (int)vmask) {  // load factor > 1/2: fail loudly, never approximate
+        if (vcount > vlimit) {  // fail loudly, never approximate: the host retries with a larger table
           failed = true;
           break;
         }
         __syncwarp();
         c_evals += nfresh;
+        unsigned long long worst = wn == efk ? (ext_w_at<EPL>(w, wn - 1) & EXT_MASK) : ~0ull;
         for (int r0 = 0; r0 < nfresh; r0 += RPR) {
           int ids[U];
 #pragma unroll
@@ -199,40 +218,36 @@ __global__ void __launch_bounds__(TW * 32) traverse_ext_kernel(GraphView g, Trav
           bool want = false;
           if (holder && my_id >= 0 && d == d) {
             mykey = ((unsigned long long)ext_ord_bits(d) << 32) | (unsigned)my_id;
-            want = wn < efk || mykey < (W[wn - 1] & EXT_MASK);
+            want = mykey < worst;
           }
           unsigned m = __ballot_sync(FULL, want);
           while (m) {
             const int src = __ffs(m) - 1;
             m &= m - 1;
             const unsigned long long key = __shfl_sync(FULL, mykey, src);
-            if (wn == efk) {
-              if (!(key < (W[wn - 1] & EXT_MASK))) continue;  // W's worst moved since the ballot
-              wn--;
-              __syncwarp();
-            }
+            if (!(key < worst)) continue;  // W's worst moved since the ballot
             int pos = 0;
-            for (int b0 = 0; b0 < wn; b0 += 32) {
-              const int i = b0 + lane;
-              const bool lt = i < wn && (W[i] & EXT_MASK) < key;
-              pos += __popc(__ballot_sync(FULL, lt));
+#pragma unroll
+            for (int e = 0; e < EPL; e++)
+              if (e * 32 < wn) pos += __popc(__ballot_sync(FULL, (w[e] & EXT_MASK) < key));
+            // [pos, wn) moves up by one, top slot first; the element pushed past efk - 1 falls off
+#pragma unroll
+            for (int e = EPL - 1; e >= 0; e--) {
+              if (e * 32 + 31 >= pos && e * 32 <= wn) {
+                unsigned long long up = __shfl_up_sync(FULL, w[e], 1);
+                if (e > 0) {
+                  const unsigned long long carry = __shfl_sync(FULL, w[e - 1], 31);
+                  if (lane == 0) up = carry;
+                }
+                const int pp = e * 32 + lane;
+                if (pp > pos) w[e] = up;
+                else if (pp == pos) w[e] = key;
+                if (pp >= efk) w[e] = ~0ull;
+              }
             }
-            for (int b0 = (wn - 1) & ~31; b0 >= (pos & ~31) && wn > 0; b0 -= 32) {  // shift [pos, wn) up, top chunk first
-              const int i = b0 + lane;
-              const bool mv = i >= pos && i < wn;
-              unsigned long long v = 0;
-              if (mv) v = W[i];
-              __syncwarp();
-              if (mv) W[i + 1] = v;
-              __syncwarp();
-            }
-            if (lane == 0) {
-              W[pos] = key;
-              if (layer == 0) prefetch_l2(g.adj0 + (size_t)(key & 0x7fffffffull) * M);
-            }
-            wn++;
-            if (pos < cursor) cursor = pos;
-            __syncwarp();
+            if (wn < efk) wn++;
+            if (wn == efk) worst = ext_w_at<EPL>(w, wn - 1) & EXT_MASK;
+            if (lane == 0 && layer == 0) prefetch_l2(g.adj0 + (size_t)(key & 0x7fffffffull) * M);
           }
         }
       }
@@ -241,14 +256,17 @@ __global__ void __launch_bounds__(TW * 32) traverse_ext_kernel(GraphView g, Trav
       const int rlen = wn < kcur ? wn : kcur;
       if (!p.out_rows && layer <= lvl) {  // Add sink (graph.go:510): this layer takes the new node
         const long long slot = p.slot_off[q] + layer;
-        for (int i = lane; i < rlen; i += 32) {
-          const unsigned long long kv = W[i];
-          p.slot_rows[slot * p.sink_stride + i] = (int)(kv & 0x7fffffffull);
-          p.slot_dists[slot * p.sink_stride + i] = ext_ord_float((uint32_t)(kv >> 32));
+#pragma unroll
+        for (int e = 0; e < EPL; e++) {
+          const int i = e * 32 + lane;
+          if (i < rlen) {
+            p.slot_rows[slot * p.sink_stride + i] = (int)(w[e] & 0x7fffffffull);
+            p.slot_dists[slot * p.sink_stride + i] = ext_ord_float((uint32_t)(w[e] >> 32));
+          }
         }
         if (lane == 0) p.slot_cnt[slot] = rlen;
       }
-      elev_key = W[0];
+      elev_key = __shfl_sync(FULL, w[0], 0);
       elevator = (int)(elev_key & 0x7fffffffull);
       __syncwarp();
     }
@@ -263,11 +281,14 @@ __global__ void __launch_bounds__(TW * 32) traverse_ext_kernel(GraphView g, Trav
     } else if (p.out_rows) {
       const int rlen = empty_out ? 0 : (wn < p.k ? wn : p.k);
       const OutPtrs o = search_out(p, q);
-      for (int i = lane; i < p.k; i += 32) {
-        const bool ok = i < rlen;
-        const unsigned long long kv = ok ? W[i] : 0;
-        o.rows[i] = ok ? (int)(kv & 0x7fffffffull) : -1;
-        o.dists[i] = ok ? ext_ord_float((uint32_t)(kv >> 32)) : __int_as_float(0x7fc00000);
+#pragma unroll
+      for (int e = 0; e < EPL; e++) {
+        const int i = e * 32 + lane;
+        if (i < p.k) {
+          const bool ok = i < rlen;
+          o.rows[i] = ok ? (int)(w[e] & 0x7fffffffull) : -1;
+          o.dists[i] = ok ? ext_ord_float((uint32_t)(w[e] >> 32)) : __int_as_float(0x7fc00000);
+        }
       }
       if (lane == 0) *o.count = rlen;
     } else if (empty_out && lane == 0) {

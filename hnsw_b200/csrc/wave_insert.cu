@@ -884,7 +884,15 @@ extern "C" int b200hnsw_add_batch_waves(b200hnsw_t *h, const float *vectors, con
       h->n_layers = n_layers_before;
       return fail(cuda_fail(e, "add_waves memset"));
     }
-    rc = launch_traverse(h, t, 1024, s);
+    if (h->build_mode == B200HNSW_MODE_EXTENDED) {
+      // NOT the reference: the textbook layer search (traverse_ext.cuh) with k = M, ef = EfSearch on every layer
+      const int efk = ef > m ? ef : m;
+      int vis = ext_visited_default(efk, M);
+      const int mx = max_visited_cap_ext(h, efk);
+      rc = launch_traverse_ext(h, t, ef, vis < mx ? vis : mx, s);
+    } else {
+      rc = launch_traverse(h, t, 1024, s);
+    }
     h->n_layers = n_layers_before;
     if (rc) return fail(rc);
     p.first_row = (int)(h->n + wv.start);

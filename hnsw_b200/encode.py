@@ -73,40 +73,78 @@ def _read_exact(r, n):
     return b
 
 
+# ---- keys on the wire (encode.go:66-126): K = int -> binary.PutVarint (zig-zag); K = string -> varint length + bytes;
+#      any other fixed-size K -> binary.Write little endian.  The Python host has int (Go int), float (Go float64) and
+#      str / bytes (Go string) keys.
+def _key_kind(g, key_type=None):
+    if key_type is not None:
+        return {int: "int", float: "float", str: "str", bytes: "bytes"}[key_type]
+    kind = getattr(getattr(g, "_codec", None), "kind", None)
+    if kind in (None, "int"):
+        return "int"
+    if kind == "float":
+        return "float"
+    sample = next((k for k in g._keys), "")
+    return "bytes" if isinstance(sample, bytes) else "str"
+
+
+def put_key(kind: str, key) -> bytes:
+    if kind == "int":
+        return put_varint(int(key))
+    if kind == "float":
+        return struct.pack("<d", float(key))
+    b = key if isinstance(key, bytes) else str(key).encode("utf-8")
+    return put_varint(len(b)) + b
+
+
+def read_key(kind: str, r: BinaryIO):
+    if kind == "int":
+        return read_varint(r)
+    if kind == "float":
+        return struct.unpack("<d", _read_exact(r, 8))[0]
+    n = read_varint(r)
+    b = _read_exact(r, n)
+    return b if kind == "bytes" else b.decode("utf-8")
+
+
 def export_graph(g, w: BinaryIO) -> None:
-    """Graph.Export (encode.go:133-174): reads the lists back from the device."""
+    """Graph.Export (encode.go:133-174): reads the lists back from the device.  Like the reference it writes what
+    layer.nodes holds: after a Delete that is the live nodes only, whose neighbour lists can still name deleted keys
+    (isolate leaves one-way links and replenish re-links isolated nodes, graph.go:172-235); Import resolves those to nil
+    neighbours, which Search skips (encode.go:253-257, graph.go:140-143)."""
     name, ok = distanceFuncToName(g.Distance)
     if not ok:
         raise ValueError(f"distance function {g.Distance!r} must be registered with RegisterDistanceFunc")
     w.write(put_varint(encodingVersion) + put_varint(g.M) + struct.pack("<d", float(g.Ml)) +
             put_varint(g.EfSearch) + put_string(name))
-    if getattr(g, "_retired", None):
-        # the reference would write live nodes whose neighbour lists still name deleted keys (replenish re-links
-        # isolated nodes, graph.go:172-219); Import turns those into nil neighbours.  Not reproduced.
-        raise NotImplementedError("Export after Delete is not supported")
-    if getattr(getattr(g, "_codec", None), "kind", None) not in (None, "int"):
-        # encode.go:40-75 writes a string key length-prefixed and any other K through binary.Write; only the int form is
-        # restated here (and in the oracle)
-        raise NotImplementedError("Export is implemented for integer keys only")
-    if g.Len() == 0:
+    if g._h is None or not g._keys:
         w.write(put_varint(0))
         return
-    vec, keys, levels, layer_lists, _ = g.dump_flat()
+    kind = _key_kind(g)
+    vec, codes, levels, layer_lists, _ = g.dump_flat()
     w.write(put_varint(len(layer_lists)))
     dim_prefix = put_varint(vec.shape[1])
-    key_bytes = [put_varint(int(k)) for k in keys]
+    user_keys = g._keys                      # row -> the caller's key (the device orders rows by `codes`)
+    key_bytes = [put_key(kind, k) for k in user_keys]
+    live = np.zeros(len(user_keys), dtype=bool)
+    live[np.fromiter(g._row_of.values(), dtype=np.int64, count=len(g._row_of))] = True
     for rows, ptr, nbr in layer_lists:
-        w.write(put_varint(len(rows)))
-        order = np.argsort(keys[rows], kind="stable")
+        member = live[rows]
+        w.write(put_varint(int(member.sum())))
+        order = np.argsort(codes[rows], kind="stable")
         for i in order:
+            if not member[i]:
+                continue  # delete(layer.nodes, key): the node is no longer in the map Export iterates
             r = int(rows[i])
             nb = nbr[ptr[i]:ptr[i + 1]]  # already in ascending key order on the device
             w.write(key_bytes[r] + dim_prefix + vec[r].astype("<f4").tobytes() + put_varint(len(nb)) +
                     b"".join(key_bytes[int(t)] for t in nb))
 
 
-def import_graph(g, r: BinaryIO) -> None:
-    """Graph.Import (encode.go:180-262): parameters come from the stream, the content replaces the graph's."""
+def import_graph(g, r: BinaryIO, key_type=None) -> None:
+    """Graph.Import (encode.go:180-262): parameters come from the stream, the content replaces the graph's.  key_type
+    (int, float, str, bytes) plays Go's type parameter K; default: the graph's current key type, else int."""
+    kind = _key_kind(g, key_type)
     version = read_varint(r)
     m = read_varint(r)
     ml = struct.unpack("<d", _read_exact(r, 8))[0]
@@ -124,11 +162,11 @@ def import_graph(g, r: BinaryIO) -> None:
         n_nodes = read_varint(r)
         members = []
         for _ in range(n_nodes):
-            key = read_varint(r)
+            key = read_key(kind, r)
             ln = read_varint(r)
             v = np.frombuffer(_read_exact(r, 4 * ln), dtype="<f4")
             nn = read_varint(r)
-            nbk = [read_varint(r) for _ in range(nn)]
+            nbk = [read_key(kind, r) for _ in range(nn)]
             if l == 0:
                 if key in row_of:
                     continue  # a Go map keeps one node per key
@@ -164,8 +202,7 @@ def import_graph(g, r: BinaryIO) -> None:
             if lv >= l and row not in have:
                 raise ValueError(f"key {keys[row]} is in layer {lv} but not in layer {l}: not a graph Export wrote")
     g.close()
-    g.load_flat(np.stack(vecs).astype(np.float32), np.asarray(keys, np.int64), np.asarray(levels, np.int32),
-                layer_lists)
+    g.load_flat(np.stack(vecs).astype(np.float32), keys, np.asarray(levels, np.int32), layer_lists)
 
 
 class SavedGraph:

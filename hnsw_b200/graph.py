@@ -86,6 +86,8 @@ class Graph:
         h = C.c_void_p()
         _lib.check(_lib.lib().b200hnsw_create(C.byref(cfg), C.byref(h)))
         self._h, self._dim, self._max_m = h, dim, cfg.max_m
+        if getattr(self, "_build_mode", 0):
+            _lib.check(_lib.lib().b200hnsw_set_build_mode(self._h, self._build_mode))
         self._vecs = np.zeros((max(self._capacity, 1024), dim), np.float32)
 
     def close(self):
@@ -194,33 +196,70 @@ class Graph:
         self._ensure_device(dim0)
         if self.M > self._max_m:
             raise ValueError(f"M={self.M} exceeds the device list stride {self._max_m} fixed at the first Add")
-        keys = []
-        for nd in nodes:
-            k = nd.Key
+        lv_all = None if levels is None else list(levels)
+        if lv_all is not None and len(lv_all) != len(nodes):
+            raise ValueError("levels must have one entry per node")
+
+        def norm(k):
             self._codec.check(k)  # int, float, str or bytes, the same kind for the whole graph (Go: the type parameter K)
             if isinstance(k, (int, np.integer)):
-                k = int(k)
-            elif isinstance(k, (float, np.floating)):
-                k = float(k)
-            if k in self._row_of or k in keys:
-                # graph.go:1016-1024 isolates the old node in the middle of the insertion and then links the new
-                # one into maps keyed by the same key; lists keyed by row cannot hold that state
-                raise NotImplementedError(f"key {k} already present: replacing a node in place is not supported; "
-                                          f"Delete it and Add it under a new key")
-            if k in self._retired:
-                raise NotImplementedError(f"key {k} was deleted: its node can still be linked under that key "
-                                          f"(graph.go:172-219 re-links isolated nodes); use a new key")
-            keys.append(k)
+                return int(k)
+            if isinstance(k, (float, np.floating)):
+                return float(k)
+            return k
+
+        def flush(lo, hi):
+            if hi > lo:
+                self._add_keys([norm(nd.Key) for nd in nodes[lo:hi]], np.stack(vecs[lo:hi]),
+                               None if lv_all is None else lv_all[lo:hi], metric)
+
+        start, seen = 0, set()
+        for i, nd in enumerate(nodes):
+            k = norm(nd.Key)
+            if k in self._row_of or k in seen:
+                # "If another node with the same ID exists, it is replaced" (graph.go:435-436).  The reference deletes the
+                # old node in the middle of the insertion (graph.go:1016-1024: isolate on every layer) and then fails its
+                # own invariant -- Len() did not grow -- so BatchAdd returns "node not added" with the replacement done and
+                # the rest of the batch untouched (graph.go:1035-1037); Add deadlocks (graph.go:438 + 844).  Here: the
+                # nodes in front go in, the old node is deleted, the new one inserted under a new row, and the
+                # reference's error is raised.  The delete runs in FRONT of the insertion, not inside it, so the link
+                # structure is Delete + Add's, which is what the doc comment promises.
+                flush(start, i)
+                self.BatchDelete([k])
+                self._retired.discard(k)
+                flush(i, i + 1)
+                if self.REPLACE_RAISES:
+                    raise ValueError("node not added")
+                start = i + 1
+                seen = set()
+                continue
+            seen.add(k)
+        flush(start, len(nodes))
+
+    # graph.go:1035-1037: the reference's BatchAdd reports "node not added" after replacing an existing key; False makes
+    # the replacement silent and lets the batch continue
+    REPLACE_RAISES = True
+
+    def _add_keys(self, keys, V, levels, metric):
+        """Insert nodes whose keys are new to the graph (or were deleted: the key then names the new row; lists that
+        still hold the deleted row under that key are overwritten when the new row reaches them, as the Go map would)."""
+        for k in keys:
+            self._retired.discard(k)
         if self._codec.kind == "int":
-            self._add_arrays(keys, np.stack(vecs), levels, metric)
+            self._add_arrays(keys, V, levels, metric)
             return
         # other ordered key types: the device sees order-preserving int64 codes (hnsw_b200/keys.py)
-        codes, respaced = self._codec.assign(keys)
+        known = getattr(self._codec, "_code_of", {})
+        fresh = [k for k in keys if self._codec.kind != "ordered" or k not in known]
+        fresh_codes, respaced = self._codec.assign(fresh)
+        by_key = dict(zip(fresh, (int(c) for c in fresh_codes)))
+        # a key that was deleted and comes back keeps its code (the codec never forgets a stored key)
+        codes = np.asarray([by_key[k] if k in by_key else (respaced or known)[k] for k in keys], dtype=np.int64)
         try:
             if respaced:  # a gap between codes ran out: every stored row gets its new code
                 allc = np.asarray([respaced[k] for k in self._keys], dtype=np.int64)
                 _lib.check(_lib.lib().b200hnsw_set_keys(self._h, 0, len(allc), allc.ctypes.data_as(_lib.i64p)))
-            self._add_arrays(codes, np.stack(vecs), levels, metric, user_keys=keys)
+            self._add_arrays(codes, V, levels, metric, user_keys=keys)
         except BaseException:
             self._codec.forget_new([k for k in keys if k not in self._row_of])  # nodes in front of a failing one are in
             raise
@@ -338,6 +377,12 @@ class Graph:
         """graph.go:843-866."""
         return self.BatchDelete([key])[0]
 
+    def set_build_mode(self, mode: int):
+        """NOT the reference: the layer search the wave-batched Add runs (_lib.MODE_EXTENDED = textbook search)."""
+        self._build_mode = int(mode)
+        if self._h is not None:
+            _lib.check(_lib.lib().b200hnsw_set_build_mode(self._h, self._build_mode))
+
     def Add(self, *nodes: Node, levels: Optional[Sequence[int]] = None):
         """graph.go:437-531 (same body as BatchAdd; the reference's Add deadlocks on a duplicate key, F9)."""
         self.BatchAdd(nodes, levels=levels)
@@ -348,7 +393,19 @@ class Graph:
         vectors = np.ascontiguousarray(vectors, dtype=np.float32)
         n, dim = vectors.shape
         self._ensure_device(dim)
-        keys = np.ascontiguousarray(keys, dtype=np.int64)
+        user_keys = list(keys)
+        codec = KeyCodec()
+        for k in user_keys[:1]:
+            codec.check(k)
+        if codec.kind in (None, "int"):
+            codec.kind = "int"
+            user_keys = [int(k) for k in user_keys]
+            keys = np.ascontiguousarray(user_keys, dtype=np.int64)
+        else:  # float / str / bytes keys: the device orders rows by order-preserving codes (hnsw_b200/keys.py)
+            if codec.kind == "float":
+                user_keys = [float(k) for k in user_keys]
+            codes, _ = codec.assign(user_keys)
+            keys = np.ascontiguousarray(codes, dtype=np.int64)
         levels = np.ascontiguousarray(levels, dtype=np.int32)
         nl = len(layer_lists)
         sizes = np.array([len(r) for r, _, _ in layer_lists], dtype=np.int64)
@@ -366,10 +423,10 @@ class Graph:
             levels.ctypes.data_as(_lib.i32p), nl, ent.ctypes.data_as(_lib.i32p) if ent is not None else None,
             sizes.ctypes.data_as(_lib.i64p), rows.ctypes.data_as(_lib.i32p), ptr.ctypes.data_as(_lib.i64p),
             nbr.ctypes.data_as(_lib.i32p)))
-        self._codec = KeyCodec()
-        self._codec.kind = "int"
-        self._keys = [int(k) for k in keys]
+        self._codec = codec
+        self._keys = user_keys
         self._row_of = {k: i for i, k in enumerate(self._keys)}
+        self._retired = set()
         self._vecs = vectors.copy()
 
     def entries(self) -> np.ndarray:
@@ -520,9 +577,10 @@ class Graph:
         from .encode import export_graph
         export_graph(self, w)
 
-    def Import(self, r) -> None:
+    def Import(self, r, key_type=None) -> None:
+        """key_type (int, float, str, bytes) plays Go's type parameter K when the graph has no keys yet."""
         from .encode import import_graph
-        import_graph(self, r)
+        import_graph(self, r, key_type)
 
     def ParallelSearch(self, near, k: int, numWorkers: int = 0) -> List[Node]:
         """graph.go:631-826.  The reference's goroutine fan-out consumes results in channel-arrival order

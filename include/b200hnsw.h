@@ -199,6 +199,14 @@ int b200hnsw_add_batch_waves(b200hnsw_t *h, const float *vectors, const int64_t 
                              int64_t n, int32_t m, int32_t ef, int32_t metric, int64_t wave_max,
                              b200hnsw_stats *stats);
 
+/* NOT the reference: which layer search the wave-batched Add runs.  B200HNSW_MODE_EXTENDED = the textbook search
+ * (k = M, ef = EfSearch on every layer) instead of layerNode.search; links are still made by the reference's rule
+ * (link to every result, evict the farthest, replenish with cosine).  The graph it builds answers extended-mode
+ * searches with markedly higher recall; its oracle is ora_graph_add_waves with the same build mode.
+ * b200hnsw_add_batch (the reference's sequential Add) refuses to run while the mode is set. */
+int b200hnsw_set_build_mode(b200hnsw_t *h, int32_t mode);
+int32_t b200hnsw_get_build_mode(const b200hnsw_t *h);
+
 /* Graph.Delete / Graph.BatchDelete (graph.go:843-895; layerNode.isolate graph.go:223-235, replenish graph.go:172-219).
  * rows[i] = the row the caller's key map holds for the i-th key, -1 for an unknown key; processed in call order, as
  * the reference's loop under one lock.  out_deleted[i] (may be null) mirrors the reference's []bool: 1 iff the row

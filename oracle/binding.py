@@ -94,6 +94,8 @@ def lib():
     L.ora_graph_dead_count.argtypes = [C.c_void_p]
     L.ora_graph_set_build_mode.restype = None
     L.ora_graph_set_build_mode.argtypes = [C.c_void_p, C.c_int]
+    L.ora_graph_set_flavor.restype = None
+    L.ora_graph_set_flavor.argtypes = [C.c_void_p, C.c_int]
     L.ora_graph_add.restype = C.c_int32
     L.ora_graph_add.argtypes = [C.c_void_p, C.c_int64, f32p, C.c_int, C.c_int]
     L.ora_graph_put_node.restype = C.c_int32
@@ -249,6 +251,11 @@ class Graph:
 
     def set_build_mode(self, mode):
         self.L.ora_graph_set_build_mode(self.h, int(mode))
+
+    def set_flavor(self, flavor):
+        """Summation order used from now on (one loaded graph searched under several orders)."""
+        self.L.ora_graph_set_flavor(self.h, int(flavor))
+        self.flavor = int(flavor)
 
     def add_many(self, keys, vecs, levels, ef):
         vecs = np.ascontiguousarray(vecs, dtype=np.float32)

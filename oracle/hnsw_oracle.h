@@ -99,6 +99,7 @@ int ora_graph_is_dead(const ora_graph *g, int32_t row);
 int64_t ora_graph_dead_count(const ora_graph *g);
 /* NOT the reference: layer search used by Add (ORA_MODE_*); only for the recall study in scripts/ext_recall.py */
 void ora_graph_set_build_mode(ora_graph *g, int mode);
+void ora_graph_set_flavor(ora_graph *g, int flavor);
 /* Hand-build a layer (test fixtures such as graph_test.go:27-74): appends a node to `layer`
  * without linking; ora_graph_link adds a one-directional edge. */
 int32_t ora_graph_put_node(ora_graph *g, int64_t key, const float *vec, int level);

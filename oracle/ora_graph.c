@@ -177,6 +177,11 @@ static void list_insert(const ora_graph *g, int32_t *l, int32_t *deg, int32_t ro
   if (list_find(g, l, *deg, row) >= 0) return; /* map overwrite: length unchanged */
   int i = *deg;
   int64_t k = g->key[row];
+  for (int j = 0; j < *deg; j++)
+    if (g->key[l[j]] == k) { /* another row under the same key (a key deleted and added again): the map entry is */
+      l[j] = row;            /* overwritten, n.neighbors[key] = newNode (graph.go:50) */
+      return;
+    }
   while (i > 0 && g->key[l[i - 1]] > k) {
     l[i] = l[i - 1];
     i--;
@@ -593,6 +598,8 @@ int32_t ora_graph_add(ora_graph *g, int64_t key, const float *vec, int level, in
  * link it again one-way through a neighbour that still lists it, traversals walk through it and can return it;
  * only layer.nodes lookups (entry point, elevator, Lookup, Len) stop seeing it. */
 void ora_graph_set_build_mode(ora_graph *g, int mode) { g->build_mode = mode; }
+/* summation order used from now on (the flavour report and the bench search one loaded graph under several) */
+void ora_graph_set_flavor(ora_graph *g, int flavor) { g->flavor = flavor; }
 int ora_graph_is_dead(const ora_graph *g, int32_t row) { return row >= 0 && row < g->n ? g->dead[row] : -1; }
 int64_t ora_graph_dead_count(const ora_graph *g) { return g->n_dead; }
 

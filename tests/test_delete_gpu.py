@@ -86,11 +86,7 @@ def test_add_after_delete_matches_oracle(oracle):
     # a batch that fails in the middle keeps the nodes in front of the failing one, like the per-node loop
     if bad:
         assert dg.Len() == n - 100 + ok
-    # replacing a key in place and re-using a deleted key are refused
-    with pytest.raises(NotImplementedError):
-        dg.Add(hnsw_b200.Node(int(keys[0]) if int(keys[0]) not in victims else int(keys[1]), X[0]), levels=[0])
-    with pytest.raises(NotImplementedError):
-        dg.Add(hnsw_b200.Node(victims[0], X[0]), levels=[0])
+    # replacing a key in place and re-using a deleted key: tests/test_dropin_gpu.py
 
 
 def test_emptied_top_layers(oracle):

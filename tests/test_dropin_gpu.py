@@ -1,0 +1,135 @@
+"""The holes VERDICT r1 listed in the drop-in surface: Add / BatchAdd of a key that already exists (graph.go:435-436,
+1016-1037), Export after Delete (encode.go:133-174 writes what layer.nodes holds) and the v1 wire format for string and
+fixed-size keys (encode.go:66-126)."""
+import io
+
+import numpy as np
+import pytest
+
+from util import draw_levels
+
+pytestmark = pytest.mark.gpu
+
+
+def _lists_equal(og, dg):
+    assert og.topography() == dg.Topography()
+    for l in range(og.n_layers):
+        rows, ptr, nbr = og.dump_layer(l)
+        dn, _ = dg.neighbors(l)
+        for i, r in enumerate(rows):
+            assert list(dn[r][dn[r] >= 0]) == list(nbr[ptr[i]:ptr[i + 1]]), (l, int(r))
+
+
+@pytest.mark.parametrize("metric", [0, 1])
+def test_readding_an_existing_key_replaces_the_node(oracle, metric):
+    import hnsw_b200
+    rng = np.random.default_rng(21)
+    n, d, M, ef = 600, 16, 8, 24
+    X = rng.standard_normal((n, d)).astype(np.float32)
+    levels = draw_levels(oracle, n, 0.25, 5)
+    keys = np.arange(n, dtype=np.int64) * 3
+    dist = hnsw_b200.EuclideanDistance if metric == 0 else hnsw_b200.CosineDistance
+    og = oracle.Graph(d, M, metric)
+    og.add_many(keys, X, levels, ef)
+    dg = hnsw_b200.Graph(M=M, Ml=0.25, EfSearch=ef, Distance=dist)
+    dg.add_arrays(keys, X, levels)
+    # a batch of two new nodes, then a key that exists, then one more new node the reference never reaches
+    newv = rng.standard_normal((4, d)).astype(np.float32)
+    batch = [hnsw_b200.Node(5000, newv[0]), hnsw_b200.Node(5001, newv[1]), hnsw_b200.Node(300, newv[2]),
+             hnsw_b200.Node(5002, newv[3])]
+    with pytest.raises(ValueError, match="node not added"):      # graph.go:1035-1037
+        dg.BatchAdd(batch, levels=[0, 1, 2, 0])
+    og.add(5000, newv[0], 0, ef)
+    og.add(5001, newv[1], 1, ef)
+    assert og.delete(300)
+    og.add(300, newv[2], 2, ef)
+    assert dg.Len() == og_len(og) == n + 2
+    _lists_equal(og, dg)
+    v, ok = dg.Lookup(300)
+    assert ok and np.array_equal(v, newv[2])
+    assert dg.Lookup(5002) == (None, False)                      # the rest of the batch was not processed
+    Q = rng.standard_normal((64, d)).astype(np.float32)
+    o_rows, o_d, o_cnt, _ = og.batch_search(Q, 10, ef)
+    r, dd, c = dg.search_rows(Q, 10, ef)
+    assert np.array_equal(o_rows, r) and np.array_equal(o_cnt, c)
+    # silent mode: the batch continues; a key repeated inside one batch replaces itself
+    dg.REPLACE_RAISES = False
+    dg.BatchAdd([hnsw_b200.Node(7000, newv[0]), hnsw_b200.Node(7000, newv[1]), hnsw_b200.Node(7001, newv[3])],
+                levels=[0, 0, 0])
+    og.add(7000, newv[0], 0, ef)
+    assert og.delete(7000)
+    og.add(7000, newv[1], 0, ef)
+    og.add(7001, newv[3], 0, ef)
+    _lists_equal(og, dg)
+    assert np.array_equal(dg.Lookup(7000)[0], newv[1])
+    # a key that was deleted comes back under a new row
+    assert dg.Delete(9) and og.delete(9)
+    dg.Add(hnsw_b200.Node(9, newv[2]), levels=[1])
+    og.add(9, newv[2], 1, ef)
+    _lists_equal(og, dg)
+
+
+def og_len(og):
+    return og.topography()[0]
+
+
+def test_export_after_delete_and_import(oracle):
+    import hnsw_b200
+    rng = np.random.default_rng(22)
+    n, d = 500, 12
+    X = rng.uniform(-1, 1, (n, d)).astype(np.float32)
+    g = hnsw_b200.Graph(M=8, Ml=0.25, EfSearch=20, Distance=hnsw_b200.EuclideanDistance)
+    g.add_arrays(np.arange(n, dtype=np.int64), X, draw_levels(oracle, n, 0.25, 6))
+    gone = [int(k) for k in rng.choice(n, 60, replace=False)]
+    assert all(g.BatchDelete(gone))
+    buf = io.BytesIO()
+    g.Export(buf)                                                  # encode.go:152-171: the live nodes only
+    g2 = hnsw_b200.NewGraph()
+    g2.Import(io.BytesIO(buf.getvalue()))
+    assert g2.Len() == n - 60 == g.Len()
+    assert all(g2.Lookup(k) == (None, False) for k in gone[:10])
+    live = [k for k in range(n) if k not in set(gone)]
+    for k in live[:20]:
+        assert np.array_equal(g2.Lookup(k)[0], X[k])
+    # every neighbour the import kept is a live member of the layer (deleted keys resolved to nil, encode.go:253-257)
+    for l in range(len(g2.Topography())):
+        nb, mem = g2.neighbors(l)
+        assert (nb[mem][nb[mem] >= 0] < g2.Len()).all()
+    out = g2.BatchSearch(X[live[:50]], 5)
+    assert all(res for res in out) and all(nd.Key not in set(gone) for res in out for nd in res)
+    buf2 = io.BytesIO()
+    g2.Export(buf2)
+    g3 = hnsw_b200.NewGraph()
+    g3.Import(io.BytesIO(buf2.getvalue()))
+    assert g3.Topography() == g2.Topography()
+
+
+@pytest.mark.parametrize("key_type,make", [(str, lambda i: f"doc-{i:05d}"), (bytes, lambda i: b"k%05d" % i),
+                                           (float, lambda i: i * 0.5 - 100.0)])
+def test_export_import_other_key_types(oracle, key_type, make):
+    import hnsw_b200
+    from hnsw_b200.encode import put_key, put_varint
+    rng = np.random.default_rng(23)
+    n, d = 300, 10
+    X = rng.uniform(-1, 1, (n, d)).astype(np.float32)
+    g = hnsw_b200.Graph(M=6, Ml=0.25, EfSearch=20, Distance=hnsw_b200.CosineDistance)
+    order = rng.permutation(n)
+    g.BatchAdd([hnsw_b200.Node(make(int(i)), X[i]) for i in order], levels=list(draw_levels(oracle, n, 0.25, 7)))
+    buf = io.BytesIO()
+    g.Export(buf)
+    raw = buf.getvalue()
+    if key_type is str:   # encode_test.go:35-50: a string is its varint length followed by its bytes
+        assert put_key("str", "hello") == put_varint(5) + b"hello"
+        assert b"doc-00007" in raw
+    if key_type is float:  # encode.go:118-124: binary.Write little endian
+        assert put_key("float", 1.5) == np.float64(1.5).tobytes()
+    g2 = hnsw_b200.NewGraph()
+    g2.Import(io.BytesIO(raw), key_type=key_type)
+    assert g2.Len() == n and g2.Topography() == g.Topography() and g2.Distance is hnsw_b200.CosineDistance
+    Q = rng.uniform(-1, 1, (40, d)).astype(np.float32)
+    a = [[nd.Key for nd in res] for res in g.BatchSearch(Q, 5)]
+    b = [[nd.Key for nd in res] for res in g2.BatchSearch(Q, 5)]
+    assert a == b
+    out = io.BytesIO()
+    g2.Export(out)
+    assert out.getvalue() == raw

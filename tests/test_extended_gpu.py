@@ -105,3 +105,42 @@ def test_extended_visited_table_grows(oracle):
     Q = rng.uniform(-1, 1, (64, 16)).astype(np.float32)
     _same(g, dg, Q, 50, 512, EXT)
     _same(g, dg, Q, 10, 64, 0)
+
+
+@pytest.mark.parametrize("n,d,M,ef,metric,wave_max", [
+    (3000, 128, 16, 64, 0, 4096),
+    (1500, 32, 8, 24, 1, 128),
+    (900, 768, 32, 40, 1, 256),
+])
+def test_extended_wave_build_matches_oracle(oracle, n, d, M, ef, metric, wave_max):
+    """The wave-batched Add with the textbook layer search inside (b200hnsw_set_build_mode; NOT the reference) against
+    the oracle's add_waves in the same build mode: every list, the counters, and searches in both modes."""
+    import hnsw_b200
+    from hnsw_b200 import _lib
+    from util import draw_levels
+    rng = np.random.default_rng(31)
+    X = rng.standard_normal((n, d)).astype(np.float32)
+    keys = np.arange(n, dtype=np.int64)
+    levels = draw_levels(oracle, n, 0.25, 46)
+    g = oracle.Graph(d, M, metric)
+    g.set_build_mode(oracle.MODE_EXTENDED)
+    g.add_waves(keys, X, levels, ef, wave_max, n_threads=4)
+    dist = hnsw_b200.EuclideanDistance if metric == 0 else hnsw_b200.CosineDistance
+    dg = hnsw_b200.Graph(M=M, Ml=0.25, EfSearch=ef, Distance=dist)
+    dg.set_build_mode(_lib.MODE_EXTENDED)
+    dg.add_arrays(keys, X, levels, wave_max=wave_max)
+    st = dg.last_stats
+    assert g.topography() == dg.Topography()
+    for l in range(g.n_layers):
+        rows, ptr, nbr = g.dump_layer(l)
+        dn, member = dg.neighbors(l)
+        for i, r in enumerate(rows):
+            assert [int(v) for v in dn[r] if v >= 0] == list(nbr[ptr[i]:ptr[i + 1]]), (l, int(r))
+    c = g.counters()
+    for kk in ("dist_evals", "expansions", "nbr_reads", "evict_evals", "replenish_evals", "evictions"):
+        assert st[kk] == c[kk], kk
+    Q = rng.standard_normal((100, d)).astype(np.float32)
+    _same(g, dg, Q, 10, ef, EXT)
+    _same(g, dg, Q, 10, ef, 0)
+    with pytest.raises(_lib.B200Error):   # the sequential Add is the reference's: no extended build there
+        dg.add_arrays(np.array([n + 5], dtype=np.int64), X[:1], [0])
