@@ -7,6 +7,7 @@
 namespace b200 {
 
 int launch_ext_e2(b200hnsw *h, const GraphView &g, TraverseParams &p, int ef_upper, cudaStream_t s);
+int launch_ext_e4(b200hnsw *h, const GraphView &g, TraverseParams &p, int ef_upper, cudaStream_t s);
 int launch_ext_e8(b200hnsw *h, const GraphView &g, TraverseParams &p, int ef_upper, cudaStream_t s);
 int launch_ext_e32(b200hnsw *h, const GraphView &g, TraverseParams &p, int ef_upper, cudaStream_t s);
 
@@ -39,6 +40,7 @@ int launch_traverse_ext(b200hnsw *h, TraverseParams &p, int ef_upper, int vis_ca
   const int efk_max = e0 > eU ? e0 : eU;
   p.vis_cap = pow2_ge(vis_cap < 256 ? 256 : vis_cap);
   if (efk_max <= 64) return launch_ext_e2(h, g, p, ef_upper, s);
+  if (efk_max <= 128) return launch_ext_e4(h, g, p, ef_upper, s);
   if (efk_max <= 256) return launch_ext_e8(h, g, p, ef_upper, s);
   if (efk_max <= 1024) return launch_ext_e32(h, g, p, ef_upper, s);
   set_error("extended search: max(ef, k) = %d > 1024 not supported", efk_max);

@@ -9,9 +9,9 @@
 
 namespace b200 {
 
-template <int G, int CH, int U, int MINB = 1, int TW = TRAV_WARPS>
+template <int G, int CH, int U, int MINB = 1, int TW = TRAV_WARPS, bool NANG = false>
 static int launch_t(b200hnsw *h, const GraphView &g, TraverseParams &p, cudaStream_t s) {
-  auto kern = traverse_kernel<G, CH, U, MINB, TW>;
+  auto kern = traverse_kernel<G, CH, U, MINB, TW, NANG>;
   constexpr int NG = 32 / G;
   size_t smem = traverse_group_bytes(p) * TW * NG;
   if (smem > h->smem_optin - 512) {
@@ -69,6 +69,41 @@ int max_visited_cap(const b200hnsw *h, int k, int ef) {
   return cap;
 }
 
+// the dispatch table: group width x chunks per lane x rows per batch (x the NaN-guard instantiation, traverse.cuh)
+template <bool NANG>
+static int traverse_dispatch(b200hnsw *h, const GraphView &g, TraverseParams &p, int G, int ch, cudaStream_t s) {
+#define K1(G_, CH_, U_) \
+  return launch_t<G_, CH_, U_, ((CH_) >= 12 ? 2 : ((CH_) * (U_) <= 8 ? 5 : 4)), TRAV_WARPS, NANG>(h, g, p, s)
+  if (G == 8) {
+    // G = 8 kernels load rows without bounds tests: CH must equal row_chunks / 8 exactly (gdist.cuh)
+    if (ch == 1) K1(8, 1, 8);
+    if (ch == 2) K1(8, 2, 4);
+    if (ch == 3) K1(8, 3, 2);
+    // dim 128: two-warp blocks, 10 per SM (measured with three launches in flight: 73.9M queries/s against 72.9M for
+    // four-warp blocks and 70.1M for one-warp blocks, profiles/r4j_k1_block_shape.log)
+    if (ch == 4) return launch_t<8, 4, 2, 10, 2, NANG>(h, g, p, s);
+    G = 16;
+    ch = (g.row_chunks + 15) / 16;
+  }
+  if (G == 16) {
+    if (ch <= 1) K1(16, 1, 8);
+    if (ch <= 2) K1(16, 2, 4);
+    if (ch <= 4) K1(16, 4, 4);
+    G = 32;
+    ch = (g.row_chunks + 31) / 32;
+  }
+  if (ch <= 1) K1(32, 1, 8);
+  if (ch <= 2) K1(32, 2, 4);
+  if (ch <= 4) K1(32, 4, 4);
+  if (ch <= 6) K1(32, 6, 2);
+  if (ch <= 8) K1(32, 8, 2);
+  if (ch <= 12) K1(32, 12, 1);
+  if (ch <= 16) K1(32, 16, 1);
+#undef K1
+  set_error("search: dim %d > 2048 not supported", g.dim);
+  return B200HNSW_ERR_UNSUPPORTED;
+}
+
 int launch_traverse(b200hnsw *h, TraverseParams &p, int vis_cap, cudaStream_t s) {
   GraphView g = h->view();
   if (p.n_layers == 0) p.n_layers = h->n_layers;
@@ -98,6 +133,7 @@ int launch_traverse(b200hnsw *h, TraverseParams &p, int vis_cap, cudaStream_t s)
   // a large visited table (retry after overflow) only fits with one traversal per warp
   if (traverse_group_bytes(p) * TRAV_WARPS * (32 / G) > h->smem_optin - 512) G = 32;
   int ch = (g.row_chunks + G - 1) / G;
+#ifdef B200_K1_TUNING  // tuning builds only (scripts/k1_variants.py): eighteen more instantiations for dim 128
   if (const char *v = getenv("B200HNSW_K1_VARIANT")) {  // tuning experiments (dim 128 only)
     int id = atoi(v);
     if (g.row_chunks == 32) {
@@ -121,35 +157,8 @@ int launch_traverse(b200hnsw *h, TraverseParams &p, int vis_cap, cudaStream_t s)
       if (id == 18) return launch_t<8, 4, 2, 10, 2>(h, g, p, s);
     }
   }
-#define K1(G_, CH_, U_) return launch_t<G_, CH_, U_, ((CH_) >= 12 ? 2 : ((CH_) * (U_) <= 8 ? 5 : 4))>(h, g, p, s)
-  if (G == 8) {
-    // G = 8 kernels load rows without bounds tests: CH must equal row_chunks / 8 exactly (gdist.cuh)
-    if (ch == 1) K1(8, 1, 8);
-    if (ch == 2) K1(8, 2, 4);
-    if (ch == 3) K1(8, 3, 2);
-    // dim 128: two-warp blocks, 10 per SM (measured with three launches in flight: 73.9M queries/s against 72.9M for
-    // four-warp blocks and 70.1M for one-warp blocks, profiles/r4j_k1_block_shape.log)
-    if (ch == 4) return launch_t<8, 4, 2, 10, 2>(h, g, p, s);
-    G = 16;
-    ch = (g.row_chunks + 15) / 16;
-  }
-  if (G == 16) {
-    if (ch <= 1) K1(16, 1, 8);
-    if (ch <= 2) K1(16, 2, 4);
-    if (ch <= 4) K1(16, 4, 4);
-    G = 32;
-    ch = (g.row_chunks + 31) / 32;
-  }
-  if (ch <= 1) K1(32, 1, 8);
-  if (ch <= 2) K1(32, 2, 4);
-  if (ch <= 4) K1(32, 4, 4);
-  if (ch <= 6) K1(32, 6, 2);
-  if (ch <= 8) K1(32, 8, 2);
-  if (ch <= 12) K1(32, 12, 1);
-  if (ch <= 16) K1(32, 16, 1);
-#undef K1
-  set_error("search: dim %d > 2048 not supported", g.dim);
-  return B200HNSW_ERR_UNSUPPORTED;
+#endif
+  return p.heap_c_full ? traverse_dispatch<true>(h, g, p, G, ch, s) : traverse_dispatch<false>(h, g, p, G, ch, s);
 }
 
 int launch_search(b200hnsw *h, const float *d_queries, int64_t B, int k, int ef, int metric, int mode,

@@ -87,7 +87,12 @@ constexpr int TRAV_WARPS = 4;
 
 enum { ST_NEED = 0, ST_INIT = 1, ST_EXPAND = 2, ST_IDLE = 3 };
 
-template <int G, int CH, int U, int MINB, int TW = TRAV_WARPS>
+// NANG (NaN guard): the instantiation for graphs that hold rows able to produce NaN distances, and for the retry of a
+// batch with such a query: the Go-exact candidate queue is kept for the whole layer (full ef + 1 capacity).  The
+// NANG = false kernels -- the ones every ordinary search runs -- carry no per-step cost for it (measured: the guard
+// inside the hot loop cost 7 %, profiles/r5g_k1_guard_ab.log): they refuse to run on a flagged graph and fail a risky
+// query loudly (error 3), and the host runs the batch again through the NANG = true kernels.
+template <int G, int CH, int U, int MINB, int TW = TRAV_WARPS, bool NANG = false>
 __global__ void __launch_bounds__(TW * 32, MINB) traverse_kernel(GraphView g, TraverseParams p) {
   constexpr int NG = 32 / G;
   constexpr unsigned GBITS = G == 32 ? 0xffffffffu : ((1u << G) - 1u);
@@ -120,8 +125,13 @@ __global__ void __launch_bounds__(TW * 32, MINB) traverse_kernel(GraphView g, Tr
   int best_id = -1, r1 = 0;
   int imp_id = -1;      // leader: last row that improved on result.Min() in this step
   bool cfree = false;   // leader: the candidate queue is no longer needed on this layer (see the decision below)
-  const bool nan_rows = p.row_flags != nullptr && (__ldg(p.row_flags) & 1);
-  bool keepc = nan_rows;  // this traversal may meet NaN distances: never drop the candidate queue
+  constexpr bool keepc = NANG;  // never drop the candidate queue (see the decision below)
+  if constexpr (!NANG) {
+    if (p.row_flags != nullptr && (__ldg(p.row_flags) & 1)) {  // rows that can yield NaN entered the graph: not my job
+      if (threadIdx.x == 0) *p.error = 3;
+      return;
+    }
+  }
 
 #ifdef B200_K1_TIMING
   long long tphase[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tlast = clock64();
@@ -144,14 +154,24 @@ __global__ void __launch_bounds__(TW * 32, MINB) traverse_kernel(GraphView g, Tr
         layer = p.n_layers - 1;
         elevator = -1;
         lvl = p.levels ? p.levels[q] : -1;
-        keepc = nan_rows || (p.metric != 0 && !(NQ.qq >= 1e-20f && NQ.qq <= 1e20f));
         st = ST_INIT;
+        if constexpr (!NANG) {
+          // a query whose |q|^2 is 0, non-finite or out of range under cosine can meet NaN distances: fail it loudly
+          if (p.metric != 0 && !(NQ.qq >= 1e-20f && NQ.qq <= 1e20f)) {
+            if (leader) {
+              *p.error = 3;
+              c_over++;
+              if (p.out_rows) *search_out(p, q).count = -1;
+              else p.slot_cnt[p.slot_off[q]] = -1;
+            }
+            st = ST_NEED;
+          }
+        }
       }
     }
     if (__all_sync(FULL, st == ST_IDLE)) break;
     const bool init = st == ST_INIT, expand = st == ST_EXPAND;
     bool improved = false;  // leader
-    bool cerr = false;      // leader: the candidate queue would outgrow its (short) allocation
     int nfresh = 0;
     // ---- INIT (top layer, or a layer reached without an elevator): the entry point is the only row to evaluate ----
     if (init) {
@@ -300,12 +320,8 @@ __global__ void __launch_bounds__(TW * 32, MINB) traverse_kernel(GraphView g, Tr
             }
           }
           if (!cfree) {
-            if (C.len >= p.heap_c) {
-              cerr = true;  // only with NaN distances in play and the short queue: reported, the host retries in full
-            } else {
-              C.push(du, ids[u]);
-              if (C.len > p.ef) C.pop_last();  // graph.go:157-159
-            }
+            C.push(du, ids[u]);
+            if (C.len > p.ef) C.pop_last();  // graph.go:157-159
           }
         }
       }
@@ -314,9 +330,8 @@ __global__ void __launch_bounds__(TW * 32, MINB) traverse_kernel(GraphView g, Tr
     if (leader) c_evals += nfresh;  // E: one per evaluated row
     if (init && nfresh > 0) vcount = 1;
     // ---- leader decides: next node, end of layer ---------------------------------------------------------------------
-    int next = -1;  // leader: row to expand next; -1 = the layer ends; -2 = the short candidate queue would overflow
-    if (leader && cerr) next = -2;
-    if (leader && (init || expand) && !overflow && !cerr) {
+    int next = -1;  // leader: row to expand next; -1 = the layer ends
+    if (leader && (init || expand) && !overflow) {
       const int rl = kcur == 1 ? r1 : R.len;
       if (init) {
         if (nfresh > 0) next = cur;                                 // graph.go:125-127, first iteration
@@ -334,7 +349,6 @@ __global__ void __launch_bounds__(TW * 32, MINB) traverse_kernel(GraphView g, Tr
       if (rl >= kcur && !keepc) cfree = true;
     }
     next = __shfl_sync(FULL, next, leader_lane);
-    const bool cfail = next == -2;
     const int rlen = __shfl_sync(FULL, kcur == 1 ? r1 : R.len, leader_lane);
     const int r0_id = __shfl_sync(FULL, best_id, leader_lane);    // k = 1 layers: the result itself
     const float r0_d = __shfl_sync(FULL, best_d, leader_lane);
@@ -343,9 +357,9 @@ __global__ void __launch_bounds__(TW * 32, MINB) traverse_kernel(GraphView g, Tr
     bool chain = false;
     float elev_d = 0.f;
     if (init || expand) {
-      if (overflow || cfail) {
+      if (overflow) {
         if (leader) {
-          *p.error = overflow ? 1 : 3;
+          *p.error = 1;
           c_over++;
           if (p.out_rows) *search_out(p, q).count = -1;
           else p.slot_cnt[p.slot_off[q]] = -1;

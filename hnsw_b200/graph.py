@@ -289,7 +289,7 @@ class Graph:
         mirror.start()
         total = None
         try:
-            off = 0
+            off, stalled = 0, False
             while True:
                 st = _lib.Stats()
                 try:
@@ -307,7 +307,8 @@ class Graph:
                     done = int(L.b200hnsw_rows(self._h)) - rows0
                     # rows that can yield NaN distances entered the graph with this batch: the handle now runs the full
                     # candidate queue; the nodes that were not inserted go in again (include/b200hnsw.h)
-                    if e.code == _lib.ERR_STATE and "add the rest again" in str(e) and done > off:
+                    if e.code == _lib.ERR_STATE and "add the rest again" in str(e) and (done > off or not stalled):
+                        stalled = done == off  # no progress is fine once: the handle learned about the rows only now
                         off = done
                         continue
                     raise

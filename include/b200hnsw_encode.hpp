@@ -87,10 +87,9 @@ void Export(const Graph<K> &g, std::ostream &w) {
   enc::putString(out, name.first);
   const b200hnsw_t *h = g.Handle();
   const int64_t rows = h ? b200hnsw_rows(h) : 0;
-  if (h && b200hnsw_len(h) != rows)
-    // the reference would write live nodes whose neighbour lists still name deleted keys (replenish re-links isolated
-    // nodes, graph.go:172-219); Import turns those into nil neighbours.  Not reproduced.
-    throw Error("Export after Delete is not supported");
+  // After a Delete the reference writes what layer.nodes holds: the live nodes only, whose neighbour lists can still
+  // name deleted keys (isolate leaves one-way links, replenish re-links isolated nodes, graph.go:172-235); Import
+  // resolves those to nil neighbours, which Search skips (encode.go:253-257, graph.go:140-143).
   if (rows == 0) {
     enc::putVarint(out, 0);
     w.write(out.data(), (std::streamsize)out.size());
@@ -110,7 +109,7 @@ void Export(const Graph<K> &g, std::ostream &w) {
     detail::check(b200hnsw_get_neighbors(h, l, 0, rows, nbr.data(), member.data()));
     order.clear();
     for (int64_t r = 0; r < rows; r++)
-      if (member[(size_t)r]) order.push_back((int32_t)r);
+      if (member[(size_t)r] && b200hnsw_is_deleted(h, (int32_t)r) == 0) order.push_back((int32_t)r);
     std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t b) { return keys[a] < keys[b]; });
     enc::putVarint(out, (int64_t)order.size());
     for (int32_t r : order) {

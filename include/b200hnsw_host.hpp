@@ -144,6 +144,7 @@ class Graph {
   double Ml = 0.25;
   int EfSearch = 20;
   int Device = 0;  // CUDA device ordinal of the mirror (no counterpart in the reference)
+  bool ReplaceRaises = true;  // graph.go:1035-1037: BatchAdd of an existing key replaces it AND returns "node not added"
 
   Graph() = default;
   Graph(const Graph &) = delete;
@@ -345,15 +346,26 @@ class Graph {
     }
     if (M > max_m_)
       throw Error(detail::fmt("M=%d exceeds the device list stride %d fixed at the first Add", M, max_m_));
-    std::unordered_set<int64_t> fresh;
-    for (auto &n : nodes) {
-      const int64_t k = (int64_t)n.Key;
-      if (row_of_.count(k) || !fresh.insert(k).second)
-        throw Error(detail::fmt("key %lld already present: replacing a node in place is not supported; Delete it "
-                                "and Add it under a new key", (long long)k));
-      if (retired_.count(k))
-        throw Error(detail::fmt("key %lld was deleted: its node can still be linked under that key; use a new key",
-                                (long long)k));
+    // "If another node with the same ID exists, it is replaced" (graph.go:435-436).  The reference deletes the old node
+    // in the middle of the insertion (graph.go:1016-1024) and then fails its own invariant, so BatchAdd returns "node
+    // not added" with the replacement done and the rest of the batch untouched (graph.go:1035-1037); Add deadlocks
+    // (graph.go:438 + 844).  Here: the nodes in front go in, the old node is deleted, the new one inserted under a new
+    // row, and the reference's error is raised (ReplaceRaises = false: silently, and the batch continues).
+    {
+      std::unordered_set<int64_t> fresh;
+      for (size_t i = 0; i < nodes.size(); i++) {
+        const int64_t k = (int64_t)nodes[i].Key;
+        if (row_of_.count(k) || !fresh.insert(k).second) {
+          add(std::vector<Node<K>>(nodes.begin(), nodes.begin() + (long)i), waveMax);
+          BatchDelete(std::vector<K>{nodes[i].Key});
+          retired_.erase(k);
+          add(std::vector<Node<K>>{nodes[i]}, 0);
+          if (ReplaceRaises) throw Error("node not added");
+          add(std::vector<Node<K>>(nodes.begin() + (long)i + 1, nodes.end()), waveMax);
+          return;
+        }
+      }
+      for (auto &n : nodes) retired_.erase((int64_t)n.Key);  // a deleted key that comes back names the new row
     }
     // levels: randomLevel() for consecutive insertions; the bound maxLevel(Ml, len(layer 0)) grows as nodes land
     const size_t n = nodes.size();

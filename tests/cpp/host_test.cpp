@@ -186,7 +186,20 @@ static void gpu_tests() {
     int cnt = ora_graph_search(og, qs[0].data(), k, ef, ORA_MODE_REFERENCE, nullptr, rows, dist);
     CHECK((int)after.size() == cnt);
     for (int j = 0; j < cnt && j < (int)after.size(); j++) CHECK(after[j].Key == ora_graph_key(og, rows[j]));
-    CHECK(contains(error_of([&] { g.Add(nodes[7]); }), "already present"));
+    // a key that exists is replaced and the reference's own error comes back (graph.go:435-436, 1016-1037)
+    {
+      auto repl = nodes[7];
+      for (auto &v : repl.Value) v = -v;
+      CHECK(contains(error_of([&] { g.Add(repl); }), "node not added"));
+      CHECK(g.Len() == n - 1 && g.Lookup(repl.Key).second && g.Lookup(repl.Key).first == repl.Value);
+      // Export after Delete writes the live nodes only; Import of that stream answers like the exporter's live part
+      std::ostringstream os2;
+      Export(g, os2);
+      std::istringstream is2(os2.str());
+      auto g4 = NewGraph<int64_t>();
+      Import(g4, is2);
+      CHECK(g4.Len() == g.Len() && !g4.Lookup(nodes[5].Key).second && g4.Lookup(repl.Key).first == repl.Value);
+    }
     ora_graph_free(og);
   }
 }
