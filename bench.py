@@ -56,10 +56,12 @@ def parse_args():
                          "the textbook one (B200HNSW_MODE_EXTENDED, not the reference)")
     ap.add_argument("--layout", default=None, choices=["replicas", "sharded"])
     ap.add_argument("--sides", default="default", help="side workloads: default | none | comma list")
-    ap.add_argument("--n", type=int, default=None, help="rows (per GPU, or in total for c4/c5); default: the workload's")
+    ap.add_argument("--n", "--rows", dest="n", type=int, default=None,
+                    help="rows (per GPU, or in total for c4/c5); default: the workload's.  Under torchrun write --rows: its "
+                         "own parser takes --n for an abbreviation of --nnodes")
     ap.add_argument("--dim", type=int, default=None)
     ap.add_argument("--batch", type=int, default=None)
-    ap.add_argument("--m", type=int, default=None)
+    ap.add_argument("--m", "--graph-m", dest="m", type=int, default=None)
     ap.add_argument("--ef", type=int, default=None)
     ap.add_argument("--k", type=int, default=None)
     ap.add_argument("--ml", type=float, default=0.25)

@@ -676,7 +676,22 @@ int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_
   for (int i = 0; i < 5; i++) ctr[i] = 0;
   int launches = 0;
   bool staged = false;
-  if (nchunk == 1) {  // one chunk: copy first, so that kernel_ms (ev0..ev1) is the traversal kernel alone
+  // Page-locked QUERIES could be read by the kernel itself as well (each traversal fetching its 4*dim bytes over PCIe
+  // when it starts).  Measured and rejected as the default (profiles/r5j_direct_in_ab.log): one caller 29.4 M vs 30.2 M
+  // queries/s, four callers 54 M vs 71 M -- a traversal that waits 2 us for its query holds its slot on the SM, and
+  // the copy engine moves the same bytes without occupying one.  B200HNSW_DIRECT_IN=1 selects it for experiments.
+  const float *q_src = d_q;
+  {
+    const char *v = getenv("B200HNSW_DIRECT_IN");
+    if (v && v[0] == '1') {
+      if (void *zq = mapped_host(queries)) {
+        q_src = (const float *)zq;
+        staged = true;
+      }
+    }
+  }
+  const bool direct_in = q_src != d_q;
+  if (nchunk == 1 && !staged) {  // one chunk: copy first, so that kernel_ms (ev0..ev1) is the traversal kernel alone
     if ((e = cudaMemcpyAsync(d_q, queries, qb, cudaMemcpyHostToDevice, s)) != cudaSuccess)
       return fail(cuda_fail(e, "search staging"));
     staged = true;
@@ -706,7 +721,7 @@ int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_
       if (!staged && (e = cudaMemcpyAsync(d_q + q0 * dim, queries + q0 * dim, sizeof(float) * (size_t)nq * dim,
                                           cudaMemcpyHostToDevice, sc)) != cudaSuccess)
         return fail(cuda_fail(e, "search staging"));
-      rc = launch_search(h, d_q + q0 * dim, nq, k, ef, metric, mode, entries, d_rows + q0 * k, d_dists + q0 * k,
+      rc = launch_search(h, q_src + q0 * dim, nq, k, ef, metric, mode, entries, d_rows + q0 * k, d_dists + q0 * k,
                          d_cnt + q0, d_ctr, d_err, vis, sc, 0, 0, nullptr, 0, full_queue);
       if (rc) return fail(rc);
       launches++;
@@ -758,8 +773,8 @@ int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_
     float kms = 0.f;
     cudaEventElapsedTime(&kms, c->ev0, c->ev1);
     fprintf(stderr, "b200hnsw_search_batch slow call: total %.2f ms (context %.2f, queued at %.2f), device ev0..ev1 %.2f ms, "
-                    "B=%lld chunks=%d visited table %d direct_out=%d\n", since(), w_acq, w_queued, kms, (long long)B,
-            nchunk, h->vis_hint.load(), (int)direct_out);
+                    "B=%lld chunks=%d visited table %d direct_out=%d direct_in=%d\n", since(), w_acq, w_queued, kms,
+            (long long)B, nchunk, h->vis_hint.load(), (int)direct_out, (int)direct_in);
   }
   h->release(c);
   return 0;
