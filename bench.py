@@ -287,7 +287,7 @@ def graph_block(ctx, args, g, wl, mode, ef, Qh, steps, warmup, headline, ov=None
     return blk
 
 
-def make_graph(ctx, args, wl, seed_rows, seed_levels, rank_offset=0):
+def make_graph(ctx, args, wl, seed_rows, seed_levels, rank_offset=0, build_mode=0):
     """Rows, levels and the device graph of one workload on this rank (wave-batched Add unless --wave-max 0)."""
     from benchlib.device import build_graph
     n = wl["n_local"]
@@ -295,7 +295,7 @@ def make_graph(ctx, args, wl, seed_rows, seed_levels, rank_offset=0):
     levels = draw_levels(n, args.ml, seed_levels)
     keys = np.arange(n, dtype=np.int64) + rank_offset
     g, build = build_graph(ctx.hnsw_b200, X, levels, keys, wl["m"], args.ml, wl["ef"], wl["metric"], ctx.local_rank,
-                           args.wave_max)
+                           args.wave_max, build_mode)
     build["semantics"] = (f"wave-batched Add, waves of <= {args.wave_max} nodes (b200hnsw_add_batch_waves; bit-identical "
                           "to the oracle's restatement of the same schedule, NOT the reference's sequential graph)"
                           ) if args.wave_max > 0 else "exact sequential Graph.Add order (bit-identical to the oracle)"
@@ -414,6 +414,24 @@ def run_sides_single(ctx, args, wl, g, X, Qh, ov, mode, sides):
                 curve.append({"EfSearch": ef, "recall_at_10": recall_at_k(ctx.torch, ctx.dev, X2, Q2[0].numpy()[:1000],
                                                                           r, w2["k"])})
             blk["extended"]["recall_vs_ef"] = curve
+            if args.wave_max > 0:
+                # the same rows linked by the extended wave Add (textbook search inside the build): the graph a caller
+                # who wants recall would build, searched in the extended mode
+                g2.close()
+                g2, _, _, _, build3 = make_graph(ctx, args, w2, 42, 44, build_mode=1)
+                ov3 = oracle_view(ctx, args, g2, w2)
+                eb = graph_block(ctx, args, g2, w2, 1, w2["ef"], Q2, S, W, False, ov3, X2)
+                build3["semantics"] = ("extended wave Add (b200hnsw_set_build_mode(EXTENDED) + b200hnsw_add_batch_waves): "
+                                       "NOT the reference's graph")
+                eb["build"] = build3
+                curve = []
+                for ef in (16, 32, 128, 256):
+                    r, _, _ = g2.search_rows(Q2[0].numpy()[:1000], w2["k"], ef, mode=1)
+                    curve.append({"EfSearch": ef, "recall_at_10": recall_at_k(ctx.torch, ctx.dev, X2,
+                                                                              Q2[0].numpy()[:1000], r, w2["k"])})
+                eb["recall_vs_ef"] = curve
+                blk["extended_build"] = eb
+                del ov3
         out[name] = blk
         g2.close()
         del g2, X2, ov2

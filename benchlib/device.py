@@ -13,9 +13,11 @@ def distance_of(hnsw_b200, metric):
     return hnsw_b200.EuclideanDistance if metric == "l2" else hnsw_b200.CosineDistance
 
 
-def build_graph(hnsw_b200, X, levels, keys, m, ml, ef, metric, device, wave_max):
+def build_graph(hnsw_b200, X, levels, keys, m, ml, ef, metric, device, wave_max, build_mode=0):
     g = hnsw_b200.Graph(M=m, Ml=ml, EfSearch=ef, Distance=distance_of(hnsw_b200, metric), device=device,
                         capacity=len(X))
+    if build_mode:
+        g.set_build_mode(build_mode)  # NOT the reference: the wave Add runs the textbook layer search
     t0 = time.perf_counter()
     g.add_arrays(keys, X, levels, wave_max=wave_max)
     wall = time.perf_counter() - t0

@@ -30,6 +30,10 @@ for name, b in (l.get("sides") or {}).items():
         if "extended" in b and isinstance(b["extended"], dict):
             brief(name + ".extended", b["extended"])
             print(tag, name, "recall_vs_ef", b["extended"].get("recall_vs_ef"))
+        if isinstance(b.get("extended_build"), dict):
+            eb = b["extended_build"]
+            brief(name + ".extended_build", eb)
+            print(tag, name, "extended_build recall_vs_ef", eb.get("recall_vs_ef"), "build vec/s %.0f" % eb["build"]["vec_per_s"])
         if "build" in b:
             print(tag, name, "build vec/s %.0f kernel %.0f" % (b["build"]["vec_per_s"], b["build"]["kernel_vec_per_s"]))
 fl = (l.get("parity") or {}).get("flavours")
