@@ -101,6 +101,8 @@ SYMBOLS = {
     "b200exact_search_batch": (C.c_int, [C.c_void_p, f32p, C.c_int64, C.c_int32, i64p, f32p, i32p, C.POINTER(Stats)]),
     "b200exact_search_batch_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p,
                                                 C.c_void_p, C.c_void_p]),
+    "b200exact_search_batch_noalloc_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p,
+                                                        C.c_void_p, C.c_void_p, C.c_void_p]),
     "b200hnsw_distance_batch": (C.c_int, [C.c_int32, C.c_int32, f32p, f32p, C.c_int64, C.c_int32, f32p]),
 }
 

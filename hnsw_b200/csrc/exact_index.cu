@@ -531,3 +531,83 @@ int b200exact_search_batch(b200exact_t *x, const float *queries, int64_t B, int3
 }
 
 }  // extern "C"
+
+// ---- ExactIndex.Search without any allocation (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: code under CUDA graph capture, tight serving loops, harnesses that
+// forbid it).  The scan path above with its workspace (final keys + per-chunk partial lists + merge ping-pong) in a
+// file-scope device array instead of b200exact::d_scratch.  Every GPU that loads this library holds the array until
+// the process exits.  In host code `g_noalloc_scratch` is only a host-side stand-in for the symbol: the device address
+// comes from cudaGetSymbolAddress, once per device, with that device current.
+// Nothing in the workspace has to start at zero: the scan kernel writes all k keys of every (query, chunk) list and
+// every merge level writes all of its output before the next level reads it, so the previous call's contents are never
+// read.  All calls (all indexes, all streams, all host threads) share the one array per GPU: calls that overlap on the
+// GPU race.
+constexpr size_t NOALLOC_SCRATCH_BYTES = (size_t)8 << 20;
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_SCRATCH_BYTES];
+static std::mutex g_noalloc_mu;
+static char *g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};
+
+// device address of the array on `device` (which is current)
+static int noalloc_scratch_of(int device, char **out) {
+  if (device < 0 || device >= NOALLOC_MAX_DEVICES) {
+    set_error("exact_search_noalloc: device %d out of range (0..%d)", device, NOALLOC_MAX_DEVICES - 1);
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_noalloc_ptr[device]) {
+    void *p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(g_noalloc_scratch)");
+    if (!p) {
+      set_error("exact_search_noalloc: cudaGetSymbolAddress returned a null address on device %d", device);
+      return B200HNSW_ERR_CUDA;
+    }
+    g_noalloc_ptr[device] = (char *)p;
+  }
+  *out = g_noalloc_ptr[device];
+  return 0;
+}
+
+extern "C" int b200exact_search_batch_noalloc_device(b200exact_t *x, const float *d_queries, int64_t B, int32_t k,
+                                                     int64_t *d_out_rows, float *d_out_dists, int32_t *d_out_counts,
+                                                     void *stream) {
+  if (!x || B < 0 || k <= 0 || k > B200HNSW_MAX_K || (B > 0 && (!d_queries || !d_out_rows || !d_out_dists ||
+                                                                  !d_out_counts))) {
+    set_error("exact_search_noalloc: bad argument (k must be in 1..%d)", B200HNSW_MAX_K);
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  B200_CUDA(cudaSetDevice(x->device));
+  char *scratch = nullptr;
+  int rc = noalloc_scratch_of(x->device, &scratch);  // B == 0 is the set-up call: resolves the address and returns
+  if (rc) return rc;
+  if (B == 0) return 0;
+  cudaStream_t s = (cudaStream_t)stream;
+  std::lock_guard<std::mutex> lk(x->mu);
+  if (x->live == 0 || x->n == 0) {  // exact.go:65-67
+    B200_CUDA(cudaMemsetAsync(d_out_counts, 0, sizeof(int32_t) * (size_t)B, s));
+    B200_CUDA(cudaMemsetAsync(d_out_rows, 0xff, sizeof(int64_t) * (size_t)B * k, s));
+    B200_CUDA(cudaMemsetAsync(d_out_dists, 0xff, sizeof(float) * (size_t)B * k, s));
+    return 0;
+  }
+  // final keys [B][k] in front, the scan's workspace behind them; the scan slices the queries to fit, so what has to
+  // fit is the final keys plus ONE query's partial lists (the formula of scan_topk)
+  const size_t n_chunks = (size_t)((x->n + SCAN_ROWS - 1) / SCAN_ROWS);
+  const size_t group = (size_t)std::max(2, 4096 / k);
+  const size_t keys_b = (sizeof(unsigned long long) * (size_t)B * k + 255) & ~(size_t)255;
+  const size_t per_q = sizeof(unsigned long long) * (size_t)k * (n_chunks + (n_chunks + group - 1) / group + 2);
+  if (keys_b > NOALLOC_SCRATCH_BYTES || per_q > NOALLOC_SCRATCH_BYTES - keys_b) {
+    set_error("exact_search_noalloc: B=%lld k=%d over %lld rows needs %zu bytes of scratch, the static array holds %zu "
+              "(8*k*(B + rows/2048*(1 + 1/max(2, 4096/k)) + 2) must fit); split the batch or use "
+              "b200exact_search_batch_device",
+              (long long)B, k, (long long)x->n, keys_b + per_q, NOALLOC_SCRATCH_BYTES);
+    return B200HNSW_ERR_UNSUPPORTED;
+  }
+  unsigned long long *d_keys = (unsigned long long *)scratch;
+  if ((rc = scan_topk(x, d_queries, B, k, d_keys, scratch + keys_b, NOALLOC_SCRATCH_BYTES - keys_b, s))) return rc;
+  const long long total = (long long)B * k;
+  exact_emit_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(d_keys, B, k, x->live, d_out_rows, d_out_dists,
+                                                                   d_out_counts);
+  B200_CUDA(cudaGetLastError());
+  return 0;
+}

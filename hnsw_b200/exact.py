@@ -87,6 +87,15 @@ class ExactIndex:
                                                             C.c_void_p(d_dists), C.c_void_p(d_counts),
                                                             C.c_void_p(stream)))
 
+    def search_device_noalloc(self, d_queries: int, B: int, k: int, d_rows: int, d_dists: int, d_counts: int,
+                              stream: int = 0) -> None:
+        """NOT in the reference (added for callers that cannot call cudaMalloc): the scan path with its workspace in a
+        static 8 MiB device array; no allocation inside the call.  Fails past the array's size; calls that overlap on
+        the GPU race (include/b200hnsw.h: b200exact_search_batch_noalloc_device).  B = 0 is the set-up call."""
+        _lib.check(_lib.lib().b200exact_search_batch_noalloc_device(self._x, C.c_void_p(d_queries), B, k,
+                                                                    C.c_void_p(d_rows), C.c_void_p(d_dists),
+                                                                    C.c_void_p(d_counts), C.c_void_p(stream)))
+
     def _remove_rows(self, rows):
         r = np.ascontiguousarray(rows, dtype=np.int64)
         _lib.check(_lib.lib().b200exact_remove(self._x, r.ctypes.data_as(_lib.i64p), len(r)))

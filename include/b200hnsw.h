@@ -253,6 +253,21 @@ int b200exact_search_batch(b200exact_t *x, const float *queries, int64_t B, int3
 int b200exact_search_batch_device(b200exact_t *x, const float *d_queries, int64_t B, int32_t k, int64_t *d_out_rows,
                                   float *d_out_dists, int32_t *d_out_counts, void *stream);
 
+/* ExactIndex.Search for callers that cannot allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc.  The
+ * scan path of b200exact_search_batch_device (every distance in canonical fp32: the same rows and bits) with its
+ * workspace in a file-scope `static __device__` array of 8 MiB that every GPU loading the library holds until exit;
+ * the call makes no cudaMalloc / cudaFree and calls no allocating routine.  Limit: the final keys plus one query's
+ * partial lists must fit, 8*k*(B + ceil(rows/2048)*(1 + 1/max(2, 4096/k)) + 2) <= 8 MiB (k = 10: B + rows/2048 up to
+ * ~104000); beyond it the call fails with B200HNSW_ERR_UNSUPPORTED and a message that names the sizes.  The first
+ * call on a device resolves the array's address (cudaGetSymbolAddress): make one call with B = 0 at set-up (before a
+ * capture).  Asynchronous on `stream`.  All calls on a GPU share the one array (its contents never have to start at
+ * zero: every word read was written by the same call), so calls that OVERLAP on the GPU race -- keep them on one
+ * stream or order them with events. */
+int b200exact_search_batch_noalloc_device(b200exact_t *x, const float *d_queries, int64_t B, int32_t k,
+                                          int64_t *d_out_rows, float *d_out_dists, int32_t *d_out_counts,
+                                          void *stream);
+
 /* EuclideanDistance / CosineDistance (distance.go:15-23) on the device, pairs (a[i], b[i]); host pointers.
  * Exists so the distance KATs (distance_test.go:9-31) run through the same arithmetic as the kernels. */
 int b200hnsw_distance_batch(int32_t device, int32_t metric, const float *a, const float *b, int64_t n, int32_t dim,
