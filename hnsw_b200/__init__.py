@@ -6,7 +6,7 @@ from .distance import (CosineDistance, EuclideanDistance, RegisterDistanceFunc, 
 from .encode import LoadSavedGraph, SavedGraph
 from .exact import ExactIndex, NewExactIndex
 from ._lib import B200Error
-from .graph import Graph, GoRand, MakeNode, NewGraph, NewGraphWithConfig, Node, maxLevel
+from .graph import Graph, LevelRand, MakeNode, NewGraph, NewGraphWithConfig, Node, maxLevel
 
-__all__ = ["B200Error", "LoadSavedGraph", "SavedGraph", "ExactIndex", "NewExactIndex", "Graph", "GoRand", "Node", "MakeNode", "NewGraph", "NewGraphWithConfig", "maxLevel", "CosineDistance",
+__all__ = ["B200Error", "LoadSavedGraph", "SavedGraph", "ExactIndex", "NewExactIndex", "Graph", "LevelRand", "Node", "MakeNode", "NewGraph", "NewGraphWithConfig", "maxLevel", "CosineDistance",
            "EuclideanDistance", "RegisterDistanceFunc", "distanceFuncs", "distanceFuncToName"]

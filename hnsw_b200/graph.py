@@ -37,8 +37,11 @@ def MakeNode(key, vec) -> Node:
     return Node(key, np.asarray(vec, dtype=np.float32))
 
 
-class GoRand:
-    """Stand-in for *rand.Rand: anything with Float64().  Go's math/rand stream itself is not reproducible here."""
+class LevelRand:
+    """What Graph.Rng has to be: anything with Float64() (the one method randomLevel, graph.go:388-417, calls on its
+    *rand.Rand).  This one is a numpy PCG64 stream, NOT Go's math/rand: a seed gives a reproducible stream here, not the
+    levels the Go reference draws from the same seed (graph_test.go:86-133 therefore cannot be replayed value for value;
+    tests pass explicit levels wherever they compare with the oracle)."""
 
     def __init__(self, seed: Optional[int] = None):
         self._g = np.random.default_rng(seed if seed is not None else time.time_ns())
@@ -64,7 +67,7 @@ class Graph:
     def __init__(self, M=16, Ml=0.25, EfSearch=20, Distance=CosineDistance, Rng=None, device: int = 0,
                  capacity: int = 0):
         self.M, self.Ml, self.EfSearch, self.Distance = M, Ml, EfSearch, Distance
-        self.Rng = Rng if Rng is not None else GoRand()
+        self.Rng = Rng if Rng is not None else LevelRand()
         self.device = device
         self._capacity = capacity
         self._h = None          # b200hnsw_t*
@@ -144,7 +147,7 @@ class Graph:
             mx = maxLevel(self.Ml, self.Len())
         for level in range(mx):
             if self.Rng is None:
-                self.Rng = GoRand()
+                self.Rng = LevelRand()
             if self.Rng.Float64() > self.Ml:
                 return level
         return mx
@@ -377,6 +380,19 @@ class Graph:
     def Delete(self, key) -> bool:
         """graph.go:843-866."""
         return self.BatchDelete([key])[0]
+
+    @property
+    def visited_capacity(self) -> int:
+        """Entries of the per-traversal visited set the device-pointer entry points use (b200hnsw_get_visited_capacity)."""
+        if self._h is None:
+            raise RuntimeError("the graph has no device handle yet (nothing was added or loaded)")
+        return int(_lib.lib().b200hnsw_get_visited_capacity(self._h))
+
+    @visited_capacity.setter
+    def visited_capacity(self, entries: int):
+        if self._h is None:
+            raise RuntimeError("the graph has no device handle yet (nothing was added or loaded)")
+        _lib.check(_lib.lib().b200hnsw_set_visited_capacity(self._h, int(entries)))
 
     def set_build_mode(self, mode: int):
         """NOT the reference: the layer search the wave-batched Add runs (_lib.MODE_EXTENDED = textbook search)."""

@@ -145,7 +145,41 @@ class SegmentedResults:
         return self.m_d, self.m_i, self.m_c
 
 
-class ShardPipeline:
+class _CheckedRuns:
+    """search_all: the visited-capacity retry of b200hnsw_search_batch for the pipelines, which drive the device-pointer
+    entry points (those report a failed traversal in d_counters[4] instead of retrying, include/b200hnsw.h)."""
+
+    def search_all(self, d_query_ptrs, before=None, after=None, max_rounds: int = 4):
+        """Queue every batch of `d_query_ptrs` (device pointers), drain, then read the traversal error word on every
+        rank.  If a traversal overflowed its visited set on ANY rank, every rank raises its graph's capacity (x4) and the
+        whole list is issued again (traversals are deterministic: the same outputs are rewritten).  Collective when the
+        pipeline has a process group.  Returns the slots of the batches, in order."""
+        import torch
+        if getattr(self, "_ctr", None) is None:
+            self._ctr = torch.zeros(8, dtype=torch.int64, device=self.main.device)
+        for _ in range(max_rounds):
+            self._ctr.zero_()
+            slots = [self.search(p, self._ctr.data_ptr(), before=before, after=after) for p in d_query_ptrs]
+            self.drain()
+            self.main.synchronize()
+            err = self._ctr[4:5].to(torch.int32)
+            if self.dist is not None and self.world > 1:
+                codes = [torch.zeros_like(err) for _ in range(self.world)]
+                self.dist.all_gather(codes, err)
+                codes = [int(c.item()) for c in codes]
+            else:
+                codes = [int(err.item())]
+            if not any(codes):
+                return slots
+            if any(c not in (0, 1) for c in codes):
+                raise RuntimeError(f"a traversal failed with error {codes} (3: a query or row with a non-finite or extreme "
+                                   f"norm; b200hnsw_search_batch handles those with the full candidate queue)")
+            self.g.visited_capacity = self.g.visited_capacity * 4  # raises B200Error past what the device can give
+        raise RuntimeError("search_all: traversals still overflow the visited set after raising it "
+                           f"{max_rounds - 1} times")
+
+
+class ShardPipeline(_CheckedRuns):
     """Sharded batched search as a pipeline.  `depth` traversal streams take the batches in turn (two traversal kernels
     in flight fill the SMs that one kernel's tail leaves idle: a 10k-query launch lasts as long as its slowest
     traversal), and the all-to-all + K4 merge of every batch run on ONE side stream (so the collectives are issued in
@@ -238,7 +272,7 @@ class ShardPipeline:
         return {"exchange_ms": sum(x) / len(x), "merge_ms": sum(m) / len(m), "steps": len(x)}
 
 
-class P2PShardPipeline:
+class P2PShardPipeline(_CheckedRuns):
     """The sharded batched search with search and exchange FUSED: the traversal kernel writes every rank's share of its
     results straight into that rank's receive buffer (peer memory over NVLink / NVSwitch, mapped through CUDA IPC), so
     no collective and no extra kernel moves data.  What is left of the exchange is two flags per (slot, peer):

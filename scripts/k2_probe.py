@@ -4,7 +4,7 @@ import hnsw_b200
 N = int(sys.argv[1]); d = int(sys.argv[2]); M = int(sys.argv[3]); ef = int(sys.argv[4])
 rng = np.random.default_rng(42)
 X = rng.uniform(-1, 1, (N, d)).astype(np.float32)
-g = hnsw_b200.Graph(M=M, Ml=0.25, EfSearch=ef, Distance=hnsw_b200.EuclideanDistance, Rng=hnsw_b200.GoRand(44), capacity=N)
+g = hnsw_b200.Graph(M=M, Ml=0.25, EfSearch=ef, Distance=hnsw_b200.EuclideanDistance, Rng=hnsw_b200.LevelRand(44), capacity=N)
 step = max(N // 10, 1)
 for a in range(0, N, step):
     b = min(N, a + step)

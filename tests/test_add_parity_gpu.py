@@ -84,7 +84,7 @@ def test_add_in_several_calls_and_shuffled_keys(oracle):
 def test_add_search_api_like_reference(oracle):
     # graph_test.go:86-133 through the public API: 128 1-D points, M=6, Ml=.5, ef=20, Euclidean
     import hnsw_b200
-    g = hnsw_b200.Graph(M=6, Ml=0.5, EfSearch=20, Distance=hnsw_b200.EuclideanDistance, Rng=hnsw_b200.GoRand(0))
+    g = hnsw_b200.Graph(M=6, Ml=0.5, EfSearch=20, Distance=hnsw_b200.EuclideanDistance, Rng=hnsw_b200.LevelRand(0))
     for i in range(128):
         g.Add(hnsw_b200.Node(i, [float(i)]))
     topo = g.Topography()

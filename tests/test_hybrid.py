@@ -101,9 +101,9 @@ def test_tier_switch_matches_the_plain_indexes():
     cfg = hybrid.DefaultIndexConfig()
     cfg.ExactThreshold, cfg.Distance = thr, hnsw_b200.EuclideanDistance
     idx = hybrid.HybridIndex(cfg)
-    idx.hnswIndex.Rng = hnsw_b200.GoRand(11)
+    idx.hnswIndex.Rng = hnsw_b200.LevelRand(11)
     exact = hnsw_b200.ExactIndex(hnsw_b200.EuclideanDistance)
-    graph = hnsw_b200.Graph(M=cfg.M, Ml=cfg.Ml, EfSearch=cfg.EfSearch, Distance=cfg.Distance, Rng=hnsw_b200.GoRand(11))
+    graph = hnsw_b200.Graph(M=cfg.M, Ml=cfg.Ml, EfSearch=cfg.EfSearch, Distance=cfg.Distance, Rng=hnsw_b200.LevelRand(11))
     Q = rng.uniform(-1, 1, (20, d)).astype(np.float32)
     for i in range(thr):
         idx.Add(i, V[i])

@@ -127,3 +127,51 @@ def test_failed_load_leaves_an_empty_graph(oracle):
         dg.load_flat(flat[0], flat[1], flat[2], bad, flat[4])
     # rejected while validating: the old graph is untouched and still answers
     _same(g, dg, X[:10], 5, 20)
+
+
+@pytest.mark.parametrize("kind", ["p2p", "nccl"])
+def test_pipeline_search_all_raises_the_visited_capacity_and_reissues(oracle, kind):
+    """The pipelines drive the device-pointer entry points, which report an overflowed visited set in d_counters[4]
+    instead of retrying (include/b200hnsw.h): search_all reads it, raises the capacity and issues the batches again.
+    One rank here (no process group); the 2-rank agreement on the gathered error word is in test_sharded_gpu.py."""
+    import torch
+    from hnsw_b200 import sharded
+    rng = np.random.default_rng(21)
+    n, d, k, ef, B = 3000, 32, 200, 256, 64
+    X = rng.uniform(-1, 1, (n, d)).astype(np.float32)
+    g, _, _ = build_oracle_graph(oracle, X, 16, 0.25, 64, 0)
+    dg = _device_graph(oracle, g, 16, ef, 0)
+    dg.visited_capacity = 256                                   # k = 200 visits more than that
+    dev = torch.device("cuda:0")
+    cls = sharded.P2PShardPipeline if kind == "p2p" else sharded.ShardPipeline
+    pipe = cls(dg, None, B, k, n, dev)
+    Qs = [rng.uniform(-1, 1, (B, d)).astype(np.float32) for _ in range(5)]
+    qds = [torch.from_numpy(q).to(dev) for q in Qs]
+    keep_i = torch.full((len(Qs), B, k), -9, dtype=torch.int64, device=dev)
+    keep_c = torch.full((len(Qs), B), -9, dtype=torch.int32, device=dev)
+    order = {}
+
+    def after(stream, slot):
+        i = order[slot].pop(0)
+        md, mi, mc = pipe.merged(slot)
+        keep_i[i].copy_(mi[:B], non_blocking=True)
+        keep_c[i].copy_(mc[:B], non_blocking=True)
+
+    def before(stream, slot):
+        order.setdefault(slot, []).append(before.i % len(Qs))
+        before.i += 1
+    before.i = 0
+    slots = pipe.search_all([q.data_ptr() for q in qds], before=before, after=after)
+    assert len(slots) == len(Qs)
+    assert before.i == 2 * len(Qs)                              # every batch was issued twice: 256 -> 1024 was enough
+    assert dg.visited_capacity == 1024
+    torch.cuda.synchronize(dev)
+    for i, Q in enumerate(Qs):
+        rows, dists, cnt = dg.search_rows(Q, k, ef)             # the host-pointer call (retries by itself)
+        assert np.array_equal(cnt, keep_c[i].cpu().numpy())
+        got = keep_i[i].cpu().numpy()
+        for q in range(B):                                      # K4 returns the list ascending (stable), Search heap order
+            o = np.argsort(dists[q, :cnt[q]], kind="stable")
+            assert np.array_equal(rows[q, :cnt[q]][o], got[q, :cnt[q]])
+    if hasattr(pipe, "close"):
+        pipe.close()

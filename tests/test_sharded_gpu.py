@@ -71,6 +71,28 @@ def _worker(rank, world, port, tmp, kind="nccl"):
     for s_ in range(nq):  # this shard's own lists for all queries, through the plain host call
         r_, d_, c_ = g.search_rows(Qs[s_], k, ef)
         out[f"prows{s_}"], out[f"pdd{s_}"], out[f"pcnt{s_}"] = r_, d_, c_
+    # search_all: only rank 1 starts with a visited set too small for ef = 32 walks with k = 10 ... every rank must see
+    # the gathered error word, raise its capacity and issue the list again, or the ranks would fall out of step
+    if rank == 1:
+        g.visited_capacity = 256
+        g.EfSearch = 200   # rank 1's traversals visit more than 128 nodes
+    keep_i.fill_(-9)
+    issued = [0]
+
+    def before2(stream, slot):
+        issued[0] += 1
+
+    def after2(stream, slot):
+        md, mi, mc = pipe.merged(slot)
+        keep_i[(issued[0] - 1) % nq].copy_(mi, non_blocking=True)
+    pipe.search_all([q.data_ptr() for q in qds], before=before2, after=after2)
+    torch.cuda.synchronize(dev)
+    out["sa_issued"] = np.array(issued[0])
+    out["sa_cap"] = np.array(g.visited_capacity)
+    out["sa_i"] = keep_i.cpu().numpy()
+    for s_ in range(nq):
+        r_, d_, c_ = g.search_rows(Qs[s_], k, g.EfSearch)
+        out[f"sarows{s_}"], out[f"sadd{s_}"], out[f"sacnt{s_}"] = r_, d_, c_
     np.savez(os.path.join(tmp, f"rank{rank}.npz"), **out)
     if kind == "p2p":
         pipe.close()
@@ -103,6 +125,22 @@ def test_two_gpu_pipeline_matches_merge_spec(tmp_path):
             assert np.array_equal(r[i][f"c{step}"][:q1 - q0], m[2][q0:q1])
         assert (m[1] >= 3000).any() and (m[1][m[1] >= 0] < 3000).any()
     _check_back_to_back(r, world, 6, merge_topk_ref)
+    _check_search_all(r, world, 6, merge_topk_ref)
+
+
+def _check_search_all(r, world, nq, merge_topk_ref):
+    """Both ranks issued the list twice (rank 1 overflowed at 256 entries) and the second pass is what was kept."""
+    assert int(r[0]["sa_issued"]) == int(r[1]["sa_issued"]) == 2 * nq
+    assert int(r[1]["sa_cap"]) == 1024
+    for step in range(nq):
+        all_d = np.stack([r[i][f"sadd{step}"] for i in range(world)])
+        all_i = np.stack([np.where(r[i][f"sarows{step}"] >= 0, r[i][f"sarows{step}"].astype(np.int64) + i * 3000, -1)
+                          for i in range(world)])
+        all_c = np.stack([r[i][f"sacnt{step}"] for i in range(world)])
+        m = merge_topk_ref(all_d, all_i, all_c, 10)
+        for i in range(world):
+            q0, q1 = int(r[i]["q0"]), int(r[i]["q1"])
+            assert np.array_equal(r[i]["sa_i"][step][:q1 - q0], m[1][q0:q1])
 
 
 def _check_back_to_back(r, world, nq, merge_topk_ref):
@@ -197,3 +235,4 @@ def test_two_gpu_fused_search_exchange_matches_merge_spec(tmp_path):
     mp.spawn(_worker, args=(world, port, str(tmp_path), "p2p"), nprocs=world, join=True)
     r = [np.load(tmp_path / f"rank{i}.npz") for i in range(world)]
     _check_back_to_back(r, world, 11, merge_topk_ref)
+    _check_search_all(r, world, 11, merge_topk_ref)
