@@ -364,7 +364,7 @@ def exact_block(ctx, args, wl, X, Qh, steps):
                         "frac": flops / (ms / 1e3) / 1e12 / tpeak, "traffic": None,
                         "kernel": "b200::exact_gemm_kernel (K3 tensor path) + re-rank, whole call",
                         "algorithmic_flops_per_launch": flops, "peak_source": psrc + " bf16_tflops_sustained",
-                        "tensor_pipe_active_ncu": "profiles/r5a_k3_gemm_counters.json (sm__pipe_tensor_cycles_active)"},
+                        "tensor_pipe_active_ncu": "profiles/r5n_k3_v3_counters.json (sm__pipe_tensor_cycles_active 43 %)"},
            "path": {1: "scan", 2: "tensor"}.get(int(st["launches"]), str(st["launches"])),
            "candidates_per_query": st["dist_evals"] / B, "fallback_queries": int(st["expansions"]),
            "add_vec_per_s": n / add_s, "gpu_launches": steps * 4, "clocks": ctx.sampler.summary(mark),

@@ -116,6 +116,27 @@ __device__ __forceinline__ void tmem_ld_wait(uint32_t (&v)[32]) {
                :
                : "memory");
 }
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, "
+      "[%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait16(uint32_t (&v)[16]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]),
+                 "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15])
+               :
+               : "memory");
+}
+__device__ __forceinline__ void tmem_ld4_sync(uint32_t taddr, uint32_t (&v)[4]) {  // load + wait (rare path)
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3])
+               : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]) : : "memory");
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
@@ -186,6 +207,28 @@ __device__ __forceinline__ void sts_f1(uint32_t addr, float v) {
 template <int METRIC>
 __device__ __forceinline__ float gm_score(float acc, float a, float qf) {
   return METRIC == 0 ? fmaf(qf, acc, a) : fmaf(acc * a, qf, 1.f);
+}
+
+// four scores with two packed FMAs (FFMA2; each half a plain IEEE rn operation, so the values are those of gm_score)
+template <int METRIC>
+__device__ __forceinline__ void gm_score4(uint32_t v0, uint32_t v1, uint32_t v2, uint32_t v3, const float4 &a, f32x2 qf2,
+                                          float &s0, float &s1, float &s2, float &s3) {
+  const f32x2 acc01 = pk2(__uint_as_float(v0), __uint_as_float(v1)), acc23 = pk2(__uint_as_float(v2), __uint_as_float(v3));
+  const f32x2 a01 = pk2(a.x, a.y), a23 = pk2(a.z, a.w);
+  f32x2 r01, r23;
+  if (METRIC == 0) {
+    r01 = fma2(qf2, acc01, a01);
+    r23 = fma2(qf2, acc23, a23);
+  } else {
+    const f32x2 one2 = pk2(1.f, 1.f);
+    f32x2 m01, m23;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(m01) : "l"(acc01), "l"(a01));
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(m23) : "l"(acc23), "l"(a23));
+    r01 = fma2(m01, qf2, one2);
+    r23 = fma2(m23, qf2, one2);
+  }
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(s0), "=f"(s1) : "l"(r01));
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(s2), "=f"(s3) : "l"(r23));
 }
 
 // min.f32 with three inputs (sm_100: one FMNMX3); a NaN input is dropped unless all are NaN, as with fminf
@@ -319,7 +362,8 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     const float margin = live_q ? p.q_margin[q] : 0.f;
     const float qf = live_q ? p.q_inv[q] : 0.f;  // turns the accumulator into -2 q.x (Euclidean) or -q.x/|q| (cosine)
     const float INF = __int_as_float(0x7f800000);
-    float thr = INF;
+    const f32x2 qf2 = pk2(qf, qf);
+    float thr = INF, tau_loc = INF;  // tau_loc: max over this thread's slots when it was last computed
     int sub = 0;
     uint32_t sl_a = slots_a;                   // slot the next block minimum goes to
     // Candidates are staged per thread (cbuf[i][et], conflict-free) and appended to the query's global list a batch at
@@ -368,33 +412,53 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       mbar_wait(bar_tfull + 8 * as, (idx >> 1) & 1);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + as * GM_N + ch0 * 32;
-      uint32_t va[32], vb[32];
-      tmem_ld32(taddr, va);
+      uint32_t va[16], vb[16];  // the two 16-column halves of a 32-column block; the next half is in flight while
+      tmem_ld16(taddr, va);     // this one is scored
 #pragma unroll
       for (int cl = 0; cl < CHUNKS; cl++) {
-        uint32_t (&v)[32] = (cl & 1) == 0 ? va : vb;
-        tmem_ld_wait(v);  // chunk cl has landed; chunk cl+1 is requested before cl is looked at
-        if (cl + 1 < CHUNKS) tmem_ld32(taddr + (cl + 1) * 32, (cl & 1) == 0 ? vb : va);
         const uint32_t axc = ax + (uint32_t)(cl * 32) * 4u;
-        float m8[8], r8[8];
+        float g8[8];
+        float4 a4[4];  // the per-row terms of the half are fetched under the latency of the accumulator load
 #pragma unroll
-        for (int j4 = 0; j4 < 8; j4++) {  // 32 independent scores: no branch, no dependent chain
-          const float4 a = lds_f4(axc + j4 * 16);
-          const float s0 = gm_score<METRIC>(__uint_as_float(v[4 * j4 + 0]), a.x, qf);
-          const float s1 = gm_score<METRIC>(__uint_as_float(v[4 * j4 + 1]), a.y, qf);
-          const float s2 = gm_score<METRIC>(__uint_as_float(v[4 * j4 + 2]), a.z, qf);
-          r8[j4] = gm_score<METRIC>(__uint_as_float(v[4 * j4 + 3]), a.w, qf);
-          m8[j4] = fmin3(s0, s1, s2);  // three-input minimum (FMNMX3): 16 instructions per 32 scores instead of 31;
-        }                              // like fminf it drops NaN (dead rows)
-        const float bmin = fmin3(fmin3(fmin3(m8[0], m8[1], m8[2]), fmin3(m8[3], m8[4], m8[5]), fmin3(m8[6], m8[7], r8[0])),
-                                 fmin3(r8[1], r8[2], r8[3]), fmin3(fmin3(r8[4], r8[5], r8[6]), r8[7], r8[7]));
-        if (emit && bmin <= thr) {  // some row of this block passes the filter: score the block again, row by row
+        for (int j4 = 0; j4 < 4; j4++) a4[j4] = lds_f4(axc + j4 * 16);
+        tmem_ld_wait16(va);
+        tmem_ld16(taddr + cl * 32 + 16, vb);
+#pragma unroll
+        for (int j4 = 0; j4 < 4; j4++) {  // 16 independent scores, two per packed FMA; no branch, no dependent chain
+          float s0, s1, s2, s3;
+          gm_score4<METRIC>(va[4 * j4 + 0], va[4 * j4 + 1], va[4 * j4 + 2], va[4 * j4 + 3], a4[j4], qf2, s0, s1, s2, s3);
+          g8[j4] = fminf(fmin3(s0, s1, s2), s3);  // FMNMX3 + FMNMX; like fminf they drop NaN (dead rows)
+        }
+#pragma unroll
+        for (int j4 = 0; j4 < 4; j4++) a4[j4] = lds_f4(axc + (j4 + 4) * 16);
+        tmem_ld_wait16(vb);
+        if (cl + 1 < CHUNKS) tmem_ld16(taddr + (cl + 1) * 32, va);
+#pragma unroll
+        for (int j4 = 0; j4 < 4; j4++) {
+          float s0, s1, s2, s3;
+          gm_score4<METRIC>(vb[4 * j4 + 0], vb[4 * j4 + 1], vb[4 * j4 + 2], vb[4 * j4 + 3], a4[j4], qf2, s0, s1, s2, s3);
+          g8[4 + j4] = fminf(fmin3(s0, s1, s2), s3);
+        }
+        const float bmin = fmin3(fmin3(g8[0], g8[1], g8[2]), fmin3(g8[3], g8[4], g8[5]), fminf(g8[6], g8[7]));
+        // Some row of this block passes some lane's filter (warp-uniform test: 32 lanes = 32 queries, so about a third
+        // of the blocks get here): only the groups of four columns whose minimum passes are scored again, row by row.
+        if (__any_sync(FULL, emit && bmin <= thr)) {
           unsigned pass = 0;
 #pragma unroll
-          for (int j = 0; j < 32; j++) {  // branch-free; dead rows score +inf / NaN
-            const float sj = gm_score<METRIC>(__uint_as_float(v[j]), lds_f1(axc + j * 4), qf);
-            pass |= (unsigned)((sj <= thr) & (sj < INF)) << j;
+          for (int j4 = 0; j4 < 8; j4++) {
+            if (__any_sync(FULL, emit && g8[j4] <= thr)) {
+              // the accumulators are still in TMEM (the stage is released at the end of the tile): four columns again
+              uint32_t w[4];
+              tmem_ld4_sync(taddr + cl * 32 + j4 * 4, w);
+              const float4 a = lds_f4(axc + j4 * 16);
+              float s[4];
+              gm_score4<METRIC>(w[0], w[1], w[2], w[3], a, qf2, s[0], s[1], s[2], s[3]);
+#pragma unroll
+              for (int i = 0; i < 4; i++)  // dead rows score +inf / NaN
+                pass |= (unsigned)((s[i] <= thr) & (s[i] < INF)) << (4 * j4 + i);
+            }
           }
+          if (!emit) pass = 0;
           const int np = __popc(pass);
           const int row0 = tile * GM_N + (ch0 + cl) * 32;
           if (ccnt + np > GM_CB) flush();
@@ -416,11 +480,13 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
             }
           }
         }
-        if (__any_sync(FULL, ccnt >= GM_CB / 2)) flush();
         // slot `sub mod k` holds the minimum over a set of rows disjoint from every other slot's set
-        if (bmin < lds_f1(sl_a)) {
-          sts_f1(sl_a, bmin);
-          changed = true;
+        {
+          const float old = lds_f1(sl_a);
+          if (bmin < old) {
+            sts_f1(sl_a, bmin);
+            changed |= old >= tau_loc;  // tau = max(slots) can only move when the slot that held the maximum is lowered
+          }
         }
         sl_a += 4;
         if (sl_a == slots_end) sl_a = slots_a;
@@ -429,6 +495,7 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
+      if (__any_sync(FULL, ccnt >= GM_CB / 2)) flush();  // once per tile: a block that would overflow the stage flushes first
       // next tile's terms into the other buffer (this warp's reads of it ended one tile ago)
       if (idx + 1 < seq) aux_store(as ^ 1, nx);
       __syncwarp();
@@ -437,12 +504,20 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         // and CTAs that work on this query: slot j of each covers rows disjoint from slot j' of any other, so the
         // element-wise minimum is again k minima over k disjoint row sets.
         const int done = idx + 1;
-        if (sub - CHUNKS < kk || (done & (done - 1)) == 0 || (done & 31) == 0 || idx == seq - 1) {
+        if (sub - CHUNKS < kk || (done & (done - 1)) == 0 || (done & 63) == 0 || idx == seq - 1) {
           uint32_t *sg = p.slots_g + q * kk;
-          for (int j = 0; j < kk; j++) {
-            const uint32_t mine = ord_bits(lds_f1(slots_a + j * 4));
-            const uint32_t old = atomicMin(&sg[j], mine);
-            if (old < mine) sts_f1(slots_a + j * 4, ord_float(old));
+          // reductions without a return value (RED), then the merged values read back eight at a time: two round trips
+          // to L2 for k = 10 instead of one per four slots.  A value read here may miss a concurrent update: every value
+          // ever stored in sg[j] is the score of a row of class j, so whatever is read is a valid bound.
+          for (int j = 0; j < kk; j++) atomicMin(&sg[j], ord_bits(lds_f1(slots_a + j * 4)));
+          for (int j0 = 0; j0 < kk; j0 += 8) {
+            uint32_t got[8];
+#pragma unroll
+            for (int i = 0; i < 8; i++) got[i] = j0 + i < kk ? __ldcg(&sg[j0 + i]) : 0xffffffffu;
+#pragma unroll
+            for (int i = 0; i < 8; i++)
+              if (j0 + i < kk && got[i] < ord_bits(lds_f1(slots_a + (j0 + i) * 4)))
+                sts_f1(slots_a + (j0 + i) * 4, ord_float(got[i]));
           }
           changed = true;
         }
@@ -450,6 +525,7 @@ exact_gemm_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
           // k distinct rows score <= max(slots): an upper bound on the k-th smallest score of the whole index
           float tau = lds_f1(slots_a);
           for (int j = 1; j < kk; j++) tau = fmaxf(tau, lds_f1(slots_a + j * 4));
+          tau_loc = tau;
           thr = fminf(thr, tau + margin);
         }
       }
