@@ -3,6 +3,7 @@
 N=${1:-4}
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=index,name --format=csv,noheader | head -8; nproc
+nvidia-smi topo -m 2>&1 | head -24 | tee gpurun_out/r5s_topo_${N}.txt
 (timeout 900 python -m pytest tests/test_sharded_gpu.py -m gpu -x -q 2>&1 | tail -5) | tee gpurun_out/r5s_pytest_2gpu_on_${N}.log
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29611"
 SECONDS=0

@@ -71,28 +71,34 @@ def _worker(rank, world, port, tmp, kind="nccl"):
     for s_ in range(nq):  # this shard's own lists for all queries, through the plain host call
         r_, d_, c_ = g.search_rows(Qs[s_], k, ef)
         out[f"prows{s_}"], out[f"pdd{s_}"], out[f"pcnt{s_}"] = r_, d_, c_
-    # search_all: only rank 1 starts with a visited set too small for ef = 32 walks with k = 10 ... every rank must see
-    # the gathered error word, raise its capacity and issue the list again, or the ranks would fall out of step
+    # search_all: a second pipeline with k = 200 (a traversal then visits more than 200 nodes); only rank 1 starts with
+    # the smallest visited set (256 entries, full at 128).  Every rank must see the gathered error word, raise its
+    # capacity and issue the list again, or the ranks would fall out of step.
+    k2 = 200
     if rank == 1:
         g.visited_capacity = 256
-        g.EfSearch = 200   # rank 1's traversals visit more than 128 nodes
-    keep_i.fill_(-9)
+    cls = sharded.P2PShardPipeline if kind == "p2p" else sharded.ShardPipeline
+    pipe2 = cls(g, dist, B, k2, n, dev)
+    seg2 = pipe2.seg
+    keep2 = torch.full((nq, seg2, k2), -9, dtype=torch.int64, device=dev)
     issued = [0]
 
     def before2(stream, slot):
         issued[0] += 1
 
     def after2(stream, slot):
-        md, mi, mc = pipe.merged(slot)
-        keep_i[(issued[0] - 1) % nq].copy_(mi, non_blocking=True)
-    pipe.search_all([q.data_ptr() for q in qds], before=before2, after=after2)
+        md, mi, mc = pipe2.merged(slot)
+        keep2[(issued[0] - 1) % nq].copy_(mi, non_blocking=True)
+    pipe2.search_all([q.data_ptr() for q in qds], before=before2, after=after2)
     torch.cuda.synchronize(dev)
     out["sa_issued"] = np.array(issued[0])
     out["sa_cap"] = np.array(g.visited_capacity)
-    out["sa_i"] = keep_i.cpu().numpy()
+    out["sa_i"] = keep2.cpu().numpy()
     for s_ in range(nq):
-        r_, d_, c_ = g.search_rows(Qs[s_], k, g.EfSearch)
+        r_, d_, c_ = g.search_rows(Qs[s_], k2, ef)
         out[f"sarows{s_}"], out[f"sadd{s_}"], out[f"sacnt{s_}"] = r_, d_, c_
+    if kind == "p2p":
+        pipe2.close()
     np.savez(os.path.join(tmp, f"rank{rank}.npz"), **out)
     if kind == "p2p":
         pipe.close()
@@ -129,15 +135,16 @@ def test_two_gpu_pipeline_matches_merge_spec(tmp_path):
 
 
 def _check_search_all(r, world, nq, merge_topk_ref):
-    """Both ranks issued the list twice (rank 1 overflowed at 256 entries) and the second pass is what was kept."""
-    assert int(r[0]["sa_issued"]) == int(r[1]["sa_issued"]) == 2 * nq
-    assert int(r[1]["sa_cap"]) == 1024
+    """Both ranks issued the list the same number of times, more than once (rank 1 overflowed at 256 entries), rank 1
+    ended with a larger visited set, and the last pass is what was kept."""
+    assert int(r[0]["sa_issued"]) == int(r[1]["sa_issued"]) and int(r[0]["sa_issued"]) in (2 * nq, 3 * nq)
+    assert int(r[1]["sa_cap"]) >= 1024
     for step in range(nq):
         all_d = np.stack([r[i][f"sadd{step}"] for i in range(world)])
         all_i = np.stack([np.where(r[i][f"sarows{step}"] >= 0, r[i][f"sarows{step}"].astype(np.int64) + i * 3000, -1)
                           for i in range(world)])
         all_c = np.stack([r[i][f"sacnt{step}"] for i in range(world)])
-        m = merge_topk_ref(all_d, all_i, all_c, 10)
+        m = merge_topk_ref(all_d, all_i, all_c, 200)
         for i in range(world):
             q0, q1 = int(r[i]["q0"]), int(r[i]["q1"])
             assert np.array_equal(r[i]["sa_i"][step][:q1 - q0], m[1][q0:q1])
