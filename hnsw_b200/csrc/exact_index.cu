@@ -190,6 +190,7 @@ int b200exact::ensure_capacity(int64_t rows) {
   if ((rc = grow_arr(d_alive, n, nc, stream))) return rc;
   if ((rc = grow_arr(d_vech, n * kpad, nc * kpad, stream))) return rc;
   if ((rc = grow_arr(d_aux, n, nc, stream))) return rc;
+  if (metric == B200HNSW_EUCLIDEAN && (rc = grow_arr(d_vext, n * 16, nc * 16, stream))) return rc;
   cap = nc;
   tmap_rows = -1;
   return 0;
@@ -408,6 +409,7 @@ void b200exact_destroy(b200exact_t *x) {
   cudaFree(x->d_alive);
   cudaFree(x->d_vech);
   cudaFree(x->d_aux);
+  cudaFree(x->d_vext);
   cudaFree(x->d_scratch);
   cudaFree(x->d_maxn2);
   cudaFree(x->d_gemm_ws);
@@ -463,6 +465,10 @@ int b200exact_remove(b200exact_t *x, const int64_t *rows, int64_t n) {
     // the tensor path skips the row: |x|^2 = +inf (L2) / 1/|x| = NaN scores it out of every candidate list
     const float dead = x->metric == B200HNSW_EUCLIDEAN ? __builtin_inff() : __builtin_nanf("");
     B200_CUDA(cudaMemcpyAsync(x->d_aux + r, &dead, sizeof dead, cudaMemcpyHostToDevice, x->stream));
+    if (x->d_vext) {  // the folded per-row term: -inf makes the accumulator -inf, i.e. the score +inf
+      static const uint16_t dead_h[4] = {0xfc00u, 0, 0, 0};
+      B200_CUDA(cudaMemcpyAsync(x->d_vext + r * 16, dead_h, sizeof dead_h, cudaMemcpyHostToDevice, x->stream));
+    }
   }
   B200_CUDA(cudaStreamSynchronize(x->stream));
   return 0;

@@ -14,6 +14,8 @@ struct b200exact {
   uint8_t *d_alive = nullptr;        // [cap] 0 = deleted (exact.go:114-145)
   __half *d_vech = nullptr;          // [cap][kpad] fp16 copy of the rows scaled by 2^sx_exp, for the tensor path
   float *d_aux = nullptr;            // [cap] L2: |x|^2, cosine: 1/|x|; +inf / 0 for deleted rows
+  __half *d_vext = nullptr;          // [cap][16] L2 only: -|x 2^sx|^2 2^-11 in three fp16 pieces (extra K columns of the
+                                     // tensor path: the per-row term of the score comes out of the GEMM itself)
   int sx_exp = 0;                    // power-of-two scale of d_vech: chosen so that every component fits fp16
   bool have_scale = false;
   std::vector<uint8_t> h_alive;
@@ -22,7 +24,7 @@ struct b200exact {
   cudaStream_t stream = nullptr;
   void *d_scratch = nullptr;
   size_t scratch_bytes = 0;
-  void *tmap_x = nullptr;            // CUtensorMap of d_vech (exact_gemm.cu), rebuilt when storage moves
+  void *tmap_x = nullptr;            // CUtensorMap of d_vech, then of d_vext (exact_gemm.cu), rebuilt when storage moves
   int64_t tmap_rows = -1;
   uint32_t *d_maxn2 = nullptr;       // [0] bits of max |x|^2, [1] bits of min |x|^2 > 0, [2] bits of max |x_i| over rows ever added
   int64_t aux_dead_cap = -1;         // capacity up to which d_aux of unused rows holds the dead value

@@ -83,6 +83,7 @@ def test_exact_api_like_reference(oracle):
     (70000, 1024, 10, 1, 200),   # C5 shape
     (50000, 96, 32, 0, 130),
     (33000, 200, 10, 1, 257),    # dim not a multiple of 64
+    (60000, 320, 10, 0, 150),    # Euclidean with the query tile NOT resident: the fold block travels in the main ring
 ])
 def test_exact_tensor_path_matches_oracle(oracle, n, d, k, metric, B):
     rng = np.random.default_rng(6)
@@ -92,3 +93,48 @@ def test_exact_tensor_path_matches_oracle(oracle, n, d, k, metric, B):
     Q = rng.standard_normal((B, d)).astype(np.float32)
     Q[:5] = X[100:105]  # exact hits
     _check(oracle, X, Q, k, metric, "tensor")
+
+
+def test_exact_tensor_path_query_scales_and_deletes(oracle):
+    """Euclidean tensor path: the per-row term comes out of the GEMM (fold block, exact_gemm.cu), which needs the query's
+    fp16 scale within a window of the rows'.  Queries far outside it (x 1e4: moved into the window; x 1e5: given an infinite
+    margin and answered by the scan path; x 1e-3: a smaller scale) and rows of very different norms must still
+    give the oracle's rows and bits.  Deleted rows (the nearest ones among them) never come back."""
+    import hnsw_b200
+    os.environ["B200EXACT_PATH"] = "tensor"
+    try:
+        rng = np.random.default_rng(16)
+        n, d, k, B = 40000, 128, 10, 96
+        X = rng.uniform(-1, 1, (n, d)).astype(np.float32)
+        X[7] *= 4.0                                      # one row sets the scale of the fp16 copy
+        X[11:200] *= 0.01
+        Q = rng.standard_normal((B, d)).astype(np.float32)
+        Q[:4] *= 1e5                                     # outside the window: scan path
+        Q[4:8] *= 1e4                                    # moved into the window
+        Q[8:16] *= 1e-3
+        Q[16:20] = X[300:304]
+        ix = hnsw_b200.NewExactIndex(hnsw_b200.EuclideanDistance)
+        ix.BatchAdd(list(range(n)), X)
+        rows, dists, counts = ix.search_rows(Q, k)
+        st = ix.last_stats
+        assert st["launches"] == 2, st
+        assert 4 <= st["expansions"] <= 12, st          # the x 1e5 queries are answered by the scan, hardly any other
+        o_idx, o_d = oracle.exact_batch_search(X, Q, k, 0, n_threads=8)
+        assert np.array_equal(rows, o_idx.astype(np.int64))
+        assert np.array_equal(dists.view(np.uint32), o_d.view(np.uint32))
+        # delete the nearest rows of the ordinary queries and 500 others
+        gone = np.unique(np.concatenate([rows[20:, :3].ravel(), rng.choice(n, 500, replace=False)]))
+        for key in gone:
+            assert ix.Delete(int(key))
+        keep = np.ones(n, bool)
+        keep[gone] = False
+        ids = np.nonzero(keep)[0]
+        rows2, dists2, counts2 = ix.search_rows(Q[16:], k)
+        assert ix.last_stats["launches"] == 2
+        o_idx2, o_d2 = oracle.exact_batch_search(X[keep], Q[16:], k, 0, n_threads=8)
+        assert np.array_equal(rows2, ids[o_idx2].astype(np.int64))
+        assert np.array_equal(dists2.view(np.uint32), o_d2.view(np.uint32))
+        assert not np.isin(rows2, gone).any()
+        ix.Close()
+    finally:
+        os.environ.pop("B200EXACT_PATH", None)
