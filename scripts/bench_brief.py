@@ -17,8 +17,8 @@ def brief(name, b):
           f" (1 caller {e.get('pinned_1_caller', 0) / 1e6:.2f}M, pageable {e.get('pageable_1_caller', 0) / 1e6:.2f}M)"
           f" frac {r.get('frac', 0):.2f} solo {r.get('algorithmic_frac_solo') or 0:.2f} dram {r.get('dram_frac') or 0:.3f}"
           f" E/q {r.get('dist_evals_per_query', 0):.0f} recall {b.get('recall_at_10')}"
-          f" parity {[p.get(k) for k in ('rows_equal', 'dists_bit_equal', 'counts_equal')]} cpu {cb.get('value', 0) / 1e6:.3f}M"
-          f" (1 thread {cb.get('single_thread_value', 0) / 1e3:.1f}k)")
+          f" parity {[p.get(k) for k in ('rows_equal', 'dists_bit_equal', 'counts_equal')]} cpu {(cb.get('value') or 0) / 1e6:.3f}M"
+          f" (1 thread {(cb.get('single_thread_value') or 0) / 1e3:.1f}k)")
 
 
 brief("headline", l)

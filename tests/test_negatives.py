@@ -76,3 +76,66 @@ def test_negatives_match_restatement(oracle, metric_name, d, n):
         assert [nd.Key for nd in gb] == search_with_negatives_ref(oracle, g, metric, X, keys, q, ng, k, w, ef)
     # keys 7-9 exist in this graph, so the +0.2 boost was exercised whenever they were candidates
     assert any(any(nd.Key in (7, 8, 9) for nd in gb) for gb in got_b) or True
+
+
+def _animals(levels_seed=3):
+    """negative_test.go:11-29 / 148-166: nine 3-d vectors in three groups, M=16, Ml=0.25, EfSearch=20, cosine."""
+    import hnsw_b200
+    g = hnsw_b200.NewGraphWithConfig(16, 0.25, 20, hnsw_b200.CosineDistance)
+    g.Rng = hnsw_b200.LevelRand(levels_seed)
+    vecs = {1: [1.0, 0.2, 0.1], 2: [0.9, 0.3, 0.2], 3: [0.8, 0.3, 0.3],      # dog, puppy, canine
+            4: [0.1, 1.0, 0.2], 5: [0.2, 0.9, 0.3], 6: [0.3, 0.8, 0.3],      # cat, kitten, feline
+            7: [0.1, 0.2, 1.0], 8: [0.2, 0.3, 0.9], 9: [0.3, 0.3, 0.8]}      # bird, sparrow, avian
+    for key, v in vecs.items():
+        g.Add(hnsw_b200.MakeNode(key, v))
+    return g
+
+
+def _pos(results, key):
+    for i, r in enumerate(results):
+        if r.Key == key:
+            return i
+    return -1
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("levels_seed", [1, 2, 3, 4, 5])
+def test_reference_negative_test_go_assertions(levels_seed):
+    """The assertions of the reference's own negative_test.go (TestSearchWithNegative, lines 31-145, and
+    TestBatchSearchWithNegatives, lines 168-259), replayed through the public API on the device.  The levels come from
+    our own random stream (Go's math/rand cannot be reproduced here), so five different streams are tried: the
+    reference's assertions do not depend on the levels drawn."""
+    g = _animals(levels_seed)
+    dog, puppy, cat, kitten = [1.0, 0.2, 0.1], [0.9, 0.3, 0.2], [0.1, 1.0, 0.2], [0.2, 0.9, 0.3]
+    # "Basic search without negative" (31-44)
+    res = g.Search(dog, 3)
+    assert len(res) == 3 and {r.Key for r in res} == {1, 2, 3}
+    # "Search with negative example" (46-85)
+    res = g.SearchWithNegative(dog, puppy, 3, 0.5)
+    assert len(res) == 3 and res[0].Key == 1
+    regular = g.Search(dog, 9)
+    np_, rp = _pos(res, 2), _pos(regular, 2)
+    if np_ != -1 and rp != -1:
+        assert np_ > rp
+    # "Search with multiple negative examples" (87-108)
+    res = g.SearchWithNegatives([0.4, 0.4, 0.4], [dog, cat], 3, 0.7)
+    assert len(res) == 3 and sum(7 <= r.Key <= 9 for r in res) >= 1
+    # "Negative weight impact" (110-145)
+    low = g.SearchWithNegative(dog, puppy, 3, 0.1)
+    high = g.SearchWithNegative(dog, puppy, 3, 0.9)
+    lp, hp = _pos(low, 2), _pos(high, 2)
+    if lp != -1 and hp != -1:
+        assert hp > lp
+    elif lp != -1:
+        assert hp == -1
+    # TestBatchSearchWithNegatives: "Batch search with negatives" (168-194)
+    res = g.BatchSearchWithNegatives([dog, cat], [[puppy], [kitten]], 3, 0.5)
+    assert len(res) == 2 and len(res[0]) == 3 and len(res[1]) == 3
+    assert res[0][0].Key == 1 and res[1][0].Key == 4
+    # "Batch search with empty negatives" (196-220)
+    res = g.BatchSearchWithNegatives([dog, cat], [[], [kitten]], 3, 0.5)
+    assert len(res) == 2 and len(res[0]) == 3 and len(res[1]) == 3
+    assert res[0][0].Key == 1 and res[1][0].Key == 4
+    # "Batch search with multiple negatives" (222-258)
+    res = g.BatchSearchWithNegatives([[0.4, 0.4, 0.4]], [[dog, cat]], 3, 0.7)
+    assert len(res) == 1 and len(res[0]) == 3 and sum(7 <= r.Key <= 9 for r in res[0]) >= 1
