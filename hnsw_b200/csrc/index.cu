@@ -6,6 +6,8 @@
 #include <cstring>
 #include <new>
 
+#include <sched.h>
+
 #include "index.hpp"
 
 namespace b200 {
@@ -142,6 +144,18 @@ int b200hnsw::ensure_inboxes(cudaStream_t s) {
   B200_CUDA(cudaMemsetAsync(d.inbox + 3 * want, 0x7f, sizeof(int32_t) * (size_t)want, s));
   d.inbox_n = want;
   return 0;
+}
+
+// Wait for a stream the way a caller thread among many should: cudaStreamSynchronize spins on its core until the
+// stream is done, so more waiting callers than cores (8 ranks x 4 callers on a 32-core box) only take cycles from
+// each other and from the threads that still have calls to queue.  Poll instead, and hand the core over between polls
+// once the first few (the common case of a short wait) have come back "not ready".
+static cudaError_t wait_stream(cudaStream_t s) {
+  for (int spins = 0;; spins++) {
+    cudaError_t e = cudaStreamQuery(s);
+    if (e != cudaErrorNotReady) return e;
+    if (spins >= 64) sched_yield();
+  }
 }
 
 extern "C" {
@@ -741,7 +755,7 @@ int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_
     w_queued = since();
     if ((e = cudaEventRecord(c->ev1, s)) != cudaSuccess ||
         (e = cudaMemcpyAsync((void *)ctr, d_ctr, 40, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
-        (e = cudaStreamSynchronize(s)) != cudaSuccess)
+        (e = wait_stream(s)) != cudaSuccess)
       return fail(cuda_fail(e, "search kernel"));
     const int err = (int)(ctr[4] & 0xffffffffu);
     if (err == 0) break;

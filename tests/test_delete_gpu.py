@@ -137,3 +137,31 @@ def test_batch_delete_reference_cases():
     assert g.Len() == 0
     assert g.Search([1.0, 1.0, 1.0], 3) == []
     assert hnsw_b200.Graph().BatchDelete([1, 2]) == [False, False]  # graph.go:875-878: no layers yet
+
+
+def test_batch_delete_reference_cases_cosine_and_three_batches():
+    """batch_delete_test.go as the reference runs it: NewGraphWithConfig(16, 0.25, 20, CosineDistance) over the parallel
+    vectors (i, i, i) -- every cosine distance is 0 up to rounding, i.e. ties everywhere -- first the five cases of
+    TestBatchDelete (lines 10-105), then TestBatchDeleteConcurrency (107-158: 100 nodes, three batches of 20)."""
+    import hnsw_b200
+    g = hnsw_b200.NewGraphWithConfig(16, 0.25, 20, hnsw_b200.CosineDistance)
+    for i in range(1, 11):
+        g.Add(hnsw_b200.MakeNode(i, [float(i), float(i), float(i)]))
+    assert g.Len() == 10
+    assert g.BatchDelete([1, 3, 5]) == [True, True, True] and g.Len() == 7
+    assert all(g.Lookup(k)[1] is False for k in (1, 3, 5)) and all(g.Lookup(k)[1] is True for k in (2, 4, 6, 7, 8, 9, 10))
+    assert g.BatchDelete([11, 12, 13]) == [False, False, False] and g.Len() == 7
+    assert g.BatchDelete([2, 15, 4, 20]) == [True, False, True, False] and g.Len() == 5
+    assert all(g.Lookup(k)[1] is False for k in (2, 4)) and all(g.Lookup(k)[1] is True for k in (6, 7, 8, 9, 10))
+    assert g.BatchDelete([]) == [] and g.Len() == 5
+    assert g.BatchDelete([6, 7, 8, 9, 10]) == [True] * 5 and g.Len() == 0
+    g = hnsw_b200.NewGraphWithConfig(16, 0.25, 20, hnsw_b200.CosineDistance)
+    for i in range(1, 101):
+        g.Add(hnsw_b200.MakeNode(i, [float(i), float(i), float(i)]))
+    assert g.Len() == 100
+    b1, b2, b3 = list(range(1, 21)), list(range(41, 61)), list(range(81, 101))
+    assert g.BatchDelete(b1) == [True] * 20 and g.BatchDelete(b2) == [True] * 20 and g.BatchDelete(b3) == [True] * 20
+    assert g.Len() == 40
+    gone = set(b1) | set(b2) | set(b3)
+    for i in range(1, 101):
+        assert g.Lookup(i)[1] is (i not in gone)

@@ -99,12 +99,15 @@ def _pos(results, key):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("levels_seed", [1, 2, 3, 4, 5])
+@pytest.mark.parametrize("levels_seed", [1, 3, 4, 5])
 def test_reference_negative_test_go_assertions(levels_seed):
     """The assertions of the reference's own negative_test.go (TestSearchWithNegative, lines 31-145, and
     TestBatchSearchWithNegatives, lines 168-259), replayed through the public API on the device.  The levels come from
-    our own random stream (Go's math/rand cannot be reproduced here), so five different streams are tried: the
-    reference's assertions do not depend on the levels drawn."""
+    our own random stream (Go's math/rand cannot be reproduced here); four streams are tried.  The assertions are NOT
+    independent of the levels: with stream 2 the layer-0 entry differs and the reference's own result queue (heap.Max()
+    is the last array slot, graph.go:150-155) drops one of the three dog vectors from Search(dog, 3) -- on the device
+    and in the oracle alike (profiles/r6c_pytest_negatives.log); the reference's test passes under the levels Go's
+    stream happens to draw.  Device-equals-oracle on arbitrary levels is test_negatives_match_restatement."""
     g = _animals(levels_seed)
     dog, puppy, cat, kitten = [1.0, 0.2, 0.1], [0.9, 0.3, 0.2], [0.1, 1.0, 0.2], [0.2, 0.9, 0.3]
     # "Basic search without negative" (31-44)
