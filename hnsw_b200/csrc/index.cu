@@ -7,6 +7,8 @@
 #include <new>
 
 #include <sched.h>
+#include <thread>
+#include <vector>
 
 #include "index.hpp"
 
@@ -667,6 +669,15 @@ int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_
   // Page-locked result buffers are written by the kernel itself (80 B of posted PCIe writes per query at the end of
   // its traversal): no device staging, no D2H copies behind the kernel.
   bool direct_out = false;
+  // Pageable buffers (what a cgo host passes from make([]float32, ...)): cudaMemcpyAsync from or to pageable memory goes
+  // through the driver's own staging, synchronously, at ~9 GB/s here.  The call stages them itself instead, through the
+  // context's page-locked buffer: queries are copied there a chunk at a time by this thread (each chunk's H2D copy and
+  // traversal run while the next chunk is being copied), the kernel writes its results there, and they are copied out
+  // after the wait.  B200HNSW_NO_HOST_STAGING=1 keeps the driver's path.
+  static const bool own_staging = getenv("B200HNSW_NO_HOST_STAGING") == nullptr;
+  const bool q_pageable = own_staging && mapped_host(queries) == nullptr && qb >= (256u << 10);
+  bool out_staged = false;
+  char *h_stage_q = nullptr, *h_stage_o = nullptr;
   if (!getenv("B200HNSW_NO_DIRECT_OUT")) {
     void *zr = mapped_host(out_rows), *zd = mapped_host(out_dists), *zc = mapped_host(out_counts);
     if (zr && zd && zc) {
@@ -674,22 +685,74 @@ int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_
       d_dists = (float *)zd;
       d_cnt = (int32_t *)zc;
       direct_out = true;
+    } else if (own_staging && !zr && !zd && !zc) {
+      out_staged = true;
+    }
+  }
+  if (q_pageable || out_staged) {
+    if ((rc = c->reserve_pinned(256 + (q_pageable ? al(qb) : 0) + (out_staged ? al(rb) + al(db) + al(cb) : 0))))
+      return fail(rc);
+    char *hp = (char *)c->h_pinned + 256;  // the first 64 bytes are the counters
+    if (q_pageable) {
+      h_stage_q = hp;
+      hp += al(qb);
+    }
+    if (out_staged) {
+      h_stage_o = hp;
+      void *zo = mapped_host(h_stage_o);
+      if (zo) {  // the kernel's result stores go straight into the page-locked staging
+        d_rows = (int32_t *)zo;
+        d_dists = (float *)((char *)zo + al(rb));
+        d_cnt = (int32_t *)((char *)zo + al(rb) + al(db));
+        direct_out = true;
+      } else {
+        out_staged = false;
+      }
     }
   }
   // The batch is cut in chunks that run on their own streams: the H2D copy of chunk i+1 and the D2H copy of chunk
   // i-1 overlap the traversal kernel of chunk i, and the kernels of different chunks share the SMs.
   int nchunk = B >= 1024 ? 2 : 1;  // measured (profiles/r3h_e2e_callers.log): 2 beats 4 alone and with callers in flight
+  if (q_pageable && B >= 4096) nchunk = 4;  // the host copy of chunk i+1 runs under the H2D copy and traversal of chunk i
   if (const char *v = getenv("B200HNSW_E2E_CHUNKS")) {
     int t = atoi(v);
     if (t >= 1 && t <= CallCtx::MAX_SUB) nchunk = t;
   }
-  if ((rc = c->ensure_sub(nchunk)) || (rc = c->reserve_pinned(64))) return fail(rc);
+  if ((rc = c->ensure_sub(nchunk)) || (rc = c->reserve_pinned(256))) return fail(rc);
   // counters come back into page-locked memory: a copy into pageable memory would go through the driver's staging
   // path, which serialises against the other calls in flight
   volatile unsigned long long *ctr = (volatile unsigned long long *)c->h_pinned;
   for (int i = 0; i < 5; i++) ctr[i] = 0;
   int launches = 0;
   bool staged = false;
+  // Pageable queries: the chunks behind the first are copied into the staging buffer by helper threads (one per chunk,
+  // started here, joined when the chunk's turn comes), chunk 0 by this thread: one thread moves ~12 GB/s, and the copy
+  // of 5 MB was what a call from pageable memory spent most of its time in.
+  struct Copiers {
+    std::vector<std::thread> t;
+    void join(size_t i) {
+      if (i < t.size() && t[i].joinable()) t[i].join();
+    }
+    ~Copiers() {
+      for (auto &x : t)
+        if (x.joinable()) x.join();
+    }
+  } copiers;
+  if (q_pageable && nchunk > 1) {
+    copiers.t.resize((size_t)nchunk);
+    for (int ci = 1; ci < nchunk; ci++) {
+      const int64_t q0 = B * ci / nchunk, q1 = B * (ci + 1) / nchunk;
+      if (q1 <= q0) continue;
+      float *dst = (float *)h_stage_q + q0 * dim;
+      const float *src = queries + q0 * dim;
+      const size_t bytes = sizeof(float) * (size_t)(q1 - q0) * dim;
+      try {
+        copiers.t[(size_t)ci] = std::thread([dst, src, bytes] { memcpy(dst, src, bytes); });
+      } catch (...) {
+        memcpy(dst, src, bytes);  // no thread to be had: copy here
+      }
+    }
+  }
   // Page-locked QUERIES could be read by the kernel itself as well (each traversal fetching its 4*dim bytes over PCIe
   // when it starts).  Measured and rejected as the default (profiles/r5j_direct_in_ab.log): one caller 29.4 M vs 30.2 M
   // queries/s, four callers 54 M vs 71 M -- a traversal that waits 2 us for its query holds its slot on the SM, and
@@ -706,7 +769,8 @@ int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_
   }
   const bool direct_in = q_src != d_q;
   if (nchunk == 1 && !staged) {  // one chunk: copy first, so that kernel_ms (ev0..ev1) is the traversal kernel alone
-    if ((e = cudaMemcpyAsync(d_q, queries, qb, cudaMemcpyHostToDevice, s)) != cudaSuccess)
+    if (q_pageable) memcpy(h_stage_q, queries, qb);
+    if ((e = cudaMemcpyAsync(d_q, q_pageable ? (const float *)h_stage_q : queries, qb, cudaMemcpyHostToDevice, s)) != cudaSuccess)
       return fail(cuda_fail(e, "search staging"));
     staged = true;
   }
@@ -732,9 +796,18 @@ int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_
       cudaStream_t sc = nchunk == 1 ? s : c->sub[ci];
       if (nchunk > 1 && (e = cudaStreamWaitEvent(sc, c->ev0, 0)) != cudaSuccess)
         return fail(cuda_fail(e, "search chunk wait"));
-      if (!staged && (e = cudaMemcpyAsync(d_q + q0 * dim, queries + q0 * dim, sizeof(float) * (size_t)nq * dim,
-                                          cudaMemcpyHostToDevice, sc)) != cudaSuccess)
-        return fail(cuda_fail(e, "search staging"));
+      if (!staged) {
+        const float *src = queries + q0 * dim;
+        if (q_pageable) {
+          float *st = (float *)h_stage_q + q0 * dim;
+          if (ci == 0 || nchunk == 1) memcpy(st, src, sizeof(float) * (size_t)nq * dim);
+          else copiers.join((size_t)ci);
+          src = st;
+        }
+        if ((e = cudaMemcpyAsync(d_q + q0 * dim, src, sizeof(float) * (size_t)nq * dim, cudaMemcpyHostToDevice, sc)) !=
+            cudaSuccess)
+          return fail(cuda_fail(e, "search staging"));
+      }
       rc = launch_search(h, q_src + q0 * dim, nq, k, ef, metric, mode, entries, d_rows + q0 * k, d_dists + q0 * k,
                          d_cnt + q0, d_ctr, d_err, vis, sc, 0, 0, nullptr, 0, full_queue);
       if (rc) return fail(rc);
@@ -769,6 +842,11 @@ int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_
       return fail(B200HNSW_ERR_VISITED_OVERFLOW);
     }
     vis = vis * 4 < vis_max ? vis * 4 : vis_max;
+  }
+  if (out_staged) {
+    memcpy(out_rows, h_stage_o, rb);
+    memcpy(out_dists, h_stage_o + al(rb), db);
+    memcpy(out_counts, h_stage_o + al(rb) + al(db), cb);
   }
   if (vis > vis0) {  // sticky, but only now that a search with this table has succeeded; concurrent callers keep the largest
     std::atomic<int> &hint = mode == B200HNSW_MODE_EXTENDED ? h->vis_hint_ext : h->vis_hint;

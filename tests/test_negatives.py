@@ -98,47 +98,53 @@ def _pos(results, key):
     return -1
 
 
-@pytest.mark.gpu
-@pytest.mark.parametrize("levels_seed", [1, 3, 4, 5])
-def test_reference_negative_test_go_assertions(levels_seed):
-    """The assertions of the reference's own negative_test.go (TestSearchWithNegative, lines 31-145, and
-    TestBatchSearchWithNegatives, lines 168-259), replayed through the public API on the device.  The levels come from
-    our own random stream (Go's math/rand cannot be reproduced here); four streams are tried.  The assertions are NOT
-    independent of the levels: with stream 2 the layer-0 entry differs and the reference's own result queue (heap.Max()
-    is the last array slot, graph.go:150-155) drops one of the three dog vectors from Search(dog, 3) -- on the device
-    and in the oracle alike (profiles/r6c_pytest_negatives.log); the reference's test passes under the levels Go's
-    stream happens to draw.  Device-equals-oracle on arbitrary levels is test_negatives_match_restatement."""
-    g = _animals(levels_seed)
+def _negative_test_go_scenario(g):
+    """The assertions of negative_test.go in order; returns the first one that does not hold (None = all hold)."""
     dog, puppy, cat, kitten = [1.0, 0.2, 0.1], [0.9, 0.3, 0.2], [0.1, 1.0, 0.2], [0.2, 0.9, 0.3]
-    # "Basic search without negative" (31-44)
-    res = g.Search(dog, 3)
-    assert len(res) == 3 and {r.Key for r in res} == {1, 2, 3}
-    # "Search with negative example" (46-85)
-    res = g.SearchWithNegative(dog, puppy, 3, 0.5)
-    assert len(res) == 3 and res[0].Key == 1
+    res = g.Search(dog, 3)                                             # "Basic search without negative" (31-44)
+    if not (len(res) == 3 and {r.Key for r in res} == {1, 2, 3}):
+        return "basic search: dog, puppy, canine"
+    res = g.SearchWithNegative(dog, puppy, 3, 0.5)                     # "Search with negative example" (46-85)
+    if not (len(res) == 3 and res[0].Key == 1):
+        return "negative example: dog first"
     regular = g.Search(dog, 9)
     np_, rp = _pos(res, 2), _pos(regular, 2)
-    if np_ != -1 and rp != -1:
-        assert np_ > rp
-    # "Search with multiple negative examples" (87-108)
-    res = g.SearchWithNegatives([0.4, 0.4, 0.4], [dog, cat], 3, 0.7)
-    assert len(res) == 3 and sum(7 <= r.Key <= 9 for r in res) >= 1
-    # "Negative weight impact" (110-145)
-    low = g.SearchWithNegative(dog, puppy, 3, 0.1)
+    if np_ != -1 and rp != -1 and not np_ > rp:
+        return "negative example: puppy ranked lower"
+    res = g.SearchWithNegatives([0.4, 0.4, 0.4], [dog, cat], 3, 0.7)   # "multiple negative examples" (87-108)
+    if not (len(res) == 3 and sum(7 <= r.Key <= 9 for r in res) >= 1):
+        return "multiple negatives: a bird-related vector"
+    low = g.SearchWithNegative(dog, puppy, 3, 0.1)                     # "Negative weight impact" (110-145)
     high = g.SearchWithNegative(dog, puppy, 3, 0.9)
     lp, hp = _pos(low, 2), _pos(high, 2)
-    if lp != -1 and hp != -1:
-        assert hp > lp
-    elif lp != -1:
-        assert hp == -1
-    # TestBatchSearchWithNegatives: "Batch search with negatives" (168-194)
-    res = g.BatchSearchWithNegatives([dog, cat], [[puppy], [kitten]], 3, 0.5)
-    assert len(res) == 2 and len(res[0]) == 3 and len(res[1]) == 3
-    assert res[0][0].Key == 1 and res[1][0].Key == 4
-    # "Batch search with empty negatives" (196-220)
-    res = g.BatchSearchWithNegatives([dog, cat], [[], [kitten]], 3, 0.5)
-    assert len(res) == 2 and len(res[0]) == 3 and len(res[1]) == 3
-    assert res[0][0].Key == 1 and res[1][0].Key == 4
-    # "Batch search with multiple negatives" (222-258)
-    res = g.BatchSearchWithNegatives([[0.4, 0.4, 0.4]], [[dog, cat]], 3, 0.7)
-    assert len(res) == 1 and len(res[0]) == 3 and sum(7 <= r.Key <= 9 for r in res[0]) >= 1
+    if lp != -1 and hp != -1 and not hp > lp:
+        return "negative weight: puppy lower with the higher weight"
+    if lp != -1 and hp == -1:
+        pass                                                           # excluded entirely: what the reference accepts
+    res = g.BatchSearchWithNegatives([dog, cat], [[puppy], [kitten]], 3, 0.5)     # batch (168-194)
+    if not (len(res) == 2 and len(res[0]) == 3 and len(res[1]) == 3 and res[0][0].Key == 1 and res[1][0].Key == 4):
+        return "batch: dog first, cat first"
+    res = g.BatchSearchWithNegatives([dog, cat], [[], [kitten]], 3, 0.5)          # empty negatives (196-220)
+    if not (len(res) == 2 and len(res[0]) == 3 and len(res[1]) == 3 and res[0][0].Key == 1 and res[1][0].Key == 4):
+        return "batch with empty negatives: dog first, cat first"
+    res = g.BatchSearchWithNegatives([[0.4, 0.4, 0.4]], [[dog, cat]], 3, 0.7)     # multiple negatives (222-258)
+    if not (len(res) == 1 and len(res[0]) == 3 and sum(7 <= r.Key <= 9 for r in res[0]) >= 1):
+        return "batch with multiple negatives: a bird-related vector"
+    return None
+
+
+@pytest.mark.gpu
+def test_reference_negative_test_go_assertions():
+    """The assertions of the reference's own negative_test.go (TestSearchWithNegative, lines 31-145, and
+    TestBatchSearchWithNegatives, lines 168-259), replayed through the public API on the device.  The node levels come
+    from our own random stream (Go's math/rand cannot be reproduced here) and the assertions are NOT independent of
+    them: for some draws the layer-0 entry is such that the reference's result queue (heap.Max() is the last array slot,
+    graph.go:150-155) drops one of the three dog vectors from Search(dog, 3) -- the reference's test passes under the
+    levels Go's stream happens to draw (and the entry point Go's map iteration happens to return, graph.go:250-258).
+    So twelve streams are tried: the first assertion (Search(dog, 3) = the three dog vectors) holds under about half of
+    them (profiles/r6f_negatives_streams.log: 6 of 12), and WHENEVER it holds every other assertion of the file has to
+    hold.  Device-equals-oracle on arbitrary levels is test_negatives_match_restatement."""
+    outcome = {seed: _negative_test_go_scenario(_animals(seed)) for seed in range(1, 13)}
+    print("negative_test.go scenario per level stream:", outcome)
+    assert sum(v is None for v in outcome.values()) >= 4, outcome
+    assert all(v is None or v.startswith("basic search") for v in outcome.values()), outcome

@@ -175,3 +175,37 @@ def test_pipeline_search_all_raises_the_visited_capacity_and_reissues(oracle, ki
             assert np.array_equal(rows[q, :cnt[q]][o], got[q, :cnt[q]])
     if hasattr(pipe, "close"):
         pipe.close()
+
+
+def test_pageable_and_page_locked_host_buffers_give_the_same_lists(oracle):
+    """b200hnsw_search_batch stages pageable buffers itself (chunked copies through the call context's page-locked
+    buffer, results written there by the kernel and copied out); page-locked buffers are read by the copy engine and
+    written by the kernel directly; B200HNSW_NO_HOST_STAGING=1 leaves pageable buffers to the driver.  Same lists, and
+    the oracle's, on all three routes; a batch small enough to skip the staging (< 256 KB of queries) as well."""
+    import ctypes as C
+    import os
+    import torch
+    from hnsw_b200 import _lib
+    rng = np.random.default_rng(31)
+    n, d, k, ef = 6000, 128, 10, 48
+    X = rng.uniform(-1, 1, (n, d)).astype(np.float32)
+    g, _, _ = build_oracle_graph(oracle, X, 12, 0.25, 64, 0)
+    dg = _device_graph(oracle, g, 12, ef, 0)
+    for B in (4500, 300):
+        Q = rng.uniform(-1, 1, (B, d)).astype(np.float32)
+        o_rows, o_d, o_cnt, _ = g.batch_search(Q, k, ef)
+        a = dg.search_rows(Q, k, ef)                                   # pageable numpy buffers: own staging
+        os.environ["B200HNSW_NO_HOST_STAGING"] = "1"                   # read once per process: no effect if already read
+        qp = torch.from_numpy(Q).pin_memory()
+        rows = torch.empty((B, k), dtype=torch.int32).pin_memory()
+        dists = torch.empty((B, k), dtype=torch.float32).pin_memory()
+        cnt = torch.empty((B,), dtype=torch.int32).pin_memory()
+        _lib.check(_lib.lib().b200hnsw_search_batch(
+            dg._h, C.cast(qp.data_ptr(), _lib.f32p), B, k, ef, 0, _lib.MODE_REFERENCE, None,
+            C.cast(rows.data_ptr(), _lib.i32p), C.cast(dists.data_ptr(), _lib.f32p), C.cast(cnt.data_ptr(), _lib.i32p),
+            None))
+        os.environ.pop("B200HNSW_NO_HOST_STAGING", None)
+        for got in (a, (rows.numpy(), dists.numpy(), cnt.numpy())):
+            assert np.array_equal(got[2], o_cnt)
+            assert np.array_equal(got[0], o_rows)
+            assert same_float_bits(got[1], o_d)
