@@ -7,8 +7,6 @@
 #include <new>
 
 #include <sched.h>
-#include <thread>
-#include <vector>
 
 #include "index.hpp"
 
@@ -725,34 +723,6 @@ int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_
   for (int i = 0; i < 5; i++) ctr[i] = 0;
   int launches = 0;
   bool staged = false;
-  // Pageable queries: the chunks behind the first are copied into the staging buffer by helper threads (one per chunk,
-  // started here, joined when the chunk's turn comes), chunk 0 by this thread: one thread moves ~12 GB/s, and the copy
-  // of 5 MB was what a call from pageable memory spent most of its time in.
-  struct Copiers {
-    std::vector<std::thread> t;
-    void join(size_t i) {
-      if (i < t.size() && t[i].joinable()) t[i].join();
-    }
-    ~Copiers() {
-      for (auto &x : t)
-        if (x.joinable()) x.join();
-    }
-  } copiers;
-  if (q_pageable && nchunk > 1) {
-    copiers.t.resize((size_t)nchunk);
-    for (int ci = 1; ci < nchunk; ci++) {
-      const int64_t q0 = B * ci / nchunk, q1 = B * (ci + 1) / nchunk;
-      if (q1 <= q0) continue;
-      float *dst = (float *)h_stage_q + q0 * dim;
-      const float *src = queries + q0 * dim;
-      const size_t bytes = sizeof(float) * (size_t)(q1 - q0) * dim;
-      try {
-        copiers.t[(size_t)ci] = std::thread([dst, src, bytes] { memcpy(dst, src, bytes); });
-      } catch (...) {
-        memcpy(dst, src, bytes);  // no thread to be had: copy here
-      }
-    }
-  }
   // Page-locked QUERIES could be read by the kernel itself as well (each traversal fetching its 4*dim bytes over PCIe
   // when it starts).  Measured and rejected as the default (profiles/r5j_direct_in_ab.log): one caller 29.4 M vs 30.2 M
   // queries/s, four callers 54 M vs 71 M -- a traversal that waits 2 us for its query holds its slot on the SM, and
@@ -800,8 +770,7 @@ int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_
         const float *src = queries + q0 * dim;
         if (q_pageable) {
           float *st = (float *)h_stage_q + q0 * dim;
-          if (ci == 0 || nchunk == 1) memcpy(st, src, sizeof(float) * (size_t)nq * dim);
-          else copiers.join((size_t)ci);
+          memcpy(st, src, sizeof(float) * (size_t)nq * dim);
           src = st;
         }
         if ((e = cudaMemcpyAsync(d_q + q0 * dim, src, sizeof(float) * (size_t)nq * dim, cudaMemcpyHostToDevice, sc)) !=
