@@ -127,7 +127,11 @@ int b200hnsw_get_neighbors(const b200hnsw_t *h, int32_t layer, int64_t first, in
  * One traversal per query, all B in one launch.  out_rows/out_dists are [B][k] in the reference's order, i.e.
  * the raw heap array of the layer-0 result queue (graph.go:169, 588-593: index 0 is the nearest, the rest in
  * binary-heap layout); unused slots are -1 / NaN; out_counts[b] = len(result).  entries may be NULL.
- * k <= B200HNSW_MAX_K, ef <= B200HNSW_MAX_EF.  An empty graph yields counts of 0 (graph.go:554-556). */
+ * k <= B200HNSW_MAX_K, ef <= B200HNSW_MAX_EF.  An empty graph yields counts of 0 (graph.go:554-556).
+ * The host-pointer call is synchronous and may be made from several threads at once (the reference admits concurrent
+ * BatchSearch callers under its read lock); a waiting call polls and yields its core.  Buffers may be page-locked
+ * (read by the copy engine, results written by the kernel directly) or ordinary pageable memory (staged by the call
+ * through its own page-locked buffer).  The _device variant takes device pointers and is asynchronous on `stream`. */
 int b200hnsw_search_batch(b200hnsw_t *h, const float *queries, int64_t B, int32_t k, int32_t ef, int32_t metric,
                           int32_t mode, const int32_t *entries, int32_t *out_rows, float *out_dists,
                           int32_t *out_counts, b200hnsw_stats *stats);
@@ -141,7 +145,7 @@ int b200hnsw_search_batch_device(b200hnsw_t *h, const float *d_queries, int64_t 
  * is kept for later calls once that retry has succeeded.  Device-pointer calls cannot retry (they are asynchronous):
  * they report the overflow in d_counters[4] (1 = visited set, 3 = NaN distances met with the short candidate queue),
  * mark the affected queries with count -1, and leave it to the caller to raise the capacity here and issue the batch
- * again (hnsw_b200/sharded.py does).  set fails with B200HNSW_ERR_UNSUPPORTED past what the device can give. */
+ * again (hnsw_b200/sharded.py: search_all does, agreeing on the error word across the ranks).  set fails with B200HNSW_ERR_UNSUPPORTED past what the device can give. */
 int32_t b200hnsw_get_visited_capacity(const b200hnsw_t *h);
 int b200hnsw_set_visited_capacity(b200hnsw_t *h, int32_t entries);
 
