@@ -187,7 +187,11 @@ def roofline_block(ctx, args, wl, mode, rec, steps, total_ms, solo_ms, depth):
     kern_avg_ms = float(np.mean(rec["kernel_ms"]))
     eff_ms = (total_ms / steps) if depth > 1 else kern_avg_ms
     achieved = alg / (eff_ms / 1e3) / 1e9
-    tr = load_traffic() if (mode == 0 and dim == 128 and wl["name"] == "c2") else None
+    tr = None
+    if mode == 0 and dim == 128 and wl["name"] == "c2":
+        tr = load_traffic()
+    elif mode == 0 and wl["name"] == "c3" and dim == 768:
+        tr = load_traffic("k1_traffic_c3.json")
     out = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
            "traffic": (tr or {}).get("dram_bytes_per_launch"),
            "kernel": k1_name(mode, dim), "kernel_ms": eff_ms,
@@ -204,13 +208,19 @@ def roofline_block(ctx, args, wl, mode, rec, steps, total_ms, solo_ms, depth):
     if tr:
         # DRAM bytes of ONE cold launch of the shipped template (ncu --set full, committed under profiles/) over the
         # launch-alone time measured in THIS run: the fraction of the HBM peak the kernel really pulls
-        out["traffic_source"] = f"profiles/k1_traffic.json ({tr.get('kernel')}; ncu --set full of one cold launch)"
+        out["traffic_source"] = (f"profiles/k1_traffic{'_c3' if wl['name'] == 'c3' else ''}.json ({tr.get('kernel')}; ncu "
+                                 f"--set full of one launch)")
         if solo_ms:
             out["dram_frac"] = tr["dram_bytes_per_launch"] / (solo_ms / 1e3) / 1e9 / peak
         out["issue_busy"] = (tr.get("issue_slots_busy_pct") or 0) / 100.0
         out["l2_hit_rate"] = (tr.get("lts_hit_rate_pct") or 0) / 100.0
         out["achieved_occupancy"] = (tr.get("achieved_occupancy_pct") or 0) / 100.0
-    if mode == 0:
+    if mode == 0 and wl["name"] == "c3":
+        out["bound_observed"] = "latency x resident traversals (shuffle latency of the 32-lane reductions)"
+        out["note"] = ("3 KB rows: DRAM serves 30 % of the sectors (1.4 TB/s, ~21 % of the HBM peak, for one launch "
+                       "alone); the warps wait on the cross-lane reductions (short scoreboard 5 cycles per issue, "
+                       "profiles/r7d_k1_c3_counters.json), not on HBM")
+    elif mode == 0:
         out["bound_observed"] = "latency x resident traversals"
         out["note"] = ("bytes are ALGORITHMIC (SURVEY 8d); frac can pass 1 because the traversals of a batch share the "
                        "upper layers and the hub rows of layer 0 (L2 serves ~87% of the sectors, see traffic / "

@@ -93,9 +93,9 @@ def load_peaks():
     return 6650.0, 1400.0, "fallback (B200_PROFILING.md: 6.65 TB/s, 1.4 PFLOP/s sustained)"
 
 
-def load_traffic():
-    """Counters of the committed ncu --set full capture of the traversal kernel (profiles/k1_traffic.json), if any."""
-    p = ROOT / "profiles" / "k1_traffic.json"
+def load_traffic(name="k1_traffic.json"):
+    """Counters of a committed ncu --set full capture of the traversal kernel (profiles/k1_traffic*.json), if any."""
+    p = ROOT / "profiles" / name
     if p.exists():
         try:
             return json.loads(p.read_text())
