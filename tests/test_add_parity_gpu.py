@@ -49,6 +49,7 @@ def _assert_same_graph(g, dg, M):
     (400, 8, 6, 20, 0),       # low dimension: many evictions and replenishes
     (128, 1, 6, 20, 0),       # graph_test.go:86-133 shape: 128 points on a line, M=6
     (200, 40, 48, 30, 1),     # M > 32
+    (260, 24, 64, 100, 0),    # MAX_M, ef > M
 ])
 def test_add_matches_oracle(oracle, n, d, M, ef, metric):
     rng = np.random.default_rng(7)

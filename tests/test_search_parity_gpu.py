@@ -41,6 +41,9 @@ def _assert_same(oracle, g, dg, Q, k, ef):
     (500, 3, 6, 20, 4, 0),        # tiny dims like the reference's unit tests
     (300, 1, 6, 20, 4, 0),        # 1-D line graph (graph_test.go:86-133 shape)
     (400, 200, 48, 30, 64, 0),    # M > 32 (two list rounds), k > ef
+    (700, 2048, 64, 1024, 256, 1),  # every limit of the C ABI at once: dim 2048, MAX_M, MAX_EF, MAX_K (cosine)
+    (900, 1536, 64, 512, 200, 0),   # the same neighbourhood under L2
+    (1200, 100, 64, 1024, 256, 0),  # dim not a multiple of 32, limits of M / ef / k
 ])
 def test_batch_search_matches_oracle(oracle, n, d, M, ef, k, metric):
     rng = np.random.default_rng(42)
@@ -162,3 +165,27 @@ def test_packed_shard_merge_matches_spec():
         assert np.array_equal(mc.cpu().numpy(), rc)
         assert np.array_equal(mi.cpu().numpy(), ri)
         assert np.array_equal(md.cpu().numpy(), rd, equal_nan=True)
+
+
+def test_limits_are_refused_loudly(oracle):
+    """Past the limits of the C ABI (include/b200hnsw.h: MAX_K 256, MAX_EF 1024, MAX_M 64, dim 2048) calls fail with a
+    message; nothing is clamped silently."""
+    import hnsw_b200
+    from hnsw_b200 import _lib
+    rng = np.random.default_rng(3)
+    X = rng.uniform(-1, 1, (300, 16)).astype(np.float32)
+    g, _, _ = build_oracle_graph(oracle, X, 8, 0.25, 20, 0)
+    dg = _device_graph(oracle, g, 8, 20, 0)
+    Q = X[:4]
+    with pytest.raises(_lib.B200Error, match="k must be greater than 0 and <= 256"):
+        dg.search_rows(Q, 257, 20)
+    with pytest.raises(_lib.B200Error, match="EfSearch must be greater than 0 and <= 1024"):
+        dg.search_rows(Q, 10, 1025)
+    rows, _, cnt = dg.search_rows(Q, 256, 1024)              # the limits themselves are fine
+    assert (cnt > 0).all() and (rows[:, 0] == np.arange(4)).all()
+    big = hnsw_b200.Graph(M=65, Ml=0.25, EfSearch=20, Distance=hnsw_b200.EuclideanDistance)
+    with pytest.raises(Exception):
+        big.add_arrays([0, 1], np.zeros((2, 8), np.float32), levels=[0, 0])
+    wide = hnsw_b200.Graph(M=8, Ml=0.25, EfSearch=20, Distance=hnsw_b200.EuclideanDistance)
+    with pytest.raises(Exception):
+        wide.add_arrays([0, 1], np.zeros((2, 2049), np.float32), levels=[0, 0])

@@ -31,6 +31,7 @@ def _assert_same_graph(g, dg):
     (1500, 8, 6, 20, 0, 4096),      # low dimension: many evictions, several requests per target
     (600, 40, 48, 30, 1, 128),      # M > 32
     (400, 16, 8, 20, 0, 1),         # waves of one node
+    (900, 32, 64, 128, 0, 512),     # MAX_M
 ])
 def test_wave_add_matches_oracle(oracle, n, d, M, ef, metric, wave_max):
     import hnsw_b200
