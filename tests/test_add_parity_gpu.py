@@ -100,3 +100,32 @@ def test_add_search_api_like_reference(oracle):
     assert len(out) == 1 and out[0].Key == 1 and list(out[0].Value) == [1, 1]
     with pytest.raises(ValueError, match="embedding dimension mismatch: 2 != 3"):
         g2.Add(hnsw_b200.Node(9, [1, 2, 3]))
+
+
+def test_whole_graph_kat_on_device_under_the_reference_topography(oracle):
+    """graph_test.go:86-133 on the device (see tests/test_oracle_kat.py for the CPU half): for level assignments with the
+    reference's topography, exact sequential Add + Search([64.5], 4) through the public API return what the oracle
+    returns, and the reference's list [64, 65, 62, 63] -- in its heap-array order -- is the most frequent answer."""
+    import hnsw_b200
+    topo = [128, 67, 28, 12, 6, 2, 1, 1]
+    n = 128
+    rng = np.random.default_rng(0)
+    seen = {}
+    for _ in range(24):
+        lv = np.zeros(n, np.int32)
+        members = np.arange(n)
+        for l in range(1, len(topo)):
+            members = rng.choice(members, topo[l], replace=False)
+            lv[members] = l
+        og = oracle.Graph(1, 6, oracle.EUCLIDEAN)
+        for i in range(n):
+            og.add(i, [float(i)], int(lv[i]), 20)
+        want = [int(x) for x in og.batch_search(np.array([[64.5]], np.float32), 4, 20)[0][0]]
+        g = hnsw_b200.Graph(M=6, Ml=0.5, EfSearch=20, Distance=hnsw_b200.EuclideanDistance)
+        g.Add(*[hnsw_b200.Node(i, [float(i)]) for i in range(n)], levels=[int(x) for x in lv])
+        assert g.Topography() == topo
+        got = [nd.Key for nd in g.Search([64.5], 4)]
+        assert got == want
+        seen[tuple(got)] = seen.get(tuple(got), 0) + 1
+        g.close()
+    assert max(seen, key=seen.get) == (64, 65, 62, 63), seen

@@ -237,3 +237,33 @@ def test_exact_ties_keep_insertion_order(oracle):
     X = np.array([[1, 0], [0, 1], [-1, 0], [0, -1], [2, 0]], dtype=np.float32)
     idx, d = oracle.exact_search(X, [0, 0], 5, oracle.EUCLIDEAN, faithful=True)
     assert list(idx) == [0, 1, 2, 3, 4]
+
+
+def test_whole_graph_kat_under_the_reference_topography(oracle):
+    """graph_test.go:86-133, the reference's only whole-graph known answer: 128 points on a line, M=6, Ml=0.5,
+    EfSearch=20; Topography() == [128, 67, 28, 12, 6, 2, 1, 1] and Search([64.5], 4) == keys [64, 65, 62, 63] IN THAT
+    ORDER (the raw heap array: 62 in front of 63).  Which nodes sit on which layer comes from Go's math/rand and cannot
+    be regenerated here, so level assignments with exactly that topography are drawn at random: the reference's list,
+    in its order, is the most frequent answer of the oracle by far, and the sorted order [64, 65, 63, 62] -- what an
+    implementation without Go's heap layout and last-slot eviction would return -- never occurs."""
+    topo = [128, 67, 28, 12, 6, 2, 1, 1]
+    n = 128
+    rng = np.random.default_rng(0)
+    seen = {}
+    for _ in range(120):
+        lv = np.zeros(n, np.int32)
+        members = np.arange(n)
+        for l in range(1, len(topo)):
+            members = rng.choice(members, topo[l], replace=False)
+            lv[members] = l
+        g = oracle.Graph(1, 6, oracle.EUCLIDEAN)
+        for i in range(n):
+            g.add(i, [float(i)], int(lv[i]), 20)
+        assert g.topography() == topo
+        rows = tuple(int(x) for x in g.batch_search(np.array([[64.5]], np.float32), 4, 20)[0][0])
+        seen[rows] = seen.get(rows, 0) + 1
+    best = max(seen, key=seen.get)
+    assert best == (64, 65, 62, 63), seen
+    assert seen[best] >= 36, seen                      # ~43 % of the assignments
+    assert (64, 65, 63, 62) not in seen, seen
+    assert all(set(r) <= set(range(58, 70)) for r in seen), seen
