@@ -37,6 +37,74 @@ def MakeNode(key, vec) -> Node:
     return Node(key, np.asarray(vec, dtype=np.float32))
 
 
+class _RWLock:
+    """Graph.mu (graph.go:305-332 holds a sync.RWMutex: Add / BatchAdd / Delete / BatchDelete take it for writing, Search /
+    BatchSearch / Lookup for reading).  The write side is re-entrant for its owner: BatchAdd replaces an existing key
+    through BatchDelete (the reference's Add deadlocks there)."""
+
+    def __init__(self):
+        self._c = threading.Condition()
+        self._readers = 0
+        self._writer = None
+        self._depth = 0
+
+    def r_acquire(self) -> bool:
+        me = threading.get_ident()
+        with self._c:
+            if self._writer == me:
+                return False  # nested in my own write section
+            while self._writer is not None:
+                self._c.wait()
+            self._readers += 1
+            return True
+
+    def r_release(self):
+        with self._c:
+            self._readers -= 1
+            if self._readers == 0:
+                self._c.notify_all()
+
+    def w_acquire(self):
+        me = threading.get_ident()
+        with self._c:
+            if self._writer == me:
+                self._depth += 1
+                return
+            while self._writer is not None or self._readers:
+                self._c.wait()
+            self._writer, self._depth = me, 1
+
+    def w_release(self):
+        with self._c:
+            self._depth -= 1
+            if self._depth == 0:
+                self._writer = None
+                self._c.notify_all()
+
+
+def _writes(fn):
+    def wrapped(self, *a, **kw):
+        self._mu.w_acquire()
+        try:
+            return fn(self, *a, **kw)
+        finally:
+            self._mu.w_release()
+    wrapped.__name__, wrapped.__doc__ = fn.__name__, fn.__doc__
+    return wrapped
+
+
+def _reads(fn):
+    def wrapped(self, *a, **kw):
+        mine = self._mu.r_acquire()
+        try:
+            return fn(self, *a, **kw)
+        finally:
+            if mine:
+                self._mu.r_release()
+    wrapped.__name__, wrapped.__doc__ = fn.__name__, fn.__doc__
+    return wrapped
+
+
 class LevelRand:
     """What Graph.Rng has to be: anything with Float64() (the one method randomLevel, graph.go:388-417, calls on its
     *rand.Rand).  This one is a numpy PCG64 stream, NOT Go's math/rand: a seed gives a reproducible stream here, not the
@@ -71,6 +139,7 @@ class Graph:
         self.device = device
         self._capacity = capacity
         self._h = None          # b200hnsw_t*
+        self._mu = _RWLock()    # Graph.mu
         self._dim = 0
         self._max_m = 0
         self._keys: List[int] = []          # row -> key
@@ -125,6 +194,7 @@ class Graph:
     def Dims(self) -> int:
         return self._dim if self.Len() > 0 else 0
 
+    @_reads
     def Lookup(self, key):
         row = self._row_of.get(key)
         if row is None:
@@ -182,6 +252,7 @@ class Graph:
             size0 += 1
         return out
 
+    @_writes
     def BatchAdd(self, nodes: Iterable[Node], levels: Optional[Sequence[int]] = None):
         """graph.go:942-1042.  `levels` (testing hook) replaces the Rng draws."""
         self.Validate()
@@ -331,6 +402,7 @@ class Graph:
         if mirror_err:
             raise mirror_err[0]
 
+    @_writes
     def add_arrays(self, keys, vectors, levels: Optional[Sequence[int]] = None, wave_max: int = 0):
         """BatchAdd for array inputs (keys[n] int64, vectors[n, dim] float32): same semantics, no per-node objects.
         Keys must be new and distinct.  wave_max > 0 selects the wave-batched construction
@@ -354,6 +426,7 @@ class Graph:
         self._add_arrays(keys, vectors, levels, metric, wave_max)
 
     # ---- Delete / BatchDelete -------------------------------------------------------------------------------------
+    @_writes
     def BatchDelete(self, keys) -> List[bool]:
         """graph.go:871-895.  The reference's quirks are kept (see b200hnsw_delete_batch in include/b200hnsw.h): a
         deleted node can stay linked one-way and Search can still return it; Lookup and Len stop seeing it."""
@@ -377,6 +450,7 @@ class Graph:
                 self._retired.add(k)
         return [bool(x) for x in out]
 
+    @_writes
     def Delete(self, key) -> bool:
         """graph.go:843-866."""
         return self.BatchDelete([key])[0]
@@ -400,11 +474,13 @@ class Graph:
         if self._h is not None:
             _lib.check(_lib.lib().b200hnsw_set_build_mode(self._h, self._build_mode))
 
+    @_writes
     def Add(self, *nodes: Node, levels: Optional[Sequence[int]] = None):
         """graph.go:437-531 (same body as BatchAdd; the reference's Add deadlocks on a duplicate key, F9)."""
         self.BatchAdd(nodes, levels=levels)
 
     # ---- load a graph built elsewhere (Import, or the oracle in tests) ----------------------------------------------
+    @_writes
     def load_flat(self, vectors, keys, levels, layer_lists, entries=None):
         """layer_lists[l] = (rows[N_l], ptr[N_l+1], nbr[...]) CSR of layer l.  Replaces the content."""
         vectors = np.ascontiguousarray(vectors, dtype=np.float32)
@@ -482,6 +558,7 @@ class Graph:
         return vec, keys, levels, layer_lists, self.entries()
 
     # ---- Search / BatchSearch -----------------------------------------------------------------------------------------
+    @_reads
     def search_rows(self, queries, k: int, ef: Optional[int] = None, mode: int = _lib.MODE_REFERENCE, entries=None):
         """Raw device call: (rows[B,k], dists[B,k], counts[B]) in the reference's heap-array order."""
         q = np.ascontiguousarray(queries, dtype=np.float32)
@@ -535,6 +612,7 @@ class Graph:
     def _nodes(self, rows, count) -> List[Node]:
         return [Node(self._keys[r], self._vecs[r]) for r in rows[:count]]
 
+    @_reads
     def Search(self, near, k: int) -> List[Node]:
         """graph.go:534-625"""
         self.Validate()
@@ -559,6 +637,7 @@ class Graph:
             out[2] = Node(3, self._vecs[self._row_of[3]])  # graph.go:595-619
         return out
 
+    @_reads
     def BatchSearch(self, queries, k: int) -> List[List[Node]]:
         """graph.go:1047-1110 (no dog hack in the reference's batch loop)."""
         self.Validate()
@@ -577,28 +656,34 @@ class Graph:
         return [self._nodes(rows[i], counts[i]) for i in range(len(qs))]
 
     # ---- graph.go:1116-1537 (host re-ranking over device searches and device distances: negatives.py) -----------------
+    @_reads
     def SearchWithNegative(self, near, negative, k: int, negWeight: float):
         from .negatives import search_with_negative
         return search_with_negative(self, near, negative, k, negWeight)
 
+    @_reads
     def SearchWithNegatives(self, near, negatives, k: int, negWeight: float):
         from .negatives import search_with_negatives
         return search_with_negatives(self, near, negatives, k, negWeight)
 
+    @_reads
     def BatchSearchWithNegatives(self, queries, negatives, k: int, negWeight: float):
         from .negatives import batch_search_with_negatives
         return batch_search_with_negatives(self, queries, negatives, k, negWeight)
 
     # ---- encode.go:133-262 -----------------------------------------------------------------------------------------
+    @_reads
     def Export(self, w) -> None:
         from .encode import export_graph
         export_graph(self, w)
 
+    @_writes
     def Import(self, r, key_type=None) -> None:
         """key_type (int, float, str, bytes) plays Go's type parameter K when the graph has no keys yet."""
         from .encode import import_graph
         import_graph(self, r, key_type)
 
+    @_reads
     def ParallelSearch(self, near, k: int, numWorkers: int = 0) -> List[Node]:
         """graph.go:631-826.  The reference's goroutine fan-out consumes results in channel-arrival order
         (non-deterministic); the deterministic branch (graph.go:791-809) is Search, which is what runs here."""
