@@ -19,8 +19,10 @@
 #include <initializer_list>
 #include <map>
 #include <memory>
+#include <mutex>
 #include <optional>
 #include <random>
+#include <shared_mutex>
 #include <stdexcept>
 #include <string>
 #include <type_traits>
@@ -177,6 +179,7 @@ class Graph {
   int Dims() const { return Len() > 0 ? dim_ : 0; }
   // graph.go:898-912
   std::pair<Vector, bool> Lookup(K key) const {
+    std::shared_lock<std::shared_mutex> lk(mu_);
     auto it = row_of_.find((int64_t)key);
     if (it == row_of_.end()) return {Vector{}, false};
     return {vecs_[(size_t)it->second], true};
@@ -235,12 +238,19 @@ class Graph {
   }
 
   // graph.go:942-1042: strictly sequential insertion (b200hnsw_add_batch), one device call for the whole batch
-  void BatchAdd(const std::vector<Node<K>> &nodes) { add(nodes, 0); }
+  void BatchAdd(const std::vector<Node<K>> &nodes) {
+    std::unique_lock<std::shared_mutex> lk(mu_);  // graph.go:943: h.mu.Lock()
+    add(nodes, 0);
+  }
   // the wave-batched construction (b200hnsw_add_batch_waves): the throughput path, NOT the reference's graph
-  void BatchAddWaves(const std::vector<Node<K>> &nodes, int64_t waveMax = 4096) { add(nodes, waveMax); }
+  void BatchAddWaves(const std::vector<Node<K>> &nodes, int64_t waveMax = 4096) {
+    std::unique_lock<std::shared_mutex> lk(mu_);
+    add(nodes, waveMax);
+  }
 
   // graph.go:534-625
   std::vector<Node<K>> Search(const Vector &near, int k) {
+    std::shared_lock<std::shared_mutex> lk(mu_);  // graph.go:535: h.mu.RLock()
     Validate();
     if (k <= 0) throw Error(detail::fmt("k must be greater than 0, got %d", k));
     if (Len() > 0 && Dims() != (int)near.size())
@@ -267,6 +277,7 @@ class Graph {
 
   // graph.go:1047-1110: ONE device launch for all queries (the reference loops serially; no dog hack in its loop)
   std::vector<std::vector<Node<K>>> BatchSearch(const std::vector<Vector> &queries, int k) {
+    std::shared_lock<std::shared_mutex> lk(mu_);  // graph.go:1048
     Validate();
     if (k <= 0) throw Error(detail::fmt("k must be greater than 0, got %d", k));
     if (Len() > 0)
@@ -295,6 +306,13 @@ class Graph {
   // graph.go:843-866 / 869-895
   bool Delete(K key) { return BatchDelete({key})[0]; }
   std::vector<bool> BatchDelete(const std::vector<K> &keys) {
+    std::unique_lock<std::shared_mutex> lk(mu_);  // graph.go:872
+    return delete_unlocked(keys);
+  }
+
+ private:
+  mutable std::shared_mutex mu_;  // Graph.mu (graph.go:305-332): writers Add / BatchAdd / Delete / BatchDelete, readers Search / Lookup
+  std::vector<bool> delete_unlocked(const std::vector<K> &keys) {
     std::vector<bool> res(keys.size(), false);
     if (!h_ || b200hnsw_layers(h_) == 0 || keys.empty()) return res;
     std::vector<int32_t> rows(keys.size());
@@ -313,7 +331,6 @@ class Graph {
     return res;
   }
 
- private:
   b200hnsw_t *h_ = nullptr;
   int dim_ = 0, max_m_ = 0;
   std::vector<int64_t> keys_;                    // row -> key
@@ -357,7 +374,7 @@ class Graph {
         const int64_t k = (int64_t)nodes[i].Key;
         if (row_of_.count(k) || !fresh.insert(k).second) {
           add(std::vector<Node<K>>(nodes.begin(), nodes.begin() + (long)i), waveMax);
-          BatchDelete(std::vector<K>{nodes[i].Key});
+          delete_unlocked(std::vector<K>{nodes[i].Key});
           retired_.erase(k);
           add(std::vector<Node<K>>{nodes[i]}, 0);
           if (ReplaceRaises) throw Error("node not added");

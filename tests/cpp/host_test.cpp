@@ -7,7 +7,9 @@
 //                     oracle's on the same rows and levels
 #include <cstdio>
 #include <cstdlib>
+#include <atomic>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include <sstream>
@@ -252,12 +254,59 @@ static void gpu_exact_tests() {
   }
 }
 
+// TestThreadSafety (graph_test.go): goroutines mixing Add / Search / Delete / Lookup on one graph.  Graph.mu is a
+// std::shared_mutex in the host mirror; an Add may legitimately fail with the reference's own "no nodes found" text when
+// a concurrent Delete emptied the neighbourhood (the reference test only logs those), everything else must hold.
+static void gpu_thread_safety_test() {
+  using namespace hnsw;
+  auto g = NewGraph<int64_t>();
+  g.Rng = Rand(5);
+  const int d = 8, threads = 8, ops = 40;
+  for (int i = 0; i < 32; i++) {
+    Vector v(d);
+    for (int j = 0; j < d; j++) v[j] = (float)((i * 7 + j * 3) % 11) / 11.f + 0.01f;
+    g.Add(MakeNode<int64_t>(i, v));
+  }
+  std::atomic<int> hard{0}, soft{0};
+  std::vector<std::thread> pool;
+  for (int t = 0; t < threads; t++)
+    pool.emplace_back([&, t] {
+      std::mt19937 rng(100 + t);
+      std::uniform_real_distribution<float> U(0.f, 1.f);
+      for (int i = 0; i < ops; i++) {
+        Vector v(d);
+        for (auto &x : v) x = U(rng) + 0.01f;
+        const int64_t key = 1000 + t * ops + i;
+        try {
+          switch (i % 4) {
+            case 0: g.Add(MakeNode<int64_t>(key, v)); break;
+            case 1: {
+              auto r = g.Search(v, 3);
+              if (r.size() > 3) hard++;
+            } break;
+            case 2: g.Delete(key - 2); break;
+            default: g.Lookup(key - 3);
+          }
+        } catch (const Error &e) {
+          if (i % 4 == 0) soft++; else hard++;
+        }
+      }
+    });
+  for (auto &th : pool) th.join();
+  CHECK(hard == 0);
+  CHECK(g.Len() >= 1 && g.Len() <= 32 + threads * ops / 4);
+  auto r = g.Search(Vector(d, 0.5f), 3);
+  CHECK(!r.empty() && r.size() <= 3);
+  std::printf("thread safety: %d add(s) refused with the reference's own error, len %d\n", (int)soft, g.Len());
+}
+
 int main(int argc, char **argv) {
   const std::string mode = argc > 1 ? argv[1] : "--cpu";
   cpu_tests();
   if (mode == "--gpu") {
     gpu_tests();
     gpu_exact_tests();
+    gpu_thread_safety_test();
   }
   else if (mode == "--cpu-nodevice") no_device_test();
   std::printf("%s: %d failure(s)\n", mode.c_str(), failures);
