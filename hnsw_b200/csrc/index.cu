@@ -242,6 +242,7 @@ void b200hnsw_destroy(b200hnsw_t *h) {
   cudaFree(h->d.adjU);
   cudaFree(h->d.inbox);
   cudaFree(h->d_err_word);
+  if (h->d_spec) cudaFree(h->d_spec);
   delete h;
 }
 
@@ -490,6 +491,21 @@ int b200hnsw_set_build_mode(b200hnsw_t *h, int32_t mode) {
   return 0;
 }
 int32_t b200hnsw_get_build_mode(const b200hnsw_t *h) { return h ? h->build_mode : 0; }
+
+int b200hnsw_set_add_window(b200hnsw_t *h, int32_t window) {
+  if (!h || window < 0 || window > 128) {
+    set_error("set_add_window: window must be 0 (automatic), 1 (sequential) or 2..128, got %d", window);
+    return B200HNSW_ERR_BAD_ARG;
+  }
+  h->add_window = window;
+  return 0;
+}
+int b200hnsw_get_add_window_stats(const b200hnsw_t *h, int64_t *accepted, int64_t *redone) {
+  if (!h) return B200HNSW_ERR_BAD_ARG;
+  if (accepted) *accepted = (int64_t)h->spec_accepted_redone[0];
+  if (redone) *redone = (int64_t)h->spec_accepted_redone[1];
+  return 0;
+}
 
 int32_t b200hnsw_get_visited_capacity(const b200hnsw_t *h) { return h ? h->vis_hint.load() : 0; }
 int b200hnsw_set_visited_capacity(b200hnsw_t *h, int32_t entries) {

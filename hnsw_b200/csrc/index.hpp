@@ -78,6 +78,12 @@ struct b200hnsw {
   // bit 0: some stored row has |x|^2 = 0, non-finite or outside [1e-18, 1e18] (NaN distances possible: traverse.cuh).
   // d_row_flags is the device word the upload paths OR into (flag_rows); row_flags its host mirror, refreshed at the end
   // of every mutating call.
+  // the speculative windowed Add (spec_insert.cu): 0 = window chosen from the row count, 1 = the sequential kernel,
+  // >= 2 = that many nodes in flight (b200hnsw_set_add_window); d_spec = its device scratch
+  int add_window = 0;
+  void *d_spec = nullptr;
+  size_t spec_bytes = 0;
+  unsigned long long spec_accepted_redone[2] = {0, 0};
   int build_mode = 0;  // B200HNSW_MODE_*: the layer search the wave Add runs (b200hnsw_set_build_mode)
   int *d_row_flags = nullptr;
   std::atomic<int> row_flags{0};

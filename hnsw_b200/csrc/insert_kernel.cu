@@ -14,334 +14,9 @@
 #include <cstring>
 #include <vector>
 
-#include "index.hpp"
-#include "listops.cuh"
+#include "inserter.cuh"
 
 namespace b200 {
-
-constexpr int INS_WARPS = 16;
-constexpr int INS_THREADS = INS_WARPS * 32;
-
-struct InsertParams {
-  long long first_row;
-  int n;                   // nodes in this batch
-  const int32_t *levels;   // [n] device
-  int m, ef, metric;
-  int n_layers;
-  int entries[B200HNSW_MAX_LAYERS];
-  int *state_out;                 // [1 + MAX_LAYERS]: n_layers, entries
-  unsigned long long *counters;   // [8]: evals, expansions, nbr_reads, evict_evals, replenish_evals, evictions
-  int *error;
-  int heap_c, heap_r, vis_cap;    // search scratch (uint2 slots, uint2 slots, u32 entries)
-  int cand_cap, rep_cap;          // replenish candidates (<= M*M) and its visited table (power of two)
-  const uint8_t *dead;            // [rows] deleted flags, null while nothing was deleted
-  // Delete (delete_kernel): rows to isolate, in call order
-  const int32_t *del_rows;
-  const int32_t *del_levels;
-  uint8_t *dead_set;              // deleted flags, written by the delete kernel
-};
-
-struct MutGraph {
-  float4 *vec;
-  int64_t *keys;
-  int32_t *adj0;
-  int32_t *adjU;
-  int32_t *upper_off;
-  int32_t row_chunks, M, dim;
-  __device__ __forceinline__ int32_t *list(int layer, int row) const {
-    if (layer == 0) return adj0 + (size_t)row * M;
-    return adjU + ((size_t)upper_off[row] + (layer - 1)) * M;
-  }
-};
-
-// shared-memory control block
-struct InsCtl {
-  int n_layers;
-  int elevator;
-  int cnt;        // neighbourhood size of the current layer search, -1 on overflow
-  int flag;       // overflow / continue flag of the current block-wide step
-  int tmp_len;    // entries in tmp list
-  int worst;      // evicted neighbour
-  int wl_len;     // degree of the node being replenished
-  int ncand;      // replenish candidates
-  int need_heap;  // replenish needs the exact heap (NaN present or more than one pop)
-  int abort_;
-  int entries[B200HNSW_MAX_LAYERS];
-  int cnts[B200HNSW_MAX_LAYERS];  // neighbourhood sizes of the node being inserted, -1 = the layer was empty
-};
-
-// ---- block-wide state -------------------------------------------------------------------------------------------
-template <int CPL, int U>
-struct Inserter {
-  MutGraph g;
-  InsertParams p;
-  InsCtl *ctl;
-  int *nbh;        // [MAX_LAYERS][M] neighbourhood rows per layer (heap-array order)
-  int *tmp;        // [M+1] list being edited
-  float *tmpd;     // [M+1] eviction-scan distances
-  int *wl;         // [M+1] list of the node being replenished
-  int *cand;       // [cand_cap] replenish candidates in push order
-  float *candd;    // [cand_cap]
-  uint32_t *rep;   // [rep_cap] replenish visited table
-  GoHeap C, R;
-  Visited V;
-  int tid, lane, warp;
-  unsigned long long c_evict, c_repl, c_evictions;  // thread-local counters (summed at the end)
-
-  // distance(row = a, query = b) for a set of rows against one "query" row, warps striding over the items
-  __device__ __forceinline__ void block_distances(const int *ids, int n, int qrow, int metric, float *out) {
-    QueryRegs<CPL> Q;
-    load_query<CPL>(Q, reinterpret_cast<const float *>(g.vec + (size_t)qrow * g.row_chunks), g.dim, g.row_chunks,
-                    lane);
-    for (int base = warp * U; base < n; base += INS_WARPS * U) {
-      float4 rows[U][CPL];
-#pragma unroll
-      for (int u = 0; u < U; u++)
-        if (base + u < n) load_row<CPL>(rows[u], g.vec + (size_t)ids[base + u] * g.row_chunks, g.row_chunks, lane);
-#pragma unroll
-      for (int u = 0; u < U; u++)
-        if (base + u < n) {
-          float d = finish_distance<CPL>(rows[u], Q, metric);
-          if (lane == 0) out[base + u] = d;
-        }
-    }
-  }
-
-  // layerNode.replenish(m) -- graph.go:172-219; always CosineDistance.  Block-wide; ends with a barrier.
-  __device__ void replenish(int layer, int w) {
-    const int m = p.m, M = g.M;
-    int32_t *lw = g.list(layer, w);
-    __syncthreads();  // every thread has finished reading the control block of the previous step
-    for (int i = tid; i < p.rep_cap; i += INS_THREADS) rep[i] = ~0u;
-    if (warp == 0) {
-      int deg = warp_load_list(lw, M, wl, lane);
-      if (lane == 0) {
-        ctl->wl_len = deg;
-        ctl->flag = deg < m;  // graph.go:173-175
-        ctl->ncand = 0;
-      }
-    }
-    __syncthreads();
-    if (!ctl->flag) return;
-    // all neighbours' lists are fetched at once (independent gathers), one list per warp, into shared memory
-    int *nl = reinterpret_cast<int *>(candd);  // [deg][M], free until the distances are written
-    {
-      const int deg = ctl->wl_len;
-      for (int i = warp; i < deg; i += INS_WARPS) {
-        const int32_t *ln = g.list(layer, wl[i]);
-        for (int j = lane; j < M; j += 32) nl[i * M + j] = ln[j];
-      }
-    }
-    __syncthreads();
-    if (warp == 0) {
-      Visited RV{rep, (uint32_t)p.rep_cap - 1, 0};
-      const int deg = ctl->wl_len;
-      // graph.go:183-190: visited = {w} U neighbours(w)
-      if (lane == 0) RV.insert((uint32_t)w);
-      for (int i = lane; i < deg; i += 32) RV.insert((uint32_t)wl[i]);
-      __syncwarp();
-      // graph.go:193-210: neighbours of neighbours, ascending key order at both levels
-      int nc = 0;
-      for (int i = 0; i < deg; i++) {
-        const int *ln = nl + i * M;
-        for (int base = 0; base < M; base += 32) {
-          int v = -1;
-          if (base + lane < M) v = ln[base + lane];
-          unsigned vm = __ballot_sync(FULL, v >= 0);
-          if (!vm) break;
-          bool fresh = v >= 0 && RV.insert((uint32_t)v);
-          unsigned fm = __ballot_sync(FULL, fresh);
-          if (fresh) cand[nc + __popc(fm & ((1u << lane) - 1))] = v;
-          nc += __popc(fm);
-          if (vm != FULL) break;
-        }
-      }
-      if (lane == 0) ctl->ncand = nc;
-    }
-    __syncthreads();
-    const int nc = ctl->ncand;
-    if (nc == 0) return;
-    block_distances(cand, nc, w, 1 /*cosine*/, candd);  // CosineDistance(candidate.Value, n.Value)
-    if (tid == 0) c_repl += nc;
-    __syncthreads();
-    if (warp == 0) {
-      // graph.go:213-218: pop best-first until the list is full.  The first pop of a min-heap filled by pushes is
-      // the first-pushed global minimum; that shortcut is exact when one pop suffices and no distance is NaN.
-      int deg = ctl->wl_len;
-      const int need = m - deg;
-      bool nan = false;
-      for (int i = lane; i < nc; i += 32) nan = nan || (candd[i] != candd[i]);
-      nan = __any_sync(FULL, nan);
-      if (need == 1 && !nan) {
-        float bd = __int_as_float(0x7f800000);
-        int bi = 0x7fffffff;
-        for (int i = lane; i < nc; i += 32) {
-          float d = candd[i];
-          if (d < bd || (d == bd && i < bi)) {
-            bd = d;
-            bi = i;
-          }
-        }
-#pragma unroll
-        for (int off = 16; off >= 1; off >>= 1) {
-          float od = __shfl_xor_sync(FULL, bd, off);
-          int oi = __shfl_xor_sync(FULL, bi, off);
-          if (od < bd || (od == bd && oi < bi)) {
-            bd = od;
-            bi = oi;
-          }
-        }
-        deg = warp_sorted_insert(wl, deg, cand[bi], g.keys, lane);
-      } else {
-        // exact heap emulation (lane 0) in the search heap C's storage is too small in general: use candd/cand
-        // in place as a binary heap built by successive pushes.
-        if (lane == 0) {
-          // build: push i-th element into heap of size i (arrays themselves are the heap storage)
-          for (int i = 1; i < nc; i++) {
-            float d = candd[i];
-            int id_ = cand[i];
-            int j = i;
-            while (j > 0) {
-              int pi = (j - 1) >> 1;
-              if (!(d < candd[pi])) break;
-              candd[j] = candd[pi];
-              cand[j] = cand[pi];
-              j = pi;
-            }
-            candd[j] = d;
-            cand[j] = id_;
-          }
-        }
-        __syncwarp();
-        int hn = nc;
-        while (hn > 0 && deg < m) {
-          int best = cand[0];
-          __syncwarp();
-          if (lane == 0) {  // container/heap.Pop
-            int n = --hn;
-            float md = candd[n];
-            int mid = cand[n];
-            int i = 0;
-            for (;;) {
-              int j1 = 2 * i + 1;
-              if (j1 >= n) break;
-              int j = j1;
-              if (j1 + 1 < n && candd[j1 + 1] < candd[j1]) j = j1 + 1;
-              if (!(candd[j] < md)) break;
-              candd[i] = candd[j];
-              cand[i] = cand[j];
-              i = j;
-            }
-            if (n > 0) {
-              candd[i] = md;
-              cand[i] = mid;
-            }
-          }
-          hn = __shfl_sync(FULL, hn, 0);
-          __syncwarp();
-          deg = warp_sorted_insert(wl, deg, best, g.keys, lane);  // addNeighbor(best): len <= m, no overflow
-        }
-      }
-      warp_store_list(lw, M, wl, deg, lane);
-    }
-    __syncthreads();
-  }
-
-  // layerNode.addNeighbor(newNode, m, dist) on node n -- graph.go:41-81.  Block-wide; ends with a barrier.
-  __device__ void add_neighbor(int layer, int n, int x, int metric) {
-    const int m = p.m, M = g.M;
-    int32_t *ln = g.list(layer, n);
-    __syncthreads();  // every thread has finished reading the control block of the previous step
-    if (warp == 0) {
-      int deg = warp_load_list(ln, M, tmp, lane);
-      int nd = warp_sorted_insert(tmp, deg, x, g.keys, lane);  // graph.go:50
-      bool over = nd > m;                                      // graph.go:51-53
-      if (!over && nd != deg) warp_store_list(ln, M, tmp, nd, lane);
-      if (lane == 0) {
-        ctl->flag = over;
-        ctl->tmp_len = nd;
-      }
-    }
-    __syncthreads();
-    if (!ctl->flag) return;
-    const int len = ctl->tmp_len;  // m + 1
-    // graph.go:60-71: dist(neighbor.Value, n.Value) for every neighbour
-    block_distances(tmp, len, n, metric, tmpd);
-    __syncthreads();
-    if (tid == 0) {
-      c_evict += len;
-      float worst_d = __int_as_float(0xff800000);  // -Inf
-      int worst = -1, wpos = -1;
-      for (int i = 0; i < len; i++) {  // ascending key order stands in for Go's map order
-        float d = tmpd[i];
-        if (d > worst_d || worst < 0) {
-          worst_d = d;
-          worst = tmp[i];
-          wpos = i;
-        }
-      }
-      for (int i = wpos; i + 1 < len; i++) tmp[i] = tmp[i + 1];  // delete(n.neighbors, worst.Key)
-      ctl->worst = worst;
-      ctl->tmp_len = len - 1;
-      c_evictions++;
-    }
-    __syncthreads();
-    const int worst = ctl->worst;
-    if (warp == 0) warp_store_list(ln, M, tmp, ctl->tmp_len, lane);
-    if (warp == 1) {  // graph.go:75-78: delete the back-link
-      int32_t *lwp = g.list(layer, worst);
-      int dw = warp_load_list(lwp, M, wl, lane);
-      int nd = warp_list_remove(wl, dw, n, lane);
-      if (nd != dw) warp_store_list(lwp, M, wl, nd, lane);
-    }
-    __syncthreads();
-    replenish(layer, worst);  // graph.go:79
-  }
-
-  // layerNode.isolate(m) -- graph.go:223-235: every neighbour drops its link to n and is replenished at once, in
-  // ascending key order (the stand-in for Go's map order).  n's own list is left as it is, as in the reference.
-  __device__ void isolate(int layer, int n) {
-    const int M = g.M;
-    __syncthreads();
-    if (warp == 0) {
-      int deg = warp_load_list(g.list(layer, n), M, nbh, lane);
-      if (lane == 0) ctl->cnt = deg;
-    }
-    __syncthreads();
-    const int deg = ctl->cnt;
-    for (int i = 0; i < deg; i++) {
-      const int nb = nbh[i];
-      if (warp == 1) {  // graph.go:232: delete(neighbor.neighbors, n.Key)
-        int32_t *l = g.list(layer, nb);
-        int d = warp_load_list(l, M, wl, lane);
-        int nd = warp_list_remove(wl, d, n, lane);
-        if (nd != d) warp_store_list(l, M, wl, nd, lane);
-      }
-      replenish(layer, nb);  // graph.go:233 (starts with a barrier)
-    }
-  }
-};
-
-static __host__ __device__ inline size_t al16(size_t v) { return (v + 15) & ~(size_t)15; }
-
-struct InsLayout {
-  size_t ctl, heapC, heapR, vis, nbh, tmp, tmpd, wl, cand, candd, rep, total;
-  __host__ __device__ InsLayout(const InsertParams &p, int M) {
-    size_t o = 0;
-    ctl = o;   o += al16(sizeof(InsCtl));
-    heapC = o; o += al16(sizeof(uint2) * p.heap_c);
-    heapR = o; o += al16(sizeof(uint2) * p.heap_r);
-    vis = o;   o += al16(sizeof(uint32_t) * p.vis_cap);
-    nbh = o;   o += al16(sizeof(int) * (size_t)B200HNSW_MAX_LAYERS * M);
-    tmp = o;   o += al16(sizeof(int) * (M + 1));
-    tmpd = o;  o += al16(sizeof(float) * (M + 1));
-    wl = o;    o += al16(sizeof(int) * (M + 1));
-    cand = o;  o += al16(sizeof(int) * p.cand_cap);
-    candd = o; o += al16(sizeof(float) * p.cand_cap);
-    rep = o;   o += al16(sizeof(uint32_t) * p.rep_cap);
-    total = o;
-  }
-};
 
 template <int CPL, int U>
 __global__ void __launch_bounds__(INS_THREADS) insert_kernel(MutGraph g, InsertParams p) {
@@ -492,12 +167,6 @@ __global__ void __launch_bounds__(INS_THREADS) delete_kernel(MutGraph g, InsertP
   if (I.tid == 0) atomicAdd(&p.counters[4], I.c_repl);
 }
 
-static int pow2_at_least(int v) {
-  int r = 1;
-  while (r < v) r <<= 1;
-  return r;
-}
-
 template <int CPL, int U>
 static int launch_insert_t(b200hnsw *h, const MutGraph &g, InsertParams &p, cudaStream_t s) {
   auto kern = p.del_rows ? delete_kernel<CPL, U> : insert_kernel<CPL, U>;
@@ -513,20 +182,8 @@ static int launch_insert_t(b200hnsw *h, const MutGraph &g, InsertParams &p, cuda
 }
 
 static int launch_insert(b200hnsw *h, InsertParams &p, cudaStream_t s) {
-  MutGraph g;
-  g.vec = reinterpret_cast<float4 *>(h->d.vec);
-  g.keys = h->d.keys;
-  g.adj0 = h->d.adj0;
-  g.adjU = h->d.adjU;
-  g.upper_off = h->d.upper_off;
-  g.row_chunks = h->row_floats / 4;
-  g.M = h->M;
-  g.dim = h->cfg.dim;
-  p.heap_c = (p.ef + 2) & ~1;
-  p.heap_r = (p.m + 2) & ~1;
-  p.vis_cap = 1024;
-  p.cand_cap = g.M * g.M + 4;  // also holds the [deg][M] staging of the neighbours' lists
-  p.rep_cap = pow2_at_least(2 * (g.M * g.M + g.M + 2));
+  MutGraph g = mut_graph_of(h);
+  size_insert_scratch(p, g);
   int cpl = (g.row_chunks + 31) / 32;
   switch (cpl) {
     case 1: return launch_insert_t<1, 4>(h, g, p, s);
@@ -670,15 +327,12 @@ extern "C" int b200hnsw_add_batch(b200hnsw_t *h, const float *vectors, const int
     h->n_layers = n_layers;
     memcpy(h->entry, entries, sizeof entries);
   };
-  for (int64_t off = 0; off < n; off += CH) {
-    int64_t cnt = std::min(CH, n - off);
-    if ((e = cudaMemcpyAsync(d_levels, levels + off, sizeof(int32_t) * (size_t)cnt, cudaMemcpyHostToDevice, s)) !=
-        cudaSuccess)
-      return fail(cuda_fail(e, "levels copy"));
+  // `count` nodes starting at batch index `first` through the sequential kernel; *bad = nodes of them that went in
+  auto run_sequential = [&](int64_t first, int64_t count, const int32_t *d_lev, int *err, int64_t *bad) -> int {
     InsertParams p{};
-    p.first_row = h->n + off;
-    p.n = (int)cnt;
-    p.levels = d_levels;
+    p.first_row = h->n + first;
+    p.n = (int)count;
+    p.levels = d_lev;
     p.m = m;
     p.ef = ef;
     p.metric = metric;
@@ -688,23 +342,78 @@ extern "C" int b200hnsw_add_batch(b200hnsw_t *h, const float *vectors, const int
     p.counters = d_ctr;
     p.error = d_err;
     p.dead = h->n_dead ? h->d.dead : nullptr;
-    if ((rc = launch_insert(h, p, s))) return fail(rc);
+    int rc2 = launch_insert(h, p, s);
+    if (rc2) return rc2;
     launches++;
     int state[2 + B200HNSW_MAX_LAYERS];
-    int err = 0;
-    if ((e = cudaMemcpyAsync(state, d_state, sizeof state, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
-        (e = cudaMemcpyAsync(&err, d_err, sizeof err, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
-        (e = cudaStreamSynchronize(s)) != cudaSuccess)
-      return fail(cuda_fail(e, "add kernel"));
+    *err = 0;
+    cudaError_t e2;
+    if ((e2 = cudaMemcpyAsync(state, d_state, sizeof state, cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
+        (e2 = cudaMemcpyAsync(err, d_err, sizeof(int), cudaMemcpyDeviceToHost, s)) != cudaSuccess ||
+        (e2 = cudaStreamSynchronize(s)) != cudaSuccess)
+      return cuda_fail(e2, "add kernel");
     n_layers = state[0];
     memcpy(entries, state + 1, sizeof entries);
-    if (err) {
-      // the kernel stopped in front of node `bad` with the graph as its predecessors left it: keep those
-      const int64_t bad = off + state[1 + B200HNSW_MAX_LAYERS];
-      commit(bad);
-      set_error(err == 1 ? "add: a layer search overflowed the visited set (node %lld of the batch)"
-                         : "no nodes found in neighborhood search (node %lld of the batch)", (long long)bad);
-      return fail(err == 1 ? B200HNSW_ERR_VISITED_OVERFLOW : B200HNSW_ERR_STATE);
+    *bad = *err ? state[1 + B200HNSW_MAX_LAYERS] : count;
+    return 0;
+  };
+  auto report = [&](int err, int64_t bad) {  // the kernel stopped in front of node `bad`: its predecessors stay
+    commit(bad);
+    if (err == 9) {
+      set_error("add: internal wait timed out in the windowed Add (node %lld of the batch)", (long long)bad);
+      return fail(B200HNSW_ERR_CUDA);
+    }
+    set_error(err == 1 ? "add: a layer search overflowed the visited set (node %lld of the batch)"
+                       : "no nodes found in neighborhood search (node %lld of the batch)", (long long)bad);
+    return fail(err == 1 ? B200HNSW_ERR_VISITED_OVERFLOW : B200HNSW_ERR_STATE);
+  };
+  for (int64_t off = 0; off < n; off += CH) {
+    int64_t cnt = std::min(CH, n - off);
+    if ((e = cudaMemcpyAsync(d_levels, levels + off, sizeof(int32_t) * (size_t)cnt, cudaMemcpyHostToDevice, s)) !=
+            cudaSuccess ||
+        (e = cudaMemsetAsync(d_err, 0, sizeof(int), s)) != cudaSuccess)
+      return fail(cuda_fail(e, "levels copy"));
+    // The same graph either way (spec_insert.cu): a window of insertions speculated in parallel and committed in input
+    // order where that pays (enough rows for two neighbourhoods to be apart), else one CTA one node at a time.
+    int window = h->add_window ? h->add_window : spec_window_auto(h->n + off);
+    int64_t pos = 0;
+    while (pos < cnt) {
+      int err = 0;
+      if (window >= 2 && cnt - pos >= 2) {
+        InsertParams p{};
+        p.first_row = h->n + off + pos;
+        p.n = (int)(cnt - pos);
+        p.levels = d_levels + pos;
+        p.m = m;
+        p.ef = ef;
+        p.metric = metric;
+        p.n_layers = n_layers;
+        memcpy(p.entries, entries, sizeof entries);
+        p.counters = d_ctr;
+        p.dead = h->n_dead ? h->d.dead : nullptr;
+        int done = 0;
+        rc = launch_spec_insert(h, p, window, &done, &err, &n_layers, entries, h->spec_accepted_redone, s);
+        if (rc < 0) return fail(rc);
+        if (rc > 0) {
+          window = 1;  // does not fit this device / this dim: sequential
+          continue;
+        }
+        launches++;
+        pos += done;
+        if (err == 8) {  // this node writes more lists than the overlay holds: the sequential kernel takes it
+          int64_t bad = 0;
+          if ((rc = run_sequential(off + pos, 1, d_levels + pos, &err, &bad))) return fail(rc);
+          if (err) return report(err, off + pos);
+          pos += 1;
+        } else if (err) {
+          return report(err, off + pos);
+        }
+      } else {
+        int64_t bad = 0;
+        if ((rc = run_sequential(off + pos, cnt - pos, d_levels + pos, &err, &bad))) return fail(rc);
+        if (err) return report(err, off + pos + bad);
+        pos = cnt;
+      }
     }
   }
   unsigned long long ctr[8];

@@ -9,12 +9,23 @@ namespace b200 {
 // ---- warp-level list helpers (lists: stride M, sorted by key, -1 padded) -----------------------------------------
 
 // load a list into shared memory; returns its degree (uniform over the warp)
+// CG: read past L1 (the speculative Add: another CTA may have rewritten the list since this SM last saw it)
+template <bool CG = false>
 __device__ __forceinline__ int warp_load_list(const int32_t *lp, int M, int *dst, int lane) {
   int deg = 0;
   for (int base = 0; base < M; base += 32) {
     int v = -1;
-    if (base + lane < M) v = lp[base + lane];
+    if (base + lane < M) v = CG ? __ldcg(lp + base + lane) : lp[base + lane];
     unsigned mk = __ballot_sync(FULL, v >= 0);
+    if constexpr (CG) {
+      // a list caught while its owner rewrites it can show a gap; only the entries in front of it are used (the read is
+      // thrown away by the commit test anyway, it just must not index anything with -1)
+      const int lead = __ffs(~mk) - 1;  // -1 when all 32 are valid
+      if (lead >= 0) {
+        mk = (1u << lead) - 1u;
+        if (lane >= lead) v = -1;
+      }
+    }
     if (base + lane < M) dst[base + lane] = v;
     deg += __popc(mk);
     if (mk != FULL) break;

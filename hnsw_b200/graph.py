@@ -160,6 +160,8 @@ class Graph:
         self._h, self._dim, self._max_m = h, dim, cfg.max_m
         if getattr(self, "_build_mode", 0):
             _lib.check(_lib.lib().b200hnsw_set_build_mode(self._h, self._build_mode))
+        if getattr(self, "_add_window", 0):
+            _lib.check(_lib.lib().b200hnsw_set_add_window(self._h, self._add_window))
         self._vecs = np.zeros((max(self._capacity, 1024), dim), np.float32)
 
     def close(self):
@@ -473,6 +475,22 @@ class Graph:
         self._build_mode = int(mode)
         if self._h is not None:
             _lib.check(_lib.lib().b200hnsw_set_build_mode(self._h, self._build_mode))
+
+    def set_add_window(self, window: int):
+        """The SCHEDULE of Add / BatchAdd, never the graph they build (include/b200hnsw.h: b200hnsw_set_add_window):
+        0 = automatic, 1 = one node at a time on one CTA, >= 2 = that many insertions speculated in parallel and committed
+        in input order."""
+        self._add_window = int(window)
+        if self._h is not None:
+            _lib.check(_lib.lib().b200hnsw_set_add_window(self._h, self._add_window))
+
+    def add_window_stats(self):
+        """(speculations accepted, insertions run again by the committer) since the handle was created."""
+        if self._h is None:
+            return 0, 0
+        a, r = np.zeros(1, np.int64), np.zeros(1, np.int64)
+        _lib.check(_lib.lib().b200hnsw_get_add_window_stats(self._h, a.ctypes.data_as(_lib.i64p), r.ctypes.data_as(_lib.i64p)))
+        return int(a[0]), int(r[0])
 
     @_writes
     def Add(self, *nodes: Node, levels: Optional[Sequence[int]] = None):

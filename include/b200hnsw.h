@@ -211,6 +211,18 @@ int b200hnsw_add_batch_waves(b200hnsw_t *h, const float *vectors, const int64_t 
 int b200hnsw_set_build_mode(b200hnsw_t *h, int32_t mode);
 int32_t b200hnsw_get_build_mode(const b200hnsw_t *h);
 
+/* The SCHEDULE of b200hnsw_add_batch, never its result (no reference counterpart: the reference's Add is a loop).
+ * The reference-order Add speculates a window of pending insertions in parallel -- each on its own CTA, reads logged,
+ * writes kept in a private overlay -- and commits them in input order; a speculation that read a list an earlier commit
+ * of the window wrote is run again at the head of the order (hnsw_b200/csrc/spec_insert.cu).  The graph is the one the
+ * one-node-at-a-time kernel builds, bit for bit (tests/test_add_parity_gpu.py runs both against the oracle).
+ * window = 0: chosen from the number of rows (1 below ~12 000 rows, then ~sqrt(rows / 3000), at most 48);
+ * window = 1: one CTA, one node at a time; 2..128: that many insertions in flight.
+ * b200hnsw_get_add_window_stats: speculations accepted / insertions the committer ran again, summed over the handle's
+ * life. */
+int b200hnsw_set_add_window(b200hnsw_t *h, int32_t window);
+int b200hnsw_get_add_window_stats(const b200hnsw_t *h, int64_t *accepted, int64_t *redone);
+
 /* Graph.Delete / Graph.BatchDelete (graph.go:843-895; layerNode.isolate graph.go:223-235, replenish graph.go:172-219).
  * rows[i] = the row the caller's key map holds for the i-th key, -1 for an unknown key; processed in call order, as
  * the reference's loop under one lock.  out_deleted[i] (may be null) mirrors the reference's []bool: 1 iff the row

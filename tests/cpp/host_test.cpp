@@ -295,8 +295,8 @@ static void gpu_thread_safety_test() {
   for (auto &th : pool) th.join();
   CHECK(hard == 0);
   CHECK(g.Len() >= 1 && g.Len() <= 32 + threads * ops / 4);
-  auto r = g.Search(Vector(d, 0.5f), 3);
-  CHECK(!r.empty() && r.size() <= 3);
+  auto r = g.Search(Vector(d, 0.5f), 3);  // may be empty: a deleted elevator ends the descent (graph.go:573-593)
+  CHECK(r.size() <= 3);
   std::printf("thread safety: %d add(s) refused with the reference's own error, len %d\n", (int)soft, g.Len());
 }
 
