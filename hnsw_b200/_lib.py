@@ -76,7 +76,7 @@ SYMBOLS = {
     "b200hnsw_set_build_mode": (C.c_int, [C.c_void_p, C.c_int32]),
     "b200hnsw_get_build_mode": (C.c_int32, [C.c_void_p]),
     "b200hnsw_set_add_window": (C.c_int, [C.c_void_p, C.c_int32]),
-    "b200hnsw_get_add_window_stats": (C.c_int, [C.c_void_p, i64p, i64p]),
+    "b200hnsw_get_add_window_stats": (C.c_int, [C.c_void_p, i64p, i64p, i64p]),
     "b200hnsw_get_visited_capacity": (C.c_int32, [C.c_void_p]),
     "b200hnsw_set_visited_capacity": (C.c_int, [C.c_void_p, C.c_int32]),
     "b200hnsw_merge_topk_device": (C.c_int, [C.c_int32, C.c_int32, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p,

@@ -500,10 +500,11 @@ int b200hnsw_set_add_window(b200hnsw_t *h, int32_t window) {
   h->add_window = window;
   return 0;
 }
-int b200hnsw_get_add_window_stats(const b200hnsw_t *h, int64_t *accepted, int64_t *redone) {
+int b200hnsw_get_add_window_stats(const b200hnsw_t *h, int64_t *accepted, int64_t *redone, int64_t *repaired) {
   if (!h) return B200HNSW_ERR_BAD_ARG;
   if (accepted) *accepted = (int64_t)h->spec_accepted_redone[0];
   if (redone) *redone = (int64_t)h->spec_accepted_redone[1];
+  if (repaired) *repaired = (int64_t)h->spec_accepted_redone[2];
   return 0;
 }
 

@@ -83,7 +83,7 @@ struct b200hnsw {
   int add_window = 0;
   void *d_spec = nullptr;
   size_t spec_bytes = 0;
-  unsigned long long spec_accepted_redone[2] = {0, 0};
+  unsigned long long spec_accepted_redone[3] = {0, 0, 0};  // + repaired by workers
   int build_mode = 0;  // B200HNSW_MODE_*: the layer search the wave Add runs (b200hnsw_set_build_mode)
   int *d_row_flags = nullptr;
   std::atomic<int> row_flags{0};

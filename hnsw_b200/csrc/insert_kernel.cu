@@ -33,6 +33,10 @@ __global__ void __launch_bounds__(INS_THREADS) insert_kernel(MutGraph g, InsertP
   I.cand = reinterpret_cast<int *>(smem + lay.cand);
   I.candd = reinterpret_cast<float *>(smem + lay.candd);
   I.rep = reinterpret_cast<uint32_t *>(smem + lay.rep);
+  I.repi = reinterpret_cast<int *>(smem + lay.repi);
+  I.own = reinterpret_cast<int *>(smem + lay.own);
+  I.ownk = reinterpret_cast<long long *>(smem + lay.ownk);
+  I.nbk = reinterpret_cast<long long *>(smem + lay.nbk);
   I.C = GoHeap{reinterpret_cast<uint2 *>(smem + lay.heapC), 0};
   I.R = GoHeap{reinterpret_cast<uint2 *>(smem + lay.heapR), 0};
   I.V = Visited{reinterpret_cast<uint32_t *>(smem + lay.vis), (uint32_t)p.vis_cap - 1, 0};
@@ -48,16 +52,12 @@ __global__ void __launch_bounds__(INS_THREADS) insert_kernel(MutGraph g, InsertP
     for (int l = 0; l < B200HNSW_MAX_LAYERS; l++) ctl->entries[l] = p.entries[l];
   }
   __syncthreads();
-  GraphView gv;
-  gv.vec = g.vec;
-  gv.adj0 = g.adj0;
-  gv.adjU = g.adjU;
-  gv.upper_off = g.upper_off;
-  gv.row_chunks = g.row_chunks;
-  gv.M = g.M;
-  gv.dim = g.dim;
   SearchCounters sc{0, 0, 0};
   bool aborted = false;
+#ifdef B200_K2_TIMING
+  for (int i = 0; i < 16; i++) I.tph[i] = 0;
+  I.tlast = clock64();
+#endif
   for (int j = 0; j < p.n && !aborted; j++) {
     const int row = (int)(p.first_row + j);
     const int L = p.levels[j];                          // randomLevel() drawn by the host (graph.go:457)
@@ -66,8 +66,8 @@ __global__ void __launch_bounds__(INS_THREADS) insert_kernel(MutGraph g, InsertP
     // Every layer search first, then the linking.  A layer's search reads that layer's lists only and linking at
     // layer l writes layer-l lists only, so the neighbourhoods equal those of the reference's interleaved loop
     // (graph.go:475-522); a failed Add (deleted elevator) then leaves the graph untouched.
-    if (warp == 0) {
-      QueryRegs<CPL> Q;
+    {
+      QueryRegs<CPL> Q;  // every warp holds the new node's vector: the block evaluates an expansion's rows together
       load_query<CPL>(Q, reinterpret_cast<const float *>(g.vec + (size_t)row * g.row_chunks), g.dim, g.row_chunks,
                       lane);
       int elevator = -1, bad = 0;
@@ -78,8 +78,8 @@ __global__ void __launch_bounds__(INS_THREADS) insert_kernel(MutGraph g, InsertP
           if (elevator >= 0 && p.dead && p.dead[elevator]) {
             cnt = 0;  // layer.nodes[*elevator] == nil: the search returns nothing (graph.go:101-103)
           } else {
-            cnt = layer_search_ref<CPL, U>(gv, l, sp, p.m, p.ef, p.metric, Q, I.C, I.R, I.V, sc, lane);  // :500
-            for (int i = lane; i < cnt; i += 32) I.nbh[l * g.M + i] = I.R.id(i);
+            cnt = I.block_layer_search(l, sp, Q, sc);   // graph.go:500
+            for (int i = tid; i < cnt; i += INS_THREADS) I.nbh[l * g.M + i] = I.R.id(i);
             if (cnt > 0) elevator = I.R.id(0);          // graph.go:508
           }
           if (cnt <= 0) {  // visited overflow (< 0) or "no nodes found in neighborhood search" (graph.go:501-505)
@@ -87,12 +87,14 @@ __global__ void __launch_bounds__(INS_THREADS) insert_kernel(MutGraph g, InsertP
             break;
           }
         }
-        if (lane == 0) ctl->cnts[l] = cnt;
-        __syncwarp();
+        if (tid == 0) ctl->cnts[l] = cnt;
       }
-      if (lane == 0) ctl->flag = bad;
+      if (tid == 0) ctl->flag = bad;
     }
     __syncthreads();
+#ifdef B200_K2_TIMING
+    if (tid == 0) { const long long t__ = clock64(); I.tph[9] += t__ - I.tlast; I.tlast = t__; }
+#endif
     if (ctl->flag) {
       aborted = true;
       if (tid == 0) {
@@ -108,10 +110,12 @@ __global__ void __launch_bounds__(INS_THREADS) insert_kernel(MutGraph g, InsertP
         continue;
       }
       if (L >= l) {  // graph.go:510-521
+        I.own_begin(I.nbh + l * g.M, cnt);
         for (int t = 0; t < cnt; t++) {
           const int nb = I.nbh[l * g.M + t];
           I.add_neighbor(l, nb, row, p.metric);
-          I.add_neighbor(l, row, nb, p.metric);
+          if (ctl->own_dirty) I.add_neighbor(l, row, nb, p.metric);  // the general path (inserter.cuh: own_dirty)
+          else I.add_own(l, row, nb, I.nbk[t]);
         }
       }
     }
@@ -119,6 +123,13 @@ __global__ void __launch_bounds__(INS_THREADS) insert_kernel(MutGraph g, InsertP
     if (tid == 0 && L + 1 > old_layers) ctl->n_layers = L + 1;
     __syncthreads();
   }
+#ifdef B200_K2_TIMING
+  if (tid == 0)
+    printf("K2 cycles per node: search %lld | addNeighbor: load+insert %lld scan-dist %lld decide %lld store+backlink %lld | "
+           "replenish: load %lld nbr-lists %lld candidates %lld cand-dist %lld select+store %lld\n", I.tph[9] / p.n,
+           I.tph[0] / p.n, I.tph[1] / p.n, I.tph[2] / p.n, I.tph[3] / p.n, I.tph[4] / p.n, I.tph[5] / p.n, I.tph[6] / p.n,
+           I.tph[7] / p.n, I.tph[8] / p.n);
+#endif
   if (tid == 0) {
     p.state_out[0] = ctl->n_layers;
     for (int l = 0; l < B200HNSW_MAX_LAYERS; l++) p.state_out[1 + l] = ctl->entries[l];
@@ -126,7 +137,7 @@ __global__ void __launch_bounds__(INS_THREADS) insert_kernel(MutGraph g, InsertP
     atomicAdd(&p.counters[4], I.c_repl);
     atomicAdd(&p.counters[5], I.c_evictions);
   }
-  if (warp == 0 && lane == 0) {
+  if (tid == 0) {
     atomicAdd(&p.counters[0], sc.evals);
     atomicAdd(&p.counters[1], sc.expansions);
     atomicAdd(&p.counters[2], sc.nbr_reads);
@@ -151,6 +162,10 @@ __global__ void __launch_bounds__(INS_THREADS) delete_kernel(MutGraph g, InsertP
   I.cand = reinterpret_cast<int *>(smem + lay.cand);
   I.candd = reinterpret_cast<float *>(smem + lay.candd);
   I.rep = reinterpret_cast<uint32_t *>(smem + lay.rep);
+  I.repi = reinterpret_cast<int *>(smem + lay.repi);
+  I.own = reinterpret_cast<int *>(smem + lay.own);
+  I.ownk = reinterpret_cast<long long *>(smem + lay.ownk);
+  I.nbk = reinterpret_cast<long long *>(smem + lay.nbk);
   I.C = GoHeap{reinterpret_cast<uint2 *>(smem + lay.heapC), 0};
   I.R = GoHeap{reinterpret_cast<uint2 *>(smem + lay.heapR), 0};
   I.V = Visited{reinterpret_cast<uint32_t *>(smem + lay.vis), (uint32_t)p.vis_cap - 1, 0};

@@ -53,6 +53,13 @@ struct InsCtl {
   int n_layers;
   int elevator;
   int cnt;        // neighbourhood size of the current layer search, -1 on overflow
+  int cur;        // block_layer_search: node to expand next, -1 = the layer ends
+  int fresh_n;    // block_layer_search: unvisited neighbours of this expansion, -1 on visited overflow
+  int vcount;     // block_layer_search: entries in the visited table
+  int own_len;    // entries in the new node's own list on the layer being linked (own / ownk)
+  int own_dirty;  // the new node itself was evicted from a neighbour (its own list lost the back-link and was replenished,
+                  // graph.go:73-79): the shared-memory copy is dead, the rest of the layer goes through add_neighbor
+  int wsum[17];   // replenish: candidates found per warp (block-wide compaction)
   int flag;       // overflow / continue flag of the current block-wide step
   int tmp_len;    // entries in tmp list
   int worst;      // evicted neighbour
@@ -70,8 +77,17 @@ struct InsCtl {
 constexpr int OV_MAX = 1024;   // overlay lists per speculated node (33 per layer the node joins at M neighbours)
 constexpr int OV_HASH = 2048;  // shared-memory hash slots over them
 
+#ifdef B200_K2_TIMING  // exploration build only: cycles per phase as thread 0 sees them, printed by the kernel at its end
+#define K2_T(i) { if (tid == 0) { const long long t__ = clock64(); tph[i] += t__ - tlast; tlast = t__; } }
+#else
+#define K2_T(i)
+#endif
+
 template <int CPL, int U, bool SPEC = false>
 struct Inserter {
+#ifdef B200_K2_TIMING
+  long long tph[16], tlast;
+#endif
   MutGraph g;
   InsertParams p;
   InsCtl *ctl;
@@ -81,7 +97,11 @@ struct Inserter {
   int *wl;         // [M+1] list of the node being replenished
   int *cand;       // [cand_cap] replenish candidates in push order
   float *candd;    // [cand_cap]
-  uint32_t *rep;   // [rep_cap] replenish visited table
+  uint32_t *rep;   // [rep_cap] replenish: hash of the rows met (neighbours of neighbours, and the excluded ones)
+  int *repi;       // [rep_cap] replenish: position of the first occurrence of that row in the scan, -1 = excluded
+  int *own;        // [M + 1] the new node's own list on the layer being linked, sorted by key
+  long long *ownk; // [M + 1] their keys
+  long long *nbk;  // [M] keys of the layer's neighbourhood (nbh)
   GoHeap C, R;
   Visited V;
   int tid, lane, warp;
@@ -160,10 +180,8 @@ struct Inserter {
   }
 
   // distance(row = a, query = b) for a set of rows against one "query" row, warps striding over the items
-  __device__ __forceinline__ void block_distances(const int *ids, int n, int qrow, int metric, float *out) {
-    QueryRegs<CPL> Q;
-    load_query<CPL>(Q, reinterpret_cast<const float *>(g.vec + (size_t)qrow * g.row_chunks), g.dim, g.row_chunks,
-                    lane);
+  __device__ __forceinline__ void block_distances_q(const int *ids, int n, const QueryRegs<CPL> &Q, int metric,
+                                                    float *out) {
     for (int base = warp * U; base < n; base += INS_WARPS * U) {
       float4 rows[U][CPL];
 #pragma unroll
@@ -177,12 +195,119 @@ struct Inserter {
         }
     }
   }
+  __device__ __forceinline__ void block_distances(const int *ids, int n, int qrow, int metric, float *out) {
+    QueryRegs<CPL> Q;
+    load_query<CPL>(Q, reinterpret_cast<const float *>(g.vec + (size_t)qrow * g.row_chunks), g.dim, g.row_chunks,
+                    lane);
+    block_distances_q(ids, n, Q, metric, out);
+  }
+
+  // layerNode.search (graph.go:94-170) for the node being inserted (k = m), BLOCK-wide: warp 0 reads the popped node's
+  // list and filters it through the visited set, every warp evaluates rows of the expansion (all of them in flight at
+  // once: one memory round trip per expansion instead of one per U rows), thread 0 replays the order-dependent part
+  // (graph.go:146-166) in key order on the Go-exact heaps.  Every warp holds the query in registers (Q).
+  // Returns the result count (R holds the heap array, valid for every thread) or -1 on visited overflow.
+  __device__ int block_layer_search(int layer, int entry, const QueryRegs<CPL> &Q, SearchCounters &sc) {
+    const int M = g.M, k = p.m, ef = p.ef, metric = p.metric;
+    int *fresh = cand;       // [<= M] unvisited neighbours of the expansion, key order
+    float *freshd = candd;
+    __syncthreads();  // cand / candd / ctl are free
+    if (warp == 0) {
+      V.clear(lane);
+      if (lane == 0) fresh[0] = entry;
+    }
+    __syncthreads();
+    block_distances_q(fresh, 1, Q, metric, freshd);  // graph.go:107-108
+    __syncthreads();
+    if (tid == 0) {
+      // graph.go:109-127: candidates.Push(entry); result.Push(entry); visited[entry]; the first Pop takes it back
+      C.len = 0;
+      R.len = 0;
+      sc.evals++;
+      C.push(freshd[0], entry);
+      R.push(freshd[0], entry);
+      V.insert((uint32_t)entry);
+      ctl->cur = (int)C.pop().y;
+      ctl->vcount = 1;
+      ctl->cnt = 1;
+    }
+    for (;;) {
+      __syncthreads();
+      const int cur = ctl->cur;
+      if (cur < 0) break;
+      if (warp == 0) {
+        const int32_t *list = rlist(layer, cur);
+        int nf = 0, vc = ctl->vcount, nbr = 0;
+        bool ovf = false;
+        for (int base = 0; base < M; base += 32) {  // graph.go:137-144: ascending key order, unvisited only
+          int nb = -1;
+          if (base + lane < M) nb = ldl(list + base + lane);
+          const bool valid = nb >= 0;
+          const unsigned vm = __ballot_sync(FULL, valid);
+          if (vm == 0) break;
+          nbr += __popc(vm);
+          const bool fr = valid && V.insert((uint32_t)nb);
+          const unsigned fm = __ballot_sync(FULL, fr);
+          if (fr) {
+            fresh[nf + __popc(fm & ((1u << lane) - 1u))] = nb;
+            const float4 *rowp = g.vec + (size_t)nb * g.row_chunks;
+            for (int c = 0; c < g.row_chunks; c += 8) prefetch_l2(rowp + c);
+          }
+          nf += __popc(fm);
+          vc += __popc(fm);
+          if (vc * 2 > (int)V.mask) {  // load factor > 1/2: fail loudly
+            ovf = true;
+            break;
+          }
+        }
+        if (lane == 0) {
+          ctl->fresh_n = ovf ? -1 : nf;
+          ctl->vcount = vc;
+          sc.expansions++;
+          sc.nbr_reads += nbr;
+        }
+      }
+      __syncthreads();
+      const int nf = ctl->fresh_n;
+      if (nf < 0) return -1;
+      if (nf > 0) {
+        block_distances_q(fresh, nf, Q, metric, freshd);
+        __syncthreads();
+      }
+      if (tid == 0) {
+        bool improved = false;
+        for (int i = 0; i < nf; i++) {  // graph.go:146-159, key order
+          const float d = freshd[i];
+          const int id = fresh[i];
+          improved = improved || (R.len > 0 && d < R.min_dist());  // graph.go:147
+          if (R.len < k) {
+            R.push(d, id);
+          } else if (d < R.max_dist()) {  // result.Max() is the last slot
+            R.pop_last();
+            R.push(d, id);
+          }
+          C.push(d, id);
+          if (C.len > ef) C.pop_last();  // graph.go:157-159
+        }
+        sc.evals += nf;
+        int next;
+        if (!improved && R.len >= k) next = -1;             // graph.go:164-166
+        else next = C.len > 0 ? (int)C.pop().y : -1;         // graph.go:125-127
+        ctl->cur = next;
+        ctl->cnt = R.len;
+      }
+    }
+    return ctl->cnt;
+  }
 
   // layerNode.replenish(m) -- graph.go:172-219; always CosineDistance.  Block-wide; ends with a barrier.
   __device__ void replenish(int layer, int w) {
     const int m = p.m, M = g.M;
     __syncthreads();  // every thread has finished reading the control block of the previous step
-    for (int i = tid; i < p.rep_cap; i += INS_THREADS) rep[i] = ~0u;
+    for (int i = tid; i < p.rep_cap; i += INS_THREADS) {
+      rep[i] = ~0u;
+      repi[i] = 0x7fffffff;
+    }
     if (warp == 0) {
       int deg = warp_load_list<SPEC>(rlist(layer, w), M, wl, lane);
       if (lane == 0) {
@@ -192,6 +317,7 @@ struct Inserter {
       }
     }
     __syncthreads();
+    K2_T(4)
     if (!ctl->flag) return;
     // all neighbours' lists are fetched at once (independent gathers), one list per warp, into shared memory
     int *nl = reinterpret_cast<int *>(candd);  // [deg][M], free until the distances are written
@@ -203,37 +329,72 @@ struct Inserter {
       }
     }
     __syncthreads();
-    if (warp == 0) {
-      Visited RV{rep, (uint32_t)p.rep_cap - 1, 0};
+    K2_T(5)
+    {
+      // graph.go:183-210: the candidates are the neighbours of neighbours outside {w} U neighbours(w), in the order a
+      // scan of the lists (ascending key at both levels) FIRST meets them -- the heap's tie rule depends on that order.
+      // Block-wide: every row met goes into a hash with the smallest scan position it was seen at (-1 for the excluded
+      // rows); a position is a candidate iff it holds that smallest position; a prefix sum compacts them in scan order.
       const int deg = ctl->wl_len;
-      // graph.go:183-190: visited = {w} U neighbours(w)
-      if (lane == 0) RV.insert((uint32_t)w);
-      for (int i = lane; i < deg; i += 32) RV.insert((uint32_t)wl[i]);
-      __syncwarp();
-      // graph.go:193-210: neighbours of neighbours, ascending key order at both levels
-      int nc = 0;
-      for (int i = 0; i < deg; i++) {
-        const int *ln = nl + i * M;
-        for (int base = 0; base < M; base += 32) {
-          int v = -1;
-          if (base + lane < M) v = ln[base + lane];
-          unsigned vm = __ballot_sync(FULL, v >= 0);
-          if (!vm) break;
-          bool fresh = v >= 0 && RV.insert((uint32_t)v);
-          unsigned fm = __ballot_sync(FULL, fresh);
-          if (fresh) cand[nc + __popc(fm & ((1u << lane) - 1))] = v;
-          nc += __popc(fm);
-          if (vm != FULL) break;
+      const uint32_t rmask = (uint32_t)p.rep_cap - 1;
+      auto note = [&](uint32_t v, int pos) {
+        uint32_t h = (v * 2654435761u) >> 7;
+        for (;;) {
+          h &= rmask;
+          const uint32_t old = atomicCAS(&rep[h], ~0u, v);
+          if (old == ~0u || old == v) break;
+          h++;
         }
+        atomicMin(&repi[h], pos);
+      };
+      if (tid == 0) note((uint32_t)w, -1);
+      if (tid >= 32 && tid - 32 < deg) note((uint32_t)wl[tid - 32], -1);
+      const int total = deg * M;
+      for (int e = tid; e < total; e += INS_THREADS) {
+        const int v = nl[e];
+        if (v >= 0) note((uint32_t)v, e);
       }
-      if (lane == 0) ctl->ncand = nc;
+      __syncthreads();
+      int base_n = 0;
+      for (int c0 = 0; c0 < total; c0 += INS_THREADS) {
+        const int e = c0 + tid;
+        int v = -1;
+        bool is = false;
+        if (e < total) {
+          v = nl[e];
+          if (v >= 0) {
+            uint32_t h = ((uint32_t)v * 2654435761u) >> 7;
+            for (;;) {
+              h &= rmask;
+              if (rep[h] == (uint32_t)v) break;
+              h++;
+            }
+            is = repi[h] == e;
+          }
+        }
+        const unsigned bm = __ballot_sync(FULL, is);
+        if (lane == 0) ctl->wsum[warp] = __popc(bm);
+        __syncthreads();
+        int off = base_n, tot = 0;
+        for (int ww = 0; ww < INS_WARPS; ww++) {
+          const int c = ctl->wsum[ww];
+          if (ww < warp) off += c;
+          tot += c;
+        }
+        if (is) cand[off + __popc(bm & ((1u << lane) - 1u))] = v;
+        base_n += tot;
+        __syncthreads();
+      }
+      if (tid == 0) ctl->ncand = base_n;
     }
     __syncthreads();
+    K2_T(6)
     const int nc = ctl->ncand;
     if (nc == 0) return;
     block_distances(cand, nc, w, 1 /*cosine*/, candd);  // CosineDistance(candidate.Value, n.Value)
     if (tid == 0) c_repl += nc;
     __syncthreads();
+    K2_T(7)
     if (warp == 0) {
       // graph.go:213-218: pop best-first until the list is full.  The first pop of a min-heap filled by pushes is
       // the first-pushed global minimum; that shortcut is exact when one pop suffices and no distance is NaN.
@@ -315,6 +476,7 @@ struct Inserter {
       warp_store_list(wlist(layer, w), M, wl, deg, lane);
     }
     __syncthreads();
+    K2_T(8)
   }
 
   // layerNode.addNeighbor(newNode, m, dist) on node n -- graph.go:41-81.  Block-wide; ends with a barrier.
@@ -332,29 +494,55 @@ struct Inserter {
       }
     }
     __syncthreads();
+    K2_T(0)
     if (!ctl->flag) return;
     const int len = ctl->tmp_len;  // m + 1
     // graph.go:60-71: dist(neighbor.Value, n.Value) for every neighbour
     block_distances(tmp, len, n, metric, tmpd);
     __syncthreads();
-    if (tid == 0) {
-      c_evict += len;
-      float worst_d = __int_as_float(0xff800000);  // -Inf
-      int worst = -1, wpos = -1;
-      for (int i = 0; i < len; i++) {  // ascending key order stands in for Go's map order
+    K2_T(1)
+    if (warp == 0) {
+      // graph.go:60-71 over the entries in key order (the stand-in for Go's map order): `d > worst || worst == nil`
+      // keeps the FIRST maximum; a NaN never wins unless it is the first entry, and then nothing replaces it.
+      const float d0 = tmpd[0];
+      float bd = __int_as_float(0xff800000);  // -Inf
+      int bi = 0x7fffffff;
+      for (int i = lane; i < len; i += 32) {
         float d = tmpd[i];
-        if (d > worst_d || worst < 0) {
-          worst_d = d;
-          worst = tmp[i];
-          wpos = i;
+        if (d != d) d = __int_as_float(0xff800000);
+        if (d > bd || (d == bd && i < bi)) {
+          bd = d;
+          bi = i;
         }
       }
-      for (int i = wpos; i + 1 < len; i++) tmp[i] = tmp[i + 1];  // delete(n.neighbors, worst.Key)
-      ctl->worst = worst;
-      ctl->tmp_len = len - 1;
-      c_evictions++;
+#pragma unroll
+      for (int off = 16; off >= 1; off >>= 1) {
+        const float od = __shfl_xor_sync(FULL, bd, off);
+        const int oi = __shfl_xor_sync(FULL, bi, off);
+        if (od > bd || (od == bd && oi < bi)) {
+          bd = od;
+          bi = oi;
+        }
+      }
+      const int wpos = (d0 != d0) ? 0 : bi;
+      const int worst = tmp[wpos];
+      __syncwarp();
+      int moved[3];
+      int cm = 0;
+      for (int i = wpos + lane; i + 1 < len; i += 32) moved[cm++] = tmp[i + 1];  // delete(n.neighbors, worst.Key)
+      __syncwarp();
+      cm = 0;
+      for (int i = wpos + lane; i + 1 < len; i += 32) tmp[i] = moved[cm++];
+      if (lane == 0) {
+        c_evict += len;
+        if (worst == x) ctl->own_dirty = 1;  // x is being linked by the caller's loop: its shared-memory list is stale now
+        ctl->worst = worst;
+        ctl->tmp_len = len - 1;
+        c_evictions++;
+      }
     }
     __syncthreads();
+    K2_T(2)
     const int worst = ctl->worst;
     if (warp == 0) warp_store_list(wlist(layer, n), M, tmp, ctl->tmp_len, lane);
     if (warp == 1) {  // graph.go:75-78: delete the back-link
@@ -363,7 +551,67 @@ struct Inserter {
       if (nd != dw) warp_store_list(wlist(layer, worst), M, wl, nd, lane);
     }
     __syncthreads();
+    K2_T(3)
     replenish(layer, worst);  // graph.go:79
+  }
+
+  // The new node's side of graph.go:516-520 (newNode.addNeighbor(node)): its list on this layer starts empty and, as long
+  // as the node is not itself evicted from a neighbour (own_dirty), only this loop writes it and it cannot overflow (the
+  // neighbourhood has at most m members): it is kept in shared memory, sorted by key, and stored after every insertion --
+  // replenish may read it in between through another node's list.
+  __device__ void own_begin(const int *nbrs, int cnt) {
+    __syncthreads();
+    for (int i = tid; i < cnt; i += INS_THREADS) nbk[i] = g.keys[nbrs[i]];
+    if (tid == 0) {
+      ctl->own_len = 0;
+      ctl->own_dirty = 0;
+    }
+  }
+  __device__ void add_own(int layer, int row, int x, long long kx) {
+    if (warp != 0) return;
+    const int M = g.M;
+    const int len = ctl->own_len;
+    int pos = 0, eqpos = -1;
+    bool present = false;
+    for (int base = 0; base < len; base += 32) {
+      const int i = base + lane;
+      bool lt = false, eq = false;
+      if (i < len) {
+        present = present || own[i] == x;
+        lt = ownk[i] < kx;
+        eq = ownk[i] == kx && own[i] != x;  // another row under the same key (listops.cuh: warp_sorted_insert)
+      }
+      pos += __popc(__ballot_sync(FULL, lt));
+      const unsigned em = __ballot_sync(FULL, eq);
+      if (em && eqpos < 0) eqpos = base + __ffs(em) - 1;
+    }
+    if (__any_sync(FULL, present)) return;
+    int nlen = len;
+    if (eqpos >= 0) {
+      if (lane == 0) own[eqpos] = x;
+    } else {
+      int mv[3];
+      long long mk[3];
+      int cm = 0;
+      for (int i = pos + lane; i < len; i += 32) {
+        mv[cm] = own[i];
+        mk[cm++] = ownk[i];
+      }
+      __syncwarp();
+      cm = 0;
+      for (int i = pos + lane; i < len; i += 32) {
+        own[i + 1] = mv[cm];
+        ownk[i + 1] = mk[cm++];
+      }
+      if (lane == 0) {
+        own[pos] = x;
+        ownk[pos] = kx;
+        ctl->own_len = len + 1;
+      }
+      nlen = len + 1;
+    }
+    __syncwarp();
+    warp_store_list(wlist(layer, row), M, own, nlen, lane);
   }
 
   // layerNode.isolate(m) -- graph.go:223-235: every neighbour drops its link to n and is replenished at once, in
@@ -393,7 +641,7 @@ struct Inserter {
 static __host__ __device__ inline size_t al16(size_t v) { return (v + 15) & ~(size_t)15; }
 
 struct InsLayout {
-  size_t ctl, heapC, heapR, vis, nbh, tmp, tmpd, wl, cand, candd, rep, total;
+  size_t ctl, heapC, heapR, vis, nbh, tmp, tmpd, wl, cand, candd, rep, repi, own, ownk, nbk, total;
   __host__ __device__ InsLayout(const InsertParams &p, int M) {
     size_t o = 0;
     ctl = o;   o += al16(sizeof(InsCtl));
@@ -407,6 +655,10 @@ struct InsLayout {
     cand = o;  o += al16(sizeof(int) * p.cand_cap);
     candd = o; o += al16(sizeof(float) * p.cand_cap);
     rep = o;   o += al16(sizeof(uint32_t) * p.rep_cap);
+    repi = o;  o += al16(sizeof(int) * p.rep_cap);
+    own = o;   o += al16(sizeof(int) * (M + 1));
+    ownk = o;  o += al16(sizeof(long long) * (M + 1));
+    nbk = o;   o += al16(sizeof(long long) * M);
     total = o;
   }
 };

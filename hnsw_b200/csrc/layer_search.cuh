@@ -56,13 +56,10 @@ struct SearchCounters {
 // C (capacity ef+1) and R (capacity k) are shared-memory heaps owned by this warp.  ONLY LANE 0 touches them
 // (the other lanes' C.len / R.len are meaningless); the popped node travels to the other lanes by shuffle, and
 // the caller must __syncwarp() before other lanes read R's array (this function ends with one).
-// CG (the speculative Add, spec_insert.cu): neighbour lists are read past L1 and the id of every list read (the row on
-// layer 0, 0x80000000 | upper slot above) is appended to rlog[*rlog_n++] by lane 0.
-template <int CPL, int U, bool CG = false>
+template <int CPL, int U>
 __device__ __forceinline__ int layer_search_ref(const GraphView &g, int layer, int entry, int k, int ef, int metric,
                                                 const QueryRegs<CPL> &Q, GoHeap &C, GoHeap &R, Visited &V,
-                                                SearchCounters &ctr, int lane, uint32_t *rlog = nullptr,
-                                                int *rlog_n = nullptr, int rlog_cap = 0) {
+                                                SearchCounters &ctr, int lane) {
   C.len = 0;
   R.len = 0;
   V.clear(lane);
@@ -88,25 +85,17 @@ __device__ __forceinline__ int layer_search_ref(const GraphView &g, int layer, i
     if (cur < 0) break;
     bool improved = false;  // lane 0 only
     const int32_t *list;
-    uint32_t lid = (uint32_t)cur;
     if (layer == 0) {
       list = g.adj0 + (size_t)cur * M;
     } else {
       int off = g.upper_off[cur];
       list = g.adjU + ((size_t)off + (layer - 1)) * M;
-      lid = 0x80000000u | (uint32_t)(off + (layer - 1));
-    }
-    if constexpr (CG) {
-      if (lane == 0) {
-        const int kk = (*rlog_n)++;
-        if (kk < rlog_cap) rlog[kk] = lid;
-      }
     }
     ctr.expansions++;
     // graph.go:137-144: neighbours in ascending key order (stored that way), skipping visited ones.
     for (int base = 0; base < M; base += 32) {
       int nb = -1;
-      if (base + lane < M) nb = CG ? __ldcg(list + base + lane) : list[base + lane];
+      if (base + lane < M) nb = list[base + lane];
       bool valid = nb >= 0;
       unsigned vmask = __ballot_sync(FULL, valid);
       if (vmask == 0) break;

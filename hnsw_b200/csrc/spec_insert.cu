@@ -42,12 +42,15 @@ struct SpecShared {
   int n_layers;
   int entries[B200HNSW_MAX_LAYERS];
   unsigned long long n_accepted, n_redone;
+  unsigned long long n_repaired;  // speculations a worker ran again itself while its node waited for its turn
+  unsigned long long cyc[4];      // committer cycles: waiting for the next node, checking it, running it again, committing
 };
 
 static_assert(B200HNSW_MAX_LAYERS <= 64, "ent_mask holds one bit per layer");
 
 struct SpecSlot {
-  int ready;     // node index + 1 once the speculation is complete
+  int ready;     // node index + 1: speculation complete; -(index + 1): the committer has taken it; 0: its worker is
+                 // running it again
   int status;    // 0, or the error the insertion would raise (1, 2), or 8
   int e0;        // nodes committed when the speculation started
   int sver0;     // layer-state version it used
@@ -81,8 +84,8 @@ __device__ __forceinline__ void spec_give_up(SpecShared *S) {
 // The whole insertion of node j (graph.go:445-528) against the graph as it is now, into slot `si`: overlay + read log +
 // header.  Block-wide; ends with a barrier.  Same steps as insert_kernel's loop body.
 template <int CPL, int U>
-__device__ void spec_node(Inserter<CPL, U, true> &I, const GraphView &gv, const InsertParams &p, const SpecParams &sp,
-                          int j, int si, int e0) {
+__device__ void spec_node(Inserter<CPL, U, true> &I, const InsertParams &p, const SpecParams &sp, int j, int si,
+                          int e0, int ready_val) {
   SpecShared *S = sp.S;
   InsCtl *ctl = I.ctl;
   const int tid = I.tid, lane = I.lane, warp = I.warp;
@@ -110,7 +113,7 @@ __device__ void spec_node(Inserter<CPL, U, true> &I, const GraphView &gv, const 
   const int L = p.levels[j];
   const int old_layers = ctl->n_layers;
   const int top = (old_layers > L + 1 ? old_layers : L + 1) - 1;  // graph.go:462-464
-  if (warp == 0) {
+  {
     QueryRegs<CPL> Q;
     load_query<CPL>(Q, reinterpret_cast<const float *>(I.g.vec + (size_t)row * I.g.row_chunks), I.g.dim,
                     I.g.row_chunks, lane);
@@ -122,9 +125,8 @@ __device__ void spec_node(Inserter<CPL, U, true> &I, const GraphView &gv, const 
         if (elevator >= 0 && p.dead && p.dead[elevator]) {
           cnt = 0;  // layer.nodes[*elevator] == nil (graph.go:101-103)
         } else {
-          cnt = layer_search_ref<CPL, U, true>(gv, l, spn, p.m, p.ef, p.metric, Q, I.C, I.R, I.V, sc, lane, I.rlog,
-                                               &ctl->n_rd, I.rl_cap);  // graph.go:500
-          for (int i = lane; i < cnt; i += 32) I.nbh[l * M + i] = I.R.id(i);
+          cnt = I.block_layer_search(l, spn, Q, sc);  // graph.go:500; the lists it reads are logged
+          for (int i = tid; i < cnt; i += INS_THREADS) I.nbh[l * M + i] = I.R.id(i);
           if (cnt > 0) elevator = I.R.id(0);          // graph.go:508
         }
         if (cnt <= 0) {
@@ -132,10 +134,9 @@ __device__ void spec_node(Inserter<CPL, U, true> &I, const GraphView &gv, const 
           break;
         }
       }
-      if (lane == 0) ctl->cnts[l] = cnt;
-      __syncwarp();
+      if (tid == 0) ctl->cnts[l] = cnt;
     }
-    if (lane == 0) ctl->flag = bad;
+    if (tid == 0) ctl->flag = bad;
   }
   __syncthreads();
   int status = ctl->flag;
@@ -147,10 +148,12 @@ __device__ void spec_node(Inserter<CPL, U, true> &I, const GraphView &gv, const 
         continue;
       }
       if (L >= l) {  // graph.go:510-521
+        I.own_begin(I.nbh + l * M, cnt);
         for (int t = 0; t < cnt; t++) {
           const int nb = I.nbh[l * M + t];
           I.add_neighbor(l, nb, row, p.metric);
-          I.add_neighbor(l, row, nb, p.metric);
+          if (ctl->own_dirty) I.add_neighbor(l, row, nb, p.metric);  // the general path (inserter.cuh: own_dirty)
+          else I.add_own(l, row, nb, I.nbk[t]);
         }
       }
     }
@@ -175,7 +178,7 @@ __device__ void spec_node(Inserter<CPL, U, true> &I, const GraphView &gv, const 
     sl->ctr[4] = I.c_repl;
     sl->ctr[5] = I.c_evictions;
     __threadfence();
-    stv(&sl->ready, j + 1);
+    stv(&sl->ready, ready_val);
   }
   __syncthreads();
 }
@@ -195,6 +198,10 @@ __global__ void __launch_bounds__(INS_THREADS) spec_insert_kernel(MutGraph g, In
   I.cand = reinterpret_cast<int *>(smem + lay.cand);
   I.candd = reinterpret_cast<float *>(smem + lay.candd);
   I.rep = reinterpret_cast<uint32_t *>(smem + lay.rep);
+  I.repi = reinterpret_cast<int *>(smem + lay.repi);
+  I.own = reinterpret_cast<int *>(smem + lay.own);
+  I.ownk = reinterpret_cast<long long *>(smem + lay.ownk);
+  I.nbk = reinterpret_cast<long long *>(smem + lay.nbk);
   I.C = GoHeap{reinterpret_cast<uint2 *>(smem + lay.heapC), 0};
   I.R = GoHeap{reinterpret_cast<uint2 *>(smem + lay.heapR), 0};
   I.V = Visited{reinterpret_cast<uint32_t *>(smem + lay.vis), (uint32_t)p.vis_cap - 1, 0};
@@ -205,14 +212,6 @@ __global__ void __launch_bounds__(INS_THREADS) spec_insert_kernel(MutGraph g, In
   I.warp = threadIdx.x >> 5;
   const int tid = I.tid, lane = I.lane, warp = I.warp;
   SpecShared *S = sp.S;
-  GraphView gv;
-  gv.vec = g.vec;
-  gv.adj0 = g.adj0;
-  gv.adjU = g.adjU;
-  gv.upper_off = g.upper_off;
-  gv.row_chunks = g.row_chunks;
-  gv.M = g.M;
-  gv.dim = g.dim;
   __shared__ int sh_j, sh_e0, sh_ok, sh_nrd;
 
   if (blockIdx.x != 0) {
@@ -248,13 +247,55 @@ __global__ void __launch_bounds__(INS_THREADS) spec_insert_kernel(MutGraph g, In
       __syncthreads();
       const int j = sh_j, e0 = sh_e0;
       if (j >= p.n) break;
-      spec_node<CPL, U>(I, gv, p, sp, j, j % sp.depth, e0);  // ends with a barrier: sh_j may be rewritten
+      const int si = j % sp.depth;
+      SpecSlot *sl = sp.slots + si;
+      int my_e0 = e0;
+      spec_node<CPL, U>(I, p, sp, j, si, my_e0, j + 1);  // ends with a barrier: the sh_ words may be rewritten
+      // This worker's next ticket is a window away, so until node j is taken it has nothing better to do than to keep the
+      // speculation current: if a commit has meanwhile written a list it read, run it again now, off the committer's
+      // path.  (The committer's own test stays the one that counts.)
+      for (;;) {
+        if (tid == 0) sh_ok = !ldv(&S->abort_) && ldv(&S->done) <= j && ldv(&sl->ready) == j + 1;
+        __syncthreads();
+        const int waiting = sh_ok;
+        __syncthreads();
+        if (!waiting) break;
+        const int nrd = I.ctl->n_rd < I.rl_cap ? I.ctl->n_rd : I.rl_cap;
+        int stale = 0;
+        for (int r = tid; r < nrd; r += INS_THREADS) {
+          const uint32_t id = __ldcg(I.rlog + r);
+          const int lw = __ldcg((id & 0x80000000u) ? sp.lastwU + (id & 0x7fffffffu) : sp.lastw0 + id);
+          stale |= lw > my_e0;
+        }
+        stale = __syncthreads_or(stale);
+        if (!stale) {
+          __nanosleep(2000);
+          continue;
+        }
+        if (tid == 0) {
+          const int mine = atomicCAS(&sl->ready, j + 1, 0) == j + 1;  // the committer may have taken it just now
+          sh_ok = mine;
+          if (mine) {
+            sh_e0 = ldv(&S->done);
+            __threadfence();
+          }
+        }
+        __syncthreads();
+        const int mine = sh_ok;
+        my_e0 = sh_e0;
+        __syncthreads();
+        if (!mine) break;
+        spec_node<CPL, U>(I, p, sp, j, si, my_e0, j + 1);
+        if (tid == 0) atomicAdd(&S->n_repaired, 1ull);
+      }
     }
     return;
   }
 
   // ---- committer: input order -------------------------------------------------------------------------------------
   unsigned long long acc[6] = {0, 0, 0, 0, 0, 0}, n_acc = 0, n_redo = 0;
+  long long cyc[4] = {0, 0, 0, 0}, tl = clock64();
+#define SPEC_T(i) { const long long t__ = clock64(); cyc[i] += t__ - tl; tl = t__; }
   for (int j = 0; j < p.n; j++) {
     const int si = j % sp.depth;
     SpecSlot *sl = sp.slots + si;
@@ -262,7 +303,7 @@ __global__ void __launch_bounds__(INS_THREADS) spec_insert_kernel(MutGraph g, In
       int ok = -1;
       const long long t0 = clock64();
       for (;;) {
-        if (ldv(&sl->ready) == j + 1) {
+        if (ldv(&sl->ready) == j + 1 && atomicCAS(&sl->ready, j + 1, -(j + 1)) == j + 1) {  // taken: its worker lets go
           __threadfence();
           ok = ldv(&sl->status) == 0 && ldv(&sl->sver0) == ldv(&S->sver);
           break;
@@ -279,6 +320,7 @@ __global__ void __launch_bounds__(INS_THREADS) spec_insert_kernel(MutGraph g, In
       sh_nrd = ok > 0 ? ldv(&sl->n_rd) : 0;
     }
     __syncthreads();
+    SPEC_T(0)
     if (sh_ok < 0) break;
     int redo = !sh_ok;
     if (!redo) {
@@ -294,8 +336,9 @@ __global__ void __launch_bounds__(INS_THREADS) spec_insert_kernel(MutGraph g, In
       redo = __syncthreads_or(stale);
     }
     __syncthreads();
+    SPEC_T(1)
     if (redo) {
-      spec_node<CPL, U>(I, gv, p, sp, j, si, j);  // head of the order: nothing it reads can be stale
+      spec_node<CPL, U>(I, p, sp, j, si, j, -(j + 1));  // head of the order: nothing it reads can be stale
       n_redo++;
       const int status = ldv(&sl->status);
       if (status != 0) {  // the insertion itself fails (graph.go:501-505, visited overflow) or does not fit the overlay
@@ -310,6 +353,7 @@ __global__ void __launch_bounds__(INS_THREADS) spec_insert_kernel(MutGraph g, In
     } else {
       n_acc++;
     }
+    SPEC_T(2)
     // ---- commit: the overlay becomes the graph ----------------------------------------------------------------------
     const int nov = ldv(&sl->n_ov);
     const int32_t *ovl = sp.ovls + (size_t)si * (OV_MAX + 1) * g.M;
@@ -339,6 +383,7 @@ __global__ void __launch_bounds__(INS_THREADS) spec_insert_kernel(MutGraph g, In
     __threadfence();
     __syncthreads();
     if (tid == 0) stv(&S->done, j + 1);
+    SPEC_T(3)
   }
   if (tid == 0) {
     atomicAdd(&p.counters[0], acc[0]);
@@ -349,6 +394,7 @@ __global__ void __launch_bounds__(INS_THREADS) spec_insert_kernel(MutGraph g, In
     atomicAdd(&p.counters[5], acc[5]);
     S->n_accepted = n_acc;
     S->n_redone = n_redo;
+    for (int i = 0; i < 4; i++) S->cyc[i] = (unsigned long long)cyc[i];
   }
 }
 
@@ -437,8 +483,11 @@ int launch_spec_insert(b200hnsw *h, InsertParams &p, int depth, int *done, int *
   static const bool trace = getenv("B200HNSW_TRACE_ADD") != nullptr;
   if (trace)
     fprintf(stderr, "[b200hnsw] windowed add: first_row %lld n %d window %d -> done %d err %d (node %d) layers %d -> %d "
-            "accepted %llu run again %llu\n", p.first_row, p.n, depth, S1.done, S1.err, S1.err_node, p.n_layers,
-            S1.n_layers, S1.n_accepted, S1.n_redone);
+            "accepted %llu run again %llu (repaired by workers %llu)\n", p.first_row, p.n, depth, S1.done, S1.err,
+            S1.err_node, p.n_layers, S1.n_layers, S1.n_accepted, S1.n_redone, S1.n_repaired);
+  if (trace)
+    fprintf(stderr, "[b200hnsw]   committer cycles per node: wait %.0f check %.0f run-again %.0f commit %.0f\n",
+            (double)S1.cyc[0] / p.n, (double)S1.cyc[1] / p.n, (double)S1.cyc[2] / p.n, (double)S1.cyc[3] / p.n);
   *done = S1.done;
   *err = S1.err;
   *n_layers = S1.n_layers;
@@ -446,6 +495,7 @@ int launch_spec_insert(b200hnsw *h, InsertParams &p, int depth, int *done, int *
   if (accepted_redone) {
     accepted_redone[0] += S1.n_accepted;
     accepted_redone[1] += S1.n_redone;
+    accepted_redone[2] += S1.n_repaired;
   }
   return 0;
 }

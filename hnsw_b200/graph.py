@@ -485,12 +485,15 @@ class Graph:
             _lib.check(_lib.lib().b200hnsw_set_add_window(self._h, self._add_window))
 
     def add_window_stats(self):
-        """(speculations accepted, insertions run again by the committer) since the handle was created."""
+        """(speculations accepted, insertions run again by the committer, speculations run again by their workers) since
+        the handle was created."""
         if self._h is None:
-            return 0, 0
-        a, r = np.zeros(1, np.int64), np.zeros(1, np.int64)
-        _lib.check(_lib.lib().b200hnsw_get_add_window_stats(self._h, a.ctypes.data_as(_lib.i64p), r.ctypes.data_as(_lib.i64p)))
-        return int(a[0]), int(r[0])
+            return 0, 0, 0
+        a = np.zeros(3, np.int64)
+        p = a.ctypes.data_as(_lib.i64p)
+        _lib.check(_lib.lib().b200hnsw_get_add_window_stats(
+            self._h, p, C.cast(C.addressof(p.contents) + 8, _lib.i64p), C.cast(C.addressof(p.contents) + 16, _lib.i64p)))
+        return int(a[0]), int(a[1]), int(a[2])
 
     @_writes
     def Add(self, *nodes: Node, levels: Optional[Sequence[int]] = None):

@@ -218,10 +218,12 @@ int32_t b200hnsw_get_build_mode(const b200hnsw_t *h);
  * one-node-at-a-time kernel builds, bit for bit (tests/test_add_parity_gpu.py runs both against the oracle).
  * window = 0: chosen from the number of rows (1 below ~12 000 rows, then ~sqrt(rows / 3000), at most 48);
  * window = 1: one CTA, one node at a time; 2..128: that many insertions in flight.
- * b200hnsw_get_add_window_stats: speculations accepted / insertions the committer ran again, summed over the handle's
- * life. */
+ * While a node waits for its turn its worker keeps the speculation current (runs it again if a commit wrote a list it
+ * read), so the committer rarely has to.
+ * b200hnsw_get_add_window_stats: speculations accepted / insertions the committer ran again / speculations their workers
+ * ran again, summed over the handle's life. */
 int b200hnsw_set_add_window(b200hnsw_t *h, int32_t window);
-int b200hnsw_get_add_window_stats(const b200hnsw_t *h, int64_t *accepted, int64_t *redone);
+int b200hnsw_get_add_window_stats(const b200hnsw_t *h, int64_t *accepted, int64_t *redone, int64_t *repaired);
 
 /* Graph.Delete / Graph.BatchDelete (graph.go:843-895; layerNode.isolate graph.go:223-235, replenish graph.go:172-219).
  * rows[i] = the row the caller's key map holds for the i-th key, -1 for an unknown key; processed in call order, as

@@ -24,13 +24,13 @@ print(f"base graph {rows} x {dim} (waves): {time.time() - t0:.1f} s", flush=True
 at = rows
 for w in windows:
     g.set_add_window(w)
-    a0, r0 = g.add_window_stats()
+    a0, r0, w0 = g.add_window_stats()
     t0 = time.time()
     g.add_arrays(np.arange(at, at + batch, dtype=np.int64), X[at:at + batch], levels[at:at + batch], wave_max=0)
     wall = time.time() - t0
-    a1, r1 = g.add_window_stats()
+    a1, r1, w1 = g.add_window_stats()
     st = g.last_stats
     print(f"rows {at:8d} window {w:3d}: {batch / wall:9.0f} vec/s wall, kernel {st['kernel_ms']:8.1f} ms "
-          f"({batch / st['kernel_ms'] * 1e3:9.0f} vec/s), accepted {a1 - a0} run again {r1 - r0}, launches {st['launches']}",
+          f"({batch / st['kernel_ms'] * 1e3:9.0f} vec/s), accepted {a1 - a0} run again {r1 - r0} repaired {w1 - w0}, launches {st['launches']}",
           flush=True)
     at += batch
