@@ -70,6 +70,8 @@ def parse_args():
     ap.add_argument("--pool", type=int, default=16, help="distinct query batches cycled through the steps")
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="target length of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip every oracle leg (parity included)")
+    ap.add_argument("--no-ref-order", action="store_true",
+                    help="skip build.reference_order_at_full_size (Graph.Add in the reference's order on the full graph)")
     ap.add_argument("--no-exact", action="store_true", help="(kept for old command lines) drop the exact side")
     ap.add_argument("--side-steps", type=int, default=10)
     ap.add_argument("--inflight", type=int, default=3,
@@ -325,6 +327,77 @@ def query_pool(ctx, args, wl, seed, nb=None):
     nb = nb or max(1, min(args.warmup + args.steps, args.pool))
     q = gen(wl["dist"], nb * wl["batch"], wl["dim"], seed).reshape(nb, wl["batch"], wl["dim"])
     return ctx.torch.from_numpy(q).pin_memory()
+
+
+def reference_order_block(args, wl, g, ov, n_parity=500, n_dev=8000, n_one=1000, n_cpu=500):
+    """Graph.Add in the REFERENCE'S ORDER (b200hnsw_add_batch: graph.go:437-531, the graph the reference builds, bit for
+    bit) at the workload's full size: new rows are added to the graph the bench searched.  Device: the speculative
+    windowed schedule (K2s, automatic window) and the one-node-at-a-time kernel (K2).  CPU: the port's serial Graph.Add on
+    the oracle's copy of the same graph -- first the SAME rows under the canonical order (parity: every list of the layers
+    the new rows joined, bit-equal), then further rows under the AVX2-shaped order (the timed baseline).  Runs last: it
+    changes both graphs."""
+    N, dim, ef = g.Len(), wl["dim"], wl["ef"]
+    total = n_parity + n_dev + n_one + n_cpu
+    Xn = gen(wl["dist"], total, dim, 4747)
+    lv = draw_levels(total, args.ml, 4748)
+    keys = np.arange(N, N + total, dtype=np.int64)
+    out = {"rows_before": N, "semantics": "reference order (graph.go:437-531): the graph the reference builds, bit for bit",
+           "schedule": "K2s: a window of pending insertions speculated in parallel (one CTA each, reads logged, writes in "
+                       "a private overlay), committed in input order, run again when a read went stale"}
+    g.set_add_window(0)
+    at = 0
+    if ov is not None:
+        ora = ov.oracle
+        ov.g.set_flavor(ora.CANONICAL)
+        ov.g.reset_counters()
+        t0 = time.perf_counter()
+        ov.g.add_many(keys[:n_parity], Xn[:n_parity], lv[:n_parity], ef)
+        cpu_canon = n_parity / (time.perf_counter() - t0)
+        g.add_arrays(keys[:n_parity], Xn[:n_parity], lv[:n_parity], wave_max=0)
+        st = g.last_stats
+        c = ov.g.counters()
+        lists_equal, checked = True, 0
+        for l in range(int(lv[:n_parity].max()) + 1):
+            rows, ptr, nbr = ov.g.dump_layer(l)
+            dn, member = g.neighbors(l)
+            want = np.full((len(rows), dn.shape[1]), -1, np.int32)
+            deg = np.diff(ptr)
+            idx = np.repeat(np.arange(len(rows)), deg)
+            pos = np.arange(len(nbr)) - np.repeat(ptr[:-1], deg)
+            want[idx, pos] = nbr
+            lists_equal &= bool(np.array_equal(np.nonzero(member)[0], rows)) and bool(np.array_equal(dn[rows], want))
+            checked += len(rows)
+        out["parity"] = {"added": n_parity, "lists_checked": checked, "lists_equal": lists_equal,
+                         "counters_equal": all(int(st[k]) == int(c[k]) for k in
+                                               ("dist_evals", "expansions", "evict_evals", "replenish_evals", "evictions")),
+                         "against": "oracle (CPU restatement of graph.go:437-531), canonical order, same rows into its "
+                                    "copy of the same graph; every list of every layer the new rows joined"}
+        at = n_parity
+    a0 = g.add_window_stats()
+    g.add_arrays(keys[at:at + n_dev], Xn[at:at + n_dev], lv[at:at + n_dev], wave_max=0)
+    st, a1 = g.last_stats, g.add_window_stats()
+    out.update({"added": n_dev, "vec_per_s": n_dev / (st["kernel_ms"] / 1e3), "kernel_ms": st["kernel_ms"],
+                "launches": st["launches"], "window": "automatic (32 at this size)",
+                "speculations_accepted": a1[0] - a0[0], "run_again_by_committer": a1[1] - a0[1],
+                "repaired_by_workers": a1[2] - a0[2]})
+    at += n_dev
+    g.set_add_window(1)
+    g.add_arrays(keys[at:at + n_one], Xn[at:at + n_one], lv[at:at + n_one], wave_max=0)
+    out["one_node_at_a_time_vec_per_s"] = n_one / (g.last_stats["kernel_ms"] / 1e3)
+    out["one_node_at_a_time_sample"] = f"{n_one} more rows through the single-CTA kernel (K2, window 1)"
+    g.set_add_window(0)
+    at += n_one
+    if ov is not None:
+        ov.g.set_flavor(ov.oracle.SIMD)
+        t0 = time.perf_counter()
+        ov.g.add_many(keys[at:at + n_cpu], Xn[at:at + n_cpu], lv[at:at + n_cpu], ef)
+        cpu = n_cpu / (time.perf_counter() - t0)
+        ov.g.set_flavor(ov.oracle.CANONICAL)
+        out["cpu_port"] = {"vec_per_s": cpu, "canonical_order_vec_per_s": cpu_canon, "cores": 1, "kind": "port",
+                           "sample": f"{n_cpu} further rows into the oracle's copy of the same graph ({N + n_parity} rows), "
+                                     f"AVX2-shaped distance, one thread (Graph.Add is serial under the write lock)"}
+        out["vs_cpu_port"] = out["vec_per_s"] / cpu
+    return out
 
 
 def oracle_view(ctx, args, g, wl):
@@ -663,6 +736,8 @@ def run_ours(args, rank, local_rank, world):
                     "path": "hybrid.ExactIndex.Search (K3, exact: recall@10 = 1.0 by construction, results bit-identical "
                             "to the oracle)", "value": ex["value"], "unit": ex["unit"], "e2e": ex["e2e"]["value"],
                     "recall_at_10": 1.0}
+        if world == 1 and rank == 0 and not args.no_ref_order and wl["n_local"] >= 10_000:
+            line["build"]["reference_order_at_full_size"] = reference_order_block(args, wl, g, ov)
         g.close()
         del g, X, ov
 

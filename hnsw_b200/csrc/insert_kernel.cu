@@ -110,10 +110,10 @@ __global__ void __launch_bounds__(INS_THREADS) insert_kernel(MutGraph g, InsertP
         continue;
       }
       if (L >= l) {  // graph.go:510-521
-        I.own_begin(I.nbh + l * g.M, cnt);
+        I.own_begin(l, I.nbh + l * g.M, cnt);
         for (int t = 0; t < cnt; t++) {
           const int nb = I.nbh[l * g.M + t];
-          I.add_neighbor(l, nb, row, p.metric);
+          I.add_neighbor(l, nb, row, p.metric, t + 1 < cnt ? I.nbh[l * g.M + t + 1] : -1);
           if (ctl->own_dirty) I.add_neighbor(l, row, nb, p.metric);  // the general path (inserter.cuh: own_dirty)
           else I.add_own(l, row, nb, I.nbk[t]);
         }
@@ -357,6 +357,7 @@ extern "C" int b200hnsw_add_batch(b200hnsw_t *h, const float *vectors, const int
     p.counters = d_ctr;
     p.error = d_err;
     p.dead = h->n_dead ? h->d.dead : nullptr;
+    p.row_flags = h->d_row_flags;
     int rc2 = launch_insert(h, p, s);
     if (rc2) return rc2;
     launches++;
@@ -382,8 +383,9 @@ extern "C" int b200hnsw_add_batch(b200hnsw_t *h, const float *vectors, const int
                        : "no nodes found in neighborhood search (node %lld of the batch)", (long long)bad);
     return fail(err == 1 ? B200HNSW_ERR_VISITED_OVERFLOW : B200HNSW_ERR_STATE);
   };
-  for (int64_t off = 0; off < n; off += CH) {
-    int64_t cnt = std::min(CH, n - off);
+  for (int64_t off = 0, cnt = 0; off < n; off += cnt) {
+    // launches grow with the graph while it is small, so that the window is chosen anew as the rows double
+    cnt = std::min(std::min(CH, n - off), std::max<int64_t>(2048, h->n + off));
     if ((e = cudaMemcpyAsync(d_levels, levels + off, sizeof(int32_t) * (size_t)cnt, cudaMemcpyHostToDevice, s)) !=
             cudaSuccess ||
         (e = cudaMemsetAsync(d_err, 0, sizeof(int), s)) != cudaSuccess)
@@ -406,6 +408,7 @@ extern "C" int b200hnsw_add_batch(b200hnsw_t *h, const float *vectors, const int
         memcpy(p.entries, entries, sizeof entries);
         p.counters = d_ctr;
         p.dead = h->n_dead ? h->d.dead : nullptr;
+        p.row_flags = h->d_row_flags;
         int done = 0;
         rc = launch_spec_insert(h, p, window, &done, &err, &n_layers, entries, h->spec_accepted_redone, s);
         if (rc < 0) return fail(rc);

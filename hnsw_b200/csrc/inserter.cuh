@@ -29,6 +29,7 @@ struct InsertParams {
   int heap_c, heap_r, vis_cap;    // search scratch (uint2 slots, uint2 slots, u32 entries)
   int cand_cap, rep_cap;          // replenish candidates (<= M*M) and its visited table (power of two)
   const uint8_t *dead;            // [rows] deleted flags, null while nothing was deleted
+  const int *row_flags;           // device word: bit 0 = some stored row can yield NaN distances (index.hpp)
   // Delete (delete_kernel): rows to isolate, in call order
   const int32_t *del_rows;
   const int32_t *del_levels;
@@ -219,6 +220,13 @@ struct Inserter {
     __syncthreads();
     block_distances_q(fresh, 1, Q, metric, freshd);  // graph.go:107-108
     __syncthreads();
+    // Once the result queue is full it stays full, and from then on the candidate queue is never looked at again: the
+    // loop goes on only when a row improved on result.Min(), that row is strictly below everything evaluated on the
+    // layer, so candidates.Push sifted it to the root and the next Pop returns exactly the last improving row (the
+    // argument of traverse.cuh, K1).  NaN distances break it (Go's up() never moves an element past a NaN): graphs that
+    // hold rows able to produce them keep the queue for the whole layer.
+    const bool keepc = p.row_flags != nullptr && (__ldcg(p.row_flags) & 1);
+    bool cfree = false;  // thread 0
     if (tid == 0) {
       // graph.go:109-127: candidates.Push(entry); result.Push(entry); visited[entry]; the first Pop takes it back
       C.len = 0;
@@ -252,6 +260,7 @@ struct Inserter {
             fresh[nf + __popc(fm & ((1u << lane) - 1u))] = nb;
             const float4 *rowp = g.vec + (size_t)nb * g.row_chunks;
             for (int c = 0; c < g.row_chunks; c += 8) prefetch_l2(rowp + c);
+            if (layer == 0) prefetch_l2(g.adj0 + (size_t)nb * M);  // one of these rows is the next to be expanded
           }
           nf += __popc(fm);
           vc += __popc(fm);
@@ -276,23 +285,31 @@ struct Inserter {
       }
       if (tid == 0) {
         bool improved = false;
+        int imp_id = -1;
         for (int i = 0; i < nf; i++) {  // graph.go:146-159, key order
           const float d = freshd[i];
           const int id = fresh[i];
-          improved = improved || (R.len > 0 && d < R.min_dist());  // graph.go:147
+          if (R.len > 0 && d < R.min_dist()) {  // graph.go:147
+            improved = true;
+            imp_id = id;
+          }
           if (R.len < k) {
             R.push(d, id);
           } else if (d < R.max_dist()) {  // result.Max() is the last slot
             R.pop_last();
             R.push(d, id);
           }
-          C.push(d, id);
-          if (C.len > ef) C.pop_last();  // graph.go:157-159
+          if (!cfree) {
+            C.push(d, id);
+            if (C.len > ef) C.pop_last();  // graph.go:157-159
+          }
         }
         sc.evals += nf;
         int next;
-        if (!improved && R.len >= k) next = -1;             // graph.go:164-166
+        if (cfree) next = improved ? imp_id : -1;            // what candidates.Pop() would return (see above)
+        else if (!improved && R.len >= k) next = -1;         // graph.go:164-166
         else next = C.len > 0 ? (int)C.pop().y : -1;         // graph.go:125-127
+        if (R.len >= k && !keepc) cfree = true;
         ctl->cur = next;
         ctl->cnt = R.len;
       }
@@ -479,10 +496,27 @@ struct Inserter {
     K2_T(8)
   }
 
+  __device__ __forceinline__ void prefetch_neighbourhood(int layer, int n) {
+    const int M = g.M;
+    const int32_t *ln = g.list(layer, n);
+    for (int j = lane; j < M; j += 32) {
+      const int e = ldl(ln + j);
+      if (e < 0) continue;
+      const float4 *rowp = g.vec + (size_t)e * g.row_chunks;
+      for (int c = 0; c < g.row_chunks; c += 8) prefetch_l2(rowp + c);
+      prefetch_l2(g.keys + e);
+      if (layer == 0) prefetch_l2(g.adj0 + (size_t)e * M);
+    }
+  }
+
   // layerNode.addNeighbor(newNode, m, dist) on node n -- graph.go:41-81.  Block-wide; ends with a barrier.
-  __device__ void add_neighbor(int layer, int n, int x, int metric) {
+  // next_n: the node the caller's loop will call this for next (-1: none).  A spare warp requests its list, and the rows,
+  // keys and lists of its neighbours, into L2 now: a hint only (never logged, never consulted), it turns the dependent
+  // DRAM round trips of the next call into L2 hits.
+  __device__ void add_neighbor(int layer, int n, int x, int metric, int next_n = -1) {
     const int m = p.m, M = g.M;
     __syncthreads();  // every thread has finished reading the control block of the previous step
+    if (warp == INS_WARPS - 1 && next_n >= 0) prefetch_neighbourhood(layer, next_n);
     if (warp == 0) {
       int deg = warp_load_list<SPEC>(rlist(layer, n), M, tmp, lane);
       int nd = warp_sorted_insert(tmp, deg, x, g.keys, lane);  // graph.go:50
@@ -559,9 +593,10 @@ struct Inserter {
   // as the node is not itself evicted from a neighbour (own_dirty), only this loop writes it and it cannot overflow (the
   // neighbourhood has at most m members): it is kept in shared memory, sorted by key, and stored after every insertion --
   // replenish may read it in between through another node's list.
-  __device__ void own_begin(const int *nbrs, int cnt) {
+  __device__ void own_begin(int layer, const int *nbrs, int cnt) {
     __syncthreads();
     for (int i = tid; i < cnt; i += INS_THREADS) nbk[i] = g.keys[nbrs[i]];
+    if (warp == INS_WARPS - 1 && cnt > 0) prefetch_neighbourhood(layer, nbrs[0]);
     if (tid == 0) {
       ctl->own_len = 0;
       ctl->own_dirty = 0;

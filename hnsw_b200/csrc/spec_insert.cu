@@ -148,10 +148,10 @@ __device__ void spec_node(Inserter<CPL, U, true> &I, const InsertParams &p, cons
         continue;
       }
       if (L >= l) {  // graph.go:510-521
-        I.own_begin(I.nbh + l * M, cnt);
+        I.own_begin(l, I.nbh + l * M, cnt);
         for (int t = 0; t < cnt; t++) {
           const int nb = I.nbh[l * M + t];
-          I.add_neighbor(l, nb, row, p.metric);
+          I.add_neighbor(l, nb, row, p.metric, t + 1 < cnt ? I.nbh[l * M + t + 1] : -1);
           if (ctl->own_dirty) I.add_neighbor(l, row, nb, p.metric);  // the general path (inserter.cuh: own_dirty)
           else I.add_own(l, row, nb, I.nbk[t]);
         }
@@ -410,14 +410,18 @@ static int launch_spec_t(b200hnsw *h, const MutGraph &g, InsertParams &p, const 
   return 0;
 }
 
-// Window depth (= worker CTAs).  Two insertions collide when one reads a list the other writes: ~200 lists read, ~55
-// written per node, so a window of d nodes holds a stale member with probability ~ d * 1e4 / rows, and a stale member
-// costs the committer one insertion's latency: d ~ sqrt(rows / 1e4)-ish is where supply and demand meet (measured:
-// DESIGN.md K2s).  Below two the sequential kernel is the better program.
+// Window depth (= worker CTAs).  Two insertions collide when one reads a list the other writes (~200 lists read, ~55
+// written per node: probability ~1e4 / rows for a given pair).  A node that collides with one of its R*T nearest
+// predecessors (R = commit rate, T = one insertion's latency) has to be run again after that predecessor is in, which
+// stalls the committer: R ~ 1 / (T * sqrt(1e4 / 2 rows)) is the ceiling, ~29 k/s at 1 M rows.  The window only has to be
+// deep enough to keep that many insertions in flight; deeper ones cost nothing but idle workers, because a waiting
+// worker repairs its own speculation.  Measured (profiles/r8o_k2s_*.log, r8n_k2s_1m.log): 5-9 k rows: 4 -> 1.3x the
+// one-node-at-a-time kernel; 20-36 k: 16 -> 2.1x; 100 k: 32 -> 3.0x; 1 M: 32 -> 5.2x (48: the same).
 int spec_window_auto(int64_t rows) {
-  int d = (int)std::sqrt((double)rows / 3000.0);
-  if (d < 2) return 1;
-  return d > 48 ? 48 : d;
+  if (rows < 2000) return 1;
+  if (rows < 10000) return 4;
+  if (rows < 50000) return 16;
+  return 32;
 }
 
 // One launch: nodes [0, p.n) of the batch slice described by p, window `depth`.  On return *done nodes are in the graph

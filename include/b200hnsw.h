@@ -216,7 +216,8 @@ int32_t b200hnsw_get_build_mode(const b200hnsw_t *h);
  * writes kept in a private overlay -- and commits them in input order; a speculation that read a list an earlier commit
  * of the window wrote is run again at the head of the order (hnsw_b200/csrc/spec_insert.cu).  The graph is the one the
  * one-node-at-a-time kernel builds, bit for bit (tests/test_add_parity_gpu.py runs both against the oracle).
- * window = 0: chosen from the number of rows (1 below ~12 000 rows, then ~sqrt(rows / 3000), at most 48);
+ * window = 0: chosen from the number of rows in the graph (1 below 2 000 rows, 4 below 10 000, 16 below 50 000, then 32;
+ * a large batch is cut into launches that grow with the graph so that the choice follows it);
  * window = 1: one CTA, one node at a time; 2..128: that many insertions in flight.
  * While a node waits for its turn its worker keeps the speculation current (runs it again if a commit wrote a list it
  * read), so the committer rarely has to.

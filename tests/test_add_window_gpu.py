@@ -4,7 +4,7 @@ counters equal the oracle's, whatever the window.
 
 The graphs here are SMALL on purpose: with a few hundred rows nearly every speculation reads a list an earlier commit of
 its window wrote, so the reject-and-run-again path is what mostly runs; the 30 000-row case has both kinds.  Windows are
-forced (the automatic choice is one node at a time below ~12 000 rows).
+forced (the automatic choice is one node at a time below 2 000 rows).
 """
 import numpy as np
 import pytest
@@ -106,7 +106,8 @@ def test_window_one_and_automatic_build_the_same_graph(oracle):
     a, ta = _build(oracle, X, keys, levels, M, ef, 1, 1)
     b, tb = _build(oracle, X, keys, levels, M, ef, 1, 0, chunks=(20000,))
     assert a.add_window_stats() == (0, 0, 0)
-    assert sum(b.add_window_stats()[:2]) == 20000          # the second call (20 000 rows in the graph) was windowed
+    # the first 2 048 rows go one at a time, everything after them through windows that grow with the graph
+    assert sum(b.add_window_stats()[:2]) == n - 2048
     assert ta == tb
     assert a.Topography() == b.Topography() and list(a.entries()) == list(b.entries())
     for l in range(len(a.Topography())):
