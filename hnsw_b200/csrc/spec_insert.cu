@@ -183,6 +183,14 @@ __device__ void spec_node(Inserter<CPL, U, true> &I, const InsertParams &p, cons
   __syncthreads();
 }
 
+// the committer's copy, out of line: it runs one node in twenty or so, and a second inlined body of the whole insertion
+// doubles the compile time for nothing
+template <int CPL, int U>
+__device__ __noinline__ void spec_node_again(Inserter<CPL, U, true> &I, const InsertParams &p, const SpecParams &sp, int j,
+                                             int si, int e0, int ready_val) {
+  spec_node<CPL, U>(I, p, sp, j, si, e0, ready_val);
+}
+
 template <int CPL, int U>
 __global__ void __launch_bounds__(INS_THREADS) spec_insert_kernel(MutGraph g, InsertParams p, SpecParams sp) {
   extern __shared__ __align__(16) unsigned char smem[];
@@ -216,41 +224,47 @@ __global__ void __launch_bounds__(INS_THREADS) spec_insert_kernel(MutGraph g, In
 
   if (blockIdx.x != 0) {
     // ---- worker: speculate the nodes the ticket counter hands out --------------------------------------------------
+    int j = 0, my_e0 = 0;
+    bool repair = false;  // block-uniform: run node j again (its speculation went stale while it waited)
     for (;;) {
-      if (tid == 0) {
-        int j = atomicAdd(&S->ticket, 1);
-        int e0 = 0;
-        if (j < p.n) {
-          const long long t0 = clock64();
-          for (;;) {
-            if (ldv(&S->abort_)) {
-              j = p.n;
-              break;
-            }
-            const int d = ldv(&S->done);
-            if (j < d + sp.depth) {  // slot j % depth is free again and the window reaches j
-              e0 = d;
-              break;
-            }
-            __nanosleep(256);
-            if (clock64() - t0 > SPEC_TIMEOUT) {
-              spec_give_up(S);
-              j = p.n;
-              break;
+      if (!repair) {
+        if (tid == 0) {
+          int jt = atomicAdd(&S->ticket, 1);
+          int e0 = 0;
+          if (jt < p.n) {
+            const long long t0 = clock64();
+            for (;;) {
+              if (ldv(&S->abort_)) {
+                jt = p.n;
+                break;
+              }
+              const int d = ldv(&S->done);
+              if (jt < d + sp.depth) {  // slot jt % depth is free again and the window reaches jt
+                e0 = d;
+                break;
+              }
+              __nanosleep(256);
+              if (clock64() - t0 > SPEC_TIMEOUT) {
+                spec_give_up(S);
+                jt = p.n;
+                break;
+              }
             }
           }
+          __threadfence();
+          sh_j = jt;
+          sh_e0 = e0;
         }
-        __threadfence();
-        sh_j = j;
-        sh_e0 = e0;
+        __syncthreads();
+        j = sh_j;
+        my_e0 = sh_e0;
+        if (j >= p.n) break;
       }
-      __syncthreads();
-      const int j = sh_j, e0 = sh_e0;
-      if (j >= p.n) break;
       const int si = j % sp.depth;
       SpecSlot *sl = sp.slots + si;
-      int my_e0 = e0;
       spec_node<CPL, U>(I, p, sp, j, si, my_e0, j + 1);  // ends with a barrier: the sh_ words may be rewritten
+      if (repair && tid == 0) atomicAdd(&S->n_repaired, 1ull);
+      repair = false;
       // This worker's next ticket is a window away, so until node j is taken it has nothing better to do than to keep the
       // speculation current: if a commit has meanwhile written a list it read, run it again now, off the committer's
       // path.  (The committer's own test stays the one that counts.)
@@ -282,11 +296,13 @@ __global__ void __launch_bounds__(INS_THREADS) spec_insert_kernel(MutGraph g, In
         }
         __syncthreads();
         const int mine = sh_ok;
-        my_e0 = sh_e0;
+        const int e0n = sh_e0;
         __syncthreads();
-        if (!mine) break;
-        spec_node<CPL, U>(I, p, sp, j, si, my_e0, j + 1);
-        if (tid == 0) atomicAdd(&S->n_repaired, 1ull);
+        if (mine) {
+          my_e0 = e0n;
+          repair = true;
+        }
+        break;
       }
     }
     return;
@@ -338,7 +354,7 @@ __global__ void __launch_bounds__(INS_THREADS) spec_insert_kernel(MutGraph g, In
     __syncthreads();
     SPEC_T(1)
     if (redo) {
-      spec_node<CPL, U>(I, p, sp, j, si, j, -(j + 1));  // head of the order: nothing it reads can be stale
+      spec_node_again<CPL, U>(I, p, sp, j, si, j, -(j + 1));  // head of the order: nothing it reads can be stale
       n_redo++;
       const int status = ldv(&sl->status);
       if (status != 0) {  // the insertion itself fails (graph.go:501-505, visited overflow) or does not fit the overlay
