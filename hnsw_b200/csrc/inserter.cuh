@@ -318,7 +318,8 @@ struct Inserter {
   }
 
   // layerNode.replenish(m) -- graph.go:172-219; always CosineDistance.  Block-wide; ends with a barrier.
-  __device__ void replenish(int layer, int w) {
+  // have_wl: wl[0 .. ctl->wl_len) already holds w's list (the caller has just taken a back-link out of it): no reload.
+  __device__ void replenish(int layer, int w, bool have_wl = false) {
     const int m = p.m, M = g.M;
     __syncthreads();  // every thread has finished reading the control block of the previous step
     for (int i = tid; i < p.rep_cap; i += INS_THREADS) {
@@ -326,7 +327,7 @@ struct Inserter {
       repi[i] = 0x7fffffff;
     }
     if (warp == 0) {
-      int deg = warp_load_list<SPEC>(rlist(layer, w), M, wl, lane);
+      int deg = have_wl ? ctl->wl_len : warp_load_list<SPEC>(rlist(layer, w), M, wl, lane);
       if (lane == 0) {
         ctl->wl_len = deg;
         ctl->flag = deg < m;  // graph.go:173-175
@@ -583,10 +584,11 @@ struct Inserter {
       int dw = warp_load_list<SPEC>(rlist(layer, worst), M, wl, lane);
       int nd = warp_list_remove(wl, dw, n, lane);
       if (nd != dw) warp_store_list(wlist(layer, worst), M, wl, nd, lane);
+      if (lane == 0) ctl->wl_len = nd;  // replenish continues on this copy
     }
     __syncthreads();
     K2_T(3)
-    replenish(layer, worst);  // graph.go:79
+    replenish(layer, worst, true);  // graph.go:79
   }
 
   // The new node's side of graph.go:516-520 (newNode.addNeighbor(node)): its list on this layer starts empty and, as long
