@@ -1,15 +1,17 @@
 // insert_kernel.cu -- K2: Graph.Add / Graph.BatchAdd (graph.go:437-531, 942-1042) with the reference's exact
-// sequential semantics: nodes are inserted one after the other, each seeing every link of its predecessors.
+// sequential semantics, one node at a time: nodes are inserted one after the other, each seeing every link of its
+// predecessors; K2d: Graph.Delete / BatchDelete; and the host entry points of both (b200hnsw_add_batch also drives the
+// speculative windowed schedule of spec_insert.cu, which builds the same graph).
 //
-// One persistent CTA walks the batch in input order.  Per node and per layer (top -> 0):
-//   warp 0   : layerNode.search(k=M, ef) from the elevator -- the same device function as K1 (layer_search.cuh)
-//   all warps: for every result in heap-array order, addNeighbor both ways (graph.go:516-520):
-//              sorted insert; on overflow the M+1 distances of the eviction scan (graph.go:60-71) are evaluated
-//              one per warp, the worst is dropped with its back-link, and replenish (graph.go:172-219) scores
-//              the neighbours-of-neighbours with CosineDistance, all warps gathering rows in parallel.
+// One persistent CTA walks the batch in input order.  Per node and per layer (top -> 0), all in inserter.cuh:
+//   block_layer_search : layerNode.search(k=M, ef) from the elevator, the block evaluating an expansion's rows together
+//   add_neighbor / add_own : for every result in heap-array order, addNeighbor both ways (graph.go:516-520):
+//              sorted insert; on overflow the M+1 distances of the eviction scan (graph.go:60-71) across the warps,
+//              the worst is dropped with its back-link, and replenish (graph.go:172-219) scores the
+//              neighbours-of-neighbours with CosineDistance, all warps gathering rows in parallel.
 // Order-dependent decisions (scan order, tie rule `d > worst || worst == nil`, heap pop order) are taken by one
-// thread over the values the warps produced, so the result equals the oracle's bit for bit.
-// Bound: latency of dependent gathers (serial dependency between insertions), not bandwidth.
+// thread / one warp over the values the warps produced, so the result equals the oracle's bit for bit.
+// Bound: latency of dependent gathers (~290 round trips per insertion), not bandwidth.
 #include <algorithm>
 #include <cstring>
 #include <vector>
