@@ -156,7 +156,7 @@ class Graph {
     if (this != &o) {
       close();
       Distance = o.Distance, Rng = std::move(o.Rng), M = o.M, Ml = o.Ml, EfSearch = o.EfSearch, Device = o.Device;
-      h_ = o.h_, dim_ = o.dim_, max_m_ = o.max_m_;
+      h_ = o.h_, dim_ = o.dim_, max_m_ = o.max_m_, add_window_ = o.add_window_;
       keys_ = std::move(o.keys_), row_of_ = std::move(o.row_of_), retired_ = std::move(o.retired_);
       vecs_ = std::move(o.vecs_);
       o.h_ = nullptr;
@@ -208,6 +208,7 @@ class Graph {
     b200hnsw_config cfg{};
     cfg.dim = dim, cfg.max_m = M < B200HNSW_MAX_M ? M : B200HNSW_MAX_M, cfg.device = Device, cfg.capacity = n;
     detail::check(b200hnsw_create(&cfg, &h_));
+    if (add_window_) detail::check(b200hnsw_set_add_window(h_, add_window_));
     dim_ = dim, max_m_ = cfg.max_m;
     detail::check(b200hnsw_load(h_, n, flat.data(), keys.data(), levels.data(), nLayers, entries.data(),
                                 layerSizes.data(), layerRows.data(), layerPtr.data(), layerNbr.data()));
@@ -241,6 +242,14 @@ class Graph {
   void BatchAdd(const std::vector<Node<K>> &nodes) {
     std::unique_lock<std::shared_mutex> lk(mu_);  // graph.go:943: h.mu.Lock()
     add(nodes, 0);
+  }
+  // The SCHEDULE of Add / BatchAdd, never their result (b200hnsw_set_add_window): 0 = chosen from the row count, 1 = one
+  // node at a time, 2..128 = that many insertions speculated in parallel and committed in input order.  Remembered until the
+  // first Add creates the device handle.
+  void SetAddWindow(int window) {
+    std::unique_lock<std::shared_mutex> lk(mu_);
+    add_window_ = window;
+    if (h_) detail::check(b200hnsw_set_add_window(h_, window));
   }
   // the wave-batched construction (b200hnsw_add_batch_waves): the throughput path, NOT the reference's graph
   void BatchAddWaves(const std::vector<Node<K>> &nodes, int64_t waveMax = 4096) {
@@ -332,6 +341,7 @@ class Graph {
   }
 
   b200hnsw_t *h_ = nullptr;
+  int add_window_ = 0;
   int dim_ = 0, max_m_ = 0;
   std::vector<int64_t> keys_;                    // row -> key
   std::unordered_map<int64_t, int32_t> row_of_;  // live key -> row
@@ -359,6 +369,7 @@ class Graph {
       b200hnsw_config cfg{};
       cfg.dim = dim0, cfg.max_m = M < B200HNSW_MAX_M ? M : B200HNSW_MAX_M, cfg.device = Device;
       detail::check(b200hnsw_create(&cfg, &h_));
+      if (add_window_) detail::check(b200hnsw_set_add_window(h_, add_window_));
       dim_ = dim0, max_m_ = cfg.max_m;
     }
     if (M > max_m_)

@@ -122,6 +122,7 @@ static void gpu_tests() {
     }
     auto g = NewGraphWithConfig<int64_t>(M, 0.25, ef, EuclideanDistance);
     g.Rng.emplace((uint64_t)(99 + waves));
+    if (!waves) g.SetAddWindow(6);  // the speculative schedule of the reference-order Add: the same graph (spec_insert.cu)
     if (waves) g.BatchAddWaves(nodes, 256);
     else g.BatchAdd(nodes);
     CHECK(g.Len() == n);

@@ -52,3 +52,17 @@ def test_compute_call_without_a_device_fails_loudly():
     rc = L.b200hnsw_create(C.byref(cfg), C.byref(h))
     assert rc == -3 and h.value is None  # B200HNSW_ERR_CUDA: no CPU fallback
     assert b"" != L.b200hnsw_last_error()
+
+
+def test_add_window_api_without_a_device():
+    """b200hnsw_set_add_window / get_add_window_stats (the schedule of the reference-order Add, include/b200hnsw.h): argument
+    checks and the host mirror's behaviour before a handle exists need no GPU."""
+    import hnsw_b200
+    from hnsw_b200 import _lib
+    L = _lib.lib()
+    assert L.b200hnsw_set_add_window(None, 8) == _lib.ERR_BAD_ARG
+    assert b"set_add_window" in L.b200hnsw_last_error()
+    assert L.b200hnsw_get_add_window_stats(None, None, None, None) == _lib.ERR_BAD_ARG
+    g = hnsw_b200.Graph()
+    g.set_add_window(8)                      # remembered, applied when the first Add creates the handle
+    assert g.add_window_stats() == (0, 0, 0)
